@@ -1,0 +1,186 @@
+/* mdb200.h -- C ABI of the B200-native view-synthesis loss path for Monodepth2.jl.
+ *
+ * This is the only public native surface.  The reference (jumerckx/Monodepth2.jl) has no
+ * FFI: the path is ordinary Julia functions differentiated by Zygote, and the extension
+ * mechanism it already uses is `ChainRulesCore.rrule` (src/Monodepth.jl:28-29,
+ * src/utils.jl:134-145).  Each entry point below replaces the body of one reference
+ * function (cited per entry as file:line under /root/reference); the Julia glue that binds
+ * them with `ccall` + `rrule` is shown in INTEGRATION.md and shipped (unexecuted: no Julia
+ * on the build box) under monodepth2.jl_b200/julia/.
+ *
+ * Conventions
+ *  - All array arguments are DEVICE pointers to dense float32 data in Julia column-major
+ *    order (first Julia dimension fastest): images (W,H,C,N), frame stacks (W,H,C,L,N),
+ *    disparities (w,h,1,N), rvec (3,N), tvec (3,1,N), rotation stacks (3,3,N).
+ *    `K` / `invK` are HOST pointers to 9 floats, column-major 3x3 (as Julia stores them).
+ *  - Pixel coordinates are 1-based inside the math, as in the reference.
+ *  - Every call only ENQUEUES work on `stream` (a cudaStream_t passed as void*); nothing
+ *    synchronises the device.  The caller owns every buffer, including the workspace.
+ *  - Return value: 0 = OK; negative = MDB_E_* (invalid argument / shape / state);
+ *    positive = a cudaError_t passed through.  `mdb_last_error` describes the last
+ *    failure on a handle.  Nothing throws across the ABI.  There is NO CPU fallback: on a
+ *    machine without a usable CUDA device `mdb_create` fails.
+ */
+#ifndef MDB200_H
+#define MDB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* every entry point below is exported with default visibility; the library is built with
+ * -fvisibility=hidden so nothing else leaks */
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)
+#endif
+
+#define MDB_VERSION 100 /* 0.1.0 */
+
+#define MDB_OK 0
+#define MDB_E_INVALID_ARG (-1)   /* null pointer, non-positive size, unsupported C / S / Ls */
+#define MDB_E_SHAPE (-2)         /* W,H < 2 (reflect pad needs 2), scale larger than target */
+#define MDB_E_WORKSPACE (-3)     /* workspace pointer null / too small / misaligned */
+#define MDB_E_NO_DEVICE (-4)     /* no CUDA device, or device is not sm_100 */
+#define MDB_E_INTERNAL (-5)
+
+#define MDB_MAX_SCALES 8
+#define MDB_MAX_SOURCES 2
+
+typedef struct mdb_handle mdb_handle; /* opaque; caches device properties + TMA encoder */
+
+/* ---- handle ------------------------------------------------------------------------ */
+int32_t mdb_version(void);
+int32_t mdb_create(mdb_handle** out, int32_t device);
+int32_t mdb_destroy(mdb_handle* h);
+const char* mdb_last_error(const mdb_handle* h); /* valid until the next failing call */
+/* number of kernels launched through this handle since creation (bench "gpu_launches") */
+int64_t mdb_launch_count(const mdb_handle* h);
+
+/* ---- parameters of the loss ---------------------------------------------------------- */
+typedef struct mdb_loss_params {
+  float min_depth;            /* Params.min_depth            src/Monodepth.jl:38 (0.1)   */
+  float max_depth;            /* Params.max_depth            src/Monodepth.jl:39 (100)   */
+  float disparity_smoothness; /* Params.disparity_smoothness src/Monodepth.jl:40 (1e-3)  */
+  float alpha;                /* photometric_loss alpha      src/training.jl:2   (0.85)  */
+  float ssim_c1;              /* SSIM c1 = 0.01^2            src/utils.jl:23            */
+  float ssim_c2;              /* SSIM c2 = 0.03^2            src/utils.jl:23            */
+  int32_t automasking;        /* Params.automasking          src/training.jl:60-62      */
+  int32_t normalize_disparity;/* 1: train_loss (src/training.jl:64-65); 0: slow_depth   */
+  int32_t smooth_weight_mode; /* 0: disparity_smoothness*scale[k] (src/training.jl:66-67)
+                                 1: weight 1 (src/simple_depth.jl:39)                    */
+  int32_t upsample_align_corners; /* NNlib upsample_bilinear default = 1 (unpinned)      */
+  int32_t n_global;           /* batch size the means divide by; 0 = N (single GPU)      */
+  int32_t reserved;
+} mdb_loss_params;
+
+void mdb_loss_params_default(mdb_loss_params* p);
+
+/* ---- P2-P4: so3 / pose  (src/utils.jl:106-145, 185-192) ------------------------------ */
+/* hat(rvec): (3,N) -> (3,3,N)                                   src/utils.jl:123-132 */
+int32_t mdb_hat(mdb_handle* h, const float* rvec, int32_t N, float* S, void* stream);
+/* rrule(hat) pullback: d (3,3,N) -> d_rvec (3,N)                 src/utils.jl:134-145 */
+int32_t mdb_hat_pullback(mdb_handle* h, const float* d, int32_t N, float* d_rvec, void* stream);
+/* so3_exp_map(rvec): (3,N) -> (3,3,N)                            src/utils.jl:106-121 */
+int32_t mdb_so3_exp_map(mdb_handle* h, const float* rvec, int32_t N, float* R, void* stream);
+/* composeT(rvec, t, invert) -> R (3,3,N), t (3,1,N)              src/utils.jl:185-192 */
+int32_t mdb_compose_T(mdb_handle* h, const float* rvec, const float* tvec, int32_t invert,
+                      int32_t N, float* R, float* t, void* stream);
+/* pullback of composeT: (dR, dt) -> (d_rvec, d_tvec)                                    */
+int32_t mdb_compose_T_bwd(mdb_handle* h, const float* rvec, const float* tvec, int32_t invert,
+                          int32_t N, const float* dR, const float* dt, float* d_rvec,
+                          float* d_tvec, void* stream);
+
+/* ---- P5-P8: depth / backproject / project / sample ---------------------------------- */
+/* disparity_to_depth, elementwise over n values                  src/utils.jl:179-183 */
+int32_t mdb_disparity_to_depth(mdb_handle* h, const float* disparity, int64_t n, float min_depth,
+                               float max_depth, float* depth, void* stream);
+/* (b::Backproject)(depth (1,WH,N), invK) -> points (3,WH,N)      src/utils.jl:45-69   */
+int32_t mdb_backproject(mdb_handle* h, const float* depth, const float* invK, int32_t W,
+                        int32_t H, int32_t N, float* points, void* stream);
+/* (p::Project)(points, K, R, t) -> normalised uv (2,WH,N)        src/utils.jl:71-103  */
+int32_t mdb_project(mdb_handle* h, const float* points, const float* K, const float* R,
+                    const float* t, int32_t W, int32_t H, int32_t N, float* uv, void* stream);
+/* NNlib grid_sample(input (W,H,C,N), grid (2,Wo,Ho,N); padding_mode=:border),
+ * align-corners=true                          call sites src/training.jl:56, src/render.jl:88 */
+int32_t mdb_grid_sample(mdb_handle* h, const float* input, const float* grid, int32_t W,
+                        int32_t H, int32_t C, int32_t N, int32_t Wo, int32_t Ho, float* out,
+                        void* stream);
+/* warp(disp, x, Ps, ...; source_ids): called at src/simple_depth.jl:30-32, undefined in the
+ * fork; semantics = the inlined body at src/training.jl:48-57.  disp (1,W,H,N) full res,
+ * x (W,H,C,L,N), R[s] (3,3,N), t[s] (3,1,N) -> warped[s] (W,H,C,N)                       */
+int32_t mdb_warp(mdb_handle* h, const float* disp, const float* x, const float* const* R,
+                 const float* const* t, const int32_t* source_ids, int32_t S, const float* K,
+                 const float* invK, int32_t W, int32_t H, int32_t C, int32_t L, int32_t N,
+                 float min_depth, float max_depth, float* const* warped, void* stream);
+
+/* ---- P9-P11: SSIM / photometric / min-reprojection / automask ------------------------ */
+/* (ssim::SSIM)(x, y) -> (W,H,C,N)                                src/utils.jl:17-43   */
+int32_t mdb_ssim(mdb_handle* h, const float* x, const float* y, int32_t W, int32_t H, int32_t C,
+                 int32_t N, float c1, float c2, float* out, void* stream);
+/* photometric_loss(ssim, predicted, target; alpha) -> (W,H,1,N)  src/training.jl:1-7  */
+int32_t mdb_photometric_loss(mdb_handle* h, const float* predicted, const float* target,
+                             int32_t W, int32_t H, int32_t C, int32_t N, float alpha, float c1,
+                             float c2, float* out, void* stream);
+/* prediction_loss(ssim, predictions, target) -> (W,H,1,N)        src/training.jl:13-15 */
+int32_t mdb_prediction_loss(mdb_handle* h, const float* const* predictions, int32_t S,
+                            const float* target, int32_t W, int32_t H, int32_t C, int32_t N,
+                            float alpha, float c1, float c2, float* out, void* stream);
+/* automasking_loss(ssim, inputs (W,H,C,L,N), target; source_ids) src/training.jl:9-11 */
+int32_t mdb_automasking_loss(mdb_handle* h, const float* x, int32_t target_id,
+                             const int32_t* source_ids, int32_t S, int32_t W, int32_t H,
+                             int32_t C, int32_t L, int32_t N, float alpha, float c1, float c2,
+                             float* out, void* stream);
+/* _apply_mask(mask, warp_loss): elementwise min over n values    src/training.jl:17-19 */
+int32_t mdb_apply_mask(mdb_handle* h, const float* mask, const float* warp_loss, int64_t n,
+                       float* out, void* stream);
+
+/* ---- S1-S2: smoothness  (src/utils.jl:163-177) ---------------------------------------- */
+/* smooth_loss(disparity (W,H,N), image (W,H,C,N)) -> scalar *loss (device); if d_disparity
+ * is non-null also writes d loss / d disparity (W,H,N).  Deterministic (no float atomics).
+ * workspace: mdb_smooth_loss_workspace_bytes(W,H,N) bytes, 256-byte aligned.              */
+size_t mdb_smooth_loss_workspace_bytes(int32_t W, int32_t H, int32_t N);
+int32_t mdb_smooth_loss(mdb_handle* h, const float* disparity, const float* image, int32_t W,
+                        int32_t H, int32_t C, int32_t N, float* loss, float* d_disparity,
+                        void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- P12: the fused hot path  (src/training.jl:21-78; src/simple_depth.jl:25-41) ------ */
+typedef struct mdb_loss_io {
+  /* inputs */
+  const float* x;                 /* frame stack (W,H,C,L,N)                             */
+  int32_t W, H, C, L, N;
+  int32_t target_id;              /* 1-based, cache.target_id                            */
+  int32_t S;                      /* number of sources (<= MDB_MAX_SOURCES)              */
+  int32_t source_ids[MDB_MAX_SOURCES]; /* 1-based, cache.source_ids                     */
+  int32_t invert[MDB_MAX_SOURCES];     /* source_id < target_id, src/training.jl:28     */
+  const float* rvec[MDB_MAX_SOURCES];  /* Pose.rvec (3,N)                               */
+  const float* tvec[MDB_MAX_SOURCES];  /* Pose.tvec (3,1,N)                             */
+  int32_t Ls;                     /* number of scales (<= MDB_MAX_SCALES)                */
+  const float* disparity[MDB_MAX_SCALES]; /* (w_k,h_k,1,N), native resolution           */
+  int32_t dw[MDB_MAX_SCALES], dh[MDB_MAX_SCALES];
+  float scale[MDB_MAX_SCALES];    /* cache.scales                                        */
+  const float* auto_loss;         /* (W,H,1,N) identity-reprojection loss or NULL        */
+  float K[9], invK[9];            /* column-major 3x3                                     */
+  /* outputs */
+  float* loss;                    /* 1 float: loss / Ls summed over the LOCAL items      */
+  float* d_disparity[MDB_MAX_SCALES]; /* d loss / d disparity[k], native resolution     */
+  float* d_rvec[MDB_MAX_SOURCES]; /* (3,N)                                               */
+  float* d_tvec[MDB_MAX_SOURCES]; /* (3,1,N)                                             */
+  float* vis_warp_loss;           /* optional (W,H,1,N): warp_loss of the last scale     */
+} mdb_loss_io;
+
+size_t mdb_train_loss_workspace_bytes(const mdb_loss_io* io);
+/* train_loss value AND gradient in one pass (forward of the rrule; the pullback scales the
+ * cached gradients by the incoming scalar cotangent).                                    */
+int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_loss_params* p,
+                              void* workspace, size_t workspace_bytes, void* stream);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+#ifdef __cplusplus
+}
+#endif
+#endif /* MDB200_H */

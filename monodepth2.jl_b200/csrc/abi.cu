@@ -1,0 +1,62 @@
+// abi.cu -- handle life-cycle and error reporting of the C ABI (include/mdb200.h).
+#include "mdb_common.cuh"
+
+extern "C" {
+
+int32_t mdb_version(void) { return MDB_VERSION; }
+
+int32_t mdb_create(mdb_handle** out, int32_t device) {
+  if (!out) return MDB_E_INVALID_ARG;
+  *out = nullptr;
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count <= 0 || device < 0 || device >= count) {
+    (void)cudaGetLastError();
+    return MDB_E_NO_DEVICE;  // no CPU fallback exists
+  }
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return MDB_E_NO_DEVICE;
+  if (prop.major != 10) return MDB_E_NO_DEVICE;  // the library only contains sm_100a code
+  mdb_handle* h = new mdb_handle();
+  h->device = device;
+  h->num_sms = prop.multiProcessorCount;
+  h->cc_major = prop.major;
+  h->cc_minor = prop.minor;
+  h->smem_optin = prop.sharedMemPerBlockOptin;
+  // driver entry point for TMA descriptors (no link-time dependency on libcuda)
+  cudaDriverEntryPointQueryResult qres;
+  void* fn = nullptr;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) == cudaSuccess &&
+      qres == cudaDriverEntryPointSuccess)
+    h->encode_tiled = fn;
+  (void)cudaGetLastError();
+  *out = h;
+  return MDB_OK;
+}
+
+int32_t mdb_destroy(mdb_handle* h) {
+  delete h;
+  return MDB_OK;
+}
+
+const char* mdb_last_error(const mdb_handle* h) { return h ? h->err : "null handle"; }
+
+int64_t mdb_launch_count(const mdb_handle* h) { return h ? h->launches : 0; }
+
+void mdb_loss_params_default(mdb_loss_params* p) {
+  if (!p) return;
+  p->min_depth = 0.1f;
+  p->max_depth = 100.0f;
+  p->disparity_smoothness = 1e-3f;
+  p->alpha = 0.85f;
+  p->ssim_c1 = 0.01f * 0.01f;
+  p->ssim_c2 = 0.03f * 0.03f;
+  p->automasking = 1;
+  p->normalize_disparity = 1;
+  p->smooth_weight_mode = 0;
+  p->upsample_align_corners = 1;
+  p->n_global = 0;
+  p->reserved = 0;
+}
+
+}  // extern "C"

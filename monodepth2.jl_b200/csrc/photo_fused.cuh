@@ -1,0 +1,157 @@
+// photo_fused.cuh -- argument blocks and shared device math of the fused photometric path.
+#pragma once
+#include "mdb_common.cuh"
+
+// ---- tile geometry of the fused kernel ------------------------------------------------
+// One CTA owns a TW x TH block of target pixels.  SSIM windows need warped samples one
+// pixel around every window centre, and the backward pass needs windows one pixel around
+// every interior pixel, so warped samples are produced on the tile + 2 pixel halo (R2) and
+// window statistics on the tile + 1 pixel halo (R1).
+constexpr int TW = 32, TH = 16;
+constexpr int R2W = TW + 4, R2H = TH + 4, R2N = R2W * R2H;  // 36 x 20
+constexpr int R1W = TW + 2, R1H = TH + 2, R1N = R1W * R1H;  // 34 x 18
+constexpr int FUSED_THREADS = 256;
+constexpr int NPOSE = 12;  // dL/dA (9) + dL/db (3) per (item, source)
+
+// Per (item, source) projection constants produced by pose_prep_kernel:
+//   P = depth * (A q) + b,  q = [w, h, 1],  A = K R' invK,  b = K t'   (src/utils.jl:67-69,99-103
+//   with K (R X + t) pre-composed).  dA = A - I is stored so the pixel *displacement* can be
+//   computed without cancellation (see project_flow).
+struct PosePrep {
+  float dA[9];  // row-major
+  float b[3];
+};
+
+struct ScaleStat {
+  float inv_mp;  // 1 / (mean(disparity) + 1e-7), or 1 when the disparity is not normalised
+  float cconst;  // constant added to every full-res disparity gradient (mean-normalisation term)
+  float loss;    // this (scale, item)'s smoothness loss, all weights applied
+  float pad;
+};
+
+struct FusedArgs {
+  const float* x;
+  int W, H, L, N;
+  int tgt;                      // 0-based frame index of the target
+  int src[MDB_MAX_SOURCES];     // 0-based frame indices of the sources
+  int Ls;
+  const float* disp[MDB_MAX_SCALES];
+  int dw[MDB_MAX_SCALES], dh[MDB_MAX_SCALES];
+  float rx[MDB_MAX_SCALES], ry[MDB_MAX_SCALES];  // (w_k-1)/(W-1), (h_k-1)/(H-1)
+  int native[MDB_MAX_SCALES];
+  float* gout[MDB_MAX_SCALES];  // full-res disparity gradient target (output or workspace)
+  float kx[MDB_MAX_SCALES], ky[MDB_MAX_SCALES];  // smoothness weights incl. 1/Ls and the means
+  const float* auto_loss;
+  float mind, dd;               // 1/max_depth, 1/min_depth - 1/max_depth
+  float alpha, c1, c2;
+  int automask;
+  float up;                     // 1 / (W H N_global Ls)
+  const PosePrep* pp;           // [N][S]
+  const ScaleStat* stats;       // [Ls][N]
+  float* partials;              // [N][tiles][1 + NPOSE*S]
+  float* vis;
+  int tiles_x, tiles_y;
+};
+
+#ifdef __CUDACC__
+// bilinear upsample (align-corners) of a native disparity map at the 0-based full-res pixel
+// (gx, gy); mirrors NNlib upsample_bilinear / torch interpolate(align_corners=True).
+MDB_DEV float upsample_at(const float* __restrict__ d, int dw, int dh, float rx, float ry, int gx,
+                          int gy) {
+  const float fx = (float)gx * rx, fy = (float)gy * ry;
+  int x0 = (int)fx, y0 = (int)fy;
+  x0 = min(x0, dw - 1);
+  y0 = min(y0, dh - 1);
+  const float lx = fx - (float)x0, ly = fy - (float)y0;
+  const int x1 = min(x0 + 1, dw - 1), y1 = min(y0 + 1, dh - 1);
+  const float v00 = ldg(d + (size_t)y0 * dw + x0), v01 = ldg(d + (size_t)y0 * dw + x1);
+  const float v10 = ldg(d + (size_t)y1 * dw + x0), v11 = ldg(d + (size_t)y1 * dw + x1);
+  const float top = v00 + lx * (v01 - v00), bot = v10 + lx * (v11 - v10);
+  return top + ly * (bot - top);
+}
+
+// the same interpolation weights, for the transposed (backward) gather
+MDB_DEV void upsample_coords(int g, float r, int dn, int& i0, int& i1, float& l) {
+  const float f = (float)g * r;
+  i0 = min((int)f, dn - 1);
+  l = f - (float)i0;
+  i1 = min(i0 + 1, dn - 1);
+}
+
+struct Proj {
+  float fu, fv;    // displacement (u - w, v - h) of the projected point, unclamped
+  float zinv;      // 1 / (P3 + 1e-7)
+  float aq0, aq1, aq2;  // A q
+};
+
+// Projection of pixel (px, py) (1-based, as floats) at `depth` into a source frame.
+// Reference chain: Backproject (src/utils.jl:67-69) -> Project (src/utils.jl:99-103) ->
+// normalize -> grid_sample's unnormalize, which cancel to the pixel coordinate u = P1/(P3+1e-7).
+// Computed as a displacement:  u - w = (P1 - w z') / z'  with  A = I + dA, so that
+// P1 - w z' = depth (dA1.q - w dA3.q) + b1 - w (b3 + 1e-7): no large terms cancel.
+MDB_DEV Proj project_flow(const PosePrep& pp, float depth, float px, float py) {
+  Proj r;
+  const float d0 = fmaf(pp.dA[0], px, fmaf(pp.dA[1], py, pp.dA[2]));
+  const float d1 = fmaf(pp.dA[3], px, fmaf(pp.dA[4], py, pp.dA[5]));
+  const float d2 = fmaf(pp.dA[6], px, fmaf(pp.dA[7], py, pp.dA[8]));
+  r.aq0 = px + d0;
+  r.aq1 = py + d1;
+  r.aq2 = 1.0f + d2;
+  const float b3e = pp.b[2] + 1e-7f;
+  const float z = fmaf(depth, r.aq2, b3e);
+  r.zinv = 1.0f / z;
+  const float nu = fmaf(depth, fmaf(-px, d2, d0), fmaf(-px, b3e, pp.b[0]));
+  const float nv = fmaf(depth, fmaf(-py, d2, d1), fmaf(-py, b3e, pp.b[1]));
+  r.fu = nu * r.zinv;
+  r.fv = nv * r.zinv;
+  return r;
+}
+
+struct Taps {
+  int o00, o01, o10, o11;  // offsets inside one channel plane
+  float fx, fy;            // fractional weights
+  float mx, my;            // 1 if the coordinate was not clamped (gradient flows), else 0
+};
+
+// NNlib grid_sample(padding_mode=:border), align-corners=true, composed with `normalize`:
+// sample position = clamp(u, 1, W) (1-based).  Gradient is zero where clamped.
+MDB_DEV Taps make_taps(float fu, float fv, int gx, int gy, int W, int H) {
+  Taps t;
+  const float lox = -(float)gx, hix = (float)(W - 1 - gx);
+  const float loy = -(float)gy, hiy = (float)(H - 1 - gy);
+  t.mx = (fu > lox && fu < hix) ? 1.0f : 0.0f;
+  t.my = (fv > loy && fv < hiy) ? 1.0f : 0.0f;
+  const float cu = fminf(fmaxf(fu, lox), hix), cv = fminf(fmaxf(fv, loy), hiy);
+  const float flx = floorf(cu), fly = floorf(cv);
+  t.fx = cu - flx;
+  t.fy = cv - fly;
+  const int x0 = gx + (int)flx, y0 = gy + (int)fly;
+  const int x1 = min(x0 + 1, W - 1), y1 = min(y0 + 1, H - 1);
+  t.o00 = y0 * W + x0; t.o01 = y0 * W + x1;
+  t.o10 = y1 * W + x0; t.o11 = y1 * W + x1;
+  return t;
+}
+
+// SSIM of one 3x3 window from its five raw sums, plus the coefficients of its pullback:
+//   d s / d x_p = (m_pq / 9) (A + 2 x_p B + y_p C).   Reference: src/utils.jl:29-43.
+MDB_DEV float ssim_window(float Sx, float Sy, float Sxx, float Syy, float Sxy, float c1, float c2,
+                          float& A, float& B, float& C) {
+  const float k = 1.0f / 9.0f;
+  const float mx = Sx * k, my = Sy * k;
+  const float sx = fmaf(Sxx, k, -mx * mx), sy = fmaf(Syy, k, -my * my), sxy = fmaf(Sxy, k, -mx * my);
+  const float n1 = fmaf(2.0f * mx, my, c1), n2 = fmaf(2.0f, sxy, c2);
+  const float d1 = fmaf(mx, mx, fmaf(my, my, c1)), d2 = sx + sy + c2;
+  const float n = n1 * n2, d = d1 * d2;
+  const float dinv = 1.0f / d;
+  const float raw = (1.0f - n * dinv) * 0.5f;
+  const bool inside = (raw >= 0.0f) && (raw <= 1.0f);
+  const float dn = inside ? -0.5f * dinv : 0.0f;      // ds/dn
+  const float ddn = inside ? 0.5f * n * dinv * dinv : 0.0f;  // ds/dd
+  A = dn * 2.0f * my * (n2 - n1) + ddn * 2.0f * mx * (d2 - d1);
+  B = ddn * d1;
+  C = dn * 2.0f * n1;
+  return fminf(fmaxf(raw, 0.0f), 1.0f);
+}
+
+MDB_DEV float sgnf(float v) { return (float)((v > 0.0f) - (v < 0.0f)); }
+#endif

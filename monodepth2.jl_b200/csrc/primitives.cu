@@ -1,0 +1,383 @@
+// primitives.cu -- un-fused entry points that mirror the reference's fine-grained functions
+// (P5-P11, P13, S2 of SURVEY 8a).  They exist so that every function the reference's tests
+// and drivers call by name has a device implementation behind the C ABI; the training hot
+// path uses the fused kernel in photo_fused.cu instead.
+#include "photo_fused.cuh"
+
+namespace {
+
+inline int nblk(int64_t n, int b) { return (int)((n + b - 1) / b); }
+
+// disparity_to_depth -- src/utils.jl:179-183
+__global__ void d2d_kernel(const float* __restrict__ d, int64_t n, float mind, float dd, float* __restrict__ out) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = 1.0f / fmaf(d[i], dd, mind);
+}
+
+struct Mat3 { float m[9]; };  // math row-major
+
+// Backproject -- src/utils.jl:45-69: points(:, w + (h-1) W, n) = depth * invK [w, h, 1]
+__global__ void backproject_kernel(const float* __restrict__ depth, Mat3 iK, int W, int H, int N,
+                                   float* __restrict__ pts) {
+  const int64_t total = (int64_t)W * H * N;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int pix = (int)(i % ((int64_t)W * H));
+    const float w = (float)(pix % W + 1), hh = (float)(pix / W + 1);
+    const float d = depth[i];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) pts[3 * i + r] = d * (iK.m[3 * r] * w + iK.m[3 * r + 1] * hh + iK.m[3 * r + 2]);
+  }
+}
+
+// Project + normalize -- src/utils.jl:71-103
+__global__ void project_kernel(const float* __restrict__ pts, Mat3 K, const float* __restrict__ R,
+                               const float* __restrict__ t, int W, int H, int N, float* __restrict__ uv) {
+  const int64_t wh = (int64_t)W * H, total = wh * N;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int n = (int)(i / wh);
+    const float* Rn = R + 9 * n;  // column-major: R[i][j] at j*3+i
+    const float X0 = pts[3 * i], X1 = pts[3 * i + 1], X2 = pts[3 * i + 2];
+    float Y[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) Y[r] = Rn[r] * X0 + Rn[3 + r] * X1 + Rn[6 + r] * X2 + t[3 * n + r];
+    float P[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) P[r] = K.m[3 * r] * Y[0] + K.m[3 * r + 1] * Y[1] + K.m[3 * r + 2] * Y[2];
+    const float den = 1.0f / (P[2] + 1e-7f);
+    uv[2 * i] = (((P[0] * den) - 1.0f) / (float)(W - 1) - 0.5f) * 2.0f;
+    uv[2 * i + 1] = (((P[1] * den) - 1.0f) / (float)(H - 1) - 0.5f) * 2.0f;
+  }
+}
+
+// NNlib grid_sample (bilinear, :border, align-corners=true): input (W,H,C,N), grid (2,Wo,Ho,N)
+__global__ void grid_sample_kernel(const float* __restrict__ in, const float* __restrict__ grid, int W, int H,
+                                   int C, int N, int Wo, int Ho, float* __restrict__ out) {
+  const int64_t who = (int64_t)Wo * Ho, total = who * N;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int n = (int)(i / who);
+    const int64_t pix = i % who;
+    float ix = (grid[2 * i] + 1.0f) * 0.5f * (float)(W - 1);   // 0-based
+    float iy = (grid[2 * i + 1] + 1.0f) * 0.5f * (float)(H - 1);
+    ix = fminf(fmaxf(ix, 0.0f), (float)(W - 1));
+    iy = fminf(fmaxf(iy, 0.0f), (float)(H - 1));
+    const float fx0 = floorf(ix), fy0 = floorf(iy);
+    const float fx = ix - fx0, fy = iy - fy0;
+    const int x0 = (int)fx0, y0 = (int)fy0, x1 = min(x0 + 1, W - 1), y1 = min(y0 + 1, H - 1);
+    for (int c = 0; c < C; ++c) {
+      const float* p = in + ((size_t)n * C + c) * W * H;
+      const float v00 = p[y0 * W + x0], v01 = p[y0 * W + x1], v10 = p[y1 * W + x0], v11 = p[y1 * W + x1];
+      const float top = fmaf(fx, v01 - v00, v00), bot = fmaf(fx, v11 - v10, v10);
+      out[((size_t)n * C + c) * who + pix] = fmaf(fy, bot - top, top);
+    }
+  }
+}
+
+// warp (P13): disparity -> depth -> backproject -> project -> sample, per source.
+struct WarpArgs {
+  const float* disp; const float* x; float* out[MDB_MAX_SOURCES];
+  PosePrep pp_unused;
+  const PosePrep* pp; int src[MDB_MAX_SOURCES];
+  int S, W, H, C, L, N; float mind, dd;
+};
+
+__global__ void warp_kernel(WarpArgs a) {
+  const int64_t wh = (int64_t)a.W * a.H, total = wh * a.N;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int n = (int)(i / wh);
+    const int pix = (int)(i % wh), gx = pix % a.W, gy = pix / a.W;
+    const float depth = 1.0f / fmaf(a.disp[i], a.dd, a.mind);
+    for (int s = 0; s < a.S; ++s) {
+      const Proj pr = project_flow(a.pp[n * a.S + s], depth, (float)(gx + 1), (float)(gy + 1));
+      const Taps t = make_taps(pr.fu, pr.fv, gx, gy, a.W, a.H);
+      for (int c = 0; c < a.C; ++c) {
+        const float* p = a.x + (((size_t)n * a.L + a.src[s]) * a.C + c) * wh;
+        const float v00 = p[t.o00], v01 = p[t.o01], v10 = p[t.o10], v11 = p[t.o11];
+        const float top = fmaf(t.fx, v01 - v00, v00), bot = fmaf(t.fx, v11 - v10, v10);
+        a.out[s][((size_t)n * a.C + c) * wh + pix] = fmaf(t.fy, bot - top, top);
+      }
+    }
+  }
+}
+
+// pose constants from already-composed (R, t) (Julia layout), for mdb_warp
+struct WarpPoseArgs { const float* R[MDB_MAX_SOURCES]; const float* t[MDB_MAX_SOURCES]; double K[9], invK[9]; int N, S; };
+__global__ void warp_pose_kernel(WarpPoseArgs a, PosePrep* __restrict__ out) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= a.N * a.S) return;
+  const int n = idx / a.S, s = idx % a.S;
+  double R[9], KR[9], A[9];
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) R[3 * i + j] = a.R[s][9 * n + 3 * j + i];
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) { double v = 0; for (int k = 0; k < 3; ++k) v += a.K[3 * i + k] * R[3 * k + j]; KR[3 * i + j] = v; }
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) { double v = 0; for (int k = 0; k < 3; ++k) v += KR[3 * i + k] * a.invK[3 * k + j]; A[3 * i + j] = v; }
+  PosePrep p;
+  for (int k = 0; k < 9; ++k) p.dA[k] = (float)(A[k] - ((k % 4 == 0) ? 1.0 : 0.0));
+  for (int i = 0; i < 3; ++i) {
+    double v = 0; for (int k = 0; k < 3; ++k) v += a.K[3 * i + k] * (double)a.t[s][3 * n + k];
+    p.b[i] = (float)v;
+  }
+  out[idx] = p;
+}
+
+// ---- SSIM / photometric, one thread per output pixel ----------------------------------
+// mode 0: write SSIM per channel (W,H,C,N); mode 1: photometric loss (W,H,1,N);
+// mode 2: min over S predictions of the photometric loss (W,H,1,N)
+struct PhotoArgs {
+  const float* pred[4]; int64_t pred_nstride[4];  // per-item stride of each prediction
+  const float* target; int64_t tgt_nstride;
+  int S, W, H, C, N, mode; float alpha, c1, c2; float* out;
+};
+
+__device__ float photo_pixel(const float* __restrict__ x, const float* __restrict__ y, int gx, int gy, int W, int H,
+                             int C, float alpha, float c1, float c2, float* ssim_out, int64_t ssim_cstride) {
+  const size_t plane = (size_t)W * H;
+  int cx[3], ry[3];
+  for (int k = 0; k < 3; ++k) { cx[k] = reflect1(gx + k, W) - 1; ry[k] = (reflect1(gy + k, H) - 1) * W; }
+  float ls = 0.0f, l1 = 0.0f;
+  for (int c = 0; c < C; ++c) {
+    float Sx = 0, Sy = 0, Sxx = 0, Syy = 0, Sxy = 0;
+    for (int k = 0; k < 9; ++k) {
+      const float xv = x[c * plane + ry[k / 3] + cx[k % 3]], yv = y[c * plane + ry[k / 3] + cx[k % 3]];
+      Sx += xv; Sy += yv; Sxx = fmaf(xv, xv, Sxx); Syy = fmaf(yv, yv, Syy); Sxy = fmaf(xv, yv, Sxy);
+    }
+    float A, B, Cc;
+    const float s = ssim_window(Sx, Sy, Sxx, Syy, Sxy, c1, c2, A, B, Cc);
+    if (ssim_out) ssim_out[c * ssim_cstride] = s;
+    ls += s;
+    l1 += fabsf(y[c * plane + gy * W + gx] - x[c * plane + gy * W + gx]);
+  }
+  return alpha * (ls / C) + (1.0f - alpha) * (l1 / C);
+}
+
+__global__ void photo_kernel(PhotoArgs a) {
+  const int64_t wh = (int64_t)a.W * a.H, total = wh * a.N;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int n = (int)(i / wh);
+    const int pix = (int)(i % wh), gx = pix % a.W, gy = pix / a.W;
+    const float* y = a.target + n * a.tgt_nstride;
+    if (a.mode == 0) {
+      photo_pixel(a.pred[0] + n * a.pred_nstride[0], y, gx, gy, a.W, a.H, a.C, a.alpha, a.c1, a.c2,
+                  a.out + (size_t)n * a.C * wh + pix, wh);
+    } else {
+      float best = 0.0f;
+      for (int s = 0; s < a.S; ++s) {
+        const float v = photo_pixel(a.pred[s] + n * a.pred_nstride[s], y, gx, gy, a.W, a.H, a.C, a.alpha, a.c1,
+                                    a.c2, nullptr, 0);
+        best = (s == 0 || v < best) ? v : best;
+      }
+      a.out[i] = best;
+    }
+  }
+}
+
+__global__ void min2_kernel(const float* __restrict__ a, const float* __restrict__ b, int64_t n, float* __restrict__ out) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = fminf(a[i], b[i]);
+}
+
+// ---- smooth_loss (S2) -- src/utils.jl:163-177 -----------------------------------------
+constexpr int SM_THREADS = 256, SM_ROWS = 8;
+
+__global__ void __launch_bounds__(SM_THREADS)
+smooth_kernel(const float* __restrict__ disp, const float* __restrict__ img, int W, int H, int C, int N,
+              float kx, float ky, float* __restrict__ part, float* __restrict__ grad) {
+  const int n = blockIdx.y, rb = blockIdx.x;
+  const size_t plane = (size_t)W * H;
+  const float* d = disp + n * plane;
+  const float* im = img + (size_t)n * C * plane;
+  const int y0 = rb * SM_ROWS, y1 = min(y0 + SM_ROWS, H);
+  float ax = 0.0f, ay = 0.0f;
+  for (int i = threadIdx.x; i < (y1 - y0) * W; i += SM_THREADS) {
+    const int gy = y0 + i / W, gx = i % W;
+    const size_t o = (size_t)gy * W + gx;
+    const float v = d[o];
+    float g = 0.0f;
+    auto wgt = [&](size_t o0, size_t o1) {
+      float e = 0.0f;
+      for (int c = 0; c < C; ++c) e += fabsf(im[c * plane + o0] - im[c * plane + o1]);
+      return expf(-e / (float)C);
+    };
+    if (gx + 1 < W) { const float df = v - d[o + 1]; const float w = wgt(o, o + 1); ax += fabsf(df) * w; g += kx * sgnf(df) * w; }
+    if (gx > 0) { const float df = d[o - 1] - v; g -= kx * sgnf(df) * wgt(o - 1, o); }
+    if (gy + 1 < H) { const float df = v - d[o + W]; const float w = wgt(o, o + W); ay += fabsf(df) * w; g += ky * sgnf(df) * w; }
+    if (gy > 0) { const float df = d[o - W] - v; g -= ky * sgnf(df) * wgt(o - W, o); }
+    if (grad) grad[n * plane + o] = g;
+  }
+  __shared__ float red[SM_THREADS / 32][2];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  ax = warp_sum(ax); ay = warp_sum(ay);
+  if (lane == 0) { red[warp][0] = ax; red[warp][1] = ay; }
+  __syncthreads();
+  if (threadIdx.x < 2) {
+    float v = 0.0f;
+    for (int w = 0; w < SM_THREADS / 32; ++w) v += red[w][threadIdx.x];
+    part[((size_t)n * gridDim.x + rb) * 2 + threadIdx.x] = v;
+  }
+}
+
+__global__ void smooth_finalize_kernel(const float* __restrict__ part, int count, double kx, double ky,
+                                       float* __restrict__ loss) {
+  __shared__ double red[8];
+  double v = 0.0;
+  for (int i = threadIdx.x; i < count; i += blockDim.x) v += kx * (double)part[2 * i] + ky * (double)part[2 * i + 1];
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(MDB_FULL, v, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) { double s = 0; for (int w = 0; w < (int)(blockDim.x >> 5); ++w) s += red[w]; *loss = (float)s; }
+}
+
+int grid_for(mdb_handle* h, int64_t n, int b) { return (int)min((int64_t)h->num_sms * 16, (n + b - 1) / b); }
+Mat3 to_math(const float* cm) { Mat3 m; for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) m.m[3 * i + j] = cm[3 * j + i]; return m; }
+
+}  // namespace
+
+extern "C" {
+
+int32_t mdb_disparity_to_depth(mdb_handle* h, const float* disparity, int64_t n, float min_depth,
+                               float max_depth, float* depth, void* stream) {
+  MDB_REQUIRE(h, h && disparity && depth && n > 0, MDB_E_INVALID_ARG, "mdb_disparity_to_depth: bad argument");
+  const float mind = 1.0f / max_depth, maxd = 1.0f / min_depth;
+  d2d_kernel<<<grid_for(h, n, 256), 256, 0, (cudaStream_t)stream>>>(disparity, n, mind, maxd - mind, depth);
+  MDB_LAUNCHED(h);
+  return MDB_OK;
+}
+
+int32_t mdb_backproject(mdb_handle* h, const float* depth, const float* invK, int32_t W, int32_t H,
+                        int32_t N, float* points, void* stream) {
+  MDB_REQUIRE(h, h && depth && invK && points && W > 0 && H > 0 && N > 0, MDB_E_INVALID_ARG, "mdb_backproject: bad argument");
+  backproject_kernel<<<grid_for(h, (int64_t)W * H * N, 256), 256, 0, (cudaStream_t)stream>>>(depth, to_math(invK), W, H, N, points);
+  MDB_LAUNCHED(h);
+  return MDB_OK;
+}
+
+int32_t mdb_project(mdb_handle* h, const float* points, const float* K, const float* R, const float* t,
+                    int32_t W, int32_t H, int32_t N, float* uv, void* stream) {
+  MDB_REQUIRE(h, h && points && K && R && t && uv && W > 1 && H > 1 && N > 0, MDB_E_INVALID_ARG, "mdb_project: bad argument");
+  project_kernel<<<grid_for(h, (int64_t)W * H * N, 256), 256, 0, (cudaStream_t)stream>>>(points, to_math(K), R, t, W, H, N, uv);
+  MDB_LAUNCHED(h);
+  return MDB_OK;
+}
+
+int32_t mdb_grid_sample(mdb_handle* h, const float* input, const float* grid, int32_t W, int32_t H,
+                        int32_t C, int32_t N, int32_t Wo, int32_t Ho, float* out, void* stream) {
+  MDB_REQUIRE(h, h && input && grid && out && W > 0 && H > 0 && C > 0 && N > 0 && Wo > 0 && Ho > 0,
+              MDB_E_INVALID_ARG, "mdb_grid_sample: bad argument");
+  grid_sample_kernel<<<grid_for(h, (int64_t)Wo * Ho * N, 256), 256, 0, (cudaStream_t)stream>>>(input, grid, W, H, C, N, Wo, Ho, out);
+  MDB_LAUNCHED(h);
+  return MDB_OK;
+}
+
+int32_t mdb_warp(mdb_handle* h, const float* disp, const float* x, const float* const* R,
+                 const float* const* t, const int32_t* source_ids, int32_t S, const float* K,
+                 const float* invK, int32_t W, int32_t H, int32_t C, int32_t L, int32_t N,
+                 float min_depth, float max_depth, float* const* warped, void* stream) {
+  MDB_REQUIRE(h, h && disp && x && R && t && source_ids && K && invK && warped, MDB_E_INVALID_ARG, "mdb_warp: null argument");
+  MDB_REQUIRE(h, S >= 1 && S <= MDB_MAX_SOURCES && W > 1 && H > 1 && C > 0 && L > 0 && N > 0, MDB_E_SHAPE, "mdb_warp: bad shape");
+  cudaStream_t st = (cudaStream_t)stream;
+  WarpPoseArgs pa{};
+  WarpArgs wa{};
+  pa.N = N; pa.S = S;
+  for (int s = 0; s < S; ++s) {
+    MDB_REQUIRE(h, R[s] && t[s] && warped[s] && source_ids[s] >= 1 && source_ids[s] <= L, MDB_E_INVALID_ARG, "mdb_warp: bad source %d", s);
+    pa.R[s] = R[s]; pa.t[s] = t[s]; wa.out[s] = warped[s]; wa.src[s] = source_ids[s] - 1;
+  }
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) { pa.K[3 * i + j] = K[3 * j + i]; pa.invK[3 * i + j] = invK[3 * j + i]; }
+  PosePrep* pp = nullptr;
+  MDB_CUDA(h, cudaMallocAsync((void**)&pp, sizeof(PosePrep) * N * S, st));
+  warp_pose_kernel<<<nblk(N * S, 128), 128, 0, st>>>(pa, pp);
+  MDB_LAUNCHED(h);
+  wa.disp = disp; wa.x = x; wa.pp = pp; wa.S = S; wa.W = W; wa.H = H; wa.C = C; wa.L = L; wa.N = N;
+  wa.mind = 1.0f / max_depth; wa.dd = 1.0f / min_depth - 1.0f / max_depth;
+  warp_kernel<<<grid_for(h, (int64_t)W * H * N, 256), 256, 0, st>>>(wa);
+  MDB_LAUNCHED(h);
+  MDB_CUDA(h, cudaFreeAsync(pp, st));
+  return MDB_OK;
+}
+
+static int32_t photo_launch(mdb_handle* h, PhotoArgs& a, void* stream) {
+  MDB_REQUIRE(h, a.W >= 2 && a.H >= 2 && a.C >= 1 && a.N >= 1, MDB_E_SHAPE, "SSIM needs W,H >= 2 (reflect pad)");
+  photo_kernel<<<grid_for(h, (int64_t)a.W * a.H * a.N, 128), 128, 0, (cudaStream_t)stream>>>(a);
+  MDB_LAUNCHED(h);
+  return MDB_OK;
+}
+
+int32_t mdb_ssim(mdb_handle* h, const float* x, const float* y, int32_t W, int32_t H, int32_t C,
+                 int32_t N, float c1, float c2, float* out, void* stream) {
+  MDB_REQUIRE(h, h && x && y && out, MDB_E_INVALID_ARG, "mdb_ssim: null argument");
+  PhotoArgs a{};
+  a.pred[0] = x; a.pred_nstride[0] = (int64_t)W * H * C; a.target = y; a.tgt_nstride = (int64_t)W * H * C;
+  a.S = 1; a.W = W; a.H = H; a.C = C; a.N = N; a.mode = 0; a.alpha = 1.0f; a.c1 = c1; a.c2 = c2; a.out = out;
+  return photo_launch(h, a, stream);
+}
+
+int32_t mdb_photometric_loss(mdb_handle* h, const float* predicted, const float* target, int32_t W,
+                             int32_t H, int32_t C, int32_t N, float alpha, float c1, float c2,
+                             float* out, void* stream) {
+  MDB_REQUIRE(h, h && predicted && target && out, MDB_E_INVALID_ARG, "mdb_photometric_loss: null argument");
+  PhotoArgs a{};
+  a.pred[0] = predicted; a.pred_nstride[0] = (int64_t)W * H * C; a.target = target; a.tgt_nstride = (int64_t)W * H * C;
+  a.S = 1; a.W = W; a.H = H; a.C = C; a.N = N; a.mode = 1; a.alpha = alpha; a.c1 = c1; a.c2 = c2; a.out = out;
+  return photo_launch(h, a, stream);
+}
+
+int32_t mdb_prediction_loss(mdb_handle* h, const float* const* predictions, int32_t S,
+                            const float* target, int32_t W, int32_t H, int32_t C, int32_t N,
+                            float alpha, float c1, float c2, float* out, void* stream) {
+  MDB_REQUIRE(h, h && predictions && target && out && S >= 1 && S <= 4, MDB_E_INVALID_ARG, "mdb_prediction_loss: bad argument");
+  PhotoArgs a{};
+  for (int s = 0; s < S; ++s) { MDB_REQUIRE(h, predictions[s], MDB_E_INVALID_ARG, "null prediction"); a.pred[s] = predictions[s]; a.pred_nstride[s] = (int64_t)W * H * C; }
+  a.target = target; a.tgt_nstride = (int64_t)W * H * C;
+  a.S = S; a.W = W; a.H = H; a.C = C; a.N = N; a.mode = 2; a.alpha = alpha; a.c1 = c1; a.c2 = c2; a.out = out;
+  return photo_launch(h, a, stream);
+}
+
+int32_t mdb_automasking_loss(mdb_handle* h, const float* x, int32_t target_id, const int32_t* source_ids,
+                             int32_t S, int32_t W, int32_t H, int32_t C, int32_t L, int32_t N,
+                             float alpha, float c1, float c2, float* out, void* stream) {
+  MDB_REQUIRE(h, h && x && source_ids && out && S >= 1 && S <= 4 && target_id >= 1 && target_id <= L,
+              MDB_E_INVALID_ARG, "mdb_automasking_loss: bad argument");
+  PhotoArgs a{};
+  const int64_t frame = (int64_t)W * H * C;
+  for (int s = 0; s < S; ++s) {
+    MDB_REQUIRE(h, source_ids[s] >= 1 && source_ids[s] <= L, MDB_E_INVALID_ARG, "source id out of range");
+    a.pred[s] = x + (source_ids[s] - 1) * frame; a.pred_nstride[s] = frame * L;
+  }
+  a.target = x + (target_id - 1) * frame; a.tgt_nstride = frame * L;
+  a.S = S; a.W = W; a.H = H; a.C = C; a.N = N; a.mode = 2; a.alpha = alpha; a.c1 = c1; a.c2 = c2; a.out = out;
+  return photo_launch(h, a, stream);
+}
+
+int32_t mdb_apply_mask(mdb_handle* h, const float* mask, const float* warp_loss, int64_t n, float* out, void* stream) {
+  MDB_REQUIRE(h, h && mask && warp_loss && out && n > 0, MDB_E_INVALID_ARG, "mdb_apply_mask: bad argument");
+  min2_kernel<<<grid_for(h, n, 256), 256, 0, (cudaStream_t)stream>>>(mask, warp_loss, n, out);
+  MDB_LAUNCHED(h);
+  return MDB_OK;
+}
+
+size_t mdb_smooth_loss_workspace_bytes(int32_t W, int32_t H, int32_t N) {
+  if (W < 1 || H < 1 || N < 1) return 0;
+  return mdb_align_up(sizeof(float) * 2 * (size_t)N * ((H + SM_ROWS - 1) / SM_ROWS), 256);
+}
+
+int32_t mdb_smooth_loss(mdb_handle* h, const float* disparity, const float* image, int32_t W, int32_t H,
+                        int32_t C, int32_t N, float* loss, float* d_disparity, void* workspace,
+                        size_t workspace_bytes, void* stream) {
+  MDB_REQUIRE(h, h && disparity && image && loss, MDB_E_INVALID_ARG, "mdb_smooth_loss: null argument");
+  MDB_REQUIRE(h, W >= 2 && H >= 2 && C >= 1 && N >= 1, MDB_E_SHAPE, "mdb_smooth_loss: need W,H >= 2");
+  MDB_REQUIRE(h, workspace && workspace_bytes >= mdb_smooth_loss_workspace_bytes(W, H, N) && ((uintptr_t)workspace & 255) == 0,
+              MDB_E_WORKSPACE, "mdb_smooth_loss: workspace too small or misaligned");
+  const int rb = (H + SM_ROWS - 1) / SM_ROWS;
+  const double kx = 1.0 / ((double)(W - 1) * H * N), ky = 1.0 / ((double)W * (H - 1) * N);
+  dim3 grid(rb, N);
+  smooth_kernel<<<grid, SM_THREADS, 0, (cudaStream_t)stream>>>(disparity, image, W, H, C, N, (float)kx, (float)ky,
+                                                               (float*)workspace, d_disparity);
+  MDB_LAUNCHED(h);
+  smooth_finalize_kernel<<<1, 256, 0, (cudaStream_t)stream>>>((const float*)workspace, rb * N, kx, ky, loss);
+  MDB_LAUNCHED(h);
+  return MDB_OK;
+}
+
+}  // extern "C"

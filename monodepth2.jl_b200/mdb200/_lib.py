@@ -1,0 +1,115 @@
+"""ctypes binding of libmdb200.so (the C ABI declared in include/mdb200.h).
+
+The library is built in-tree by ``make -C monodepth2.jl_b200`` (or
+``__graft_entry__.build()``).  There is no fallback: if the shared object is missing the
+import fails, and if no sm_100 device is present ``mdb_create`` fails.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libmdb200.so")
+
+MAX_SCALES = 8
+MAX_SOURCES = 2
+
+c_f32p = C.POINTER(C.c_float)
+
+
+class LossParams(C.Structure):
+    _fields_ = [
+        ("min_depth", C.c_float), ("max_depth", C.c_float), ("disparity_smoothness", C.c_float),
+        ("alpha", C.c_float), ("ssim_c1", C.c_float), ("ssim_c2", C.c_float),
+        ("automasking", C.c_int32), ("normalize_disparity", C.c_int32),
+        ("smooth_weight_mode", C.c_int32), ("upsample_align_corners", C.c_int32),
+        ("n_global", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+
+class LossIO(C.Structure):
+    _fields_ = [
+        ("x", C.c_void_p),
+        ("W", C.c_int32), ("H", C.c_int32), ("C", C.c_int32), ("L", C.c_int32), ("N", C.c_int32),
+        ("target_id", C.c_int32), ("S", C.c_int32),
+        ("source_ids", C.c_int32 * MAX_SOURCES), ("invert", C.c_int32 * MAX_SOURCES),
+        ("rvec", C.c_void_p * MAX_SOURCES), ("tvec", C.c_void_p * MAX_SOURCES),
+        ("Ls", C.c_int32),
+        ("disparity", C.c_void_p * MAX_SCALES),
+        ("dw", C.c_int32 * MAX_SCALES), ("dh", C.c_int32 * MAX_SCALES),
+        ("scale", C.c_float * MAX_SCALES),
+        ("auto_loss", C.c_void_p),
+        ("K", C.c_float * 9), ("invK", C.c_float * 9),
+        ("loss", C.c_void_p),
+        ("d_disparity", C.c_void_p * MAX_SCALES),
+        ("d_rvec", C.c_void_p * MAX_SOURCES), ("d_tvec", C.c_void_p * MAX_SOURCES),
+        ("vis_warp_loss", C.c_void_p),
+    ]
+
+
+def _load() -> C.CDLL:
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} not found: build it with `make -C monodepth2.jl_b200` "
+            "(there is no CPU fallback for the mdb200 kernels)")
+    return C.CDLL(LIB_PATH)
+
+
+lib = _load()
+
+_vp, _i32, _i64, _f32, _sz = C.c_void_p, C.c_int32, C.c_int64, C.c_float, C.c_size_t
+
+# name -> (restype, argtypes); mirrors include/mdb200.h one to one
+PROTOTYPES = {
+    "mdb_version": (_i32, []),
+    "mdb_create": (_i32, [C.POINTER(_vp), _i32]),
+    "mdb_destroy": (_i32, [_vp]),
+    "mdb_last_error": (C.c_char_p, [_vp]),
+    "mdb_launch_count": (_i64, [_vp]),
+    "mdb_loss_params_default": (None, [C.POINTER(LossParams)]),
+    "mdb_hat": (_i32, [_vp, _vp, _i32, _vp, _vp]),
+    "mdb_hat_pullback": (_i32, [_vp, _vp, _i32, _vp, _vp]),
+    "mdb_so3_exp_map": (_i32, [_vp, _vp, _i32, _vp, _vp]),
+    "mdb_compose_T": (_i32, [_vp, _vp, _vp, _i32, _i32, _vp, _vp, _vp]),
+    "mdb_compose_T_bwd": (_i32, [_vp, _vp, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp]),
+    "mdb_disparity_to_depth": (_i32, [_vp, _vp, _i64, _f32, _f32, _vp, _vp]),
+    "mdb_backproject": (_i32, [_vp, _vp, c_f32p, _i32, _i32, _i32, _vp, _vp]),
+    "mdb_project": (_i32, [_vp, _vp, c_f32p, _vp, _vp, _i32, _i32, _i32, _vp, _vp]),
+    "mdb_grid_sample": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
+    "mdb_warp": (_i32, [_vp, _vp, _vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_i32), _i32, c_f32p,
+                        c_f32p, _i32, _i32, _i32, _i32, _i32, _f32, _f32, C.POINTER(_vp), _vp]),
+    "mdb_ssim": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _f32, _f32, _vp, _vp]),
+    "mdb_photometric_loss": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _f32, _f32, _f32, _vp, _vp]),
+    "mdb_prediction_loss": (_i32, [_vp, C.POINTER(_vp), _i32, _vp, _i32, _i32, _i32, _i32, _f32, _f32,
+                                   _f32, _vp, _vp]),
+    "mdb_automasking_loss": (_i32, [_vp, _vp, _i32, C.POINTER(_i32), _i32, _i32, _i32, _i32, _i32, _i32,
+                                    _f32, _f32, _f32, _vp, _vp]),
+    "mdb_apply_mask": (_i32, [_vp, _vp, _vp, _i64, _vp, _vp]),
+    "mdb_smooth_loss_workspace_bytes": (_sz, [_i32, _i32, _i32]),
+    "mdb_smooth_loss": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _sz, _vp]),
+    "mdb_train_loss_workspace_bytes": (_sz, [C.POINTER(LossIO)]),
+    "mdb_train_loss_fwdbwd": (_i32, [_vp, C.POINTER(LossIO), C.POINTER(LossParams), _vp, _sz, _vp]),
+}
+
+
+def _bind():
+    for name, (res, args) in PROTOTYPES.items():
+        fn = getattr(lib, name)  # AttributeError here = header/library mismatch: fail loudly
+        fn.restype = res
+        fn.argtypes = args
+
+
+_bind()
+
+
+class MdbError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"mdb200 error {code}: {msg}")
+        self.code = code
+
+
+def check(handle, code: int):
+    if code != 0:
+        msg = lib.mdb_last_error(handle).decode() if handle else "no handle"
+        raise MdbError(code, msg)

@@ -1,0 +1,434 @@
+"""Host-side mirror of the reference's Julia API for the view-synthesis loss path.
+
+Same names, argument order and meaning as the reference functions (file:line cited per
+function), implemented as thin calls into libmdb200.so through the C ABI.  Julia is not
+installed on the build or GPU boxes, so this Python layer plays the role of the Julia glue
+(monodepth2.jl_b200/julia/); `torch` is used only for device memory and
+streams.
+
+Array convention: a Julia array of size (d1,...,dk) is a contiguous CUDA float32 tensor of
+shape (dk,...,d1) -- identical bytes, no transposes anywhere.  Images (W,H,C,N) are
+(N,C,H,W); rvec (3,N) is (N,3); tvec (3,1,N) is (N,1,3); rotation stacks (3,3,N) are
+(N,3,3) indexed [n, j, i]; K (3,3) is K_math.T.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import Callable, List, Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import lib, check
+
+_handles = {}
+
+
+def handle(device: Optional[int] = None):
+    """One mdb_handle per CUDA device (created on first use; fails without a B200)."""
+    if not torch.cuda.is_available():
+        raise RuntimeError("mdb200 needs a CUDA device (sm_100); there is no CPU fallback")
+    dev = torch.cuda.current_device() if device is None else device
+    if dev not in _handles:
+        h = C.c_void_p()
+        rc = lib.mdb_create(C.byref(h), dev)
+        if rc != 0:
+            raise _lib.MdbError(rc, "mdb_create failed (no sm_100 device?)")
+        _handles[dev] = h
+    return _handles[dev]
+
+
+def launch_count() -> int:
+    return int(lib.mdb_launch_count(handle()))
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _p(t: Optional[torch.Tensor]):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def _chk(t: torch.Tensor, name: str) -> torch.Tensor:
+    if not (isinstance(t, torch.Tensor) and t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
+        raise TypeError(f"{name}: expected a contiguous CUDA float32 tensor "
+                        f"(got {type(t).__name__}, {getattr(t, 'dtype', None)}, "
+                        f"cuda={getattr(t, 'is_cuda', None)})")
+    return t
+
+
+def _k9(K) -> "C.Array":
+    """K / invK as 9 host floats in Julia (column-major) order."""
+    k = torch.as_tensor(K, dtype=torch.float32, device="cpu").reshape(9)
+    return (C.c_float * 9)(*k.tolist())
+
+
+# --------------------------------------------------------------------------------------
+# types -- src/pose_decoder.jl:1-5, src/Monodepth.jl:37-60
+# --------------------------------------------------------------------------------------
+@dataclass
+class Pose:
+    rvec: torch.Tensor  # (N,3)     Julia (3,N)
+    tvec: torch.Tensor  # (N,1,3)   Julia (3,1,N)   [render: (B,3) Julia (3,B)]
+
+
+@dataclass
+class Params:
+    min_depth: float = 0.1
+    max_depth: float = 100.0
+    disparity_smoothness: float = 1e-3
+    frame_ids: List[int] = field(default_factory=lambda: [1, 2, 3])
+    automasking: bool = True
+    target_size: Tuple[int, int] = (416, 128)  # (width, height)
+    batch_size: int = 1
+
+
+class SSIM:
+    """`SSIM()` -- src/utils.jl:17-43 (3x3 mean pool over a reflect-padded image)."""
+
+    def __init__(self, c1: float = 0.01 ** 2, c2: float = 0.03 ** 2):
+        self.c1, self.c2 = c1, c2
+
+    def __call__(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        _chk(x, "x"); _chk(y, "y")
+        N, Cc, H, W = x.shape
+        out = torch.empty_like(x)
+        check(handle(), lib.mdb_ssim(handle(), _p(x), _p(y), W, H, Cc, N, self.c1, self.c2, _p(out), _stream()))
+        return out
+
+
+class Backproject:
+    """`Backproject(; width, height)` -- src/utils.jl:45-69."""
+
+    def __init__(self, *, width: int, height: int):
+        self.width, self.height = width, height
+
+    def __call__(self, depth: torch.Tensor, invK) -> torch.Tensor:
+        """depth (N,WH,1) [Julia (1,WH,N)] -> points (N,WH,3) [Julia (3,WH,N)]."""
+        _chk(depth, "depth")
+        N = depth.shape[0]
+        pts = torch.empty((N, self.width * self.height, 3), device=depth.device, dtype=torch.float32)
+        check(handle(), lib.mdb_backproject(handle(), _p(depth), _k9(invK), self.width, self.height, N, _p(pts), _stream()))
+        return pts
+
+
+class Project:
+    """`Project(; width, height)` -- src/utils.jl:71-103."""
+
+    def __init__(self, *, width: int, height: int):
+        self.width, self.height = width, height
+
+    def __call__(self, points: torch.Tensor, K, R: torch.Tensor, t: torch.Tensor) -> torch.Tensor:
+        """points (N,WH,3), R (N,3,3), t (N,1,3) -> normalised uv (N,WH,2) [Julia (2,WH,N)]."""
+        _chk(points, "points"); _chk(R, "R"); _chk(t, "t")
+        N = points.shape[0]
+        uv = torch.empty((N, self.width * self.height, 2), device=points.device, dtype=torch.float32)
+        check(handle(), lib.mdb_project(handle(), _p(points), _k9(K), _p(R), _p(t), self.width, self.height, N, _p(uv), _stream()))
+        return uv
+
+
+@dataclass
+class TrainCache:
+    """`TrainCache` -- src/Monodepth.jl:49-60."""
+    ssim: SSIM
+    backprojections: Backproject
+    projections: Project
+    K: torch.Tensor      # (3,3) Julia layout, host or device
+    invK: torch.Tensor
+    target_id: int
+    source_ids: List[int]
+    scales: List[float]
+
+
+# --------------------------------------------------------------------------------------
+# so3 / pose -- src/utils.jl:106-145, 185-192
+# --------------------------------------------------------------------------------------
+def hat(rvec: torch.Tensor) -> torch.Tensor:
+    _chk(rvec, "rvec")
+    N = rvec.shape[0]
+    S = torch.empty((N, 3, 3), device=rvec.device, dtype=torch.float32)
+    check(handle(), lib.mdb_hat(handle(), _p(rvec), N, _p(S), _stream()))
+    return S
+
+
+def hat_pullback(d: torch.Tensor) -> torch.Tensor:
+    _chk(d, "d")
+    N = d.shape[0]
+    g = torch.empty((N, 3), device=d.device, dtype=torch.float32)
+    check(handle(), lib.mdb_hat_pullback(handle(), _p(d), N, _p(g), _stream()))
+    return g
+
+
+def so3_exp_map(rvec: torch.Tensor) -> torch.Tensor:
+    _chk(rvec, "rvec")
+    N = rvec.shape[0]
+    R = torch.empty((N, 3, 3), device=rvec.device, dtype=torch.float32)
+    check(handle(), lib.mdb_so3_exp_map(handle(), _p(rvec), N, _p(R), _stream()))
+    return R
+
+
+def composeT(rvec: torch.Tensor, t: torch.Tensor, invert: bool):
+    _chk(rvec, "rvec"); _chk(t, "t")
+    N = rvec.shape[0]
+    R = torch.empty((N, 3, 3), device=rvec.device, dtype=torch.float32)
+    to = torch.empty((N, 1, 3), device=rvec.device, dtype=torch.float32)
+    check(handle(), lib.mdb_compose_T(handle(), _p(rvec), _p(t), int(bool(invert)), N, _p(R), _p(to), _stream()))
+    return R, to
+
+
+def composeT_pullback(rvec, t, invert, dR, dt):
+    for a, nm in ((rvec, "rvec"), (t, "t"), (dR, "dR"), (dt, "dt")):
+        _chk(a, nm)
+    N = rvec.shape[0]
+    dr = torch.empty_like(rvec)
+    dtv = torch.empty_like(t)
+    check(handle(), lib.mdb_compose_T_bwd(handle(), _p(rvec), _p(t), int(bool(invert)), N, _p(dR), _p(dt), _p(dr), _p(dtv), _stream()))
+    return dr, dtv
+
+
+# --------------------------------------------------------------------------------------
+# elementwise / sampling primitives
+# --------------------------------------------------------------------------------------
+def disparity_to_depth(disparity: torch.Tensor, min_depth: float, max_depth: float) -> torch.Tensor:
+    """src/utils.jl:179-183."""
+    _chk(disparity, "disparity")
+    out = torch.empty_like(disparity)
+    check(handle(), lib.mdb_disparity_to_depth(handle(), _p(disparity), disparity.numel(), float(min_depth), float(max_depth), _p(out), _stream()))
+    return out
+
+
+def grid_sample(inp: torch.Tensor, grid: torch.Tensor, padding_mode: str = "border") -> torch.Tensor:
+    """NNlib `grid_sample(input, grid; padding_mode=:border)`; inp (N,C,H,W), grid (N,Ho,Wo,2)."""
+    if padding_mode != "border":
+        raise ValueError("only padding_mode=:border is on the reference's path")
+    _chk(inp, "input"); _chk(grid, "grid")
+    N, Cc, H, W = inp.shape
+    Ho, Wo = grid.shape[1:3]
+    out = torch.empty((N, Cc, Ho, Wo), device=inp.device, dtype=torch.float32)
+    check(handle(), lib.mdb_grid_sample(handle(), _p(inp), _p(grid), W, H, Cc, N, Wo, Ho, _p(out), _stream()))
+    return out
+
+
+def warp(disp: torch.Tensor, x: torch.Tensor, Ps, backprojections, projections, invKs, Ks, *,
+         min_depth: float, max_depth: float, source_ids: Sequence[int]) -> List[torch.Tensor]:
+    """`warp(...)` as called at src/simple_depth.jl:30-32 (body: src/training.jl:48-57).
+    disp (N,H,W,1) or (N,1,H,W); x (N,L,C,H,W); Ps = [(R (N,3,3), t (N,1,3))]."""
+    _chk(disp, "disp"); _chk(x, "x")
+    N, L, Cc, H, W = x.shape
+    S = len(Ps)
+    outs = [torch.empty((N, Cc, H, W), device=x.device, dtype=torch.float32) for _ in range(S)]
+    Rp = (C.c_void_p * S)(*[_chk(P[0], "R").data_ptr() for P in Ps])
+    tp = (C.c_void_p * S)(*[_chk(P[1], "t").data_ptr() for P in Ps])
+    op = (C.c_void_p * S)(*[o.data_ptr() for o in outs])
+    ids = (C.c_int32 * S)(*[int(s) for s in source_ids])
+    check(handle(), lib.mdb_warp(handle(), _p(disp), _p(x), Rp, tp, ids, S, _k9(Ks), _k9(invKs), W, H, Cc, L, N,
+                                 float(min_depth), float(max_depth), op, _stream()))
+    return outs
+
+
+def photometric_loss(ssim: SSIM, predicted: torch.Tensor, target: torch.Tensor, alpha: float = 0.85):
+    """src/training.jl:1-7 -> (N,1,H,W)."""
+    _chk(predicted, "predicted"); _chk(target, "target")
+    N, Cc, H, W = predicted.shape
+    out = torch.empty((N, 1, H, W), device=predicted.device, dtype=torch.float32)
+    check(handle(), lib.mdb_photometric_loss(handle(), _p(predicted), _p(target), W, H, Cc, N, alpha, ssim.c1, ssim.c2, _p(out), _stream()))
+    return out
+
+
+def prediction_loss(ssim: SSIM, predictions: Sequence[torch.Tensor], target: torch.Tensor, alpha: float = 0.85):
+    """src/training.jl:13-15."""
+    _chk(target, "target")
+    N, Cc, H, W = target.shape
+    S = len(predictions)
+    pp = (C.c_void_p * S)(*[_chk(p, "prediction").data_ptr() for p in predictions])
+    out = torch.empty((N, 1, H, W), device=target.device, dtype=torch.float32)
+    check(handle(), lib.mdb_prediction_loss(handle(), pp, S, _p(target), W, H, Cc, N, alpha, ssim.c1, ssim.c2, _p(out), _stream()))
+    return out
+
+
+def automasking_loss(ssim: SSIM, inputs: torch.Tensor, target_id: int, *, source_ids: Sequence[int], alpha: float = 0.85):
+    """src/training.jl:9-11.  `inputs` (N,L,C,H,W); the target is frame `target_id` of it
+    (the reference passes the slice; the ABI takes the index so no copy is made)."""
+    _chk(inputs, "inputs")
+    N, L, Cc, H, W = inputs.shape
+    S = len(source_ids)
+    ids = (C.c_int32 * S)(*[int(s) for s in source_ids])
+    out = torch.empty((N, 1, H, W), device=inputs.device, dtype=torch.float32)
+    check(handle(), lib.mdb_automasking_loss(handle(), _p(inputs), int(target_id), ids, S, W, H, Cc, L, N, alpha, ssim.c1, ssim.c2, _p(out), _stream()))
+    return out
+
+
+def _apply_mask(mask: torch.Tensor, warp_loss: torch.Tensor) -> torch.Tensor:
+    """src/training.jl:17-19."""
+    _chk(mask, "mask"); _chk(warp_loss, "warp_loss")
+    out = torch.empty_like(warp_loss)
+    check(handle(), lib.mdb_apply_mask(handle(), _p(mask), _p(warp_loss), warp_loss.numel(), _p(out), _stream()))
+    return out
+
+
+def smooth_loss(disparity: torch.Tensor, image: torch.Tensor, with_grad: bool = False):
+    """src/utils.jl:163-177.  disparity (N,H,W), image (N,C,H,W) -> 0-dim loss tensor
+    (and d loss / d disparity when `with_grad`)."""
+    _chk(disparity, "disparity"); _chk(image, "image")
+    N, Cc, H, W = image.shape
+    wsb = lib.mdb_smooth_loss_workspace_bytes(W, H, N)
+    ws = torch.empty(wsb, dtype=torch.uint8, device=image.device)
+    loss = torch.empty((), dtype=torch.float32, device=image.device)
+    grad = torch.empty_like(disparity) if with_grad else None
+    check(handle(), lib.mdb_smooth_loss(handle(), _p(disparity), _p(image), W, H, Cc, N, _p(loss), _p(grad), _p(ws), wsb, _stream()))
+    return (loss, grad) if with_grad else loss
+
+
+# --------------------------------------------------------------------------------------
+# the fused hot path: train_loss forward + backward in one pass
+# --------------------------------------------------------------------------------------
+@dataclass
+class LossResult:
+    loss: torch.Tensor                 # 0-dim, loss / Ls over the local items
+    d_disparities: List[torch.Tensor]  # native resolution, same shapes as the inputs
+    d_poses: List[Pose]                # (d_rvec (N,3), d_tvec (N,1,3)) per source
+    vis_warp_loss: Optional[torch.Tensor] = None
+
+
+class FusedLoss:
+    """Pre-planned call of `mdb_train_loss_fwdbwd` for fixed shapes.  Owns the workspace and
+    the gradient buffers so the per-step path allocates nothing (the caller-owns-everything
+    rule of the ABI; the Julia glue does the same in its `rrule`)."""
+
+    def __init__(self, *, W: int, H: int, C: int, L: int, N: int, disp_sizes: Sequence[Tuple[int, int]],
+                 scales: Sequence[float], target_id: int, source_ids: Sequence[int], K, invK,
+                 min_depth: float = 0.1, max_depth: float = 100.0, disparity_smoothness: float = 1e-3,
+                 automasking: bool = False, normalize_disparity: bool = True, smooth_weight_mode: int = 0,
+                 n_global: int = 0, alpha: float = 0.85, want_vis: bool = False, device=None):
+        self.dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.shape = (N, L, C, H, W)
+        self.disp_sizes = [(int(w), int(h)) for (w, h) in disp_sizes]
+        self.S = len(source_ids)
+        self.Ls = len(scales)
+        p = _lib.LossParams()
+        lib.mdb_loss_params_default(C.byref(p))
+        p.min_depth, p.max_depth, p.disparity_smoothness, p.alpha = min_depth, max_depth, disparity_smoothness, alpha
+        p.automasking = int(automasking)
+        p.normalize_disparity = int(normalize_disparity)
+        p.smooth_weight_mode = int(smooth_weight_mode)
+        p.n_global = int(n_global)
+        self.params = p
+        io = _lib.LossIO()
+        io.W, io.H, io.C, io.L, io.N = W, H, C, L, N
+        io.target_id = int(target_id)
+        io.S = self.S
+        for s, sid in enumerate(source_ids):
+            io.source_ids[s] = int(sid)
+            io.invert[s] = int(sid < target_id)  # src/training.jl:28
+        io.Ls = self.Ls
+        for k, ((w, h), sc) in enumerate(zip(self.disp_sizes, scales)):
+            io.dw[k], io.dh[k], io.scale[k] = w, h, float(sc)
+        kk, ik = _k9(K), _k9(invK)
+        for i in range(9):
+            io.K[i], io.invK[i] = kk[i], ik[i]
+        self.io = io
+        f32 = dict(device=self.dev, dtype=torch.float32)
+        self.loss = torch.zeros((), **f32)
+        self.d_disp = [torch.empty((N, 1, h, w), **f32) for (w, h) in self.disp_sizes]
+        self.d_rvec = [torch.empty((N, 3), **f32) for _ in range(self.S)]
+        self.d_tvec = [torch.empty((N, 1, 3), **f32) for _ in range(self.S)]
+        self.vis = torch.empty((N, 1, H, W), **f32) if want_vis else None
+        io.loss = self.loss.data_ptr()
+        for k in range(self.Ls):
+            io.d_disparity[k] = self.d_disp[k].data_ptr()
+        for s in range(self.S):
+            io.d_rvec[s] = self.d_rvec[s].data_ptr()
+            io.d_tvec[s] = self.d_tvec[s].data_ptr()
+        io.vis_warp_loss = self.vis.data_ptr() if want_vis else None
+        self.ws_bytes = int(lib.mdb_train_loss_workspace_bytes(C.byref(io)))
+        if self.ws_bytes == 0:
+            raise _lib.MdbError(_lib.lib.mdb_version() * 0 - 2, "unsupported shape for the fused loss")
+        self.ws = torch.empty(self.ws_bytes, dtype=torch.uint8, device=self.dev)
+
+    def __call__(self, x: torch.Tensor, disparities: Sequence[torch.Tensor], poses: Sequence[Pose],
+                 auto_loss: Optional[torch.Tensor] = None) -> LossResult:
+        io = self.io
+        _chk(x, "x")
+        if tuple(x.shape) != self.shape:
+            raise ValueError(f"x has shape {tuple(x.shape)}, planned for {self.shape}")
+        io.x = x.data_ptr()
+        for k, d in enumerate(disparities):
+            _chk(d, f"disparities[{k}]")
+            if d.shape[-1] != self.disp_sizes[k][0] or d.shape[-2] != self.disp_sizes[k][1]:
+                raise ValueError(f"disparities[{k}] has shape {tuple(d.shape)}, planned {self.disp_sizes[k]}")
+            io.disparity[k] = d.data_ptr()
+        for s, pz in enumerate(poses):
+            io.rvec[s] = _chk(pz.rvec, "rvec").data_ptr()
+            io.tvec[s] = _chk(pz.tvec, "tvec").data_ptr()
+        io.auto_loss = _chk(auto_loss, "auto_loss").data_ptr() if auto_loss is not None else None
+        h = handle()
+        check(h, lib.mdb_train_loss_fwdbwd(h, C.byref(io), C.byref(self.params), _p(self.ws), self.ws_bytes, _stream()))
+        return LossResult(self.loss, self.d_disp, [Pose(r, t) for r, t in zip(self.d_rvec, self.d_tvec)], self.vis)
+
+
+class _TrainLossFn(torch.autograd.Function):
+    """The Python twin of the Julia `rrule`: forward runs the fused fwd+bwd kernels with unit
+    seed and caches the gradients; backward scales them by the incoming scalar cotangent."""
+
+    @staticmethod
+    def forward(ctx, plan: FusedLoss, x, auto_loss, n_disp, *tensors):
+        disps = tensors[:n_disp]
+        rest = tensors[n_disp:]
+        S = len(rest) // 2
+        poses = [Pose(rest[2 * s].detach(), rest[2 * s + 1].detach()) for s in range(S)]
+        res = plan(x, [d.detach() for d in disps], poses, auto_loss)
+        ctx.saved = [g.clone() for g in res.d_disparities] + \
+            [t.clone() for pz in res.d_poses for t in (pz.rvec, pz.tvec)]
+        return res.loss.clone()
+
+    @staticmethod
+    def backward(ctx, delta):
+        return (None, None, None, None) + tuple(g * delta for g in ctx.saved)
+
+
+def train_loss(model: Callable, x: torch.Tensor, auto_loss: Optional[torch.Tensor], cache: TrainCache,
+               parameters: Params, do_visualization: bool = False, _plans={}):
+    """`train_loss(model, x, auto_loss, cache, parameters, do_visualization)` --
+    src/training.jl:21-78.  `model(x, source_ids, target_id)` returns (disparities, poses).
+    Returns (loss, vis_disparity, vis_warped, vis_loss) like the reference; the loss is
+    differentiable w.r.t. the disparities and poses through a custom autograd Function."""
+    _chk(x, "x")
+    N, L, Cc, H, W = x.shape
+    disparities, poses = model(x, cache.source_ids, cache.target_id)
+    sizes = tuple((d.shape[-1], d.shape[-2]) for d in disparities)
+    key = (N, L, Cc, H, W, sizes, tuple(cache.scales), cache.target_id, tuple(cache.source_ids),
+           parameters.automasking, parameters.min_depth, parameters.max_depth, parameters.disparity_smoothness,
+           bool(do_visualization), x.device.index)
+    if key not in _plans:
+        _plans[key] = FusedLoss(W=W, H=H, C=Cc, L=L, N=N, disp_sizes=sizes, scales=cache.scales,
+                                target_id=cache.target_id, source_ids=cache.source_ids, K=cache.K, invK=cache.invK,
+                                min_depth=parameters.min_depth, max_depth=parameters.max_depth,
+                                disparity_smoothness=parameters.disparity_smoothness,
+                                automasking=parameters.automasking, want_vis=bool(do_visualization), device=x.device)
+    plan = _plans[key]
+    flat = list(disparities) + [t for pz in poses for t in (pz.rvec, pz.tvec)]
+    loss = _TrainLossFn.apply(plan, x, auto_loss if parameters.automasking else None, len(disparities), *flat)
+    vis_disparity = vis_warped = vis_loss = None
+    if do_visualization:
+        vis_disparity = disparities[-1].detach().cpu()
+        vis_loss = plan.vis.detach().cpu()
+        Ps = [composeT(pz.rvec.detach(), pz.tvec.detach(), sid < cache.target_id)
+              for pz, sid in zip(poses, cache.source_ids)]
+        full = disparities[-1].detach()
+        vis_warped = [w.cpu() for w in warp(full, x, Ps, cache.backprojections, cache.projections, cache.invK,
+                                            cache.K, min_depth=parameters.min_depth, max_depth=parameters.max_depth,
+                                            source_ids=cache.source_ids)]
+    return loss, vis_disparity, vis_warped, vis_loss
+
+
+def simple_depth_plan(x: torch.Tensor, K, invK, *, target_id: int = 2, source_ids: Sequence[int] = (1, 3),
+                      min_depth: float = 0.1, max_depth: float = 100.0) -> FusedLoss:
+    """The closure `slow_depth` differentiates (src/simple_depth.jl:25-41): one full-res scale,
+    `mean(prediction_loss) + smooth_loss(disp, target)` with un-normalised disparity and
+    smoothness weight 1."""
+    N, L, Cc, H, W = x.shape
+    return FusedLoss(W=W, H=H, C=Cc, L=L, N=N, disp_sizes=[(W, H)], scales=[1.0], target_id=target_id,
+                     source_ids=source_ids, K=K, invK=invK, min_depth=min_depth, max_depth=max_depth,
+                     automasking=False, normalize_disparity=False, smooth_weight_mode=1, device=x.device)
