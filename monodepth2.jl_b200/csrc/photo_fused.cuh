@@ -132,24 +132,32 @@ MDB_DEV Taps make_taps(float fu, float fv, int gx, int gy, int W, int H) {
   return t;
 }
 
-// SSIM of one 3x3 window from its five raw sums, plus the coefficients of its pullback:
-//   d s / d x_p = (m_pq / 9) (A + 2 x_p B + y_p C).   Reference: src/utils.jl:29-43.
-MDB_DEV float ssim_window(float Sx, float Sy, float Sxx, float Syy, float Sxy, float c1, float c2,
-                          float& A, float& B, float& C) {
+// SSIM of one 3x3 window and the coefficients of its pullback.  Reference: src/utils.jl:29-43.
+// The five sums are taken over values SHIFTED by the window's centre pixel (x' = x - xc,
+// y' = y - yc): the variances sigma = E[x'^2] - E[x']^2 are then free of the catastrophic
+// cancellation E[x^2] - mu^2 has in float32 on flat image regions, while
+// being the same numbers mathematically.  The pullback is returned in the shifted basis too:
+//   d s / d x_p = (m_pq / 9) (A + 2 (x_p - xc) B + (y_p - yc) C)
+// with A = ds/dmu_x - 2 mu_x' B - mu_y' C, B = ds/dsigma_x, C = ds/dsigma_xy.
+MDB_DEV float ssim_window(float Sx, float Sy, float Sxx, float Syy, float Sxy, float xc, float yc,
+                          float c1, float c2, float& A, float& B, float& C) {
   const float k = 1.0f / 9.0f;
-  const float mx = Sx * k, my = Sy * k;
-  const float sx = fmaf(Sxx, k, -mx * mx), sy = fmaf(Syy, k, -my * my), sxy = fmaf(Sxy, k, -mx * my);
+  const float mxs = Sx * k, mys = Sy * k;            // shifted means
+  const float sx = fmaf(Sxx, k, -mxs * mxs), sy = fmaf(Syy, k, -mys * mys), sxy = fmaf(Sxy, k, -mxs * mys);
+  const float mx = xc + mxs, my = yc + mys;
   const float n1 = fmaf(2.0f * mx, my, c1), n2 = fmaf(2.0f, sxy, c2);
   const float d1 = fmaf(mx, mx, fmaf(my, my, c1)), d2 = sx + sy + c2;
-  const float n = n1 * n2, d = d1 * d2;
-  const float dinv = 1.0f / d;
-  const float raw = (1.0f - n * dinv) * 0.5f;
+  const float i1 = 1.0f / d1, i2 = 1.0f / d2;
+  const float r1 = n1 * i1, r2 = n2 * i2;            // n/d = r1 r2
+  const float raw = (1.0f - r1 * r2) * 0.5f;
   const bool inside = (raw >= 0.0f) && (raw <= 1.0f);
-  const float dn = inside ? -0.5f * dinv : 0.0f;      // ds/dn
-  const float ddn = inside ? 0.5f * n * dinv * dinv : 0.0f;  // ds/dd
-  A = dn * 2.0f * my * (n2 - n1) + ddn * 2.0f * mx * (d2 - d1);
-  B = ddn * d1;
-  C = dn * 2.0f * n1;
+  // ds/dmu_x = n2 (mu_x - mu_y) (mu_y (mu_x + mu_y) + c1) / (d1^2 d2), with mu_x - mu_y formed
+  // from the raw centre difference so no large terms cancel
+  const float dmu = (xc - yc) + (mxs - mys);
+  const float Abar = r2 * i1 * i1 * dmu * fmaf(my, mx + my, c1);
+  B = inside ? 0.5f * r1 * r2 * i2 : 0.0f;           // ds/dsigma_x  = n1 n2 / (2 d1 d2^2)
+  C = inside ? -r1 * i2 : 0.0f;                       // ds/dsigma_xy = -n1 / (d1 d2)
+  A = inside ? Abar - 2.0f * mxs * B - mys * C : 0.0f;
   return fminf(fmaxf(raw, 0.0f), 1.0f);
 }
 

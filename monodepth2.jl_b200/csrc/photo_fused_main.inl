@@ -136,28 +136,29 @@ photo_fused_kernel(const __grid_constant__ FusedArgs a) {
 #pragma unroll
       for (int c = 0; c < C; ++c) {
         float yv[9], Sy = 0.0f, Syy = 0.0f;
+        const float yc = s_tgt[c * R2N + ry[1] + cx[1]];
 #pragma unroll
         for (int k = 0; k < 9; ++k) {
-          yv[k] = s_tgt[c * R2N + ry[k / 3] + cx[k % 3]];
+          yv[k] = s_tgt[c * R2N + ry[k / 3] + cx[k % 3]] - yc;   // shifted by the window centre
           Sy += yv[k];
           Syy = fmaf(yv[k], yv[k], Syy);
         }
 #pragma unroll
         for (int s = 0; s < S; ++s) {
           const float* w = s_wrp + (s * C + c) * R2N;
-          float Sx = 0.0f, Sxx = 0.0f, Sxy = 0.0f, xc = 0.0f;
+          const float xc = w[ry[1] + cx[1]];
+          float Sx = 0.0f, Sxx = 0.0f, Sxy = 0.0f;
 #pragma unroll
           for (int k = 0; k < 9; ++k) {
-            const float xv = w[ry[k / 3] + cx[k % 3]];
-            if (k == 4) xc = xv;
+            const float xv = w[ry[k / 3] + cx[k % 3]] - xc;
             Sx += xv;
             Sxx = fmaf(xv, xv, Sxx);
             Sxy = fmaf(xv, yv[k], Sxy);
           }
           float A, B, Cc;
-          const float sv = ssim_window(Sx, Sy, Sxx, Syy, Sxy, a.c1, a.c2, A, B, Cc);
+          const float sv = ssim_window(Sx, Sy, Sxx, Syy, Sxy, xc, yc, a.c1, a.c2, A, B, Cc);
           cf[s][3 * c + 0] = A; cf[s][3 * c + 1] = B; cf[s][3 * c + 2] = Cc;
-          lossv[s] += a.alpha * (1.0f / C) * sv + kl * fabsf(yv[4] - xc);
+          lossv[s] += a.alpha * (1.0f / C) * sv + kl * fabsf(yc - xc);
         }
       }
       int best = 0;
@@ -216,7 +217,9 @@ photo_fused_kernel(const __grid_constant__ FusedArgs a) {
             for (int s = 1; s < S; ++s) xs = (sel == s) ? xp[s][c] : xs;
             const float A = s_coef[(3 * c + 0) * R1N + r1], B = s_coef[(3 * c + 1) * R1N + r1],
                         Cc = s_coef[(3 * c + 2) * R1N + r1];
-            float v = m * fmaf(2.0f * xs, B, fmaf(yp[c], Cc, A));
+            const int q2 = r2 + dy * R2W + dx;                       // the window's centre pixel
+            const float xq = s_wrp[(sel * C + c) * R2N + q2], yq = s_tgt[c * R2N + q2];
+            float v = m * fmaf(2.0f * (xs - xq), B, fmaf(yp[c] - yq, Cc, A));
             if (dx == 0 && dy == 0) v += kl * sgnf(xs - yp[c]);
 #pragma unroll
             for (int s = 0; s < S; ++s) G[s][c] += (sel == s) ? v : 0.0f;

@@ -138,12 +138,13 @@ __device__ float photo_pixel(const float* __restrict__ x, const float* __restric
   float ls = 0.0f, l1 = 0.0f;
   for (int c = 0; c < C; ++c) {
     float Sx = 0, Sy = 0, Sxx = 0, Syy = 0, Sxy = 0;
+    const float xc = x[c * plane + gy * W + gx], yc = y[c * plane + gy * W + gx];
     for (int k = 0; k < 9; ++k) {
-      const float xv = x[c * plane + ry[k / 3] + cx[k % 3]], yv = y[c * plane + ry[k / 3] + cx[k % 3]];
+      const float xv = x[c * plane + ry[k / 3] + cx[k % 3]] - xc, yv = y[c * plane + ry[k / 3] + cx[k % 3]] - yc;
       Sx += xv; Sy += yv; Sxx = fmaf(xv, xv, Sxx); Syy = fmaf(yv, yv, Syy); Sxy = fmaf(xv, yv, Sxy);
     }
     float A, B, Cc;
-    const float s = ssim_window(Sx, Sy, Sxx, Syy, Sxy, c1, c2, A, B, Cc);
+    const float s = ssim_window(Sx, Sy, Sxx, Syy, Sxy, xc, yc, c1, c2, A, B, Cc);
     if (ssim_out) ssim_out[c * ssim_cstride] = s;
     ls += s;
     l1 += fabsf(y[c * plane + gy * W + gx] - x[c * plane + gy * W + gx]);

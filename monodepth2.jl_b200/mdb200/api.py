@@ -13,7 +13,7 @@ shape (dk,...,d1) -- identical bytes, no transposes anywhere.  Images (W,H,C,N) 
 """
 from __future__ import annotations
 
-import ctypes as C
+import ctypes as ct
 from dataclasses import dataclass, field
 from typing import Callable, List, Optional, Sequence, Tuple
 
@@ -31,8 +31,8 @@ def handle(device: Optional[int] = None):
         raise RuntimeError("mdb200 needs a CUDA device (sm_100); there is no CPU fallback")
     dev = torch.cuda.current_device() if device is None else device
     if dev not in _handles:
-        h = C.c_void_p()
-        rc = lib.mdb_create(C.byref(h), dev)
+        h = ct.c_void_p()
+        rc = lib.mdb_create(ct.byref(h), dev)
         if rc != 0:
             raise _lib.MdbError(rc, "mdb_create failed (no sm_100 device?)")
         _handles[dev] = h
@@ -44,11 +44,11 @@ def launch_count() -> int:
 
 
 def _stream():
-    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    return ct.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
 def _p(t: Optional[torch.Tensor]):
-    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+    return ct.c_void_p(t.data_ptr()) if t is not None else ct.c_void_p(0)
 
 
 def _chk(t: torch.Tensor, name: str) -> torch.Tensor:
@@ -59,10 +59,10 @@ def _chk(t: torch.Tensor, name: str) -> torch.Tensor:
     return t
 
 
-def _k9(K) -> "C.Array":
+def _k9(K) -> "ct.Array":
     """K / invK as 9 host floats in Julia (column-major) order."""
     k = torch.as_tensor(K, dtype=torch.float32, device="cpu").reshape(9)
-    return (C.c_float * 9)(*k.tolist())
+    return (ct.c_float * 9)(*k.tolist())
 
 
 # --------------------------------------------------------------------------------------
@@ -219,10 +219,10 @@ def warp(disp: torch.Tensor, x: torch.Tensor, Ps, backprojections, projections, 
     N, L, Cc, H, W = x.shape
     S = len(Ps)
     outs = [torch.empty((N, Cc, H, W), device=x.device, dtype=torch.float32) for _ in range(S)]
-    Rp = (C.c_void_p * S)(*[_chk(P[0], "R").data_ptr() for P in Ps])
-    tp = (C.c_void_p * S)(*[_chk(P[1], "t").data_ptr() for P in Ps])
-    op = (C.c_void_p * S)(*[o.data_ptr() for o in outs])
-    ids = (C.c_int32 * S)(*[int(s) for s in source_ids])
+    Rp = (ct.c_void_p * S)(*[_chk(P[0], "R").data_ptr() for P in Ps])
+    tp = (ct.c_void_p * S)(*[_chk(P[1], "t").data_ptr() for P in Ps])
+    op = (ct.c_void_p * S)(*[o.data_ptr() for o in outs])
+    ids = (ct.c_int32 * S)(*[int(s) for s in source_ids])
     check(handle(), lib.mdb_warp(handle(), _p(disp), _p(x), Rp, tp, ids, S, _k9(Ks), _k9(invKs), W, H, Cc, L, N,
                                  float(min_depth), float(max_depth), op, _stream()))
     return outs
@@ -242,7 +242,7 @@ def prediction_loss(ssim: SSIM, predictions: Sequence[torch.Tensor], target: tor
     _chk(target, "target")
     N, Cc, H, W = target.shape
     S = len(predictions)
-    pp = (C.c_void_p * S)(*[_chk(p, "prediction").data_ptr() for p in predictions])
+    pp = (ct.c_void_p * S)(*[_chk(p, "prediction").data_ptr() for p in predictions])
     out = torch.empty((N, 1, H, W), device=target.device, dtype=torch.float32)
     check(handle(), lib.mdb_prediction_loss(handle(), pp, S, _p(target), W, H, Cc, N, alpha, ssim.c1, ssim.c2, _p(out), _stream()))
     return out
@@ -254,7 +254,7 @@ def automasking_loss(ssim: SSIM, inputs: torch.Tensor, target_id: int, *, source
     _chk(inputs, "inputs")
     N, L, Cc, H, W = inputs.shape
     S = len(source_ids)
-    ids = (C.c_int32 * S)(*[int(s) for s in source_ids])
+    ids = (ct.c_int32 * S)(*[int(s) for s in source_ids])
     out = torch.empty((N, 1, H, W), device=inputs.device, dtype=torch.float32)
     check(handle(), lib.mdb_automasking_loss(handle(), _p(inputs), int(target_id), ids, S, W, H, Cc, L, N, alpha, ssim.c1, ssim.c2, _p(out), _stream()))
     return out
@@ -308,7 +308,7 @@ class FusedLoss:
         self.S = len(source_ids)
         self.Ls = len(scales)
         p = _lib.LossParams()
-        lib.mdb_loss_params_default(C.byref(p))
+        lib.mdb_loss_params_default(ct.byref(p))
         p.min_depth, p.max_depth, p.disparity_smoothness, p.alpha = min_depth, max_depth, disparity_smoothness, alpha
         p.automasking = int(automasking)
         p.normalize_disparity = int(normalize_disparity)
@@ -342,7 +342,7 @@ class FusedLoss:
             io.d_rvec[s] = self.d_rvec[s].data_ptr()
             io.d_tvec[s] = self.d_tvec[s].data_ptr()
         io.vis_warp_loss = self.vis.data_ptr() if want_vis else None
-        self.ws_bytes = int(lib.mdb_train_loss_workspace_bytes(C.byref(io)))
+        self.ws_bytes = int(lib.mdb_train_loss_workspace_bytes(ct.byref(io)))
         if self.ws_bytes == 0:
             raise _lib.MdbError(_lib.lib.mdb_version() * 0 - 2, "unsupported shape for the fused loss")
         self.ws = torch.empty(self.ws_bytes, dtype=torch.uint8, device=self.dev)
@@ -364,7 +364,7 @@ class FusedLoss:
             io.tvec[s] = _chk(pz.tvec, "tvec").data_ptr()
         io.auto_loss = _chk(auto_loss, "auto_loss").data_ptr() if auto_loss is not None else None
         h = handle()
-        check(h, lib.mdb_train_loss_fwdbwd(h, C.byref(io), C.byref(self.params), _p(self.ws), self.ws_bytes, _stream()))
+        check(h, lib.mdb_train_loss_fwdbwd(h, ct.byref(io), ct.byref(self.params), _p(self.ws), self.ws_bytes, _stream()))
         return LossResult(self.loss, self.d_disp, [Pose(r, t) for r, t in zip(self.d_rvec, self.d_tvec)], self.vis)
 
 
