@@ -61,9 +61,9 @@ int64_t mdb_launch_count(const mdb_handle* h);
 
 /* ---- parameters of the loss ---------------------------------------------------------- */
 typedef struct mdb_loss_params {
-  float min_depth;            /* Params.min_depth            src/Monodepth.jl:38 (0.1)   */
-  float max_depth;            /* Params.max_depth            src/Monodepth.jl:39 (100)   */
-  float disparity_smoothness; /* Params.disparity_smoothness src/Monodepth.jl:40 (1e-3)  */
+  double min_depth;           /* Params.min_depth (Float64)  src/Monodepth.jl:38 (0.1)   */
+  double max_depth;           /* Params.max_depth (Float64)  src/Monodepth.jl:39 (100)   */
+  double disparity_smoothness;/* Params.disparity_smoothness src/Monodepth.jl:40 (1e-3)  */
   float alpha;                /* photometric_loss alpha      src/training.jl:2   (0.85)  */
   float ssim_c1;              /* SSIM c1 = 0.01^2            src/utils.jl:23            */
   float ssim_c2;              /* SSIM c2 = 0.03^2            src/utils.jl:23            */
@@ -73,7 +73,6 @@ typedef struct mdb_loss_params {
                                  1: weight 1 (src/simple_depth.jl:39)                    */
   int32_t upsample_align_corners; /* NNlib upsample_bilinear default = 1 (unpinned)      */
   int32_t n_global;           /* batch size the means divide by; 0 = N (single GPU)      */
-  int32_t reserved;
 } mdb_loss_params;
 
 void mdb_loss_params_default(mdb_loss_params* p);
@@ -95,8 +94,8 @@ int32_t mdb_compose_T_bwd(mdb_handle* h, const float* rvec, const float* tvec, i
 
 /* ---- P5-P8: depth / backproject / project / sample ---------------------------------- */
 /* disparity_to_depth, elementwise over n values                  src/utils.jl:179-183 */
-int32_t mdb_disparity_to_depth(mdb_handle* h, const float* disparity, int64_t n, float min_depth,
-                               float max_depth, float* depth, void* stream);
+int32_t mdb_disparity_to_depth(mdb_handle* h, const float* disparity, int64_t n, double min_depth,
+                               double max_depth, float* depth, void* stream);
 /* (b::Backproject)(depth (1,WH,N), invK) -> points (3,WH,N)      src/utils.jl:45-69   */
 int32_t mdb_backproject(mdb_handle* h, const float* depth, const float* invK, int32_t W,
                         int32_t H, int32_t N, float* points, void* stream);
@@ -114,7 +113,7 @@ int32_t mdb_grid_sample(mdb_handle* h, const float* input, const float* grid, in
 int32_t mdb_warp(mdb_handle* h, const float* disp, const float* x, const float* const* R,
                  const float* const* t, const int32_t* source_ids, int32_t S, const float* K,
                  const float* invK, int32_t W, int32_t H, int32_t C, int32_t L, int32_t N,
-                 float min_depth, float max_depth, float* const* warped, void* stream);
+                 double min_depth, double max_depth, float* const* warped, void* stream);
 
 /* ---- P9-P11: SSIM / photometric / min-reprojection / automask ------------------------ */
 /* (ssim::SSIM)(x, y) -> (W,H,C,N)                                src/utils.jl:17-43   */

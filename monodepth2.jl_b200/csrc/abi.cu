@@ -45,9 +45,9 @@ int64_t mdb_launch_count(const mdb_handle* h) { return h ? h->launches : 0; }
 
 void mdb_loss_params_default(mdb_loss_params* p) {
   if (!p) return;
-  p->min_depth = 0.1f;
-  p->max_depth = 100.0f;
-  p->disparity_smoothness = 1e-3f;
+  p->min_depth = 0.1;
+  p->max_depth = 100.0;
+  p->disparity_smoothness = 1e-3;
   p->alpha = 0.85f;
   p->ssim_c1 = 0.01f * 0.01f;
   p->ssim_c2 = 0.03f * 0.03f;
@@ -56,7 +56,6 @@ void mdb_loss_params_default(mdb_loss_params* p) {
   p->smooth_weight_mode = 0;
   p->upsample_align_corners = 1;
   p->n_global = 0;
-  p->reserved = 0;
 }
 
 }  // extern "C"

@@ -31,7 +31,7 @@ struct PoseArgs {
   int N, S;
 };
 
-__global__ void pose_prep_kernel(PoseArgs a, PosePrep* __restrict__ out) {
+__global__ void pose_prep_kernel(PoseArgs a, PosePrep* __restrict__ out, PosePrepD* __restrict__ outd) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= a.N * a.S) return;
   const int n = idx / a.S, s = idx % a.S;
@@ -42,10 +42,14 @@ __global__ void pose_prep_kernel(PoseArgs a, PosePrep* __restrict__ out) {
   mat3_mul(a.K, Rp, KR);
   mat3_mul(KR, a.invK, A);
   PosePrep p;
-  for (int k = 0; k < 9; ++k) p.dA[k] = (float)(A[k] - ((k % 4 == 0) ? 1.0 : 0.0));
-  for (int i = 0; i < 3; ++i)
-    p.b[i] = (float)(a.K[3 * i] * tp[0] + a.K[3 * i + 1] * tp[1] + a.K[3 * i + 2] * tp[2]);
+  PosePrepD pd;
+  for (int k = 0; k < 9; ++k) { pd.dA[k] = A[k] - ((k % 4 == 0) ? 1.0 : 0.0); p.dA[k] = (float)pd.dA[k]; }
+  for (int i = 0; i < 3; ++i) {
+    pd.b[i] = a.K[3 * i] * tp[0] + a.K[3 * i + 1] * tp[1] + a.K[3 * i + 2] * tp[2];
+    p.b[i] = (float)pd.b[i];
+  }
   out[idx] = p;
+  outd[idx] = pd;
 }
 
 // ---------------------------------------------------------------------------------------

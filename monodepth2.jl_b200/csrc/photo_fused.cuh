@@ -22,6 +22,11 @@ struct PosePrep {
   float b[3];
 };
 
+struct PosePrepD {  // the same constants in double: the geometric chain runs in double
+  double dA[9];
+  double b[3];
+};
+
 struct ScaleStat {
   float inv_mp;  // 1 / (mean(disparity) + 1e-7), or 1 when the disparity is not normalised
   float cconst;  // constant added to every full-res disparity gradient (mean-normalisation term)
@@ -43,6 +48,9 @@ struct FusedArgs {
   float kx[MDB_MAX_SCALES], ky[MDB_MAX_SCALES];  // smoothness weights incl. 1/Ls and the means
   const float* auto_loss;
   float mind, dd;               // 1/max_depth, 1/min_depth - 1/max_depth
+  double mind_d, dd_d;          // the same in double
+  double rxd[MDB_MAX_SCALES], ryd[MDB_MAX_SCALES];
+  const PosePrepD* ppd;         // [N][S]
   float alpha, c1, c2;
   int automask;
   float up;                     // 1 / (W H N_global Ls)
@@ -78,58 +86,71 @@ MDB_DEV void upsample_coords(int g, float r, int dn, int& i0, int& i1, float& l)
   i1 = min(i0 + 1, dn - 1);
 }
 
-struct Proj {
-  float fu, fv;    // displacement (u - w, v - h) of the projected point, unclamped
-  float zinv;      // 1 / (P3 + 1e-7)
-  float aq0, aq1, aq2;  // A q
-};
-
-// Projection of pixel (px, py) (1-based, as floats) at `depth` into a source frame.
-// Reference chain: Backproject (src/utils.jl:67-69) -> Project (src/utils.jl:99-103) ->
-// normalize -> grid_sample's unnormalize, which cancel to the pixel coordinate u = P1/(P3+1e-7).
-// Computed as a displacement:  u - w = (P1 - w z') / z'  with  A = I + dA, so that
-// P1 - w z' = depth (dA1.q - w dA3.q) + b1 - w (b3 + 1e-7): no large terms cancel.
-MDB_DEV Proj project_flow(const PosePrep& pp, float depth, float px, float py) {
-  Proj r;
-  const float d0 = fmaf(pp.dA[0], px, fmaf(pp.dA[1], py, pp.dA[2]));
-  const float d1 = fmaf(pp.dA[3], px, fmaf(pp.dA[4], py, pp.dA[5]));
-  const float d2 = fmaf(pp.dA[6], px, fmaf(pp.dA[7], py, pp.dA[8]));
-  r.aq0 = px + d0;
-  r.aq1 = py + d1;
-  r.aq2 = 1.0f + d2;
-  const float b3e = pp.b[2] + 1e-7f;
-  const float z = fmaf(depth, r.aq2, b3e);
-  r.zinv = 1.0f / z;
-  const float nu = fmaf(depth, fmaf(-px, d2, d0), fmaf(-px, b3e, pp.b[0]));
-  const float nv = fmaf(depth, fmaf(-py, d2, d1), fmaf(-py, b3e, pp.b[1]));
-  r.fu = nu * r.zinv;
-  r.fv = nv * r.zinv;
-  return r;
-}
-
 struct Taps {
   int o00, o01, o10, o11;  // offsets inside one channel plane
   float fx, fy;            // fractional weights
   float mx, my;            // 1 if the coordinate was not clamped (gradient flows), else 0
 };
 
-// NNlib grid_sample(padding_mode=:border), align-corners=true, composed with `normalize`:
-// sample position = clamp(u, 1, W) (1-based).  Gradient is zero where clamped.
-MDB_DEV Taps make_taps(float fu, float fv, int gx, int gy, int W, int H) {
+struct Samp {
   Taps t;
-  const float lox = -(float)gx, hix = (float)(W - 1 - gx);
-  const float loy = -(float)gy, hiy = (float)(H - 1 - gy);
+  float fu, fv;  // displacement (u - w, v - h) of the projected point, unclamped
+  float zinv;    // 1 / z'',  z'' = A3.q + invd (b3 + 1e-7)
+};
+
+// Projection of the 0-based pixel (gx, gy) with inverse depth `invd` into a source frame, and
+// the bilinear taps there.  Reference chain: disparity_to_depth (src/utils.jl:179-183) ->
+// Backproject (:67-69) -> Project (:99-103) -> normalize -> grid_sample's unnormalize, which
+// cancel to the pixel coordinate u = P1 / (P3 + 1e-7), P = depth (A q) + b.  Dividing through by
+// depth (invd = 1/depth = d (1/min - 1/max) + 1/max needs no division) and writing A = I + dA:
+//   u - w = [ (dA1.q - w dA3.q) + invd (b1 - w (b3 + 1e-7)) ] / [ 1 + dA3.q + invd (b3 + 1e-7) ]
+// This short chain runs in DOUBLE.  Displacements reach hundreds of pixels (f t / depth), so a
+// float32 chain leaves ~1e-5 px of error, part of it coherent over the image (rounded
+// constants); the SSIM pullback amplifies that to ~1e-4 relative in the pose gradients, and it
+// flips which bilinear cell a sample falls in (the only discontinuity of the pullback) a few
+// times per image.  In double both effects vanish, for ~30 FP64 ops per sample on a part whose
+// FP64 rate is half its FP32 rate.  Then NNlib grid_sample(padding_mode=:border),
+// align-corners=true: sample position = clamp(u, 1, W); gradient is zero where clamped.
+MDB_DEV Samp sample_coords(const PosePrepD& pp, double invd, int gx, int gy, int W, int H) {
+  Samp r;
+  const double px = (double)(gx + 1), py = (double)(gy + 1);
+  const double d0 = fma(pp.dA[0], px, fma(pp.dA[1], py, pp.dA[2]));
+  const double d1 = fma(pp.dA[3], px, fma(pp.dA[4], py, pp.dA[5]));
+  const double d2 = fma(pp.dA[6], px, fma(pp.dA[7], py, pp.dA[8]));
+  const double b3e = pp.b[2] + 1e-7;
+  const double z = fma(invd, b3e, 1.0 + d2);
+  double zi = (double)__frcp_rn((float)z);     // float seed + one Newton step = ~1e-14 relative
+  zi = fma(zi, fma(-z, zi, 1.0), zi);
+  const double fu = fma(invd, fma(-px, b3e, pp.b[0]), fma(-px, d2, d0)) * zi;
+  const double fv = fma(invd, fma(-py, b3e, pp.b[1]), fma(-py, d2, d1)) * zi;
+  const double lox = 1.0 - px, hix = (double)W - px, loy = 1.0 - py, hiy = (double)H - py;
+  Taps& t = r.t;
   t.mx = (fu > lox && fu < hix) ? 1.0f : 0.0f;
   t.my = (fv > loy && fv < hiy) ? 1.0f : 0.0f;
-  const float cu = fminf(fmaxf(fu, lox), hix), cv = fminf(fmaxf(fv, loy), hiy);
-  const float flx = floorf(cu), fly = floorf(cv);
-  t.fx = cu - flx;
-  t.fy = cv - fly;
+  const double cu = fmin(fmax(fu, lox), hix), cv = fmin(fmax(fv, loy), hiy);
+  const double flx = floor(cu), fly = floor(cv);
+  t.fx = (float)(cu - flx);
+  t.fy = (float)(cv - fly);
   const int x0 = gx + (int)flx, y0 = gy + (int)fly;
   const int x1 = min(x0 + 1, W - 1), y1 = min(y0 + 1, H - 1);
   t.o00 = y0 * W + x0; t.o01 = y0 * W + x1;
   t.o10 = y1 * W + x0; t.o11 = y1 * W + x1;
-  return t;
+  r.fu = (float)fu;
+  r.fv = (float)fv;
+  r.zinv = (float)zi;
+  return r;
+}
+
+// double-precision bilinear upsample (align-corners) of a native disparity map
+MDB_DEV double upsample_at_d(const float* __restrict__ d, int dw, int dh, double rx, double ry, int gx, int gy) {
+  const double fx = gx * rx, fy = gy * ry;
+  const int x0 = min((int)fx, dw - 1), y0 = min((int)fy, dh - 1);
+  const double lx = fx - x0, ly = fy - y0;
+  const int x1 = min(x0 + 1, dw - 1), y1 = min(y0 + 1, dh - 1);
+  const double v00 = ldg(d + (size_t)y0 * dw + x0), v01 = ldg(d + (size_t)y0 * dw + x1);
+  const double v10 = ldg(d + (size_t)y1 * dw + x0), v11 = ldg(d + (size_t)y1 * dw + x1);
+  const double top = fma(lx, v01 - v00, v00), bot = fma(lx, v11 - v10, v10);
+  return fma(ly, bot - top, top);
 }
 
 // SSIM of one 3x3 window and the coefficients of its pullback.  Reference: src/utils.jl:29-43.

@@ -81,7 +81,7 @@ __global__ void finalize_loss_kernel(const double* __restrict__ item_loss, int N
 }
 
 struct FusedLayout {
-  size_t o_pp, o_statpart, o_stats, o_partials, o_itemloss, o_gfull[MDB_MAX_SCALES], total;
+  size_t o_pp, o_ppd, o_statpart, o_stats, o_partials, o_itemloss, o_gfull[MDB_MAX_SCALES], total;
   int tiles_x, tiles_y, rowblocks, npart;
 };
 
@@ -94,6 +94,7 @@ FusedLayout fused_layout(const mdb_loss_io* io) {
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off = mdb_align_up(off + bytes, 256); return o; };
   L.o_pp = take(sizeof(PosePrep) * io->N * io->S);
+  L.o_ppd = take(sizeof(PosePrepD) * io->N * io->S);
   L.o_statpart = take(sizeof(float) * (size_t)io->N * L.rowblocks * io->Ls * 3);
   L.o_stats = take(sizeof(ScaleStat) * (size_t)io->Ls * io->N);
   L.o_partials = take(sizeof(float) * (size_t)io->N * L.tiles_x * L.tiles_y * L.npart);
@@ -177,8 +178,10 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
   for (int s = 0; s < Ls; ++s) {
     fa.disp[s] = io->disparity[s]; fa.dw[s] = io->dw[s]; fa.dh[s] = io->dh[s];
     fa.native[s] = (io->dw[s] == W && io->dh[s] == H) ? 1 : 0;
-    fa.rx[s] = (float)((double)(io->dw[s] - 1) / (double)(W - 1));
-    fa.ry[s] = (float)((double)(io->dh[s] - 1) / (double)(H - 1));
+    fa.rxd[s] = (double)(io->dw[s] - 1) / (double)(W - 1);
+    fa.ryd[s] = (double)(io->dh[s] - 1) / (double)(H - 1);
+    fa.rx[s] = (float)fa.rxd[s];
+    fa.ry[s] = (float)fa.ryd[s];
     fa.gout[s] = fa.native[s] ? io->d_disparity[s] : (float*)(ws + L.o_gfull[s]);
     const double wsm = p->smooth_weight_mode == 0 ? (double)p->disparity_smoothness * (double)io->scale[s] : 1.0;
     fa.kx[s] = (float)(wsm / ((double)Ls * (double)(W - 1) * H * Ng));
@@ -186,8 +189,11 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
   }
   fa.auto_loss = p->automasking ? io->auto_loss : nullptr;
   fa.automask = p->automasking ? 1 : 0;
-  fa.mind = 1.0f / p->max_depth;
-  fa.dd = 1.0f / p->min_depth - 1.0f / p->max_depth;
+  fa.mind_d = 1.0 / p->max_depth;
+  fa.dd_d = 1.0 / p->min_depth - 1.0 / p->max_depth;
+  fa.mind = (float)fa.mind_d;
+  fa.dd = (float)fa.dd_d;
+  fa.ppd = (const PosePrepD*)(ws + L.o_ppd);
   fa.alpha = p->alpha; fa.c1 = p->ssim_c1; fa.c2 = p->ssim_c2;
   const double up = 1.0 / ((double)W * H * Ng * Ls);
   fa.up = (float)up;
@@ -197,7 +203,7 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
   fa.vis = io->vis_warp_loss;
   fa.tiles_x = L.tiles_x; fa.tiles_y = L.tiles_y;
 
-  pose_prep_kernel<<<(N * S + 127) / 128, 128, 0, st>>>(pa, (PosePrep*)(ws + L.o_pp));
+  pose_prep_kernel<<<(N * S + 127) / 128, 128, 0, st>>>(pa, (PosePrep*)(ws + L.o_pp), (PosePrepD*)(ws + L.o_ppd));
   MDB_LAUNCHED(h);
   {
     dim3 grid(L.rowblocks, N);

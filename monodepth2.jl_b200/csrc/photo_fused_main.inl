@@ -13,7 +13,9 @@ struct FusedSmem {
   static constexpr int o_wy = o_wx + WXN;
   static constexpr int o_red = o_wy + WYN;
   static constexpr int o_pp = o_red + (FUSED_THREADS / 32) * NPART;
-  static constexpr int o_sel = o_pp + S * 12;  // bytes from here on
+  static constexpr int o_ppd = (o_pp + S * 12 + 1) / 2 * 2;   // 8-byte aligned doubles
+  static constexpr int o_invd = o_ppd + S * 24;
+  static constexpr int o_sel = o_invd + 2 * R2N;  // bytes from here on
   static constexpr size_t bytes = (size_t)o_sel * 4 + ((R1N + 15) / 16) * 16;
 };
 
@@ -30,6 +32,8 @@ photo_fused_kernel(const __grid_constant__ FusedArgs a) {
   float* s_wy = smem + SM::o_wy;
   float* s_red = smem + SM::o_red;
   PosePrep* s_pp = reinterpret_cast<PosePrep*>(smem + SM::o_pp);
+  PosePrepD* s_ppd = reinterpret_cast<PosePrepD*>(smem + SM::o_ppd);
+  double* s_invd = reinterpret_cast<double*>(smem + SM::o_invd);
   unsigned char* s_sel = reinterpret_cast<unsigned char*>(smem + SM::o_sel);
 
   const int tid = threadIdx.x;
@@ -42,7 +46,10 @@ photo_fused_kernel(const __grid_constant__ FusedArgs a) {
 #pragma unroll
   for (int s = 0; s < S; ++s) srcp[s] = a.x + ((size_t)n * a.L + a.src[s]) * C * plane;
 
-  if (tid < S * 12) reinterpret_cast<float*>(s_pp)[tid] = reinterpret_cast<const float*>(a.pp + (size_t)n * S)[tid];
+  if (tid < S * 12) {
+    reinterpret_cast<float*>(s_pp)[tid] = reinterpret_cast<const float*>(a.pp + (size_t)n * S)[tid];
+    reinterpret_cast<double*>(s_ppd)[tid] = reinterpret_cast<const double*>(a.ppd + (size_t)n * S)[tid];
+  }
 
   // ---- phase 0: target tile + 2-pixel halo, smoothness edge weights ------------------
   for (int i = tid; i < R2N; i += FUSED_THREADS) {
@@ -98,15 +105,15 @@ photo_fused_kernel(const __grid_constant__ FusedArgs a) {
     for (int i = tid; i < R2N; i += FUSED_THREADS) {
       const int gx = X0 - 2 + i % R2W, gy = Y0 - 2 + i / R2W;
       if (gx < 0 || gx >= W || gy < 0 || gy >= H) continue;
-      const float d = native ? ldg(dsp + (size_t)gy * W + gx)
-                             : upsample_at(dsp, a.dw[sc], a.dh[sc], a.rx[sc], a.ry[sc], gx, gy);
-      s_dsp[i] = d;
-      const float depth = 1.0f / fmaf(d, a.dd, a.mind);
-      const float px = (float)(gx + 1), py = (float)(gy + 1);
+      const double dd_ = native ? (double)ldg(dsp + (size_t)gy * W + gx)
+                                : upsample_at_d(dsp, a.dw[sc], a.dh[sc], a.rxd[sc], a.ryd[sc], gx, gy);
+      s_dsp[i] = (float)dd_;
+      s_invd[i] = fma(dd_, a.dd_d, a.mind_d);   // 1 / depth  (src/utils.jl:179-183)
+      const double invd = s_invd[i];
 #pragma unroll
       for (int s = 0; s < S; ++s) {
-        const Proj pr = project_flow(s_pp[s], depth, px, py);
-        const Taps t = make_taps(pr.fu, pr.fv, gx, gy, W, H);
+        const Samp sp = sample_coords(s_ppd[s], invd, gx, gy, W, H);
+        const Taps& t = sp.t;
 #pragma unroll
         for (int c = 0; c < C; ++c) {
           const float* p = srcp[s] + c * plane;
@@ -226,17 +233,19 @@ photo_fused_kernel(const __grid_constant__ FusedArgs a) {
           }
         }
       const float d = s_dsp[r2];
-      const float depth = 1.0f / fmaf(d, a.dd, a.mind);
+      const double invd_d = s_invd[r2];
+      const float invd = (float)invd_d;
       const float px = (float)(gx + 1), py = (float)(gy + 1);
-      float ddepth = 0.0f;
+      float dinvd = 0.0f;
 #pragma unroll
       for (int s = 0; s < S; ++s) {
         bool any = false;
 #pragma unroll
         for (int c = 0; c < C; ++c) any |= (G[s][c] != 0.0f);
         if (!any) continue;
-        const Proj pr = project_flow(s_pp[s], depth, px, py);
-        const Taps t = make_taps(pr.fu, pr.fv, gx, gy, W, H);
+        const PosePrep& pp = s_pp[s];
+        const Samp sp = sample_coords(s_ppd[s], invd_d, gx, gy, W, H);
+        const Taps& t = sp.t;
         float gu = 0.0f, gv = 0.0f;
 #pragma unroll
         for (int c = 0; c < C; ++c) {
@@ -249,18 +258,18 @@ photo_fused_kernel(const __grid_constant__ FusedArgs a) {
         }
         gu *= t.mx * a.up;
         gv *= t.my * a.up;
-        // u = P1 / z', v = P2 / z'
-        const float u = px + pr.fu, v = py + pr.fv;
-        const float dP0 = gu * pr.zinv, dP1 = gv * pr.zinv, dP2 = -(gu * u + gv * v) * pr.zinv;
-        ddepth += dP0 * pr.aq0 + dP1 * pr.aq1 + dP2 * pr.aq2;
-        const float q0 = depth * px, q1 = depth * py;
-        pacc[s][0] = fmaf(dP0, q0, pacc[s][0]); pacc[s][1] = fmaf(dP0, q1, pacc[s][1]); pacc[s][2] = fmaf(dP0, depth, pacc[s][2]);
-        pacc[s][3] = fmaf(dP1, q0, pacc[s][3]); pacc[s][4] = fmaf(dP1, q1, pacc[s][4]); pacc[s][5] = fmaf(dP1, depth, pacc[s][5]);
-        pacc[s][6] = fmaf(dP2, q0, pacc[s][6]); pacc[s][7] = fmaf(dP2, q1, pacc[s][7]); pacc[s][8] = fmaf(dP2, depth, pacc[s][8]);
-        pacc[s][9] += dP0; pacc[s][10] += dP1; pacc[s][11] += dP2;
+        // u = P'1 / z'', v = P'2 / z''  with  P' = A q + invd b,  z'' = P'3 + invd 1e-7
+        const float u = px + sp.fu, v = py + sp.fv;
+        const float dP0 = gu * sp.zinv, dP1 = gv * sp.zinv, dP2 = -(gu * u + gv * v) * sp.zinv;
+        dinvd += dP0 * pp.b[0] + dP1 * pp.b[1] + dP2 * (pp.b[2] + 1e-7f);
+        pacc[s][0] = fmaf(dP0, px, pacc[s][0]); pacc[s][1] = fmaf(dP0, py, pacc[s][1]); pacc[s][2] += dP0;
+        pacc[s][3] = fmaf(dP1, px, pacc[s][3]); pacc[s][4] = fmaf(dP1, py, pacc[s][4]); pacc[s][5] += dP1;
+        pacc[s][6] = fmaf(dP2, px, pacc[s][6]); pacc[s][7] = fmaf(dP2, py, pacc[s][7]); pacc[s][8] += dP2;
+        pacc[s][9] = fmaf(dP0, invd, pacc[s][9]); pacc[s][10] = fmaf(dP1, invd, pacc[s][10]);
+        pacc[s][11] = fmaf(dP2, invd, pacc[s][11]);
       }
-      // d depth / d disparity  (src/utils.jl:179-183)
-      float g = -ddepth * depth * depth * a.dd;
+      // d invd / d disparity = 1/min_depth - 1/max_depth
+      float g = dinvd * a.dd;
       // smoothness pullback (src/utils.jl:163-177), mean-normalisation constant from disp_stats
       float gsx = 0.0f, gsy = 0.0f;
       if (gx + 1 < W) gsx += sgnf(d - s_dsp[r2 + 1]) * s_wx[iy * (TW + 1) + ix + 1];

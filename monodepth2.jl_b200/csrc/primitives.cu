@@ -75,20 +75,19 @@ __global__ void grid_sample_kernel(const float* __restrict__ in, const float* __
 // warp (P13): disparity -> depth -> backproject -> project -> sample, per source.
 struct WarpArgs {
   const float* disp; const float* x; float* out[MDB_MAX_SOURCES];
-  PosePrep pp_unused;
-  const PosePrep* pp; int src[MDB_MAX_SOURCES];
-  int S, W, H, C, L, N; float mind, dd;
+  const PosePrep* pp; const PosePrepD* ppd; int src[MDB_MAX_SOURCES];
+  int S, W, H, C, L, N; float mind, dd; double mind_d, dd_d;
 };
 
-__global__ void warp_kernel(WarpArgs a) {
+__global__ void warp_kernel(const __grid_constant__ WarpArgs a) {
   const int64_t wh = (int64_t)a.W * a.H, total = wh * a.N;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int n = (int)(i / wh);
     const int pix = (int)(i % wh), gx = pix % a.W, gy = pix / a.W;
-    const float depth = 1.0f / fmaf(a.disp[i], a.dd, a.mind);
+    const double invd = fma((double)a.disp[i], a.dd_d, a.mind_d);
     for (int s = 0; s < a.S; ++s) {
-      const Proj pr = project_flow(a.pp[n * a.S + s], depth, (float)(gx + 1), (float)(gy + 1));
-      const Taps t = make_taps(pr.fu, pr.fv, gx, gy, a.W, a.H);
+      const Samp sp = sample_coords(a.ppd[n * a.S + s], invd, gx, gy, a.W, a.H);
+      const Taps& t = sp.t;
       for (int c = 0; c < a.C; ++c) {
         const float* p = a.x + (((size_t)n * a.L + a.src[s]) * a.C + c) * wh;
         const float v00 = p[t.o00], v01 = p[t.o01], v10 = p[t.o10], v11 = p[t.o11];
@@ -101,7 +100,7 @@ __global__ void warp_kernel(WarpArgs a) {
 
 // pose constants from already-composed (R, t) (Julia layout), for mdb_warp
 struct WarpPoseArgs { const float* R[MDB_MAX_SOURCES]; const float* t[MDB_MAX_SOURCES]; double K[9], invK[9]; int N, S; };
-__global__ void warp_pose_kernel(WarpPoseArgs a, PosePrep* __restrict__ out) {
+__global__ void warp_pose_kernel(WarpPoseArgs a, PosePrep* __restrict__ out, PosePrepD* __restrict__ outd) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= a.N * a.S) return;
   const int n = idx / a.S, s = idx % a.S;
@@ -113,12 +112,14 @@ __global__ void warp_pose_kernel(WarpPoseArgs a, PosePrep* __restrict__ out) {
   for (int i = 0; i < 3; ++i)
     for (int j = 0; j < 3; ++j) { double v = 0; for (int k = 0; k < 3; ++k) v += KR[3 * i + k] * a.invK[3 * k + j]; A[3 * i + j] = v; }
   PosePrep p;
-  for (int k = 0; k < 9; ++k) p.dA[k] = (float)(A[k] - ((k % 4 == 0) ? 1.0 : 0.0));
+  PosePrepD pd;
+  for (int k = 0; k < 9; ++k) { pd.dA[k] = A[k] - ((k % 4 == 0) ? 1.0 : 0.0); p.dA[k] = (float)pd.dA[k]; }
   for (int i = 0; i < 3; ++i) {
     double v = 0; for (int k = 0; k < 3; ++k) v += a.K[3 * i + k] * (double)a.t[s][3 * n + k];
-    p.b[i] = (float)v;
+    pd.b[i] = v; p.b[i] = (float)v;
   }
   out[idx] = p;
+  outd[idx] = pd;
 }
 
 // ---- SSIM / photometric, one thread per output pixel ----------------------------------
@@ -236,11 +237,11 @@ Mat3 to_math(const float* cm) { Mat3 m; for (int i = 0; i < 3; ++i) for (int j =
 
 extern "C" {
 
-int32_t mdb_disparity_to_depth(mdb_handle* h, const float* disparity, int64_t n, float min_depth,
-                               float max_depth, float* depth, void* stream) {
+int32_t mdb_disparity_to_depth(mdb_handle* h, const float* disparity, int64_t n, double min_depth,
+                               double max_depth, float* depth, void* stream) {
   MDB_REQUIRE(h, h && disparity && depth && n > 0, MDB_E_INVALID_ARG, "mdb_disparity_to_depth: bad argument");
-  const float mind = 1.0f / max_depth, maxd = 1.0f / min_depth;
-  d2d_kernel<<<grid_for(h, n, 256), 256, 0, (cudaStream_t)stream>>>(disparity, n, mind, maxd - mind, depth);
+  const double mind = 1.0 / max_depth, maxd = 1.0 / min_depth;
+  d2d_kernel<<<grid_for(h, n, 256), 256, 0, (cudaStream_t)stream>>>(disparity, n, (float)mind, (float)(maxd - mind), depth);
   MDB_LAUNCHED(h);
   return MDB_OK;
 }
@@ -273,7 +274,7 @@ int32_t mdb_grid_sample(mdb_handle* h, const float* input, const float* grid, in
 int32_t mdb_warp(mdb_handle* h, const float* disp, const float* x, const float* const* R,
                  const float* const* t, const int32_t* source_ids, int32_t S, const float* K,
                  const float* invK, int32_t W, int32_t H, int32_t C, int32_t L, int32_t N,
-                 float min_depth, float max_depth, float* const* warped, void* stream) {
+                 double min_depth, double max_depth, float* const* warped, void* stream) {
   MDB_REQUIRE(h, h && disp && x && R && t && source_ids && K && invK && warped, MDB_E_INVALID_ARG, "mdb_warp: null argument");
   MDB_REQUIRE(h, S >= 1 && S <= MDB_MAX_SOURCES && W > 1 && H > 1 && C > 0 && L > 0 && N > 0, MDB_E_SHAPE, "mdb_warp: bad shape");
   cudaStream_t st = (cudaStream_t)stream;
@@ -286,15 +287,19 @@ int32_t mdb_warp(mdb_handle* h, const float* disp, const float* x, const float* 
   }
   for (int i = 0; i < 3; ++i)
     for (int j = 0; j < 3; ++j) { pa.K[3 * i + j] = K[3 * j + i]; pa.invK[3 * i + j] = invK[3 * j + i]; }
-  PosePrep* pp = nullptr;
-  MDB_CUDA(h, cudaMallocAsync((void**)&pp, sizeof(PosePrep) * N * S, st));
-  warp_pose_kernel<<<nblk(N * S, 128), 128, 0, st>>>(pa, pp);
+  char* buf = nullptr;
+  const size_t ppd_off = mdb_align_up(sizeof(PosePrep) * N * S, 256);
+  MDB_CUDA(h, cudaMallocAsync((void**)&buf, ppd_off + sizeof(PosePrepD) * N * S, st));
+  PosePrep* pp = (PosePrep*)buf;
+  PosePrepD* ppd = (PosePrepD*)(buf + ppd_off);
+  warp_pose_kernel<<<nblk(N * S, 128), 128, 0, st>>>(pa, pp, ppd);
   MDB_LAUNCHED(h);
-  wa.disp = disp; wa.x = x; wa.pp = pp; wa.S = S; wa.W = W; wa.H = H; wa.C = C; wa.L = L; wa.N = N;
-  wa.mind = 1.0f / max_depth; wa.dd = 1.0f / min_depth - 1.0f / max_depth;
+  wa.disp = disp; wa.x = x; wa.pp = pp; wa.ppd = ppd; wa.S = S; wa.W = W; wa.H = H; wa.C = C; wa.L = L; wa.N = N;
+  wa.mind_d = 1.0 / max_depth; wa.dd_d = 1.0 / min_depth - 1.0 / max_depth;
+  wa.mind = (float)wa.mind_d; wa.dd = (float)wa.dd_d;
   warp_kernel<<<grid_for(h, (int64_t)W * H * N, 256), 256, 0, st>>>(wa);
   MDB_LAUNCHED(h);
-  MDB_CUDA(h, cudaFreeAsync(pp, st));
+  MDB_CUDA(h, cudaFreeAsync(buf, st));
   return MDB_OK;
 }
 

@@ -20,11 +20,11 @@ c_f32p = C.POINTER(C.c_float)
 
 class LossParams(C.Structure):
     _fields_ = [
-        ("min_depth", C.c_float), ("max_depth", C.c_float), ("disparity_smoothness", C.c_float),
+        ("min_depth", C.c_double), ("max_depth", C.c_double), ("disparity_smoothness", C.c_double),
         ("alpha", C.c_float), ("ssim_c1", C.c_float), ("ssim_c2", C.c_float),
         ("automasking", C.c_int32), ("normalize_disparity", C.c_int32),
         ("smooth_weight_mode", C.c_int32), ("upsample_align_corners", C.c_int32),
-        ("n_global", C.c_int32), ("reserved", C.c_int32),
+        ("n_global", C.c_int32),
     ]
 
 
@@ -58,7 +58,7 @@ def _load() -> C.CDLL:
 
 lib = _load()
 
-_vp, _i32, _i64, _f32, _sz = C.c_void_p, C.c_int32, C.c_int64, C.c_float, C.c_size_t
+_vp, _i32, _i64, _f32, _f64, _sz = C.c_void_p, C.c_int32, C.c_int64, C.c_float, C.c_double, C.c_size_t
 
 # name -> (restype, argtypes); mirrors include/mdb200.h one to one
 PROTOTYPES = {
@@ -73,12 +73,12 @@ PROTOTYPES = {
     "mdb_so3_exp_map": (_i32, [_vp, _vp, _i32, _vp, _vp]),
     "mdb_compose_T": (_i32, [_vp, _vp, _vp, _i32, _i32, _vp, _vp, _vp]),
     "mdb_compose_T_bwd": (_i32, [_vp, _vp, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp]),
-    "mdb_disparity_to_depth": (_i32, [_vp, _vp, _i64, _f32, _f32, _vp, _vp]),
+    "mdb_disparity_to_depth": (_i32, [_vp, _vp, _i64, _f64, _f64, _vp, _vp]),
     "mdb_backproject": (_i32, [_vp, _vp, c_f32p, _i32, _i32, _i32, _vp, _vp]),
     "mdb_project": (_i32, [_vp, _vp, c_f32p, _vp, _vp, _i32, _i32, _i32, _vp, _vp]),
     "mdb_grid_sample": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
     "mdb_warp": (_i32, [_vp, _vp, _vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_i32), _i32, c_f32p,
-                        c_f32p, _i32, _i32, _i32, _i32, _i32, _f32, _f32, C.POINTER(_vp), _vp]),
+                        c_f32p, _i32, _i32, _i32, _i32, _i32, _f64, _f64, C.POINTER(_vp), _vp]),
     "mdb_ssim": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _f32, _f32, _vp, _vp]),
     "mdb_photometric_loss": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _f32, _f32, _f32, _vp, _vp]),
     "mdb_prediction_loss": (_i32, [_vp, C.POINTER(_vp), _i32, _vp, _i32, _i32, _i32, _i32, _f32, _f32,
