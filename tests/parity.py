@@ -8,11 +8,11 @@ from oracle import torch_ref as T
 
 LOSS_RTOL = 1e-5
 GRAD_RTOL = 1e-4
-# A pixel whose two per-source losses are equal to within float32 rounding can pick the other
-# arg-min than the float64 oracle; that flips the gradient of that pixel's 3x3 window (a
-# property of min(), not of the implementation -- the reference's own float32 run does the
-# same).  Such pixels are measure-zero; allow a tiny fraction of outliers and bound their size.
-OUTLIER_FRAC = 2e-3
+# The pullback has measure-zero discontinuities (arg-min ties of min(), sign(0) of the L1 term,
+# bilinear cell edges).  The kernel takes the geometric decisions in double so they agree with
+# the float64 oracle; an exact float32 tie of two per-source losses can still pick the other
+# arg-min, so a handful of entries (never more than MAX_OUTLIERS) may disagree.
+MAX_OUTLIERS = 2
 
 
 def oracle_train_loss(inp, dtype=torch.float64, normalize=True, smooth_mode=0, n_global=None):
@@ -36,14 +36,14 @@ def oracle_train_loss(inp, dtype=torch.float64, normalize=True, smooth_mode=0, n
     gs = torch.autograd.grad(loss, disps + [p.rvec for p in poses] + [p.tvec for p in poses])
     nd = len(disps)
     S = len(poses)
-    return dict(loss=float(loss), d_disp=list(gs[:nd]), d_rvec=list(gs[nd:nd + S]), d_tvec=list(gs[nd + S:]),
+    return dict(loss=float(loss.detach()), d_disp=list(gs[:nd]), d_rvec=list(gs[nd:nd + S]), d_tvec=list(gs[nd + S:]),
                 auto=auto)
 
 
-def grad_report(name, got, ref, rtol=GRAD_RTOL):
+def grad_report(name, got, ref, rtol=GRAD_RTOL, scale_floor=0.0):
     got = got.detach().double().cpu().reshape(-1)
     ref = ref.detach().double().cpu().reshape(-1)
-    scale = ref.abs().max().item()
+    scale = max(ref.abs().max().item(), scale_floor)
     err = (got - ref).abs() / max(scale, 1e-300)
     n_out = int((err > rtol).sum())
     inl = err[err <= rtol]
@@ -52,11 +52,11 @@ def grad_report(name, got, ref, rtol=GRAD_RTOL):
                 rel_l2=float((got - ref).norm() / max(ref.norm().item(), 1e-300)))
 
 
-def assert_dense_grad(name, got, ref, rtol=GRAD_RTOL, frac=OUTLIER_FRAC):
-    r = grad_report(name, got, ref, rtol)
-    allowed = max(2, int(frac * r["numel"]))
-    assert r["n_out"] <= allowed, f"{r}"
-    assert r["rel_l2"] < 2e-2, f"{r}"
+def assert_dense_grad(name, got, ref, rtol=GRAD_RTOL, scale_floor=0.0):
+    r = grad_report(name, got, ref, rtol, scale_floor)
+    assert r["n_out"] <= MAX_OUTLIERS, f"{r}"
+    if scale_floor == 0.0:
+        assert r["rel_l2"] < 1e-3, f"{r}"
     return r
 
 

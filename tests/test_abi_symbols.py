@@ -1,0 +1,105 @@
+"""CPU-side checks of the drop-in boundary: the shared library loads, exports every symbol
+include/mdb200.h declares, the ctypes prototypes cover exactly that set, struct layouts agree
+with the C compiler, and the product path refuses to run without a GPU (no CPU fallback)."""
+import ctypes
+import os
+import re
+import subprocess
+import sys
+import tempfile
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "mdb200.h")
+
+
+def _declared():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(mdb_[a-z0-9_A-Z]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    from mdb200 import _lib
+    names = _declared()
+    assert len(names) >= 25
+    for n in names:
+        assert hasattr(_lib.lib, n), f"libmdb200.so does not export {n}"
+    assert sorted(_lib.PROTOTYPES) == names, "ctypes prototypes and header disagree"
+
+
+def test_no_undeclared_exports():
+    from mdb200 import _lib
+    out = subprocess.run(["nm", "-D", "--defined-only", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    exported = sorted(l.split()[-1] for l in out.splitlines() if " T " in l)
+    assert [e for e in exported if not e.startswith("mdb_")] == []
+    assert sorted(e for e in exported if e.startswith("mdb_")) == _declared()
+
+
+def test_struct_layout_matches_c():
+    """sizeof/offsetof of the two ABI structs as gcc sees them vs the ctypes mirrors."""
+    from mdb200 import _lib
+    code = r'''
+#include <stdio.h>
+#include <stddef.h>
+#include "mdb200.h"
+int main(void) {
+  printf("%zu %zu %zu %zu\n", sizeof(mdb_loss_params), offsetof(mdb_loss_params, alpha),
+         offsetof(mdb_loss_params, automasking), offsetof(mdb_loss_params, n_global));
+  printf("%zu %zu %zu %zu %zu %zu %zu\n", sizeof(mdb_loss_io), offsetof(mdb_loss_io, rvec),
+         offsetof(mdb_loss_io, disparity), offsetof(mdb_loss_io, scale), offsetof(mdb_loss_io, K),
+         offsetof(mdb_loss_io, loss), offsetof(mdb_loss_io, vis_warp_loss));
+  return 0;
+}'''
+    with tempfile.TemporaryDirectory() as td:
+        c = os.path.join(td, "t.c"); exe = os.path.join(td, "t")
+        open(c, "w").write(code)
+        subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), c, "-o", exe], check=True)
+        lines = subprocess.run([exe], capture_output=True, text=True, check=True).stdout.split("\n")
+    p, io = _lib.LossParams, _lib.LossIO
+    assert [int(v) for v in lines[0].split()] == [ctypes.sizeof(p), p.alpha.offset, p.automasking.offset, p.n_global.offset]
+    assert [int(v) for v in lines[1].split()] == [ctypes.sizeof(io), io.rvec.offset, io.disparity.offset,
+                                                  io.scale.offset, io.K.offset, io.loss.offset, io.vis_warp_loss.offset]
+
+
+def test_defaults_and_version():
+    from mdb200 import _lib
+    assert _lib.lib.mdb_version() == 100
+    p = _lib.LossParams()
+    _lib.lib.mdb_loss_params_default(ctypes.byref(p))
+    assert (p.min_depth, p.max_depth, p.disparity_smoothness) == (0.1, 100.0, 1e-3)
+    assert abs(p.alpha - 0.85) < 1e-7 and p.automasking == 1 and p.normalize_disparity == 1
+
+
+def test_workspace_query_and_shape_validation_need_no_gpu():
+    from mdb200 import _lib
+    io = _lib.LossIO()
+    io.W, io.H, io.C, io.L, io.N, io.S, io.Ls = 416, 128, 3, 3, 12, 2, 4
+    for k, (w, h) in enumerate([(52, 16), (104, 32), (208, 64), (416, 128)]):
+        io.dw[k], io.dh[k] = w, h
+    ws = _lib.lib.mdb_train_loss_workspace_bytes(ctypes.byref(io))
+    assert ws > 3 * 12 * 416 * 128 * 4  # three low-res scales need a full-res gradient buffer
+    io.C = 2
+    assert _lib.lib.mdb_train_loss_workspace_bytes(ctypes.byref(io)) == 0
+    io.C, io.W = 3, 1
+    assert _lib.lib.mdb_train_loss_workspace_bytes(ctypes.byref(io)) == 0
+
+
+@pytest.mark.skipif(__import__("torch").cuda.is_available(), reason="checks the no-GPU behaviour")
+def test_product_path_fails_loudly_without_gpu():
+    import mdb200
+    from mdb200 import _lib
+    h = ctypes.c_void_p()
+    assert _lib.lib.mdb_create(ctypes.byref(h), 0) == -4  # MDB_E_NO_DEVICE, no CPU fallback
+    with pytest.raises(RuntimeError):
+        mdb200.handle()
+
+
+def test_product_code_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "monodepth2.jl_b200")
+    for dp, _, fs in os.walk(pkg):
+        for f in fs:
+            if f.endswith((".py", ".cu", ".cuh", ".inl", ".jl")):
+                txt = open(os.path.join(dp, f)).read()
+                assert "torch_ref" not in txt and "from oracle" not in txt and "import oracle" not in txt, f

@@ -30,12 +30,12 @@ def _run_gpu(inp, normalize=True, smooth_mode=0, auto=None, n_global=0):
     return res, plan
 
 
-def _compare(inp, ref, res):
+def _compare(inp, ref, res, scale_floor=0.0):
     got = float(res.loss)
     assert abs(got - ref["loss"]) <= P.LOSS_RTOL * abs(ref["loss"]), (got, ref["loss"])
     rep = []
     for k, (g, r) in enumerate(zip(res.d_disparities, ref["d_disp"])):
-        rep.append(P.assert_dense_grad(f"d_disp[{k}]", g, r))
+        rep.append(P.assert_dense_grad(f"d_disp[{k}]", g, r, scale_floor=scale_floor))
     for s in range(len(ref["d_rvec"])):
         rep.append(P.assert_small_grad(f"d_rvec[{s}]", res.d_poses[s].rvec, ref["d_rvec"][s]))
         rep.append(P.assert_small_grad(f"d_tvec[{s}]", res.d_poses[s].tvec, ref["d_tvec"][s]))
@@ -77,7 +77,10 @@ def test_simple_depth_parity():
     inp.tvecs = [np.zeros((1, 1, 3), np.float32) for _ in range(2)]
     ref = P.oracle_train_loss(inp, normalize=False, smooth_mode=1)
     res, _ = _run_gpu(inp, normalize=False, smooth_mode=1)
-    _compare(inp, ref, res)
+    # zero translation => the projection does not depend on depth: d loss / d disp is identically
+    # zero up to the 1e-7 in the projective divide (|ref| ~ 1e-8), so compare it on the scale the
+    # gradient has once the pose moves (the perturbed state below, ~1e-6)
+    _compare(inp, ref, res, scale_floor=1e-6)
     # perturbed state (after a few optimiser steps the disparity is no longer flat)
     inp2 = synth.make_loss_inputs(416, 128, 1, seed=11, scales=(1.0,))
     ref2 = P.oracle_train_loss(inp2, normalize=False, smooth_mode=1)
