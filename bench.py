@@ -1,0 +1,317 @@
+#!/usr/bin/env python
+"""bench.py -- warped px/s of the view-synthesis photometric loss, forward + backward.
+
+Metric (BASELINE.json): warped px/s (loss fwd+bwd).  One *warped pixel* = one (item, scale,
+source, full-res target pixel); one step = one `train_loss` value+gradient evaluation
+(src/training.jl:21-78) over one batch: N * Ls * S * W * H warped pixels.
+
+Workload at every GPU count: BASELINE config 5 geometry -- 1024x320, batch 64 PER GPU
+("scaling": "weak"), 3-frame stacks, 2 sources, 4 scales -- synthetic images / disparities /
+poses from mdb200.synth (no dataset or checkpoint is reachable).  The step's inputs are larger
+than L2 (866 MB vs 126 MB), so no explicit flush is needed between iterations.
+
+  value     device-resident inputs, CUDA-event timed on the launching stream, max over ranks
+  e2e       the same call made through mdb200.train_loss_host with PINNED HOST buffers: every
+            step copies the inputs H2D and the loss + all gradients D2H inside the timed region
+  roofline  the dominant kernel (photo_fused_kernel) timed live with CUDA events recorded
+            inside the C-ABI call (mdb_profile_*), against the algorithmic bytes of SURVEY 8d
+  cpu_baseline / --impl reference
+            the reference's algorithm on the host cores: the torch-CPU float32 restatement
+            (oracle/torch_ref.py, autograd backward), all threads, on a bounded sample.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "monodepth2.jl_b200"), os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+METRIC = "warped px/s (loss fwd+bwd)"
+UNIT = "warped_px/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="config5", choices=["config2", "config3", "config5"])
+    ap.add_argument("--batch", type=int, default=0, help="per-GPU batch override (default: the config's)")
+    ap.add_argument("--cpu-sample-items", type=int, default=4)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            return float(json.load(open(path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def algorithmic_bytes(inp, N):
+    """every distinct input byte once + every output byte once, fp32:
+    4 N [ W H C (1+S) + 2 sum_k w_k h_k + (automask ? W H : 0) ]."""
+    S = len(inp.source_ids)
+    per_item = inp.W * inp.H * inp.C * (1 + S) + 2 * sum(d.shape[-1] * d.shape[-2] for d in inp.disparities)
+    if inp.automasking:
+        per_item += inp.W * inp.H
+    return 4 * N * per_item
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx, self.proc, self.path = gpu_index, None, f"/tmp/mdb_clocks_{os.getpid()}.csv"
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.idx), "-lms", "100"], stdout=open(self.path, "w"),
+                                         stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in open(self.path):
+            f = [c.strip() for c in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def make_inputs(args):
+    from mdb200 import synth
+    kw = dict(synth.CONFIGS[args.config])
+    if args.batch:
+        kw["N"] = args.batch
+    return synth.make_loss_inputs(**kw), kw
+
+
+def cpu_reference_rate(inp, items, steps, warmup):
+    """The reference algorithm on the host cores: torch-CPU float32 restatement, autograd
+    backward, all threads.  Returns (warped px/s, cores, seconds per step)."""
+    import copy
+    import torch
+    import parity as P
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    one = copy.copy(inp)
+    items = min(items, inp.N)
+    one.N = items
+    one.x = inp.x[:items]
+    one.disparities = [d[:items] for d in inp.disparities]
+    one.rvecs = [r[:items] for r in inp.rvecs]
+    one.tvecs = [t[:items] for t in inp.tvecs]
+    units = items * len(inp.disparities) * len(inp.source_ids) * inp.W * inp.H
+    for _ in range(warmup):
+        P.oracle_train_loss(one, dtype=torch.float32)
+    ts = []
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        P.oracle_train_loss(one, dtype=torch.float32)
+        ts.append(time.perf_counter() - t0)
+    t = sum(ts) / len(ts)
+    return units / t, cores, t, items
+
+
+def run_reference(args):
+    rank, _, world = dist_env()
+    if rank != 0:
+        return
+    inp, _ = make_inputs(argparse.Namespace(config=args.config, batch=min(args.batch or 8, 8)))
+    steps, warm = max(1, min(args.steps, 5)), max(1, min(args.warmup, 2))
+    rate, cores, t, items = cpu_reference_rate(inp, args.cpu_sample_items, steps, warm)
+    sample = (f"{items} of the per-GPU batch's items at {inp.W}x{inp.H}, {len(inp.disparities)} scales, "
+              f"{steps} steps after {warm} warm-up (torch-CPU float32 restatement of the Julia path, autograd backward)")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": steps, "warmup": warm, "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.config}: {inp.W}x{inp.H}, CPU sample of {items} items", "timing": "host wall clock"},
+        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import mdb200
+
+    rank, local_rank, world = dist_env()
+    assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU fallback for the product path)"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    inp, kw = make_inputs(args)
+    N, W, H, C = inp.N, inp.W, inp.H, inp.C
+    S, Ls = len(inp.source_ids), len(inp.disparities)
+    Ng = N * world                                    # weak scaling: the global batch grows with the GPU count
+    units_per_rank = N * Ls * S * W * H
+    sizes = [(d.shape[-1], d.shape[-2]) for d in inp.disparities]
+
+    # pinned host copies (e2e) and device-resident copies (value)
+    hx = torch.from_numpy(inp.x).pin_memory()
+    hd = [torch.from_numpy(d).pin_memory() for d in inp.disparities]
+    hr = [torch.from_numpy(r).pin_memory() for r in inp.rvecs]
+    ht = [torch.from_numpy(t).pin_memory() for t in inp.tvecs]
+    x = hx.to(dev); disps = [d.to(dev) for d in hd]
+    poses = [mdb200.Pose(r.to(dev), t.to(dev)) for r, t in zip(hr, ht)]
+    auto = mdb200.automasking_loss(mdb200.SSIM(), x, inp.target_id, source_ids=inp.source_ids) if inp.automasking else None
+    hauto = auto.cpu().pin_memory() if auto is not None else None
+
+    common = dict(W=W, H=H, C=C, L=3, disp_sizes=sizes, scales=inp.scales, target_id=inp.target_id,
+                  source_ids=inp.source_ids, K=inp.K, invK=inp.invK, automasking=inp.automasking)
+    plan = mdb200.FusedLoss(N=N, n_global=Ng, device=dev, **common)
+    # [loss, d_rvec (S,N,3), d_tvec (S,N,3)] of every rank, all-reduced once per step
+    packed = torch.zeros(1 + 6 * S * Ng, device=dev)
+
+    def step():
+        res = plan(x, disps, poses, auto)
+        if world > 1:
+            packed.zero_()
+            packed[0] = res.loss
+            off = 1 + 6 * S * N * rank
+            packed[off:off + 6 * S * N] = torch.cat([t.reshape(-1) for p in res.d_poses for t in (p.rvec, p.tvec)])
+            dist.all_reduce(packed)
+        return res
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    sync_all()
+    sampler = ClockSampler(local_rank)
+    mdb200.profile_begin(args.steps)
+    l0 = mdb200.launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler.start()
+    sync_all()
+    ev0.record()
+    for _ in range(args.steps):
+        res = step()
+    ev1.record()
+    sync_all()
+    clocks = sampler.stop()
+    launches = mdb200.launch_count() - l0
+    ms = torch.tensor([ev0.elapsed_time(ev1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms)
+    seg = np.array([mdb200.profile_read(i) for i in range(args.steps)])  # [steps][4] ms
+    mdb200.profile_begin(0)
+    loss_val = float(packed[0]) if world > 1 else float(res.loss)
+
+    # ---- e2e: host buffers, copies inside the timed region ---------------------------------
+    e2e = None
+    if not args.no_e2e:
+        hplan = mdb200.HostLoss(N=N, n_global=Ng, device=dev, chunk=max(1, N // 8), **common)
+        hposes = [mdb200.Pose(r, t) for r, t in zip(hr, ht)]
+        e_steps = max(3, min(args.steps, 10))
+        for _ in range(3):
+            mdb200.train_loss_host(hplan, hx, hd, hposes, hauto)
+        sync_all()
+        t0 = time.perf_counter()
+        for _ in range(e_steps):
+            hres = mdb200.train_loss_host(hplan, hx, hd, hposes, hauto)   # returns after the D2H of the result
+            if world > 1:
+                dist.all_reduce(packed)                                    # same collective as the device path
+        sync_all()
+        dt = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        e2e = {"value": units_per_rank * world * e_steps / float(dt), "unit": UNIT,
+               "h2d_bytes_per_step": hplan.h2d_bytes * world, "d2h_bytes_per_step": hplan.d2h_bytes * world,
+               "ms_per_step": float(dt) / e_steps * 1e3, "steps": e_steps,
+               "loss_matches_device_path": bool(abs(hres.loss * (1 if world == 1 else 1) - float(res.loss)) <= 1e-5 * abs(float(res.loss)))}
+
+    if rank == 0:
+        peak, peak_src = load_peaks()
+        b_alg = algorithmic_bytes(inp, N)
+        k_ms = float(seg[:, 1].mean())
+        achieved = b_alg / (k_ms * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": units_per_rank * world * args.steps / (ms_total * 1e-3), "unit": UNIT,
+            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{args.config}: {W}x{H} batch {N} per GPU, 3-frame stacks, {S} sources, "
+                                   f"{Ls} scales, SSIM+L1 min-reprojection{' + automask' if inp.automasking else ''} "
+                                   f"+ smoothness, fwd+bwd", "global_batch": Ng, "l2": "inputs_larger_than_l2",
+                       "parallelism": f"batch-sharded x{world}, 1 all-reduce of [loss, pose grads] per step",
+                       "units_per_step": units_per_rank * world, "loss": loss_val},
+            "clocks": clocks,
+            "e2e": e2e,
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": "photo_fused_kernel", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": b_alg, "kernel_ms": k_ms,
+                         "segments_ms": {"prep_stats": float(seg[:, 0].mean()), "fused": k_ms,
+                                         "upsample_bwd": float(seg[:, 2].mean()), "finalize": float(seg[:, 3].mean())},
+                         "note": "fused kernel is FP32/FP64-issue bound (SURVEY F10): ~6 B of compulsory HBM traffic "
+                                 "per warped pixel against several hundred flops"},
+        }
+        if not args.no_cpu_baseline and world == 1:
+            rate, cores, t, items = cpu_reference_rate(inp, args.cpu_sample_items, 3, 1)
+            line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
+                                    "sample": f"{items} of the batch's {N} items, 3 steps after 1 warm-up, torch-CPU "
+                                              f"float32 restatement with autograd backward, {cores} threads ({t:.2f} s/step)"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

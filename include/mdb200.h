@@ -59,6 +59,15 @@ const char* mdb_last_error(const mdb_handle* h); /* valid until the next failing
 /* number of kernels launched through this handle since creation (bench "gpu_launches") */
 int64_t mdb_launch_count(const mdb_handle* h);
 
+/* Optional segment timing of mdb_train_loss_fwdbwd for the bench roofline: after
+ * mdb_profile_begin(h, slots) every call records CUDA events on the caller's stream around its
+ * 4 segments (0 pose/stats pre-pass, 1 fused kernel, 2 upsample transpose, 3 finalize) into the
+ * next slot; mdb_profile_read waits for that slot and returns the 4 durations in ms.
+ * mdb_profile_begin(h, 0) switches it off.  No reference counterpart (the reference's only
+ * timing is `CUDA.@time` in scratch files, src/test.jl:30).                                 */
+int32_t mdb_profile_begin(mdb_handle* h, int32_t slots);
+int32_t mdb_profile_read(mdb_handle* h, int32_t slot, float* ms_out /* 4 floats */);
+
 /* ---- parameters of the loss ---------------------------------------------------------- */
 typedef struct mdb_loss_params {
   double min_depth;           /* Params.min_depth (Float64)  src/Monodepth.jl:38 (0.1)   */

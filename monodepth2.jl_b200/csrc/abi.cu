@@ -34,8 +34,39 @@ int32_t mdb_create(mdb_handle** out, int32_t device) {
   return MDB_OK;
 }
 
+static void prof_free(mdb_handle* h) {
+  if (!h->prof_ev) return;
+  for (int i = 0; i < h->prof_slots * (mdb_handle::kProfSegments + 1); ++i) cudaEventDestroy(h->prof_ev[i]);
+  delete[] h->prof_ev;
+  h->prof_ev = nullptr;
+  h->prof_slots = h->prof_next = 0;
+}
+
 int32_t mdb_destroy(mdb_handle* h) {
+  if (h) prof_free(h);
   delete h;
+  return MDB_OK;
+}
+
+int32_t mdb_profile_begin(mdb_handle* h, int32_t slots) {
+  MDB_REQUIRE(h, h != nullptr, MDB_E_INVALID_ARG, "null handle");
+  prof_free(h);
+  if (slots <= 0) return MDB_OK;  // profiling off
+  const int n = slots * (mdb_handle::kProfSegments + 1);
+  h->prof_ev = new cudaEvent_t[n];
+  for (int i = 0; i < n; ++i) MDB_CUDA(h, cudaEventCreate(&h->prof_ev[i]));
+  h->prof_slots = slots;
+  h->prof_next = 0;
+  return MDB_OK;
+}
+
+int32_t mdb_profile_read(mdb_handle* h, int32_t slot, float* ms_out) {
+  MDB_REQUIRE(h, h && ms_out, MDB_E_INVALID_ARG, "mdb_profile_read: bad argument");
+  MDB_REQUIRE(h, h->prof_ev && slot >= 0 && slot < h->prof_slots && slot < h->prof_next, MDB_E_INVALID_ARG,
+              "mdb_profile_read: slot %d was not recorded", slot);
+  cudaEvent_t* e = h->prof_ev + slot * (mdb_handle::kProfSegments + 1);
+  MDB_CUDA(h, cudaEventSynchronize(e[mdb_handle::kProfSegments]));
+  for (int s = 0; s < mdb_handle::kProfSegments; ++s) MDB_CUDA(h, cudaEventElapsedTime(&ms_out[s], e[s], e[s + 1]));
   return MDB_OK;
 }
 

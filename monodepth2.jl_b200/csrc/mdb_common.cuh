@@ -15,6 +15,10 @@ struct mdb_handle {
   size_t smem_optin = 0;
   int64_t launches = 0;
   void* encode_tiled = nullptr;  // cuTensorMapEncodeTiled, resolved at create time
+  // optional per-call segment timing (mdb_profile_*): events recorded on the caller's stream
+  static constexpr int kProfSegments = 4;  // 0 prep+stats, 1 fused kernel, 2 upsample_bwd, 3 finalize
+  int prof_slots = 0, prof_next = 0;
+  cudaEvent_t* prof_ev = nullptr;  // [slots][kProfSegments + 1]
   char err[512] = {0};
 };
 
@@ -47,6 +51,11 @@ inline int32_t mdb_fail(mdb_handle* h, int32_t code, const char* fmt, ...) {
     (h)->launches++;                         \
     MDB_CUDA((h), cudaPeekAtLastError());    \
   } while (0)
+
+// record the boundary event `seg` of the current profiling slot (no-op when profiling is off)
+inline void mdb_prof_mark(mdb_handle* h, int slot, int seg, cudaStream_t st) {
+  if (h->prof_ev && slot >= 0) cudaEventRecord(h->prof_ev[slot * (mdb_handle::kProfSegments + 1) + seg], st);
+}
 
 static inline size_t mdb_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 

@@ -203,6 +203,8 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
   fa.vis = io->vis_warp_loss;
   fa.tiles_x = L.tiles_x; fa.tiles_y = L.tiles_y;
 
+  const int pslot = (h->prof_ev && h->prof_next < h->prof_slots) ? h->prof_next++ : -1;
+  mdb_prof_mark(h, pslot, 0, st);
   pose_prep_kernel<<<(N * S + 127) / 128, 128, 0, st>>>(pa, (PosePrep*)(ws + L.o_pp), (PosePrepD*)(ws + L.o_ppd));
   MDB_LAUNCHED(h);
   {
@@ -214,12 +216,14 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
                                                                      p->normalize_disparity, (ScaleStat*)(ws + L.o_stats));
     MDB_LAUNCHED(h);
   }
+  mdb_prof_mark(h, pslot, 1, st);
   int32_t rc;
   if (io->C == 3 && S == 2) rc = launch_fused<3, 2>(h, fa, L, st);
   else if (io->C == 3 && S == 1) rc = launch_fused<3, 1>(h, fa, L, st);
   else if (io->C == 1 && S == 2) rc = launch_fused<1, 2>(h, fa, L, st);
   else rc = launch_fused<1, 1>(h, fa, L, st);
   if (rc != MDB_OK) return rc;
+  mdb_prof_mark(h, pslot, 2, st);
 
   for (int s = 0; s < Ls; ++s) {
     if (fa.native[s]) continue;
@@ -228,6 +232,7 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
                                               io->d_disparity[s]);
     MDB_LAUNCHED(h);
   }
+  mdb_prof_mark(h, pslot, 3, st);
   const int tiles = L.tiles_x * L.tiles_y;
   double* item_loss = (double*)(ws + L.o_itemloss);
   if (S == 2)
@@ -239,6 +244,7 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
   MDB_LAUNCHED(h);
   finalize_loss_kernel<<<1, 256, 0, st>>>(item_loss, N, fa.stats, Ls * N, up, io->loss);
   MDB_LAUNCHED(h);
+  mdb_prof_mark(h, pslot, 4, st);
   return MDB_OK;
 }
 

@@ -67,6 +67,8 @@ PROTOTYPES = {
     "mdb_destroy": (_i32, [_vp]),
     "mdb_last_error": (C.c_char_p, [_vp]),
     "mdb_launch_count": (_i64, [_vp]),
+    "mdb_profile_begin": (_i32, [_vp, _i32]),
+    "mdb_profile_read": (_i32, [_vp, _i32, c_f32p]),
     "mdb_loss_params_default": (None, [C.POINTER(LossParams)]),
     "mdb_hat": (_i32, [_vp, _vp, _i32, _vp, _vp]),
     "mdb_hat_pullback": (_i32, [_vp, _vp, _i32, _vp, _vp]),

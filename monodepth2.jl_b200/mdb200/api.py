@@ -43,6 +43,18 @@ def launch_count() -> int:
     return int(lib.mdb_launch_count(handle()))
 
 
+def profile_begin(slots: int) -> None:
+    """Record per-segment CUDA events inside the next `slots` fused-loss calls (0 = off)."""
+    check(handle(), lib.mdb_profile_begin(handle(), int(slots)))
+
+
+def profile_read(slot: int):
+    """-> [prep+stats, fused kernel, upsample transpose, finalize] durations of that call, ms."""
+    out = (ct.c_float * 4)()
+    check(handle(), lib.mdb_profile_read(handle(), int(slot), out))
+    return list(out)
+
+
 def _stream():
     return ct.c_void_p(torch.cuda.current_stream().cuda_stream)
 
@@ -432,3 +444,93 @@ def simple_depth_plan(x: torch.Tensor, K, invK, *, target_id: int = 2, source_id
     return FusedLoss(W=W, H=H, C=Cc, L=L, N=N, disp_sizes=[(W, H)], scales=[1.0], target_id=target_id,
                      source_ids=source_ids, K=K, invK=invK, min_depth=min_depth, max_depth=max_depth,
                      automasking=False, normalize_disparity=False, smooth_weight_mode=1, device=x.device)
+
+
+# --------------------------------------------------------------------------------------
+# host-buffer entry: the call a user with HOST arrays makes (bench "e2e")
+# --------------------------------------------------------------------------------------
+@dataclass
+class HostLossResult:
+    loss: float
+    d_disparities: List[torch.Tensor]   # pinned host tensors, native resolution
+    d_rvec: List[torch.Tensor]          # pinned host (N,3) per source
+    d_tvec: List[torch.Tensor]          # pinned host (N,1,3) per source
+
+
+class HostLoss:
+    """`train_loss` value + gradients for inputs that live in (pinned) HOST memory.
+
+    The batch is cut into chunks of `chunk` items; chunk k+1 is copied host->device on a copy
+    stream while chunk k runs on the compute stream and chunk k-1's gradients drain
+    device->host on a third stream, so the step costs about max(PCIe, compute) instead of
+    their sum.  Every chunk is one `mdb_train_loss_fwdbwd` call with `n_global = N`, the same
+    contract the multi-GPU shards use, so chunk losses simply add."""
+
+    def __init__(self, *, W, H, C, L, N, disp_sizes, scales, target_id, source_ids, K, invK, chunk=8,
+                 automasking=False, n_global=0, device=None, **kw):
+        self.dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.N, self.L, self.C, self.H, self.W = N, L, C, H, W
+        self.S = len(source_ids)
+        self.disp_sizes = [(int(w), int(h)) for (w, h) in disp_sizes]
+        self.automasking = automasking
+        self.chunks = [(s, min(s + chunk, N)) for s in range(0, N, chunk)]
+        ng = n_global if n_global > 0 else N
+        f32 = dict(device=self.dev, dtype=torch.float32)
+        with torch.cuda.device(self.dev):
+            self.copy_in, self.copy_out = torch.cuda.Stream(), torch.cuda.Stream()
+            self.plans, self.dx, self.dd, self.dr, self.dt, self.da = [], [], [], [], [], []
+            for (a, b) in self.chunks:
+                n = b - a
+                self.plans.append(FusedLoss(W=W, H=H, C=C, L=L, N=n, disp_sizes=disp_sizes, scales=scales,
+                                            target_id=target_id, source_ids=source_ids, K=K, invK=invK,
+                                            automasking=automasking, n_global=ng, device=self.dev, **kw))
+                self.dx.append(torch.empty((n, L, C, H, W), **f32))
+                self.dd.append([torch.empty((n, 1, h, w), **f32) for (w, h) in self.disp_sizes])
+                self.dr.append([torch.empty((n, 3), **f32) for _ in range(self.S)])
+                self.dt.append([torch.empty((n, 1, 3), **f32) for _ in range(self.S)])
+                self.da.append(torch.empty((n, 1, H, W), **f32) if automasking else None)
+        pin = dict(dtype=torch.float32, pin_memory=True)
+        self.h_loss = torch.empty((len(self.chunks),), **pin)
+        self.h_dd = [torch.empty((N, 1, h, w), **pin) for (w, h) in self.disp_sizes]
+        self.h_dr = [torch.empty((N, 3), **pin) for _ in range(self.S)]
+        self.h_dt = [torch.empty((N, 1, 3), **pin) for _ in range(self.S)]
+        self.h2d_bytes = 4 * (N * L * C * H * W + sum(N * w * h for (w, h) in self.disp_sizes) + 6 * N * self.S
+                              + (N * H * W if automasking else 0))
+        self.d2h_bytes = 4 * (len(self.chunks) + sum(N * w * h for (w, h) in self.disp_sizes) + 6 * N * self.S)
+
+    def __call__(self, x, disparities, rvecs, tvecs, auto_loss=None) -> HostLossResult:
+        """All arguments are HOST float32 tensors (pinned for full PCIe rate)."""
+        compute = torch.cuda.current_stream(self.dev)
+        self.copy_in.wait_stream(compute)
+        self.copy_out.wait_stream(compute)
+        for k, (a, b) in enumerate(self.chunks):
+            with torch.cuda.stream(self.copy_in):
+                self.dx[k].copy_(x[a:b], non_blocking=True)
+                for j, d in enumerate(disparities):
+                    self.dd[k][j].copy_(d[a:b], non_blocking=True)
+                for s in range(self.S):
+                    self.dr[k][s].copy_(rvecs[s][a:b], non_blocking=True)
+                    self.dt[k][s].copy_(tvecs[s][a:b], non_blocking=True)
+                if self.automasking:
+                    self.da[k].copy_(auto_loss[a:b], non_blocking=True)
+                ready = self.copy_in.record_event()
+            compute.wait_event(ready)
+            res = self.plans[k](self.dx[k], self.dd[k], [Pose(r, t) for r, t in zip(self.dr[k], self.dt[k])], self.da[k])
+            done = compute.record_event()
+            with torch.cuda.stream(self.copy_out):
+                self.copy_out.wait_event(done)
+                self.h_loss[k:k + 1].copy_(res.loss.reshape(1), non_blocking=True)
+                for j in range(len(self.disp_sizes)):
+                    self.h_dd[j][a:b].copy_(res.d_disparities[j], non_blocking=True)
+                for s in range(self.S):
+                    self.h_dr[s][a:b].copy_(res.d_poses[s].rvec, non_blocking=True)
+                    self.h_dt[s][a:b].copy_(res.d_poses[s].tvec, non_blocking=True)
+        self.copy_out.synchronize()
+        compute.wait_stream(self.copy_out)
+        return HostLossResult(float(self.h_loss.sum()), self.h_dd, self.h_dr, self.h_dt)
+
+
+def train_loss_host(plan: HostLoss, x, disparities, poses: Sequence[Pose], auto_loss=None) -> HostLossResult:
+    """Public host-buffer call: `train_loss` (src/training.jl:21-78) value + gradients for HOST
+    inputs; `plan` is a HostLoss built once for the shapes."""
+    return plan(x, disparities, [p.rvec for p in poses], [p.tvec for p in poses], auto_loss)
