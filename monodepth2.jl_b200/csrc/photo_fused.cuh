@@ -86,6 +86,13 @@ MDB_DEV void upsample_coords(int g, float r, int dn, int& i0, int& i1, float& l)
   i1 = min(i0 + 1, dn - 1);
 }
 
+// MUFU.RCP: 1 ulp, no slow path (callers guarantee a normal, positive argument)
+MDB_DEV float rcp_approx(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
 struct Taps {
   int o00, o01, o10, o11;  // offsets inside one channel plane
   float fx, fy;            // fractional weights
@@ -168,7 +175,8 @@ MDB_DEV float ssim_window(float Sx, float Sy, float Sxx, float Syy, float Sxy, f
   const float mx = xc + mxs, my = yc + mys;
   const float n1 = fmaf(2.0f * mx, my, c1), n2 = fmaf(2.0f, sxy, c2);
   const float d1 = fmaf(mx, mx, fmaf(my, my, c1)), d2 = sx + sy + c2;
-  const float i1 = 1.0f / d1, i2 = 1.0f / d2;
+  // d1 >= c1 > 0 and d2 >= c2 - rounding > 0: the 1-ulp hardware reciprocal is enough here
+  const float i1 = rcp_approx(d1), i2 = rcp_approx(d2);
   const float r1 = n1 * i1, r2 = n2 * i2;            // n/d = r1 r2
   const float raw = (1.0f - r1 * r2) * 0.5f;
   const bool inside = (raw >= 0.0f) && (raw <= 1.0f);
