@@ -185,6 +185,49 @@ size_t mdb_train_loss_workspace_bytes(const mdb_loss_io* io);
 int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_loss_params* p,
                               void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- R1-R7: plane-disparity volume rendering  (src/render.jl) ------------------------------
+ * Layouts: rgb (W,H,3,Np,B), sigma (W,H,1,Np,B), xyz (3,W,H,Np,B), disparity_src (Np,B),
+ * pose rvec (3,B), tvec (3,B) (2-D, as test/test_sample.jl:46 builds it).  The reference's
+ * quirks are reproduced as written; 1 <= Np <= 64.                              */
+/* Monodepth.inv: batched 3x3 inverse (3,3,M)                       src/render.jl:3-17    */
+int32_t mdb_inv3x3_batched(mdb_handle* h, const float* A, int32_t M, float* out, void* stream);
+/* create_meshgrid(H, W) -> (3,W,H) = [w,h,1], 1-based              src/render.jl:21-23   */
+int32_t mdb_create_meshgrid(mdb_handle* h, int32_t H, int32_t W, float* out, void* stream);
+/* get_src_xyz_from_plane_disparity(meshgrid, disparity, K_inv)     src/render.jl:25-30   */
+int32_t mdb_plane_xyz_src(mdb_handle* h, const float* meshgrid, const float* disparity, const float* K_inv,
+                          int32_t W, int32_t H, int32_t Np, int32_t B, float* out, void* stream);
+/* get_tgt_xyz_from_plane_disparity(xyz_src, pose)                  src/render.jl:51-62   */
+int32_t mdb_plane_xyz_tgt(mdb_handle* h, const float* xyz_src, const float* rvec, const float* tvec, int32_t W,
+                          int32_t H, int32_t Np, int32_t B, float* out, void* stream);
+/* workspace for mdb_sample / mdb_render_* (0 if the shape is unsupported)                   */
+size_t mdb_render_workspace_bytes(int32_t W, int32_t H, int32_t Np, int32_t B);
+/* sample(src (W,H,Cs,Np*B), depth_src (Np,B), pose, K, K_inv) -> tgt, valid_mask (W*H, Np*B)
+ * as bytes                                                          src/render.jl:64-90   */
+int32_t mdb_sample(mdb_handle* h, const float* src, const float* depth_src, const float* rvec, const float* tvec,
+                   const float* K, const float* K_inv, int32_t W, int32_t H, int32_t Cs, int32_t Np, int32_t B,
+                   float* tgt, uint8_t* valid_mask, void* workspace, size_t workspace_bytes, void* stream);
+/* plane_volume_rendering(rgb, sigma, xyz) -> rgb_out (W,H,3,B), transparency_acc, weights
+ * (W,H,1,Np,B); weights may be NULL                                 src/render.jl:32-49   */
+int32_t mdb_plane_volume_rendering(mdb_handle* h, const float* rgb, const float* sigma, const float* xyz, int32_t W,
+                                   int32_t H, int32_t Np, int32_t B, float* rgb_out, float* transparency_acc,
+                                   float* weights, void* stream);
+/* render_tgt_rgb_depth(rgb, sigma, disparity_src, xyz_tgt, pose, K_inv, K) -> rgb (W,H,3,B),
+ * "depth" = transparency_acc (W,H,1,Np,B), mask (W,H,1,1,B) int32   src/render.jl:92-114  */
+int32_t mdb_render_tgt_rgb_depth_fwd(mdb_handle* h, const float* rgb, const float* sigma, const float* disparity_src,
+                                     const float* xyz_tgt, const float* rvec, const float* tvec, const float* K_inv,
+                                     const float* K, int32_t W, int32_t H, int32_t Np, int32_t B, float* rgb_out,
+                                     float* depth_out, int32_t* mask_out, void* workspace, size_t workspace_bytes,
+                                     void* stream);
+/* pullback of the above (the reference has none: its `sample` mutates in place).  depth_saved is
+ * the forward's depth output; g_depth may be NULL; d_disparity_src / d_rvec / d_tvec may be NULL.
+ * d_rgb / d_sigma / d_xyz_tgt are zeroed here and accumulated with red.global.add.f32.        */
+int32_t mdb_render_tgt_rgb_depth_bwd(mdb_handle* h, const float* rgb, const float* sigma, const float* disparity_src,
+                                     const float* xyz_tgt, const float* rvec, const float* tvec, const float* K_inv,
+                                     const float* K, int32_t W, int32_t H, int32_t Np, int32_t B, const float* depth_saved,
+                                     const float* g_rgb_out, const float* g_depth, float* d_rgb, float* d_sigma,
+                                     float* d_xyz_tgt, float* d_disparity_src, float* d_rvec, float* d_tvec,
+                                     void* workspace, size_t workspace_bytes, void* stream);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

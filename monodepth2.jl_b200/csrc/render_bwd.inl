@@ -1,0 +1,437 @@
+// render_bwd.inl -- pullback of render_tgt_rgb_depth and the C-ABI entries of the render path.
+// The reference has NO backward for this path (in-place mutation inside `sample`,
+// src/render.jl:83-84, defeats Zygote): the semantics here are the pullback of the
+// functional restatement, checked against autograd of the oracle.
+namespace {
+
+struct RenderBwdArgs {
+  const float* rgb; const float* sigma; const float* xyz;
+  const PlanePrep* prep;
+  const float* tacc;        // saved forward output [B][Np][1][H][W]
+  const float* g_rgb_out;   // [B][3][H][W]
+  const float* g_tacc;      // [B][Np][1][H][W] or null
+  int W, H, Np, B;
+  float Kinv_f[9];
+  const float* tvec;        // [B][3]
+  float* d_rgb; float* d_sigma; float* d_xyz;   // zero-initialised, accumulated with red.global.add
+  float* part_pose;         // [B][blocks][12]
+  float* part_disp;         // [B][blocks][Np]
+};
+
+constexpr int RB_THREADS = 128;
+constexpr int RB_MAXP = 64;   // planes supported by the per-warp shared accumulators
+
+struct Pend {
+  int o00, o01, o10, o11;
+  float fx, fy, mx, my;
+  float dxv[3], dyv[3];   // d(sampled xyz_c)/d(ix), d/d(iy)
+  float dix, diy;         // contribution of the rgb + sigma channels, complete
+  float gx[3];            // d L / d(sampled xyz) received so far (from the later plane's distance)
+  float X0, X1, X2, x, y;
+  int k;
+};
+
+MDB_DEV void scatter4(float* __restrict__ base, int stride, const Pend& t, float g) {
+  const float w11 = t.fx * t.fy, w01 = t.fx - w11, w10 = t.fy - w11, w00 = 1.0f - t.fx - t.fy + w11;
+  atomicAdd(base + stride * t.o00, g * w00);
+  atomicAdd(base + stride * t.o01, g * w01);
+  atomicAdd(base + stride * t.o10, g * w10);
+  atomicAdd(base + stride * t.o11, g * w11);
+}
+
+__global__ void __launch_bounds__(RB_THREADS) render_bwd_kernel(const __grid_constant__ RenderBwdArgs a) {
+  __shared__ float s_disp[RB_THREADS / 32][RB_MAXP];
+  __shared__ float s_pose[RB_THREADS / 32][12];
+  const int pix = blockIdx.x * RB_THREADS + threadIdx.x;
+  const int b = blockIdx.y;
+  const int WH = a.W * a.H;
+  const bool active = pix < WH;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int u = active ? pix % a.W : 0, v = active ? pix / a.W : 0;
+  const int pp = active ? pix : 0;
+  float gO[3];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) gO[c] = active ? ldg(a.g_rgb_out + ((size_t)b * 3 + c) * WH + pp) : 0.0f;
+  const float t0 = a.tvec[3 * b], t1 = a.tvec[3 * b + 1], t2 = a.tvec[3 * b + 2];
+  const float sxw = (float)(a.W - 1) / (float)a.W, syh = (float)(a.H - 1) / (float)a.H;
+  float acc[12];
+#pragma unroll
+  for (int i = 0; i < 12; ++i) acc[i] = 0.0f;
+  for (int i = lane; i < RB_MAXP; i += 32) s_disp[warp][i] = 0.0f;
+  __syncwarp();
+
+  float Q = 0.0f;
+  float n_xyz[3] = {0, 0, 0};   // sampled xyz of plane k+1
+  Pend pd;
+  pd.k = -1;
+
+  // pullback of the pending plane's sample position into (dR, dt, d disparity)
+  auto finish = [&](Pend& p, const float* gextra) {
+    float gx[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) gx[c] = p.gx[c] + gextra[c];
+    float ddisp = 0.0f;
+    if (active) {
+      const int kb = b * a.Np + p.k;
+      float* dx = a.d_xyz + (size_t)kb * WH * 3;
+      float dix = p.dix, diy = p.diy;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        if (gx[c] != 0.0f) scatter4(dx + c, 3, p, gx[c]);
+        dix = fmaf(gx[c], p.dxv[c], dix);
+        diy = fmaf(gx[c], p.dyv[c], diy);
+      }
+      const float gxs = dix * p.mx * sxw, gys = diy * p.my * syh;   // d/dx_src, d/dy_src
+      const float i2 = 1.0f / p.X2;
+      const float g0 = gxs * i2, g1 = gys * i2, g2 = -(gxs * p.x + gys * p.y) * i2;
+      const float* G1 = a.prep[kb].G1;
+      const float a0 = G1[0] * g0 + G1[1] * g1 + G1[2] * g2;
+      const float a1 = G1[3] * g0 + G1[4] * g1 + G1[5] * g2;
+      const float a2 = G1[6] * g0 + G1[7] * g1 + G1[8] * g2;
+      const float Y0 = a.Kinv_f[0] * p.X0 + a.Kinv_f[1] * p.X1 + a.Kinv_f[2] * p.X2;
+      const float Y1 = a.Kinv_f[3] * p.X0 + a.Kinv_f[4] * p.X1 + a.Kinv_f[5] * p.X2;
+      const float Y2 = a.Kinv_f[6] * p.X0 + a.Kinv_f[7] * p.X1 + a.Kinv_f[8] * p.X2;
+      // dM = -a' (x) Y ;  M = R + t n^T disparity
+      acc[0] -= a0 * Y0; acc[1] -= a0 * Y1; acc[2] -= a0 * Y2;
+      acc[3] -= a1 * Y0; acc[4] -= a1 * Y1; acc[5] -= a1 * Y2;
+      acc[6] -= a2 * Y0; acc[7] -= a2 * Y1; acc[8] -= a2 * Y2;
+      const float dsp = a.prep[kb].disp;
+      acc[9] -= a0 * Y2 * dsp; acc[10] -= a1 * Y2 * dsp; acc[11] -= a2 * Y2 * dsp;
+      ddisp = -(a0 * t0 + a1 * t1 + a2 * t2) * Y2;
+    }
+    ddisp = warp_sum(ddisp);
+    if (lane == 0) s_disp[warp][p.k] += ddisp;
+  };
+
+  for (int k = a.Np - 1; k >= 0; --k) {
+    const int kb = b * a.Np + k;
+    const RTaps t = render_taps(a.prep[kb].Hst, u, v, a.W, a.H);
+    Pend cur;
+    cur.o00 = t.o00; cur.o01 = t.o01; cur.o10 = t.o10; cur.o11 = t.o11;
+    cur.fx = t.fx; cur.fy = t.fy; cur.mx = t.mx; cur.my = t.my;
+    cur.X0 = (float)t.X0; cur.X1 = (float)t.X1; cur.X2 = (float)t.X2; cur.x = t.x; cur.y = t.y; cur.k = k;
+    float rgbv[3], dxr[3], dyr[3], xyzv[3];
+    const float* pr = a.rgb + (size_t)kb * 3 * WH;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const float v00 = ldg(pr + c * WH + t.o00), v01 = ldg(pr + c * WH + t.o01), v10 = ldg(pr + c * WH + t.o10), v11 = ldg(pr + c * WH + t.o11);
+      rgbv[c] = bil(t, v00, v01, v10, v11);
+      dxr[c] = fmaf(t.fy, (v11 - v10) - (v01 - v00), v01 - v00);
+      dyr[c] = fmaf(t.fx, (v11 - v01) - (v10 - v00), v10 - v00);
+    }
+    const float* ps = a.sigma + (size_t)kb * WH;
+    float sraw, dxs, dys;
+    {
+      const float v00 = ldg(ps + t.o00), v01 = ldg(ps + t.o01), v10 = ldg(ps + t.o10), v11 = ldg(ps + t.o11);
+      sraw = bil(t, v00, v01, v10, v11);
+      dxs = fmaf(t.fy, (v11 - v10) - (v01 - v00), v01 - v00);
+      dys = fmaf(t.fx, (v11 - v01) - (v10 - v00), v10 - v00);
+    }
+    const float* px = a.xyz + (size_t)kb * WH * 3;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const float v00 = ldg(px + 3 * t.o00 + c), v01 = ldg(px + 3 * t.o01 + c), v10 = ldg(px + 3 * t.o10 + c), v11 = ldg(px + 3 * t.o11 + c);
+      xyzv[c] = bil(t, v00, v01, v10, v11);
+      cur.dxv[c] = fmaf(t.fy, (v11 - v10) - (v01 - v00), v01 - v00);
+      cur.dyv[c] = fmaf(t.fx, (v11 - v01) - (v10 - v00), v10 - v00);
+    }
+    const bool spos = sraw >= 0.0f;
+    const float sig = spos ? sraw : 0.0f;
+    float dist = 1e3f, df[3] = {0, 0, 0};
+    if (k < a.Np - 1) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) df[c] = n_xyz[c] - xyzv[c];
+      dist = sqrtf(df[0] * df[0] + df[1] * df[1] + df[2] * df[2]);
+    }
+    const float T = expf(-dist * sig);
+    const float alpha = 1.0f - T;
+    const float tacc = active ? ldg(a.tacc + (size_t)kb * WH + pp) : 0.0f;
+    const float gT = (active && a.g_tacc) ? ldg(a.g_tacc + (size_t)kb * WH + pp) : 0.0f;
+    const float dw = gO[0] * rgbv[0] + gO[1] * rgbv[1] + gO[2] * rgbv[2];
+    const float w = tacc * alpha;
+    const float tau = fmaf(dw, alpha, gT);           // total d L / d transparency_acc_k
+    const float dT = Q / (T + 1e-6f) - dw * tacc;    // via the later planes' products and via alpha_k
+    Q = fmaf(tau, tacc, Q);
+    const float de = -T * dT;                        // T = exp(-e), e = dist * sigma
+    const float gsig = spos ? de * dist : 0.0f;
+    float gnext[3] = {0, 0, 0};
+    cur.gx[0] = cur.gx[1] = cur.gx[2] = 0.0f;
+    if (k < a.Np - 1) {
+      const float gd = de * sig / dist;              // NaN if two sampled planes coincide, like sqrt'(0)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) { gnext[c] = gd * df[c]; cur.gx[c] = -gd * df[c]; }
+      finish(pd, gnext);                             // plane k+1 is now complete
+    }
+    // rgb and sigma of plane k are complete now
+    float dix = 0.0f, diy = 0.0f;
+    if (active) {
+      float* dr = a.d_rgb + (size_t)kb * 3 * WH;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const float g = gO[c] * w;
+        if (g != 0.0f) scatter4(dr + c * WH, 1, cur, g);
+        dix = fmaf(g, dxr[c], dix);
+        diy = fmaf(g, dyr[c], diy);
+      }
+      if (gsig != 0.0f) scatter4(a.d_sigma + (size_t)kb * WH, 1, cur, gsig);
+      dix = fmaf(gsig, dxs, dix);
+      diy = fmaf(gsig, dys, diy);
+    }
+    cur.dix = dix; cur.diy = diy;
+    pd = cur;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) n_xyz[c] = xyzv[c];
+  }
+  {
+    const float zero[3] = {0, 0, 0};
+    finish(pd, zero);   // plane 0
+  }
+#pragma unroll
+  for (int i = 0; i < 12; ++i) {
+    const float vsum = warp_sum(acc[i]);
+    if (lane == 0) s_pose[warp][i] = vsum;
+  }
+  __syncthreads();
+  const size_t blk = (size_t)b * gridDim.x + blockIdx.x;
+  if (threadIdx.x < 12) {
+    float vsum = 0.0f;
+    for (int w = 0; w < RB_THREADS / 32; ++w) vsum += s_pose[w][threadIdx.x];
+    a.part_pose[blk * 12 + threadIdx.x] = vsum;
+  }
+  for (int i = threadIdx.x; i < a.Np; i += RB_THREADS) {
+    float vsum = 0.0f;
+    for (int w = 0; w < RB_THREADS / 32; ++w) vsum += s_disp[w][i];
+    a.part_disp[blk * a.Np + i] = vsum;
+  }
+}
+
+// fixed-order sums of the block partials, then so3 pullback for rvec
+__global__ void render_bwd_finalize_kernel(const float* __restrict__ part_pose, const float* __restrict__ part_disp,
+                                           int blocks, int Np, int B, const float* __restrict__ rvec,
+                                           float* __restrict__ d_rvec, float* __restrict__ d_tvec,
+                                           float* __restrict__ d_disp) {
+  const int b = blockIdx.x;
+  __shared__ double tot[12];
+  if (threadIdx.x < 12) {
+    double s = 0.0;
+    for (int i = 0; i < blocks; ++i) s += (double)part_pose[((size_t)b * blocks + i) * 12 + threadIdx.x];
+    tot[threadIdx.x] = s;
+  }
+  for (int k = threadIdx.x; k < Np; k += blockDim.x) {
+    double s = 0.0;
+    for (int i = 0; i < blocks; ++i) s += (double)part_disp[((size_t)b * blocks + i) * Np + k];
+    if (d_disp) d_disp[b * Np + k] = (float)s;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double r[3] = {rvec[3 * b], rvec[3 * b + 1], rvec[3 * b + 2]}, R[9], dr[3];
+    So3Aux aux;
+    so3_exp_d(r, R, aux);
+    so3_exp_bwd_d(r, aux, tot, dr);
+    for (int k = 0; k < 3; ++k) {
+      if (d_rvec) d_rvec[3 * b + k] = (float)dr[k];
+      if (d_tvec) d_tvec[3 * b + k] = (float)tot[9 + k];
+    }
+  }
+}
+
+// ---- stand-alone R5 / R6 forwards (the reference's tests call them by name) ---------------
+__global__ void sample_fwd_kernel(const float* __restrict__ src, const PlanePrep* __restrict__ prep, int W, int H,
+                                  int Cs, int M, float* __restrict__ out, unsigned char* __restrict__ valid) {
+  const int pix = blockIdx.x * blockDim.x + threadIdx.x;
+  const int m = blockIdx.y;
+  const int WH = W * H;
+  if (pix >= WH) return;
+  const RTaps t = render_taps(prep[m].Hst, pix % W, pix / W, W, H);
+  if (valid) valid[(size_t)m * WH + pix] = t.valid ? 1 : 0;
+  for (int c = 0; c < Cs; ++c) {
+    const float* p = src + ((size_t)m * Cs + c) * WH;
+    out[((size_t)m * Cs + c) * WH + pix] = bil(t, ldg(p + t.o00), ldg(p + t.o01), ldg(p + t.o10), ldg(p + t.o11));
+  }
+}
+
+__global__ void pvr_fwd_kernel(const float* __restrict__ rgb, const float* __restrict__ sigma, const float* __restrict__ xyz,
+                               int WH, int Np, int B, float* __restrict__ rgb_out, float* __restrict__ tacc_out,
+                               float* __restrict__ w_out) {
+  const int pix = blockIdx.x * blockDim.x + threadIdx.x;
+  const int b = blockIdx.y;
+  if (pix >= WH) return;
+  float out[3] = {0, 0, 0}, tacc = 1.0f;
+  for (int k = 0; k < Np; ++k) {
+    const int kb = b * Np + k;
+    float dist = 1e3f;
+    if (k + 1 < Np) {
+      const float* p0 = xyz + ((size_t)kb * WH + pix) * 3;
+      const float* p1 = p0 + (size_t)WH * 3;
+      const float dx = p1[0] - p0[0], dy = p1[1] - p0[1], dz = p1[2] - p0[2];
+      dist = sqrtf(dx * dx + dy * dy + dz * dz);
+    }
+    const float T = expf(-dist * sigma[(size_t)kb * WH + pix]);
+    const float w = tacc * (1.0f - T);
+    tacc_out[(size_t)kb * WH + pix] = tacc;
+    if (w_out) w_out[(size_t)kb * WH + pix] = w;
+    for (int c = 0; c < 3; ++c) out[c] = fmaf(w, rgb[((size_t)kb * 3 + c) * WH + pix], out[c]);
+    tacc *= (T + 1e-6f);
+  }
+  for (int c = 0; c < 3; ++c) rgb_out[((size_t)b * 3 + c) * WH + pix] = out[c];
+}
+
+RenderConst make_rc(const float* K, const float* Kinv) {
+  RenderConst rc;
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) {
+      rc.K[3 * i + j] = K ? K[3 * j + i] : (i == j);
+      rc.Kinv[3 * i + j] = Kinv[3 * j + i];
+      rc.Kinv_f[3 * i + j] = Kinv[3 * j + i];
+    }
+  return rc;
+}
+
+struct RenderLayout { size_t o_prep, o_pose, o_disp, total; int blocks; };
+RenderLayout render_layout(int W, int H, int Np, int B) {
+  RenderLayout L;
+  L.blocks = (W * H + RB_THREADS - 1) / RB_THREADS;
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t o = off; off = mdb_align_up(off + bytes, 256); return o; };
+  L.o_prep = take(sizeof(PlanePrep) * Np * B);
+  L.o_pose = take(sizeof(float) * 12 * (size_t)B * L.blocks);
+  L.o_disp = take(sizeof(float) * (size_t)Np * B * L.blocks);
+  L.total = off;
+  return L;
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t mdb_inv3x3_batched(mdb_handle* h, const float* A, int32_t M, float* out, void* stream) {
+  MDB_REQUIRE(h, h && A && out && M > 0, MDB_E_INVALID_ARG, "mdb_inv3x3_batched: bad argument");
+  inv3_kernel<<<(M + 127) / 128, 128, 0, (cudaStream_t)stream>>>(A, M, out);
+  MDB_LAUNCHED(h);
+  return MDB_OK;
+}
+
+int32_t mdb_create_meshgrid(mdb_handle* h, int32_t H, int32_t W, float* out, void* stream) {
+  MDB_REQUIRE(h, h && out && W > 0 && H > 0, MDB_E_INVALID_ARG, "mdb_create_meshgrid: bad argument");
+  meshgrid_kernel<<<(W * H + 255) / 256, 256, 0, (cudaStream_t)stream>>>(W, H, out);
+  MDB_LAUNCHED(h);
+  return MDB_OK;
+}
+
+int32_t mdb_plane_xyz_src(mdb_handle* h, const float* meshgrid, const float* disparity, const float* K_inv,
+                          int32_t W, int32_t H, int32_t Np, int32_t B, float* out, void* stream) {
+  MDB_REQUIRE(h, h && meshgrid && disparity && K_inv && out && W > 0 && H > 0 && Np > 0 && B > 0, MDB_E_INVALID_ARG,
+              "mdb_plane_xyz_src: bad argument");
+  const int64_t total = (int64_t)W * H * Np * B;
+  const int grid = (int)std::min<int64_t>((total + 255) / 256, (int64_t)h->num_sms * 16);
+  plane_xyz_src_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(meshgrid, disparity, make_rc(nullptr, K_inv), W * H, Np, B, out);
+  MDB_LAUNCHED(h);
+  return MDB_OK;
+}
+
+int32_t mdb_plane_xyz_tgt(mdb_handle* h, const float* xyz_src, const float* rvec, const float* tvec, int32_t W,
+                          int32_t H, int32_t Np, int32_t B, float* out, void* stream) {
+  MDB_REQUIRE(h, h && xyz_src && rvec && tvec && out && W > 0 && H > 0 && Np > 0 && B > 0, MDB_E_INVALID_ARG,
+              "mdb_plane_xyz_tgt: bad argument");
+  const int64_t per_b = (int64_t)W * H * Np;
+  dim3 grid((unsigned)std::min<int64_t>((per_b + 255) / 256, (int64_t)h->num_sms * 8), B);
+  plane_xyz_tgt_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(xyz_src, rvec, tvec, per_b, B, out);
+  MDB_LAUNCHED(h);
+  return MDB_OK;
+}
+
+size_t mdb_render_workspace_bytes(int32_t W, int32_t H, int32_t Np, int32_t B) {
+  if (W < 2 || H < 2 || Np < 1 || Np > RB_MAXP || B < 1) return 0;
+  return render_layout(W, H, Np, B).total;
+}
+
+int32_t mdb_sample(mdb_handle* h, const float* src, const float* depth_src, const float* rvec, const float* tvec,
+                   const float* K, const float* K_inv, int32_t W, int32_t H, int32_t Cs, int32_t Np, int32_t B,
+                   float* tgt, uint8_t* valid_mask, void* workspace, size_t workspace_bytes, void* stream) {
+  MDB_REQUIRE(h, h && src && depth_src && rvec && tvec && K && K_inv && tgt, MDB_E_INVALID_ARG, "mdb_sample: null argument");
+  MDB_REQUIRE(h, W >= 2 && H >= 2 && Cs >= 1 && Np >= 1 && Np <= RB_MAXP && B >= 1, MDB_E_SHAPE, "mdb_sample: bad shape");
+  const RenderLayout L = render_layout(W, H, Np, B);
+  MDB_REQUIRE(h, workspace && workspace_bytes >= L.total && ((uintptr_t)workspace & 255) == 0, MDB_E_WORKSPACE,
+              "mdb_sample: workspace must be >= %zu bytes, 256-byte aligned", L.total);
+  cudaStream_t st = (cudaStream_t)stream;
+  PlanePrep* prep = (PlanePrep*)((char*)workspace + L.o_prep);
+  render_prep_kernel<<<(Np * B + 63) / 64, 64, 0, st>>>(depth_src, 1, rvec, tvec, make_rc(K, K_inv), Np, B, prep);
+  MDB_LAUNCHED(h);
+  dim3 grid((W * H + 127) / 128, Np * B);
+  sample_fwd_kernel<<<grid, 128, 0, st>>>(src, prep, W, H, Cs, Np * B, tgt, valid_mask);
+  MDB_LAUNCHED(h);
+  return MDB_OK;
+}
+
+int32_t mdb_plane_volume_rendering(mdb_handle* h, const float* rgb, const float* sigma, const float* xyz, int32_t W,
+                                   int32_t H, int32_t Np, int32_t B, float* rgb_out, float* transparency_acc,
+                                   float* weights, void* stream) {
+  MDB_REQUIRE(h, h && rgb && sigma && xyz && rgb_out && transparency_acc && W > 0 && H > 0 && Np > 0 && B > 0,
+              MDB_E_INVALID_ARG, "mdb_plane_volume_rendering: bad argument");
+  dim3 grid((W * H + 127) / 128, B);
+  pvr_fwd_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(rgb, sigma, xyz, W * H, Np, B, rgb_out, transparency_acc, weights);
+  MDB_LAUNCHED(h);
+  return MDB_OK;
+}
+
+int32_t mdb_render_tgt_rgb_depth_fwd(mdb_handle* h, const float* rgb, const float* sigma, const float* disparity_src,
+                                     const float* xyz_tgt, const float* rvec, const float* tvec, const float* K_inv,
+                                     const float* K, int32_t W, int32_t H, int32_t Np, int32_t B, float* rgb_out,
+                                     float* depth_out, int32_t* mask_out, void* workspace, size_t workspace_bytes,
+                                     void* stream) {
+  MDB_REQUIRE(h, h && rgb && sigma && disparity_src && xyz_tgt && rvec && tvec && K_inv && K && rgb_out && depth_out && mask_out,
+              MDB_E_INVALID_ARG, "mdb_render_tgt_rgb_depth_fwd: null argument");
+  MDB_REQUIRE(h, W >= 2 && H >= 2 && Np >= 1 && Np <= RB_MAXP && B >= 1, MDB_E_SHAPE,
+              "mdb_render_tgt_rgb_depth_fwd: need W,H >= 2 and 1 <= Np <= %d", RB_MAXP);
+  const RenderLayout L = render_layout(W, H, Np, B);
+  MDB_REQUIRE(h, workspace && workspace_bytes >= L.total && ((uintptr_t)workspace & 255) == 0, MDB_E_WORKSPACE,
+              "render workspace must be >= %zu bytes, 256-byte aligned", L.total);
+  cudaStream_t st = (cudaStream_t)stream;
+  PlanePrep* prep = (PlanePrep*)((char*)workspace + L.o_prep);
+  render_prep_kernel<<<(Np * B + 63) / 64, 64, 0, st>>>(disparity_src, 0, rvec, tvec, make_rc(K, K_inv), Np, B, prep);
+  MDB_LAUNCHED(h);
+  RenderArgs a{rgb, sigma, xyz_tgt, prep, W, H, Np, B, rgb_out, depth_out, mask_out};
+  dim3 grid((W * H + RENDER_THREADS - 1) / RENDER_THREADS, B);
+  render_fwd_kernel<<<grid, RENDER_THREADS, 0, st>>>(a);
+  MDB_LAUNCHED(h);
+  return MDB_OK;
+}
+
+int32_t mdb_render_tgt_rgb_depth_bwd(mdb_handle* h, const float* rgb, const float* sigma, const float* disparity_src,
+                                     const float* xyz_tgt, const float* rvec, const float* tvec, const float* K_inv,
+                                     const float* K, int32_t W, int32_t H, int32_t Np, int32_t B, const float* depth_saved,
+                                     const float* g_rgb_out, const float* g_depth, float* d_rgb, float* d_sigma,
+                                     float* d_xyz_tgt, float* d_disparity_src, float* d_rvec, float* d_tvec,
+                                     void* workspace, size_t workspace_bytes, void* stream) {
+  MDB_REQUIRE(h, h && rgb && sigma && disparity_src && xyz_tgt && rvec && tvec && K_inv && K && depth_saved && g_rgb_out &&
+                  d_rgb && d_sigma && d_xyz_tgt, MDB_E_INVALID_ARG, "mdb_render_tgt_rgb_depth_bwd: null argument");
+  MDB_REQUIRE(h, W >= 2 && H >= 2 && Np >= 1 && Np <= RB_MAXP && B >= 1, MDB_E_SHAPE,
+              "mdb_render_tgt_rgb_depth_bwd: need W,H >= 2 and 1 <= Np <= %d", RB_MAXP);
+  const RenderLayout L = render_layout(W, H, Np, B);
+  MDB_REQUIRE(h, workspace && workspace_bytes >= L.total && ((uintptr_t)workspace & 255) == 0, MDB_E_WORKSPACE,
+              "render workspace must be >= %zu bytes, 256-byte aligned", L.total);
+  cudaStream_t st = (cudaStream_t)stream;
+  char* ws = (char*)workspace;
+  PlanePrep* prep = (PlanePrep*)(ws + L.o_prep);
+  const RenderConst rc = make_rc(K, K_inv);
+  render_prep_kernel<<<(Np * B + 63) / 64, 64, 0, st>>>(disparity_src, 0, rvec, tvec, rc, Np, B, prep);
+  MDB_LAUNCHED(h);
+  const size_t planes = (size_t)W * H * Np * B;
+  MDB_CUDA(h, cudaMemsetAsync(d_rgb, 0, planes * 3 * sizeof(float), st));
+  MDB_CUDA(h, cudaMemsetAsync(d_sigma, 0, planes * sizeof(float), st));
+  MDB_CUDA(h, cudaMemsetAsync(d_xyz_tgt, 0, planes * 3 * sizeof(float), st));
+  RenderBwdArgs a{};
+  a.rgb = rgb; a.sigma = sigma; a.xyz = xyz_tgt; a.prep = prep; a.tacc = depth_saved; a.g_rgb_out = g_rgb_out;
+  a.g_tacc = g_depth; a.W = W; a.H = H; a.Np = Np; a.B = B; a.tvec = tvec;
+  for (int i = 0; i < 9; ++i) a.Kinv_f[i] = rc.Kinv_f[i];
+  a.d_rgb = d_rgb; a.d_sigma = d_sigma; a.d_xyz = d_xyz_tgt;
+  a.part_pose = (float*)(ws + L.o_pose); a.part_disp = (float*)(ws + L.o_disp);
+  dim3 grid(L.blocks, B);
+  render_bwd_kernel<<<grid, RB_THREADS, 0, st>>>(a);
+  MDB_LAUNCHED(h);
+  render_bwd_finalize_kernel<<<B, 64, 0, st>>>(a.part_pose, a.part_disp, L.blocks, Np, B, rvec, d_rvec, d_tvec, d_disparity_src);
+  MDB_LAUNCHED(h);
+  return MDB_OK;
+}
+
+}  // extern "C"

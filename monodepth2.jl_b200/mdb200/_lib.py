@@ -92,6 +92,17 @@ PROTOTYPES = {
     "mdb_smooth_loss": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _sz, _vp]),
     "mdb_train_loss_workspace_bytes": (_sz, [C.POINTER(LossIO)]),
     "mdb_train_loss_fwdbwd": (_i32, [_vp, C.POINTER(LossIO), C.POINTER(LossParams), _vp, _sz, _vp]),
+    "mdb_inv3x3_batched": (_i32, [_vp, _vp, _i32, _vp, _vp]),
+    "mdb_create_meshgrid": (_i32, [_vp, _i32, _i32, _vp, _vp]),
+    "mdb_plane_xyz_src": (_i32, [_vp, _vp, _vp, c_f32p, _i32, _i32, _i32, _i32, _vp, _vp]),
+    "mdb_plane_xyz_tgt": (_i32, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp]),
+    "mdb_render_workspace_bytes": (_sz, [_i32, _i32, _i32, _i32]),
+    "mdb_sample": (_i32, [_vp, _vp, _vp, _vp, _vp, c_f32p, c_f32p, _i32, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _sz, _vp]),
+    "mdb_plane_volume_rendering": (_i32, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _vp]),
+    "mdb_render_tgt_rgb_depth_fwd": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, c_f32p, c_f32p, _i32, _i32, _i32, _i32,
+                                            _vp, _vp, _vp, _vp, _sz, _vp]),
+    "mdb_render_tgt_rgb_depth_bwd": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, c_f32p, c_f32p, _i32, _i32, _i32, _i32,
+                                            _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
 }
 
 

@@ -534,3 +534,119 @@ def train_loss_host(plan: HostLoss, x, disparities, poses: Sequence[Pose], auto_
     """Public host-buffer call: `train_loss` (src/training.jl:21-78) value + gradients for HOST
     inputs; `plan` is a HostLoss built once for the shapes."""
     return plan(x, disparities, [p.rvec for p in poses], [p.tvec for p in poses], auto_loss)
+
+
+# --------------------------------------------------------------------------------------
+# plane-disparity volume rendering -- src/render.jl
+# Layouts (reversed dims): rgb (B,Np,3,H,W), sigma (B,Np,1,H,W), xyz (B,Np,H,W,3),
+# disparity_src (B,Np), pose.rvec (B,3), pose.tvec (B,3).
+# --------------------------------------------------------------------------------------
+def inv(x: torch.Tensor) -> torch.Tensor:
+    """`Monodepth.inv` -- src/render.jl:3-17: (3,3) or batched (M,3,3) inverse."""
+    _chk(x, "x")
+    M = x.numel() // 9
+    out = torch.empty_like(x)
+    check(handle(), lib.mdb_inv3x3_batched(handle(), _p(x), M, _p(out), _stream()))
+    return out
+
+
+def create_meshgrid(H: int, W: int, device=None) -> torch.Tensor:
+    """src/render.jl:21-23 -> (H,W,3) [Julia (3,W,H)]."""
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else device
+    out = torch.empty((H, W, 3), device=dev, dtype=torch.float32)
+    check(handle(), lib.mdb_create_meshgrid(handle(), H, W, _p(out), _stream()))
+    return out
+
+
+def get_src_xyz_from_plane_disparity(meshgrid_src_homo, mpi_disparity_src, K_src_inv) -> torch.Tensor:
+    """src/render.jl:25-30."""
+    _chk(meshgrid_src_homo, "meshgrid"); _chk(mpi_disparity_src, "disparity")
+    H, W = meshgrid_src_homo.shape[:2]
+    B, Np = mpi_disparity_src.shape
+    out = torch.empty((B, Np, H, W, 3), device=meshgrid_src_homo.device, dtype=torch.float32)
+    check(handle(), lib.mdb_plane_xyz_src(handle(), _p(meshgrid_src_homo), _p(mpi_disparity_src), _k9(K_src_inv), W, H, Np, B, _p(out), _stream()))
+    return out
+
+
+def get_tgt_xyz_from_plane_disparity(xyz_src: torch.Tensor, pose: Pose) -> torch.Tensor:
+    """src/render.jl:51-62."""
+    _chk(xyz_src, "xyz_src"); _chk(pose.rvec, "rvec"); _chk(pose.tvec, "tvec")
+    B, Np, H, W, _ = xyz_src.shape
+    out = torch.empty_like(xyz_src)
+    check(handle(), lib.mdb_plane_xyz_tgt(handle(), _p(xyz_src), _p(pose.rvec), _p(pose.tvec), W, H, Np, B, _p(out), _stream()))
+    return out
+
+
+def _render_ws(W, H, Np, B, dev):
+    n = int(lib.mdb_render_workspace_bytes(W, H, Np, B))
+    if n == 0:
+        raise _lib.MdbError(-2, f"unsupported render shape W={W} H={H} Np={Np} B={B} (need W,H>=2, Np<=64)")
+    return torch.empty(n, dtype=torch.uint8, device=dev), n
+
+
+def sample(src: torch.Tensor, depth_src: torch.Tensor, pose: Pose, K, K_inv):
+    """`sample` -- src/render.jl:64-90.  src (B,Np,Cs,H,W) [Julia (W,H,Cs,Np*B)], depth_src (B,Np)
+    -> tgt (B,Np,Cs,H,W), valid_mask (B,Np,H,W) bool."""
+    _chk(src, "src"); _chk(depth_src, "depth_src")
+    B, Np, Cs, H, W = src.shape
+    ws, n = _render_ws(W, H, Np, B, src.device)
+    tgt = torch.empty_like(src)
+    valid = torch.empty((B, Np, H, W), dtype=torch.uint8, device=src.device)
+    check(handle(), lib.mdb_sample(handle(), _p(src), _p(depth_src), _p(pose.rvec), _p(pose.tvec), _k9(K), _k9(K_inv),
+                                   W, H, Cs, Np, B, _p(tgt), ct.c_void_p(valid.data_ptr()), _p(ws), n, _stream()))
+    return tgt, valid.bool()
+
+
+def plane_volume_rendering(rgb: torch.Tensor, sigma: torch.Tensor, xyz: torch.Tensor):
+    """src/render.jl:32-49 -> rgb_out (B,3,H,W), transparency_acc (B,Np,1,H,W), weights (B,Np,1,H,W)."""
+    _chk(rgb, "rgb"); _chk(sigma, "sigma"); _chk(xyz, "xyz")
+    B, Np, _, H, W = rgb.shape
+    rgb_out = torch.empty((B, 3, H, W), device=rgb.device, dtype=torch.float32)
+    tacc = torch.empty((B, Np, 1, H, W), device=rgb.device, dtype=torch.float32)
+    wts = torch.empty_like(tacc)
+    check(handle(), lib.mdb_plane_volume_rendering(handle(), _p(rgb), _p(sigma), _p(xyz), W, H, Np, B, _p(rgb_out), _p(tacc), _p(wts), _stream()))
+    return rgb_out, tacc, wts
+
+
+class _RenderFn(torch.autograd.Function):
+    """Forward = mdb_render_tgt_rgb_depth_fwd; backward = mdb_render_tgt_rgb_depth_bwd (the Julia
+    glue registers the same pair as a ChainRulesCore.rrule)."""
+
+    @staticmethod
+    def forward(ctx, rgb, sigma, disparity_src, xyz_tgt, rvec, tvec, K_inv, K):
+        B, Np, _, H, W = rgb.shape
+        ws, n = _render_ws(W, H, Np, B, rgb.device)
+        rgb_out = torch.empty((B, 3, H, W), device=rgb.device, dtype=torch.float32)
+        depth = torch.empty((B, Np, 1, H, W), device=rgb.device, dtype=torch.float32)
+        mask = torch.empty((B, 1, 1, H, W), device=rgb.device, dtype=torch.int32)
+        check(handle(), lib.mdb_render_tgt_rgb_depth_fwd(handle(), _p(rgb), _p(sigma), _p(disparity_src), _p(xyz_tgt), _p(rvec),
+                                                         _p(tvec), _k9(K_inv), _k9(K), W, H, Np, B, _p(rgb_out), _p(depth),
+                                                         ct.c_void_p(mask.data_ptr()), _p(ws), n, _stream()))
+        ctx.save_for_backward(rgb, sigma, disparity_src, xyz_tgt, rvec, tvec, depth)
+        ctx.K, ctx.K_inv, ctx.ws, ctx.n = K, K_inv, ws, n
+        ctx.mark_non_differentiable(mask)
+        return rgb_out, depth, mask
+
+    @staticmethod
+    def backward(ctx, g_rgb, g_depth, _g_mask):
+        rgb, sigma, disp, xyz, rvec, tvec, depth = ctx.saved_tensors
+        B, Np, _, H, W = rgb.shape
+        g_rgb = torch.zeros((B, 3, H, W), device=rgb.device) if g_rgb is None else g_rgb.contiguous()
+        g_depth = None if g_depth is None else g_depth.contiguous()
+        d_rgb, d_sigma, d_xyz = torch.empty_like(rgb), torch.empty_like(sigma), torch.empty_like(xyz)
+        d_disp, d_r, d_t = torch.empty_like(disp), torch.empty_like(rvec), torch.empty_like(tvec)
+        check(handle(), lib.mdb_render_tgt_rgb_depth_bwd(handle(), _p(rgb), _p(sigma), _p(disp), _p(xyz), _p(rvec), _p(tvec),
+                                                         _k9(ctx.K_inv), _k9(ctx.K), W, H, Np, B, _p(depth), _p(g_rgb), _p(g_depth),
+                                                         _p(d_rgb), _p(d_sigma), _p(d_xyz), _p(d_disp), _p(d_r), _p(d_t),
+                                                         _p(ctx.ws), ctx.n, _stream()))
+        return d_rgb, d_sigma, d_disp, d_xyz, d_r, d_t, None, None
+
+
+def render_tgt_rgb_depth(rgb, sigma, disparity_src, xyz_tgt, pose: Pose, K_inv, K):
+    """`render_tgt_rgb_depth` -- src/render.jl:92-114 -> (rgb (B,3,H,W), depth = transparency_acc
+    (B,Np,1,H,W), mask (B,1,1,H,W) int32).  Differentiable (autograd) w.r.t. rgb, sigma,
+    disparity_src, xyz_tgt and the pose."""
+    for t, nm in ((rgb, "rgb"), (sigma, "sigma"), (disparity_src, "disparity_src"), (xyz_tgt, "xyz_tgt"),
+                  (pose.rvec, "rvec"), (pose.tvec, "tvec")):
+        _chk(t, nm)
+    return _RenderFn.apply(rgb, sigma, disparity_src, xyz_tgt, pose.rvec, pose.tvec, K_inv, K)

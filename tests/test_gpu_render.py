@@ -1,0 +1,101 @@
+"""GPU parity of the plane-disparity rendering path (R1-R7, src/render.jl) against the float64
+oracle.  BASELINE.json tolerance: rendered rgb / "depth" within 1e-5; gradients 1e-4 relative.
+Shapes follow the reference's own scripts (test/test_render_tgt_rgb_depth.jl: B,N,H,W = 2,32,100,200,
+inputs ~ rand) and BASELINE config 4 (416x128, 32 planes, B=2)."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _dev(a):
+    return torch.tensor(a, device=DEV).contiguous()
+
+
+def _oracle_inputs(ri, grad=False):
+    from oracle import torch_ref as T
+    f = lambda a: torch.tensor(a, dtype=torch.float64, requires_grad=grad)
+    return (f(ri.rgb), f(ri.sigma), f(ri.disparity_src), f(ri.xyz_tgt), T.Pose(f(ri.rvec), f(ri.tvec)),
+            torch.tensor(ri.K_inv.astype(np.float64)), torch.tensor(ri.K.astype(np.float64)))
+
+
+def _rand_inputs(W, H, Np, B, seed, pose_scale):
+    """test/test_render_tgt_rgb_depth.jl style: everything ~ rand, pose ~ pose_scale * randn."""
+    from mdb200 import synth
+    ri = synth.make_render_inputs(W, H, Np, B, seed=seed, pose_scale=pose_scale)
+    rng = np.random.default_rng(seed)
+    ri.xyz_tgt = rng.random(ri.xyz_tgt.shape).astype(np.float32)
+    ri.sigma = (rng.random(ri.sigma.shape) - 0.2).astype(np.float32)   # some negative: exercises sigma .* (sigma .>= 0)
+    return ri
+
+
+@pytest.mark.parametrize("maker", ["config4", "rand_small_pose", "rand_big_pose"])
+def test_render_forward(maker):
+    import mdb200
+    from mdb200 import synth
+    from oracle import torch_ref as T
+    if maker == "config4":
+        ri = synth.make_render_inputs(416, 128, 32, 2)
+    elif maker == "rand_small_pose":
+        ri = _rand_inputs(200, 100, 32, 2, 1, 1.0)
+    else:
+        ri = _rand_inputs(64, 40, 8, 2, 2, 20.0)     # rvec ~ 0.2, tvec ~ 1: strongly non-identity homographies
+    rgb64, sig64, dsp64, xyz64, pose64, Ki64, K64 = _oracle_inputs(ri)
+    ro, do, mo = T.render_tgt_rgb_depth(rgb64, sig64, dsp64, xyz64, pose64, Ki64, K64)
+    rg, dg, mg = mdb200.render_tgt_rgb_depth(_dev(ri.rgb), _dev(ri.sigma), _dev(ri.disparity_src), _dev(ri.xyz_tgt),
+                                             mdb200.Pose(_dev(ri.rvec), _dev(ri.tvec)), ri.K_inv, ri.K)
+    assert (rg.double().cpu() - ro).abs().max() < 1e-5
+    assert (dg.double().cpu() - do).abs().max() < 1e-5
+    assert torch.equal(mg.cpu().long(), mo)
+
+
+def test_render_backward_vs_autograd():
+    import mdb200
+    from oracle import torch_ref as T
+    ri = _rand_inputs(96, 48, 12, 2, 3, 2.0)
+    ri.xyz_tgt = (ri.xyz_tgt + np.arange(12, dtype=np.float32)[None, :, None, None, None] * 0.5).astype(np.float32)
+    rgb64, sig64, dsp64, xyz64, pose64, Ki64, K64 = _oracle_inputs(ri, grad=True)
+    ro, do, _ = T.render_tgt_rgb_depth(rgb64, sig64, dsp64, xyz64, pose64, Ki64, K64)
+    g = torch.Generator().manual_seed(0)
+    wr = torch.rand(ro.shape, generator=g, dtype=torch.float64); wd = torch.rand(do.shape, generator=g, dtype=torch.float64)
+    loss64 = (ro * wr).sum() + (do * wd).sum()
+    refs = torch.autograd.grad(loss64, (rgb64, sig64, dsp64, xyz64, pose64.rvec, pose64.tvec))
+    ins = [_dev(a).requires_grad_() for a in (ri.rgb, ri.sigma, ri.disparity_src, ri.xyz_tgt, ri.rvec, ri.tvec)]
+    rg, dg, _ = mdb200.render_tgt_rgb_depth(ins[0], ins[1], ins[2], ins[3], mdb200.Pose(ins[4], ins[5]), ri.K_inv, ri.K)
+    ((rg * wr.to(DEV, torch.float32)).sum() + (dg * wd.to(DEV, torch.float32)).sum()).backward()
+    names = ["d_rgb", "d_sigma", "d_disparity_src", "d_xyz_tgt", "d_rvec", "d_tvec"]
+    for nm, t, r in zip(names, ins, refs):
+        err = (t.grad.double().cpu() - r).abs().max() / r.abs().max()
+        assert err < 1e-4, (nm, float(err))
+
+
+def test_render_primitives():
+    """inv, create_meshgrid, plane xyz producers, sample, plane_volume_rendering vs the oracle."""
+    import mdb200
+    from mdb200 import synth
+    from oracle import torch_ref as T
+    ri = synth.make_render_inputs(64, 32, 6, 2, seed=5, pose_scale=3.0)
+    A = torch.rand(5, 3, 3) + 2 * torch.eye(3)
+    assert torch.allclose(mdb200.inv(A.to(DEV)).cpu(), torch.linalg.inv(A.transpose(1, 2)).transpose(1, 2), atol=1e-5)
+    mesh = mdb200.create_meshgrid(32, 64)
+    assert torch.equal(mesh.cpu().double(), T.create_meshgrid(32, 64))
+    pose = mdb200.Pose(_dev(ri.rvec), _dev(ri.tvec))
+    pose64 = T.Pose(torch.tensor(ri.rvec, dtype=torch.float64), torch.tensor(ri.tvec, dtype=torch.float64))
+    Ki64, K64 = torch.tensor(ri.K_inv.astype(np.float64)), torch.tensor(ri.K.astype(np.float64))
+    xs = mdb200.get_src_xyz_from_plane_disparity(mesh, _dev(ri.disparity_src), ri.K_inv)
+    xs64 = T.get_src_xyz_from_plane_disparity(T.create_meshgrid(32, 64), torch.tensor(ri.disparity_src, dtype=torch.float64), Ki64)
+    assert torch.allclose(xs.cpu().double(), xs64, rtol=1e-5, atol=1e-5)
+    xt = mdb200.get_tgt_xyz_from_plane_disparity(xs, pose)
+    assert torch.allclose(xt.cpu().double(), T.get_tgt_xyz_from_plane_disparity(xs64, pose64), rtol=1e-5, atol=1e-4)
+    src = torch.rand(2, 6, 7, 32, 64)
+    depth = 1.0 / torch.tensor(ri.disparity_src)
+    tg, vm = mdb200.sample(src.to(DEV), depth.to(DEV), pose, ri.K, ri.K_inv)
+    tg64, vm64 = T.sample(src.double(), depth.double(), pose64, K64, Ki64)
+    assert (tg.cpu().double() - tg64).abs().max() < 1e-5 and torch.equal(vm.cpu(), vm64)
+    rgb, sig, xyz = torch.rand(2, 6, 3, 32, 64), torch.rand(2, 6, 1, 32, 64), torch.rand(2, 6, 32, 64, 3)
+    outs = mdb200.plane_volume_rendering(rgb.to(DEV), sig.to(DEV), xyz.to(DEV))
+    outs64 = T.plane_volume_rendering(rgb.double(), sig.double(), xyz.double())
+    for a, b in zip(outs, outs64):
+        assert (a.cpu().double() - b).abs().max() < 1e-5
