@@ -209,16 +209,14 @@ def run_ours(args):
                   source_ids=inp.source_ids, K=inp.K, invK=inp.invK, automasking=inp.automasking)
     plan = mdb200.FusedLoss(N=N, n_global=Ng, device=dev, **common)
     # [loss, d_rvec (S,N,3), d_tvec (S,N,3)] of every rank, all-reduced once per step
-    packed = torch.zeros(1 + 6 * S * Ng, device=dev)
+    from mdb200 import dist as mdist
+    packed = torch.zeros(mdist.packed_size(Ng, S), device=dev)
 
     def step():
         res = plan(x, disps, poses, auto)
         if world > 1:
-            packed.zero_()
-            packed[0] = res.loss
-            off = 1 + 6 * S * N * rank
-            packed[off:off + 6 * S * N] = torch.cat([t.reshape(-1) for p in res.d_poses for t in (p.rvec, p.tvec)])
-            dist.all_reduce(packed)
+            mdist.pack(res.loss, [p.rvec for p in res.d_poses], [p.tvec for p in res.d_poses], Ng, rank * N, out=packed)
+            mdist.allreduce_loss_posegrads(packed)
         return res
 
     def sync_all():
