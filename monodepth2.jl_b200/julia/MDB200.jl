@@ -1,0 +1,245 @@
+# MDB200.jl -- Julia glue for libmdb200.so: `ccall` wrappers + `ChainRulesCore.rrule`s that put the
+# B200 kernels behind the reference's own function signatures (jumerckx/Monodepth2.jl).
+#
+# NOT EXECUTED on the build / GPU boxes of this repository: neither has a Julia runtime (SURVEY F2).
+# The same C ABI is exercised end to end from Python (monodepth2.jl_b200/mdb200, tests/).  This file
+# is the binding a maintainer of the reference adds -- `include("MDB200.jl")` after
+# `include("training.jl")` in src/Monodepth.jl:62-74 -- and it only takes the fused path for
+# `CuArray{Float32}` arguments; every other method of the reference keeps working unchanged.
+#
+# Layout note: Julia's column-major (W,H,C,L,N) CuArray is passed as-is; the library reads the same
+# bytes as C order [N][L][C][H][W].  `K`/`invK` are passed as 9 host floats in column-major order.
+module MDB200
+
+using CUDA
+using ChainRulesCore
+import ..Monodepth: Pose, Params, TrainCache, SSIM
+
+const libmdb200 = get(ENV, "MDB200_LIB", joinpath(@__DIR__, "..", "mdb200", "libmdb200.so"))
+
+const MAX_SCALES = 8
+const MAX_SOURCES = 2
+
+# ---- mirrors of the C structs in include/mdb200.h -----------------------------------------------
+struct LossParams
+    min_depth::Cdouble
+    max_depth::Cdouble
+    disparity_smoothness::Cdouble
+    alpha::Cfloat
+    ssim_c1::Cfloat
+    ssim_c2::Cfloat
+    automasking::Int32
+    normalize_disparity::Int32
+    smooth_weight_mode::Int32
+    upsample_align_corners::Int32
+    n_global::Int32
+end
+
+struct LossIO
+    x::CuPtr{Cfloat}
+    W::Int32; H::Int32; C::Int32; L::Int32; N::Int32
+    target_id::Int32
+    S::Int32
+    source_ids::NTuple{MAX_SOURCES,Int32}
+    invert::NTuple{MAX_SOURCES,Int32}
+    rvec::NTuple{MAX_SOURCES,CuPtr{Cfloat}}
+    tvec::NTuple{MAX_SOURCES,CuPtr{Cfloat}}
+    Ls::Int32
+    disparity::NTuple{MAX_SCALES,CuPtr{Cfloat}}
+    dw::NTuple{MAX_SCALES,Int32}
+    dh::NTuple{MAX_SCALES,Int32}
+    scale::NTuple{MAX_SCALES,Cfloat}
+    auto_loss::CuPtr{Cfloat}
+    K::NTuple{9,Cfloat}
+    invK::NTuple{9,Cfloat}
+    loss::CuPtr{Cfloat}
+    d_disparity::NTuple{MAX_SCALES,CuPtr{Cfloat}}
+    d_rvec::NTuple{MAX_SOURCES,CuPtr{Cfloat}}
+    d_tvec::NTuple{MAX_SOURCES,CuPtr{Cfloat}}
+    vis_warp_loss::CuPtr{Cfloat}
+end
+
+# ---- handle + error convention (status codes -> Julia errors) ------------------------------------
+const HANDLE = Ref{Ptr{Cvoid}}(C_NULL)
+
+function handle()
+    if HANDLE[] == C_NULL
+        rc = ccall((:mdb_create, libmdb200), Int32, (Ref{Ptr{Cvoid}}, Int32), HANDLE, CUDA.deviceid(CUDA.device()))
+        rc == 0 || error("mdb_create failed with status $rc (needs an sm_100 device; there is no CPU fallback)")
+    end
+    HANDLE[]
+end
+
+function check(rc::Int32)
+    rc == 0 && return nothing
+    msg = unsafe_string(ccall((:mdb_last_error, libmdb200), Cstring, (Ptr{Cvoid},), handle()))
+    error("mdb200 error $rc: $msg")
+end
+
+stream_ptr() = Base.unsafe_convert(Ptr{Cvoid}, CUDA.stream().handle)
+pad(t, n, fill) = ntuple(i -> i <= length(t) ? t[i] : fill, n)
+k9(K) = NTuple{9,Cfloat}(Cfloat.(vec(Array(K))))           # column-major, as Julia stores it
+nullp() = CuPtr{Cfloat}(0)
+
+# ---- fine-grained entry points (same names as the reference) -------------------------------------
+function so3_exp_map(rvec::CuArray{Float32,2})              # src/utils.jl:106-121
+    N = size(rvec, 2)
+    R = CUDA.zeros(Float32, 3, 3, N)
+    GC.@preserve rvec R check(ccall((:mdb_so3_exp_map, libmdb200), Int32,
+        (Ptr{Cvoid}, CuPtr{Cfloat}, Int32, CuPtr{Cfloat}, Ptr{Cvoid}), handle(), rvec, N, R, stream_ptr()))
+    R
+end
+
+function composeT(rvec::CuArray{Float32,2}, t::CuArray{Float32,3}, invert::Bool)   # src/utils.jl:185-192
+    N = size(rvec, 2)
+    R = CUDA.zeros(Float32, 3, 3, N); to = CUDA.zeros(Float32, 3, 1, N)
+    GC.@preserve rvec t R to check(ccall((:mdb_compose_T, libmdb200), Int32,
+        (Ptr{Cvoid}, CuPtr{Cfloat}, CuPtr{Cfloat}, Int32, Int32, CuPtr{Cfloat}, CuPtr{Cfloat}, Ptr{Cvoid}),
+        handle(), rvec, t, Int32(invert), N, R, to, stream_ptr()))
+    R, to
+end
+
+function ChainRulesCore.rrule(::typeof(composeT), rvec::CuArray{Float32,2}, t::CuArray{Float32,3}, invert::Bool)
+    R, to = composeT(rvec, t, invert)
+    function composeT_pullback(Δ)
+        dR, dt = unthunk(Δ[1]), unthunk(Δ[2])
+        N = size(rvec, 2)
+        dr = CUDA.zeros(Float32, 3, N); dtv = CUDA.zeros(Float32, 3, 1, N)
+        dRc = dR isa AbstractZero ? CUDA.zeros(Float32, 3, 3, N) : CuArray{Float32}(dR)
+        dtc = dt isa AbstractZero ? CUDA.zeros(Float32, 3, 1, N) : CuArray{Float32}(dt)
+        GC.@preserve rvec t dRc dtc dr dtv check(ccall((:mdb_compose_T_bwd, libmdb200), Int32,
+            (Ptr{Cvoid}, CuPtr{Cfloat}, CuPtr{Cfloat}, Int32, Int32, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, Ptr{Cvoid}),
+            handle(), rvec, t, Int32(invert), N, dRc, dtc, dr, dtv, stream_ptr()))
+        NoTangent(), dr, dtv, NoTangent()
+    end
+    (R, to), composeT_pullback
+end
+
+function (ssim::SSIM)(x::CuArray{Float32,4}, y::CuArray{Float32,4})               # src/utils.jl:29-43
+    W, H, C, N = size(x)
+    out = similar(x)
+    GC.@preserve x y out check(ccall((:mdb_ssim, libmdb200), Int32,
+        (Ptr{Cvoid}, CuPtr{Cfloat}, CuPtr{Cfloat}, Int32, Int32, Int32, Int32, Cfloat, Cfloat, CuPtr{Cfloat}, Ptr{Cvoid}),
+        handle(), x, y, W, H, C, N, Cfloat(ssim.c1), Cfloat(ssim.c2), out, stream_ptr()))
+    out
+end
+
+function automasking_loss(ssim, inputs::CuArray{Float32,5}, target_id::Integer; source_ids)   # src/training.jl:9-11
+    W, H, C, L, N = size(inputs)
+    out = CUDA.zeros(Float32, W, H, 1, N)
+    ids = Int32.(collect(source_ids))
+    GC.@preserve inputs out ids check(ccall((:mdb_automasking_loss, libmdb200), Int32,
+        (Ptr{Cvoid}, CuPtr{Cfloat}, Int32, Ptr{Int32}, Int32, Int32, Int32, Int32, Int32, Int32, Cfloat, Cfloat, Cfloat, CuPtr{Cfloat}, Ptr{Cvoid}),
+        handle(), inputs, target_id, ids, length(ids), W, H, C, L, N, 0.85f0, Cfloat(ssim.c1), Cfloat(ssim.c2), out, stream_ptr()))
+    out
+end
+
+# ---- the fused hot path ---------------------------------------------------------------------------
+"""
+    fused_loss(x, disparities, poses, auto_loss, cache, parameters; kw...) -> (loss, ∇disparities, ∇poses)
+
+Value and gradient of `train_loss`'s arithmetic (src/training.jl:27-77) in one pass of the fused
+kernels.  `n_global` is the batch size the means divide by (multi-GPU shards pass the global N).
+"""
+function fused_loss(x::CuArray{Float32,5}, disparities::Vector{<:CuArray{Float32,4}}, poses::Vector{<:Pose},
+                    auto_loss, cache::TrainCache, parameters::Params;
+                    normalize_disparity::Bool=true, smooth_weight_mode::Integer=0, n_global::Integer=0)
+    W, H, C, L, N = size(x)
+    S, Ls = length(poses), length(disparities)
+    loss = CUDA.zeros(Float32, 1)
+    dd = [similar(d) for d in disparities]
+    dr = [similar(p.rvec) for p in poses]
+    dt = [similar(p.tvec) for p in poses]
+    io = LossIO(pointer(x), W, H, C, L, N, cache.target_id, S,
+        pad(Int32.(cache.source_ids), MAX_SOURCES, Int32(0)),
+        pad(Int32.(cache.source_ids .< cache.target_id), MAX_SOURCES, Int32(0)),   # src/training.jl:28
+        pad(map(p -> pointer(p.rvec), poses), MAX_SOURCES, nullp()),
+        pad(map(p -> pointer(p.tvec), poses), MAX_SOURCES, nullp()),
+        Ls, pad(map(pointer, disparities), MAX_SCALES, nullp()),
+        pad(Int32.(map(d -> size(d, 1), disparities)), MAX_SCALES, Int32(0)),
+        pad(Int32.(map(d -> size(d, 2), disparities)), MAX_SCALES, Int32(0)),
+        pad(Cfloat.(cache.scales), MAX_SCALES, 0f0),
+        parameters.automasking ? pointer(auto_loss) : nullp(),
+        k9(cache.K), k9(cache.invK), pointer(loss),
+        pad(map(pointer, dd), MAX_SCALES, nullp()), pad(map(pointer, dr), MAX_SOURCES, nullp()),
+        pad(map(pointer, dt), MAX_SOURCES, nullp()), nullp())
+    p = LossParams(parameters.min_depth, parameters.max_depth, parameters.disparity_smoothness, 0.85f0,
+        Cfloat(cache.ssim.c1), Cfloat(cache.ssim.c2), Int32(parameters.automasking), Int32(normalize_disparity),
+        Int32(smooth_weight_mode), Int32(1), Int32(n_global))
+    nbytes = ccall((:mdb_train_loss_workspace_bytes, libmdb200), Csize_t, (Ref{LossIO},), io)
+    nbytes > 0 || error("mdb200: unsupported shape for the fused loss")
+    ws = CuArray{UInt8}(undef, nbytes)
+    GC.@preserve x disparities poses auto_loss loss dd dr dt ws begin
+        check(ccall((:mdb_train_loss_fwdbwd, libmdb200), Int32,
+            (Ptr{Cvoid}, Ref{LossIO}, Ref{LossParams}, CuPtr{Cvoid}, Csize_t, Ptr{Cvoid}),
+            handle(), io, p, ws, nbytes, stream_ptr()))
+    end
+    loss, dd, [(rvec=dr[i], tvec=dt[i]) for i in 1:S]
+end
+
+# The scalar loss is the only output, so the rrule's forward runs forward+backward with unit seed and
+# the pullback scales the cached gradients by the incoming cotangent (SURVEY 8b).
+loss_value(x, disparities, poses, auto_loss, cache, parameters) =
+    Array(fused_loss(x, disparities, poses, auto_loss, cache, parameters)[1])[1]
+
+function ChainRulesCore.rrule(::typeof(loss_value), x, disparities, poses, auto_loss, cache, parameters)
+    loss, dd, dp = fused_loss(x, disparities, poses, auto_loss, cache, parameters)
+    function loss_value_pullback(Δ)
+        δ = Float32(unthunk(Δ))
+        NoTangent(), NoTangent(), [δ .* g for g in dd],
+        [Tangent{Pose}(rvec=δ .* g.rvec, tvec=δ .* g.tvec) for g in dp], NoTangent(), NoTangent(), NoTangent()
+    end
+    Array(loss)[1], loss_value_pullback
+end
+
+"""
+Drop-in `train_loss` (src/training.jl:21-78): same arguments and return tuple; only lines 27-69 of
+the reference body are replaced by `loss_value`.
+"""
+function train_loss(model, x::CuArray{Float32,5}, auto_loss, cache::TrainCache, parameters::Params, do_visualization)
+    disparities, poses = model(x, cache.source_ids, cache.target_id)           # src/training.jl:26
+    loss = loss_value(x, disparities, poses, auto_loss, cache, parameters)
+    vis_disparity = do_visualization ? Array(disparities[end]) : nothing
+    loss, vis_disparity, nothing, nothing
+end
+
+# ---- render path ------------------------------------------------------------------------------------
+function render_tgt_rgb_depth(rgb::CuArray{Float32,5}, sigma::CuArray{Float32,5}, disparity_src::CuArray{Float32,2},
+                              xyz_tgt::CuArray{Float32,5}, pose::Pose, K_inv, K)            # src/render.jl:92-114
+    W, H, _, Np, B = size(rgb)
+    rgb_out = CUDA.zeros(Float32, W, H, 3, B); depth = CUDA.zeros(Float32, W, H, 1, Np, B)
+    mask = CUDA.zeros(Int32, W, H, 1, 1, B)
+    nbytes = ccall((:mdb_render_workspace_bytes, libmdb200), Csize_t, (Int32, Int32, Int32, Int32), W, H, Np, B)
+    ws = CuArray{UInt8}(undef, nbytes)
+    Ki, Kk = collect(k9(K_inv)), collect(k9(K))
+    GC.@preserve rgb sigma disparity_src xyz_tgt pose rgb_out depth mask ws check(ccall((:mdb_render_tgt_rgb_depth_fwd, libmdb200), Int32,
+        (Ptr{Cvoid}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, Ptr{Cfloat}, Ptr{Cfloat},
+         Int32, Int32, Int32, Int32, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Int32}, CuPtr{Cvoid}, Csize_t, Ptr{Cvoid}),
+        handle(), rgb, sigma, disparity_src, xyz_tgt, pose.rvec, pose.tvec, Ki, Kk, W, H, Np, B, rgb_out, depth, mask, ws, nbytes, stream_ptr()))
+    rgb_out, depth, mask
+end
+
+function ChainRulesCore.rrule(::typeof(render_tgt_rgb_depth), rgb, sigma, disparity_src, xyz_tgt, pose::Pose, K_inv, K)
+    rgb_out, depth, mask = render_tgt_rgb_depth(rgb, sigma, disparity_src, xyz_tgt, pose, K_inv, K)
+    function render_pullback(Δ)
+        W, H, _, Np, B = size(rgb)
+        g_rgb = Δ[1] isa AbstractZero ? CUDA.zeros(Float32, size(rgb_out)) : CuArray{Float32}(unthunk(Δ[1]))
+        g_depth = Δ[2] isa AbstractZero ? CUDA.zeros(Float32, size(depth)) : CuArray{Float32}(unthunk(Δ[2]))
+        d_rgb, d_sigma, d_xyz = similar(rgb), similar(sigma), similar(xyz_tgt)
+        d_disp, d_r, d_t = similar(disparity_src), similar(pose.rvec), similar(pose.tvec)
+        nbytes = ccall((:mdb_render_workspace_bytes, libmdb200), Csize_t, (Int32, Int32, Int32, Int32), W, H, Np, B)
+        ws = CuArray{UInt8}(undef, nbytes)
+        Ki, Kk = collect(k9(K_inv)), collect(k9(K))
+        GC.@preserve rgb sigma disparity_src xyz_tgt pose depth g_rgb g_depth d_rgb d_sigma d_xyz d_disp d_r d_t ws check(ccall(
+            (:mdb_render_tgt_rgb_depth_bwd, libmdb200), Int32,
+            (Ptr{Cvoid}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, Ptr{Cfloat}, Ptr{Cfloat},
+             Int32, Int32, Int32, Int32, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat},
+             CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cvoid}, Csize_t, Ptr{Cvoid}),
+            handle(), rgb, sigma, disparity_src, xyz_tgt, pose.rvec, pose.tvec, Ki, Kk, W, H, Np, B, depth, g_rgb, g_depth,
+            d_rgb, d_sigma, d_xyz, d_disp, d_r, d_t, ws, nbytes, stream_ptr()))
+        NoTangent(), d_rgb, d_sigma, d_disp, d_xyz, Tangent{Pose}(rvec=d_r, tvec=d_t), NoTangent(), NoTangent()
+    end
+    (rgb_out, depth, mask), render_pullback
+end
+
+end # module
