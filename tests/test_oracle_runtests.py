@@ -83,9 +83,12 @@ def test_disparity_to_depth():  # runtests.jl:85-92
 
 
 def test_identity_warp():  # runtests.jl:94-122
+    # Seeded: with depth ~ U(0,1) the `+1e-7` in Project (src/utils.jl:101) moves u by 16e-7/depth px,
+    # so the reference's own unseeded test fails whenever a depth < ~2e-3 is drawn (~40 % of runs).
+    g = torch.Generator().manual_seed(94)
     res, N = 16, 2
-    image = torch.rand(N, 1, res, res, dtype=DT)
-    depth = torch.rand(N, res * res, dtype=DT)
+    image = torch.rand(N, 1, res, res, dtype=DT, generator=g)
+    depth = 0.05 + 0.95 * torch.rand(N, res * res, dtype=DT, generator=g)
     K_m = torch.tensor([[910.0, 0, res / 2], [0, 910.0, res / 2], [0, 0, 1]], dtype=DT)
     invK_m = torch.linalg.inv(K_m)
     R = T.so3_exp_map_m(torch.zeros(N, 3, dtype=DT))
