@@ -140,4 +140,5 @@ __global__ void disp_stats_finalize_kernel(FusedArgs a, const float* __restrict_
 }  // namespace
 
 #include "photo_fused_main.inl"
+#include "photo_strip.inl"
 #include "photo_fused_host.inl"

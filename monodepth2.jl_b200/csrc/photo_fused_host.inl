@@ -83,10 +83,37 @@ __global__ void finalize_loss_kernel(const double* __restrict__ item_loss, int N
 struct FusedLayout {
   size_t o_pp, o_ppd, o_statpart, o_stats, o_partials, o_itemloss, o_gfull[MDB_MAX_SCALES], total;
   int tiles_x, tiles_y, rowblocks, npart;
+  StripGeom strip;   // decomposition of the streaming kernel
+  int records;       // partial-sum records per item (tile kernel: tiles; strip kernel: warps per item)
+  bool use_strip;
 };
 
-FusedLayout fused_layout(const mdb_loss_io* io) {
+// MDB_FUSED_IMPL=tile selects the first-generation tiled kernel (kept for A/B measurements)
+inline bool mdb_use_strip() {
+  static const int v = [] { const char* e = getenv("MDB_FUSED_IMPL"); return (e && !strcmp(e, "tile")) ? 0 : 1; }();
+  return v != 0;
+}
+
+// Rows per segment: long segments amortise the 4 halo rows, short ones give the machine enough
+// warps.  Aim for ~16 resident sets of 12 warps per SM, never below 32 rows.
+inline StripGeom strip_geom(const mdb_loss_io* io, int num_sms) {
+  StripGeom g{};
+  g.nstrips = (io->W + STRIP_PX - 1) / STRIP_PX;
+  const long long base = (long long)io->N * io->Ls * g.nstrips;
+  long long want = ((long long)16 * 12 * (num_sms > 0 ? num_sms : 148) + base - 1) / base;
+  if (const char* e = getenv("MDB_STRIP_SEGS")) want = atoll(e);
+  const int max_segs = std::max(1, io->H / 32);
+  g.nsegs = (int)std::min<long long>(std::max<long long>(want, 1), max_segs);
+  g.seg_rows = (io->H + g.nsegs - 1) / g.nsegs;
+  g.nsegs = (io->H + g.seg_rows - 1) / g.seg_rows;
+  g.total = (int)(base * g.nsegs);
+  return g;
+}
+
+FusedLayout fused_layout(const mdb_loss_io* io, int num_sms = 148) {
   FusedLayout L{};
+  L.use_strip = mdb_use_strip();
+  L.strip = strip_geom(io, num_sms);
   L.tiles_x = (io->W + TW - 1) / TW;
   L.tiles_y = (io->H + TH - 1) / TH;
   L.rowblocks = (io->H + STAT_ROWS - 1) / STAT_ROWS;
@@ -97,7 +124,8 @@ FusedLayout fused_layout(const mdb_loss_io* io) {
   L.o_ppd = take(sizeof(PosePrepD) * io->N * io->S);
   L.o_statpart = take(sizeof(float) * (size_t)io->N * L.rowblocks * io->Ls * 3);
   L.o_stats = take(sizeof(ScaleStat) * (size_t)io->Ls * io->N);
-  L.o_partials = take(sizeof(float) * (size_t)io->N * L.tiles_x * L.tiles_y * L.npart);
+  L.records = L.use_strip ? L.strip.nsegs * L.strip.nstrips * io->Ls : L.tiles_x * L.tiles_y;
+  L.o_partials = take(sizeof(float) * (size_t)io->N * L.records * L.npart);
   L.o_itemloss = take(sizeof(double) * io->N);
   for (int s = 0; s < io->Ls; ++s) {
     const bool native = io->dw[s] == io->W && io->dh[s] == io->H;
@@ -123,6 +151,13 @@ int32_t launch_fused(mdb_handle* h, const FusedArgs& fa, const FusedLayout& L, c
   (void)configured;
   MDB_CUDA(h, cudaFuncSetAttribute(photo_fused_kernel<C, S>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    (int)SM::bytes));
+  if (L.use_strip) {
+    constexpr size_t smem = (size_t)3 * (S * (2 * C + 2) / 4) * STRIP_THREADS * sizeof(float4);
+    const int blocks = (L.strip.total + STRIP_WARPS - 1) / STRIP_WARPS;
+    photo_strip_kernel<C, S><<<blocks, STRIP_THREADS, smem, st>>>(fa, L.strip);
+    MDB_LAUNCHED(h);
+    return MDB_OK;
+  }
   dim3 grid(L.tiles_x, L.tiles_y, fa.N);
   photo_fused_kernel<C, S><<<grid, FUSED_THREADS, SM::bytes, st>>>(fa);
   MDB_LAUNCHED(h);
@@ -135,7 +170,9 @@ extern "C" {
 
 size_t mdb_train_loss_workspace_bytes(const mdb_loss_io* io) {
   if (!io_shape_ok(io)) return 0;
-  return fused_layout(io).total;
+  int dev = 0, sms = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  return fused_layout(io, sms).total;
 }
 
 int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_loss_params* p,
@@ -156,7 +193,7 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
   }
   for (int s = 0; s < io->Ls; ++s)
     MDB_REQUIRE(h, io->disparity[s] && io->d_disparity[s], MDB_E_INVALID_ARG, "null disparity pointer (scale %d)", s);
-  const FusedLayout L = fused_layout(io);
+  const FusedLayout L = fused_layout(io, h->num_sms);
   MDB_REQUIRE(h, workspace && workspace_bytes >= L.total && ((uintptr_t)workspace & 255) == 0, MDB_E_WORKSPACE,
               "workspace must be >= %zu bytes and 256-byte aligned", L.total);
   cudaStream_t st = (cudaStream_t)stream;
@@ -233,7 +270,7 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
     MDB_LAUNCHED(h);
   }
   mdb_prof_mark(h, pslot, 3, st);
-  const int tiles = L.tiles_x * L.tiles_y;
+  const int tiles = L.records;
   double* item_loss = (double*)(ws + L.o_itemloss);
   if (S == 2)
     finalize_item_kernel<2><<<N, FIN_THREADS, 0, st>>>(fa.partials, tiles, pa, nullptr, io->d_rvec[0], io->d_rvec[1],

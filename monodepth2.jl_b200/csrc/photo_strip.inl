@@ -1,0 +1,447 @@
+// photo_strip.inl -- the streaming "warp-strip" fused forward+backward kernel (included by
+// photo_fused.cu).  Reference path: src/training.jl:42-69 with everything it calls in
+// src/utils.jl (P5-P12, S2 of SURVEY 8a).
+//
+// One WARP owns a 28-pixel-wide column strip of one (item, scale) and streams down the rows of
+// its segment.  Lane l handles sample column X0 - 2 + l: 32 sample columns feed 30 window
+// columns feed 28 pixel columns, so the only redundancy is the 2+2 column halo.  Everything a
+// row needs from the rows above it lives in REGISTERS (three-row rings), everything it needs
+// from the columns beside it arrives by warp shuffle.  There is no block barrier and no
+// shared-memory tile; the only shared memory is a thread-private three-row ring that parks the
+// bilinear-sample derivatives between the forward row and its pullback two rows later.
+//
+//   row r arrives:  A  disparity -> depth -> project (double) -> 4 taps x C x S  -> x(r), dx/du, dx/dv
+//                   C  window row r-1: 3x3 moments as a vertical triple (registers) combined
+//                      across the three columns (shuffle) with Chan's update, which keeps the
+//                      variances free of the float32 cancellation of E[x^2]-mu^2; SSIM + L1 per
+//                      source, first-arg-min, automask, pullback coefficients of the winner
+//                   D  pixel row r-2: 3x3 box sums of the coefficient fields (vertical in
+//                      registers, horizontal by shuffle) -> d/d(sample) -> d/d(position) ->
+//                      dP' -> d disparity (written once) and the 12 pose sums per source
+//
+// The two sources ride in the two halves of packed f32x2 registers (FFMA2/FADD2/FMUL2, new in
+// sm_100): one issue slot does the arithmetic of both sources.
+namespace {
+
+constexpr int STRIP_PX = 28;
+constexpr int STRIP_WARPS = 4;
+constexpr int STRIP_THREADS = 32 * STRIP_WARPS;
+constexpr int SEL_NONE = 255;
+
+// ---- S floats packed: S = 2 uses the sm_100 f32x2 pipe ----------------------------------
+template <int S> struct Pk;
+template <> struct Pk<1> {
+  float v;
+  MDB_DEV Pk() {}
+  MDB_DEV explicit Pk(float f) : v(f) {}
+  MDB_DEV float get(int) const { return v; }
+  MDB_DEV void set(int, float f) { v = f; }
+  friend MDB_DEV Pk operator+(Pk a, Pk b) { return Pk(a.v + b.v); }
+  friend MDB_DEV Pk operator-(Pk a, Pk b) { return Pk(a.v - b.v); }
+  friend MDB_DEV Pk operator*(Pk a, Pk b) { return Pk(a.v * b.v); }
+  friend MDB_DEV Pk pfma(Pk a, Pk b, Pk c) { return Pk(fmaf(a.v, b.v, c.v)); }
+  MDB_DEV Pk shfl(int src) const { return Pk(__shfl_sync(MDB_FULL, v, src)); }
+};
+template <> struct Pk<2> {
+  float2 v;
+  MDB_DEV Pk() {}
+  MDB_DEV explicit Pk(float f) : v(make_float2(f, f)) {}
+  MDB_DEV Pk(float a, float b) : v(make_float2(a, b)) {}
+  MDB_DEV explicit Pk(float2 f) : v(f) {}
+  MDB_DEV float get(int s) const { return s == 0 ? v.x : v.y; }
+  MDB_DEV void set(int s, float f) { if (s == 0) v.x = f; else v.y = f; }
+  friend MDB_DEV Pk operator+(Pk a, Pk b) { return Pk(__fadd2_rn(a.v, b.v)); }
+  friend MDB_DEV Pk operator-(Pk a, Pk b) { return Pk(__fadd2_rn(a.v, make_float2(-b.v.x, -b.v.y))); }
+  friend MDB_DEV Pk operator*(Pk a, Pk b) { return Pk(__fmul2_rn(a.v, b.v)); }
+  friend MDB_DEV Pk pfma(Pk a, Pk b, Pk c) { return Pk(__ffma2_rn(a.v, b.v, c.v)); }
+  MDB_DEV Pk shfl(int src) const {
+    return Pk(__shfl_sync(MDB_FULL, v.x, src), __shfl_sync(MDB_FULL, v.y, src));
+  }
+};
+template <int S> MDB_DEV Pk<S> pfma(Pk<S> a, float b, Pk<S> c) { return pfma(a, Pk<S>(b), c); }
+template <int S> MDB_DEV Pk<S> operator*(Pk<S> a, float b) { return a * Pk<S>(b); }
+template <int S> MDB_DEV Pk<S> operator+(Pk<S> a, float b) { return a + Pk<S>(b); }
+
+struct StripGeom {
+  int nstrips, nsegs, seg_rows, total;  // total = N * nsegs * nstrips * Ls warps
+};
+
+template <int C, int S>
+__global__ void __launch_bounds__(STRIP_THREADS)
+photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
+  using P = Pk<S>;
+  constexpr int NPART = 1 + NPOSE * S;
+  constexpr int DRV = S * (2 * C + 2);  // floats parked per (thread, row): dx/du, dx/dv per channel, u, v
+  constexpr int DRV4 = DRV / 4;
+  extern __shared__ float4 s_drv[];     // [3 rows][DRV4][STRIP_THREADS]
+
+  // the shuffle makes the warp index provably warp-uniform, so every branch on the strip geometry
+  // below is uniform for the compiler and the row shuffles need no WARPSYNC
+  const int lane = threadIdx.x & 31, warp = __shfl_sync(MDB_FULL, (int)(threadIdx.x >> 5), 0);
+  int w = blockIdx.x * STRIP_WARPS + warp;
+  if (w >= g.total) return;
+  const int rec = w;
+  const int sc = w % a.Ls; w /= a.Ls;
+  const int strip = w % g.nstrips; w /= g.nstrips;
+  const int seg = w % g.nsegs;
+  const int n = w / g.nsegs;
+
+  const int W = a.W, H = a.H;
+  const size_t plane = (size_t)W * H;
+  const int X0 = strip * STRIP_PX;
+  const int Y0 = seg * g.seg_rows, Y1 = min(Y0 + g.seg_rows, H);
+  const int gx = X0 - 2 + lane;
+  const bool colv = gx >= 0 && gx < W;                          // a real sample column
+  const bool wcol = colv && lane >= 1 && lane <= 30;            // a window column of this strip
+  const bool pcol = colv && lane >= 2 && lane <= 29;            // a pixel column this warp owns
+  // neighbour lanes of a window column, with pad_reflect(1) folded in (src/utils.jl:30-31)
+  const int nl = (gx == 0) ? lane + 1 : max(lane - 1, 0);
+  const int nr = (gx == W - 1) ? lane - 1 : min(lane + 1, 31);
+  // multiplicity of this pixel inside its left / right neighbour windows (reflected twice at the border)
+  const float wl = (gx == 1) ? 2.0f : 1.0f, wr_ = (gx == W - 2) ? 2.0f : 1.0f;
+
+  const float* tgt = a.x + ((size_t)n * a.L + a.tgt) * C * plane;
+  const float* srcp[S];
+#pragma unroll
+  for (int s = 0; s < S; ++s) srcp[s] = a.x + ((size_t)n * a.L + a.src[s]) * C * plane;
+  const float* dsp = a.disp[sc] + (size_t)n * a.dw[sc] * a.dh[sc];
+  float* gout = a.gout[sc] + (size_t)n * plane;
+  const bool native = a.native[sc] != 0;
+  const int dw = a.dw[sc], dh = a.dh[sc];
+
+  // ---- per-lane projection state: P' = A q + invd b, q = [px, py, 1], A = I + dA -------------
+  // p_i = A_i . q is carried down the rows by adding column 1 of A (double: no drift that matters)
+  double p1[S], p2[S], p3[S], i1[S], i2[S], i3[S], b0[S], b1[S], b3e[S];
+  float b0f[S], b1f[S], b3f[S];
+  {
+    const double px = (double)(gx + 1), py = (double)(Y0 - 2 + 1);
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+      const PosePrepD& pp = a.ppd[(size_t)n * S + s];
+      p1[s] = fma(1.0 + pp.dA[0], px, fma(pp.dA[1], py, pp.dA[2]));
+      p2[s] = fma(pp.dA[3], px, fma(1.0 + pp.dA[4], py, pp.dA[5]));
+      p3[s] = fma(pp.dA[6], px, fma(pp.dA[7], py, 1.0 + pp.dA[8]));
+      i1[s] = pp.dA[1]; i2[s] = 1.0 + pp.dA[4]; i3[s] = pp.dA[7];
+      b0[s] = pp.b[0]; b1[s] = pp.b[1]; b3e[s] = pp.b[2] + 1e-7;
+      b0f[s] = (float)b0[s]; b1f[s] = (float)b1[s]; b3f[s] = (float)b3e[s];
+    }
+  }
+  // bilinear up-sampling of the disparity (align-corners): the column part is per lane
+  int ux0 = 0, ux1 = 0;
+  double ulx = 0.0;
+  if (!native) {
+    const double f = (double)min(max(gx, 0), W - 1) * a.rxd[sc];
+    ux0 = min((int)f, dw - 1);
+    ulx = f - (double)ux0;
+    ux1 = min(ux0 + 1, dw - 1);
+  }
+
+  const float ksu = a.alpha / (9.0f * C) * a.up;   // SSIM pullback factor alpha / C / 9, times 1/(W H N Ls)
+  const float klu = (1.0f - a.alpha) / C * a.up;   // L1 factor
+  const float kl = (1.0f - a.alpha) / C, ka = a.alpha / C;
+  const ScaleStat st = a.stats[(size_t)sc * a.N + n];
+  const float skx = st.inv_mp * a.kx[sc], sky = st.inv_mp * a.ky[sc];
+
+  // ---- rings (registers) ---------------------------------------------------------------------
+  P xr1[C], xr2[C];            // warped samples of rows r-1, r-2 (both sources packed)
+  float yr1[C], yr2[C];        // target rows r-1, r-2
+  float F1[3 * C], F2[3 * C];  // winner's pullback coefficients of window rows r-2 (F1), r-3 (F2)
+  int sel1 = SEL_NONE, sel2 = SEL_NONE;
+  float d1 = 0.0f, d2 = 0.0f, d3 = 0.0f;  // disparity rows r-1, r-2, r-3
+  float wy_dn = 0.0f;                      // smoothness weight between rows r-2 and r-1
+#pragma unroll
+  for (int c = 0; c < C; ++c) { xr1[c] = P(0.0f); xr2[c] = P(0.0f); yr1[c] = yr2[c] = 0.0f; }
+#pragma unroll
+  for (int k = 0; k < 3 * C; ++k) F1[k] = F2[k] = 0.0f;
+
+  float loss_acc = 0.0f;
+  P S0[3], SP[3], SI[3];  // sum dP_i, sum dP_i py, sum dP_i invd  (times px at the end for column 0)
+#pragma unroll
+  for (int i = 0; i < 3; ++i) { S0[i] = P(0.0f); SP[i] = P(0.0f); SI[i] = P(0.0f); }
+
+  int slot = 0;  // ring slot of row r in s_drv
+  for (int r = Y0 - 2; r <= Y1 + 1; ++r) {
+    const bool rowv = r >= 0 && r < H;
+    // =========================== A: sample row r ===============================================
+    P xn[C];
+    float yn[C], dn = 0.0f;
+#pragma unroll
+    for (int c = 0; c < C; ++c) { xn[c] = P(0.0f); yn[c] = 0.0f; }
+    if (rowv && colv) {
+      double dd_;
+      if (native) {
+        dd_ = (double)ldg(dsp + (size_t)r * W + gx);
+      } else {
+        const double fy = (double)r * a.ryd[sc];
+        const int y0 = min((int)fy, dh - 1), y1 = min(y0 + 1, dh - 1);
+        const double ly = fy - (double)y0;
+        const double v00 = ldg(dsp + (size_t)y0 * dw + ux0), v01 = ldg(dsp + (size_t)y0 * dw + ux1);
+        const double v10 = ldg(dsp + (size_t)y1 * dw + ux0), v11 = ldg(dsp + (size_t)y1 * dw + ux1);
+        const double top = fma(ulx, v01 - v00, v00), bot = fma(ulx, v11 - v10, v10);
+        dd_ = fma(ly, bot - top, top);
+      }
+      dn = (float)dd_;
+      const double invd = fma(dd_, a.dd_d, a.mind_d);   // 1 / depth (src/utils.jl:179-183)
+#pragma unroll
+      for (int c = 0; c < C; ++c) yn[c] = ldg(tgt + c * plane + (size_t)r * W + gx);
+
+      int o00[S], o01[S], o10[S], o11[S];
+      P fx, fy_, mzx, mzy, uu, vv;
+#pragma unroll
+      for (int s = 0; s < S; ++s) {
+        // Backproject -> Project -> normalize -> grid_sample's unnormalize (src/utils.jl:67-69,
+        // 99-103; src/training.jl:56) cancel to u = P'1 / z'', z'' = P'3 + invd 1e-7 (in units of depth)
+        const double P1 = fma(invd, b0[s], p1[s]), P2 = fma(invd, b1[s], p2[s]), z = fma(invd, b3e[s], p3[s]);
+        double zi = (double)rcp_approx((float)z);      // float seed + one Newton step: ~1e-14 relative
+        zi = fma(zi, fma(-z, zi, 1.0), zi);
+        const double X = fma(P1, zi, -1.0), Y = fma(P2, zi, -1.0);   // 0-based source coordinates
+        int ix = __double2int_rd(X), iy = __double2int_rd(Y);
+        float fxs = (float)(X - (double)ix), fys = (float)(Y - (double)iy);
+        // NNlib grid_sample(padding_mode=:border), align-corners: clamp to [0, W-1]; no gradient where clamped
+        const bool inx = ix >= 0 && ix <= W - 2 && !(ix == 0 && fxs == 0.0f);
+        const bool iny = iy >= 0 && iy <= H - 2 && !(iy == 0 && fys == 0.0f);
+        if (!inx) { ix = min(max(ix, 0), W - 1); fxs = 0.0f; }
+        if (!iny) { iy = min(max(iy, 0), H - 1); fys = 0.0f; }
+        const int ix1 = min(ix + 1, W - 1), iy1 = min(iy + 1, H - 1);
+        o00[s] = iy * W + ix; o01[s] = iy * W + ix1; o10[s] = iy1 * W + ix; o11[s] = iy1 * W + ix1;
+        const float zf = (float)zi;
+        fx.set(s, fxs); fy_.set(s, fys);
+        mzx.set(s, inx ? zf : 0.0f); mzy.set(s, iny ? zf : 0.0f);
+        uu.set(s, (float)X + 1.0f); vv.set(s, (float)Y + 1.0f);
+      }
+      float park[DRV];
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+        P v00, v01, v10, v11;
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+          const float* p = srcp[s] + c * plane;
+          v00.set(s, ldg(p + o00[s])); v01.set(s, ldg(p + o01[s]));
+          v10.set(s, ldg(p + o10[s])); v11.set(s, ldg(p + o11[s]));
+        }
+        const P h0 = v01 - v00, h1 = v11 - v10;
+        const P top = pfma(fx, h0, v00), bot = pfma(fx, h1, v10);
+        const P dyv = bot - top;
+        xn[c] = pfma(fy_, dyv, top);
+        const P dxv = pfma(fy_, h1 - h0, h0);
+        const P dxz = dxv * mzx, dyz = dyv * mzy;   // d sample / d P'1, d P'2 up to the common 1/z''
+#pragma unroll
+        for (int s = 0; s < S; ++s) { park[(2 * c) * S + s] = dxz.get(s); park[(2 * c + 1) * S + s] = dyz.get(s); }
+      }
+#pragma unroll
+      for (int s = 0; s < S; ++s) { park[2 * C * S + s] = uu.get(s); park[(2 * C + 1) * S + s] = vv.get(s); }
+#pragma unroll
+      for (int k = 0; k < DRV4; ++k)
+        s_drv[(slot * DRV4 + k) * STRIP_THREADS + threadIdx.x] =
+            make_float4(park[4 * k], park[4 * k + 1], park[4 * k + 2], park[4 * k + 3]);
+    }
+#pragma unroll
+    for (int s = 0; s < S; ++s) { p1[s] += i1[s]; p2[s] += i2[s]; p3[s] += i3[s]; }
+
+    // =========================== C: window row r-1 =============================================
+    const int wr = r - 1;
+    float Fn[3 * C];
+    int seln = SEL_NONE;
+#pragma unroll
+    for (int k = 0; k < 3 * C; ++k) Fn[k] = 0.0f;
+    if (r >= Y0 && wr >= 0 && wr < H) {             // warp-uniform
+      const bool rt = wr == 0, rb = wr == H - 1;    // reflected rows
+      P vm[C], vq[C], vc[C];
+      float vmy[C], vqy[C];
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+        const P top = rt ? xn[c] : xr2[c], bot = rb ? xr2[c] : xn[c], mid = xr1[c];
+        const float ty = rt ? yn[c] : yr2[c], by = rb ? yr2[c] : yn[c], my_ = yr1[c];
+        const float e1 = ty - my_, e2 = by - my_, se = e1 + e2, se3 = se * (-1.0f / 3.0f);
+        vmy[c] = fmaf(se, 1.0f / 3.0f, my_);
+        vqy[c] = fmaf(e1, e1, fmaf(e2, e2, se * se3));
+        const P g1 = top - mid, g2 = bot - mid, sg = g1 + g2, sg3 = sg * (-1.0f / 3.0f);
+        vm[c] = pfma(sg, 1.0f / 3.0f, mid);
+        vq[c] = pfma(g1, g1, pfma(g2, g2, sg * sg3));
+        vc[c] = pfma(g1, e1, pfma(g2, e2, sg3 * se));
+      }
+      P lossv(0.0f);
+      P cA[C], cB[C], cC[C];
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+        // combine the column triples l-1, l, l+1 (Chan): M2 = sum q_j + 3 sum (m_j - M)^2
+        const float myL = __shfl_sync(MDB_FULL, vmy[c], nl), myR = __shfl_sync(MDB_FULL, vmy[c], nr);
+        const float qyL = __shfl_sync(MDB_FULL, vqy[c], nl), qyR = __shfl_sync(MDB_FULL, vqy[c], nr);
+        const P mL = vm[c].shfl(nl), mR = vm[c].shfl(nr);
+        const P qL = vq[c].shfl(nl), qR = vq[c].shfl(nr);
+        const P cL = vc[c].shfl(nl), cR = vc[c].shfl(nr);
+        const float e1 = myL - vmy[c], e2 = myR - vmy[c], se = e1 + e2, se3 = se * (-1.0f / 3.0f);
+        const float My = fmaf(se, 1.0f / 3.0f, vmy[c]);
+        const float Qy = fmaf(3.0f, fmaf(e1, e1, fmaf(e2, e2, se * se3)), qyL + vqy[c] + qyR);   // 9 var(y)
+        const P g1 = mL - vm[c], g2 = mR - vm[c], sg = g1 + g2, sg3 = sg * (-1.0f / 3.0f);
+        const P Mx = pfma(sg, 1.0f / 3.0f, vm[c]);
+        const P Qx = pfma(pfma(g1, g1, pfma(g2, g2, sg * sg3)), 3.0f, qL + vq[c] + qR);          // 9 var(x)
+        const P Cxy = pfma(pfma(g1, e1, pfma(g2, e2, sg3 * se)), 3.0f, cL + vc[c] + cR);         // 9 cov(x,y)
+        // SSIM (src/utils.jl:29-43) and its pullback wrt mu_x (A), sigma_x (B), sigma_xy (Cc)
+        const P n1 = pfma(Mx, 2.0f * My, P(a.c1));
+        const P n2 = pfma(Cxy, 2.0f / 9.0f, P(a.c2));
+        const P dd1 = pfma(Mx, Mx, P(fmaf(My, My, a.c1)));
+        const P dd2 = pfma(Qx + Qy, 1.0f / 9.0f, P(a.c2));
+        P r1, r2, q1, q2;
+#pragma unroll
+        for (int s = 0; s < S; ++s) { q1.set(s, rcp_approx(dd1.get(s))); q2.set(s, rcp_approx(dd2.get(s))); }
+        r1 = n1 * q1; r2 = n2 * q2;
+        const P r12 = r1 * r2;
+        const P raw = pfma(r12, -0.5f, P(0.5f));
+        const P dmu = Mx + (-My);
+        const P Abar = (r2 * q1) * (q1 * dmu) * pfma(Mx + My, My, P(a.c1));
+        const P Bb = (r12 * q2) * 0.5f;
+        const P Cb = (r1 * q2) * (-1.0f);
+        const P A0 = pfma(Mx * Bb, -2.0f, pfma(Cb, -My, Abar));   // A - 2 mu_x B - mu_y C
+        const P l1 = xr1[c] + (-yr1[c]);
+        P sv, ab;
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+          const float rw = raw.get(s);
+          const bool inside = rw >= 0.0f && rw <= 1.0f;
+          sv.set(s, fminf(fmaxf(rw, 0.0f), 1.0f));
+          ab.set(s, fabsf(l1.get(s)));
+          cA[c].set(s, inside ? A0.get(s) : 0.0f);
+          cB[c].set(s, inside ? Bb.get(s) : 0.0f);
+          cC[c].set(s, inside ? Cb.get(s) : 0.0f);
+        }
+        lossv = pfma(sv, ka, pfma(ab, kl, lossv));
+      }
+      int best = 0;
+      float val = lossv.get(0);
+#pragma unroll
+      for (int s = 1; s < S; ++s)
+        if (lossv.get(s) < val) { val = lossv.get(s); best = s; }   // first arg-min wins ties
+      if (a.automask && wcol) {
+        const float am = ldg(a.auto_loss + (size_t)n * plane + (size_t)wr * W + gx);
+        if (am <= val) { val = am; best = SEL_NONE; }               // mask precedes warp_loss
+      }
+      if (!wcol) best = SEL_NONE;
+      seln = best;
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+        float fa = cA[c].get(0), fb = cB[c].get(0), fc = cC[c].get(0);
+#pragma unroll
+        for (int s = 1; s < S; ++s) {
+          fa = (best == s) ? cA[c].get(s) : fa; fb = (best == s) ? cB[c].get(s) : fb; fc = (best == s) ? cC[c].get(s) : fc;
+        }
+        const bool none = best == SEL_NONE;
+        Fn[3 * c] = none ? 0.0f : fa; Fn[3 * c + 1] = none ? 0.0f : fb; Fn[3 * c + 2] = none ? 0.0f : fc;
+      }
+      if (pcol && wr >= Y0 && wr < Y1) {
+        loss_acc += val;
+        if (a.vis && sc == a.Ls - 1) a.vis[(size_t)n * plane + (size_t)wr * W + gx] = val;
+      }
+    }
+
+    // =========================== D: pixel row r-2 ==============================================
+    const int pr = r - 2;
+    const float wy_up = wy_dn;
+    if (r >= Y0 + 1) {  // weight between rows r-2 and r-1 (needed below, and as wy_up next iteration)
+      float e = 0.0f;
+#pragma unroll
+      for (int c = 0; c < C; ++c) e += fabsf(yr2[c] - yr1[c]);
+      wy_dn = (pr >= 0 && pr + 1 < H) ? __expf(-e * (1.0f / C)) : 0.0f;
+    }
+    if (r >= Y0 + 2) {  // warp-uniform; pr in [Y0, Y1)
+      // box sums of the coefficient fields over the 3x3 windows containing this pixel, per source
+      const float wu = (pr == 1) ? 2.0f : 1.0f, wd = (pr == H - 2) ? 2.0f : 1.0f;
+      P ma, mb, mc;   // row weights gated by which source won the window
+#pragma unroll
+      for (int s = 0; s < S; ++s) {
+        ma.set(s, sel2 == s ? wu : 0.0f); mb.set(s, sel1 == s ? 1.0f : 0.0f); mc.set(s, seln == s ? wd : 0.0f);
+      }
+      P T[3 * C];
+#pragma unroll
+      for (int k = 0; k < 3 * C; ++k) {
+        const P V = pfma(ma, F2[k], pfma(mb, F1[k], mc * Fn[k]));
+        const P VL = V.shfl(lane - 1 < 0 ? 0 : lane - 1), VR = V.shfl(lane + 1 > 31 ? 31 : lane + 1);
+        T[k] = pfma(VL, wl, pfma(VR, wr_, V));
+      }
+      // smoothness neighbours (src/utils.jl:163-177)
+      const float dl = __shfl_sync(MDB_FULL, d2, max(lane - 1, 0)), dr = __shfl_sync(MDB_FULL, d2, min(lane + 1, 31));
+      float ex = 0.0f;
+#pragma unroll
+      for (int c = 0; c < C; ++c) ex += fabsf(yr2[c] - __shfl_sync(MDB_FULL, yr2[c], min(lane + 1, 31)));
+      const float wxr = (gx + 1 < W) ? __expf(-ex * (1.0f / C)) : 0.0f;
+      const float wxl = __shfl_sync(MDB_FULL, wxr, max(lane - 1, 0));
+      if (pcol) {
+        const float4* dv = s_drv + (size_t)((slot + 1) % 3 * DRV4) * STRIP_THREADS + threadIdx.x;
+        float park[DRV];
+#pragma unroll
+        for (int k = 0; k < DRV4; ++k) {
+          const float4 q = dv[k * STRIP_THREADS];
+          park[4 * k] = q.x; park[4 * k + 1] = q.y; park[4 * k + 2] = q.z; park[4 * k + 3] = q.w;
+        }
+        P dP0(0.0f), dP1(0.0f);
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+          const P x = xr2[c];
+          const float y = yr2[c];
+          P sg;
+#pragma unroll
+          for (int s = 0; s < S; ++s) sg.set(s, sel1 == s ? sgnf(x.get(s) - y) : 0.0f);
+          // d loss / d sample = ks [T_A + 2 x T_B + y T_C] + kl sign(x - y) [this window chose s]
+          const P G = pfma(pfma(x * 2.0f, T[3 * c + 1], pfma(T[3 * c + 2], y, T[3 * c])), ksu, sg * klu);
+          P dxz, dyz;
+#pragma unroll
+          for (int s = 0; s < S; ++s) { dxz.set(s, park[(2 * c) * S + s]); dyz.set(s, park[(2 * c + 1) * S + s]); }
+          dP0 = pfma(G, dxz, dP0);
+          dP1 = pfma(G, dyz, dP1);
+        }
+        P uu, vv;
+#pragma unroll
+        for (int s = 0; s < S; ++s) { uu.set(s, park[2 * C * S + s]); vv.set(s, park[(2 * C + 1) * S + s]); }
+        // u = P'1 / z'', v = P'2 / z''  =>  dP'3 = -(u dP'1 + v dP'2)   (the 1/z'' is already inside dxz, dyz)
+        const P dP2 = pfma(dP0, uu, dP1 * vv) * (-1.0f);
+        const float invd = fmaf(d2, a.dd, a.mind);
+        const float py = (float)(pr + 1);
+        S0[0] = S0[0] + dP0; S0[1] = S0[1] + dP1; S0[2] = S0[2] + dP2;
+        SP[0] = pfma(dP0, py, SP[0]); SP[1] = pfma(dP1, py, SP[1]); SP[2] = pfma(dP2, py, SP[2]);
+        SI[0] = pfma(dP0, invd, SI[0]); SI[1] = pfma(dP1, invd, SI[1]); SI[2] = pfma(dP2, invd, SI[2]);
+        float dinvd = 0.0f;
+#pragma unroll
+        for (int s = 0; s < S; ++s)
+          dinvd += dP0.get(s) * b0f[s] + dP1.get(s) * b1f[s] + dP2.get(s) * b3f[s];
+        float gr = dinvd * a.dd;   // d invd / d disparity = 1/min_depth - 1/max_depth
+        float gsx = 0.0f, gsy = 0.0f;
+        if (gx + 1 < W) gsx += sgnf(d2 - dr) * wxr;
+        if (gx > 0) gsx -= sgnf(dl - d2) * wxl;
+        if (pr + 1 < H) gsy += sgnf(d2 - d1) * wy_dn;
+        if (pr > 0) gsy -= sgnf(d3 - d2) * wy_up;
+        gr += skx * gsx + sky * gsy + st.cconst;
+        gout[(size_t)pr * W + gx] = gr;
+      }
+    }
+
+    // ---- rotate the rings ---------------------------------------------------------------------
+#pragma unroll
+    for (int c = 0; c < C; ++c) { xr2[c] = xr1[c]; xr1[c] = xn[c]; yr2[c] = yr1[c]; yr1[c] = yn[c]; }
+#pragma unroll
+    for (int k = 0; k < 3 * C; ++k) { F2[k] = F1[k]; F1[k] = Fn[k]; }
+    sel2 = sel1; sel1 = seln;
+    d3 = d2; d2 = d1; d1 = dn;
+    slot = (slot + 1) % 3;
+  }
+
+  // ---- one record per warp: loss + 12 pose sums per source (no atomics) -------------------------
+  float* out = a.partials + (size_t)rec * NPART;
+  {
+    const float v = warp_sum(loss_acc);
+    if (lane == 0) out[0] = v;
+  }
+  const float px = (float)(gx + 1);
+#pragma unroll
+  for (int s = 0; s < S; ++s)
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const float s0 = S0[i].get(s);
+      const float v0 = warp_sum(s0 * px), v1 = warp_sum(SP[i].get(s)), v2 = warp_sum(s0), v3 = warp_sum(SI[i].get(s));
+      if (lane == 0) {
+        out[1 + s * NPOSE + 3 * i] = v0; out[1 + s * NPOSE + 3 * i + 1] = v1; out[1 + s * NPOSE + 3 * i + 2] = v2;
+        out[1 + s * NPOSE + 9 + i] = v3;
+      }
+    }
+}
+
+}  // namespace
