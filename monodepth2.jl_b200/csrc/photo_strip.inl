@@ -27,6 +27,9 @@ constexpr int STRIP_PX = 28;
 constexpr int STRIP_WARPS = 4;
 constexpr int STRIP_THREADS = 32 * STRIP_WARPS;
 constexpr int SEL_NONE = 255;
+#ifndef STRIP_MINB
+#define STRIP_MINB 4   // CTAs per SM the register allocation aims for (128 registers; measured best of 2/3/4)
+#endif
 
 // ---- S floats packed: S = 2 uses the sm_100 f32x2 pipe ----------------------------------
 template <int S> struct Pk;
@@ -58,6 +61,9 @@ template <> struct Pk<2> {
     return Pk(__shfl_sync(MDB_FULL, v.x, src), __shfl_sync(MDB_FULL, v.y, src));
   }
 };
+// sign(v) with sign(0) = 0, without an int->float conversion
+MDB_DEV float sgn1(float v) { return v == 0.0f ? 0.0f : copysignf(1.0f, v); }
+
 template <int S> MDB_DEV Pk<S> pfma(Pk<S> a, float b, Pk<S> c) { return pfma(a, Pk<S>(b), c); }
 template <int S> MDB_DEV Pk<S> operator*(Pk<S> a, float b) { return a * Pk<S>(b); }
 template <int S> MDB_DEV Pk<S> operator+(Pk<S> a, float b) { return a + Pk<S>(b); }
@@ -67,7 +73,7 @@ struct StripGeom {
 };
 
 template <int C, int S>
-__global__ void __launch_bounds__(STRIP_THREADS)
+__global__ void __launch_bounds__(STRIP_THREADS, STRIP_MINB)
 photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   using P = Pk<S>;
   constexpr int NPART = 1 + NPOSE * S;
@@ -88,6 +94,7 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
 
   const int W = a.W, H = a.H;
   const size_t plane = (size_t)W * H;
+  const int planei = W * H;   // io_shape_ok guarantees C * W * H < 2^31: plane offsets are 32-bit
   const int X0 = strip * STRIP_PX;
   const int Y0 = seg * g.seg_rows, Y1 = min(Y0 + g.seg_rows, H);
   const int gx = X0 - 2 + lane;
@@ -108,6 +115,7 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   float* gout = a.gout[sc] + (size_t)n * plane;
   const bool native = a.native[sc] != 0;
   const int dw = a.dw[sc], dh = a.dh[sc];
+  const double ryd = a.ryd[sc];
 
   // ---- per-lane projection state: P' = A q + invd b, q = [px, py, 1], A = I + dA -------------
   // p_i = A_i . q is carried down the rows by adding column 1 of A (double: no drift that matters)
@@ -127,8 +135,8 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
     }
   }
   // bilinear up-sampling of the disparity (align-corners): the column part is per lane
-  int ux0 = 0, ux1 = 0;
-  double ulx = 0.0;
+  int ux0 = 0, ux1 = 0, uy0 = -1;          // uy0: native row whose column-interpolated values are cached
+  double ulx = 0.0, utop = 0.0, udif = 0.0;
   if (!native) {
     const double f = (double)min(max(gx, 0), W - 1) * a.rxd[sc];
     ux0 = min((int)f, dw - 1);
@@ -170,44 +178,59 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
     if (rowv && colv) {
       double dd_;
       if (native) {
-        dd_ = (double)ldg(dsp + (size_t)r * W + gx);
+        dd_ = (double)ldg(dsp + (r * W + gx));
       } else {
-        const double fy = (double)r * a.ryd[sc];
-        const int y0 = min((int)fy, dh - 1), y1 = min(y0 + 1, dh - 1);
-        const double ly = fy - (double)y0;
-        const double v00 = ldg(dsp + (size_t)y0 * dw + ux0), v01 = ldg(dsp + (size_t)y0 * dw + ux1);
-        const double v10 = ldg(dsp + (size_t)y1 * dw + ux0), v11 = ldg(dsp + (size_t)y1 * dw + ux1);
-        const double top = fma(ulx, v01 - v00, v00), bot = fma(ulx, v11 - v10, v10);
-        dd_ = fma(ly, bot - top, top);
+        // rows of the low-res map change every 1/ry full-res rows: keep the column-interpolated pair
+        const double fy = (double)r * ryd;
+        const int y0 = min((int)fy, dh - 1);
+        if (y0 != uy0) {   // warp-uniform
+          uy0 = y0;
+          const int y1 = min(y0 + 1, dh - 1);
+          const double v00 = ldg(dsp + (y0 * dw + ux0)), v01 = ldg(dsp + (y0 * dw + ux1));
+          const double v10 = ldg(dsp + (y1 * dw + ux0)), v11 = ldg(dsp + (y1 * dw + ux1));
+          utop = fma(ulx, v01 - v00, v00);
+          udif = fma(ulx, v11 - v10, v10) - utop;
+        }
+        dd_ = fma(fy - (double)y0, udif, utop);
       }
       dn = (float)dd_;
       const double invd = fma(dd_, a.dd_d, a.mind_d);   // 1 / depth (src/utils.jl:179-183)
+      {
+        const float* tp = tgt + (r * W + gx);
 #pragma unroll
-      for (int c = 0; c < C; ++c) yn[c] = ldg(tgt + c * plane + (size_t)r * W + gx);
+        for (int c = 0; c < C; ++c) yn[c] = ldg(tp + c * planei);
+      }
 
-      int o00[S], o01[S], o10[S], o11[S];
+      int ot[S];   // top-left tap; the other three are +1, +W, +W+1 (x0 <= W-2, y0 <= H-2 always)
       P fx, fy_, mzx, mzy, uu, vv;
 #pragma unroll
       for (int s = 0; s < S; ++s) {
         // Backproject -> Project -> normalize -> grid_sample's unnormalize (src/utils.jl:67-69,
         // 99-103; src/training.jl:56) cancel to u = P'1 / z'', z'' = P'3 + invd 1e-7 (in units of depth)
         const double P1 = fma(invd, b0[s], p1[s]), P2 = fma(invd, b1[s], p2[s]), z = fma(invd, b3e[s], p3[s]);
-        double zi = (double)rcp_approx((float)z);      // float seed + one Newton step: ~1e-14 relative
+        double zi;
+        asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(zi) : "d"(z));   // MUFU.RCP64H: ~2^-20, squared by the Newton step
         zi = fma(zi, fma(-z, zi, 1.0), zi);
         const double X = fma(P1, zi, -1.0), Y = fma(P2, zi, -1.0);   // 0-based source coordinates
-        int ix = __double2int_rd(X), iy = __double2int_rd(Y);
-        float fxs = (float)(X - (double)ix), fys = (float)(Y - (double)iy);
-        // NNlib grid_sample(padding_mode=:border), align-corners: clamp to [0, W-1]; no gradient where clamped
+        // floor by the 2^52 trick (round-down add): integer part in the low word, no F2I / I2F
+        const double MAGIC = 6755399441055744.0;
+        const double tX = __dadd_rd(X, MAGIC), tY = __dadd_rd(Y, MAGIC);
+        int ix = __double2loint(tX), iy = __double2loint(tY);
+        float fxs = (float)(X - (tX - MAGIC)), fys = (float)(Y - (tY - MAGIC));
+        if (!(fabs(X) < 1073741824.0)) { ix = (X > 0.0) ? W : -1; fxs = 0.0f; }   // far outside / NaN
+        if (!(fabs(Y) < 1073741824.0)) { iy = (Y > 0.0) ? H : -1; fys = 0.0f; }
+        // NNlib grid_sample(padding_mode=:border), align-corners: clamp to [0, W-1]; no gradient where
+        // clamped (position <= 0 or >= W-1).  The right border is the cell W-2 with weight 1.
         const bool inx = ix >= 0 && ix <= W - 2 && !(ix == 0 && fxs == 0.0f);
         const bool iny = iy >= 0 && iy <= H - 2 && !(iy == 0 && fys == 0.0f);
-        if (!inx) { ix = min(max(ix, 0), W - 1); fxs = 0.0f; }
-        if (!iny) { iy = min(max(iy, 0), H - 1); fys = 0.0f; }
-        const int ix1 = min(ix + 1, W - 1), iy1 = min(iy + 1, H - 1);
-        o00[s] = iy * W + ix; o01[s] = iy * W + ix1; o10[s] = iy1 * W + ix; o11[s] = iy1 * W + ix1;
+        if (ix < 0) { ix = 0; fxs = 0.0f; } else if (ix > W - 2) { ix = W - 2; fxs = 1.0f; }
+        if (iy < 0) { iy = 0; fys = 0.0f; } else if (iy > H - 2) { iy = H - 2; fys = 1.0f; }
+        ot[s] = iy * W + ix;
         const float zf = (float)zi;
         fx.set(s, fxs); fy_.set(s, fys);
         mzx.set(s, inx ? zf : 0.0f); mzy.set(s, iny ? zf : 0.0f);
-        uu.set(s, (float)X + 1.0f); vv.set(s, (float)Y + 1.0f);
+        // u, v only multiply dP'1, dP'2, which vanish where clamped: the clamped position is good enough
+        uu.set(s, (float)ix + (fxs + 1.0f)); vv.set(s, (float)iy + (fys + 1.0f));
       }
       float park[DRV];
 #pragma unroll
@@ -215,9 +238,10 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
         P v00, v01, v10, v11;
 #pragma unroll
         for (int s = 0; s < S; ++s) {
-          const float* p = srcp[s] + c * plane;
-          v00.set(s, ldg(p + o00[s])); v01.set(s, ldg(p + o01[s]));
-          v10.set(s, ldg(p + o10[s])); v11.set(s, ldg(p + o11[s]));
+          const float* p = srcp[s] + (ot[s] + c * planei);
+          const float* pb = p + W;
+          v00.set(s, ldg(p)); v01.set(s, ldg(p + 1));
+          v10.set(s, ldg(pb)); v11.set(s, ldg(pb + 1));
         }
         const P h0 = v01 - v00, h1 = v11 - v10;
         const P top = pfma(fx, h0, v00), bot = pfma(fx, h1, v10);
@@ -294,17 +318,15 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
         const P Cb = (r1 * q2) * (-1.0f);
         const P A0 = pfma(Mx * Bb, -2.0f, pfma(Cb, -My, Abar));   // A - 2 mu_x B - mu_y C
         const P l1 = xr1[c] + (-yr1[c]);
-        P sv, ab;
+        // clamp(raw, 0, 1) passes gradient on the closed interval only: raw in [0,1] <=> |r1 r2| <= 1
+        P sv, ab, ins;
 #pragma unroll
         for (int s = 0; s < S; ++s) {
-          const float rw = raw.get(s);
-          const bool inside = rw >= 0.0f && rw <= 1.0f;
-          sv.set(s, fminf(fmaxf(rw, 0.0f), 1.0f));
+          sv.set(s, __saturatef(raw.get(s)));
           ab.set(s, fabsf(l1.get(s)));
-          cA[c].set(s, inside ? A0.get(s) : 0.0f);
-          cB[c].set(s, inside ? Bb.get(s) : 0.0f);
-          cC[c].set(s, inside ? Cb.get(s) : 0.0f);
+          ins.set(s, fabsf(r12.get(s)) <= 1.0f ? 1.0f : 0.0f);
         }
+        cA[c] = A0 * ins; cB[c] = Bb * ins; cC[c] = Cb * ins;
         lossv = pfma(sv, ka, pfma(ab, kl, lossv));
       }
       int best = 0;
@@ -325,8 +347,7 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
         for (int s = 1; s < S; ++s) {
           fa = (best == s) ? cA[c].get(s) : fa; fb = (best == s) ? cB[c].get(s) : fb; fc = (best == s) ? cC[c].get(s) : fc;
         }
-        const bool none = best == SEL_NONE;
-        Fn[3 * c] = none ? 0.0f : fa; Fn[3 * c + 1] = none ? 0.0f : fb; Fn[3 * c + 2] = none ? 0.0f : fc;
+        Fn[3 * c] = fa; Fn[3 * c + 1] = fb; Fn[3 * c + 2] = fc;   // SEL_NONE windows are gated out by the row masks in D
       }
       if (pcol && wr >= Y0 && wr < Y1) {
         loss_acc += val;
@@ -363,7 +384,7 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
       float ex = 0.0f;
 #pragma unroll
       for (int c = 0; c < C; ++c) ex += fabsf(yr2[c] - __shfl_sync(MDB_FULL, yr2[c], min(lane + 1, 31)));
-      const float wxr = (gx + 1 < W) ? __expf(-ex * (1.0f / C)) : 0.0f;
+      const float wxr = (gx >= 0 && gx + 1 < W) ? __expf(-ex * (1.0f / C)) : 0.0f;
       const float wxl = __shfl_sync(MDB_FULL, wxr, max(lane - 1, 0));
       if (pcol) {
         const float4* dv = s_drv + (size_t)((slot + 1) % 3 * DRV4) * STRIP_THREADS + threadIdx.x;
@@ -378,9 +399,11 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
         for (int c = 0; c < C; ++c) {
           const P x = xr2[c];
           const float y = yr2[c];
+          const P df = x + (-y);
           P sg;
 #pragma unroll
-          for (int s = 0; s < S; ++s) sg.set(s, sel1 == s ? sgnf(x.get(s) - y) : 0.0f);
+          for (int s = 0; s < S; ++s) sg.set(s, sgn1(df.get(s)));
+          sg = sg * mb;
           // d loss / d sample = ks [T_A + 2 x T_B + y T_C] + kl sign(x - y) [this window chose s]
           const P G = pfma(pfma(x * 2.0f, T[3 * c + 1], pfma(T[3 * c + 2], y, T[3 * c])), ksu, sg * klu);
           P dxz, dyz;
@@ -405,10 +428,9 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
           dinvd += dP0.get(s) * b0f[s] + dP1.get(s) * b1f[s] + dP2.get(s) * b3f[s];
         float gr = dinvd * a.dd;   // d invd / d disparity = 1/min_depth - 1/max_depth
         float gsx = 0.0f, gsy = 0.0f;
-        if (gx + 1 < W) gsx += sgnf(d2 - dr) * wxr;
-        if (gx > 0) gsx -= sgnf(dl - d2) * wxl;
-        if (pr + 1 < H) gsy += sgnf(d2 - d1) * wy_dn;
-        if (pr > 0) gsy -= sgnf(d3 - d2) * wy_up;
+        // the weights are already zero across the image border
+        gsx = sgn1(d2 - dr) * wxr - sgn1(dl - d2) * wxl;
+        gsy = sgn1(d2 - d1) * wy_dn - sgn1(d3 - d2) * wy_up;
         gr += skx * gsx + sky * gsy + st.cconst;
         gout[(size_t)pr * W + gx] = gr;
       }
