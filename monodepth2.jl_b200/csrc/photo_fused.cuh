@@ -54,7 +54,6 @@ struct FusedArgs {
   float alpha, c1, c2;
   int automask;
   float up;                     // 1 / (W H N_global Ls)
-  const PosePrep* pp;           // [N][S]
   const ScaleStat* stats;       // [Ls][N]
   float* partials;              // [N][tiles][1 + NPOSE*S]
   float* vis;

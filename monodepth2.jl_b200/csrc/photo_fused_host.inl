@@ -1,41 +1,77 @@
-// photo_fused_host.inl -- finalize kernels and the C-ABI entry of the fused loss
+// photo_fused_host.inl -- finalize kernels, up-sample transpose and the C-ABI entry of the fused loss
 namespace {
 
 // ---------------------------------------------------------------------------------------
-// 6. per-item finalize: fixed-order sum of tile partials (double), pose chain to rvec/tvec
+// 4. per-item finalize: fixed-order sum of the warp records (double); pose chain to rvec/tvec;
+//    smoothness loss per scale and the mean-normalisation constant of its gradient
 // ---------------------------------------------------------------------------------------
 constexpr int FIN_THREADS = 128;
 
+struct FinArgs {
+  float* d_rvec[MDB_MAX_SOURCES];
+  float* d_tvec[MDB_MAX_SOURCES];
+  float kx[MDB_MAX_SCALES], ky[MDB_MAX_SCALES];
+  int Ls, N, W, H, normalize;
+};
+
 template <int S>
 __global__ void __launch_bounds__(FIN_THREADS)
-finalize_item_kernel(const float* __restrict__ partials, int tiles, PoseArgs pa,
-                     float* const* d_rvec_unused, float* dr0, float* dr1, float* dt0, float* dt1,
-                     double* __restrict__ item_loss) {
-  constexpr int NPART = 1 + NPOSE * S;
+finalize_item_kernel(const float* __restrict__ partials, int records, PoseArgs pa, FinArgs fa,
+                     ScaleStat* __restrict__ stats, double* __restrict__ item_loss) {
+  constexpr int NPART = STRIP_NHEAD + NPOSE * S;
+  constexpr int NRED = 1 + NPOSE * S;   // photometric sum + pose sums, reduced over all records of the item
   const int n = blockIdx.x;
-  double acc[NPART];
-#pragma unroll
-  for (int k = 0; k < NPART; ++k) acc[k] = 0.0;
-  for (int t = threadIdx.x; t < tiles; t += FIN_THREADS) {
-    const float* p = partials + ((size_t)n * tiles + t) * NPART;
-#pragma unroll
-    for (int k = 0; k < NPART; ++k) acc[k] += (double)p[k];
-  }
-  __shared__ double red[FIN_THREADS / 32][NPART];
-  __shared__ double tot[NPART];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __shared__ double red[FIN_THREADS / 32][NRED];
+  __shared__ double tot[NRED];
+  __shared__ double sred[FIN_THREADS / 32][2];
+
+  double acc[NRED];
 #pragma unroll
-  for (int k = 0; k < NPART; ++k) {
+  for (int k = 0; k < NRED; ++k) acc[k] = 0.0;
+  for (int t = threadIdx.x; t < records; t += FIN_THREADS) {
+    const float* p = partials + ((size_t)n * records + t) * NPART;
+    acc[0] += (double)p[0];
+#pragma unroll
+    for (int k = 1; k < NRED; ++k) acc[k] += (double)p[STRIP_NHEAD - 1 + k];
+  }
+#pragma unroll
+  for (int k = 0; k < NRED; ++k) {
     double v = acc[k];
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(MDB_FULL, v, o);
     if (lane == 0) red[warp][k] = v;
   }
   __syncthreads();
-  if (threadIdx.x < NPART) {
+  if (threadIdx.x < NRED) {
     double v = 0.0;
     for (int w = 0; w < FIN_THREADS / 32; ++w) v += red[w][threadIdx.x];
     tot[threadIdx.x] = v;
+  }
+  // smoothness (src/utils.jl:163-177, src/training.jl:64-67): records are ordered [..][scale]
+  const int per_scale = records / fa.Ls;
+  for (int sc = 0; sc < fa.Ls; ++sc) {
+    double sx = 0.0, sy = 0.0;
+    for (int t = threadIdx.x; t < per_scale; t += FIN_THREADS) {
+      const float* p = partials + ((size_t)n * records + (size_t)t * fa.Ls + sc) * NPART;
+      sx += (double)p[1]; sy += (double)p[2];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { sx += __shfl_xor_sync(MDB_FULL, sx, o); sy += __shfl_xor_sync(MDB_FULL, sy, o); }
+    __syncthreads();   // sred reuse (and, first time round, tot[] visible below)
+    if (lane == 0) { sred[warp][0] = sx; sred[warp][1] = sy; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double tx = 0.0, ty = 0.0;
+      for (int w = 0; w < FIN_THREADS / 32; ++w) { tx += sred[w][0]; ty += sred[w][1]; }
+      ScaleStat st = stats[(size_t)sc * fa.N + n];
+      const double inv_mp = (double)st.inv_mp;
+      const double l = ((double)fa.kx[sc] * tx + (double)fa.ky[sc] * ty) * inv_mp;
+      st.loss = (float)l;
+      // d/dd of S(d / (m + eps)): the part through the mean is the constant -S / ((m + eps) W H)
+      st.cconst = fa.normalize ? (float)(-l * inv_mp / ((double)fa.W * fa.H)) : 0.0f;
+      stats[(size_t)sc * fa.N + n] = st;
+    }
   }
   __syncthreads();
   if (threadIdx.x == 0) item_loss[n] = tot[0];
@@ -53,16 +89,71 @@ finalize_item_kernel(const float* __restrict__ partials, int tiles, PoseArgs pa,
     double r[3], t[3], dr[3], dt[3];
     for (int k = 0; k < 3; ++k) { r[k] = pa.rvec[s][3 * n + k]; t[k] = pa.tvec[s][3 * n + k]; }
     compose_T_bwd_d(r, t, pa.invert[s] != 0, dRp, dtp, dr, dt);
-    float* orv = s == 0 ? dr0 : dr1;
-    float* otv = s == 0 ? dt0 : dt1;
     for (int k = 0; k < 3; ++k) {
-      if (orv) orv[3 * n + k] = (float)dr[k];
-      if (otv) otv[3 * n + k] = (float)dt[k];
+      if (fa.d_rvec[s]) fa.d_rvec[s][3 * n + k] = (float)dr[k];
+      if (fa.d_tvec[s]) fa.d_tvec[s][3 * n + k] = (float)dt[k];
     }
   }
 }
 
-// 7. scalar loss = up * sum(item photometric sums) + sum(smoothness terms)
+// ---------------------------------------------------------------------------------------
+// 5. transpose of upsample_bilinear (align-corners) as a gather: one thread per NATIVE pixel sums
+//    the full-resolution gradients whose interpolation stencil touches it.  The weight of full-res
+//    column p for native column j is the hat function max(0, 1 - |p r - j|), r = (dw-1)/(W-1),
+//    evaluated on the exact integer numerator p (dw-1) - j (W-1).  Native scales only get the
+//    mean-normalisation constant added (grid-stride, in place).
+// ---------------------------------------------------------------------------------------
+struct UpArgs {
+  const float* gfull[MDB_MAX_SCALES];   // null for native scales
+  float* gnat[MDB_MAX_SCALES];
+  int dw[MDB_MAX_SCALES], dh[MDB_MAX_SCALES];
+  int Ls, W, H, N;
+};
+
+__global__ void __launch_bounds__(256)
+upsample_bwd_kernel(const __grid_constant__ UpArgs a, const ScaleStat* __restrict__ stats) {
+  const int sc = blockIdx.y, n = blockIdx.z;
+  const int W = a.W, H = a.H, dw = a.dw[sc], dh = a.dh[sc];
+  const float cc = stats[(size_t)sc * a.N + n].cconst;
+  float* out = a.gnat[sc] + (size_t)n * dw * dh;
+  const float* g = a.gfull[sc];
+  if (g == nullptr) {   // native: out already holds the gradient; add the constant
+    if (cc == 0.0f) return;
+    float4* o4 = reinterpret_cast<float4*>(out);
+    const int n4 = (((uintptr_t)out & 15) == 0) ? dw * dh / 4 : 0;   // item slab 16-byte aligned?
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < n4; i += gridDim.x * 256) {
+      float4 v = o4[i];
+      v.x += cc; v.y += cc; v.z += cc; v.w += cc;
+      o4[i] = v;
+    }
+    for (int i = 4 * n4 + blockIdx.x * 256 + threadIdx.x; i < dw * dh; i += gridDim.x * 256) out[i] += cc;
+    return;
+  }
+  g += (size_t)n * W * H;
+  const int dx1 = dw - 1, dy1 = dh - 1, W1 = W - 1, H1 = H - 1;
+  const float iw = 1.0f / (float)W1, ih = 1.0f / (float)H1;
+  for (int j = blockIdx.x * 256 + threadIdx.x; j < dw * dh; j += gridDim.x * 256) {
+    const int jx = j % dw, jy = j / dw;
+    // full-res p with |p dx1 - jx W1| < W1  <=>  (jx-1) W1 / dx1 < p < (jx+1) W1 / dx1
+    const int px_lo = max(0, ((jx - 1) * W1) / dx1), px_hi = min(W1, ((jx + 1) * W1 + dx1 - 1) / dx1);
+    const int py_lo = max(0, ((jy - 1) * H1) / dy1), py_hi = min(H1, ((jy + 1) * H1 + dy1 - 1) / dy1);
+    float acc = 0.0f;
+    for (int py = py_lo; py <= py_hi; ++py) {
+      const float wy = 1.0f - (float)abs(py * dy1 - jy * H1) * ih;
+      if (wy <= 0.0f) continue;
+      const float* row = g + (size_t)py * W;
+      float racc = 0.0f;
+      for (int px = px_lo; px <= px_hi; ++px) {
+        const float wx = fmaxf(1.0f - (float)abs(px * dx1 - jx * W1) * iw, 0.0f);
+        racc = fmaf(wx, ldg(row + px) + cc, racc);
+      }
+      acc = fmaf(wy, racc, acc);
+    }
+    out[j] = acc;
+  }
+}
+
+// 6. scalar loss = up * sum(item photometric sums) + sum(smoothness terms)
 __global__ void finalize_loss_kernel(const double* __restrict__ item_loss, int N, const ScaleStat* __restrict__ stats,
                                      int nstats, double up, float* __restrict__ loss) {
   __shared__ double red[32];
@@ -81,26 +172,19 @@ __global__ void finalize_loss_kernel(const double* __restrict__ item_loss, int N
 }
 
 struct FusedLayout {
-  size_t o_pp, o_ppd, o_statpart, o_stats, o_partials, o_itemloss, o_gfull[MDB_MAX_SCALES], total;
-  int tiles_x, tiles_y, rowblocks, npart;
+  size_t o_ppd, o_meanpart, o_stats, o_partials, o_itemloss, o_gfull[MDB_MAX_SCALES], total;
+  int rowblocks, npart;
   StripGeom strip;   // decomposition of the streaming kernel
-  int records;       // partial-sum records per item (tile kernel: tiles; strip kernel: warps per item)
-  bool use_strip;
+  int records;       // partial-sum records per item = warps per item
 };
 
-// MDB_FUSED_IMPL=tile selects the first-generation tiled kernel (kept for A/B measurements)
-inline bool mdb_use_strip() {
-  static const int v = [] { const char* e = getenv("MDB_FUSED_IMPL"); return (e && !strcmp(e, "tile")) ? 0 : 1; }();
-  return v != 0;
-}
-
 // Rows per segment: long segments amortise the 4 halo rows, short ones give the machine enough
-// warps.  Aim for ~16 resident sets of 12 warps per SM, never below 32 rows.
+// warps.  Aim for ~16 resident sets of 16 warps per SM, never below 32 rows.
 inline StripGeom strip_geom(const mdb_loss_io* io, int num_sms) {
   StripGeom g{};
   g.nstrips = (io->W + STRIP_PX - 1) / STRIP_PX;
   const long long base = (long long)io->N * io->Ls * g.nstrips;
-  long long want = ((long long)16 * 12 * (num_sms > 0 ? num_sms : 148) + base - 1) / base;
+  long long want = ((long long)16 * 16 * (num_sms > 0 ? num_sms : 148) + base - 1) / base;
   if (const char* e = getenv("MDB_STRIP_SEGS")) want = atoll(e);
   const int max_segs = std::max(1, io->H / 32);
   g.nsegs = (int)std::min<long long>(std::max<long long>(want, 1), max_segs);
@@ -112,19 +196,15 @@ inline StripGeom strip_geom(const mdb_loss_io* io, int num_sms) {
 
 FusedLayout fused_layout(const mdb_loss_io* io, int num_sms = 148) {
   FusedLayout L{};
-  L.use_strip = mdb_use_strip();
   L.strip = strip_geom(io, num_sms);
-  L.tiles_x = (io->W + TW - 1) / TW;
-  L.tiles_y = (io->H + TH - 1) / TH;
-  L.rowblocks = (io->H + STAT_ROWS - 1) / STAT_ROWS;
-  L.npart = 1 + NPOSE * io->S;
+  L.rowblocks = (io->H + MEAN_ROWS - 1) / MEAN_ROWS;
+  L.npart = STRIP_NHEAD + NPOSE * io->S;
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off = mdb_align_up(off + bytes, 256); return o; };
-  L.o_pp = take(sizeof(PosePrep) * io->N * io->S);
   L.o_ppd = take(sizeof(PosePrepD) * io->N * io->S);
-  L.o_statpart = take(sizeof(float) * (size_t)io->N * L.rowblocks * io->Ls * 3);
+  L.o_meanpart = take(sizeof(double) * (size_t)io->N * L.rowblocks * io->Ls);
   L.o_stats = take(sizeof(ScaleStat) * (size_t)io->Ls * io->N);
-  L.records = L.use_strip ? L.strip.nsegs * L.strip.nstrips * io->Ls : L.tiles_x * L.tiles_y;
+  L.records = L.strip.nsegs * L.strip.nstrips * io->Ls;
   L.o_partials = take(sizeof(float) * (size_t)io->N * L.records * L.npart);
   L.o_itemloss = take(sizeof(double) * io->N);
   for (int s = 0; s < io->Ls; ++s) {
@@ -138,6 +218,7 @@ FusedLayout fused_layout(const mdb_loss_io* io, int num_sms = 148) {
 bool io_shape_ok(const mdb_loss_io* io) {
   if (!io || io->W < 2 || io->H < 2 || io->N < 1 || io->L < 1) return false;
   if (io->C != 1 && io->C != 3) return false;
+  if ((long long)io->W * io->H * io->C >= (1ll << 31)) return false;   // 32-bit plane offsets in the kernels
   if (io->S < 1 || io->S > MDB_MAX_SOURCES || io->Ls < 1 || io->Ls > MDB_MAX_SCALES) return false;
   for (int s = 0; s < io->Ls; ++s)
     if (io->dw[s] < 2 || io->dh[s] < 2 || io->dw[s] > io->W || io->dh[s] > io->H) return false;
@@ -146,20 +227,9 @@ bool io_shape_ok(const mdb_loss_io* io) {
 
 template <int C, int S>
 int32_t launch_fused(mdb_handle* h, const FusedArgs& fa, const FusedLayout& L, cudaStream_t st) {
-  using SM = FusedSmem<C, S>;
-  static bool configured = false;  // per-process; the attribute is per-function, per-device context
-  (void)configured;
-  MDB_CUDA(h, cudaFuncSetAttribute(photo_fused_kernel<C, S>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   (int)SM::bytes));
-  if (L.use_strip) {
-    constexpr size_t smem = (size_t)3 * (S * (2 * C + 2) / 4) * STRIP_THREADS * sizeof(float4);
-    const int blocks = (L.strip.total + STRIP_WARPS - 1) / STRIP_WARPS;
-    photo_strip_kernel<C, S><<<blocks, STRIP_THREADS, smem, st>>>(fa, L.strip);
-    MDB_LAUNCHED(h);
-    return MDB_OK;
-  }
-  dim3 grid(L.tiles_x, L.tiles_y, fa.N);
-  photo_fused_kernel<C, S><<<grid, FUSED_THREADS, SM::bytes, st>>>(fa);
+  constexpr size_t smem = (size_t)3 * (S * (2 * C + 2) / 4) * STRIP_THREADS * sizeof(float4);
+  const int blocks = (L.strip.total + STRIP_WARPS - 1) / STRIP_WARPS;
+  photo_strip_kernel<C, S><<<blocks, STRIP_THREADS, smem, st>>>(fa, L.strip);
   MDB_LAUNCHED(h);
   return MDB_OK;
 }
@@ -208,6 +278,8 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
     for (int j = 0; j < 3; ++j) { pa.K[3 * i + j] = io->K[3 * j + i]; pa.invK[3 * i + j] = io->invK[3 * j + i]; }
 
   FusedArgs fa{};
+  FinArgs fin{};
+  UpArgs ua{};
   fa.x = io->x; fa.W = W; fa.H = H; fa.L = io->L; fa.N = N;
   fa.tgt = io->target_id - 1;
   for (int s = 0; s < S; ++s) fa.src[s] = io->source_ids[s] - 1;
@@ -223,6 +295,10 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
     const double wsm = p->smooth_weight_mode == 0 ? (double)p->disparity_smoothness * (double)io->scale[s] : 1.0;
     fa.kx[s] = (float)(wsm / ((double)Ls * (double)(W - 1) * H * Ng));
     fa.ky[s] = (float)(wsm / ((double)Ls * (double)W * (H - 1) * Ng));
+    fin.kx[s] = fa.kx[s]; fin.ky[s] = fa.ky[s];
+    ua.gfull[s] = fa.native[s] ? nullptr : fa.gout[s];
+    ua.gnat[s] = io->d_disparity[s];
+    ua.dw[s] = io->dw[s]; ua.dh[s] = io->dh[s];
   }
   fa.auto_loss = p->automasking ? io->auto_loss : nullptr;
   fa.automask = p->automasking ? 1 : 0;
@@ -234,23 +310,24 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
   fa.alpha = p->alpha; fa.c1 = p->ssim_c1; fa.c2 = p->ssim_c2;
   const double up = 1.0 / ((double)W * H * Ng * Ls);
   fa.up = (float)up;
-  fa.pp = (const PosePrep*)(ws + L.o_pp);
   fa.stats = (const ScaleStat*)(ws + L.o_stats);
   fa.partials = (float*)(ws + L.o_partials);
   fa.vis = io->vis_warp_loss;
-  fa.tiles_x = L.tiles_x; fa.tiles_y = L.tiles_y;
+  for (int s = 0; s < S; ++s) { fin.d_rvec[s] = io->d_rvec[s]; fin.d_tvec[s] = io->d_tvec[s]; }
+  fin.Ls = Ls; fin.N = N; fin.W = W; fin.H = H; fin.normalize = p->normalize_disparity;
+  ua.Ls = Ls; ua.W = W; ua.H = H; ua.N = N;
+  ScaleStat* stats = (ScaleStat*)(ws + L.o_stats);
+  double* mean_part = (double*)(ws + L.o_meanpart);
 
   const int pslot = (h->prof_ev && h->prof_next < h->prof_slots) ? h->prof_next++ : -1;
   mdb_prof_mark(h, pslot, 0, st);
-  pose_prep_kernel<<<(N * S + 127) / 128, 128, 0, st>>>(pa, (PosePrep*)(ws + L.o_pp), (PosePrepD*)(ws + L.o_ppd));
-  MDB_LAUNCHED(h);
   {
-    dim3 grid(L.rowblocks, N);
-    if (io->C == 3) disp_stats_kernel<3><<<grid, STAT_THREADS, 0, st>>>(fa, (float*)(ws + L.o_statpart));
-    else disp_stats_kernel<1><<<grid, STAT_THREADS, 0, st>>>(fa, (float*)(ws + L.o_statpart));
+    dim3 grid(L.rowblocks, Ls, N);
+    disp_mean_kernel<<<grid, MEAN_THREADS, 0, st>>>(fa, mean_part);
     MDB_LAUNCHED(h);
-    disp_stats_finalize_kernel<<<(Ls * N + 127) / 128, 128, 0, st>>>(fa, (const float*)(ws + L.o_statpart), L.rowblocks,
-                                                                     p->normalize_disparity, (ScaleStat*)(ws + L.o_stats));
+    const int threads = N * S + Ls * N;
+    prep_kernel<<<(threads + 127) / 128, 128, 0, st>>>(pa, (PosePrepD*)(ws + L.o_ppd), mean_part, L.rowblocks, Ls, W, H,
+                                                       p->normalize_disparity, stats);
     MDB_LAUNCHED(h);
   }
   mdb_prof_mark(h, pslot, 1, st);
@@ -262,24 +339,17 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
   if (rc != MDB_OK) return rc;
   mdb_prof_mark(h, pslot, 2, st);
 
-  for (int s = 0; s < Ls; ++s) {
-    if (fa.native[s]) continue;
-    dim3 blk(32, 8), grid((io->dw[s] + 31) / 32, (io->dh[s] + 7) / 8, N);
-    upsample_bwd_kernel<<<grid, blk, 0, st>>>(fa.gout[s], W, H, N, io->dw[s], io->dh[s], fa.rx[s], fa.ry[s],
-                                              io->d_disparity[s]);
+  double* item_loss = (double*)(ws + L.o_itemloss);
+  if (S == 2) finalize_item_kernel<2><<<N, FIN_THREADS, 0, st>>>(fa.partials, L.records, pa, fin, stats, item_loss);
+  else finalize_item_kernel<1><<<N, FIN_THREADS, 0, st>>>(fa.partials, L.records, pa, fin, stats, item_loss);
+  MDB_LAUNCHED(h);
+  {
+    dim3 grid(40, Ls, N);
+    upsample_bwd_kernel<<<grid, 256, 0, st>>>(ua, stats);
     MDB_LAUNCHED(h);
   }
   mdb_prof_mark(h, pslot, 3, st);
-  const int tiles = L.records;
-  double* item_loss = (double*)(ws + L.o_itemloss);
-  if (S == 2)
-    finalize_item_kernel<2><<<N, FIN_THREADS, 0, st>>>(fa.partials, tiles, pa, nullptr, io->d_rvec[0], io->d_rvec[1],
-                                                       io->d_tvec[0], io->d_tvec[1], item_loss);
-  else
-    finalize_item_kernel<1><<<N, FIN_THREADS, 0, st>>>(fa.partials, tiles, pa, nullptr, io->d_rvec[0], nullptr,
-                                                       io->d_tvec[0], nullptr, item_loss);
-  MDB_LAUNCHED(h);
-  finalize_loss_kernel<<<1, 256, 0, st>>>(item_loss, N, fa.stats, Ls * N, up, io->loss);
+  finalize_loss_kernel<<<1, 256, 0, st>>>(item_loss, N, stats, Ls * N, up, io->loss);
   MDB_LAUNCHED(h);
   mdb_prof_mark(h, pslot, 4, st);
   return MDB_OK;

@@ -27,6 +27,7 @@ constexpr int STRIP_PX = 28;
 constexpr int STRIP_WARPS = 4;
 constexpr int STRIP_THREADS = 32 * STRIP_WARPS;
 constexpr int SEL_NONE = 255;
+constexpr int STRIP_NHEAD = 3;   // record head: photometric sum, smoothness x-sum, smoothness y-sum
 #ifndef STRIP_MINB
 #define STRIP_MINB 4   // CTAs per SM the register allocation aims for (128 registers; measured best of 2/3/4)
 #endif
@@ -76,7 +77,7 @@ template <int C, int S>
 __global__ void __launch_bounds__(STRIP_THREADS, STRIP_MINB)
 photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   using P = Pk<S>;
-  constexpr int NPART = 1 + NPOSE * S;
+  constexpr int NPART = STRIP_NHEAD + NPOSE * S;
   constexpr int DRV = S * (2 * C + 2);  // floats parked per (thread, row): dx/du, dx/dv per channel, u, v
   constexpr int DRV4 = DRV / 4;
   extern __shared__ float4 s_drv[];     // [3 rows][DRV4][STRIP_THREADS]
@@ -162,7 +163,7 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
 #pragma unroll
   for (int k = 0; k < 3 * C; ++k) F1[k] = F2[k] = 0.0f;
 
-  float loss_acc = 0.0f;
+  float loss_acc = 0.0f, smx_acc = 0.0f, smy_acc = 0.0f;
   P S0[3], SP[3], SI[3];  // sum dP_i, sum dP_i py, sum dP_i invd  (times px at the end for column 0)
 #pragma unroll
   for (int i = 0; i < 3; ++i) { S0[i] = P(0.0f); SP[i] = P(0.0f); SI[i] = P(0.0f); }
@@ -431,7 +432,9 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
         // the weights are already zero across the image border
         gsx = sgn1(d2 - dr) * wxr - sgn1(dl - d2) * wxl;
         gsy = sgn1(d2 - d1) * wy_dn - sgn1(d3 - d2) * wy_up;
-        gr += skx * gsx + sky * gsy + st.cconst;
+        gr += skx * gsx + sky * gsy;   // the mean-normalisation constant is added after the item's sum is known
+        smx_acc = fmaf(fabsf(d2 - dr), wxr, smx_acc);
+        smy_acc = fmaf(fabsf(d2 - d1), wy_dn, smy_acc);
         gout[(size_t)pr * W + gx] = gr;
       }
     }
@@ -449,8 +452,8 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   // ---- one record per warp: loss + 12 pose sums per source (no atomics) -------------------------
   float* out = a.partials + (size_t)rec * NPART;
   {
-    const float v = warp_sum(loss_acc);
-    if (lane == 0) out[0] = v;
+    const float v = warp_sum(loss_acc), vx = warp_sum(smx_acc), vy = warp_sum(smy_acc);
+    if (lane == 0) { out[0] = v; out[1] = vx; out[2] = vy; }
   }
   const float px = (float)(gx + 1);
 #pragma unroll
@@ -460,8 +463,8 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
       const float s0 = S0[i].get(s);
       const float v0 = warp_sum(s0 * px), v1 = warp_sum(SP[i].get(s)), v2 = warp_sum(s0), v3 = warp_sum(SI[i].get(s));
       if (lane == 0) {
-        out[1 + s * NPOSE + 3 * i] = v0; out[1 + s * NPOSE + 3 * i + 1] = v1; out[1 + s * NPOSE + 3 * i + 2] = v2;
-        out[1 + s * NPOSE + 9 + i] = v3;
+        out[STRIP_NHEAD + s * NPOSE + 3 * i] = v0; out[STRIP_NHEAD + s * NPOSE + 3 * i + 1] = v1; out[STRIP_NHEAD + s * NPOSE + 3 * i + 2] = v2;
+        out[STRIP_NHEAD + s * NPOSE + 9 + i] = v3;
       }
     }
 }
