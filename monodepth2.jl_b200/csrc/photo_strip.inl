@@ -108,10 +108,19 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   // multiplicity of this pixel inside its left / right neighbour windows (reflected twice at the border)
   const float wl = (gx == 1) ? 2.0f : 1.0f, wr_ = (gx == W - 2) ? 2.0f : 1.0f;
 
-  const float* tgt = a.x + ((size_t)n * a.L + a.tgt) * C * plane;
-  const float* srcp[S];
+  // one 64-bit base per item; everything inside the item is addressed with 32-bit element offsets
+  // (io_shape_ok guarantees L * C * W * H < 2^31)
+  const float* xb;
+  {
+    // opaque to the optimiser: otherwise it re-derives this base from n in 64-bit arithmetic at every load
+    unsigned long long xbi = (unsigned long long)(a.x + (size_t)n * a.L * C * plane);
+    asm volatile("" : "+l"(xbi));
+    xb = reinterpret_cast<const float*>(xbi);
+  }
+  const unsigned tgt_off = a.tgt * C * planei;
+  unsigned src_off[S];
 #pragma unroll
-  for (int s = 0; s < S; ++s) srcp[s] = a.x + ((size_t)n * a.L + a.src[s]) * C * plane;
+  for (int s = 0; s < S; ++s) src_off[s] = a.src[s] * C * planei;
   const float* dsp = a.disp[sc] + (size_t)n * a.dw[sc] * a.dh[sc];
   float* gout = a.gout[sc] + (size_t)n * plane;
   const bool native = a.native[sc] != 0;
@@ -197,12 +206,11 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
       dn = (float)dd_;
       const double invd = fma(dd_, a.dd_d, a.mind_d);   // 1 / depth (src/utils.jl:179-183)
       {
-        const float* tp = tgt + (r * W + gx);
 #pragma unroll
-        for (int c = 0; c < C; ++c) yn[c] = ldg(tp + c * planei);
+        for (int c = 0; c < C; ++c) yn[c] = ldg(xb + (unsigned)(tgt_off + c * planei + r * W + gx));
       }
 
-      int ot[S];   // top-left tap; the other three are +1, +W, +W+1 (x0 <= W-2, y0 <= H-2 always)
+      unsigned ot[S];   // top-left tap; the other three are +1, +W, +W+1 (x0 <= W-2, y0 <= H-2 always)
       P fx, fy_, mzx, mzy, uu, vv;
 #pragma unroll
       for (int s = 0; s < S; ++s) {
@@ -218,15 +226,18 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
         const double tX = __dadd_rd(X, MAGIC), tY = __dadd_rd(Y, MAGIC);
         int ix = __double2loint(tX), iy = __double2loint(tY);
         float fxs = (float)(X - (tX - MAGIC)), fys = (float)(Y - (tY - MAGIC));
-        if (!(fabs(X) < 1073741824.0)) { ix = (X > 0.0) ? W : -1; fxs = 0.0f; }   // far outside / NaN
-        if (!(fabs(Y) < 1073741824.0)) { iy = (Y > 0.0) ? H : -1; fys = 0.0f; }
+        // |X| < 2^31 leaves the high word of X + 2^52 + 2^51 at 0x43380000 (X >= 0) or 0x4337ffff (X < 0);
+        // anything else is far outside the image (or NaN): send it to the border on its side
+        const int hX = __double2hiint(tX), hY = __double2hiint(tY);
+        if ((unsigned)(hX - 0x4337ffff) > 1u) { ix = (hX >= 0x43380000) ? W : -1; fxs = 0.0f; }
+        if ((unsigned)(hY - 0x4337ffff) > 1u) { iy = (hY >= 0x43380000) ? H : -1; fys = 0.0f; }
         // NNlib grid_sample(padding_mode=:border), align-corners: clamp to [0, W-1]; no gradient where
         // clamped (position <= 0 or >= W-1).  The right border is the cell W-2 with weight 1.
         const bool inx = ix >= 0 && ix <= W - 2 && !(ix == 0 && fxs == 0.0f);
         const bool iny = iy >= 0 && iy <= H - 2 && !(iy == 0 && fys == 0.0f);
         if (ix < 0) { ix = 0; fxs = 0.0f; } else if (ix > W - 2) { ix = W - 2; fxs = 1.0f; }
         if (iy < 0) { iy = 0; fys = 0.0f; } else if (iy > H - 2) { iy = H - 2; fys = 1.0f; }
-        ot[s] = iy * W + ix;
+        ot[s] = (unsigned)(iy * W + ix) + src_off[s];
         const float zf = (float)zi;
         fx.set(s, fxs); fy_.set(s, fys);
         mzx.set(s, inx ? zf : 0.0f); mzy.set(s, iny ? zf : 0.0f);
@@ -239,8 +250,8 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
         P v00, v01, v10, v11;
 #pragma unroll
         for (int s = 0; s < S; ++s) {
-          const float* p = srcp[s] + (ot[s] + c * planei);
-          const float* pb = p + W;
+          const float* p = xb + (ot[s] + (unsigned)(c * planei));
+          const float* pb = xb + (ot[s] + (unsigned)(c * planei + W));
           v00.set(s, ldg(p)); v01.set(s, ldg(p + 1));
           v10.set(s, ldg(pb)); v11.set(s, ldg(pb + 1));
         }
@@ -271,6 +282,8 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
     for (int k = 0; k < 3 * C; ++k) Fn[k] = 0.0f;
     if (r >= Y0 && wr >= 0 && wr < H) {             // warp-uniform
       const bool rt = wr == 0, rb = wr == H - 1;    // reflected rows
+      P Mxa[C], Qxa[C], Cxya[C];
+      float Mya[C], Qya[C];
       P vm[C], vq[C], vc[C];
       float vmy[C], vqy[C];
 #pragma unroll
@@ -285,8 +298,6 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
         vq[c] = pfma(g1, g1, pfma(g2, g2, sg * sg3));
         vc[c] = pfma(g1, e1, pfma(g2, e2, sg3 * se));
       }
-      P lossv(0.0f);
-      P cA[C], cB[C], cC[C];
 #pragma unroll
       for (int c = 0; c < C; ++c) {
         // combine the column triples l-1, l, l+1 (Chan): M2 = sum q_j + 3 sum (m_j - M)^2
@@ -296,12 +307,19 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
         const P qL = vq[c].shfl(nl), qR = vq[c].shfl(nr);
         const P cL = vc[c].shfl(nl), cR = vc[c].shfl(nr);
         const float e1 = myL - vmy[c], e2 = myR - vmy[c], se = e1 + e2, se3 = se * (-1.0f / 3.0f);
-        const float My = fmaf(se, 1.0f / 3.0f, vmy[c]);
-        const float Qy = fmaf(3.0f, fmaf(e1, e1, fmaf(e2, e2, se * se3)), qyL + vqy[c] + qyR);   // 9 var(y)
+        Mya[c] = fmaf(se, 1.0f / 3.0f, vmy[c]);
+        Qya[c] = fmaf(3.0f, fmaf(e1, e1, fmaf(e2, e2, se * se3)), qyL + vqy[c] + qyR);   // 9 var(y)
         const P g1 = mL - vm[c], g2 = mR - vm[c], sg = g1 + g2, sg3 = sg * (-1.0f / 3.0f);
-        const P Mx = pfma(sg, 1.0f / 3.0f, vm[c]);
-        const P Qx = pfma(pfma(g1, g1, pfma(g2, g2, sg * sg3)), 3.0f, qL + vq[c] + qR);          // 9 var(x)
-        const P Cxy = pfma(pfma(g1, e1, pfma(g2, e2, sg3 * se)), 3.0f, cL + vc[c] + cR);         // 9 cov(x,y)
+        Mxa[c] = pfma(sg, 1.0f / 3.0f, vm[c]);
+        Qxa[c] = pfma(pfma(g1, g1, pfma(g2, g2, sg * sg3)), 3.0f, qL + vq[c] + qR);          // 9 var(x)
+        Cxya[c] = pfma(pfma(g1, e1, pfma(g2, e2, sg3 * se)), 3.0f, cL + vc[c] + cR);         // 9 cov(x,y)
+      }
+      P lossv(0.0f);
+      P cA[C], cB[C], cC[C];
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+        const P Mx = Mxa[c], Qx = Qxa[c], Cxy = Cxya[c];
+        const float My = Mya[c], Qy = Qya[c];
         // SSIM (src/utils.jl:29-43) and its pullback wrt mu_x (A), sigma_x (B), sigma_xy (Cc)
         const P n1 = pfma(Mx, 2.0f * My, P(a.c1));
         const P n2 = pfma(Cxy, 2.0f / 9.0f, P(a.c2));
