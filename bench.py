@@ -41,7 +41,8 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--config", default="config5", choices=["config2", "config3", "config5"])
+    ap.add_argument("--config", default="config5", choices=["config2", "config3", "config5", "config4"])
+    ap.add_argument("--render-batch", type=int, default=2, help="config4: render batch B (reference scripts use 2 and 4)")
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch override (default: the config's)")
     ap.add_argument("--cpu-sample-items", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -307,9 +308,67 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def run_render(args):
+    """BASELINE config 4: render_tgt_rgb_depth forward + backward (src/render.jl:92-114), 32 planes at
+    416x128.  Not the headline line (bench.py's default stays config 5); prints its own JSON line with
+    the HBM roofline of the two render kernels.  The working set (110 MB at B=2) fits L2, so a buffer
+    larger than L2 is written between the timed calls."""
+    import ctypes as ct
+    import torch
+    import mdb200
+    from mdb200 import synth, api
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    ri = synth.make_render_inputs(B=args.render_batch)
+    W, H, Np, B = ri.W, ri.H, ri.Np, ri.B
+    t = lambda a: torch.tensor(a, device=dev)
+    rgb, sigma, disp, xyz, rvec, tvec = t(ri.rgb), t(ri.sigma), t(ri.disparity_src), t(ri.xyz_tgt), t(ri.rvec), t(ri.tvec)
+    g_rgb = torch.rand((B, 3, H, W), device=dev)
+    g_dep = torch.rand((B, Np, 1, H, W), device=dev) * 0.1
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    f_ms, b_ms = [], []
+    l0 = None
+    for it in range(args.warmup + args.steps):
+        if it == args.warmup:
+            l0 = mdb200.launch_count()
+        rgb_r, sig_r, xyz_r = rgb.clone().requires_grad_(True), sigma.clone().requires_grad_(True), xyz.clone().requires_grad_(True)
+        flush.zero_()
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        e[0].record()
+        out, depth, mask = mdb200.render_tgt_rgb_depth(rgb_r, sig_r, disp, xyz_r, mdb200.Pose(rvec, tvec), ri.K_inv, ri.K)
+        e[1].record()
+        flush.zero_()
+        e[2].record()
+        torch.autograd.backward([out, depth], [g_rgb, g_dep])
+        e[3].record()
+        torch.cuda.synchronize()
+        if it >= args.warmup:
+            f_ms.append(e[0].elapsed_time(e[1])); b_ms.append(e[2].elapsed_time(e[3]))
+    launches = mdb200.launch_count() - l0
+    fm, bm = sum(f_ms) / len(f_ms), sum(b_ms) / len(b_ms)
+    units = W * H * Np * B
+    inp = 7 * units * 4
+    outb = (3 * W * H * B + units) * 4
+    peak, peak_src = load_peaks()
+    fwd_b, bwd_b = inp + outb, 2 * inp + outb
+    line = {"metric": "plane-px/s (render_tgt_rgb_depth fwd+bwd)", "value": units / ((fm + bm) * 1e-3), "unit": "plane_px/s",
+            "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": fm + bm, "higher_is_better": True,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"config4: {W}x{H}, {Np} planes, B={B}, render_tgt_rgb_depth fwd+bwd", "l2": "flushed between calls",
+                       "timing": "CUDA events around the public call (torch allocation of the outputs included)"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": "render_fwd_kernel + render_bwd_kernel", "unit": "GB/s", "peak": peak, "peak_source": peak_src,
+                         "fwd": {"ms": fm, "algorithmic_bytes": fwd_b, "achieved": fwd_b / (fm * 1e-3) / 1e9, "frac": fwd_b / (fm * 1e-3) / 1e9 / peak},
+                         "bwd": {"ms": bm, "algorithmic_bytes": bwd_b, "achieved": bwd_b / (bm * 1e-3) / 1e9, "frac": bwd_b / (bm * 1e-3) / 1e9 / peak},
+                         "achieved": (fwd_b + bwd_b) / ((fm + bm) * 1e-3) / 1e9, "frac": (fwd_b + bwd_b) / ((fm + bm) * 1e-3) / 1e9 / peak}}
+    print(json.dumps(line), flush=True)
+
+
 if __name__ == "__main__":
     a = parse()
-    if a.impl == "reference":
+    if a.config == "config4" and a.impl != "reference":
+        run_render(a)
+    elif a.impl == "reference":
         run_reference(a)
     else:
         run_ours(a)

@@ -13,7 +13,8 @@ struct RenderBwdArgs {
   int W, H, Np, B;
   float Kinv_f[9];
   const float* tvec;        // [B][3]
-  float* d_rgb; float* d_sigma; float* d_xyz;   // zero-initialised, accumulated with red.global.add
+  float4* acc;              // [B Np][H W][2] zero-initialised: {d rgb, d sigma}, {d xyz, 0}; accumulated with
+                            // 128-bit red.global.add.v4.f32 (one L2 reduction per tap and channel GROUP)
   float* part_pose;         // [B][blocks][12]
   float* part_disp;         // [B][blocks][Np]
 };
@@ -31,12 +32,42 @@ struct Pend {
   int k;
 };
 
-MDB_DEV void scatter4(float* __restrict__ base, int stride, const Pend& t, float g) {
-  const float w11 = t.fx * t.fy, w01 = t.fx - w11, w10 = t.fy - w11, w00 = 1.0f - t.fx - t.fy + w11;
-  atomicAdd(base + stride * t.o00, g * w00);
-  atomicAdd(base + stride * t.o01, g * w01);
-  atomicAdd(base + stride * t.o10, g * w10);
-  atomicAdd(base + stride * t.o11, g * w11);
+// vector reduction into L2 (sm_90+): 4 floats per operation instead of 4 operations
+MDB_DEV void red_v4(float4* p, float x, float y, float z, float w) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
+}
+
+// Transpose of the bilinear gather for one channel group: `slot` 0 = {rgb, sigma}, 1 = {xyz, -}.
+// Called by all 32 lanes (`on` = this lane has something to add).  With the reference's grid
+// normalisation (no "-1") three quarters of the samples land beyond the right / bottom
+// border and pile onto border cells; when every contributing lane of the warp hits the SAME cell
+// (right column, corner) the warp sums its contribution first and lane 0 issues the reductions,
+// which takes a 32-way contention out of L2.
+MDB_DEV void scatter4(float4* __restrict__ plane, int slot, const Pend& t, bool on, float g0, float g1, float g2,
+                      float g3, int lane) {
+  const unsigned M = __ballot_sync(MDB_FULL, on);
+  if (M == 0u) return;
+  const float w11 = t.fx * t.fy;
+  float w[4] = {1.0f - t.fx - t.fy + w11, t.fx - w11, t.fy - w11, w11};
+  const int o[4] = {t.o00, t.o01, t.o10, t.o11};
+  const int lead = __ffs(M) - 1;
+  const int o_lead = __shfl_sync(MDB_FULL, t.o00, lead);
+  const bool same = __all_sync(MDB_FULL, !on || t.o00 == o_lead);
+  if (same && __popc(M) > 4) {   // warp-uniform
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float wj = on ? w[j] : 0.0f;
+      if (!__any_sync(MDB_FULL, wj != 0.0f)) continue;
+      const float s0 = warp_sum(g0 * wj), s1 = warp_sum(g1 * wj), s2 = warp_sum(g2 * wj), s3 = warp_sum(g3 * wj);
+      const int oj = __shfl_sync(MDB_FULL, o[j], lead);
+      if (lane == lead) red_v4(plane + 2 * oj + slot, s0, s1, s2, s3);
+    }
+    return;
+  }
+  if (!on) return;
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+    if (w[j] != 0.0f) red_v4(plane + 2 * o[j] + slot, g0 * w[j], g1 * w[j], g2 * w[j], g3 * w[j]);
 }
 
 __global__ void __launch_bounds__(RB_THREADS) render_bwd_kernel(const __grid_constant__ RenderBwdArgs a) {
@@ -73,11 +104,9 @@ __global__ void __launch_bounds__(RB_THREADS) render_bwd_kernel(const __grid_con
     float ddisp = 0.0f;
     if (active) {
       const int kb = b * a.Np + p.k;
-      float* dx = a.d_xyz + (size_t)kb * WH * 3;
       float dix = p.dix, diy = p.diy;
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
-        if (gx[c] != 0.0f) scatter4(dx + c, 3, p, gx[c]);
         dix = fmaf(gx[c], p.dxv[c], dix);
         diy = fmaf(gx[c], p.dyv[c], diy);
       }
@@ -99,6 +128,8 @@ __global__ void __launch_bounds__(RB_THREADS) render_bwd_kernel(const __grid_con
       acc[9] -= a0 * Y2 * dsp; acc[10] -= a1 * Y2 * dsp; acc[11] -= a2 * Y2 * dsp;
       ddisp = -(a0 * t0 + a1 * t1 + a2 * t2) * Y2;
     }
+    scatter4(a.acc + (size_t)(b * a.Np + p.k) * WH * 2, 1, p, active && (gx[0] != 0.0f || gx[1] != 0.0f || gx[2] != 0.0f),
+             gx[0], gx[1], gx[2], 0.0f, lane);
     ddisp = warp_sum(ddisp);
     if (lane == 0) s_disp[warp][p.k] += ddisp;
   };
@@ -164,16 +195,15 @@ __global__ void __launch_bounds__(RB_THREADS) render_bwd_kernel(const __grid_con
     }
     // rgb and sigma of plane k are complete now
     float dix = 0.0f, diy = 0.0f;
+    {
+      const float g0 = gO[0] * w, g1 = gO[1] * w, g2 = gO[2] * w;
+      scatter4(a.acc + (size_t)kb * WH * 2, 0, cur, active && (g0 != 0.0f || g1 != 0.0f || g2 != 0.0f || gsig != 0.0f),
+               g0, g1, g2, gsig, lane);
+    }
     if (active) {
-      float* dr = a.d_rgb + (size_t)kb * 3 * WH;
-#pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        const float g = gO[c] * w;
-        if (g != 0.0f) scatter4(dr + c * WH, 1, cur, g);
-        dix = fmaf(g, dxr[c], dix);
-        diy = fmaf(g, dyr[c], diy);
-      }
-      if (gsig != 0.0f) scatter4(a.d_sigma + (size_t)kb * WH, 1, cur, gsig);
+      const float g0 = gO[0] * w, g1 = gO[1] * w, g2 = gO[2] * w;
+      dix = fmaf(g0, dxr[0], fmaf(g1, dxr[1], fmaf(g2, dxr[2], dix)));
+      diy = fmaf(g0, dyr[0], fmaf(g1, dyr[1], fmaf(g2, dyr[2], diy)));
       dix = fmaf(gsig, dxs, dix);
       diy = fmaf(gsig, dys, diy);
     }
@@ -205,22 +235,42 @@ __global__ void __launch_bounds__(RB_THREADS) render_bwd_kernel(const __grid_con
   }
 }
 
-// fixed-order sums of the block partials, then so3 pullback for rvec
-__global__ void render_bwd_finalize_kernel(const float* __restrict__ part_pose, const float* __restrict__ part_disp,
-                                           int blocks, int Np, int B, const float* __restrict__ rvec,
-                                           float* __restrict__ d_rvec, float* __restrict__ d_tvec,
-                                           float* __restrict__ d_disp) {
-  const int b = blockIdx.x;
-  __shared__ double tot[12];
-  if (threadIdx.x < 12) {
-    double s = 0.0;
-    for (int i = 0; i < blocks; ++i) s += (double)part_pose[((size_t)b * blocks + i) * 12 + threadIdx.x];
-    tot[threadIdx.x] = s;
+// the accumulation buffer back into the caller's layouts: d_rgb [B Np][3][H W], d_sigma [B Np][H W],
+// d_xyz [B Np][H W][3]
+__global__ void __launch_bounds__(256) render_bwd_unpack_kernel(const float4* __restrict__ acc, int WH, size_t total,
+                                                                float* __restrict__ d_rgb, float* __restrict__ d_sigma,
+                                                                float* __restrict__ d_xyz) {
+  for (size_t i = blockIdx.x * (size_t)256 + threadIdx.x; i < total; i += (size_t)gridDim.x * 256) {
+    const float4 q0 = __ldcs(acc + 2 * i), q1 = __ldcs(acc + 2 * i + 1);
+    const size_t kb = i / WH, pix = i - kb * WH;
+    float* r = d_rgb + kb * 3 * WH + pix;
+    r[0] = q0.x; r[WH] = q0.y; r[2 * (size_t)WH] = q0.z;
+    d_sigma[i] = q0.w;
+    float* x = d_xyz + 3 * i;
+    x[0] = q1.x; x[1] = q1.y; x[2] = q1.z;
   }
-  for (int k = threadIdx.x; k < Np; k += blockDim.x) {
+}
+
+// fixed-order sums of the block partials (one warp per quantity, lanes stride the blocks, then a
+// butterfly: the order is fixed, so results are reproducible), then the so3 pullback for rvec
+__global__ void __launch_bounds__(256)
+render_bwd_finalize_kernel(const float* __restrict__ part_pose, const float* __restrict__ part_disp,
+                           int blocks, int Np, int B, const float* __restrict__ rvec,
+                           float* __restrict__ d_rvec, float* __restrict__ d_tvec,
+                           float* __restrict__ d_disp) {
+  const int b = blockIdx.x;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  __shared__ double tot[12];
+  for (int q = warp; q < 12 + Np; q += nwarps) {
     double s = 0.0;
-    for (int i = 0; i < blocks; ++i) s += (double)part_disp[((size_t)b * blocks + i) * Np + k];
-    if (d_disp) d_disp[b * Np + k] = (float)s;
+    if (q < 12) for (int i = lane; i < blocks; i += 32) s += (double)part_pose[((size_t)b * blocks + i) * 12 + q];
+    else for (int i = lane; i < blocks; i += 32) s += (double)part_disp[((size_t)b * blocks + i) * Np + (q - 12)];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(MDB_FULL, s, o);
+    if (lane == 0) {
+      if (q < 12) tot[q] = s;
+      else if (d_disp) d_disp[b * Np + (q - 12)] = (float)s;
+    }
   }
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -287,7 +337,7 @@ RenderConst make_rc(const float* K, const float* Kinv) {
   return rc;
 }
 
-struct RenderLayout { size_t o_prep, o_pose, o_disp, total; int blocks; };
+struct RenderLayout { size_t o_prep, o_pose, o_disp, o_acc, total; int blocks; };
 RenderLayout render_layout(int W, int H, int Np, int B) {
   RenderLayout L;
   L.blocks = (W * H + RB_THREADS - 1) / RB_THREADS;
@@ -296,6 +346,7 @@ RenderLayout render_layout(int W, int H, int Np, int B) {
   L.o_prep = take(sizeof(PlanePrep) * Np * B);
   L.o_pose = take(sizeof(float) * 12 * (size_t)B * L.blocks);
   L.o_disp = take(sizeof(float) * (size_t)Np * B * L.blocks);
+  L.o_acc = take(sizeof(float4) * 2 * (size_t)W * H * Np * B);   // backward accumulation buffer
   L.total = off;
   return L;
 }
@@ -417,19 +468,21 @@ int32_t mdb_render_tgt_rgb_depth_bwd(mdb_handle* h, const float* rgb, const floa
   render_prep_kernel<<<(Np * B + 63) / 64, 64, 0, st>>>(disparity_src, 0, rvec, tvec, rc, Np, B, prep);
   MDB_LAUNCHED(h);
   const size_t planes = (size_t)W * H * Np * B;
-  MDB_CUDA(h, cudaMemsetAsync(d_rgb, 0, planes * 3 * sizeof(float), st));
-  MDB_CUDA(h, cudaMemsetAsync(d_sigma, 0, planes * sizeof(float), st));
-  MDB_CUDA(h, cudaMemsetAsync(d_xyz_tgt, 0, planes * 3 * sizeof(float), st));
+  float4* acc = (float4*)(ws + L.o_acc);
+  MDB_CUDA(h, cudaMemsetAsync(acc, 0, planes * 2 * sizeof(float4), st));
   RenderBwdArgs a{};
   a.rgb = rgb; a.sigma = sigma; a.xyz = xyz_tgt; a.prep = prep; a.tacc = depth_saved; a.g_rgb_out = g_rgb_out;
   a.g_tacc = g_depth; a.W = W; a.H = H; a.Np = Np; a.B = B; a.tvec = tvec;
   for (int i = 0; i < 9; ++i) a.Kinv_f[i] = rc.Kinv_f[i];
-  a.d_rgb = d_rgb; a.d_sigma = d_sigma; a.d_xyz = d_xyz_tgt;
+  a.acc = acc;
   a.part_pose = (float*)(ws + L.o_pose); a.part_disp = (float*)(ws + L.o_disp);
   dim3 grid(L.blocks, B);
   render_bwd_kernel<<<grid, RB_THREADS, 0, st>>>(a);
   MDB_LAUNCHED(h);
-  render_bwd_finalize_kernel<<<B, 64, 0, st>>>(a.part_pose, a.part_disp, L.blocks, Np, B, rvec, d_rvec, d_tvec, d_disparity_src);
+  render_bwd_unpack_kernel<<<(unsigned)std::min<size_t>((planes + 255) / 256, (size_t)h->num_sms * 32), 256, 0, st>>>(
+      acc, W * H, planes, d_rgb, d_sigma, d_xyz_tgt);
+  MDB_LAUNCHED(h);
+  render_bwd_finalize_kernel<<<B, 256, 0, st>>>(a.part_pose, a.part_disp, L.blocks, Np, B, rvec, d_rvec, d_tvec, d_disparity_src);
   MDB_LAUNCHED(h);
   return MDB_OK;
 }
