@@ -28,6 +28,9 @@ constexpr int STRIP_WARPS = 4;
 constexpr int STRIP_THREADS = 32 * STRIP_WARPS;
 constexpr int SEL_NONE = 255;
 constexpr int STRIP_NHEAD = 3;   // record head: photometric sum, smoothness x-sum, smoothness y-sum
+#ifndef STRIP_PIPE
+#define STRIP_PIPE 0   // 1: issue the loads of row r+1 before stages C and D of row r (software pipelining)
+#endif
 #ifndef STRIP_MINB
 #define STRIP_MINB 4   // CTAs per SM the register allocation aims for (128 registers; measured best of 2/3/4)
 #endif
@@ -178,20 +181,28 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   for (int i = 0; i < 3; ++i) { S0[i] = P(0.0f); SP[i] = P(0.0f); SI[i] = P(0.0f); }
 
   int slot = 0;  // ring slot of row r in s_drv
-  for (int r = Y0 - 2; r <= Y1 + 1; ++r) {
-    const bool rowv = r >= 0 && r < H;
-    // =========================== A: sample row r ===============================================
-    P xn[C];
-    float yn[C], dn = 0.0f;
-#pragma unroll
-    for (int c = 0; c < C; ++c) { xn[c] = P(0.0f); yn[c] = 0.0f; }
-    if (rowv && colv) {
+
+  // ---- stage A in two halves, so that (STRIP_PIPE) the loads of row r+1 fly during C and D of row r ----
+  // in flight between issue() and consume(): 4 taps x C channels (sources packed), the target row,
+  // the bilinear weights and masks
+  P tv00[C], tv01[C], tv10[C], tv11[C];
+  float ty_[C], td_ = 0.0f;
+  P tfx, tfy, tmzx, tmzy, tuu, tvv;
+  bool tvalid = false;
+  float dq = 0.0f;   // native disparity of the NEXT row to be issued, loaded one call ahead
+  const int gxc = min(max(gx, 0), W - 1);   // loads of dead lanes / rows go to a clamped (valid) address
+  if (native) dq = ldg(dsp + (min(max(Y0 - 2, 0), H - 1) * W + gxc));
+
+  auto issue = [&](int r) {
+    tvalid = r >= 0 && r < H && colv;
+    const int rc = min(max(r, 0), H - 1);
+    {   // unconditional (clamped addresses): nothing in flight is carried from one row to the next
       double dd_;
       if (native) {
-        dd_ = (double)ldg(dsp + (r * W + gx));
+        dd_ = (double)dq;
       } else {
         // rows of the low-res map change every 1/ry full-res rows: keep the column-interpolated pair
-        const double fy = (double)r * ryd;
+        const double fy = (double)rc * ryd;
         const int y0 = min((int)fy, dh - 1);
         if (y0 != uy0) {   // warp-uniform
           uy0 = y0;
@@ -203,15 +214,12 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
         }
         dd_ = fma(fy - (double)y0, udif, utop);
       }
-      dn = (float)dd_;
+      td_ = (float)dd_;
       const double invd = fma(dd_, a.dd_d, a.mind_d);   // 1 / depth (src/utils.jl:179-183)
-      {
 #pragma unroll
-        for (int c = 0; c < C; ++c) yn[c] = ldg(xb + (unsigned)(tgt_off + c * planei + r * W + gx));
-      }
+      for (int c = 0; c < C; ++c) ty_[c] = ldg(xb + (unsigned)(tgt_off + c * planei + rc * W + gxc));
 
       unsigned ot[S];   // top-left tap; the other three are +1, +W, +W+1 (x0 <= W-2, y0 <= H-2 always)
-      P fx, fy_, mzx, mzy, uu, vv;
 #pragma unroll
       for (int s = 0; s < S; ++s) {
         // Backproject -> Project -> normalize -> grid_sample's unnormalize (src/utils.jl:67-69,
@@ -239,40 +247,70 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
         if (iy < 0) { iy = 0; fys = 0.0f; } else if (iy > H - 2) { iy = H - 2; fys = 1.0f; }
         ot[s] = (unsigned)(iy * W + ix) + src_off[s];
         const float zf = (float)zi;
-        fx.set(s, fxs); fy_.set(s, fys);
-        mzx.set(s, inx ? zf : 0.0f); mzy.set(s, iny ? zf : 0.0f);
+        tfx.set(s, fxs); tfy.set(s, fys);
+        tmzx.set(s, inx ? zf : 0.0f); tmzy.set(s, iny ? zf : 0.0f);
         // u, v only multiply dP'1, dP'2, which vanish where clamped: the clamped position is good enough
-        uu.set(s, (float)ix + (fxs + 1.0f)); vv.set(s, (float)iy + (fys + 1.0f));
+        tuu.set(s, (float)ix + (fxs + 1.0f)); tvv.set(s, (float)iy + (fys + 1.0f));
       }
-      float park[DRV];
 #pragma unroll
       for (int c = 0; c < C; ++c) {
-        P v00, v01, v10, v11;
 #pragma unroll
         for (int s = 0; s < S; ++s) {
           const float* p = xb + (ot[s] + (unsigned)(c * planei));
           const float* pb = xb + (ot[s] + (unsigned)(c * planei + W));
-          v00.set(s, ldg(p)); v01.set(s, ldg(p + 1));
-          v10.set(s, ldg(pb)); v11.set(s, ldg(pb + 1));
+          tv00[c].set(s, ldg(p)); tv01[c].set(s, ldg(p + 1));
+          tv10[c].set(s, ldg(pb)); tv11[c].set(s, ldg(pb + 1));
         }
-        const P h0 = v01 - v00, h1 = v11 - v10;
-        const P top = pfma(fx, h0, v00), bot = pfma(fx, h1, v10);
+      }
+    }
+    if (native) dq = ldg(dsp + (min(max(r + 1, 0), H - 1) * W + gxc));
+#pragma unroll
+    for (int s = 0; s < S; ++s) { p1[s] += i1[s]; p2[s] += i2[s]; p3[s] += i3[s]; }
+  };
+
+  // bilinear value and its derivatives of the issued row -> xn, yn, dn; park the derivatives in `wslot`
+  auto consume = [&](int wslot, P (&xn)[C], float (&yn)[C], float& dn) {
+    {
+      dn = tvalid ? td_ : 0.0f;
+      float park[DRV];
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+        yn[c] = tvalid ? ty_[c] : 0.0f;
+        const P h0 = tv01[c] - tv00[c], h1 = tv11[c] - tv10[c];
+        const P top = pfma(tfx, h0, tv00[c]), bot = pfma(tfx, h1, tv10[c]);
         const P dyv = bot - top;
-        xn[c] = pfma(fy_, dyv, top);
-        const P dxv = pfma(fy_, h1 - h0, h0);
-        const P dxz = dxv * mzx, dyz = dyv * mzy;   // d sample / d P'1, d P'2 up to the common 1/z''
+        xn[c] = pfma(tfy, dyv, top);
+        if (!tvalid) xn[c] = P(0.0f);
+        const P dxv = pfma(tfy, h1 - h0, h0);
+        const P dxz = dxv * tmzx, dyz = dyv * tmzy;   // d sample / d P'1, d P'2 up to the common 1/z''
 #pragma unroll
         for (int s = 0; s < S; ++s) { park[(2 * c) * S + s] = dxz.get(s); park[(2 * c + 1) * S + s] = dyz.get(s); }
       }
 #pragma unroll
-      for (int s = 0; s < S; ++s) { park[2 * C * S + s] = uu.get(s); park[(2 * C + 1) * S + s] = vv.get(s); }
+      for (int s = 0; s < S; ++s) { park[2 * C * S + s] = tuu.get(s); park[(2 * C + 1) * S + s] = tvv.get(s); }
+      if (tvalid) {
 #pragma unroll
-      for (int k = 0; k < DRV4; ++k)
-        s_drv[(slot * DRV4 + k) * STRIP_THREADS + threadIdx.x] =
-            make_float4(park[4 * k], park[4 * k + 1], park[4 * k + 2], park[4 * k + 3]);
+        for (int k = 0; k < DRV4; ++k)
+          s_drv[(wslot * DRV4 + k) * STRIP_THREADS + threadIdx.x] =
+              make_float4(park[4 * k], park[4 * k + 1], park[4 * k + 2], park[4 * k + 3]);
+      }
     }
-#pragma unroll
-    for (int s = 0; s < S; ++s) { p1[s] += i1[s]; p2[s] += i2[s]; p3[s] += i3[s]; }
+  };
+
+  P xn[C];
+  float yn[C], dn = 0.0f;
+#if STRIP_PIPE
+  issue(Y0 - 2);
+  consume(slot, xn, yn, dn);
+#endif
+  for (int r = Y0 - 2; r <= Y1 + 1; ++r) {
+#if STRIP_PIPE
+    if (r < Y1 + 1) issue(r + 1);   // its loads are consumed after C and D below
+#else
+    issue(r);
+    consume(slot, xn, yn, dn);
+#endif
+
 
     // =========================== C: window row r-1 =============================================
     const int wr = r - 1;
@@ -465,6 +503,9 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
     sel2 = sel1; sel1 = seln;
     d3 = d2; d2 = d1; d1 = dn;
     slot = (slot + 1) % 3;
+#if STRIP_PIPE
+    if (r < Y1 + 1) consume(slot, xn, yn, dn);
+#endif
   }
 
   // ---- one record per warp: loss + 12 pose sums per source (no atomics) -------------------------
