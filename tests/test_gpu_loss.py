@@ -143,3 +143,58 @@ def test_autograd_wrapper_matches_plan():
     P.assert_dense_grad("autograd d_disp", disps[-1].grad / 3.0, ref["d_disp"][-1])
     P.assert_small_grad("autograd d_rvec", poses[0].rvec.grad / 3.0, ref["d_rvec"][0])
     assert vl.shape == (inp.N, 1, inp.H, inp.W) and len(vw) == 2 and vd.shape == disps[-1].shape
+
+
+@pytest.mark.parametrize("W,H,scales", [
+    (28, 8, (0.5, 1.0)),        # exactly one strip, no right halo inside the image
+    (29, 9, (0.5, 1.0)),        # second strip owns a single pixel column
+    (57, 33, (0.25, 0.5, 1.0)), # three strips, last one column wide; odd sizes
+    (4, 4, (0.5, 1.0)),         # smallest maps the reflect padding allows at two scales (2x2 native)
+    (2, 2, (1.0,)),             # W = H = 2: every window is all reflection
+    (3, 5, (1.0,)),
+])
+def test_strip_geometry_edges(W, H, scales):
+    """Strip / halo bookkeeping of photo_strip_kernel at the sizes where it is most fragile."""
+    from mdb200 import synth
+    inp = synth.make_loss_inputs(W, H, 2, seed=21, scales=scales)
+    ref = P.oracle_train_loss(inp)
+    res, _ = _run_gpu(inp)
+    _compare(inp, ref, res)
+
+
+def test_forced_row_segments(monkeypatch):
+    """Three row segments per strip (MDB_STRIP_SEGS): the 2-row halos above and below a segment must
+    reproduce the single-segment result, and both must match the oracle."""
+    from mdb200 import synth
+    inp = synth.make_loss_inputs(60, 96, 2, seed=22, automasking=True)
+    ref = P.oracle_train_loss(inp)
+    monkeypatch.setenv("MDB_STRIP_SEGS", "1")
+    res1, _ = _run_gpu(inp, auto=ref["auto"])
+    monkeypatch.setenv("MDB_STRIP_SEGS", "3")
+    res3, _ = _run_gpu(inp, auto=ref["auto"])
+    _compare(inp, ref, res1)
+    _compare(inp, ref, res3)
+    for a, b in zip(res1.d_disparities, res3.d_disparities):
+        assert torch.allclose(a, b, rtol=1e-5, atol=1e-9)
+
+
+@pytest.mark.parametrize("C", [1, 3])
+def test_single_source(C):
+    """S = 1 (the scalar, un-packed instantiation of the kernel)."""
+    from mdb200 import synth
+    inp = synth.make_loss_inputs(72, 40, 2, C=C, seed=23)
+    inp.source_ids = [3]
+    inp.rvecs, inp.tvecs = inp.rvecs[1:], inp.tvecs[1:]
+    ref = P.oracle_train_loss(inp)
+    res, _ = _run_gpu(inp)
+    _compare(inp, ref, res)
+
+
+def test_far_outside_samples():
+    """A pose that throws most samples far outside the source frames (border clamp, zero gradient)."""
+    from mdb200 import synth
+    inp = synth.make_loss_inputs(64, 32, 1, seed=24)
+    inp.tvecs = [np.array([[[3.0, -2.0, 0.05]]], np.float32), np.array([[[-4.0, 1.0, -0.02]]], np.float32)]
+    ref = P.oracle_train_loss(inp)
+    res, _ = _run_gpu(inp)
+    _compare(inp, ref, res)
