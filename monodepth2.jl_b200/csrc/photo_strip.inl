@@ -24,12 +24,18 @@
 namespace {
 
 constexpr int STRIP_PX = 28;
-constexpr int STRIP_WARPS = 4;
+#ifndef STRIP_NWARPS
+#define STRIP_NWARPS 1   // one warp per CTA: occupancy is then set by the register cap alone
+#endif
+constexpr int STRIP_WARPS = STRIP_NWARPS;   // warps per CTA (independent of each other)
 constexpr int STRIP_THREADS = 32 * STRIP_WARPS;
 constexpr int SEL_NONE = 255;
 constexpr int STRIP_NHEAD = 3;   // record head: photometric sum, smoothness x-sum, smoothness y-sum
 #ifndef STRIP_PIPE
 #define STRIP_PIPE 0   // 1: issue the loads of row r+1 before stages C and D of row r (software pipelining)
+#endif
+#if !defined(STRIP_MAXREG) && !defined(STRIP_MINB)
+#define STRIP_MAXREG 152   // 13 warps per SM, no spills: measured best of 128 / 136 / 144 / 152 / 160 / 168 / 184
 #endif
 #ifndef STRIP_MINB
 #define STRIP_MINB 4   // CTAs per SM the register allocation aims for (128 registers; measured best of 2/3/4)
@@ -77,7 +83,11 @@ struct StripGeom {
 };
 
 template <int C, int S>
+#ifdef STRIP_MAXREG
+__global__ void __maxnreg__(STRIP_MAXREG)
+#else
 __global__ void __launch_bounds__(STRIP_THREADS, STRIP_MINB)
+#endif
 photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   using P = Pk<S>;
   constexpr int NPART = STRIP_NHEAD + NPOSE * S;
