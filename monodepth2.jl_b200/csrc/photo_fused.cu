@@ -32,10 +32,9 @@ struct PoseArgs {
 };
 
 // ---------------------------------------------------------------------------------------
-// 1. sum of the up-sampled disparity (src/training.jl:44-46, 64): thread = full-res column,
-//    walking down the rows of its block with the column-interpolated native rows cached
+// 1. sum of the up-sampled disparity (src/training.jl:44-46, 64) from the native maps alone
 // ---------------------------------------------------------------------------------------
-constexpr int MEAN_ROWS = 32;
+constexpr int MEAN_ROWS = 16;
 constexpr int MEAN_THREADS = 256;
 
 __global__ void __launch_bounds__(MEAN_THREADS)
@@ -46,29 +45,40 @@ disp_mean_kernel(const __grid_constant__ FusedArgs a, double* __restrict__ part 
   const int y0 = rb * MEAN_ROWS, y1 = min(y0 + MEAN_ROWS, H);
   double acc = 0.0;
   if (a.native[sc]) {
-    for (int i = y0 * W + threadIdx.x; i < y1 * W; i += MEAN_THREADS) acc += (double)ldg(d + i);
-  } else {
-    const double rxd = a.rxd[sc], ryd = a.ryd[sc];
-    for (int gx = threadIdx.x; gx < W; gx += MEAN_THREADS) {
-      const double f = (double)gx * rxd;
-      const int x0 = min((int)f, dw - 1), x1 = min(x0 + 1, dw - 1);
-      const double lx = f - (double)x0;
-      int cy = -1;
-      double top = 0.0, dif = 0.0;
-      for (int gy = y0; gy < y1; ++gy) {
-        const double fy = (double)gy * ryd;
-        const int r0 = min((int)fy, dh - 1);
-        if (r0 != cy) {
-          cy = r0;
-          const int r1 = min(r0 + 1, dh - 1);
-          const double v00 = ldg(d + r0 * dw + x0), v01 = ldg(d + r0 * dw + x1);
-          const double v10 = ldg(d + r1 * dw + x0), v11 = ldg(d + r1 * dw + x1);
-          top = fma(lx, v01 - v00, v00);
-          dif = fma(lx, v11 - v10, v10) - top;
-        }
-        // the strip kernel rounds the up-sampled value to float before using it; sum the same numbers
-        acc += (double)(float)fma(fy - (double)r0, dif, top);
+    const int i0 = y0 * W, i1 = y1 * W;
+    if ((((uintptr_t)(d + i0)) & 15) == 0) {   // 16-byte aligned slab: 128-bit loads, 4 in flight per thread
+      const float4* d4 = reinterpret_cast<const float4*>(d + i0);
+      const int n4 = (i1 - i0) / 4;
+      float s0 = 0.0f, s1 = 0.0f, s2 = 0.0f, s3 = 0.0f;   // <= 16 rows x W / 256 / 4 terms each: float is ample here
+#pragma unroll 4
+      for (int i = threadIdx.x; i < n4; i += MEAN_THREADS) {
+        const float4 v = __ldg(d4 + i);
+        s0 += v.x; s1 += v.y; s2 += v.z; s3 += v.w;
       }
+      acc = ((double)s0 + (double)s1) + ((double)s2 + (double)s3);
+      for (int i = i0 + 4 * n4 + threadIdx.x; i < i1; i += MEAN_THREADS) acc += (double)ldg(d + i);
+    } else {
+      for (int i = i0 + threadIdx.x; i < i1; i += MEAN_THREADS) acc += (double)ldg(d + i);
+    }
+  } else {
+    // sum over the full-res grid of the bilinear interpolant = sum_j d_j Wx(jx) Wy(jy), with
+    // W(j) = sum_p max(0, 1 - |p r - j|) on the exact integer numerator: native pixels only
+    const int dx1 = dw - 1, dy1 = dh - 1, W1 = W - 1, H1 = H - 1;
+    const int rows_per = (dh + gridDim.x - 1) / gridDim.x;
+    const int j0 = rb * rows_per, j1 = min(j0 + rows_per, dh);
+    for (int jx = threadIdx.x; jx < dw; jx += MEAN_THREADS) {
+      const int px_lo = max(0, ((jx - 1) * W1) / dx1), px_hi = min(W1, ((jx + 1) * W1 + dx1 - 1) / dx1);
+      int numx = 0;   // sum of (W1 - |p dx1 - jx W1|) over the support, exact in int (< 2^31 for W < 2^15)
+      for (int px = px_lo; px <= px_hi; ++px) numx += max(0, W1 - abs(px * dx1 - jx * W1));
+      const double wx = (double)numx / (double)W1;
+      double col = 0.0;
+      for (int jy = j0; jy < j1; ++jy) {
+        const int py_lo = max(0, ((jy - 1) * H1) / dy1), py_hi = min(H1, ((jy + 1) * H1 + dy1 - 1) / dy1);
+        int numy = 0;
+        for (int py = py_lo; py <= py_hi; ++py) numy += max(0, H1 - abs(py * dy1 - jy * H1));
+        col = fma((double)numy / (double)H1, (double)ldg(d + jy * dw + jx), col);
+      }
+      acc = fma(wx, col, acc);
     }
   }
   __shared__ double red[MEAN_THREADS / 32];

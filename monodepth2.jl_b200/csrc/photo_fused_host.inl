@@ -97,59 +97,89 @@ finalize_item_kernel(const float* __restrict__ partials, int records, PoseArgs p
 }
 
 // ---------------------------------------------------------------------------------------
-// 5. transpose of upsample_bilinear (align-corners) as a gather: one thread per NATIVE pixel sums
-//    the full-resolution gradients whose interpolation stencil touches it.  The weight of full-res
-//    column p for native column j is the hat function max(0, 1 - |p r - j|), r = (dw-1)/(W-1),
-//    evaluated on the exact integer numerator p (dw-1) - j (W-1).  Native scales only get the
-//    mean-normalisation constant added (grid-stride, in place).
+// 5. transpose of upsample_bilinear (align-corners), separable and atomic-free (deterministic):
+//    V: tmp[jy][px] = sum_py wy(py, jy) (g[py][px] + c)   thread = full-res column (coalesced, the
+//       <= 2/r + 1 row loads of a thread are independent), and the constant alone for native scales
+//    H: out[jy][jx] = sum_px wx(px, jx) tmp[jy][px]       thread = native pixel, on the small tmp
+//    The weight of full-res index p for native index j is the hat function max(0, 1 - |p r - j|),
+//    r = (dn-1)/(Dn-1), evaluated on the exact integer numerator p (dn-1) - j (Dn-1).
 // ---------------------------------------------------------------------------------------
 struct UpArgs {
   const float* gfull[MDB_MAX_SCALES];   // null for native scales
   float* gnat[MDB_MAX_SCALES];
+  float* tmp[MDB_MAX_SCALES];           // [N][dh][W] per low-res scale
   int dw[MDB_MAX_SCALES], dh[MDB_MAX_SCALES];
+  int row_start[MDB_MAX_SCALES + 1];    // prefix sums of dh: blockIdx.y -> (scale, native row)
   int Ls, W, H, N;
 };
 
+constexpr int UP_ROWS = 4;   // (scale, native row) pairs per CTA: keeps the CTA count in the thousands
+
 __global__ void __launch_bounds__(256)
-upsample_bwd_kernel(const __grid_constant__ UpArgs a, const ScaleStat* __restrict__ stats) {
-  const int sc = blockIdx.y, n = blockIdx.z;
-  const int W = a.W, H = a.H, dw = a.dw[sc], dh = a.dh[sc];
-  const float cc = stats[(size_t)sc * a.N + n].cconst;
-  float* out = a.gnat[sc] + (size_t)n * dw * dh;
-  const float* g = a.gfull[sc];
-  if (g == nullptr) {   // native: out already holds the gradient; add the constant
-    if (cc == 0.0f) return;
-    float4* o4 = reinterpret_cast<float4*>(out);
-    const int n4 = (((uintptr_t)out & 15) == 0) ? dw * dh / 4 : 0;   // item slab 16-byte aligned?
-    for (int i = blockIdx.x * 256 + threadIdx.x; i < n4; i += gridDim.x * 256) {
-      float4 v = o4[i];
-      v.x += cc; v.y += cc; v.z += cc; v.w += cc;
-      o4[i] = v;
+upsample_bwd_v_kernel(const __grid_constant__ UpArgs a, const ScaleStat* __restrict__ stats) {
+  const int n = blockIdx.y, W = a.W, H = a.H;
+  const int rows_total = a.row_start[a.Ls];
+  for (int rr = blockIdx.x * UP_ROWS; rr < min(rows_total, (int)(blockIdx.x + 1) * UP_ROWS); ++rr) {
+    int sc = 0;
+    while (sc + 1 < a.Ls && rr >= a.row_start[sc + 1]) ++sc;
+    const int jy = rr - a.row_start[sc], dh = a.dh[sc];
+    const float cc = stats[(size_t)sc * a.N + n].cconst;
+    const float* g = a.gfull[sc];
+    if (g == nullptr) {   // native: the strip kernel wrote the gradient in place; add the constant
+      if (cc != 0.0f) {
+        float* o = a.gnat[sc] + ((size_t)n * H + jy) * W;
+        for (int px = threadIdx.x; px < W; px += 256) o[px] += cc;
+      }
+      continue;
     }
-    for (int i = 4 * n4 + blockIdx.x * 256 + threadIdx.x; i < dw * dh; i += gridDim.x * 256) out[i] += cc;
-    return;
-  }
-  g += (size_t)n * W * H;
-  const int dx1 = dw - 1, dy1 = dh - 1, W1 = W - 1, H1 = H - 1;
-  const float iw = 1.0f / (float)W1, ih = 1.0f / (float)H1;
-  for (int j = blockIdx.x * 256 + threadIdx.x; j < dw * dh; j += gridDim.x * 256) {
-    const int jx = j % dw, jy = j / dw;
-    // full-res p with |p dx1 - jx W1| < W1  <=>  (jx-1) W1 / dx1 < p < (jx+1) W1 / dx1
-    const int px_lo = max(0, ((jx - 1) * W1) / dx1), px_hi = min(W1, ((jx + 1) * W1 + dx1 - 1) / dx1);
+    g += (size_t)n * W * H;
+    const int dy1 = dh - 1, H1 = H - 1;
+    const float ih = 1.0f / (float)H1;
+    // full-res p with |p dy1 - jy H1| < H1  <=>  (jy-1) H1 / dy1 < p < (jy+1) H1 / dy1
     const int py_lo = max(0, ((jy - 1) * H1) / dy1), py_hi = min(H1, ((jy + 1) * H1 + dy1 - 1) / dy1);
-    float acc = 0.0f;
-    for (int py = py_lo; py <= py_hi; ++py) {
-      const float wy = 1.0f - (float)abs(py * dy1 - jy * H1) * ih;
-      if (wy <= 0.0f) continue;
-      const float* row = g + (size_t)py * W;
-      float racc = 0.0f;
+    float* t = a.tmp[sc] + ((size_t)n * dh + jy) * W;
+    // four columns per thread with independent accumulators: 4 x 4 loads in flight per thread
+    for (int px0 = threadIdx.x; px0 < W; px0 += 4 * 256) {
+      float acc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll 4
+      for (int py = py_lo; py <= py_hi; ++py) {
+        const float wy = fmaxf(1.0f - (float)abs(py * dy1 - jy * H1) * ih, 0.0f);
+        const float* row = g + (size_t)py * W;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int px = px0 + k * 256;
+          if (px < W) acc[k] = fmaf(wy, ldg(row + px) + cc, acc[k]);
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (px0 + k * 256 < W) t[px0 + k * 256] = acc[k];
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+upsample_bwd_h_kernel(const __grid_constant__ UpArgs a) {
+  const int n = blockIdx.y, W = a.W;
+  const int rows_total = a.row_start[a.Ls];
+  for (int rr = blockIdx.x * UP_ROWS; rr < min(rows_total, (int)(blockIdx.x + 1) * UP_ROWS); ++rr) {
+    int sc = 0;
+    while (sc + 1 < a.Ls && rr >= a.row_start[sc + 1]) ++sc;
+    if (a.gfull[sc] == nullptr) continue;
+    const int jy = rr - a.row_start[sc], dw = a.dw[sc], dh = a.dh[sc];
+    const float* t = a.tmp[sc] + ((size_t)n * dh + jy) * W;
+    const int dx1 = dw - 1, W1 = W - 1;
+    const float iw = 1.0f / (float)W1;
+    for (int jx = threadIdx.x; jx < dw; jx += 256) {
+      const int px_lo = max(0, ((jx - 1) * W1) / dx1), px_hi = min(W1, ((jx + 1) * W1 + dx1 - 1) / dx1);
+      float acc = 0.0f;
+#pragma unroll 4
       for (int px = px_lo; px <= px_hi; ++px) {
         const float wx = fmaxf(1.0f - (float)abs(px * dx1 - jx * W1) * iw, 0.0f);
-        racc = fmaf(wx, ldg(row + px) + cc, racc);
+        acc = fmaf(wx, ldg(t + px), acc);
       }
-      acc = fmaf(wy, racc, acc);
+      a.gnat[sc][((size_t)n * dh + jy) * dw + jx] = acc;
     }
-    out[j] = acc;
   }
 }
 
@@ -172,7 +202,7 @@ __global__ void finalize_loss_kernel(const double* __restrict__ item_loss, int N
 }
 
 struct FusedLayout {
-  size_t o_ppd, o_meanpart, o_stats, o_partials, o_itemloss, o_gfull[MDB_MAX_SCALES], total;
+  size_t o_ppd, o_meanpart, o_stats, o_partials, o_itemloss, o_gfull[MDB_MAX_SCALES], o_tmp[MDB_MAX_SCALES], total;
   int rowblocks, npart;
   StripGeom strip;   // decomposition of the streaming kernel
   int records;       // partial-sum records per item = warps per item
@@ -210,6 +240,7 @@ FusedLayout fused_layout(const mdb_loss_io* io, int num_sms = 148) {
   for (int s = 0; s < io->Ls; ++s) {
     const bool native = io->dw[s] == io->W && io->dh[s] == io->H;
     L.o_gfull[s] = native ? 0 : take(sizeof(float) * (size_t)io->N * io->W * io->H);
+    L.o_tmp[s] = native ? 0 : take(sizeof(float) * (size_t)io->N * io->W * io->dh[s]);
   }
   L.total = off;
   return L;
@@ -298,7 +329,9 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
     fin.kx[s] = fa.kx[s]; fin.ky[s] = fa.ky[s];
     ua.gfull[s] = fa.native[s] ? nullptr : fa.gout[s];
     ua.gnat[s] = io->d_disparity[s];
+    ua.tmp[s] = fa.native[s] ? nullptr : (float*)(ws + L.o_tmp[s]);
     ua.dw[s] = io->dw[s]; ua.dh[s] = io->dh[s];
+    ua.row_start[s + 1] = ua.row_start[s] + io->dh[s];
   }
   fa.auto_loss = p->automasking ? io->auto_loss : nullptr;
   fa.automask = p->automasking ? 1 : 0;
@@ -344,9 +377,15 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
   else finalize_item_kernel<1><<<N, FIN_THREADS, 0, st>>>(fa.partials, L.records, pa, fin, stats, item_loss);
   MDB_LAUNCHED(h);
   {
-    dim3 grid(40, Ls, N);
-    upsample_bwd_kernel<<<grid, 256, 0, st>>>(ua, stats);
+    dim3 gv((ua.row_start[Ls] + UP_ROWS - 1) / UP_ROWS, N), gh = gv;
+    upsample_bwd_v_kernel<<<gv, 256, 0, st>>>(ua, stats);
     MDB_LAUNCHED(h);
+    bool any_low = false;
+    for (int s = 0; s < Ls; ++s) any_low = any_low || !fa.native[s];
+    if (any_low) {
+      upsample_bwd_h_kernel<<<gh, 256, 0, st>>>(ua);
+      MDB_LAUNCHED(h);
+    }
   }
   mdb_prof_mark(h, pslot, 3, st);
   finalize_loss_kernel<<<1, 256, 0, st>>>(item_loss, N, stats, Ls * N, up, io->loss);
