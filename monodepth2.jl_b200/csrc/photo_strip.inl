@@ -239,22 +239,17 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
         asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(zi) : "d"(z));   // MUFU.RCP64H: ~2^-20, squared by the Newton step
         zi = fma(zi, fma(-z, zi, 1.0), zi);
         const double X = fma(P1, zi, -1.0), Y = fma(P2, zi, -1.0);   // 0-based source coordinates
-        // floor by the 2^52 trick (round-down add): integer part in the low word, no F2I / I2F
-        const double MAGIC = 6755399441055744.0;
-        const double tX = __dadd_rd(X, MAGIC), tY = __dadd_rd(Y, MAGIC);
-        int ix = __double2loint(tX), iy = __double2loint(tY);
-        float fxs = (float)(X - (tX - MAGIC)), fys = (float)(Y - (tY - MAGIC));
-        // |X| < 2^31 leaves the high word of X + 2^52 + 2^51 at 0x43380000 (X >= 0) or 0x4337ffff (X < 0);
-        // anything else is far outside the image (or NaN): send it to the border on its side
-        const int hX = __double2hiint(tX), hY = __double2hiint(tY);
-        if ((unsigned)(hX - 0x4337ffff) > 1u) { ix = (hX >= 0x43380000) ? W : -1; fxs = 0.0f; }
-        if ((unsigned)(hY - 0x4337ffff) > 1u) { iy = (hY >= 0x43380000) ? H : -1; fys = 0.0f; }
+        // floor with a saturating convert (far-outside coordinates saturate and clamp to the border below)
+        int ix = __double2int_rd(X), iy = __double2int_rd(Y);
+        float fxs = (float)(X - (double)ix), fys = (float)(Y - (double)iy);
         // NNlib grid_sample(padding_mode=:border), align-corners: clamp to [0, W-1]; no gradient where
         // clamped (position <= 0 or >= W-1).  The right border is the cell W-2 with weight 1.
-        const bool inx = ix >= 0 && ix <= W - 2 && !(ix == 0 && fxs == 0.0f);
-        const bool iny = iy >= 0 && iy <= H - 2 && !(iy == 0 && fys == 0.0f);
-        if (ix < 0) { ix = 0; fxs = 0.0f; } else if (ix > W - 2) { ix = W - 2; fxs = 1.0f; }
-        if (iy < 0) { iy = 0; fys = 0.0f; } else if (iy > H - 2) { iy = H - 2; fys = 1.0f; }
+        const bool rx = (unsigned)ix <= (unsigned)(W - 2), ry = (unsigned)iy <= (unsigned)(H - 2);   // inside the cell range
+        const bool inx = rx && ((ix | __float_as_int(fxs)) != 0), iny = ry && ((iy | __float_as_int(fys)) != 0);
+        if (!rx) fxs = ix < 0 ? 0.0f : 1.0f;
+        if (!ry) fys = iy < 0 ? 0.0f : 1.0f;
+        ix = min(max(ix, 0), W - 2);
+        iy = min(max(iy, 0), H - 2);
         ot[s] = (unsigned)(iy * W + ix) + src_off[s];
         const float zf = (float)zi;
         tfx.set(s, fxs); tfy.set(s, fys);
