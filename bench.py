@@ -13,11 +13,12 @@ than L2 (866 MB vs 126 MB), so no explicit flush is needed between iterations.
   value     device-resident inputs, CUDA-event timed on the launching stream, max over ranks
   e2e       the same call made through mdb200.train_loss_host with PINNED HOST buffers: every
             step copies the inputs H2D and the loss + all gradients D2H inside the timed region
-  roofline  the dominant kernel (photo_fused_kernel) timed live with CUDA events recorded
+  roofline  the dominant kernel (photo_strip_kernel) timed live with CUDA events recorded
             inside the C-ABI call (mdb_profile_*), against the algorithmic bytes of SURVEY 8d
   cpu_baseline / --impl reference
-            the reference's algorithm on the host cores: the torch-CPU float32 restatement
-            (oracle/torch_ref.py, autograd backward), all threads, on a bounded sample.
+            the reference's algorithm on the host cores: the plain-C float32 port
+            (oracle/c_port/mdb_oracle.c, hand-written pullbacks), one item per thread on all
+            cores, on a bounded sample (one item per core).
 """
 import argparse
 import json
@@ -44,7 +45,7 @@ def parse():
     ap.add_argument("--config", default="config5", choices=["config2", "config3", "config5", "config4"])
     ap.add_argument("--render-batch", type=int, default=2, help="config4: render batch B (reference scripts use 2 and 4)")
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch override (default: the config's)")
-    ap.add_argument("--cpu-sample-items", type=int, default=4)
+    ap.add_argument("--cpu-sample-items", type=int, default=0, help="items in the CPU sample (0 = one per host core)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -128,41 +129,42 @@ def make_inputs(args):
 
 
 def cpu_reference_rate(inp, items, steps, warmup):
-    """The reference algorithm on the host cores: torch-CPU float32 restatement, autograd
-    backward, all threads.  Returns (warped px/s, cores, seconds per step)."""
-    import copy
-    import torch
-    import parity as P
+    """The reference algorithm on the host cores: the plain-C float32 port (oracle/c_port/mdb_oracle.c,
+    unfused, op by op in the reference's order, hand-written pullbacks), one item per thread on all
+    cores.  `items` <= 0 means one item per core.  Returns (warped px/s, threads, seconds per step, items)."""
+    import numpy as np
+    from oracle import c_ref
     cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    one = copy.copy(inp)
-    items = min(items, inp.N)
-    one.N = items
-    one.x = inp.x[:items]
-    one.disparities = [d[:items] for d in inp.disparities]
-    one.rvecs = [r[:items] for r in inp.rvecs]
-    one.tvecs = [t[:items] for t in inp.tvecs]
+    items = min(items if items > 0 else cores, inp.N)
+    threads = min(cores, items)
+    a = (inp.x[:items], [d[:items] for d in inp.disparities], [r[:items] for r in inp.rvecs],
+         [t[:items] for t in inp.tvecs], None, inp.K, inp.invK)
+    kw = dict(target_id=inp.target_id, source_ids=inp.source_ids, scales=inp.scales, automasking=False,
+              dtype=np.float32, threads=threads)
     units = items * len(inp.disparities) * len(inp.source_ids) * inp.W * inp.H
     for _ in range(warmup):
-        P.oracle_train_loss(one, dtype=torch.float32)
+        c_ref.train_loss(*a, **kw)
     ts = []
     for _ in range(steps):
         t0 = time.perf_counter()
-        P.oracle_train_loss(one, dtype=torch.float32)
+        c_ref.train_loss(*a, **kw)
         ts.append(time.perf_counter() - t0)
     t = sum(ts) / len(ts)
-    return units / t, cores, t, items
+    return units / t, threads, t, items
 
 
 def run_reference(args):
     rank, _, world = dist_env()
     if rank != 0:
         return
-    inp, _ = make_inputs(argparse.Namespace(config=args.config, batch=min(args.batch or 8, 8)))
-    steps, warm = max(1, min(args.steps, 5)), max(1, min(args.warmup, 2))
+    ncpu = os.cpu_count() or 1
+    want = args.cpu_sample_items if args.cpu_sample_items > 0 else ncpu
+    inp, _ = make_inputs(argparse.Namespace(config=args.config, batch=min(args.batch or want, want)))
+    steps, warm = max(1, min(args.steps, 20)), max(1, min(args.warmup, 5))
     rate, cores, t, items = cpu_reference_rate(inp, args.cpu_sample_items, steps, warm)
     sample = (f"{items} of the per-GPU batch's items at {inp.W}x{inp.H}, {len(inp.disparities)} scales, "
-              f"{steps} steps after {warm} warm-up (torch-CPU float32 restatement of the Julia path, autograd backward)")
+              f"{steps} steps after {warm} warm-up (plain-C float32 port of the Julia path, oracle/c_port, one item per thread, "
+              f"{cores} threads)")
     line = {
         "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus,
         "steps": steps, "warmup": warm, "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "weak",
@@ -311,8 +313,8 @@ def run_ours(args):
         if not args.no_cpu_baseline and world == 1:
             rate, cores, t, items = cpu_reference_rate(inp, args.cpu_sample_items, 3, 1)
             line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
-                                    "sample": f"{items} of the batch's {N} items, 3 steps after 1 warm-up, torch-CPU "
-                                              f"float32 restatement with autograd backward, {cores} threads ({t:.2f} s/step)"}
+                                    "sample": f"{items} of the batch's {N} items, 3 steps after 1 warm-up, plain-C float32 port "
+                                              f"(oracle/c_port), one item per thread, {cores} threads ({t:.2f} s/step)"}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -1,0 +1,138 @@
+"""Holds the two CPU oracles against each other: oracle/torch_ref.py (float64 torch, autograd)
+and oracle/c_port/mdb_oracle.c (plain C, every pullback written by hand), and the C one against
+the known answers of /root/reference/test/runtests.jl that concern it.  Two independent
+restatements only agree to 1e-9 if the forward and every derivative agree."""
+import numpy as np
+import pytest
+import torch
+from scipy.spatial.transform import Rotation
+
+from mdb200 import synth
+from oracle import c_ref
+from oracle import torch_ref as T
+from parity import oracle_train_loss
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _build():
+    c_ref.build()
+
+
+def _close(name, got, ref, tol):
+    got = np.asarray(got, dtype=np.float64).reshape(-1)
+    ref = ref.detach().double().numpy().reshape(-1)
+    scale = max(np.abs(ref).max(), 1e-300)
+    err = np.abs(got - ref).max() / scale
+    assert err < tol, f"{name}: max err {err:.3e} (scale {scale:.3e})"
+
+
+def _c_loss(inp, auto, dtype=np.float64, **kw):
+    return c_ref.train_loss(inp.x, inp.disparities, inp.rvecs, inp.tvecs, auto, inp.K, inp.invK,
+                            target_id=inp.target_id, source_ids=inp.source_ids, scales=inp.scales,
+                            automasking=inp.automasking, dtype=dtype, **kw)
+
+
+@pytest.mark.parametrize("W,H,N,auto,seed", [(48, 20, 2, False, 11), (64, 24, 3, True, 12), (33, 17, 1, True, 13)])
+def test_train_loss_two_oracles_agree(W, H, N, auto, seed):
+    inp = synth.make_loss_inputs(W, H, N, seed=seed, automasking=auto)
+    ref = oracle_train_loss(inp)
+    a = None if ref["auto"] is None else ref["auto"].numpy()
+    got = _c_loss(inp, a, threads=2)
+    assert abs(got["loss"] - ref["loss"]) < 1e-11 * abs(ref["loss"])
+    for k in range(len(inp.disparities)):
+        _close(f"d_disp[{k}]", got["d_disp"][k], ref["d_disp"][k], 1e-9)
+    for s in range(2):
+        _close(f"d_rvec[{s}]", got["d_rvec"][s], ref["d_rvec"][s], 1e-9)
+        _close(f"d_tvec[{s}]", got["d_tvec"][s], ref["d_tvec"][s], 1e-9)
+
+
+def test_simple_depth_two_oracles_agree():  # src/simple_depth.jl:25-41
+    inp = synth.make_loss_inputs(40, 16, 1, seed=14, scales=(1.0,))
+    ref = oracle_train_loss(inp, normalize=False, smooth_mode=1)
+    got = _c_loss(inp, None, normalize=False, smooth_mode=1)
+    assert abs(got["loss"] - ref["loss"]) < 1e-11 * abs(ref["loss"])
+    _close("d_disp", got["d_disp"][0], ref["d_disp"][0], 1e-9)
+    for s in range(2):
+        _close(f"d_rvec[{s}]", got["d_rvec"][s], ref["d_rvec"][s], 1e-9)
+        _close(f"d_tvec[{s}]", got["d_tvec"][s], ref["d_tvec"][s], 1e-9)
+
+
+def test_large_motion_border_samples():
+    """poses large enough to push samples over the border: clamp multiplier and tap bounds"""
+    inp = synth.make_loss_inputs(48, 20, 2, seed=15)
+    inp.rvecs = [r * 6 for r in inp.rvecs]
+    inp.tvecs = [t * 8 for t in inp.tvecs]
+    ref = oracle_train_loss(inp)
+    got = _c_loss(inp, None)
+    assert abs(got["loss"] - ref["loss"]) < 1e-11 * abs(ref["loss"])
+    for k in range(4):
+        _close(f"d_disp[{k}]", got["d_disp"][k], ref["d_disp"][k], 1e-9)
+    for s in range(2):
+        _close(f"d_rvec[{s}]", got["d_rvec"][s], ref["d_rvec"][s], 1e-9)
+        _close(f"d_tvec[{s}]", got["d_tvec"][s], ref["d_tvec"][s], 1e-9)
+
+
+def test_float32_variant_close_to_float64():
+    """the fp32 build (the one the CPU baseline times) is the same algorithm"""
+    inp = synth.make_loss_inputs(64, 24, 2, seed=16)
+    a = _c_loss(inp, None)
+    b = _c_loss(inp, None, dtype=np.float32, threads=2)
+    assert abs(a["loss"] - b["loss"]) < 1e-4 * abs(a["loss"])
+    g64, g32 = a["d_disp"][3].reshape(-1), b["d_disp"][3].reshape(-1).astype(np.float64)
+    assert np.linalg.norm(g64 - g32) < 5e-2 * np.linalg.norm(g64)   # argmin/sign flips allowed, not a new algorithm
+
+
+def test_threads_do_not_change_the_result():
+    inp = synth.make_loss_inputs(40, 16, 5, seed=17)
+    a, b = _c_loss(inp, None, threads=1), _c_loss(inp, None, threads=4)
+    assert a["loss"] == b["loss"]
+    assert all(np.array_equal(x, y) for x, y in zip(a["d_disp"], b["d_disp"]))
+
+
+# ---- known answers of test/runtests.jl that the C file restates ---------------------------
+def test_rotations_c():  # runtests.jl:14-29
+    rng = np.random.default_rng(0)
+    v = rng.random((5, 3))
+    R = c_ref.so3_exp_map(v)
+    for n in range(5):
+        assert np.allclose(R[n].T, Rotation.from_rotvec(v[n]).as_matrix(), atol=1e-5)
+
+
+def test_transformation_c():  # runtests.jl:31-50
+    rng = np.random.default_rng(1)
+    rvec, tvec, p = rng.random((1, 3)), rng.random((1, 1, 3)), rng.random(3)
+    R, t = c_ref.compose_T(rvec, tvec, False)
+    Ri, ti = c_ref.compose_T(rvec, tvec, True)
+    npnt = R[0].T @ p + t[0, 0]
+    assert np.allclose(npnt, Rotation.from_rotvec(rvec[0]).as_matrix() @ p + tvec[0, 0], atol=1e-6)
+    assert np.allclose(Ri[0].T @ npnt + ti[0, 0], p, atol=1e-6)
+
+
+def test_compose_T_pullback_c():
+    rng = np.random.default_rng(2)
+    for invert in (False, True):
+        r, t = 0.3 * rng.standard_normal((3, 3)), rng.standard_normal((3, 1, 3))
+        dR, dt = rng.standard_normal((3, 3, 3)), rng.standard_normal((3, 1, 3))
+        rt, tt = torch.tensor(r, requires_grad=True), torch.tensor(t, requires_grad=True)
+        Rj, tj = T.composeT(rt, tt, invert)
+        gr, gt = torch.autograd.grad((Rj * torch.tensor(dR)).sum() + (tj * torch.tensor(dt)).sum(), [rt, tt])
+        cr, ct = c_ref.compose_T_bwd(r, t, invert, dR, dt)
+        assert np.allclose(cr, gr.numpy(), atol=1e-12) and np.allclose(ct, gt.numpy().reshape(-1, 3), atol=1e-12)
+
+
+def test_smooth_loss_known_answer_c():  # runtests.jl:70-83 -> 0.2542
+    """The reference's own vectors.  smooth_loss is reached through the slow_depth closure
+    (src/simple_depth.jl:25-41): with all three frames equal and an identity pose the photometric
+    term vanishes (SSIM(x,x) = 0, the warp is the identity up to Project's 1e-7)."""
+    disp = np.array([[0.0, 0.2], [0.1, 0.3]]).reshape(1, 1, 2, 2)       # Julia column-major 0,.2,.1,.3 as (H,W)
+    K, invK = synth.intrinsics(2, 2)
+    ident = dict(rvecs=[np.full((1, 3), 1e-9)] * 2, tvecs=[np.zeros((1, 1, 3))] * 2)
+
+    def sl(image):
+        x = np.broadcast_to(image.reshape(1, 1, 1, 2, 2), (1, 3, 1, 2, 2)).copy()
+        return c_ref.train_loss(x, [disp], ident["rvecs"], ident["tvecs"], None, K, invK, scales=(1.0,), automasking=False,
+                                normalize=False, smooth_mode=1, grad=False)["loss"]
+
+    tl = np.abs(disp[..., :, :-1] - disp[..., :, 1:]).mean() + np.abs(disp[..., :-1, :] - disp[..., 1:, :]).mean()
+    assert abs(sl(np.ones((2, 2))) - tl) < 1e-6
+    assert abs(sl(np.array([[0.1, 0.3], [0.2, 0.4]])) - 0.2542) < 1e-4
