@@ -42,7 +42,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--config", default="config5", choices=["config2", "config3", "config5", "config4"])
+    ap.add_argument("--config", default="config5", choices=["config1", "config2", "config3", "config5", "config4"])
     ap.add_argument("--render-batch", type=int, default=2, help="config4: render batch B (reference scripts use 2 and 4)")
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch override (default: the config's)")
     ap.add_argument("--cpu-sample-items", type=int, default=0, help="items in the CPU sample (0 = one per host core)")
@@ -376,9 +376,82 @@ def run_render(args):
     print(json.dumps(line), flush=True)
 
 
+def run_slow_depth(args):
+    """BASELINE config 1: the `slow_depth` loop (src/simple_depth.jl:1-62) at 416x128, one triplet:
+    500 iterations of {loss fwd+bwd, ADAM(3e-4)} replayed from one CUDA graph.  Prints its own JSON line
+    (not the headline; the default stays config 5).  Compared with (a) the same kernels launched one by
+    one from the host mirror (what a Julia caller without the graph would do) and (b) the plain-C CPU
+    port doing the same iteration on one host core."""
+    import numpy as np
+    import torch
+    import mdb200
+    from mdb200 import synth
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    inp = synth.make_config("config1")
+    x = torch.tensor(inp.x, device=dev)
+    iters = 500
+    units = inp.W * inp.H * 2                    # warped px per iteration (1 item, 1 scale, 2 sources)
+    ms = []
+    l0 = None
+    for it in range(args.warmup + args.steps):
+        sd = mdb200.SlowDepth(x, inp.K, inp.invK, max_iters=iters)
+        if it == args.warmup:
+            l0 = mdb200.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        sd.run(iters)
+        e1.record()
+        torch.cuda.synchronize()
+        if it >= args.warmup:
+            ms.append(e0.elapsed_time(e1))
+        hist = sd.loss_history.cpu().numpy()
+        sd.close()
+    launches = mdb200.launch_count() - l0
+    t_graph = sum(ms) / len(ms)
+    # (a) per-kernel launches from the host mirror, no graph
+    plan = mdb200.simple_depth_plan(x, inp.K, inp.invK)
+    disp = torch.full((1, 1, inp.H, inp.W), 0.5, device=dev)
+    poses = [mdb200.Pose(torch.tensor([[0.0, 0.0, 0.01]], device=dev), torch.zeros((1, 1, 3), device=dev)) for _ in range(2)]
+    opt = mdb200.ADAM(3e-4)
+    params = [disp] + [t for pz in poses for t in (pz.rvec, pz.tvec)]
+    def eager(n):
+        for _ in range(n):
+            r = plan(x, [disp], poses, None)
+            opt.update(params, [r.d_disparities[0]] + [t for pz in r.d_poses for t in (pz.rvec, pz.tvec)])
+    eager(20)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter(); eager(iters); torch.cuda.synchronize(); t_eager = (time.perf_counter() - t0) * 1e3
+    line = {"metric": "slow_depth iterations/s (loss fwd+bwd + ADAM)", "value": iters / (t_graph * 1e-3), "unit": "iter/s",
+            "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_graph, "higher_is_better": True,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"config1: slow_depth, {inp.W}x{inp.H}, 1 triplet, {iters} iterations per step",
+                       "timing": "CUDA events around mdb_slow_depth_run (500 graph replays)", "l2": "working set 2 MB: L2-resident by design"},
+            "us_per_iteration": t_graph * 1e3 / iters, "warped_px_per_s": units * iters / (t_graph * 1e-3),
+            "eager_ms_per_500": t_eager, "eager_us_per_iteration": t_eager * 1e3 / iters,
+            "loss_first_last": [float(hist[0]), float(hist[-1])], "gpu_launches": int(launches)}
+    if not args.no_cpu_baseline:
+        from oracle import c_ref
+        d = np.full((1, 1, inp.H, inp.W), 0.5, dtype=np.float32)
+        rv = [np.array([[0, 0, 0.01]], dtype=np.float32) for _ in range(2)]
+        tv = [np.zeros((1, 1, 3), dtype=np.float32) for _ in range(2)]
+        n_cpu = 10
+        t0 = time.perf_counter()
+        for _ in range(n_cpu):          # the loss + gradient dominates; the ADAM arithmetic on 53 K numbers is noise
+            c_ref.train_loss(inp.x, [d], rv, tv, None, inp.K, inp.invK, scales=(1.0,), automasking=False, normalize=False,
+                             smooth_mode=1, dtype=np.float32, threads=1)
+        t_cpu = (time.perf_counter() - t0) / n_cpu
+        line["cpu_baseline"] = {"value": 1.0 / t_cpu, "unit": "iter/s", "cores": 1, "kind": "port",
+                                "sample": f"{n_cpu} loss+gradient evaluations of the plain-C float32 port on one core "
+                                          f"({t_cpu * 1e3:.1f} ms each; one item cannot be spread over threads)"}
+    print(json.dumps(line), flush=True)
+
+
 if __name__ == "__main__":
     a = parse()
-    if a.config == "config4" and a.impl != "reference":
+    if a.config == "config1" and a.impl != "reference":
+        run_slow_depth(a)
+    elif a.config == "config4" and a.impl != "reference":
         run_render(a)
     elif a.impl == "reference":
         run_reference(a)

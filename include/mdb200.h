@@ -228,6 +228,48 @@ int32_t mdb_render_tgt_rgb_depth_bwd(mdb_handle* h, const float* rgb, const floa
                                      float* d_xyz_tgt, float* d_disparity_src, float* d_rvec, float* d_tvec,
                                      void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- the optimiser loop of slow_depth  (src/simple_depth.jl:14-16, 22-42) ----
+ * Flux.Optimise.update!(ADAM(eta, (beta1, beta2)), theta, grads) over a list of tensors (third-party
+ * Flux.jl, unpinned; semantics restated in oracle/torch_ref.py::flux_adam_step):
+ *   m = b1 m + (1-b1) g;  v = b2 v + (1-b2) g^2;  x -= eta * m / (1 - b1^t) / (sqrt(v / (1 - b2^t)) + eps)
+ * with t = *step + 1.  `step` is a DEVICE int32 that the kernel itself advances (last block out), so the
+ * call can be replayed from a CUDA graph.  If loss_history != NULL, loss_history[*step] = *loss (both
+ * device) is recorded before the counter advances (history_len bounds the index).                 */
+typedef struct mdb_adam_params {
+  double eta;    /* 3e-4, src/simple_depth.jl:16 */
+  double beta1;  /* 0.9   (Flux default)         */
+  double beta2;  /* 0.999 (Flux default)         */
+  double eps;    /* 1e-8  (Flux <= 0.13 default) */
+} mdb_adam_params;
+#define MDB_ADAM_MAX_TENSORS 8
+/* state: n_tensors pairs (m, v) with the tensors' sizes, all zero before the first step; `ticket` is a
+ * DEVICE int32 initialised to 0 (scratch of the last-block-out counter).                          */
+int32_t mdb_adam_update(mdb_handle* h, int32_t n_tensors, float* const* params, const float* const* grads,
+                        float* const* m, float* const* v, const int64_t* sizes, const mdb_adam_params* a,
+                        int32_t* step, int32_t* ticket, const float* loss, float* loss_history,
+                        int32_t history_len, void* stream);
+
+/* `slow_depth` (src/simple_depth.jl:1-62) without its logging: `iters` iterations of
+ *   grads = d/d(disp, poses) [ mean(prediction_loss(warp(disp, x, Ps))) + smooth_loss(disp, target) ];
+ *   update!(ADAM(eta), (disp, poses), grads)
+ * One iteration (the loss kernels of mdb_train_loss_fwdbwd + the ADAM kernel) is captured ONCE into a
+ * CUDA graph at plan creation; mdb_slow_depth_run replays it `iters` times on the caller's stream with
+ * no host round trip.  `io` must describe one full-resolution scale (Ls = 1, dw = W, dh = H); its
+ * disparity / rvec / tvec buffers are the parameters and are UPDATED IN PLACE; its d_* buffers and
+ * `loss` hold the last iteration's gradients and loss.  `params` should have normalize_disparity = 0
+ * and smooth_weight_mode = 1 (src/simple_depth.jl:39).  `state` is caller-owned device memory of
+ * mdb_slow_depth_state_bytes(io) bytes, zeroed by the caller before the first run (ADAM moments +
+ * counters); `workspace` as for mdb_train_loss_fwdbwd.  All pointers must stay valid and unchanged
+ * for the life of the plan.                                                                        */
+typedef struct mdb_slow_depth_plan mdb_slow_depth_plan;
+size_t mdb_slow_depth_state_bytes(const mdb_loss_io* io);
+int32_t mdb_slow_depth_create(mdb_handle* h, const mdb_loss_io* io, const mdb_loss_params* params,
+                              const mdb_adam_params* adam, void* state, size_t state_bytes, void* workspace,
+                              size_t workspace_bytes, float* loss_history, int32_t history_len,
+                              mdb_slow_depth_plan** out);
+int32_t mdb_slow_depth_run(mdb_slow_depth_plan* plan, int32_t iters, void* stream);
+int32_t mdb_slow_depth_destroy(mdb_slow_depth_plan* plan);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

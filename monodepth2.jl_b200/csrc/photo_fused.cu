@@ -116,7 +116,8 @@ __global__ void prep_kernel(PoseArgs a, PosePrepD* __restrict__ outd, const doub
   const int j = idx - a.N * a.S;
   if (j >= Ls * a.N) return;
   double sum = 0.0;
-  for (int rb = 0; rb < rowblocks; ++rb) sum += mean_part[(size_t)j * rowblocks + rb];
+  if (normalize)
+    for (int rb = 0; rb < rowblocks; ++rb) sum += mean_part[(size_t)j * rowblocks + rb];
   ScaleStat st;
   st.inv_mp = normalize ? (float)(1.0 / (sum / ((double)W * H) + 1e-7)) : 1.0f;   // src/training.jl:64-65
   st.cconst = 0.0f;

@@ -5,13 +5,18 @@ namespace {
 // 4. per-item finalize: fixed-order sum of the warp records (double); pose chain to rvec/tvec;
 //    smoothness loss per scale and the mean-normalisation constant of its gradient
 // ---------------------------------------------------------------------------------------
-constexpr int FIN_THREADS = 128;
+#ifndef MDB_FIN_THREADS
+#define MDB_FIN_THREADS 256
+#endif
+constexpr int FIN_THREADS = MDB_FIN_THREADS;   // thread = record: all of a thread's loads are independent
 
 struct FinArgs {
   float* d_rvec[MDB_MAX_SOURCES];
   float* d_tvec[MDB_MAX_SOURCES];
   float kx[MDB_MAX_SCALES], ky[MDB_MAX_SCALES];
   int Ls, N, W, H, normalize;
+  double up;          // 1 / (W H Ng Ls): weight of the photometric sum in the loss
+  float* loss_out;    // non-null only when N == 1: the scalar loss is written here (no separate launch)
 };
 
 template <int S>
@@ -25,6 +30,7 @@ finalize_item_kernel(const float* __restrict__ partials, int records, PoseArgs p
   __shared__ double red[FIN_THREADS / 32][NRED];
   __shared__ double tot[NRED];
   __shared__ double sred[FIN_THREADS / 32][2];
+  __shared__ double sloss;   // sum of the smoothness losses of this item's scales (thread 0 only)
 
   double acc[NRED];
 #pragma unroll
@@ -68,13 +74,17 @@ finalize_item_kernel(const float* __restrict__ partials, int records, PoseArgs p
       const double inv_mp = (double)st.inv_mp;
       const double l = ((double)fa.kx[sc] * tx + (double)fa.ky[sc] * ty) * inv_mp;
       st.loss = (float)l;
+      sloss = (sc ? sloss : 0.0) + (double)st.loss;
       // d/dd of S(d / (m + eps)): the part through the mean is the constant -S / ((m + eps) W H)
       st.cconst = fa.normalize ? (float)(-l * inv_mp / ((double)fa.W * fa.H)) : 0.0f;
       stats[(size_t)sc * fa.N + n] = st;
     }
   }
   __syncthreads();
-  if (threadIdx.x == 0) item_loss[n] = tot[0];
+  if (threadIdx.x == 0) {
+    item_loss[n] = tot[0];
+    if (fa.loss_out) *fa.loss_out = (float)(tot[0] * fa.up + sloss);   // N == 1: same sum as finalize_loss_kernel
+  }
   if (threadIdx.x < S) {
     const int s = threadIdx.x;
     const double* dA = tot + 1 + s * NPOSE;  // row-major dL/dA
@@ -209,14 +219,21 @@ struct FusedLayout {
 };
 
 // Rows per segment: long segments amortise the 4 halo rows, short ones give the machine enough
-// warps.  Aim for ~16 resident sets of 16 warps per SM, never below 32 rows.
+// warps.  Aim for ~16 resident sets of 16 warps per SM, never below 32 rows -- unless the whole
+// problem cannot fill the machine once even then (config 1: 15 strips): a lone warp is latency
+// bound, so the step time is (rows per segment + 4 halo rows) x the row latency, and segments
+// shrink (down to 4 rows) until one wave of 13 warps per SM is resident.
 inline StripGeom strip_geom(const mdb_loss_io* io, int num_sms) {
   StripGeom g{};
   g.nstrips = (io->W + STRIP_PX - 1) / STRIP_PX;
+  const int sms = num_sms > 0 ? num_sms : 148;
   const long long base = (long long)io->N * io->Ls * g.nstrips;
-  long long want = ((long long)16 * 16 * (num_sms > 0 ? num_sms : 148) + base - 1) / base;
-  if (const char* e = getenv("MDB_STRIP_SEGS")) want = atoll(e);
-  const int max_segs = std::max(1, io->H / 32);
+  long long want = ((long long)16 * 16 * sms + base - 1) / base;
+  int max_segs = std::max(1, io->H / 32);
+  const long long one_wave = (long long)13 * sms;
+  if (base * max_segs < one_wave)
+    max_segs = (int)std::max<long long>(max_segs, std::min<long long>(io->H / 4, (one_wave + base - 1) / base));
+  if (const char* e = getenv("MDB_STRIP_SEGS")) { want = atoll(e); max_segs = std::max(1, io->H / 2); }
   g.nsegs = (int)std::min<long long>(std::max<long long>(want, 1), max_segs);
   g.seg_rows = (io->H + g.nsegs - 1) / g.nsegs;
   g.nsegs = (io->H + g.seg_rows - 1) / g.seg_rows;
@@ -348,6 +365,8 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
   fa.vis = io->vis_warp_loss;
   for (int s = 0; s < S; ++s) { fin.d_rvec[s] = io->d_rvec[s]; fin.d_tvec[s] = io->d_tvec[s]; }
   fin.Ls = Ls; fin.N = N; fin.W = W; fin.H = H; fin.normalize = p->normalize_disparity;
+  fin.up = up;
+  fin.loss_out = (N == 1) ? io->loss : nullptr;
   ua.Ls = Ls; ua.W = W; ua.H = H; ua.N = N;
   ScaleStat* stats = (ScaleStat*)(ws + L.o_stats);
   double* mean_part = (double*)(ws + L.o_meanpart);
@@ -355,9 +374,11 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
   const int pslot = (h->prof_ev && h->prof_next < h->prof_slots) ? h->prof_next++ : -1;
   mdb_prof_mark(h, pslot, 0, st);
   {
-    dim3 grid(L.rowblocks, Ls, N);
-    disp_mean_kernel<<<grid, MEAN_THREADS, 0, st>>>(fa, mean_part);
-    MDB_LAUNCHED(h);
+    if (p->normalize_disparity) {   // the mean only feeds the normalisation (src/training.jl:64-65)
+      dim3 grid(L.rowblocks, Ls, N);
+      disp_mean_kernel<<<grid, MEAN_THREADS, 0, st>>>(fa, mean_part);
+      MDB_LAUNCHED(h);
+    }
     const int threads = N * S + Ls * N;
     prep_kernel<<<(threads + 127) / 128, 128, 0, st>>>(pa, (PosePrepD*)(ws + L.o_ppd), mean_part, L.rowblocks, Ls, W, H,
                                                        p->normalize_disparity, stats);
@@ -378,18 +399,23 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
   MDB_LAUNCHED(h);
   {
     dim3 gv((ua.row_start[Ls] + UP_ROWS - 1) / UP_ROWS, N), gh = gv;
-    upsample_bwd_v_kernel<<<gv, 256, 0, st>>>(ua, stats);
-    MDB_LAUNCHED(h);
     bool any_low = false;
     for (int s = 0; s < Ls; ++s) any_low = any_low || !fa.native[s];
+    // native scales only receive the normalisation constant here: nothing to do without it (slow_depth)
+    if (any_low || p->normalize_disparity) {
+      upsample_bwd_v_kernel<<<gv, 256, 0, st>>>(ua, stats);
+      MDB_LAUNCHED(h);
+    }
     if (any_low) {
       upsample_bwd_h_kernel<<<gh, 256, 0, st>>>(ua);
       MDB_LAUNCHED(h);
     }
   }
   mdb_prof_mark(h, pslot, 3, st);
-  finalize_loss_kernel<<<1, 256, 0, st>>>(item_loss, N, stats, Ls * N, up, io->loss);
-  MDB_LAUNCHED(h);
+  if (N > 1) {   // N == 1: finalize_item_kernel already wrote the scalar
+    finalize_loss_kernel<<<1, 256, 0, st>>>(item_loss, N, stats, Ls * N, up, io->loss);
+    MDB_LAUNCHED(h);
+  }
   mdb_prof_mark(h, pslot, 4, st);
   return MDB_OK;
 }

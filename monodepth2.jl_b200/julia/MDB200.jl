@@ -242,4 +242,61 @@ function ChainRulesCore.rrule(::typeof(render_tgt_rgb_depth), rgb, sigma, dispar
     (rgb_out, depth, mask), render_pullback
 end
 
+# ---- SURVEY 8(f) rank 1: slow_depth's optimiser loop on the device (src/simple_depth.jl:1-62) ---------
+struct AdamParams          # mdb_adam_params
+    eta::Cdouble
+    beta1::Cdouble
+    beta2::Cdouble
+    eps::Cdouble
+end
+
+"""
+    slow_depth(x, ssim, backprojections, projections, invKs, Ks, transfer; target_id, source_ids,
+               min_depth, max_depth, log_dir)
+
+Same signature as the reference.  `disp`, the two `Pose`s and the ADAM moments live on the device; one
+iteration (loss forward+backward + `update!`) is a CUDA graph that `mdb_slow_depth_run` replays.  The
+reference's logging at iteration 1, 5, 10, ... is kept by running the graph in chunks.
+"""
+function slow_depth(x::CuArray{Float32,5}, ssim, backprojections, projections, invKs, Ks, transfer;
+                    target_id, source_ids, min_depth, max_depth, log_dir, iters::Integer=500, log_step::Integer=5)
+    W, H, C, L, N = size(x)
+    S = length(source_ids)
+    disp = CUDA.fill(0.5f0, (W, H, 1, N))                                   # (1,W,H,1) in the reference: same bytes
+    poses = [Pose(CuArray(repeat(Float32[0, 0, 0.01], 1, N)), CUDA.zeros(Float32, 3, 1, N)) for _ in 1:S]   # :9-13
+    loss = CUDA.zeros(Float32, 1)
+    dd, dr, dt = similar(disp), [similar(p.rvec) for p in poses], [similar(p.tvec) for p in poses]
+    history = CUDA.zeros(Float32, iters)
+    io = LossIO(pointer(x), W, H, C, L, N, target_id, S,
+        pad(Int32.(source_ids), MAX_SOURCES, Int32(0)), pad(Int32.(source_ids .< target_id), MAX_SOURCES, Int32(0)),
+        pad(map(p -> pointer(p.rvec), poses), MAX_SOURCES, nullp()), pad(map(p -> pointer(p.tvec), poses), MAX_SOURCES, nullp()),
+        1, pad([pointer(disp)], MAX_SCALES, nullp()), pad(Int32[W], MAX_SCALES, Int32(0)), pad(Int32[H], MAX_SCALES, Int32(0)),
+        pad(Cfloat[1], MAX_SCALES, 0f0), nullp(), k9(Ks), k9(invKs), pointer(loss),
+        pad([pointer(dd)], MAX_SCALES, nullp()), pad(map(pointer, dr), MAX_SOURCES, nullp()),
+        pad(map(pointer, dt), MAX_SOURCES, nullp()), nullp())
+    p = LossParams(min_depth, max_depth, 1e-3, 0.85f0, Cfloat(ssim.c1), Cfloat(ssim.c2), Int32(0),
+        Int32(0), Int32(1), Int32(1), Int32(0))                             # un-normalised, weight 1  (:39)
+    adam = AdamParams(3e-4, 0.9, 0.999, 1e-8)                               # ADAM(3e-4)              (:16)
+    ws = CuArray{UInt8}(undef, ccall((:mdb_train_loss_workspace_bytes, libmdb200), Csize_t, (Ref{LossIO},), io))
+    state = CUDA.zeros(UInt8, ccall((:mdb_slow_depth_state_bytes, libmdb200), Csize_t, (Ref{LossIO},), io))
+    plan = Ref{Ptr{Cvoid}}(C_NULL)
+    GC.@preserve x disp poses loss dd dr dt history ws state begin
+        check(ccall((:mdb_slow_depth_create, libmdb200), Int32,
+            (Ptr{Cvoid}, Ref{LossIO}, Ref{LossParams}, Ref{AdamParams}, CuPtr{Cvoid}, Csize_t, CuPtr{Cvoid}, Csize_t,
+             CuPtr{Cfloat}, Int32, Ptr{Ptr{Cvoid}}),
+            handle(), io, p, adam, state, sizeof(state), ws, sizeof(ws), history, Int32(iters), plan))
+        done = 0
+        while done < iters
+            nxt = done == 0 ? 1 : min(iters, (done ÷ log_step + 1) * log_step)          # :23
+            check(ccall((:mdb_slow_depth_run, libmdb200), Int32, (Ptr{Cvoid}, Int32, Ptr{Cvoid}),
+                plan[], Int32(nxt - done), stream_ptr()))
+            done = nxt
+            save_disparity(reshape(cpu(disp), (W, H)), joinpath(log_dir, "d-$done.png"))   # :45-47
+            println(done, " ", mean(disp))                                                  # :55
+        end
+        ccall((:mdb_slow_depth_destroy, libmdb200), Int32, (Ptr{Cvoid},), plan[])
+    end
+    disp, poses, Array(history)
+end
+
 end # module

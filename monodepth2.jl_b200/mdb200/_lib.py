@@ -48,6 +48,11 @@ class LossIO(C.Structure):
     ]
 
 
+class AdamParams(C.Structure):
+    """mdb_adam_params (Flux ADAM defaults; eta from src/simple_depth.jl:16)."""
+    _fields_ = [("eta", C.c_double), ("beta1", C.c_double), ("beta2", C.c_double), ("eps", C.c_double)]
+
+
 def _load() -> C.CDLL:
     if not os.path.exists(LIB_PATH):
         raise ImportError(
@@ -103,6 +108,13 @@ PROTOTYPES = {
                                             _vp, _vp, _vp, _vp, _sz, _vp]),
     "mdb_render_tgt_rgb_depth_bwd": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, c_f32p, c_f32p, _i32, _i32, _i32, _i32,
                                             _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "mdb_adam_update": (_i32, [_vp, _i32, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp),
+                               C.POINTER(_i64), C.POINTER(AdamParams), _vp, _vp, _vp, _vp, _i32, _vp]),
+    "mdb_slow_depth_state_bytes": (_sz, [C.POINTER(LossIO)]),
+    "mdb_slow_depth_create": (_i32, [_vp, C.POINTER(LossIO), C.POINTER(LossParams), C.POINTER(AdamParams), _vp, _sz,
+                                     _vp, _sz, _vp, _i32, C.POINTER(_vp)]),
+    "mdb_slow_depth_run": (_i32, [_vp, _i32, _vp]),
+    "mdb_slow_depth_destroy": (_i32, [_vp]),
 }
 
 

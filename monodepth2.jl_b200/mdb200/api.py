@@ -447,6 +447,150 @@ def simple_depth_plan(x: torch.Tensor, K, invK, *, target_id: int = 2, source_id
 
 
 # --------------------------------------------------------------------------------------
+# the optimiser loop of slow_depth, resident on the device
+# --------------------------------------------------------------------------------------
+class ADAM:
+    """`Flux.Optimise.ADAM(eta, (beta1, beta2))` -- the optimiser of src/simple_depth.jl:16.
+    `update(params, grads)` is `Flux.Optimise.update!(opt, params, grads)` in one kernel launch for the
+    whole parameter list; the step counter lives on the device."""
+
+    def __init__(self, eta: float = 1e-3, beta=(0.9, 0.999), eps: float = 1e-8):
+        self.p = _lib.AdamParams(float(eta), float(beta[0]), float(beta[1]), float(eps))
+        self.state = None
+
+    def update(self, params: Sequence[torch.Tensor], grads: Sequence[torch.Tensor]):
+        n = len(params)
+        for t, g in zip(params, grads):
+            _chk(t, "param"); _chk(g, "grad")
+            if t.numel() != g.numel():
+                raise ValueError("parameter / gradient size mismatch")
+        if self.state is None:
+            dev = params[0].device
+            self.state = dict(m=[torch.zeros_like(t) for t in params], v=[torch.zeros_like(t) for t in params],
+                              counters=torch.zeros(2, dtype=torch.int32, device=dev))
+        st = self.state
+        arr = lambda ts: (ct.c_void_p * n)(*[t.data_ptr() for t in ts])
+        sizes = (ct.c_int64 * n)(*[t.numel() for t in params])
+        h = handle()
+        c = st["counters"]
+        check(h, lib.mdb_adam_update(h, n, arr(params), arr(grads), arr(st["m"]), arr(st["v"]), sizes, ct.byref(self.p),
+                                     c.data_ptr(), c.data_ptr() + 4, None, None, 0, _stream()))
+
+    @property
+    def step(self) -> int:
+        return 0 if self.state is None else int(self.state["counters"][0])
+
+
+class SlowDepth:
+    """The loop of `slow_depth` (src/simple_depth.jl:1-62): parameters `disp (1,W,H,1)` = 0.5, one
+    `Pose([0,0,0.01], 0)` per source (:8-13), ADAM(3e-4) (:16), and per iteration the gradient of
+    `mean(prediction_loss(warp(...))) + smooth_loss(disp, target)` (:25-41) followed by `update!` (:42).
+    One iteration is a CUDA graph built once; `run(iters)` replays it with no host round trip.
+    The reference's logging every 5 iterations (:44-60) is the caller's business: call `run(5)` and
+    read `disp` / `poses` between the calls."""
+
+    def __init__(self, x: torch.Tensor, K, invK, *, target_id: int = 2, source_ids: Sequence[int] = (1, 3),
+                 min_depth: float = 0.1, max_depth: float = 100.0, eta: float = 3e-4, max_iters: int = 500,
+                 disp0: float = 0.5, rvec0=(0.0, 0.0, 0.01)):
+        _chk(x, "x")
+        N, L, Cc, H, W = x.shape
+        self.x = x
+        dev = x.device
+        f32 = dict(device=dev, dtype=torch.float32)
+        self.plan = simple_depth_plan(x, K, invK, target_id=target_id, source_ids=source_ids,
+                                      min_depth=min_depth, max_depth=max_depth)
+        S = self.plan.S
+        self.disp = torch.full((N, 1, H, W), float(disp0), **f32)
+        self.poses = [Pose(torch.tensor([list(rvec0)] * N, **f32), torch.zeros((N, 1, 3), **f32)) for _ in range(S)]
+        self.loss_history = torch.zeros(max_iters, **f32)
+        io = self.plan.io
+        io.x = x.data_ptr()
+        io.disparity[0] = self.disp.data_ptr()
+        for s, pz in enumerate(self.poses):
+            io.rvec[s], io.tvec[s] = pz.rvec.data_ptr(), pz.tvec.data_ptr()
+        io.auto_loss = None
+        self.adam = _lib.AdamParams(float(eta), 0.9, 0.999, 1e-8)
+        nbytes = int(lib.mdb_slow_depth_state_bytes(ct.byref(io)))
+        self.state = torch.zeros(nbytes, dtype=torch.uint8, device=dev)
+        self._h = ct.c_void_p()
+        h = handle()
+        check(h, lib.mdb_slow_depth_create(h, ct.byref(io), ct.byref(self.plan.params), ct.byref(self.adam),
+                                           _p(self.state), nbytes, _p(self.plan.ws), self.plan.ws_bytes,
+                                           _p(self.loss_history), max_iters, ct.byref(self._h)))
+        self.iters_done = 0
+
+    def run(self, iters: int) -> None:
+        check(handle(), lib.mdb_slow_depth_run(self._h, int(iters), _stream()))
+        self.iters_done += int(iters)
+
+    def parameters(self) -> List[torch.Tensor]:
+        """theta in the order of the optimiser state: disp, then (rvec, tvec) per source."""
+        return [self.disp] + [t for pz in self.poses for t in (pz.rvec, pz.tvec)]
+
+    def _state_views(self):
+        """(m, v) float32 views into the state buffer per parameter, and the int32 [step, ticket] pair
+        (layout of mdb_slow_depth_create: per tensor m then v, counters at the next 256-byte boundary)."""
+        f = self.state.view(torch.float32)
+        off, ms, vs = 0, [], []
+        for t in self.parameters():
+            n = t.numel()
+            ms.append(f[off:off + n].view(t.shape)); vs.append(f[off + n:off + 2 * n].view(t.shape))
+            off += 2 * n
+        c = (off * 4 + 255) // 256 * 256
+        return ms, vs, self.state[c:c + 8].view(torch.int32)
+
+    def load_state(self, params: Sequence[torch.Tensor], m: Sequence[torch.Tensor], v: Sequence[torch.Tensor], step: int):
+        """Resume from a checkpoint of (theta, ADAM moments, step count)."""
+        ms, vs, counters = self._state_views()
+        for dst, src in zip(self.parameters() + ms + vs, list(params) + list(m) + list(v)):
+            dst.copy_(src.to(dst.device, torch.float32).reshape(dst.shape))
+        counters[0] = int(step)
+        counters[1] = 0
+        self.iters_done = int(step)
+
+    @property
+    def loss(self) -> torch.Tensor:
+        return self.plan.loss
+
+    def close(self) -> None:
+        if self._h:
+            lib.mdb_slow_depth_destroy(self._h)
+            self._h = ct.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def slow_depth(x: torch.Tensor, ssim=None, backprojections=None, projections=None, invKs=None, Ks=None,
+               transfer=None, *, target_id: int, source_ids: Sequence[int], min_depth: float, max_depth: float,
+               log_dir: Optional[str] = None, iters: int = 500, log_step: int = 5, on_log: Optional[Callable] = None):
+    """`slow_depth(x, ssim, backprojections, projections, invKs, Ks, transfer; target_id, source_ids,
+    min_depth, max_depth, log_dir)` -- src/simple_depth.jl:1-62, same argument list (`ssim`,
+    `backprojections`, `projections`, `transfer` are accepted and unused: the fused kernels carry
+    them).  `on_log(iter, disp, poses, loss)` replaces the PNG / println block (:44-60) and, when given,
+    is called at iteration 1 and every `log_step` iterations like the reference.  Returns
+    (disp, poses, loss_history)."""
+    sd = SlowDepth(x, Ks, invKs, target_id=target_id, source_ids=source_ids, min_depth=min_depth,
+                   max_depth=max_depth, max_iters=iters)
+    if on_log is None:
+        sd.run(iters)
+    else:
+        done = 0
+        while done < iters:
+            nxt = 1 if done == 0 else min(iters, (done // log_step + 1) * log_step)
+            sd.run(nxt - done)
+            done = nxt
+            on_log(done, sd.disp, sd.poses, sd.loss)
+    out = (sd.disp, sd.poses, sd.loss_history[:iters])
+    torch.cuda.current_stream().synchronize()
+    sd.close()
+    return out
+
+
+# --------------------------------------------------------------------------------------
 # host-buffer entry: the call a user with HOST arrays makes (bench "e2e")
 # --------------------------------------------------------------------------------------
 @dataclass

@@ -397,3 +397,45 @@ def render_tgt_rgb_depth(rgb, sigma, disparity_src, xyz_tgt, pose: Pose, K_inv, 
     rgb_o, depth, _ = plane_volume_rendering(rgb_s, sigma_s, xyz_s.permute(0, 1, 3, 4, 2))
     mask = valid.sum(dim=1, keepdim=True).unsqueeze(1).to(torch.int64)  # (B,1,1,H,W)
     return rgb_o, depth, mask
+
+
+# --------------------------------------------------------------------------------------
+# the optimiser loop of slow_depth -- src/simple_depth.jl:8-42  
+# --------------------------------------------------------------------------------------
+def flux_adam_step(params, grads, state, eta: float = 3e-4, beta=(0.9, 0.999), eps: float = 1e-8):
+    """`Flux.Optimise.update!(ADAM(eta, beta), params, grads)` (third-party Flux.jl <= 0.13,
+    `apply!(o::ADAM, x, Δ)`; unpinned): mt = b1 mt + (1-b1) Δ; vt = b2 vt + (1-b2) Δ^2;
+    Δ' = mt / (1 - b1^t) / (sqrt(vt / (1 - b2^t)) + eps) * eta; x .-= Δ'.  `state` is a dict that
+    this function fills on first use.  In place on `params`."""
+    if not state:
+        state.update(m=[torch.zeros_like(p) for p in params], v=[torch.zeros_like(p) for p in params], t=0)
+    state["t"] += 1
+    t = state["t"]
+    for p, g, m, v in zip(params, grads, state["m"], state["v"]):
+        m.mul_(beta[0]).add_(g, alpha=1 - beta[0])
+        v.mul_(beta[1]).addcmul_(g, g, value=1 - beta[1])
+        p.sub_(m / (1 - beta[0] ** t) / (torch.sqrt(v / (1 - beta[1] ** t)) + eps) * eta)
+
+
+def slow_depth(x: torch.Tensor, K: torch.Tensor, invK: torch.Tensor, *, iters: int, target_id: int = 2,
+               source_ids: Sequence[int] = (1, 3), min_depth: float = 0.1, max_depth: float = 100.0,
+               eta: float = 3e-4):
+    """`slow_depth` -- src/simple_depth.jl:1-62 without its logging.  x (N,L,C,H,W).
+    Returns (disp (N,1,H,W), poses, [loss per iteration])."""
+    n, _, _, h, w = x.shape
+    dt = x.dtype
+    disp = torch.full((n, 1, h, w), 0.5, dtype=dt)                                   # :8
+    poses = [Pose(torch.tensor([[0.0, 0.0, 0.01]] * n, dtype=dt), torch.zeros(n, 1, 3, dtype=dt))
+             for _ in source_ids]                                                    # :9-13
+    state, hist = {}, []
+    for _ in range(iters):                                                           # :22
+        leaves = [disp.requires_grad_()] + [t.requires_grad_() for p in poses for t in (p.rvec, p.tvec)]
+        loss = simple_depth_loss(x, disp.reshape(n, h, w, 1), poses, K, invK, target_id=target_id,
+                                 source_ids=source_ids, min_depth=min_depth, max_depth=max_depth)   # :25-41
+        grads = torch.autograd.grad(loss, leaves)
+        hist.append(float(loss.detach()))
+        with torch.no_grad():
+            for t in leaves:
+                t.requires_grad_(False)
+            flux_adam_step(leaves, grads, state, eta=eta)                            # :42
+    return disp, poses, hist

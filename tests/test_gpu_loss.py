@@ -176,6 +176,11 @@ def test_forced_row_segments(monkeypatch):
     _compare(inp, ref, res3)
     for a, b in zip(res1.d_disparities, res3.d_disparities):
         assert torch.allclose(a, b, rtol=1e-5, atol=1e-9)
+    # 4-row and 2-row segments (what small problems get so that one wave fills the machine)
+    for segs in ("24", "48"):
+        monkeypatch.setenv("MDB_STRIP_SEGS", segs)
+        resn, _ = _run_gpu(inp, auto=ref["auto"])
+        _compare(inp, ref, resn)
 
 
 @pytest.mark.parametrize("C", [1, 3])
