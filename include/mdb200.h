@@ -270,6 +270,16 @@ int32_t mdb_slow_depth_create(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
 int32_t mdb_slow_depth_run(mdb_slow_depth_plan* plan, int32_t iters, void* stream);
 int32_t mdb_slow_depth_destroy(mdb_slow_depth_plan* plan);
 
+/* ---- input ingestion  (src/dtk.jl:29-46) ---------------------------------------
+ * Depth10k's `getindex`: one decoded image holds the three frames side by side.  `strips` is the decoder's
+ * raster, uint8 row-major [N][H][3W][3] (R,G,B interleaved), DEVICE memory; `flip` is NULL or N bytes
+ * (non-zero = FlipX applied to that sample: the width axis of all three frames reversed, Augmentations.jl,
+ * third-party).  Writes x (W,H,C,3,N) Float32 = value/255 (C = 3), or Gray{Float32} luma
+ * 0.299 r + 0.587 g + 0.114 b (C = 1, `grayscale` != 0; Colors.jl, third-party).  Bit-exact against the
+ * numpy restatement oracle/ingest_ref.py.                                                          */
+int32_t mdb_ingest_triplet_u8(mdb_handle* h, const uint8_t* strips, const uint8_t* flip, int32_t W, int32_t H,
+                              int32_t N, int32_t grayscale, float* x, void* stream);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

@@ -115,6 +115,7 @@ PROTOTYPES = {
                                      _vp, _sz, _vp, _i32, C.POINTER(_vp)]),
     "mdb_slow_depth_run": (_i32, [_vp, _i32, _vp]),
     "mdb_slow_depth_destroy": (_i32, [_vp]),
+    "mdb_ingest_triplet_u8": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp]),
 }
 
 

@@ -591,6 +591,31 @@ def slow_depth(x: torch.Tensor, ssim=None, backprojections=None, projections=Non
 
 
 # --------------------------------------------------------------------------------------
+# ingestion of the dataset's own format
+# --------------------------------------------------------------------------------------
+def ingest_triplet_u8(strips: torch.Tensor, width: int, flips: Optional[torch.Tensor] = None, grayscale: bool = False,
+                      out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """`Depth10k.getindex` for a batch, on the device (src/dtk.jl:29-46): strips uint8 (N,H,3W,3) decoded
+    rasters -> x float32 (N,3,C,H,W) [Julia (W,H,C,3,N)]; `flips` uint8 (N,) marks samples FlipX applies to."""
+    if strips.dtype != torch.uint8 or not strips.is_cuda or not strips.is_contiguous():
+        raise ValueError("strips must be a contiguous CUDA uint8 tensor (N,H,3W,3)")
+    N, H, W3, ch = strips.shape
+    if ch != 3 or W3 != 3 * width:
+        raise ValueError(f"strips has shape {tuple(strips.shape)}, expected (N,H,{3 * width},3)")
+    if flips is not None and (flips.dtype != torch.uint8 or not flips.is_cuda or flips.numel() != N):
+        raise ValueError("flips must be a CUDA uint8 tensor of N entries")
+    C = 1 if grayscale else 3
+    if out is None:
+        out = torch.empty((N, 3, C, H, width), device=strips.device, dtype=torch.float32)
+    elif tuple(out.shape) != (N, 3, C, H, width):
+        raise ValueError("out has the wrong shape")
+    _chk(out, "out")
+    h = handle()
+    check(h, lib.mdb_ingest_triplet_u8(h, _p(strips), _p(flips), width, H, N, int(grayscale), _p(out), _stream()))
+    return out
+
+
+# --------------------------------------------------------------------------------------
 # host-buffer entry: the call a user with HOST arrays makes (bench "e2e")
 # --------------------------------------------------------------------------------------
 @dataclass
@@ -611,7 +636,15 @@ class HostLoss:
     contract the multi-GPU shards use, so chunk losses simply add."""
 
     def __init__(self, *, W, H, C, L, N, disp_sizes, scales, target_id, source_ids, K, invK, chunk=8,
-                 automasking=False, n_global=0, device=None, **kw):
+                 automasking=False, n_global=0, device=None, x_format="f32", **kw):
+        """x_format "f32": x is the Float32 (N,L,C,H,W) stack.  "u8_strip": x is the dataset's own format,
+        uint8 (N,H,3W,3) decoded triplet strips (src/dtk.jl:29-46) -- a quarter of the PCIe bytes; the
+        device converts with mdb_ingest_triplet_u8 (C = 1: Gray luma)."""
+        if x_format not in ("f32", "u8_strip"):
+            raise ValueError("x_format must be 'f32' or 'u8_strip'")
+        if x_format == "u8_strip" and L != 3:
+            raise ValueError("triplet strips hold L = 3 frames")
+        self.x_format = x_format
         self.dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         self.N, self.L, self.C, self.H, self.W = N, L, C, H, W
         self.S = len(source_ids)
@@ -633,23 +666,34 @@ class HostLoss:
                 self.dr.append([torch.empty((n, 3), **f32) for _ in range(self.S)])
                 self.dt.append([torch.empty((n, 1, 3), **f32) for _ in range(self.S)])
                 self.da.append(torch.empty((n, 1, H, W), **f32) if automasking else None)
+            self.du8 = [torch.empty((b - a, H, 3 * W, 3), device=self.dev, dtype=torch.uint8) for (a, b) in self.chunks] \
+                if x_format == "u8_strip" else None
+            self.dflip = [torch.zeros((b - a,), device=self.dev, dtype=torch.uint8) for (a, b) in self.chunks] \
+                if x_format == "u8_strip" else None
         pin = dict(dtype=torch.float32, pin_memory=True)
         self.h_loss = torch.empty((len(self.chunks),), **pin)
         self.h_dd = [torch.empty((N, 1, h, w), **pin) for (w, h) in self.disp_sizes]
         self.h_dr = [torch.empty((N, 3), **pin) for _ in range(self.S)]
         self.h_dt = [torch.empty((N, 1, 3), **pin) for _ in range(self.S)]
-        self.h2d_bytes = 4 * (N * L * C * H * W + sum(N * w * h for (w, h) in self.disp_sizes) + 6 * N * self.S
-                              + (N * H * W if automasking else 0))
+        x_bytes = 4 * N * L * C * H * W if x_format == "f32" else N * H * 3 * W * 3 + N
+        self.h2d_bytes = x_bytes + 4 * (sum(N * w * h for (w, h) in self.disp_sizes) + 6 * N * self.S
+                                        + (N * H * W if automasking else 0))
         self.d2h_bytes = 4 * (len(self.chunks) + sum(N * w * h for (w, h) in self.disp_sizes) + 6 * N * self.S)
 
-    def __call__(self, x, disparities, rvecs, tvecs, auto_loss=None) -> HostLossResult:
-        """All arguments are HOST float32 tensors (pinned for full PCIe rate)."""
+    def __call__(self, x, disparities, rvecs, tvecs, auto_loss=None, flips=None) -> HostLossResult:
+        """All arguments are HOST tensors (pinned for full PCIe rate): float32, except x in the
+        "u8_strip" format (uint8 (N,H,3W,3)) and its optional `flips` (uint8 (N,), FlipX per sample)."""
         compute = torch.cuda.current_stream(self.dev)
         self.copy_in.wait_stream(compute)
         self.copy_out.wait_stream(compute)
         for k, (a, b) in enumerate(self.chunks):
             with torch.cuda.stream(self.copy_in):
-                self.dx[k].copy_(x[a:b], non_blocking=True)
+                if self.x_format == "f32":
+                    self.dx[k].copy_(x[a:b], non_blocking=True)
+                else:
+                    self.du8[k].copy_(x[a:b], non_blocking=True)
+                    if flips is not None:
+                        self.dflip[k].copy_(flips[a:b], non_blocking=True)
                 for j, d in enumerate(disparities):
                     self.dd[k][j].copy_(d[a:b], non_blocking=True)
                 for s in range(self.S):
@@ -659,6 +703,9 @@ class HostLoss:
                     self.da[k].copy_(auto_loss[a:b], non_blocking=True)
                 ready = self.copy_in.record_event()
             compute.wait_event(ready)
+            if self.x_format == "u8_strip":
+                ingest_triplet_u8(self.du8[k], self.W, self.dflip[k] if flips is not None else None,
+                                  grayscale=(self.C == 1), out=self.dx[k])
             res = self.plans[k](self.dx[k], self.dd[k], [Pose(r, t) for r, t in zip(self.dr[k], self.dt[k])], self.da[k])
             done = compute.record_event()
             with torch.cuda.stream(self.copy_out):
@@ -674,10 +721,10 @@ class HostLoss:
         return HostLossResult(float(self.h_loss.sum()), self.h_dd, self.h_dr, self.h_dt)
 
 
-def train_loss_host(plan: HostLoss, x, disparities, poses: Sequence[Pose], auto_loss=None) -> HostLossResult:
+def train_loss_host(plan: HostLoss, x, disparities, poses: Sequence[Pose], auto_loss=None, flips=None) -> HostLossResult:
     """Public host-buffer call: `train_loss` (src/training.jl:21-78) value + gradients for HOST
-    inputs; `plan` is a HostLoss built once for the shapes."""
-    return plan(x, disparities, [p.rvec for p in poses], [p.tvec for p in poses], auto_loss)
+    inputs; `plan` is a HostLoss built once for the shapes (and for the format of `x`)."""
+    return plan(x, disparities, [p.rvec for p in poses], [p.tvec for p in poses], auto_loss, flips)
 
 
 # --------------------------------------------------------------------------------------

@@ -173,3 +173,12 @@ def make_render_inputs(W: int = 416, H: int = 128, Np: int = 32, B: int = 2, see
     return RenderInputs(W=W, H=H, Np=Np, B=B, rgb=rgb, sigma=sigma, disparity_src=disp,
                         xyz_tgt=xyz_tgt.astype(np.float32), rvec=rvec, tvec=tvec,
                         K=K.astype(np.float32), K_inv=K_inv.astype(np.float32))
+
+
+def to_u8_strips(x: np.ndarray) -> np.ndarray:
+    """Float frame stacks (N,3,3,H,W) in [0,1] -> the dataset's own format: uint8 decoded triplet strips
+    (N,H,3W,3), the three frames side by side (src/dtk.jl:29-36).  Quantises to 8 bits."""
+    n, l, c, h, w = x.shape
+    assert l == 3 and c == 3
+    q = np.clip(np.rint(x * 255.0), 0, 255).astype(np.uint8)          # (N,L,C,H,W)
+    return np.ascontiguousarray(q.transpose(0, 3, 1, 4, 2).reshape(n, h, 3 * w, 3))

@@ -1,0 +1,75 @@
+"""sample ingestion (src/dtk.jl:29-46).  CPU part: the numpy restatement on
+hand-checkable inputs.  GPU part: mdb_ingest_triplet_u8 is bit-exact against it, and the host-buffer loss
+fed uint8 strips equals the one fed the Float32 stack the oracle makes of the same strips."""
+import numpy as np
+import pytest
+import torch
+
+from mdb200 import synth
+from oracle import ingest_ref as I
+
+DEV = "cuda:0"
+
+
+def test_oracle_layout_and_values():
+    W, H = 4, 2
+    strip = np.arange(H * 3 * W * 3, dtype=np.uint8).reshape(H, 3 * W, 3)
+    out = I.depth10k_getindex(strip, W)
+    assert out.shape == (3, 3, H, W) and out.dtype == np.float32
+    # frame j, channel c, row h, column w  <-  strip[h, j W + w, c] / 255
+    assert out[2, 1, 1, 3] == np.float32(strip[1, 2 * W + 3, 1]) / np.float32(255)
+    fl = I.depth10k_getindex(strip, W, flip=True)
+    assert np.array_equal(fl, out[..., ::-1])
+    g = I.depth10k_getindex(strip, W, grayscale=True)
+    r, gg, b = (np.float32(v) / np.float32(255) for v in strip[0, 5])
+    assert g.shape == (3, 1, H, W)
+    assert g[1, 0, 0, 1] == (np.float32(0.299) * r + np.float32(0.587) * gg) + np.float32(0.114) * b
+    assert I.n0f8_to_f32(np.array([255], dtype=np.uint8))[0] == 1.0
+
+
+def test_synth_strips_round_trip():
+    inp = synth.make_loss_inputs(24, 10, 2, seed=5)
+    s = synth.to_u8_strips(inp.x)
+    back = I.batch(s, 24)
+    assert back.shape == inp.x.shape and np.abs(back - inp.x).max() <= 0.5 / 255 + 1e-6
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("W,H,N,gray", [(416, 128, 3, False), (416, 128, 2, True), (13, 7, 4, False), (1, 1, 1, True),
+                                        (1024, 320, 2, False)])
+def test_ingest_bit_exact(W, H, N, gray):
+    import mdb200
+    rng = np.random.default_rng(W * 7 + H)
+    strips = rng.integers(0, 256, size=(N, H, 3 * W, 3), dtype=np.uint8)
+    flips = (rng.random(N) < 0.5).astype(np.uint8)
+    flips[0] = 1
+    ref = I.batch(strips, W, flips, grayscale=gray)
+    got = mdb200.ingest_triplet_u8(torch.tensor(strips, device=DEV), W, torch.tensor(flips, device=DEV), grayscale=gray)
+    assert np.array_equal(got.cpu().numpy(), ref)                      # bit-exact
+    got2 = mdb200.ingest_triplet_u8(torch.tensor(strips, device=DEV), W, None, grayscale=gray)
+    assert np.array_equal(got2.cpu().numpy(), I.batch(strips, W, None, grayscale=gray))
+    # an unaligned base pointer takes the byte path
+    pad = torch.zeros(strips.size + 3, dtype=torch.uint8, device=DEV)
+    pad[3:] = torch.tensor(strips, device=DEV).reshape(-1)
+    got3 = mdb200.ingest_triplet_u8(pad[3:].view(N, H, 3 * W, 3), W, torch.tensor(flips, device=DEV), grayscale=gray)
+    assert np.array_equal(got3.cpu().numpy(), ref)
+
+
+@pytest.mark.gpu
+def test_host_loss_from_u8_strips_matches_f32_path():
+    import mdb200
+    inp = synth.make_loss_inputs(104, 32, 5, seed=9)
+    strips = synth.to_u8_strips(inp.x)
+    flips = np.array([0, 1, 0, 1, 1], dtype=np.uint8)
+    x_ref = I.batch(strips, inp.W, flips)
+    kw = dict(W=inp.W, H=inp.H, C=3, L=3, N=inp.N, disp_sizes=[(d.shape[-1], d.shape[-2]) for d in inp.disparities],
+              scales=inp.scales, target_id=2, source_ids=[1, 3], K=inp.K, invK=inp.invK, chunk=2)
+    pin = lambda a: torch.tensor(a).pin_memory()
+    d, r, t = [pin(a) for a in inp.disparities], [pin(a) for a in inp.rvecs], [pin(a) for a in inp.tvecs]
+    a = mdb200.HostLoss(**kw)(pin(x_ref), d, r, t)
+    b = mdb200.HostLoss(x_format="u8_strip", **kw)(pin(strips), d, r, t, flips=pin(flips))
+    assert a.loss == b.loss
+    for u, v in zip(a.d_disparities + a.d_rvec + a.d_tvec, b.d_disparities + b.d_rvec + b.d_tvec):
+        assert torch.equal(u, v)
+    plan = mdb200.HostLoss(x_format="u8_strip", **kw)
+    assert plan.h2d_bytes < mdb200.HostLoss(**kw).h2d_bytes * 0.45
