@@ -150,6 +150,12 @@ def cpu_reference_rate(inp, items, steps, warmup):
         c_ref.train_loss(*a, **kw)
         ts.append(time.perf_counter() - t0)
     t = sum(ts) / len(ts)
+    # one item on one thread (the closest stand-in for the reference's single-threaded CPU broadcasts)
+    a1 = (inp.x[:1], [d[:1] for d in inp.disparities], [r[:1] for r in inp.rvecs], [t_[:1] for t_ in inp.tvecs], None, inp.K, inp.invK)
+    kw1 = dict(kw); kw1["threads"] = 1
+    t0 = time.perf_counter()
+    c_ref.train_loss(*a1, **kw1)
+    cpu_reference_rate.one_thread = (units / items) / (time.perf_counter() - t0)
     return units / t, threads, t, items
 
 
@@ -170,7 +176,8 @@ def run_reference(args):
         "steps": steps, "warmup": warm, "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.config}: {inp.W}x{inp.H}, CPU sample of {items} items", "timing": "host wall clock"},
-        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+                         "one_thread_value": cpu_reference_rate.one_thread},
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -339,6 +346,7 @@ def run_ours(args):
         if not args.no_cpu_baseline and world == 1:
             rate, cores, t, items = cpu_reference_rate(inp, args.cpu_sample_items, 3, 1)
             line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
+                                    "one_thread_value": cpu_reference_rate.one_thread,
                                     "sample": f"{items} of the batch's {N} items, 3 steps after 1 warm-up, plain-C float32 port "
                                               f"(oracle/c_port), one item per thread, {cores} threads ({t:.2f} s/step)"}
         print(json.dumps(line), flush=True)
