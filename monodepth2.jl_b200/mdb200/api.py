@@ -313,7 +313,11 @@ class FusedLoss:
                  scales: Sequence[float], target_id: int, source_ids: Sequence[int], K, invK,
                  min_depth: float = 0.1, max_depth: float = 100.0, disparity_smoothness: float = 1e-3,
                  automasking: bool = False, normalize_disparity: bool = True, smooth_weight_mode: int = 0,
-                 n_global: int = 0, alpha: float = 0.85, want_vis: bool = False, device=None):
+                 n_global: int = 0, alpha: float = 0.85, want_vis: bool = False, device=None,
+                 out: Optional[dict] = None):
+        """`out` (optional): caller-provided output tensors {"loss": 0-dim or 1-element, "d_disp": [...],
+        "d_rvec": [...], "d_tvec": [...]} of the right shapes -- e.g. row slices of whole-batch tensors --
+        instead of buffers owned by the plan."""
         self.dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         self.shape = (N, L, C, H, W)
         self.disp_sizes = [(int(w), int(h)) for (w, h) in disp_sizes]
@@ -342,10 +346,20 @@ class FusedLoss:
             io.K[i], io.invK[i] = kk[i], ik[i]
         self.io = io
         f32 = dict(device=self.dev, dtype=torch.float32)
-        self.loss = torch.zeros((), **f32)
-        self.d_disp = [torch.empty((N, 1, h, w), **f32) for (w, h) in self.disp_sizes]
-        self.d_rvec = [torch.empty((N, 3), **f32) for _ in range(self.S)]
-        self.d_tvec = [torch.empty((N, 1, 3), **f32) for _ in range(self.S)]
+        if out is None:
+            self.loss = torch.zeros((), **f32)
+            self.d_disp = [torch.empty((N, 1, h, w), **f32) for (w, h) in self.disp_sizes]
+            self.d_rvec = [torch.empty((N, 3), **f32) for _ in range(self.S)]
+            self.d_tvec = [torch.empty((N, 1, 3), **f32) for _ in range(self.S)]
+        else:
+            self.loss, self.d_disp, self.d_rvec, self.d_tvec = out["loss"], list(out["d_disp"]), list(out["d_rvec"]), list(out["d_tvec"])
+            for t, shp in [(self.loss, None)] + [(t, (N, 1, h, w)) for t, (w, h) in zip(self.d_disp, self.disp_sizes)] + \
+                    [(t, (N, 3)) for t in self.d_rvec] + [(t, (N, 1, 3)) for t in self.d_tvec]:
+                _chk(t, "out")
+                if shp is not None and tuple(t.shape) != shp:
+                    raise ValueError(f"output buffer has shape {tuple(t.shape)}, expected {shp}")
+            if self.loss.numel() != 1:
+                raise ValueError("out['loss'] must hold one float")
         self.vis = torch.empty((N, 1, H, W), **f32) if want_vis else None
         io.loss = self.loss.data_ptr()
         for k in range(self.Ls):
@@ -650,26 +664,44 @@ class HostLoss:
         self.S = len(source_ids)
         self.disp_sizes = [(int(w), int(h)) for (w, h) in disp_sizes]
         self.automasking = automasking
-        self.chunks = [(s, min(s + chunk, N)) for s in range(0, N, chunk)]
+        # Pipeline shape.  The step is bound by the host->device copy, so compute always finishes a chunk
+        # before the next one has arrived; what is NOT hidden is the work on the LAST chunk after its copy
+        # lands.  Hence chunks of `chunk` items and a geometric tail (half, quarter, ... down to 1 item).
+        sizes, left = [], N
+        while left > chunk:
+            sizes.append(chunk); left -= chunk
+        while left > 1:
+            half = (left + 1) // 2
+            sizes.append(half); left -= half
+        if left == 1:
+            sizes.append(1)
+        self.chunks, s0 = [], 0
+        for z in sizes:
+            self.chunks.append((s0, s0 + z)); s0 += z
         ng = n_global if n_global > 0 else N
         f32 = dict(device=self.dev, dtype=torch.float32)
         with torch.cuda.device(self.dev):
             self.copy_in, self.copy_out = torch.cuda.Stream(), torch.cuda.Stream()
-            self.plans, self.dx, self.dd, self.dr, self.dt, self.da = [], [], [], [], [], []
-            for (a, b) in self.chunks:
-                n = b - a
-                self.plans.append(FusedLoss(W=W, H=H, C=C, L=L, N=n, disp_sizes=disp_sizes, scales=scales,
+            # whole-batch device buffers; every chunk's plan reads and writes row slices of them, so the
+            # per-chunk host work is 1 + Ls copies in, one launch sequence, Ls copies out
+            self.d_x = torch.empty((N, L, C, H, W), **f32)
+            self.d_d = [torch.empty((N, 1, h, w), **f32) for (w, h) in self.disp_sizes]
+            self.d_rv = [torch.empty((N, 3), **f32) for _ in range(self.S)]
+            self.d_tv = [torch.empty((N, 1, 3), **f32) for _ in range(self.S)]
+            self.d_a = torch.empty((N, 1, H, W), **f32) if automasking else None
+            self.g_d = [torch.empty((N, 1, h, w), **f32) for (w, h) in self.disp_sizes]
+            self.g_rv = [torch.empty((N, 3), **f32) for _ in range(self.S)]
+            self.g_tv = [torch.empty((N, 1, 3), **f32) for _ in range(self.S)]
+            self.g_loss = torch.zeros((len(self.chunks),), **f32)
+            self.d_u8 = torch.empty((N, H, 3 * W, 3), device=self.dev, dtype=torch.uint8) if x_format == "u8_strip" else None
+            self.d_flip = torch.zeros((N,), device=self.dev, dtype=torch.uint8) if x_format == "u8_strip" else None
+            self.plans = []
+            for k, (a, b) in enumerate(self.chunks):
+                out = dict(loss=self.g_loss[k:k + 1], d_disp=[t[a:b] for t in self.g_d],
+                           d_rvec=[t[a:b] for t in self.g_rv], d_tvec=[t[a:b] for t in self.g_tv])
+                self.plans.append(FusedLoss(W=W, H=H, C=C, L=L, N=b - a, disp_sizes=disp_sizes, scales=scales,
                                             target_id=target_id, source_ids=source_ids, K=K, invK=invK,
-                                            automasking=automasking, n_global=ng, device=self.dev, **kw))
-                self.dx.append(torch.empty((n, L, C, H, W), **f32))
-                self.dd.append([torch.empty((n, 1, h, w), **f32) for (w, h) in self.disp_sizes])
-                self.dr.append([torch.empty((n, 3), **f32) for _ in range(self.S)])
-                self.dt.append([torch.empty((n, 1, 3), **f32) for _ in range(self.S)])
-                self.da.append(torch.empty((n, 1, H, W), **f32) if automasking else None)
-            self.du8 = [torch.empty((b - a, H, 3 * W, 3), device=self.dev, dtype=torch.uint8) for (a, b) in self.chunks] \
-                if x_format == "u8_strip" else None
-            self.dflip = [torch.zeros((b - a,), device=self.dev, dtype=torch.uint8) for (a, b) in self.chunks] \
-                if x_format == "u8_strip" else None
+                                            automasking=automasking, n_global=ng, device=self.dev, out=out, **kw))
         pin = dict(dtype=torch.float32, pin_memory=True)
         self.h_loss = torch.empty((len(self.chunks),), **pin)
         self.h_dd = [torch.empty((N, 1, h, w), **pin) for (w, h) in self.disp_sizes]
@@ -686,36 +718,38 @@ class HostLoss:
         compute = torch.cuda.current_stream(self.dev)
         self.copy_in.wait_stream(compute)
         self.copy_out.wait_stream(compute)
+        u8 = self.x_format == "u8_strip"
+        with torch.cuda.stream(self.copy_in):     # 6 floats per item and source: whole batch at once
+            for s in range(self.S):
+                self.d_rv[s].copy_(rvecs[s].reshape(self.N, 3), non_blocking=True)
+                self.d_tv[s].copy_(tvecs[s].reshape(self.N, 1, 3), non_blocking=True)
+            if u8 and flips is not None:
+                self.d_flip.copy_(flips, non_blocking=True)
         for k, (a, b) in enumerate(self.chunks):
             with torch.cuda.stream(self.copy_in):
-                if self.x_format == "f32":
-                    self.dx[k].copy_(x[a:b], non_blocking=True)
-                else:
-                    self.du8[k].copy_(x[a:b], non_blocking=True)
-                    if flips is not None:
-                        self.dflip[k].copy_(flips[a:b], non_blocking=True)
+                (self.d_u8 if u8 else self.d_x)[a:b].copy_(x[a:b], non_blocking=True)
                 for j, d in enumerate(disparities):
-                    self.dd[k][j].copy_(d[a:b], non_blocking=True)
-                for s in range(self.S):
-                    self.dr[k][s].copy_(rvecs[s][a:b], non_blocking=True)
-                    self.dt[k][s].copy_(tvecs[s][a:b], non_blocking=True)
+                    self.d_d[j][a:b].copy_(d[a:b], non_blocking=True)
                 if self.automasking:
-                    self.da[k].copy_(auto_loss[a:b], non_blocking=True)
+                    self.d_a[a:b].copy_(auto_loss[a:b], non_blocking=True)
                 ready = self.copy_in.record_event()
             compute.wait_event(ready)
-            if self.x_format == "u8_strip":
-                ingest_triplet_u8(self.du8[k], self.W, self.dflip[k] if flips is not None else None,
-                                  grayscale=(self.C == 1), out=self.dx[k])
-            res = self.plans[k](self.dx[k], self.dd[k], [Pose(r, t) for r, t in zip(self.dr[k], self.dt[k])], self.da[k])
+            if u8:
+                ingest_triplet_u8(self.d_u8[a:b], self.W, self.d_flip[a:b] if flips is not None else None,
+                                  grayscale=(self.C == 1), out=self.d_x[a:b])
+            self.plans[k](self.d_x[a:b], [t[a:b] for t in self.d_d],
+                          [Pose(r[a:b], t[a:b]) for r, t in zip(self.d_rv, self.d_tv)],
+                          self.d_a[a:b] if self.automasking else None)
             done = compute.record_event()
             with torch.cuda.stream(self.copy_out):
                 self.copy_out.wait_event(done)
-                self.h_loss[k:k + 1].copy_(res.loss.reshape(1), non_blocking=True)
                 for j in range(len(self.disp_sizes)):
-                    self.h_dd[j][a:b].copy_(res.d_disparities[j], non_blocking=True)
-                for s in range(self.S):
-                    self.h_dr[s][a:b].copy_(res.d_poses[s].rvec, non_blocking=True)
-                    self.h_dt[s][a:b].copy_(res.d_poses[s].tvec, non_blocking=True)
+                    self.h_dd[j][a:b].copy_(self.g_d[j][a:b], non_blocking=True)
+        with torch.cuda.stream(self.copy_out):    # the small results once, after the last chunk
+            self.h_loss.copy_(self.g_loss, non_blocking=True)
+            for s in range(self.S):
+                self.h_dr[s].copy_(self.g_rv[s], non_blocking=True)
+                self.h_dt[s].copy_(self.g_tv[s], non_blocking=True)
         self.copy_out.synchronize()
         compute.wait_stream(self.copy_out)
         return HostLossResult(float(self.h_loss.sum()), self.h_dd, self.h_dr, self.h_dt)
