@@ -280,6 +280,18 @@ int32_t mdb_slow_depth_destroy(mdb_slow_depth_plan* plan);
 int32_t mdb_ingest_triplet_u8(mdb_handle* h, const uint8_t* strips, const uint8_t* flip, int32_t W, int32_t H,
                               int32_t N, int32_t grayscale, float* x, void* stream);
 
+/* ---- the operators on the network side of the path ---------------------------
+ * PoseDecoder tail (src/pose_decoder.jl:27-32): pose = scale * mean(conv_out (w,h,6,N); dims=(1,2)),
+ * Pose(pose[1:3,1,:], pose[4:6,:,:]) -> rvec (3,N), tvec (3,1,N); scale = 1e-2 in the reference.     */
+int32_t mdb_pose_head(mdb_handle* h, const float* conv_out, int32_t w, int32_t hh, int32_t N, float scale,
+                      float* rvec, float* tvec, void* stream);
+/* its pullback: d_conv_out[w,h,c,n] = scale / (w h) * (c <= 3 ? d_rvec[c,n] : d_tvec[c-3,1,n])        */
+int32_t mdb_pose_head_bwd(mdb_handle* h, const float* d_rvec, const float* d_tvec, int32_t w, int32_t hh,
+                          int32_t N, float scale, float* d_conv_out, void* stream);
+/* per-item mean of a map with `per_item` floats per item (deterministic): the reduction of find_static,
+ * mean(automasking_loss(ssim, x, target; source_ids)) > alpha                    src/dtk.jl:51-69     */
+int32_t mdb_item_mean(mdb_handle* h, const float* map, int64_t per_item, int32_t N, float* out, void* stream);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

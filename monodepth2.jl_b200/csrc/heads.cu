@@ -1,0 +1,97 @@
+// heads.cu -- SURVEY 8(f) rank 4: the small operators on the network side of the path.
+//  * PoseDecoder tail (src/pose_decoder.jl:27-32): spatial mean of the (w,h,6,N) conv output, x 1e-2,
+//    split into Pose(rvec (3,N), tvec (3,1,N)); and its pullback.
+//  * per-item mean of a (W,H,1,N) map: the reduction of `find_static` (src/dtk.jl:51-69),
+//    mean(automasking_loss(ssim, x, target; source_ids)) > alpha.
+// Both are deterministic (fixed-order sums in double).
+#include "mdb_common.cuh"
+
+namespace {
+
+constexpr int HEAD_THREADS = 256;
+
+__device__ double block_sum_d(double v, double* red) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(MDB_FULL, v, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  double s = 0.0;
+  if (threadIdx.x == 0)
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) s += red[w];
+  __syncthreads();
+  return s;   // valid in thread 0
+}
+
+// one block per (channel c of 6, item n): conv_out is [N][6][h][w]
+__global__ void __launch_bounds__(HEAD_THREADS)
+pose_head_kernel(const float* __restrict__ y, int wh, float scale, float* __restrict__ rvec, float* __restrict__ tvec) {
+  __shared__ double red[HEAD_THREADS / 32];
+  const int c = blockIdx.x, n = blockIdx.y;
+  const float* p = y + ((size_t)n * 6 + c) * wh;
+  double acc = 0.0;
+  for (int i = threadIdx.x; i < wh; i += HEAD_THREADS) acc += (double)ldg(p + i);
+  const double s = block_sum_d(acc, red);
+  if (threadIdx.x == 0) {
+    // eltype(T)(1e-2) .* mean(...): the mean is formed first, then scaled, both in Float32 in the reference
+    const float m = (float)(s / (double)wh);
+    const float v = scale * m;
+    if (c < 3) rvec[3 * n + c] = v; else tvec[3 * n + (c - 3)] = v;
+  }
+}
+
+__global__ void pose_head_bwd_kernel(const float* __restrict__ d_rvec, const float* __restrict__ d_tvec, int wh, int N,
+                                     float scale, float* __restrict__ d_y) {
+  const size_t total = (size_t)N * 6 * wh;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int nc = (int)(i / wh), n = nc / 6, c = nc - 6 * n;
+    const float g = c < 3 ? d_rvec[3 * n + c] : d_tvec[3 * n + (c - 3)];
+    d_y[i] = g * scale / (float)wh;
+  }
+}
+
+__global__ void __launch_bounds__(HEAD_THREADS)
+item_mean_kernel(const float* __restrict__ map, long long per_item, float* __restrict__ out) {
+  __shared__ double red[HEAD_THREADS / 32];
+  const float* p = map + (size_t)blockIdx.x * per_item;
+  double acc = 0.0;
+  for (long long i = threadIdx.x; i < per_item; i += HEAD_THREADS) acc += (double)ldg(p + i);
+  const double s = block_sum_d(acc, red);
+  if (threadIdx.x == 0) out[blockIdx.x] = (float)(s / (double)per_item);
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t mdb_pose_head(mdb_handle* h, const float* conv_out, int32_t w, int32_t hh, int32_t N, float scale, float* rvec,
+                      float* tvec, void* stream) {
+  MDB_REQUIRE(h, h != nullptr, MDB_E_INVALID_ARG, "null handle");
+  MDB_REQUIRE(h, conv_out && rvec && tvec, MDB_E_INVALID_ARG, "mdb_pose_head: null pointer");
+  MDB_REQUIRE(h, w >= 1 && hh >= 1 && N >= 1 && N <= 65535, MDB_E_SHAPE, "mdb_pose_head: need w,h,N >= 1, N <= 65535");
+  pose_head_kernel<<<dim3(6, N), HEAD_THREADS, 0, (cudaStream_t)stream>>>(conv_out, w * hh, scale, rvec, tvec);
+  MDB_LAUNCHED(h);
+  return MDB_OK;
+}
+
+int32_t mdb_pose_head_bwd(mdb_handle* h, const float* d_rvec, const float* d_tvec, int32_t w, int32_t hh, int32_t N,
+                          float scale, float* d_conv_out, void* stream) {
+  MDB_REQUIRE(h, h != nullptr, MDB_E_INVALID_ARG, "null handle");
+  MDB_REQUIRE(h, d_rvec && d_tvec && d_conv_out, MDB_E_INVALID_ARG, "mdb_pose_head_bwd: null pointer");
+  MDB_REQUIRE(h, w >= 1 && hh >= 1 && N >= 1, MDB_E_SHAPE, "mdb_pose_head_bwd: need w,h,N >= 1");
+  const size_t total = (size_t)N * 6 * w * hh;
+  const int blocks = (int)std::min<size_t>((total + 255) / 256, (size_t)h->num_sms * 8);
+  pose_head_bwd_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(d_rvec, d_tvec, w * hh, N, scale, d_conv_out);
+  MDB_LAUNCHED(h);
+  return MDB_OK;
+}
+
+int32_t mdb_item_mean(mdb_handle* h, const float* map, int64_t per_item, int32_t N, float* out, void* stream) {
+  MDB_REQUIRE(h, h != nullptr, MDB_E_INVALID_ARG, "null handle");
+  MDB_REQUIRE(h, map && out, MDB_E_INVALID_ARG, "mdb_item_mean: null pointer");
+  MDB_REQUIRE(h, per_item >= 1 && N >= 1, MDB_E_SHAPE, "mdb_item_mean: need per_item, N >= 1");
+  item_mean_kernel<<<N, HEAD_THREADS, 0, (cudaStream_t)stream>>>(map, (long long)per_item, out);
+  MDB_LAUNCHED(h);
+  return MDB_OK;
+}
+
+}  // extern "C"

@@ -116,6 +116,9 @@ PROTOTYPES = {
     "mdb_slow_depth_run": (_i32, [_vp, _i32, _vp]),
     "mdb_slow_depth_destroy": (_i32, [_vp]),
     "mdb_ingest_triplet_u8": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp]),
+    "mdb_pose_head": (_i32, [_vp, _vp, _i32, _i32, _i32, _f32, _vp, _vp, _vp]),
+    "mdb_pose_head_bwd": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _f32, _vp, _vp]),
+    "mdb_item_mean": (_i32, [_vp, _vp, _i64, _i32, _vp, _vp]),
 }
 
 

@@ -630,6 +630,57 @@ def ingest_triplet_u8(strips: torch.Tensor, width: int, flips: Optional[torch.Te
 
 
 # --------------------------------------------------------------------------------------
+# the operators on the network side of the path
+# --------------------------------------------------------------------------------------
+class _PoseHeadFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, y, scale):
+        N, six, hh, w = y.shape
+        rvec = torch.empty((N, 3), device=y.device, dtype=torch.float32)
+        tvec = torch.empty((N, 1, 3), device=y.device, dtype=torch.float32)
+        check(handle(), lib.mdb_pose_head(handle(), _p(y), w, hh, N, float(scale), _p(rvec), _p(tvec), _stream()))
+        ctx.shape, ctx.scale = (N, six, hh, w), float(scale)
+        return rvec, tvec
+
+    @staticmethod
+    def backward(ctx, g_r, g_t):
+        N, _, hh, w = ctx.shape
+        dev = (g_r if g_r is not None else g_t).device
+        g_r = torch.zeros((N, 3), device=dev) if g_r is None else g_r.contiguous()
+        g_t = torch.zeros((N, 1, 3), device=dev) if g_t is None else g_t.contiguous()
+        d_y = torch.empty(ctx.shape, device=dev, dtype=torch.float32)
+        check(handle(), lib.mdb_pose_head_bwd(handle(), _p(g_r), _p(g_t), w, hh, N, ctx.scale, _p(d_y), _stream()))
+        return d_y, None
+
+
+def pose_head(conv_out: torch.Tensor, scale: float = 1e-2) -> Pose:
+    """The tail of `(decoder::PoseDecoder)(features)` -- src/pose_decoder.jl:27-32: spatial mean of the
+    (N,6,h,w) [Julia (w,h,6,N)] conv output, times 1e-2, split into `Pose(rvec (N,3), tvec (N,1,3))`.
+    Differentiable w.r.t. `conv_out`."""
+    _chk(conv_out, "conv_out")
+    if conv_out.dim() != 4 or conv_out.shape[1] != 6:
+        raise ValueError(f"conv_out has shape {tuple(conv_out.shape)}, expected (N,6,h,w)")
+    return Pose(*_PoseHeadFn.apply(conv_out, scale))
+
+
+def item_mean(m: torch.Tensor) -> torch.Tensor:
+    """mean over everything but the batch axis, one value per item (deterministic)."""
+    _chk(m, "map")
+    N = m.shape[0]
+    out = torch.empty((N,), device=m.device, dtype=torch.float32)
+    check(handle(), lib.mdb_item_mean(handle(), _p(m), m.numel() // N, N, _p(out), _stream()))
+    return out
+
+
+def find_static(x: torch.Tensor, alpha: float, *, target_id: int = 2, source_ids: Sequence[int] = (1, 3)):
+    """`find_static(dataset, alpha)` -- src/dtk.jl:51-69, for a batch at once: a sample is kept as
+    NON-static when `mean(automasking_loss(ssim, x, target; source_ids)) > alpha`.  x (N,L,C,H,W) on the
+    device (e.g. from `ingest_triplet_u8`).  Returns (non_static bool (N,), per-item means (N,))."""
+    means = item_mean(automasking_loss(SSIM(), x, target_id, source_ids=source_ids))
+    return means > alpha, means
+
+
+# --------------------------------------------------------------------------------------
 # host-buffer entry: the call a user with HOST arrays makes (bench "e2e")
 # --------------------------------------------------------------------------------------
 @dataclass

@@ -439,3 +439,18 @@ def slow_depth(x: torch.Tensor, K: torch.Tensor, invK: torch.Tensor, *, iters: i
                 t.requires_grad_(False)
             flux_adam_step(leaves, grads, state, eta=eta)                            # :42
     return disp, poses, hist
+
+
+# --------------------------------------------------------------------------------------
+# network-side boundary -- src/pose_decoder.jl:27-32, src/dtk.jl:51-69  
+# --------------------------------------------------------------------------------------
+def pose_head(conv_out: torch.Tensor, scale: float = 1e-2) -> Pose:
+    """Tail of `(decoder::PoseDecoder)(features)` -- src/pose_decoder.jl:29-31: `mean(...; dims=(1,2))`,
+    `1e-2 .* reshape(pose, (6,1,N))`, `Pose(pose[1:3,1,:], pose[4:6,:,:])`.  conv_out (N,6,h,w)."""
+    pose = scale * conv_out.mean(dim=(2, 3))              # (N,6)
+    return Pose(pose[:, 0:3], pose[:, 3:6].reshape(-1, 1, 3))
+
+
+def find_static_means(x: torch.Tensor, *, target_id: int = 2, source_ids: Sequence[int] = (1, 3)) -> torch.Tensor:
+    """The statistic `find_static` thresholds -- src/dtk.jl:59-62: mean of the automasking loss per sample."""
+    return automasking_loss(x, x[:, target_id - 1], source_ids).mean(dim=(1, 2, 3))

@@ -130,3 +130,32 @@ def test_slow_depth_reference_signature_and_logging():
     assert torch.equal(d1, d2) and torch.equal(h1, h2)             # deterministic, chunking does not matter
     assert float(h1[-1]) < float(h1[0])
     assert abs(seen[-1][1] - float(h1[-1])) == 0.0
+
+
+def test_error_codes_of_the_new_entry_points():
+    """mdb_adam_update / mdb_slow_depth_create / mdb_ingest_triplet_u8 return status codes, never throw."""
+    import ctypes as ct
+    import mdb200
+    from mdb200 import _lib
+    h = mdb200.handle()
+    lib = _lib.lib
+    ap = _lib.AdamParams(3e-4, 0.9, 0.999, 1e-8)
+    assert lib.mdb_adam_update(h, 0, None, None, None, None, None, ct.byref(ap), None, None, None, None, 0, None) == -1
+    assert b"tensors" in lib.mdb_last_error(h)
+    io = _lib.LossIO()
+    io.W, io.H, io.C, io.L, io.N, io.S, io.Ls = 64, 32, 3, 3, 1, 2, 2          # two scales: not slow_depth's shape
+    io.dw[0], io.dh[0], io.dw[1], io.dh[1] = 32, 16, 64, 32
+    p = _lib.LossParams()
+    lib.mdb_loss_params_default(ct.byref(p))
+    out = ct.c_void_p()
+    assert lib.mdb_slow_depth_create(h, ct.byref(io), ct.byref(p), ct.byref(ap), None, 0, None, 0, None, 0, ct.byref(out)) == -2
+    io.Ls, io.dw[0], io.dh[0] = 1, 64, 32
+    assert lib.mdb_slow_depth_state_bytes(ct.byref(io)) >= 2 * 4 * (64 * 32 + 12)
+    assert lib.mdb_slow_depth_create(h, ct.byref(io), ct.byref(p), ct.byref(ap), None, 0, None, 0, None, 0, ct.byref(out)) == -3
+    assert lib.mdb_slow_depth_run(None, 1, None) == -1
+    assert lib.mdb_slow_depth_destroy(None) == 0
+    x = torch.empty(8, device=DEV)
+    assert lib.mdb_ingest_triplet_u8(h, None, None, 4, 4, 1, 0, x.data_ptr(), None) == -1
+    assert lib.mdb_ingest_triplet_u8(h, x.data_ptr(), None, 0, 4, 1, 0, x.data_ptr(), None) == -2
+    with pytest.raises(ValueError):
+        mdb200.ingest_triplet_u8(torch.zeros(1, 4, 12, 3, device=DEV), 4)       # float strips: rejected by the glue
