@@ -264,7 +264,7 @@ FusedLayout fused_layout(const mdb_loss_io* io, int num_sms = 148) {
 }
 
 bool io_shape_ok(const mdb_loss_io* io) {
-  if (!io || io->W < 2 || io->H < 2 || io->N < 1 || io->L < 1) return false;
+  if (!io || io->W < 2 || io->H < 2 || io->N < 1 || io->N > 65535 || io->L < 1) return false;   // N rides in gridDim.y/z
   if (io->C != 1 && io->C != 3) return false;
   if ((long long)io->W * io->H * io->C * io->L >= (1ll << 31)) return false;   // 32-bit offsets inside an item
   if (io->S < 1 || io->S > MDB_MAX_SOURCES || io->Ls < 1 || io->Ls > MDB_MAX_SCALES) return false;

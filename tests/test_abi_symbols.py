@@ -84,6 +84,12 @@ def test_workspace_query_and_shape_validation_need_no_gpu():
     assert _lib.lib.mdb_train_loss_workspace_bytes(ctypes.byref(io)) == 0
     io.C, io.W = 3, 1
     assert _lib.lib.mdb_train_loss_workspace_bytes(ctypes.byref(io)) == 0
+    io.W, io.N = 416, 65536                       # N rides in gridDim.y / z
+    assert _lib.lib.mdb_train_loss_workspace_bytes(ctypes.byref(io)) == 0
+    io.N, io.W, io.H = 1, 32768, 8192             # W H C L >= 2^31: 32-bit offsets inside an item
+    for k in range(4):
+        io.dw[k], io.dh[k] = 32768, 8192
+    assert _lib.lib.mdb_train_loss_workspace_bytes(ctypes.byref(io)) == 0
 
 
 @pytest.mark.skipif(__import__("torch").cuda.is_available(), reason="checks the no-GPU behaviour")

@@ -238,3 +238,21 @@ def test_full_size_configs_vs_c_oracle(name, N):
             g = got.double().cpu().numpy().reshape(N, 3)
             e = np.abs(g - want.reshape(N, 3)).max(axis=1) / np.abs(want).max()
             assert (e > P.GRAD_RTOL).sum() <= 1 + N // 16 and e.max() < 5e-3, (nm, s, e)
+
+
+def test_large_single_image_vs_c_oracle():
+    """One 2048x1024 item (18.9 M floats per item: the 32-bit offset arithmetic far from the small cases),
+    two scales (1/4 and native), against the C oracle."""
+    from mdb200 import synth
+    from oracle import c_ref
+    inp = synth.make_loss_inputs(2048, 1024, 1, seed=61, scales=(0.25, 1.0))
+    ref = c_ref.train_loss(inp.x, inp.disparities, inp.rvecs, inp.tvecs, None, inp.K, inp.invK, target_id=2,
+                           source_ids=inp.source_ids, scales=inp.scales, automasking=False)
+    res, _ = _run_gpu(inp)
+    assert abs(float(res.loss) - ref["loss"]) <= P.LOSS_RTOL * abs(ref["loss"])
+    for k, (g, r) in enumerate(zip(res.d_disparities, ref["d_disp"])):
+        rep = P.grad_report(f"d_disp[{k}]", g, torch.tensor(r))
+        assert rep["n_out"] <= max(P.MAX_OUTLIERS, rep["numel"] // 10000) and rep["rel_l2"] < 1e-3, rep
+    for s in range(2):
+        e = np.abs(res.d_poses[s].rvec.double().cpu().numpy() - ref["d_rvec"][s]).max() / np.abs(ref["d_rvec"][s]).max()
+        assert e < 5e-3, e
