@@ -413,6 +413,22 @@ def run_render(args):
                          "fwd": {"ms": fm, "algorithmic_bytes": fwd_b, "achieved": fwd_b / (fm * 1e-3) / 1e9, "frac": fwd_b / (fm * 1e-3) / 1e9 / peak},
                          "bwd": {"ms": bm, "algorithmic_bytes": bwd_b, "achieved": bwd_b / (bm * 1e-3) / 1e9, "frac": bwd_b / (bm * 1e-3) / 1e9 / peak},
                          "achieved": (fwd_b + bwd_b) / ((fm + bm) * 1e-3) / 1e9, "frac": (fwd_b + bwd_b) / ((fm + bm) * 1e-3) / 1e9 / peak}}
+    if not args.no_cpu_baseline:
+        from oracle import c_ref
+        import numpy as np
+        cores = os.cpu_count() or 1
+        gr, gd = g_rgb.cpu().numpy(), g_dep.cpu().numpy()
+        call = lambda: c_ref.render_tgt_rgb_depth(ri.rgb, ri.sigma, ri.disparity_src, ri.xyz_tgt, ri.rvec, ri.tvec, ri.K_inv, ri.K,
+                                                  g_rgb=gr, g_depth=gd, dtype=np.float32, threads=cores)
+        call()
+        t0 = time.perf_counter()
+        for _ in range(3):
+            call()
+        t_cpu = (time.perf_counter() - t0) / 3
+        line["cpu_baseline"] = {"value": units / t_cpu, "unit": "plane_px/s", "cores": cores, "kind": "port",
+                                "sample": f"the whole config (B={B}), 3 calls after 1 warm-up of the plain-C float32 port "
+                                          f"(oracle/c_port: forward + hand-written pullback, rows / planes over {cores} threads, "
+                                          f"{t_cpu * 1e3:.0f} ms per call)"}
     print(json.dumps(line), flush=True)
 
 

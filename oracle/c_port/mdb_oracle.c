@@ -613,3 +613,300 @@ int mdbo_train_loss(const mdbo_desc* d, const real* x, const real* rvec, const r
 }
 
 int mdbo_sizeof_real(void) { return (int)sizeof(real); }
+
+/* ==========================================================================================
+ * plane-disparity volume rendering -- src/render.jl, quirks reproduced as written.
+ * Second, independent restatement next to oracle/torch_ref.py::render_tgt_rgb_depth (autograd):
+ * the pullback below is written by hand.
+ * Layouts (Julia column-major == these C orders): rgb [B][Np][3][H][W], sigma [B][Np][1][H][W],
+ * xyz_tgt [B][Np][H][W][3], disparity_src [B][Np], rvec [B][3], tvec [B][3];
+ * rgb_out [B][3][H][W], depth_out = transparency_acc [B][Np][1][H][W], mask [B][1][1][H][W] int32.
+ * ======================================================================================== */
+static int inv3(const double* A, double* B) {          /* Monodepth.inv, src/render.jl:3-17 */
+  const double c00 = A[4] * A[8] - A[5] * A[7], c01 = A[5] * A[6] - A[3] * A[8], c02 = A[3] * A[7] - A[4] * A[6];
+  const double det = A[0] * c00 + A[1] * c01 + A[2] * c02, id = 1.0 / det;
+  B[0] = c00 * id; B[1] = (A[2] * A[7] - A[1] * A[8]) * id; B[2] = (A[1] * A[5] - A[2] * A[4]) * id;
+  B[3] = c01 * id; B[4] = (A[0] * A[8] - A[2] * A[6]) * id; B[5] = (A[2] * A[3] - A[0] * A[5]) * id;
+  B[6] = c02 * id; B[7] = (A[1] * A[6] - A[0] * A[7]) * id; B[8] = (A[0] * A[4] - A[1] * A[3]) * id;
+  return det != 0.0;
+}
+
+typedef struct {
+  int W, H, Np, B;
+  const real *rgb, *sigma, *xyz, *disp;
+  const double *Km, *iKm;               /* math row-major */
+  const real *rvec, *tvec;
+  real *rgb_out, *tacc;
+  int32_t* mask;
+  /* backward (NULL for forward only) */
+  const real *g_out, *g_tacc;
+  real *d_rgb, *d_sigma, *d_xyz;        /* zero-initialised by the driver */
+  double* Gacc;                         /* [B][Np][9]: d loss / d H_src_tgt, math row-major */
+  real* gs;                             /* [B][Np][H W][9]: per-sample grads (7 channels) + d/d(cx), d/d(cy) */
+  atomic_int next;
+} rjob_t;
+
+typedef struct { int o[4]; real fx, fy, mx, my; double X[3], x, y; int valid; } rtap_t;
+
+/* sample coordinates of target pixel (u,v) (0-based) under H_src_tgt    src/render.jl:76-88 */
+static rtap_t render_tap(const double* Hst, int u, int v, int W, int H) {
+  rtap_t t;
+  for (int i = 0; i < 3; ++i) t.X[i] = Hst[3 * i] * u + Hst[3 * i + 1] * v + Hst[3 * i + 2];
+  t.x = t.X[0] / t.X[2]; t.y = t.X[1] / t.X[2];
+  /* Julia parses `a .< W .* a .>= 0` as (a < W a) & (W a >= 0)          src/render.jl:81, SURVEY F8c */
+  t.valid = (t.x < W * t.x) && (W * t.x >= 0.0) && (t.y < H * t.y) && (H * t.y >= 0.0);
+  /* grid = (xy + 0.5) / (W/2) without "-1" (:83-84), then grid_sample's align-corners un-normalisation */
+  const double ix = ((t.x + 0.5) / (W / 2.0) + 1.0) * 0.5 * (W - 1), iy = ((t.y + 0.5) / (H / 2.0) + 1.0) * 0.5 * (H - 1);
+  t.mx = (ix > 0.0 && ix < (double)(W - 1)) ? 1 : 0;       /* clamp multiplier of the sampling gradient */
+  t.my = (iy > 0.0 && iy < (double)(H - 1)) ? 1 : 0;
+  const double cx = fmin(fmax(ix, 0.0), (double)(W - 1)), cy = fmin(fmax(iy, 0.0), (double)(H - 1));
+  const int x0 = (int)floor(cx), y0 = (int)floor(cy);
+  const int x1 = x0 + 1 < W ? x0 + 1 : W - 1, y1 = y0 + 1 < H ? y0 + 1 : H - 1;
+  t.fx = (real)(cx - x0); t.fy = (real)(cy - y0);
+  t.o[0] = y0 * W + x0; t.o[1] = y0 * W + x1; t.o[2] = y1 * W + x0; t.o[3] = y1 * W + x1;
+  return t;
+}
+
+static inline real bil4(const rtap_t* t, real a, real b, real c, real d) {
+  const real top = a + t->fx * (b - a), bot = c + t->fx * (d - c);
+  return top + t->fy * (bot - top);
+}
+
+static void plane_homography(const rjob_t* J, int b, int k, double* Hst) {   /* src/render.jl:66-74 */
+  double r[3] = {(double)J->rvec[3 * b], (double)J->rvec[3 * b + 1], (double)J->rvec[3 * b + 2]}, R[9], M[9], KM[9], Hts[9];
+  so3_aux a;
+  so3_exp_rm(r, R, &a);
+  const double dsp = (double)J->disp[b * J->Np + k];      /* 1 / depth_src, depth_src = 1 ./ disparity_src (:93) */
+  memcpy(M, R, sizeof(M));
+  for (int i = 0; i < 3; ++i) M[3 * i + 2] += (double)J->tvec[3 * b + i] * dsp;   /* R - t n^T / (-depth) */
+  mat3_mul(J->Km, M, KM);
+  mat3_mul(KM, J->iKm, Hts);
+  inv3(Hts, Hst);
+}
+
+/* one (b, row) unit of work: forward compositing and, if asked, the per-sample pullback */
+static void render_row(rjob_t* J, int b, int v, const double* Hst_all) {
+  const int W = J->W, H = J->H, Np = J->Np, WH = W * H;
+  real* s7 = malloc((size_t)Np * 7 * sizeof(real));
+  real* tacc = malloc((size_t)(Np + 1) * sizeof(real));
+  real* Tk = malloc((size_t)Np * sizeof(real));
+  real* dist = malloc((size_t)Np * sizeof(real));
+  rtap_t* taps = malloc((size_t)Np * sizeof(rtap_t));
+  for (int u = 0; u < W; ++u) {
+    const int pix = v * W + u;
+    int nvalid = 0;
+    for (int k = 0; k < Np; ++k) {
+      const int kb = b * Np + k;
+      taps[k] = render_tap(Hst_all + 9 * kb, u, v, W, H);
+      const rtap_t* t = &taps[k];
+      nvalid += t->valid;
+      const real* pr = J->rgb + (size_t)kb * 3 * WH;
+      for (int c = 0; c < 3; ++c) s7[7 * k + c] = bil4(t, pr[c * WH + t->o[0]], pr[c * WH + t->o[1]], pr[c * WH + t->o[2]], pr[c * WH + t->o[3]]);
+      const real* ps = J->sigma + (size_t)kb * WH;
+      s7[7 * k + 3] = bil4(t, ps[t->o[0]], ps[t->o[1]], ps[t->o[2]], ps[t->o[3]]);
+      const real* px = J->xyz + (size_t)kb * WH * 3;
+      for (int c = 0; c < 3; ++c) s7[7 * k + 4 + c] = bil4(t, px[3 * t->o[0] + c], px[3 * t->o[1] + c], px[3 * t->o[2] + c], px[3 * t->o[3] + c]);
+    }
+    /* plane_volume_rendering                                              src/render.jl:32-49 */
+    real out[3] = {0, 0, 0};
+    tacc[0] = 1;
+    for (int k = 0; k < Np; ++k) {
+      real d = (real)1e3;
+      if (k + 1 < Np) {
+        const real dx = s7[7 * (k + 1) + 4] - s7[7 * k + 4], dy = s7[7 * (k + 1) + 5] - s7[7 * k + 5], dz = s7[7 * (k + 1) + 6] - s7[7 * k + 6];
+        d = (real)sqrt((double)(dx * dx + dy * dy + dz * dz));
+      }
+      dist[k] = d;
+      const real sg = s7[7 * k + 3] >= 0 ? s7[7 * k + 3] : 0;              /* sigma .* (sigma .>= 0), :101 */
+      Tk[k] = R_EXP(-d * sg);
+      const real w = tacc[k] * (1 - Tk[k]);
+      for (int c = 0; c < 3; ++c) out[c] += w * s7[7 * k + c];
+      J->tacc[(size_t)(b * Np + k) * WH + pix] = tacc[k];
+      tacc[k + 1] = tacc[k] * (Tk[k] + (real)1e-6);
+    }
+    for (int c = 0; c < 3; ++c) J->rgb_out[((size_t)b * 3 + c) * WH + pix] = out[c];
+    J->mask[(size_t)b * WH + pix] = nvalid;
+    if (!J->g_out) continue;
+
+    /* ---- pullback of the compositing, planes in reverse ---- */
+    real go[3];
+    for (int c = 0; c < 3; ++c) go[c] = J->g_out[((size_t)b * 3 + c) * WH + pix];
+    real gT_next = 0;                   /* d loss / d tacc[k+1] */
+    real gxyz_next[3] = {0, 0, 0};      /* d loss / d xyz_{k+1} from dist_k */
+    for (int k = Np - 1; k >= 0; --k) {
+      const real sgraw = s7[7 * k + 3], sg = sgraw >= 0 ? sgraw : 0;
+      const real alpha = 1 - Tk[k];
+      real gw = 0;
+      for (int c = 0; c < 3; ++c) gw += go[c] * s7[7 * k + c];
+      real* g = J->gs + ((size_t)(b * Np + k) * WH + pix) * 9;
+      for (int c = 0; c < 3; ++c) g[c] = go[c] * tacc[k] * alpha;          /* d/d rgb_k = g_out w_k */
+      const real gtk = (J->g_tacc ? J->g_tacc[(size_t)(b * Np + k) * WH + pix] : 0) + gw * alpha + gT_next * (Tk[k] + (real)1e-6);
+      const real gTk = -gw * tacc[k] + gT_next * tacc[k];                   /* d/d T_k */
+      const real ge = gTk * Tk[k];                                          /* d/d(-dist sigma) */
+      g[3] = sgraw >= 0 ? -ge * dist[k] : 0;
+      real gxyz[3] = {gxyz_next[0], gxyz_next[1], gxyz_next[2]};
+      gxyz_next[0] = gxyz_next[1] = gxyz_next[2] = 0;
+      if (k + 1 < Np) {
+        const real gd = -ge * sg;
+        for (int c = 0; c < 3; ++c) {
+          const real dv = (s7[7 * (k + 1) + 4 + c] - s7[7 * k + 4 + c]) / dist[k];
+          /* xyz_{k+1} was handled one iteration ago: add to its stored slot */
+          J->gs[((size_t)(b * Np + k + 1) * WH + pix) * 9 + 4 + c] += gd * dv;
+          gxyz[c] -= gd * dv;
+        }
+      }
+      for (int c = 0; c < 3; ++c) g[4 + c] = gxyz[c];
+      gT_next = gtk;
+    }
+    /* ---- per-sample: d/d(cx), d/d(cy) from the 7 channel grads (needs the FINAL g[4..6]) ---- */
+    for (int k = 0; k < Np; ++k) {
+      const int kb = b * Np + k;
+      const rtap_t* t = &taps[k];
+      real* g = J->gs + ((size_t)kb * WH + pix) * 9;
+      real gx = 0, gy = 0;
+      const real* pr = J->rgb + (size_t)kb * 3 * WH;
+      const real* ps = J->sigma + (size_t)kb * WH;
+      const real* px = J->xyz + (size_t)kb * WH * 3;
+      for (int ch = 0; ch < 7; ++ch) {
+        real a, bq, c, dq;
+        if (ch < 3) { a = pr[ch * WH + t->o[0]]; bq = pr[ch * WH + t->o[1]]; c = pr[ch * WH + t->o[2]]; dq = pr[ch * WH + t->o[3]]; }
+        else if (ch == 3) { a = ps[t->o[0]]; bq = ps[t->o[1]]; c = ps[t->o[2]]; dq = ps[t->o[3]]; }
+        else { const int c3 = ch - 4; a = px[3 * t->o[0] + c3]; bq = px[3 * t->o[1] + c3]; c = px[3 * t->o[2] + c3]; dq = px[3 * t->o[3] + c3]; }
+        gx += g[ch] * ((bq - a) * (1 - t->fy) + (dq - c) * t->fy);
+        gy += g[ch] * ((c - a) * (1 - t->fx) + (dq - bq) * t->fx);
+      }
+      g[7] = gx * t->mx;
+      g[8] = gy * t->my;
+    }
+  }
+  free(s7); free(tacc); free(Tk); free(dist); free(taps);
+}
+
+/* phase 2, one (b, k) plane: transpose of the bilinear gather into d_rgb / d_sigma / d_xyz (this plane's
+ * arrays only: race-free across planes) and the sum G = d loss / d H_src_tgt over the plane's pixels */
+static void render_scatter_plane(rjob_t* J, int kb, const double* Hst) {
+  const int W = J->W, H = J->H, WH = W * H;
+  real* dr = J->d_rgb + (size_t)kb * 3 * WH;
+  real* ds = J->d_sigma + (size_t)kb * WH;
+  real* dx = J->d_xyz + (size_t)kb * WH * 3;
+  double G[9] = {0};
+  for (int v = 0; v < H; ++v)
+    for (int u = 0; u < W; ++u) {
+      const rtap_t t = render_tap(Hst, u, v, W, H);
+      const real* g = J->gs + ((size_t)kb * WH + v * W + u) * 9;
+      const real w[4] = {(1 - t.fx) * (1 - t.fy), t.fx * (1 - t.fy), (1 - t.fx) * t.fy, t.fx * t.fy};
+      for (int q = 0; q < 4; ++q) {
+        for (int c = 0; c < 3; ++c) dr[c * WH + t.o[q]] += g[c] * w[q];
+        ds[t.o[q]] += g[3] * w[q];
+        for (int c = 0; c < 3; ++c) dx[3 * t.o[q] + c] += g[4 + c] * w[q];
+      }
+      /* (cx, cy) <- (x, y): d ix / d x = (W-1)/W (no "-1" grid, align-corners un-normalisation) */
+      const double gx = (double)g[7] * (double)(W - 1) / (double)W, gy = (double)g[8] * (double)(H - 1) / (double)H;
+      if (gx == 0.0 && gy == 0.0) continue;
+      const double gX[3] = {gx / t.X[2], gy / t.X[2], -(gx * t.x + gy * t.y) / t.X[2]};
+      const double q3[3] = {(double)u, (double)v, 1.0};
+      for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) G[3 * i + j] += gX[i] * q3[j];
+    }
+  memcpy(J->Gacc + 9 * kb, G, sizeof(G));
+}
+
+typedef struct { rjob_t* J; const double* Hst; int phase; } rwork_t;
+
+static void* render_worker(void* arg) {
+  rwork_t* Wk = (rwork_t*)arg;
+  rjob_t* J = Wk->J;
+  const int units = Wk->phase == 1 ? J->B * J->H : J->B * J->Np;
+  for (;;) {
+    const int i = atomic_fetch_add(&J->next, 1);
+    if (i >= units) break;
+    if (Wk->phase == 1) render_row(J, i / J->H, i % J->H, Wk->Hst);
+    else render_scatter_plane(J, i, Wk->Hst + 9 * i);
+  }
+  return NULL;
+}
+
+static void render_run(rjob_t* J, const double* Hst, int phase, int nthreads) {
+  rwork_t Wk = {J, Hst, phase};
+  atomic_store(&J->next, 0);
+  int nt = nthreads < 1 ? 1 : (nthreads > 256 ? 256 : nthreads);
+  pthread_t th[256];
+  int started = 0;
+  for (int i = 1; i < nt; ++i)
+    if (pthread_create(&th[started], NULL, render_worker, &Wk) == 0) ++started;
+  render_worker(&Wk);
+  for (int i = 0; i < started; ++i) pthread_join(th[i], NULL);
+}
+
+/* render_tgt_rgb_depth (src/render.jl:92-114) forward and, when g_rgb_out != NULL, its pullback.
+ * K_jl / Kinv_jl: the 9 numbers Julia stores.  g_depth may be NULL.  All d_* must be given for the
+ * pullback (d_disp [B][Np], d_rvec [B][3], d_tvec [B][3]).  Returns 0, -1 on bad arguments / OOM. */
+int mdbo_render_tgt_rgb_depth(int W, int H, int Np, int B, const real* rgb, const real* sigma, const real* disparity_src,
+                              const real* xyz_tgt, const real* rvec, const real* tvec, const real* Kinv_jl, const real* K_jl,
+                              real* rgb_out, real* depth_out, int32_t* mask_out, const real* g_rgb_out, const real* g_depth,
+                              real* d_rgb, real* d_sigma, real* d_disp, real* d_xyz, real* d_rvec, real* d_tvec, int nthreads) {
+  if (W < 2 || H < 2 || Np < 1 || B < 1 || !rgb || !sigma || !disparity_src || !xyz_tgt || !rvec || !tvec || !rgb_out ||
+      !depth_out || !mask_out)
+    return -1;
+  if (g_rgb_out && (!d_rgb || !d_sigma || !d_disp || !d_xyz || !d_rvec || !d_tvec)) return -1;
+  double Km[9], iKm[9];
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) { Km[3 * i + j] = (double)K_jl[3 * j + i]; iKm[3 * i + j] = (double)Kinv_jl[3 * j + i]; }
+  rjob_t J;
+  memset(&J, 0, sizeof(J));
+  J.W = W; J.H = H; J.Np = Np; J.B = B;
+  J.rgb = rgb; J.sigma = sigma; J.xyz = xyz_tgt; J.disp = disparity_src; J.Km = Km; J.iKm = iKm; J.rvec = rvec; J.tvec = tvec;
+  J.rgb_out = rgb_out; J.tacc = depth_out; J.mask = mask_out;
+  const size_t WH = (size_t)W * H, planes = (size_t)B * Np;
+  double* Hst = malloc(planes * 9 * sizeof(double));
+  if (!Hst) return -1;
+  for (int b = 0; b < B; ++b)
+    for (int k = 0; k < Np; ++k) plane_homography(&J, b, k, Hst + 9 * (b * Np + k));
+  int rc = 0;
+  if (g_rgb_out) {
+    J.g_out = g_rgb_out; J.g_tacc = g_depth; J.d_rgb = d_rgb; J.d_sigma = d_sigma; J.d_xyz = d_xyz;
+    J.gs = malloc(planes * WH * 9 * sizeof(real));
+    J.Gacc = calloc(planes * 9, sizeof(double));
+    if (!J.gs || !J.Gacc) { free(J.gs); free(J.Gacc); free(Hst); return -1; }
+    memset(d_rgb, 0, planes * 3 * WH * sizeof(real));
+    memset(d_sigma, 0, planes * WH * sizeof(real));
+    memset(d_xyz, 0, planes * 3 * WH * sizeof(real));
+  }
+  atomic_init(&J.next, 0);
+  render_run(&J, Hst, 1, nthreads);
+  if (g_rgb_out) {
+    render_run(&J, Hst, 2, nthreads);
+    /* H_src_tgt = inv(H_tgt_src), H_tgt_src = K M K^-1, M = R + t n^T disparity    src/render.jl:66-74 */
+    for (int b = 0; b < B; ++b) {
+      double gR[9] = {0}, gt[3] = {0};
+      for (int k = 0; k < Np; ++k) {
+        const double* Hs = Hst + 9 * (b * Np + k);
+        const double* G = J.Gacc + 9 * (b * Np + k);
+        double HT[9], t1[9], gHts[9], KT[9], iKT[9], t2[9], gM[9];
+        for (int i = 0; i < 3; ++i)
+          for (int j = 0; j < 3; ++j) { HT[3 * i + j] = Hs[3 * j + i]; KT[3 * i + j] = Km[3 * j + i]; iKT[3 * i + j] = iKm[3 * j + i]; }
+        mat3_mul(HT, G, t1);
+        mat3_mul(t1, HT, gHts);
+        for (int q = 0; q < 9; ++q) gHts[q] = -gHts[q];              /* d inv(A) = -A^-T G A^-T */
+        mat3_mul(KT, gHts, t2);
+        mat3_mul(t2, iKT, gM);
+        const double dsp = (double)disparity_src[b * Np + k];
+        double gd = 0;
+        for (int i = 0; i < 3; ++i) {
+          for (int j = 0; j < 3; ++j) gR[3 * i + j] += gM[3 * i + j];
+          gt[i] += gM[3 * i + 2] * dsp;
+          gd += gM[3 * i + 2] * (double)tvec[3 * b + i];
+        }
+        d_disp[b * Np + k] = (real)gd;
+      }
+      double r[3] = {(double)rvec[3 * b], (double)rvec[3 * b + 1], (double)rvec[3 * b + 2]}, R[9], dr[3];
+      so3_aux a;
+      so3_exp_rm(r, R, &a);
+      so3_exp_bwd_rm(r, &a, gR, dr);
+      for (int i = 0; i < 3; ++i) { d_rvec[3 * b + i] = (real)dr[i]; d_tvec[3 * b + i] = (real)gt[i]; }
+    }
+    free(J.gs); free(J.Gacc);
+  }
+  free(Hst);
+  return rc;
+}

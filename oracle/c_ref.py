@@ -140,3 +140,35 @@ def compose_T_bwd(rvec, tvec, invert, dR, dt):
     gr, gt = np.zeros_like(r), np.zeros_like(t)
     L.mdbo_compose_T_bwd(_ptr(r), _ptr(t), C.c_int(int(invert)), C.c_int(r.shape[0]), _ptr(dR), _ptr(dt), _ptr(gr), _ptr(gt))
     return gr, gt
+
+
+def render_tgt_rgb_depth(rgb, sigma, disparity_src, xyz_tgt, rvec, tvec, K_inv, K, *, g_rgb=None, g_depth=None,
+                         dtype=np.float64, threads: int = 1):
+    """`render_tgt_rgb_depth` (src/render.jl:92-114) forward and, when `g_rgb` is given, the hand-written
+    pullback of  sum(g_rgb * rgb_out) + sum(g_depth * depth_out).  Arrays in the repo's reversed-dims
+    convention: rgb (B,Np,3,H,W), sigma (B,Np,1,H,W), disparity_src (B,Np), xyz_tgt (B,Np,H,W,3),
+    rvec / tvec (B,3).  Returns dict(rgb, depth, mask[, d_rgb, d_sigma, d_disparity_src, d_xyz_tgt, d_rvec, d_tvec])."""
+    L = lib(dtype)
+    L.mdbo_render_tgt_rgb_depth.restype = C.c_int
+    c = lambda a: None if a is None else np.ascontiguousarray(a, dtype=dtype)
+    rgb, sigma, disparity_src, xyz_tgt, rvec, tvec = map(c, (rgb, sigma, disparity_src, xyz_tgt, rvec, tvec))
+    B, Np, _, H, W = rgb.shape
+    Ki, Kk = c(np.asarray(K_inv).reshape(9)), c(np.asarray(K).reshape(9))
+    out = np.zeros((B, 3, H, W), dtype=dtype)
+    depth = np.zeros((B, Np, 1, H, W), dtype=dtype)
+    mask = np.zeros((B, 1, 1, H, W), dtype=np.int32)
+    g_rgb, g_depth = c(g_rgb), c(g_depth)
+    grads = [None] * 6
+    if g_rgb is not None:
+        grads = [np.zeros_like(rgb), np.zeros_like(sigma), np.zeros_like(disparity_src), np.zeros_like(xyz_tgt),
+                 np.zeros_like(rvec), np.zeros_like(tvec)]
+    rc = L.mdbo_render_tgt_rgb_depth(C.c_int(W), C.c_int(H), C.c_int(Np), C.c_int(B), _ptr(rgb), _ptr(sigma), _ptr(disparity_src),
+                                     _ptr(xyz_tgt), _ptr(rvec), _ptr(tvec), _ptr(Ki), _ptr(Kk), _ptr(out), _ptr(depth),
+                                     mask.ctypes.data_as(C.c_void_p), _ptr(g_rgb), _ptr(g_depth), _ptr(grads[0]), _ptr(grads[1]),
+                                     _ptr(grads[2]), _ptr(grads[3]), _ptr(grads[4]), _ptr(grads[5]), C.c_int(threads))
+    if rc != 0:
+        raise RuntimeError(f"mdbo_render_tgt_rgb_depth failed ({rc})")
+    res = dict(rgb=out, depth=depth, mask=mask)
+    if g_rgb is not None:
+        res.update(d_rgb=grads[0], d_sigma=grads[1], d_disparity_src=grads[2], d_xyz_tgt=grads[3], d_rvec=grads[4], d_tvec=grads[5])
+    return res

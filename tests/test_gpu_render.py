@@ -118,3 +118,28 @@ def test_render_plan_matches_autograd_wrapper():
     for got, t in zip(grads, [ins[0], ins[1], ins[2], ins[3], ins[4], ins[5]]):
         ref = t.grad
         assert (got - ref).abs().max() <= 1e-5 * ref.abs().max()      # RED order differs run to run
+
+
+def test_render_config4_full_size_vs_c_oracle():
+    """BASELINE config 4 at full geometry (416x128, 32 planes, B=2), forward AND pullback, against the plain-C
+    float64 oracle with its hand-written pullback (oracle/c_port)."""
+    import mdb200
+    from mdb200 import synth
+    from oracle import c_ref
+    ri = synth.make_render_inputs(416, 128, 32, 2)
+    rng = np.random.default_rng(8)
+    wr = rng.random((2, 3, 128, 416)).astype(np.float32)
+    wd = (0.1 * rng.random((2, 32, 1, 128, 416))).astype(np.float32)
+    ref = c_ref.render_tgt_rgb_depth(ri.rgb, ri.sigma, ri.disparity_src, ri.xyz_tgt, ri.rvec, ri.tvec, ri.K_inv, ri.K,
+                                     g_rgb=wr, g_depth=wd, threads=8)
+    plan = mdb200.RenderPlan(416, 128, 32, 2, ri.K_inv, ri.K)
+    rg, dg, mg = plan.forward(_dev(ri.rgb), _dev(ri.sigma), _dev(ri.disparity_src), _dev(ri.xyz_tgt),
+                              mdb200.Pose(_dev(ri.rvec), _dev(ri.tvec)))
+    assert np.abs(rg.double().cpu().numpy() - ref["rgb"]).max() < 1e-5
+    assert np.abs(dg.double().cpu().numpy() - ref["depth"]).max() < 1e-5
+    assert np.array_equal(mg.cpu().numpy(), ref["mask"])
+    grads = plan.backward(_dev(wr), _dev(wd))
+    for got, name in zip(grads, ["d_rgb", "d_sigma", "d_disparity_src", "d_xyz_tgt", "d_rvec", "d_tvec"]):
+        r = ref[name]
+        err = np.abs(got.double().cpu().numpy() - r).max() / np.abs(r).max()
+        assert err < 1e-4, (name, float(err))

@@ -136,3 +136,44 @@ def test_smooth_loss_known_answer_c():  # runtests.jl:70-83 -> 0.2542
     tl = np.abs(disp[..., :, :-1] - disp[..., :, 1:]).mean() + np.abs(disp[..., :-1, :] - disp[..., 1:, :]).mean()
     assert abs(sl(np.ones((2, 2))) - tl) < 1e-6
     assert abs(sl(np.array([[0.1, 0.3], [0.2, 0.4]])) - 0.2542) < 1e-4
+
+
+# ---- render path: the C restatement (hand-written pullback) against the torch one (autograd) ----------
+def _render_case(W, H, Np, B, seed, pose_scale, rand_xyz):
+    ri = synth.make_render_inputs(W, H, Np, B, seed=seed, pose_scale=pose_scale)
+    rng = np.random.default_rng(seed)
+    if rand_xyz:      # test/test_render_tgt_rgb_depth.jl style: xyz_tgt ~ rand, some negative sigma
+        ri.xyz_tgt = (rng.random(ri.xyz_tgt.shape) + np.arange(Np)[None, :, None, None, None] * 0.5).astype(np.float32)
+        ri.sigma = (rng.random(ri.sigma.shape) - 0.2).astype(np.float32)
+    return ri
+
+
+@pytest.mark.parametrize("W,H,Np,B,pose_scale,rand_xyz", [(24, 16, 6, 2, 2.0, False), (40, 24, 5, 1, 20.0, True), (17, 9, 3, 2, 1.0, True)])
+def test_render_two_oracles_agree(W, H, Np, B, pose_scale, rand_xyz):
+    ri = _render_case(W, H, Np, B, 70 + W, pose_scale, rand_xyz)
+    f = lambda a: torch.tensor(a, dtype=torch.float64, requires_grad=True)
+    rgb, sig, dsp, xyz, rv, tv = f(ri.rgb), f(ri.sigma), f(ri.disparity_src), f(ri.xyz_tgt), f(ri.rvec), f(ri.tvec)
+    ro, do, mo = T.render_tgt_rgb_depth(rgb, sig, dsp, xyz, T.Pose(rv, tv), torch.tensor(ri.K_inv.astype(np.float64)),
+                                        torch.tensor(ri.K.astype(np.float64)))
+    g = torch.Generator().manual_seed(1)
+    wr, wd = torch.rand(ro.shape, generator=g, dtype=torch.float64), torch.rand(do.shape, generator=g, dtype=torch.float64)
+    refs = torch.autograd.grad((ro * wr).sum() + (do * wd).sum(), (rgb, sig, dsp, xyz, rv, tv))
+    got = c_ref.render_tgt_rgb_depth(ri.rgb, ri.sigma, ri.disparity_src, ri.xyz_tgt, ri.rvec, ri.tvec, ri.K_inv, ri.K,
+                                     g_rgb=wr.numpy(), g_depth=wd.numpy(), threads=3)
+    assert np.abs(got["rgb"] - ro.detach().numpy()).max() < 1e-12
+    assert np.abs(got["depth"] - do.detach().numpy()).max() < 1e-12
+    assert np.array_equal(got["mask"], mo.numpy())
+    for name, r in zip(["d_rgb", "d_sigma", "d_disparity_src", "d_xyz_tgt", "d_rvec", "d_tvec"], refs):
+        _close(name, got[name], r, 1e-9)
+
+
+def test_render_c_oracle_reproduces_golden():
+    import golden_io as G
+    z = G.load_render_case()
+    got = c_ref.render_tgt_rgb_depth(z["rgb"], z["sigma"], z["disparity_src"], z["xyz_tgt"], z["rvec"], z["tvec"], z["K_inv"],
+                                     z["K"], g_rgb=z["w_rgb"], g_depth=z["w_depth"])
+    assert np.abs(got["rgb"] - z["rgb_out"]).max() < 1e-12 and np.abs(got["depth"] - z["depth_out"]).max() < 1e-12
+    assert np.array_equal(got["mask"], z["mask_out"])
+    for k in ("rgb", "sigma", "disparity_src", "xyz_tgt", "rvec", "tvec"):
+        ref = z["d_" + k]
+        assert np.abs(got["d_" + k] - ref).max() < 1e-9 * np.abs(ref).max(), k
