@@ -182,3 +182,47 @@ def to_u8_strips(x: np.ndarray) -> np.ndarray:
     assert l == 3 and c == 3
     q = np.clip(np.rint(x * 255.0), 0, 255).astype(np.uint8)          # (N,L,C,H,W)
     return np.ascontiguousarray(q.transpose(0, 3, 1, 4, 2).reshape(n, h, 3 * w, 3))
+
+
+# --------------------------------------------------------------------------------------
+# on-disk form: raw little-endian float32 in Julia column-major order + a JSON sidecar,
+# so that a machine WITH Julia can feed the reference itself the same bytes
+# (monodepth2.jl_b200/julia/run_reference_on_dump.jl) and pin the parity this box cannot.
+# --------------------------------------------------------------------------------------
+def dump_loss_inputs(inp: LossInputs, out_dir: str) -> str:
+    """Writes x.f32, disp<k>.f32, rvec<s>.f32, tvec<s>.f32, K.f32, invK.f32 and inputs.json.  A C-contiguous
+    (N,L,C,H,W) array IS the Julia (W,H,C,L,N) array, so the bytes are written as they are."""
+    import json
+    import os
+    os.makedirs(out_dir, exist_ok=True)
+
+    def put(name, a):
+        np.ascontiguousarray(a, dtype="<f4").tofile(os.path.join(out_dir, name))
+
+    put("x.f32", inp.x)
+    meta = {"julia_shapes": {"x": [inp.W, inp.H, inp.C, 3, inp.N]}, "dtype": "float32 little-endian, Julia column-major",
+            "target_id": inp.target_id, "source_ids": list(inp.source_ids), "scales": [float(s) for s in inp.scales],
+            "automasking": bool(inp.automasking), "min_depth": 0.1, "max_depth": 100.0, "disparity_smoothness": 1e-3}
+    for k, d in enumerate(inp.disparities):
+        put(f"disp{k}.f32", d)
+        meta["julia_shapes"][f"disp{k}"] = [d.shape[-1], d.shape[-2], 1, inp.N]
+    for s, (r, t) in enumerate(zip(inp.rvecs, inp.tvecs)):
+        put(f"rvec{s}.f32", r); put(f"tvec{s}.f32", t)
+        meta["julia_shapes"][f"rvec{s}"] = [3, inp.N]
+        meta["julia_shapes"][f"tvec{s}"] = [3, 1, inp.N]
+    put("K.f32", inp.K); put("invK.f32", inp.invK)
+    meta["julia_shapes"]["K"] = [3, 3]; meta["julia_shapes"]["invK"] = [3, 3]
+    path = os.path.join(out_dir, "inputs.json")
+    with open(path, "w") as f:
+        json.dump(meta, f, indent=1)
+    return path
+
+
+if __name__ == "__main__":
+    import argparse
+    ap = argparse.ArgumentParser(description="dump a BASELINE configuration's synthetic inputs for a Julia run of the reference")
+    ap.add_argument("config", choices=sorted(CONFIGS))
+    ap.add_argument("out_dir")
+    ap.add_argument("--batch", type=int, default=0)
+    a = ap.parse_args()
+    print(dump_loss_inputs(make_config(a.config, **({"N": a.batch} if a.batch else {})), a.out_dir))

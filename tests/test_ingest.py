@@ -73,3 +73,16 @@ def test_host_loss_from_u8_strips_matches_f32_path():
         assert torch.equal(u, v)
     plan = mdb200.HostLoss(x_format="u8_strip", **kw)
     assert plan.h2d_bytes < mdb200.HostLoss(**kw).h2d_bytes * 0.45
+
+
+def test_dump_for_a_julia_run_round_trips(tmp_path):
+    """the synthetic inputs on disk as raw little-endian float32 in Julia column-major order."""
+    import json
+    inp = synth.make_loss_inputs(24, 10, 2, seed=6)
+    meta = json.load(open(synth.dump_loss_inputs(inp, str(tmp_path))))
+    assert meta["julia_shapes"]["x"] == [24, 10, 3, 3, 2] and meta["julia_shapes"]["disp3"] == [24, 10, 1, 2]
+    x = np.fromfile(tmp_path / "x.f32", dtype="<f4")
+    # Julia's x[w,h,c,l,n] (1-based, column-major) is the flat element (w-1) + W((h-1) + H((c-1) + C((l-1) + L(n-1))))
+    w, h, c, l, n = 5, 3, 2, 1, 2
+    assert x[(w - 1) + 24 * ((h - 1) + 10 * ((c - 1) + 3 * ((l - 1) + 3 * (n - 1))))] == inp.x[n - 1, l - 1, c - 1, h - 1, w - 1]
+    assert np.array_equal(np.fromfile(tmp_path / "rvec1.f32", dtype="<f4").reshape(2, 3), inp.rvecs[1])
