@@ -9,20 +9,24 @@
 
 namespace {
 
-constexpr int ING_THREADS = 256;
+constexpr int ING_THREADS = 256;   // == the size of the N0f8 table
 
 // Float32(::N0f8) = u / 255 in float32, correctly rounded (FixedPointNumbers, third-party)
 MDB_DEV float n0f8(unsigned char u) { return __fdiv_rn((float)u, 255.0f); }
 
-// one block per (strip row h, item n): stage the 9W source bytes in shared memory with wide loads,
-// then write the 3 (frames) x C planes' rows coalesced along w
+// One block per (strip row h, item n): stage the 9W source bytes in shared memory with 128-bit streaming
+// loads, then write the 3 (frames) x C plane rows coalesced along w.  Float32(::N0f8) is an IEEE division;
+// it is done 256 times per block into a table instead of once per output, and the output loop has no
+// integer division (plane index outside, w inside).
 __global__ void __launch_bounds__(ING_THREADS)
 ingest_triplet_u8_kernel(const unsigned char* __restrict__ strips, const unsigned char* __restrict__ flip,
                          int W, int H, int gray, float* __restrict__ x) {
   extern __shared__ __align__(16) unsigned char row[];
+  __shared__ float lut[256];
   const int h = blockIdx.x, n = blockIdx.y;
   const int nbytes = 9 * W;
   const unsigned char* src = strips + ((size_t)n * H + h) * nbytes;
+  lut[threadIdx.x] = n0f8((unsigned char)threadIdx.x);        // ING_THREADS == 256
   if ((((uintptr_t)src) & 15) == 0 && (nbytes & 15) == 0) {
     const uint4* s4 = reinterpret_cast<const uint4*>(src);
     uint4* r4 = reinterpret_cast<uint4*>(row);
@@ -35,19 +39,25 @@ ingest_triplet_u8_kernel(const unsigned char* __restrict__ strips, const unsigne
   const int C = gray ? 1 : 3;
   const size_t plane = (size_t)H * W;
   float* out = x + (size_t)n * 3 * C * plane + (size_t)h * W;
-  for (int idx = threadIdx.x; idx < 3 * C * W; idx += ING_THREADS) {
-    const int lc = idx / W, w = idx - lc * W;
-    const int l = lc / C, c = lc - l * C;
-    const unsigned char* p = row + ((size_t)l * W + (f ? W - 1 - w : w)) * 3;
-    float v;
+  for (int l = 0; l < 3; ++l) {
+    const unsigned char* fr = row + (size_t)l * W * 3;
     if (gray) {
       // Gray{Float32}(::RGB{N0f8}) = 0.299f0 r + 0.587f0 g + 0.114f0 b, products and sums rounded one by one
       // (Colors.jl, third-party; Julia does not contract to FMA)                    src/dtk.jl:33-35
-      v = __fadd_rn(__fadd_rn(__fmul_rn(0.299f, n0f8(p[0])), __fmul_rn(0.587f, n0f8(p[1]))), __fmul_rn(0.114f, n0f8(p[2])));
+      float* o = out + (size_t)l * plane;
+      for (int w = threadIdx.x; w < W; w += ING_THREADS) {
+        const unsigned char* p = fr + (f ? W - 1 - w : w) * 3;
+        const float v = __fadd_rn(__fadd_rn(__fmul_rn(0.299f, lut[p[0]]), __fmul_rn(0.587f, lut[p[1]])),
+                                  __fmul_rn(0.114f, lut[p[2]]));
+        __stcs(o + w, v);
+      }
     } else {
-      v = n0f8(p[c]);
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        float* o = out + (size_t)(l * 3 + c) * plane;
+        for (int w = threadIdx.x; w < W; w += ING_THREADS) __stcs(o + w, lut[fr[(f ? W - 1 - w : w) * 3 + c]]);
+      }
     }
-    __stcs(out + (size_t)lc * plane + w, v);
   }
 }
 
