@@ -5,6 +5,7 @@
 //    mean(automasking_loss(ssim, x, target; source_ids)) > alpha.
 // Both are deterministic (fixed-order sums in double).
 #include "mdb_common.cuh"
+#include <cooperative_groups.h>
 
 namespace {
 
@@ -49,14 +50,50 @@ __global__ void pose_head_bwd_kernel(const float* __restrict__ d_rvec, const flo
   }
 }
 
-__global__ void __launch_bounds__(HEAD_THREADS)
+// One thread-block CLUSTER of 8 CTAs per item: each CTA sums a slab (128-bit loads where aligned), the
+// partial sums meet in CTA 0 through distributed shared memory in rank order -- one launch, no workspace,
+// no atomics, bit-reproducible.
+constexpr int IM_CLUSTER = 8;
+
+__global__ void __cluster_dims__(IM_CLUSTER, 1, 1) __launch_bounds__(HEAD_THREADS)
 item_mean_kernel(const float* __restrict__ map, long long per_item, float* __restrict__ out) {
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
   __shared__ double red[HEAD_THREADS / 32];
-  const float* p = map + (size_t)blockIdx.x * per_item;
+  __shared__ double slab_sum;
+  const unsigned rank = cluster.block_rank();
+  const long long item = blockIdx.x / IM_CLUSTER;
+  const float* p = map + (size_t)item * per_item;
+  const long long chunk = (per_item + IM_CLUSTER - 1) / IM_CLUSTER;
+  const long long lo = rank * chunk, hi = lo + chunk < per_item ? lo + chunk : per_item;
   double acc = 0.0;
-  for (long long i = threadIdx.x; i < per_item; i += HEAD_THREADS) acc += (double)ldg(p + i);
+  if (lo < hi) {
+    const float* q = p + lo;
+    const long long n = hi - lo;
+    long long head = (4 - (((uintptr_t)q >> 2) & 3)) & 3;          // elements before the first 16-byte boundary
+    if (head > n) head = n;
+    for (long long i = threadIdx.x; i < head; i += HEAD_THREADS) acc += (double)ldg(q + i);
+    const float4* q4 = reinterpret_cast<const float4*>(q + head);
+    const long long n4 = (n - head) / 4;
+    float s0 = 0.0f, s1 = 0.0f, s2 = 0.0f, s3 = 0.0f;
+    long long i = threadIdx.x;
+    for (; i < n4; i += HEAD_THREADS) {
+      const float4 v = __ldg(q4 + i);
+      s0 += v.x; s1 += v.y; s2 += v.z; s3 += v.w;
+      if ((i / HEAD_THREADS & 63) == 63) { acc += ((double)s0 + s1) + ((double)s2 + s3); s0 = s1 = s2 = s3 = 0.0f; }   // bound the float run
+    }
+    acc += ((double)s0 + s1) + ((double)s2 + s3);
+    for (long long j = head + 4 * n4 + threadIdx.x; j < n; j += HEAD_THREADS) acc += (double)ldg(q + j);
+  }
   const double s = block_sum_d(acc, red);
-  if (threadIdx.x == 0) out[blockIdx.x] = (float)(s / (double)per_item);
+  if (threadIdx.x == 0) slab_sum = s;
+  cluster.sync();
+  if (rank == 0 && threadIdx.x == 0) {
+    double tot = 0.0;
+    for (unsigned r = 0; r < IM_CLUSTER; ++r) tot += *cluster.map_shared_rank(&slab_sum, r);
+    out[item] = (float)(tot / (double)per_item);
+  }
+  cluster.sync();   // keep every CTA's shared memory alive until rank 0 has read it
 }
 
 }  // namespace
@@ -89,7 +126,7 @@ int32_t mdb_item_mean(mdb_handle* h, const float* map, int64_t per_item, int32_t
   MDB_REQUIRE(h, h != nullptr, MDB_E_INVALID_ARG, "null handle");
   MDB_REQUIRE(h, map && out, MDB_E_INVALID_ARG, "mdb_item_mean: null pointer");
   MDB_REQUIRE(h, per_item >= 1 && N >= 1, MDB_E_SHAPE, "mdb_item_mean: need per_item, N >= 1");
-  item_mean_kernel<<<N, HEAD_THREADS, 0, (cudaStream_t)stream>>>(map, (long long)per_item, out);
+  item_mean_kernel<<<N * IM_CLUSTER, HEAD_THREADS, 0, (cudaStream_t)stream>>>(map, (long long)per_item, out);
   MDB_LAUNCHED(h);
   return MDB_OK;
 }

@@ -174,6 +174,10 @@ __global__ void photo_kernel(PhotoArgs a) {
   }
 }
 
+}  // namespace
+#include "photo_stream.inl"
+namespace {
+
 __global__ void min2_kernel(const float* __restrict__ a, const float* __restrict__ b, int64_t n, float* __restrict__ out) {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     out[i] = fminf(a[i], b[i]);
@@ -305,6 +309,13 @@ int32_t mdb_warp(mdb_handle* h, const float* disp, const float* x, const float* 
 
 static int32_t photo_launch(mdb_handle* h, PhotoArgs& a, void* stream) {
   MDB_REQUIRE(h, a.W >= 2 && a.H >= 2 && a.C >= 1 && a.N >= 1, MDB_E_SHAPE, "SSIM needs W,H >= 2 (reflect pad)");
+  // the streaming kernel covers the shapes the path uses (C in {1,3}, one or two sources); anything else
+  // (C = 2, 4, ...; 3-4 predictions) runs the per-pixel kernel
+  cudaStream_t st = (cudaStream_t)stream;
+  if (a.C == 3 && a.S == 2) return photo_stream_launch<3, 2>(h, a, st);
+  if (a.C == 3 && a.S == 1) return photo_stream_launch<3, 1>(h, a, st);
+  if (a.C == 1 && a.S == 2) return photo_stream_launch<1, 2>(h, a, st);
+  if (a.C == 1 && a.S == 1) return photo_stream_launch<1, 1>(h, a, st);
   photo_kernel<<<grid_for(h, (int64_t)a.W * a.H * a.N, 128), 128, 0, (cudaStream_t)stream>>>(a);
   MDB_LAUNCHED(h);
   return MDB_OK;

@@ -44,3 +44,19 @@ def test_find_static_statistic_and_threshold():
     assert means[1].item() < 1e-6 and not keep[1].item()        # SSIM(x, x) = 0 up to the approximate reciprocal
     assert np.array_equal(keep.cpu().numpy(), ref > alpha)
     assert torch.equal(means, mdb200.find_static(xd, alpha)[1])      # deterministic
+
+
+@pytest.mark.parametrize("N,per_item", [(3, 1), (2, 7), (5, 1031), (4, 64 * 24), (2, 320 * 1024 + 3)])
+def test_item_mean_cluster_reduction(N, per_item):
+    """8-CTA cluster + distributed shared memory: odd sizes, unaligned slabs, fewer elements than CTAs."""
+    import mdb200
+    g = torch.Generator().manual_seed(per_item)
+    m = torch.randn(N, per_item, generator=g, dtype=torch.float32)
+    got = mdb200.item_mean(m.to(DEV))
+    ref = m.double().mean(dim=1)
+    assert (got.double().cpu() - ref).abs().max() < 2e-7 * max(1.0, m.abs().max().item())
+    assert torch.equal(got, mdb200.item_mean(m.to(DEV)))                  # deterministic
+    # an unaligned base pointer
+    pad = torch.zeros(N * per_item + 1, device=DEV)
+    pad[1:] = m.reshape(-1).to(DEV)
+    assert torch.equal(mdb200.item_mean(pad[1:].view(N, per_item)), got)
