@@ -184,35 +184,84 @@ __global__ void min2_kernel(const float* __restrict__ a, const float* __restrict
 }
 
 // ---- smooth_loss (S2) -- src/utils.jl:163-177 -----------------------------------------
-constexpr int SM_THREADS = 256, SM_ROWS = 8;
+constexpr int SM_THREADS = 256, SM_ROWS = 16;
 
+// Thread = column, walking down SM_ROWS rows: the row below is loaded one step ahead, the vertical edge
+// weight is carried to the next row, the horizontal one comes from the left lane by shuffle -- each edge's
+// exp(-mean_c |dI|) is evaluated once (twice only at warp / block seams), each element loaded once.
+template <int C>
 __global__ void __launch_bounds__(SM_THREADS)
-smooth_kernel(const float* __restrict__ disp, const float* __restrict__ img, int W, int H, int C, int N,
+smooth_kernel(const float* __restrict__ disp, const float* __restrict__ img, int W, int H, int N,
               float kx, float ky, float* __restrict__ part, float* __restrict__ grad) {
   const int n = blockIdx.y, rb = blockIdx.x;
   const size_t plane = (size_t)W * H;
   const float* d = disp + n * plane;
   const float* im = img + (size_t)n * C * plane;
   const int y0 = rb * SM_ROWS, y1 = min(y0 + SM_ROWS, H);
+  const int lane = threadIdx.x & 31;
+  const float invC = 1.0f / (float)C;
   float ax = 0.0f, ay = 0.0f;
-  for (int i = threadIdx.x; i < (y1 - y0) * W; i += SM_THREADS) {
-    const int gy = y0 + i / W, gx = i % W;
-    const size_t o = (size_t)gy * W + gx;
-    const float v = d[o];
-    float g = 0.0f;
-    auto wgt = [&](size_t o0, size_t o1) {
-      float e = 0.0f;
-      for (int c = 0; c < C; ++c) e += fabsf(im[c * plane + o0] - im[c * plane + o1]);
-      return expf(-e / (float)C);
-    };
-    if (gx + 1 < W) { const float df = v - d[o + 1]; const float w = wgt(o, o + 1); ax += fabsf(df) * w; g += kx * sgnf(df) * w; }
-    if (gx > 0) { const float df = d[o - 1] - v; g -= kx * sgnf(df) * wgt(o - 1, o); }
-    if (gy + 1 < H) { const float df = v - d[o + W]; const float w = wgt(o, o + W); ay += fabsf(df) * w; g += ky * sgnf(df) * w; }
-    if (gy > 0) { const float df = d[o - W] - v; g -= ky * sgnf(df) * wgt(o - W, o); }
-    if (grad) grad[n * plane + o] = g;
+  auto edge = [&](const float* Ia, const float* Ib) {     // exp(-mean_c |Ia - Ib|)   src/utils.jl:168-172
+    float e = 0.0f;
+#pragma unroll
+    for (int c = 0; c < C; ++c) e += fabsf(Ia[c] - Ib[c]);
+    return __expf(-e * invC) ;
+  };
+  for (int gx0 = 0; gx0 < W; gx0 += SM_THREADS) {
+    const int gx = gx0 + threadIdx.x;
+    const bool cv = gx < W;
+    const int gxc = cv ? gx : W - 1;
+    float v, I[C], vd = 0.0f, Id[C], tup = 0.0f;          // tup: ky sign(df) w of the edge to the row above
+    v = ldg(d + (size_t)y0 * W + gxc);
+#pragma unroll
+    for (int c = 0; c < C; ++c) { I[c] = ldg(im + c * plane + (size_t)y0 * W + gxc); Id[c] = 0.0f; }
+    if (y0 > 0) {                                          // seam: the edge to the previous block's last row
+      float Iu[C];
+#pragma unroll
+      for (int c = 0; c < C; ++c) Iu[c] = ldg(im + c * plane + (size_t)(y0 - 1) * W + gxc);
+      const float df = ldg(d + (size_t)(y0 - 1) * W + gxc) - v;
+      tup = ky * sgnf(df) * edge(Iu, I);
+    }
+    for (int gy = y0; gy < y1; ++gy) {
+      const bool has_dn = gy + 1 < H;
+      if (has_dn) {
+        vd = ldg(d + (size_t)(gy + 1) * W + gxc);
+#pragma unroll
+        for (int c = 0; c < C; ++c) Id[c] = ldg(im + c * plane + (size_t)(gy + 1) * W + gxc);
+      }
+      // right neighbour: lane + 1, or a load at the warp seam
+      float vr = __shfl_down_sync(MDB_FULL, v, 1), Ir[C];
+#pragma unroll
+      for (int c = 0; c < C; ++c) Ir[c] = __shfl_down_sync(MDB_FULL, I[c], 1);
+      const bool has_r = gx + 1 < W;
+      if (lane == 31 && has_r) {
+        vr = ldg(d + (size_t)gy * W + gx + 1);
+#pragma unroll
+        for (int c = 0; c < C; ++c) Ir[c] = ldg(im + c * plane + (size_t)gy * W + gx + 1);
+      }
+      float g = 0.0f, tr = 0.0f;
+      if (cv && has_r) { const float df = v - vr, w = edge(I, Ir); ax += fabsf(df) * w; tr = kx * sgnf(df) * w; g += tr; }
+      // left edge = the left lane's right edge
+      float tl = __shfl_up_sync(MDB_FULL, tr, 1);
+      if (lane == 0 && cv && gx > 0) {
+        float Il[C];
+#pragma unroll
+        for (int c = 0; c < C; ++c) Il[c] = ldg(im + c * plane + (size_t)gy * W + gx - 1);
+        const float df = ldg(d + (size_t)gy * W + gx - 1) - v;
+        tl = kx * sgnf(df) * edge(Il, I);
+      }
+      if (cv && gx > 0) g -= tl;
+      g -= tup;
+      tup = 0.0f;
+      if (cv && has_dn) { const float df = v - vd, w = edge(I, Id); ay += fabsf(df) * w; tup = ky * sgnf(df) * w; g += tup; }
+      if (grad && cv) grad[n * plane + (size_t)gy * W + gx] = g;
+      v = vd;
+#pragma unroll
+      for (int c = 0; c < C; ++c) I[c] = Id[c];
+    }
   }
   __shared__ float red[SM_THREADS / 32][2];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int warp = threadIdx.x >> 5;
   ax = warp_sum(ax); ay = warp_sum(ay);
   if (lane == 0) { red[warp][0] = ax; red[warp][1] = ay; }
   __syncthreads();
@@ -383,14 +432,21 @@ int32_t mdb_smooth_loss(mdb_handle* h, const float* disparity, const float* imag
                         int32_t C, int32_t N, float* loss, float* d_disparity, void* workspace,
                         size_t workspace_bytes, void* stream) {
   MDB_REQUIRE(h, h && disparity && image && loss, MDB_E_INVALID_ARG, "mdb_smooth_loss: null argument");
-  MDB_REQUIRE(h, W >= 2 && H >= 2 && C >= 1 && N >= 1, MDB_E_SHAPE, "mdb_smooth_loss: need W,H >= 2");
+  MDB_REQUIRE(h, W >= 2 && H >= 2 && C >= 1 && C <= 4 && N >= 1 && N <= 65535, MDB_E_SHAPE,
+              "mdb_smooth_loss: need W,H >= 2, 1 <= C <= 4, N <= 65535");
   MDB_REQUIRE(h, workspace && workspace_bytes >= mdb_smooth_loss_workspace_bytes(W, H, N) && ((uintptr_t)workspace & 255) == 0,
               MDB_E_WORKSPACE, "mdb_smooth_loss: workspace too small or misaligned");
   const int rb = (H + SM_ROWS - 1) / SM_ROWS;
   const double kx = 1.0 / ((double)(W - 1) * H * N), ky = 1.0 / ((double)W * (H - 1) * N);
   dim3 grid(rb, N);
-  smooth_kernel<<<grid, SM_THREADS, 0, (cudaStream_t)stream>>>(disparity, image, W, H, C, N, (float)kx, (float)ky,
-                                                               (float*)workspace, d_disparity);
+  cudaStream_t st = (cudaStream_t)stream;
+  float* part = (float*)workspace;
+  switch (C) {
+    case 1: smooth_kernel<1><<<grid, SM_THREADS, 0, st>>>(disparity, image, W, H, N, (float)kx, (float)ky, part, d_disparity); break;
+    case 2: smooth_kernel<2><<<grid, SM_THREADS, 0, st>>>(disparity, image, W, H, N, (float)kx, (float)ky, part, d_disparity); break;
+    case 3: smooth_kernel<3><<<grid, SM_THREADS, 0, st>>>(disparity, image, W, H, N, (float)kx, (float)ky, part, d_disparity); break;
+    default: smooth_kernel<4><<<grid, SM_THREADS, 0, st>>>(disparity, image, W, H, N, (float)kx, (float)ky, part, d_disparity); break;
+  }
   MDB_LAUNCHED(h);
   smooth_finalize_kernel<<<1, 256, 0, (cudaStream_t)stream>>>((const float*)workspace, rb * N, kx, ky, loss);
   MDB_LAUNCHED(h);
