@@ -701,7 +701,7 @@ class HostLoss:
     contract the multi-GPU shards use, so chunk losses simply add."""
 
     def __init__(self, *, W, H, C, L, N, disp_sizes, scales, target_id, source_ids, K, invK, chunk=8,
-                 automasking=False, n_global=0, device=None, x_format="f32", **kw):
+                 automasking=False, n_global=0, device=None, x_format="f32", ramp_up=None, **kw):
         """x_format "f32": x is the Float32 (N,L,C,H,W) stack.  "u8_strip": x is the dataset's own format,
         uint8 (N,H,3W,3) decoded triplet strips (src/dtk.jl:29-46) -- a quarter of the PCIe bytes; the
         device converts with mdb_ingest_triplet_u8 (C = 1: Gray luma)."""
@@ -710,6 +710,8 @@ class HostLoss:
         if x_format == "u8_strip" and L != 3:
             raise ValueError("triplet strips hold L = 3 frames")
         self.x_format = x_format
+        if ramp_up is None:
+            ramp_up = x_format == "u8_strip"
         self.dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         self.N, self.L, self.C, self.H, self.W = N, L, C, H, W
         self.S = len(source_ids)
@@ -719,6 +721,10 @@ class HostLoss:
         # before the next one has arrived; what is NOT hidden is the work on the LAST chunk after its copy
         # lands.  Hence chunks of `chunk` items and a geometric tail (half, quarter, ... down to 1 item).
         sizes, left = [], N
+        if ramp_up:            # compute-bound pipelines (uint8 input): start computing after one item has arrived
+            z = 1
+            while z < chunk and left - z > chunk:
+                sizes.append(z); left -= z; z *= 2
         while left > chunk:
             sizes.append(chunk); left -= chunk
         while left > 1:
