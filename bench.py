@@ -77,48 +77,67 @@ def algorithmic_bytes(inp, N):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
-         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons DURING the timed region (B200_PROFILING.md's clocks line).  NVML -- what
+    nvidia-smi itself reads -- polled from a thread of this process: the first sample lands milliseconds after
+    start() (an `nvidia-smi -lms` child needs over a second to come up on an 8-GPU box, longer than a short
+    timed region), and sample_now() takes one more from the main thread while the timed steps are queued."""
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
-    def __init__(self, gpu_index):
-        self.idx, self.proc, self.path = gpu_index, None, f"/tmp/mdb_clocks_{os.getpid()}.csv"
+    def __init__(self, device):
+        self.h, self.nv, self.samples, self.thread, self.run = None, None, [], None, False
+        try:
+            import torch
+            import pynvml as nv
+            nv.nvmlInit()
+            self.nv = nv
+            try:
+                uuid = str(torch.cuda.get_device_properties(device).uuid)
+                self.h = nv.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+            except Exception:
+                vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+                idx = device.index or 0
+                self.h = nv.nvmlDeviceGetHandleByIndex(int(vis.split(",")[idx]) if vis else idx)
+            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM))
+            self.bits = [nv.nvmlClocksEventReasonHwSlowdown, nv.nvmlClocksEventReasonHwThermalSlowdown,
+                         nv.nvmlClocksEventReasonSwThermalSlowdown, nv.nvmlClocksEventReasonSwPowerCap]
+        except Exception as e:   # no NVML: say so in the line rather than fail the bench
+            self.h, self.err = None, f"{type(e).__name__}: {e}"
+
+    def sample_now(self):
+        if self.h is None:
+            return
+        nv = self.nv
+        try:
+            mhz = float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+            mask = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+            self.samples.append((mhz, mask))
+        except Exception:
+            pass
+
+    def _loop(self):
+        while self.run:
+            self.sample_now()
+            time.sleep(0.005)
 
     def start(self):
-        try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-i", str(self.idx), "-lms", "100"], stdout=open(self.path, "w"),
-                                         stderr=subprocess.DEVNULL)
-        except Exception:
-            self.proc = None
+        if self.h is None:
+            return
+        import threading
+        self.samples, self.run = [], True
+        self.thread = threading.Thread(target=self._loop, daemon=True)
+        self.thread.start()
 
     def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for line in open(self.path):
-            f = [c.strip() for c in line.split(",")]
-            if len(f) < 9:
-                continue
-            try:
-                sm.append(float(f[1])); mx.append(float(f[2]))
-            except ValueError:
-                continue
-            for nm, v in zip(names, f[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(nm)
-        if not sm:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+        if self.h is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [f"NVML unavailable ({self.err})"]}
+        self.run = False
+        self.thread.join(timeout=2)
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["no samples"]}
+        sm = sorted(m for m, _ in self.samples)
+        reasons = sorted({nm for _, mask in self.samples for nm, bit in zip(self.NAMES, self.bits) if mask & bit})
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": self.max_mhz, "reasons": reasons, "samples": len(sm),
+                "source": "NVML, polled during the timed region"}
 
 
 def make_inputs(args):
@@ -198,6 +217,9 @@ def run_ours(args):
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
+    # host threads (and, by first touch, the pinned staging buffers below) onto the GPU's own NUMA node
+    from mdb200 import dist as mdist
+    numa = mdist.bind_host_to_device(dev)
 
     inp, kw = make_inputs(args)
     N, W, H, C = inp.N, inp.W, inp.H, inp.C
@@ -238,7 +260,7 @@ def run_ours(args):
     for _ in range(max(args.warmup, 3)):
         step()
     sync_all()
-    sampler = ClockSampler(local_rank)
+    sampler = ClockSampler(dev)
     mdb200.profile_begin(args.steps)
     l0 = mdb200.launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -248,6 +270,7 @@ def run_ours(args):
     for _ in range(args.steps):
         res = step()
     ev1.record()
+    sampler.sample_now()   # the timed steps are queued or running: at least one sample under load
     sync_all()
     clocks = sampler.stop()
     launches = mdb200.launch_count() - l0
@@ -280,7 +303,7 @@ def run_ours(args):
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         e2e = {"value": units_per_rank * world * e_steps / float(dt), "unit": UNIT,
                "h2d_bytes_per_step": hplan.h2d_bytes * world, "d2h_bytes_per_step": hplan.d2h_bytes * world,
-               "ms_per_step": float(dt) / e_steps * 1e3, "steps": e_steps,
+               "ms_per_step": float(dt) / e_steps * 1e3, "steps": e_steps, "host_numa_binding": numa,
                "loss_matches_device_path": bool(abs(hres.loss * (1 if world == 1 else 1) - float(res.loss)) <= 1e-5 * abs(float(res.loss)))}
         # the same call fed the dataset's own format (src/dtk.jl:29-46): uint8 triplet strips, converted on the
         # device (mdb_ingest_triplet_u8) -- a quarter of the image bytes over PCIe.  Auxiliary: the headline

@@ -59,3 +59,31 @@ def allreduce_loss_posegrads(packed: torch.Tensor, group=None) -> torch.Tensor:
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.all_reduce(packed, op=dist.ReduceOp.SUM, group=group)
     return packed
+
+
+def bind_host_to_device(device) -> dict:
+    """Pin this rank's host threads to the CPUs NVML reports as local to `device` (its NUMA node), BEFORE the
+    pinned staging buffers are allocated: first-touch then places them on the node the GPU's PCIe root hangs
+    off, and the H2D / D2H copies of the ranks stop crossing the socket interconnect.  One process per GPU
+    makes this a per-process setting.  Returns what was done; never raises (a cpuset that excludes the ideal
+    CPUs, or no NVML, leaves the affinity alone)."""
+    import os
+    info = {"bound": False}
+    try:
+        import pynvml as nv
+        nv.nvmlInit()
+        dev = torch.device(device)
+        uuid = str(torch.cuda.get_device_properties(dev).uuid)
+        h = nv.nvmlDeviceGetHandleByUUID(uuid if uuid.startswith("GPU-") else "GPU-" + uuid)
+        ncpu = os.cpu_count() or 1
+        words = nv.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        ideal = {64 * i + b for i, w in enumerate(words) for b in range(64) if (int(w) >> b) & 1}
+        allowed = os.sched_getaffinity(0)
+        cpus = ideal & allowed
+        info.update(ideal=len(ideal), allowed=len(allowed))
+        if cpus and cpus != allowed:
+            os.sched_setaffinity(0, cpus)
+            info.update(bound=True, cpus=len(cpus))
+    except Exception as e:   # noqa: BLE001 -- advisory only
+        info["error"] = f"{type(e).__name__}: {e}"
+    return info

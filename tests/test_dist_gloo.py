@@ -78,3 +78,15 @@ def test_two_rank_allreduce_matches_single_process():
     for s in range(2):
         assert np.allclose(grv[s], ref["d_rvec"][s].numpy(), rtol=1e-5, atol=1e-8)
         assert np.allclose(gtv[s], ref["d_tvec"][s].numpy(), rtol=1e-5, atol=1e-8)
+
+
+def test_bind_host_to_device_is_advisory():
+    """No NVML / no GPU here: the call reports why it did nothing and leaves the affinity alone."""
+    import os
+    from mdb200 import dist as mdist
+    before = os.sched_getaffinity(0)
+    info = mdist.bind_host_to_device("cuda:0")
+    assert isinstance(info, dict) and "bound" in info
+    if not info["bound"]:
+        assert os.sched_getaffinity(0) == before
+    os.sched_setaffinity(0, before)
