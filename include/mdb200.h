@@ -228,6 +228,42 @@ int32_t mdb_render_tgt_rgb_depth_bwd(mdb_handle* h, const float* rgb, const floa
                                      float* d_xyz_tgt, float* d_disparity_src, float* d_rvec, float* d_tvec,
                                      void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- render variants ------------------------------------------------------
+ * What the reference's own comparison script quotes from MINE as the intended sampler
+ * (test/test_sample.jl:123-137) and the TODOs of src/render.jl:22,36,40,47,52, behind options; all zero
+ * (or opts == NULL) is the code as written.
+ *   mine_grid  grid = (x + 0.5) / (W/2) - 1 sampled with align_corners=false, border padding: the sample
+ *              lands on source pixel x itself (as written: no "- 1", align-corners=true; SURVEY F8a,b)
+ *   mine_mask  valid = -1 < x < W and -1 < y < H   (as written: x > 0 and y > 0)
+ *   depth_eps  expected depth = sum_k w_k z_k / (sum_k w_k + depth_eps), written to `expected_depth`
+ *              (W,H,1,B) when that pointer is given ("TODO: return depth?", src/render.jl:47);
+ *              `weights_sum` (W,H,1,B) = sum_k w_k is what the pullback needs back
+ * xyz_tgt == NULL folds the producers in: xyz_tgt is what get_tgt_xyz_from_plane_disparity(
+ * get_src_xyz_from_plane_disparity(create_meshgrid(H, W), disparity_src, K_inv), pose) would hold
+ * (src/render.jl:21-30, 51-62), evaluated at the sample point -- the 3 W H Np B array is never
+ * materialised, and in the pullback its gradient flows on into d_disparity_src / d_rvec / d_tvec
+ * (d_xyz_tgt must be NULL too).                                                                  */
+typedef struct mdb_render_opts {
+  int32_t mine_grid;
+  int32_t mine_mask;
+  float depth_eps;   /* 1e-5 when opts == NULL */
+  int32_t reserved;
+} mdb_render_opts;
+int32_t mdb_render_tgt_rgb_depth_fwd_ex(mdb_handle* h, const float* rgb, const float* sigma, const float* disparity_src,
+                                        const float* xyz_tgt, const float* rvec, const float* tvec, const float* K_inv,
+                                        const float* K, int32_t W, int32_t H, int32_t Np, int32_t B,
+                                        const mdb_render_opts* opts, float* rgb_out, float* depth_out, int32_t* mask_out,
+                                        float* expected_depth, float* weights_sum, void* workspace, size_t workspace_bytes,
+                                        void* stream);
+int32_t mdb_render_tgt_rgb_depth_bwd_ex(mdb_handle* h, const float* rgb, const float* sigma, const float* disparity_src,
+                                        const float* xyz_tgt, const float* rvec, const float* tvec, const float* K_inv,
+                                        const float* K, int32_t W, int32_t H, int32_t Np, int32_t B,
+                                        const mdb_render_opts* opts, const float* depth_saved,
+                                        const float* expected_depth_saved, const float* weights_sum_saved,
+                                        const float* g_rgb_out, const float* g_depth, const float* g_expected_depth,
+                                        float* d_rgb, float* d_sigma, float* d_xyz_tgt, float* d_disparity_src,
+                                        float* d_rvec, float* d_tvec, void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- the optimiser loop of slow_depth  (src/simple_depth.jl:14-16, 22-42) ----
  * Flux.Optimise.update!(ADAM(eta, (beta1, beta2)), theta, grads) over a list of tensors (third-party
  * Flux.jl, unpinned; semantics restated in oracle/torch_ref.py::flux_adam_step):

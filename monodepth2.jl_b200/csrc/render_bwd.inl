@@ -13,6 +13,10 @@ struct RenderBwdArgs {
   int W, H, Np, B;
   float Kinv_f[9];
   const float* tvec;        // [B][3]
+  const float* edepth;      // saved expected depth and sum of weights [B][1][H][W], and the depth's cotangent, or null
+  const float* wsum;
+  const float* g_edepth;
+  float depth_eps;
   float4* acc;              // [B Np][H W][2] zero-initialised: {d rgb, d sigma}, {d xyz, 0}; accumulated with
                             // 128-bit red.global.add.v4.f32 (one L2 reduction per tap and channel GROUP)
   float* part_pose;         // [B][blocks][12]
@@ -29,6 +33,8 @@ struct Pend {
   float dix, diy;         // contribution of the rgb + sigma channels, complete
   float gx[3];            // d L / d(sampled xyz) received so far (from the later plane's distance)
   float X0, X1, X2, x, y;
+  float q0, q1;           // clamped sample point, 1-based (FUSED)
+  float xyz[3];           // sampled xyz (FUSED: R xyz_src + t at the sample point)
   int k;
 };
 
@@ -70,6 +76,7 @@ MDB_DEV void scatter4(float4* __restrict__ plane, int slot, const Pend& t, bool 
     if (w[j] != 0.0f) red_v4(plane + 2 * o[j] + slot, g0 * w[j], g1 * w[j], g2 * w[j], g3 * w[j]);
 }
 
+template <int FLAGS, bool FUSED>
 __global__ void __launch_bounds__(RB_THREADS) render_bwd_kernel(const __grid_constant__ RenderBwdArgs a) {
   __shared__ float s_disp[RB_THREADS / 32][RB_MAXP];
   __shared__ float s_pose[RB_THREADS / 32][12];
@@ -84,7 +91,16 @@ __global__ void __launch_bounds__(RB_THREADS) render_bwd_kernel(const __grid_con
 #pragma unroll
   for (int c = 0; c < 3; ++c) gO[c] = active ? ldg(a.g_rgb_out + ((size_t)b * 3 + c) * WH + pp) : 0.0f;
   const float t0 = a.tvec[3 * b], t1 = a.tvec[3 * b + 1], t2 = a.tvec[3 * b + 2];
-  const float sxw = (float)(a.W - 1) / (float)a.W, syh = (float)(a.H - 1) / (float)a.H;
+  // d ix / d x: (W-1)/W for the grid as written (no "-1", align-corners un-normalisation), 1 for the MINE grid
+  const float sxw = (FLAGS & RV_MINE_GRID) ? 1.0f : (float)(a.W - 1) / (float)a.W;
+  const float syh = (FLAGS & RV_MINE_GRID) ? 1.0f : (float)(a.H - 1) / (float)a.H;
+  // expected depth  Z = sum w z / D,  D = sum w + eps  (both saved by the forward)
+  float gZ = 0.0f, Zs = 0.0f, invD = 0.0f;
+  if (a.g_edepth && active) {
+    gZ = ldg(a.g_edepth + (size_t)b * WH + pp);
+    Zs = ldg(a.edepth + (size_t)b * WH + pp);
+    invD = 1.0f / (ldg(a.wsum + (size_t)b * WH + pp) + a.depth_eps);
+  }
   float acc[12];
 #pragma unroll
   for (int i = 0; i < 12; ++i) acc[i] = 0.0f;
@@ -127,20 +143,34 @@ __global__ void __launch_bounds__(RB_THREADS) render_bwd_kernel(const __grid_con
       const float dsp = a.prep[kb].disp;
       acc[9] -= a0 * Y2 * dsp; acc[10] -= a1 * Y2 * dsp; acc[11] -= a2 * Y2 * dsp;
       ddisp = -(a0 * t0 + a1 * t1 + a2 * t2) * Y2;
+      if (FUSED) {
+        // xyz = R xs + t,  xs = K_inv (q0, q1, 1) / disparity   (src/render.jl:25-30, 51-62)
+        const float dep = 1.0f / dsp;
+        const float xs0 = (a.Kinv_f[0] * p.q0 + a.Kinv_f[1] * p.q1 + a.Kinv_f[2]) * dep;
+        const float xs1 = (a.Kinv_f[3] * p.q0 + a.Kinv_f[4] * p.q1 + a.Kinv_f[5]) * dep;
+        const float xs2 = (a.Kinv_f[6] * p.q0 + a.Kinv_f[7] * p.q1 + a.Kinv_f[8]) * dep;
+        acc[0] = fmaf(gx[0], xs0, acc[0]); acc[1] = fmaf(gx[0], xs1, acc[1]); acc[2] = fmaf(gx[0], xs2, acc[2]);
+        acc[3] = fmaf(gx[1], xs0, acc[3]); acc[4] = fmaf(gx[1], xs1, acc[4]); acc[5] = fmaf(gx[1], xs2, acc[5]);
+        acc[6] = fmaf(gx[2], xs0, acc[6]); acc[7] = fmaf(gx[2], xs1, acc[7]); acc[8] = fmaf(gx[2], xs2, acc[8]);
+        acc[9] += gx[0]; acc[10] += gx[1]; acc[11] += gx[2];
+        ddisp -= (gx[0] * (p.xyz[0] - t0) + gx[1] * (p.xyz[1] - t1) + gx[2] * (p.xyz[2] - t2)) * dep;
+      }
     }
-    scatter4(a.acc + (size_t)(b * a.Np + p.k) * WH * 2, 1, p, active && (gx[0] != 0.0f || gx[1] != 0.0f || gx[2] != 0.0f),
-             gx[0], gx[1], gx[2], 0.0f, lane);
+    if (!FUSED)
+      scatter4(a.acc + (size_t)(b * a.Np + p.k) * WH * 2, 1, p, active && (gx[0] != 0.0f || gx[1] != 0.0f || gx[2] != 0.0f),
+               gx[0], gx[1], gx[2], 0.0f, lane);
     ddisp = warp_sum(ddisp);
     if (lane == 0) s_disp[warp][p.k] += ddisp;
   };
 
   for (int k = a.Np - 1; k >= 0; --k) {
     const int kb = b * a.Np + k;
-    const RTaps t = render_taps(a.prep[kb].Hst, u, v, a.W, a.H);
+    const RTaps t = render_taps<FLAGS>(a.prep[kb].Hst, u, v, a.W, a.H);
     Pend cur;
     cur.o00 = t.o00; cur.o01 = t.o01; cur.o10 = t.o10; cur.o11 = t.o11;
     cur.fx = t.fx; cur.fy = t.fy; cur.mx = t.mx; cur.my = t.my;
     cur.X0 = (float)t.X0; cur.X1 = (float)t.X1; cur.X2 = (float)t.X2; cur.x = t.x; cur.y = t.y; cur.k = k;
+    cur.q0 = t.q0; cur.q1 = t.q1;
     float rgbv[3], dxr[3], dyr[3], xyzv[3];
     const float* pr = a.rgb + (size_t)kb * 3 * WH;
 #pragma unroll
@@ -158,14 +188,27 @@ __global__ void __launch_bounds__(RB_THREADS) render_bwd_kernel(const __grid_con
       dxs = fmaf(t.fy, (v11 - v10) - (v01 - v00), v01 - v00);
       dys = fmaf(t.fx, (v11 - v01) - (v10 - v00), v10 - v00);
     }
-    const float* px = a.xyz + (size_t)kb * WH * 3;
+    if (FUSED) {
+      const PlanePrep& pp_ = a.prep[kb];
 #pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      const float v00 = ldg(px + 3 * t.o00 + c), v01 = ldg(px + 3 * t.o01 + c), v10 = ldg(px + 3 * t.o10 + c), v11 = ldg(px + 3 * t.o11 + c);
-      xyzv[c] = bil(t, v00, v01, v10, v11);
-      cur.dxv[c] = fmaf(t.fy, (v11 - v10) - (v01 - v00), v01 - v00);
-      cur.dyv[c] = fmaf(t.fx, (v11 - v01) - (v10 - v00), v10 - v00);
+      for (int c = 0; c < 3; ++c) {
+        const float ax = ldg(pp_.Ax + 3 * c), ay = ldg(pp_.Ax + 3 * c + 1);
+        xyzv[c] = fmaf(ax, t.q0, fmaf(ay, t.q1, ldg(pp_.Ax + 3 * c + 2) + ldg(pp_.tx + c)));
+        cur.dxv[c] = ax;   // the slope of the affine map (the clamp masks mx, my are applied in finish)
+        cur.dyv[c] = ay;
+      }
+    } else {
+      const float* px = a.xyz + (size_t)kb * WH * 3;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const float v00 = ldg(px + 3 * t.o00 + c), v01 = ldg(px + 3 * t.o01 + c), v10 = ldg(px + 3 * t.o10 + c), v11 = ldg(px + 3 * t.o11 + c);
+        xyzv[c] = bil(t, v00, v01, v10, v11);
+        cur.dxv[c] = fmaf(t.fy, (v11 - v10) - (v01 - v00), v01 - v00);
+        cur.dyv[c] = fmaf(t.fx, (v11 - v01) - (v10 - v00), v10 - v00);
+      }
     }
+#pragma unroll
+    for (int c = 0; c < 3; ++c) cur.xyz[c] = xyzv[c];
     const bool spos = sraw >= 0.0f;
     const float sig = spos ? sraw : 0.0f;
     float dist = 1e3f, df[3] = {0, 0, 0};
@@ -178,19 +221,21 @@ __global__ void __launch_bounds__(RB_THREADS) render_bwd_kernel(const __grid_con
     const float alpha = 1.0f - T;
     const float tacc = active ? ldg(a.tacc + (size_t)kb * WH + pp) : 0.0f;
     const float gT = (active && a.g_tacc) ? ldg(a.g_tacc + (size_t)kb * WH + pp) : 0.0f;
-    const float dw = gO[0] * rgbv[0] + gO[1] * rgbv[1] + gO[2] * rgbv[2];
     const float w = tacc * alpha;
+    float dw = gO[0] * rgbv[0] + gO[1] * rgbv[1] + gO[2] * rgbv[2];   // d L / d w_k
+    dw = fmaf(gZ * invD, xyzv[2] - Zs, dw);             // d Z / d w_k = (z_k - Z) / D   (gZ = 0 without that output)
     const float tau = fmaf(dw, alpha, gT);           // total d L / d transparency_acc_k
     const float dT = Q / (T + 1e-6f) - dw * tacc;    // via the later planes' products and via alpha_k
     Q = fmaf(tau, tacc, Q);
     const float de = -T * dT;                        // T = exp(-e), e = dist * sigma
     const float gsig = spos ? de * dist : 0.0f;
     float gnext[3] = {0, 0, 0};
-    cur.gx[0] = cur.gx[1] = cur.gx[2] = 0.0f;
+    cur.gx[0] = cur.gx[1] = 0.0f;
+    cur.gx[2] = gZ * invD * w;                            // d Z / d z_k = w_k / D
     if (k < a.Np - 1) {
       const float gd = de * sig / dist;              // NaN if two sampled planes coincide, like sqrt'(0)
 #pragma unroll
-      for (int c = 0; c < 3; ++c) { gnext[c] = gd * df[c]; cur.gx[c] = -gd * df[c]; }
+      for (int c = 0; c < 3; ++c) { gnext[c] = gd * df[c]; cur.gx[c] -= gd * df[c]; }
       finish(pd, gnext);                             // plane k+1 is now complete
     }
     // rgb and sigma of plane k are complete now
@@ -241,13 +286,15 @@ __global__ void __launch_bounds__(256) render_bwd_unpack_kernel(const float4* __
                                                                 float* __restrict__ d_rgb, float* __restrict__ d_sigma,
                                                                 float* __restrict__ d_xyz) {
   for (size_t i = blockIdx.x * (size_t)256 + threadIdx.x; i < total; i += (size_t)gridDim.x * 256) {
-    const float4 q0 = __ldcs(acc + 2 * i), q1 = __ldcs(acc + 2 * i + 1);
+    const float4 q0 = __ldcs(acc + 2 * i), q1 = d_xyz ? __ldcs(acc + 2 * i + 1) : make_float4(0.f, 0.f, 0.f, 0.f);
     const size_t kb = i / WH, pix = i - kb * WH;
     float* r = d_rgb + kb * 3 * WH + pix;
     r[0] = q0.x; r[WH] = q0.y; r[2 * (size_t)WH] = q0.z;
     d_sigma[i] = q0.w;
-    float* x = d_xyz + 3 * i;
-    x[0] = q1.x; x[1] = q1.y; x[2] = q1.z;
+    if (d_xyz) {
+      float* x = d_xyz + 3 * i;
+      x[0] = q1.x; x[1] = q1.y; x[2] = q1.z;
+    }
   }
 }
 
@@ -356,6 +403,27 @@ RenderLayout render_layout(int W, int H, int Np, int B) {
   return L;
 }
 
+// dispatch on (mine_grid, mine_mask) x (producers folded in)
+template <bool FUSED>
+void launch_render_fwd(int flags, dim3 grid, dim3 block, cudaStream_t st, const RenderArgs& a) {
+  switch (flags & 3) {
+    case 0: render_fwd_kernel<0, FUSED><<<grid, block, 0, st>>>(a); break;
+    case 1: render_fwd_kernel<1, FUSED><<<grid, block, 0, st>>>(a); break;
+    case 2: render_fwd_kernel<2, FUSED><<<grid, block, 0, st>>>(a); break;
+    default: render_fwd_kernel<3, FUSED><<<grid, block, 0, st>>>(a); break;
+  }
+}
+template <bool FUSED>
+void launch_render_bwd(int flags, dim3 grid, cudaStream_t st, const RenderBwdArgs& a) {
+  // the valid mask has no gradient: only the grid variant matters here
+  if (flags & RV_MINE_GRID) render_bwd_kernel<RV_MINE_GRID, FUSED><<<grid, RB_THREADS, 0, st>>>(a);
+  else render_bwd_kernel<0, FUSED><<<grid, RB_THREADS, 0, st>>>(a);
+}
+
+int opts_flags(const mdb_render_opts* o) {
+  return o ? ((o->mine_grid ? RV_MINE_GRID : 0) | (o->mine_mask ? RV_MINE_MASK : 0)) : 0;
+}
+
 }  // namespace
 
 extern "C" {
@@ -430,12 +498,14 @@ int32_t mdb_plane_volume_rendering(mdb_handle* h, const float* rgb, const float*
   return MDB_OK;
 }
 
-int32_t mdb_render_tgt_rgb_depth_fwd(mdb_handle* h, const float* rgb, const float* sigma, const float* disparity_src,
-                                     const float* xyz_tgt, const float* rvec, const float* tvec, const float* K_inv,
-                                     const float* K, int32_t W, int32_t H, int32_t Np, int32_t B, float* rgb_out,
-                                     float* depth_out, int32_t* mask_out, void* workspace, size_t workspace_bytes,
-                                     void* stream) {
-  MDB_REQUIRE(h, h && rgb && sigma && disparity_src && xyz_tgt && rvec && tvec && K_inv && K && rgb_out && depth_out && mask_out,
+int32_t mdb_render_tgt_rgb_depth_fwd_ex(mdb_handle* h, const float* rgb, const float* sigma, const float* disparity_src,
+                                        const float* xyz_tgt, const float* rvec, const float* tvec, const float* K_inv,
+                                        const float* K, int32_t W, int32_t H, int32_t Np, int32_t B,
+                                        const mdb_render_opts* opts, float* rgb_out, float* depth_out, int32_t* mask_out,
+                                        float* expected_depth, float* weights_sum, void* workspace, size_t workspace_bytes,
+                                        void* stream) {
+  MDB_REQUIRE(h, h != nullptr, MDB_E_INVALID_ARG, "null handle");
+  MDB_REQUIRE(h, rgb && sigma && disparity_src && rvec && tvec && K_inv && K && rgb_out && depth_out && mask_out,
               MDB_E_INVALID_ARG, "mdb_render_tgt_rgb_depth_fwd: null argument");
   MDB_REQUIRE(h, W >= 2 && H >= 2 && Np >= 1 && Np <= RB_MAXP && B >= 1, MDB_E_SHAPE,
               "mdb_render_tgt_rgb_depth_fwd: need W,H >= 2 and 1 <= Np <= %d", RB_MAXP);
@@ -446,21 +516,40 @@ int32_t mdb_render_tgt_rgb_depth_fwd(mdb_handle* h, const float* rgb, const floa
   PlanePrep* prep = (PlanePrep*)((char*)workspace + L.o_prep);
   render_prep_kernel<<<(Np * B + 63) / 64, 64, 0, st>>>(disparity_src, 0, rvec, tvec, make_rc(K, K_inv), Np, B, prep);
   MDB_LAUNCHED(h);
-  RenderArgs a{rgb, sigma, xyz_tgt, prep, W, H, Np, B, rgb_out, depth_out, mask_out};
+  RenderArgs a{rgb, sigma, xyz_tgt, prep, W, H, Np, B, rgb_out, depth_out, mask_out, expected_depth, weights_sum,
+               opts ? opts->depth_eps : 1e-5f};
   dim3 grid((W * H + RF_PIX - 1) / RF_PIX, B), block(RF_PIX, RF_G);
-  render_fwd_kernel<<<grid, block, 0, st>>>(a);
+  if (xyz_tgt) launch_render_fwd<false>(opts_flags(opts), grid, block, st, a);
+  else launch_render_fwd<true>(opts_flags(opts), grid, block, st, a);
   MDB_LAUNCHED(h);
   return MDB_OK;
 }
 
-int32_t mdb_render_tgt_rgb_depth_bwd(mdb_handle* h, const float* rgb, const float* sigma, const float* disparity_src,
+int32_t mdb_render_tgt_rgb_depth_fwd(mdb_handle* h, const float* rgb, const float* sigma, const float* disparity_src,
                                      const float* xyz_tgt, const float* rvec, const float* tvec, const float* K_inv,
-                                     const float* K, int32_t W, int32_t H, int32_t Np, int32_t B, const float* depth_saved,
-                                     const float* g_rgb_out, const float* g_depth, float* d_rgb, float* d_sigma,
-                                     float* d_xyz_tgt, float* d_disparity_src, float* d_rvec, float* d_tvec,
-                                     void* workspace, size_t workspace_bytes, void* stream) {
-  MDB_REQUIRE(h, h && rgb && sigma && disparity_src && xyz_tgt && rvec && tvec && K_inv && K && depth_saved && g_rgb_out &&
-                  d_rgb && d_sigma && d_xyz_tgt, MDB_E_INVALID_ARG, "mdb_render_tgt_rgb_depth_bwd: null argument");
+                                     const float* K, int32_t W, int32_t H, int32_t Np, int32_t B, float* rgb_out,
+                                     float* depth_out, int32_t* mask_out, void* workspace, size_t workspace_bytes,
+                                     void* stream) {
+  MDB_REQUIRE(h, h && xyz_tgt, MDB_E_INVALID_ARG, "mdb_render_tgt_rgb_depth_fwd: null argument");
+  return mdb_render_tgt_rgb_depth_fwd_ex(h, rgb, sigma, disparity_src, xyz_tgt, rvec, tvec, K_inv, K, W, H, Np, B, nullptr,
+                                         rgb_out, depth_out, mask_out, nullptr, nullptr, workspace, workspace_bytes, stream);
+}
+
+int32_t mdb_render_tgt_rgb_depth_bwd_ex(mdb_handle* h, const float* rgb, const float* sigma, const float* disparity_src,
+                                        const float* xyz_tgt, const float* rvec, const float* tvec, const float* K_inv,
+                                        const float* K, int32_t W, int32_t H, int32_t Np, int32_t B,
+                                        const mdb_render_opts* opts, const float* depth_saved,
+                                        const float* expected_depth_saved, const float* weights_sum_saved,
+                                        const float* g_rgb_out, const float* g_depth, const float* g_expected_depth,
+                                        float* d_rgb, float* d_sigma, float* d_xyz_tgt, float* d_disparity_src,
+                                        float* d_rvec, float* d_tvec, void* workspace, size_t workspace_bytes, void* stream) {
+  MDB_REQUIRE(h, h != nullptr, MDB_E_INVALID_ARG, "null handle");
+  MDB_REQUIRE(h, rgb && sigma && disparity_src && rvec && tvec && K_inv && K && depth_saved && g_rgb_out && d_rgb && d_sigma,
+              MDB_E_INVALID_ARG, "mdb_render_tgt_rgb_depth_bwd: null argument");
+  MDB_REQUIRE(h, (xyz_tgt != nullptr) == (d_xyz_tgt != nullptr), MDB_E_INVALID_ARG,
+              "mdb_render_tgt_rgb_depth_bwd: xyz_tgt and d_xyz_tgt go together (both null = producers folded in)");
+  MDB_REQUIRE(h, !g_expected_depth || (expected_depth_saved && weights_sum_saved), MDB_E_INVALID_ARG,
+              "mdb_render_tgt_rgb_depth_bwd: g_expected_depth needs the forward's expected_depth and weights_sum");
   MDB_REQUIRE(h, W >= 2 && H >= 2 && Np >= 1 && Np <= RB_MAXP && B >= 1, MDB_E_SHAPE,
               "mdb_render_tgt_rgb_depth_bwd: need W,H >= 2 and 1 <= Np <= %d", RB_MAXP);
   const RenderLayout L = render_layout(W, H, Np, B);
@@ -478,11 +567,14 @@ int32_t mdb_render_tgt_rgb_depth_bwd(mdb_handle* h, const float* rgb, const floa
   RenderBwdArgs a{};
   a.rgb = rgb; a.sigma = sigma; a.xyz = xyz_tgt; a.prep = prep; a.tacc = depth_saved; a.g_rgb_out = g_rgb_out;
   a.g_tacc = g_depth; a.W = W; a.H = H; a.Np = Np; a.B = B; a.tvec = tvec;
+  a.edepth = expected_depth_saved; a.wsum = weights_sum_saved; a.g_edepth = g_expected_depth;
+  a.depth_eps = opts ? opts->depth_eps : 1e-5f;
   for (int i = 0; i < 9; ++i) a.Kinv_f[i] = rc.Kinv_f[i];
   a.acc = acc;
   a.part_pose = (float*)(ws + L.o_pose); a.part_disp = (float*)(ws + L.o_disp);
   dim3 grid(L.blocks, B);
-  render_bwd_kernel<<<grid, RB_THREADS, 0, st>>>(a);
+  if (xyz_tgt) launch_render_bwd<false>(opts_flags(opts), grid, st, a);
+  else launch_render_bwd<true>(opts_flags(opts), grid, st, a);
   MDB_LAUNCHED(h);
   render_bwd_unpack_kernel<<<(unsigned)std::min<size_t>((planes + 255) / 256, (size_t)h->num_sms * 32), 256, 0, st>>>(
       acc, W * H, planes, d_rgb, d_sigma, d_xyz_tgt);
@@ -491,6 +583,18 @@ int32_t mdb_render_tgt_rgb_depth_bwd(mdb_handle* h, const float* rgb, const floa
                                                                       d_disparity_src);
   MDB_LAUNCHED(h);
   return MDB_OK;
+}
+
+int32_t mdb_render_tgt_rgb_depth_bwd(mdb_handle* h, const float* rgb, const float* sigma, const float* disparity_src,
+                                     const float* xyz_tgt, const float* rvec, const float* tvec, const float* K_inv,
+                                     const float* K, int32_t W, int32_t H, int32_t Np, int32_t B, const float* depth_saved,
+                                     const float* g_rgb_out, const float* g_depth, float* d_rgb, float* d_sigma,
+                                     float* d_xyz_tgt, float* d_disparity_src, float* d_rvec, float* d_tvec,
+                                     void* workspace, size_t workspace_bytes, void* stream) {
+  MDB_REQUIRE(h, h && xyz_tgt && d_xyz_tgt, MDB_E_INVALID_ARG, "mdb_render_tgt_rgb_depth_bwd: null argument");
+  return mdb_render_tgt_rgb_depth_bwd_ex(h, rgb, sigma, disparity_src, xyz_tgt, rvec, tvec, K_inv, K, W, H, Np, B, nullptr,
+                                         depth_saved, nullptr, nullptr, g_rgb_out, g_depth, nullptr, d_rgb, d_sigma, d_xyz_tgt,
+                                         d_disparity_src, d_rvec, d_tvec, workspace, workspace_bytes, stream);
 }
 
 }  // extern "C"

@@ -53,6 +53,11 @@ class AdamParams(C.Structure):
     _fields_ = [("eta", C.c_double), ("beta1", C.c_double), ("beta2", C.c_double), ("eps", C.c_double)]
 
 
+class RenderOpts(C.Structure):
+    """mdb_render_opts; all zero = src/render.jl as written."""
+    _fields_ = [("mine_grid", C.c_int32), ("mine_mask", C.c_int32), ("depth_eps", C.c_float), ("reserved", C.c_int32)]
+
+
 def _load() -> C.CDLL:
     if not os.path.exists(LIB_PATH):
         raise ImportError(
@@ -108,6 +113,11 @@ PROTOTYPES = {
                                             _vp, _vp, _vp, _vp, _sz, _vp]),
     "mdb_render_tgt_rgb_depth_bwd": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, c_f32p, c_f32p, _i32, _i32, _i32, _i32,
                                             _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "mdb_render_tgt_rgb_depth_fwd_ex": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, c_f32p, c_f32p, _i32, _i32, _i32, _i32,
+                                               C.POINTER(RenderOpts), _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "mdb_render_tgt_rgb_depth_bwd_ex": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, c_f32p, c_f32p, _i32, _i32, _i32, _i32,
+                                               C.POINTER(RenderOpts), _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
+                                               _vp, _vp, _sz, _vp]),
     "mdb_adam_update": (_i32, [_vp, _i32, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp),
                                C.POINTER(_i64), C.POINTER(AdamParams), _vp, _vp, _vp, _vp, _i32, _vp]),
     "mdb_slow_depth_state_bytes": (_sz, [C.POINTER(LossIO)]),

@@ -890,97 +890,143 @@ def plane_volume_rendering(rgb: torch.Tensor, sigma: torch.Tensor, xyz: torch.Te
     return rgb_out, tacc, wts
 
 
+def _render_opts(mine_grid: bool, mine_mask: bool, depth_eps) -> "_lib.RenderOpts":
+    o = _lib.RenderOpts()
+    o.mine_grid, o.mine_mask = int(bool(mine_grid)), int(bool(mine_mask))
+    o.depth_eps = 1e-5 if depth_eps is None else float(depth_eps)
+    return o
+
+
 class _RenderFn(torch.autograd.Function):
-    """Forward = mdb_render_tgt_rgb_depth_fwd; backward = mdb_render_tgt_rgb_depth_bwd (the Julia
-    glue registers the same pair as a ChainRulesCore.rrule)."""
+    """Forward = mdb_render_tgt_rgb_depth_fwd_ex; backward = mdb_render_tgt_rgb_depth_bwd_ex (the Julia
+    glue registers the same pair as a ChainRulesCore.rrule).  `xyz_tgt` None = producers folded in;
+    `depth_eps` None = no expected-depth output (the reference as written)."""
 
     @staticmethod
-    def forward(ctx, rgb, sigma, disparity_src, xyz_tgt, rvec, tvec, K_inv, K):
+    def forward(ctx, rgb, sigma, disparity_src, xyz_tgt, rvec, tvec, K_inv, K, mine_grid, mine_mask, depth_eps):
         B, Np, _, H, W = rgb.shape
         ws, n = _render_ws(W, H, Np, B, rgb.device)
-        rgb_out = torch.empty((B, 3, H, W), device=rgb.device, dtype=torch.float32)
-        depth = torch.empty((B, Np, 1, H, W), device=rgb.device, dtype=torch.float32)
+        f32 = dict(device=rgb.device, dtype=torch.float32)
+        rgb_out = torch.empty((B, 3, H, W), **f32)
+        depth = torch.empty((B, Np, 1, H, W), **f32)
         mask = torch.empty((B, 1, 1, H, W), device=rgb.device, dtype=torch.int32)
-        check(handle(), lib.mdb_render_tgt_rgb_depth_fwd(handle(), _p(rgb), _p(sigma), _p(disparity_src), _p(xyz_tgt), _p(rvec),
-                                                         _p(tvec), _k9(K_inv), _k9(K), W, H, Np, B, _p(rgb_out), _p(depth),
-                                                         ct.c_void_p(mask.data_ptr()), _p(ws), n, _stream()))
-        ctx.save_for_backward(rgb, sigma, disparity_src, xyz_tgt, rvec, tvec, depth)
-        ctx.K, ctx.K_inv, ctx.ws, ctx.n = K, K_inv, ws, n
+        want_z = depth_eps is not None
+        edepth = torch.empty((B, 1, H, W), **f32) if want_z else None
+        wsum = torch.empty((B, 1, H, W), **f32) if want_z else None
+        opts = _render_opts(mine_grid, mine_mask, depth_eps)
+        check(handle(), lib.mdb_render_tgt_rgb_depth_fwd_ex(handle(), _p(rgb), _p(sigma), _p(disparity_src), _p(xyz_tgt), _p(rvec),
+                                                            _p(tvec), _k9(K_inv), _k9(K), W, H, Np, B, ct.byref(opts), _p(rgb_out),
+                                                            _p(depth), ct.c_void_p(mask.data_ptr()), _p(edepth), _p(wsum), _p(ws), n,
+                                                            _stream()))
+        ctx.save_for_backward(rgb, sigma, disparity_src, xyz_tgt, rvec, tvec, depth, edepth, wsum)
+        ctx.K, ctx.K_inv, ctx.ws, ctx.n, ctx.opts = K, K_inv, ws, n, opts
         ctx.mark_non_differentiable(mask)
+        if want_z:
+            return rgb_out, depth, mask, edepth
         return rgb_out, depth, mask
 
     @staticmethod
-    def backward(ctx, g_rgb, g_depth, _g_mask):
-        rgb, sigma, disp, xyz, rvec, tvec, depth = ctx.saved_tensors
+    def backward(ctx, g_rgb, g_depth, _g_mask, g_z=None):
+        rgb, sigma, disp, xyz, rvec, tvec, depth, edepth, wsum = ctx.saved_tensors
         B, Np, _, H, W = rgb.shape
         g_rgb = torch.zeros((B, 3, H, W), device=rgb.device) if g_rgb is None else g_rgb.contiguous()
         g_depth = None if g_depth is None else g_depth.contiguous()
-        d_rgb, d_sigma, d_xyz = torch.empty_like(rgb), torch.empty_like(sigma), torch.empty_like(xyz)
+        g_z = None if g_z is None else g_z.contiguous()
+        d_rgb, d_sigma = torch.empty_like(rgb), torch.empty_like(sigma)
+        d_xyz = None if xyz is None else torch.empty_like(xyz)
         d_disp, d_r, d_t = torch.empty_like(disp), torch.empty_like(rvec), torch.empty_like(tvec)
-        check(handle(), lib.mdb_render_tgt_rgb_depth_bwd(handle(), _p(rgb), _p(sigma), _p(disp), _p(xyz), _p(rvec), _p(tvec),
-                                                         _k9(ctx.K_inv), _k9(ctx.K), W, H, Np, B, _p(depth), _p(g_rgb), _p(g_depth),
-                                                         _p(d_rgb), _p(d_sigma), _p(d_xyz), _p(d_disp), _p(d_r), _p(d_t),
-                                                         _p(ctx.ws), ctx.n, _stream()))
-        return d_rgb, d_sigma, d_disp, d_xyz, d_r, d_t, None, None
+        check(handle(), lib.mdb_render_tgt_rgb_depth_bwd_ex(handle(), _p(rgb), _p(sigma), _p(disp), _p(xyz), _p(rvec), _p(tvec),
+                                                            _k9(ctx.K_inv), _k9(ctx.K), W, H, Np, B, ct.byref(ctx.opts), _p(depth),
+                                                            _p(edepth), _p(wsum), _p(g_rgb), _p(g_depth), _p(g_z), _p(d_rgb),
+                                                            _p(d_sigma), _p(d_xyz), _p(d_disp), _p(d_r), _p(d_t), _p(ctx.ws), ctx.n,
+                                                            _stream()))
+        return d_rgb, d_sigma, d_disp, d_xyz, d_r, d_t, None, None, None, None, None
 
 
 class RenderPlan:
     """Pre-planned `render_tgt_rgb_depth` forward + pullback for fixed shapes: owns the workspace, the
     outputs and the gradient buffers, so a call is two C-ABI calls and nothing else (what the Julia rrule
-    does with its cached buffers; `bench.py --config config4` times this)."""
+    does with its cached buffers; `bench.py --config config4` times this).
 
-    def __init__(self, W: int, H: int, Np: int, B: int, K_inv, K, device=None):
+    Variants (`mdb_render_opts`): `mine_grid`, `mine_mask`; `expected_depth=True` adds a
+    fourth output sum w z / (sum w + depth_eps); `fused_xyz=True` means forward() is given `xyz_tgt=None` and
+    the producers (src/render.jl:21-30, 51-62) are evaluated inside the kernels."""
+
+    def __init__(self, W: int, H: int, Np: int, B: int, K_inv, K, device=None, *, mine_grid: bool = False,
+                 mine_mask: bool = False, expected_depth: bool = False, depth_eps: float = 1e-5, fused_xyz: bool = False):
         self.dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         self.W, self.H, self.Np, self.B = W, H, Np, B
         self.K, self.K_inv = _k9(K), _k9(K_inv)
         self.ws, self.n = _render_ws(W, H, Np, B, self.dev)
+        self.opts = _render_opts(mine_grid, mine_mask, depth_eps)
+        self.fused_xyz = bool(fused_xyz)
         f32 = dict(device=self.dev, dtype=torch.float32)
         self.rgb_out = torch.empty((B, 3, H, W), **f32)
         self.depth = torch.empty((B, Np, 1, H, W), **f32)
         self.mask = torch.empty((B, 1, 1, H, W), device=self.dev, dtype=torch.int32)
+        self.expected_depth = torch.empty((B, 1, H, W), **f32) if expected_depth else None
+        self.weights_sum = torch.empty((B, 1, H, W), **f32) if expected_depth else None
         self.d_rgb = torch.empty((B, Np, 3, H, W), **f32)
         self.d_sigma = torch.empty((B, Np, 1, H, W), **f32)
-        self.d_xyz = torch.empty((B, Np, H, W, 3), **f32)
+        self.d_xyz = None if self.fused_xyz else torch.empty((B, Np, H, W, 3), **f32)
         self.d_disp = torch.empty((B, Np), **f32)
         self.d_rvec, self.d_tvec = torch.empty((B, 3), **f32), torch.empty((B, 3), **f32)
         self._in = None
 
     def forward(self, rgb, sigma, disparity_src, xyz_tgt, pose: Pose):
-        for t, nm in ((rgb, "rgb"), (sigma, "sigma"), (disparity_src, "disparity_src"), (xyz_tgt, "xyz_tgt"),
-                      (pose.rvec, "rvec"), (pose.tvec, "tvec")):
+        for t, nm in ((rgb, "rgb"), (sigma, "sigma"), (disparity_src, "disparity_src"), (pose.rvec, "rvec"), (pose.tvec, "tvec")):
             _chk(t, nm)
+        if self.fused_xyz != (xyz_tgt is None):
+            raise ValueError("xyz_tgt must be None exactly when the plan was made with fused_xyz=True")
+        if xyz_tgt is not None:
+            _chk(xyz_tgt, "xyz_tgt")
         if tuple(rgb.shape) != (self.B, self.Np, 3, self.H, self.W):
             raise ValueError(f"rgb has shape {tuple(rgb.shape)}, planned for {(self.B, self.Np, 3, self.H, self.W)}")
         self._in = (rgb, sigma, disparity_src, xyz_tgt, pose.rvec, pose.tvec)
         h = handle()
-        check(h, lib.mdb_render_tgt_rgb_depth_fwd(h, _p(rgb), _p(sigma), _p(disparity_src), _p(xyz_tgt), _p(pose.rvec),
-                                                  _p(pose.tvec), self.K_inv, self.K, self.W, self.H, self.Np, self.B,
-                                                  _p(self.rgb_out), _p(self.depth), ct.c_void_p(self.mask.data_ptr()),
-                                                  _p(self.ws), self.n, _stream()))
+        check(h, lib.mdb_render_tgt_rgb_depth_fwd_ex(h, _p(rgb), _p(sigma), _p(disparity_src), _p(xyz_tgt), _p(pose.rvec),
+                                                     _p(pose.tvec), self.K_inv, self.K, self.W, self.H, self.Np, self.B,
+                                                     ct.byref(self.opts), _p(self.rgb_out), _p(self.depth),
+                                                     ct.c_void_p(self.mask.data_ptr()), _p(self.expected_depth),
+                                                     _p(self.weights_sum), _p(self.ws), self.n, _stream()))
+        if self.expected_depth is not None:
+            return self.rgb_out, self.depth, self.mask, self.expected_depth
         return self.rgb_out, self.depth, self.mask
 
-    def backward(self, g_rgb: torch.Tensor, g_depth: Optional[torch.Tensor] = None):
-        """Pullback of the last forward: -> (d_rgb, d_sigma, d_disparity_src, d_xyz_tgt, d_rvec, d_tvec)."""
+    def backward(self, g_rgb: torch.Tensor, g_depth: Optional[torch.Tensor] = None,
+                 g_expected_depth: Optional[torch.Tensor] = None):
+        """Pullback of the last forward: -> (d_rgb, d_sigma, d_disparity_src, d_xyz_tgt (None when fused), d_rvec, d_tvec)."""
         if self._in is None:
             raise RuntimeError("RenderPlan.backward before forward")
         rgb, sigma, disp, xyz, rvec, tvec = self._in
         _chk(g_rgb, "g_rgb")
         if g_depth is not None:
             _chk(g_depth, "g_depth")
+        if g_expected_depth is not None:
+            _chk(g_expected_depth, "g_expected_depth")
+            if self.expected_depth is None:
+                raise ValueError("g_expected_depth given but the plan was made without expected_depth=True")
         h = handle()
-        check(h, lib.mdb_render_tgt_rgb_depth_bwd(h, _p(rgb), _p(sigma), _p(disp), _p(xyz), _p(rvec), _p(tvec), self.K_inv,
-                                                  self.K, self.W, self.H, self.Np, self.B, _p(self.depth), _p(g_rgb),
-                                                  _p(g_depth), _p(self.d_rgb), _p(self.d_sigma), _p(self.d_xyz),
-                                                  _p(self.d_disp), _p(self.d_rvec), _p(self.d_tvec), _p(self.ws), self.n,
-                                                  _stream()))
+        check(h, lib.mdb_render_tgt_rgb_depth_bwd_ex(h, _p(rgb), _p(sigma), _p(disp), _p(xyz), _p(rvec), _p(tvec), self.K_inv,
+                                                     self.K, self.W, self.H, self.Np, self.B, ct.byref(self.opts),
+                                                     _p(self.depth), _p(self.expected_depth), _p(self.weights_sum), _p(g_rgb),
+                                                     _p(g_depth), _p(g_expected_depth), _p(self.d_rgb), _p(self.d_sigma),
+                                                     _p(self.d_xyz), _p(self.d_disp), _p(self.d_rvec), _p(self.d_tvec),
+                                                     _p(self.ws), self.n, _stream()))
         return self.d_rgb, self.d_sigma, self.d_disp, self.d_xyz, self.d_rvec, self.d_tvec
 
 
-def render_tgt_rgb_depth(rgb, sigma, disparity_src, xyz_tgt, pose: Pose, K_inv, K):
+def render_tgt_rgb_depth(rgb, sigma, disparity_src, xyz_tgt, pose: Pose, K_inv, K, *, mine_grid: bool = False,
+                         mine_mask: bool = False, depth_eps: Optional[float] = None):
     """`render_tgt_rgb_depth` -- src/render.jl:92-114 -> (rgb (B,3,H,W), depth = transparency_acc
     (B,Np,1,H,W), mask (B,1,1,H,W) int32).  Differentiable (autograd) w.r.t. rgb, sigma,
-    disparity_src, xyz_tgt and the pose."""
-    for t, nm in ((rgb, "rgb"), (sigma, "sigma"), (disparity_src, "disparity_src"), (xyz_tgt, "xyz_tgt"),
-                  (pose.rvec, "rvec"), (pose.tvec, "tvec")):
+    disparity_src, xyz_tgt and the pose.
+    Keyword variants (defaults = the reference as written): `mine_grid`, `mine_mask`
+    (test/test_sample.jl:123-137); `depth_eps` given -> a fourth output, the expected depth
+    sum w z / (sum w + depth_eps) (B,1,H,W); `xyz_tgt=None` -> the producers (src/render.jl:21-30, 51-62) are
+    evaluated inside the kernels and their gradient flows on into disparity_src and the pose."""
+    for t, nm in ((rgb, "rgb"), (sigma, "sigma"), (disparity_src, "disparity_src"), (pose.rvec, "rvec"), (pose.tvec, "tvec")):
         _chk(t, nm)
-    return _RenderFn.apply(rgb, sigma, disparity_src, xyz_tgt, pose.rvec, pose.tvec, K_inv, K)
+    if xyz_tgt is not None:
+        _chk(xyz_tgt, "xyz_tgt")
+    return _RenderFn.apply(rgb, sigma, disparity_src, xyz_tgt, pose.rvec, pose.tvec, K_inv, K, mine_grid, mine_mask, depth_eps)

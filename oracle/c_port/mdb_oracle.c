@@ -643,20 +643,51 @@ typedef struct {
   real *d_rgb, *d_sigma, *d_xyz;        /* zero-initialised by the driver */
   double* Gacc;                         /* [B][Np][9]: d loss / d H_src_tgt, math row-major */
   real* gs;                             /* [B][Np][H W][9]: per-sample grads (7 channels) + d/d(cx), d/d(cy) */
+  /* variants */
+  int flags;                            /* MDBO_RENDER_* */
+  double depth_eps;
+  real* dsyn;                           /* [B][1][H][W] expected depth, or NULL */
+  const real* g_dsyn;                   /* its cotangent, or NULL */
   atomic_int next;
 } rjob_t;
 
-typedef struct { int o[4]; real fx, fy, mx, my; double X[3], x, y; int valid; } rtap_t;
+/* The reference as written is flags = 0.  The variants restate what the reference's own comparison
+ * script holds up as the intended behaviour (MINE's HomographySample.sample, quoted in
+ * test/test_sample.jl:123-137) and the TODOs of src/render.jl:22,36,40,47,52:
+ *   MINE_GRID  grid = (x + 0.5) / (W/2) - 1, grid_sample(..., padding_mode="border", align_corners=false)
+ *              (test/test_sample.jl:131-137): the sample lands at source pixel x itself
+ *   MINE_MASK  valid = (x < W) & (x > -1) & (y < H) & (y > -1)              (test/test_sample.jl:123-125)
+ *   FUSED_XYZ  xyz_tgt is not an input: it is what get_src/get_tgt_xyz_from_plane_disparity
+ *              (src/render.jl:25-30, 51-62) make of create_meshgrid (:21-23), disparity_src, K_inv, pose
+ * and, independent of the flags, the expected depth  sum_k w_k z_k / (sum_k w_k + depth_eps)  that
+ * src/render.jl:47 leaves as "TODO: return depth?" (MINE's weighted_sum_mpi).                       */
+#define MDBO_RENDER_MINE_GRID 1
+#define MDBO_RENDER_MINE_MASK 2
+#define MDBO_RENDER_FUSED_XYZ 4
+
+typedef struct { int o[4]; real fx, fy, mx, my; double X[3], x, y, sx, sy; int valid; } rtap_t;
 
 /* sample coordinates of target pixel (u,v) (0-based) under H_src_tgt    src/render.jl:76-88 */
-static rtap_t render_tap(const double* Hst, int u, int v, int W, int H) {
+static rtap_t render_tap(const double* Hst, int u, int v, int W, int H, int flags) {
   rtap_t t;
   for (int i = 0; i < 3; ++i) t.X[i] = Hst[3 * i] * u + Hst[3 * i + 1] * v + Hst[3 * i + 2];
   t.x = t.X[0] / t.X[2]; t.y = t.X[1] / t.X[2];
-  /* Julia parses `a .< W .* a .>= 0` as (a < W a) & (W a >= 0)          src/render.jl:81, SURVEY F8c */
-  t.valid = (t.x < W * t.x) && (W * t.x >= 0.0) && (t.y < H * t.y) && (H * t.y >= 0.0);
-  /* grid = (xy + 0.5) / (W/2) without "-1" (:83-84), then grid_sample's align-corners un-normalisation */
-  const double ix = ((t.x + 0.5) / (W / 2.0) + 1.0) * 0.5 * (W - 1), iy = ((t.y + 0.5) / (H / 2.0) + 1.0) * 0.5 * (H - 1);
+  if (flags & MDBO_RENDER_MINE_MASK)
+    t.valid = (t.x < W) && (t.x > -1.0) && (t.y < H) && (t.y > -1.0);
+  else
+    /* Julia parses `a .< W .* a .>= 0` as (a < W a) & (W a >= 0)          src/render.jl:81, SURVEY F8c */
+    t.valid = (t.x < W * t.x) && (W * t.x >= 0.0) && (t.y < H * t.y) && (H * t.y >= 0.0);
+  double ix, iy;
+  if (flags & MDBO_RENDER_MINE_GRID) {
+    /* g = (x + 0.5) / (W/2) - 1;  align_corners=false un-normalisation ((g + 1) W - 1) / 2 */
+    const double gx = (t.x + 0.5) / (W / 2.0) - 1.0, gy = (t.y + 0.5) / (H / 2.0) - 1.0;
+    ix = ((gx + 1.0) * W - 1.0) / 2.0; iy = ((gy + 1.0) * H - 1.0) / 2.0;
+    t.sx = 1.0; t.sy = 1.0;
+  } else {
+    /* grid = (xy + 0.5) / (W/2) without "-1" (:83-84), then grid_sample's align-corners un-normalisation */
+    ix = ((t.x + 0.5) / (W / 2.0) + 1.0) * 0.5 * (W - 1); iy = ((t.y + 0.5) / (H / 2.0) + 1.0) * 0.5 * (H - 1);
+    t.sx = (double)(W - 1) / (double)W; t.sy = (double)(H - 1) / (double)H;
+  }
   t.mx = (ix > 0.0 && ix < (double)(W - 1)) ? 1 : 0;       /* clamp multiplier of the sampling gradient */
   t.my = (iy > 0.0 && iy < (double)(H - 1)) ? 1 : 0;
   const double cx = fmin(fmax(ix, 0.0), (double)(W - 1)), cy = fmin(fmax(iy, 0.0), (double)(H - 1));
@@ -697,7 +728,7 @@ static void render_row(rjob_t* J, int b, int v, const double* Hst_all) {
     int nvalid = 0;
     for (int k = 0; k < Np; ++k) {
       const int kb = b * Np + k;
-      taps[k] = render_tap(Hst_all + 9 * kb, u, v, W, H);
+      taps[k] = render_tap(Hst_all + 9 * kb, u, v, W, H, J->flags);
       const rtap_t* t = &taps[k];
       nvalid += t->valid;
       const real* pr = J->rgb + (size_t)kb * 3 * WH;
@@ -708,7 +739,7 @@ static void render_row(rjob_t* J, int b, int v, const double* Hst_all) {
       for (int c = 0; c < 3; ++c) s7[7 * k + 4 + c] = bil4(t, px[3 * t->o[0] + c], px[3 * t->o[1] + c], px[3 * t->o[2] + c], px[3 * t->o[3] + c]);
     }
     /* plane_volume_rendering                                              src/render.jl:32-49 */
-    real out[3] = {0, 0, 0};
+    real out[3] = {0, 0, 0}, wsum = 0, wz = 0;
     tacc[0] = 1;
     for (int k = 0; k < Np; ++k) {
       real d = (real)1e3;
@@ -721,12 +752,16 @@ static void render_row(rjob_t* J, int b, int v, const double* Hst_all) {
       Tk[k] = R_EXP(-d * sg);
       const real w = tacc[k] * (1 - Tk[k]);
       for (int c = 0; c < 3; ++c) out[c] += w * s7[7 * k + c];
+      wsum += w; wz += w * s7[7 * k + 6];
       J->tacc[(size_t)(b * Np + k) * WH + pix] = tacc[k];
       tacc[k + 1] = tacc[k] * (Tk[k] + (real)1e-6);
     }
     for (int c = 0; c < 3; ++c) J->rgb_out[((size_t)b * 3 + c) * WH + pix] = out[c];
     J->mask[(size_t)b * WH + pix] = nvalid;
+    const real Dn = wsum + (real)J->depth_eps, dsyn = wz / Dn;
+    if (J->dsyn) J->dsyn[(size_t)b * WH + pix] = dsyn;
     if (!J->g_out) continue;
+    const real gds = J->g_dsyn ? J->g_dsyn[(size_t)b * WH + pix] : 0;
 
     /* ---- pullback of the compositing, planes in reverse ---- */
     real go[3];
@@ -738,6 +773,7 @@ static void render_row(rjob_t* J, int b, int v, const double* Hst_all) {
       const real alpha = 1 - Tk[k];
       real gw = 0;
       for (int c = 0; c < 3; ++c) gw += go[c] * s7[7 * k + c];
+      gw += gds * (s7[7 * k + 6] - dsyn) / Dn;                             /* depth = sum w z / (sum w + eps) */
       real* g = J->gs + ((size_t)(b * Np + k) * WH + pix) * 9;
       for (int c = 0; c < 3; ++c) g[c] = go[c] * tacc[k] * alpha;          /* d/d rgb_k = g_out w_k */
       const real gtk = (J->g_tacc ? J->g_tacc[(size_t)(b * Np + k) * WH + pix] : 0) + gw * alpha + gT_next * (Tk[k] + (real)1e-6);
@@ -755,6 +791,7 @@ static void render_row(rjob_t* J, int b, int v, const double* Hst_all) {
           gxyz[c] -= gd * dv;
         }
       }
+      gxyz[2] += gds * tacc[k] * alpha / Dn;                                /* d depth / d z_k = w_k / D */
       for (int c = 0; c < 3; ++c) g[4 + c] = gxyz[c];
       gT_next = gtk;
     }
@@ -792,7 +829,7 @@ static void render_scatter_plane(rjob_t* J, int kb, const double* Hst) {
   double G[9] = {0};
   for (int v = 0; v < H; ++v)
     for (int u = 0; u < W; ++u) {
-      const rtap_t t = render_tap(Hst, u, v, W, H);
+      const rtap_t t = render_tap(Hst, u, v, W, H, J->flags);
       const real* g = J->gs + ((size_t)kb * WH + v * W + u) * 9;
       const real w[4] = {(1 - t.fx) * (1 - t.fy), t.fx * (1 - t.fy), (1 - t.fx) * t.fy, t.fx * t.fy};
       for (int q = 0; q < 4; ++q) {
@@ -800,8 +837,8 @@ static void render_scatter_plane(rjob_t* J, int kb, const double* Hst) {
         ds[t.o[q]] += g[3] * w[q];
         for (int c = 0; c < 3; ++c) dx[3 * t.o[q] + c] += g[4 + c] * w[q];
       }
-      /* (cx, cy) <- (x, y): d ix / d x = (W-1)/W (no "-1" grid, align-corners un-normalisation) */
-      const double gx = (double)g[7] * (double)(W - 1) / (double)W, gy = (double)g[8] * (double)(H - 1) / (double)H;
+      /* (cx, cy) <- (x, y): d ix / d x = (W-1)/W (no "-1" grid, align-corners un-normalisation), 1 for the MINE grid */
+      const double gx = (double)g[7] * t.sx, gy = (double)g[8] * t.sy;
       if (gx == 0.0 && gy == 0.0) continue;
       const double gX[3] = {gx / t.X[2], gy / t.X[2], -(gx * t.x + gy * t.y) / t.X[2]};
       const double q3[3] = {(double)u, (double)v, 1.0};
@@ -838,28 +875,67 @@ static void render_run(rjob_t* J, const double* Hst, int phase, int nthreads) {
   for (int i = 0; i < started; ++i) pthread_join(th[i], NULL);
 }
 
+/* create_meshgrid -> get_src_xyz_from_plane_disparity -> get_tgt_xyz_from_plane_disparity
+ * (src/render.jl:21-23, 25-30, 51-62): xyz_tgt [B][Np][H][W][3].  xyz_src (same layout) is kept when asked. */
+static void plane_xyz(int W, int H, int Np, int B, const real* disp, const real* rvec, const real* tvec, const double* iKm,
+                      real* xyz_src, real* xyz_tgt) {
+  for (int b = 0; b < B; ++b) {
+    double r[3] = {(double)rvec[3 * b], (double)rvec[3 * b + 1], (double)rvec[3 * b + 2]}, R[9];
+    so3_aux a;
+    so3_exp_rm(r, R, &a);
+    for (int k = 0; k < Np; ++k) {
+      const real depth = (real)1 / disp[b * Np + k];                          /* :28 */
+      for (int v = 0; v < H; ++v)
+        for (int u = 0; u < W; ++u) {
+          const real m[3] = {(real)(u + 1), (real)(v + 1), (real)1};         /* 1-based meshgrid, :22 */
+          real xs[3];
+          for (int i = 0; i < 3; ++i) xs[i] = ((real)iKm[3 * i] * m[0] + (real)iKm[3 * i + 1] * m[1] + (real)iKm[3 * i + 2] * m[2]) * depth;
+          const size_t o = (((size_t)(b * Np + k) * H + v) * W + u) * 3;
+          if (xyz_src) for (int i = 0; i < 3; ++i) xyz_src[o + i] = xs[i];
+          for (int i = 0; i < 3; ++i)                                         /* R xyz_src + t, :60 */
+            xyz_tgt[o + i] = (real)R[3 * i] * xs[0] + (real)R[3 * i + 1] * xs[1] + (real)R[3 * i + 2] * xs[2] + tvec[3 * b + i];
+        }
+    }
+  }
+}
+
 /* render_tgt_rgb_depth (src/render.jl:92-114) forward and, when g_rgb_out != NULL, its pullback.
  * K_jl / Kinv_jl: the 9 numbers Julia stores.  g_depth may be NULL.  All d_* must be given for the
- * pullback (d_disp [B][Np], d_rvec [B][3], d_tvec [B][3]).  Returns 0, -1 on bad arguments / OOM. */
-int mdbo_render_tgt_rgb_depth(int W, int H, int Np, int B, const real* rgb, const real* sigma, const real* disparity_src,
-                              const real* xyz_tgt, const real* rvec, const real* tvec, const real* Kinv_jl, const real* K_jl,
-                              real* rgb_out, real* depth_out, int32_t* mask_out, const real* g_rgb_out, const real* g_depth,
-                              real* d_rgb, real* d_sigma, real* d_disp, real* d_xyz, real* d_rvec, real* d_tvec, int nthreads) {
-  if (W < 2 || H < 2 || Np < 1 || B < 1 || !rgb || !sigma || !disparity_src || !xyz_tgt || !rvec || !tvec || !rgb_out ||
-      !depth_out || !mask_out)
+ * pullback (d_disp [B][Np], d_rvec [B][3], d_tvec [B][3]).  Returns 0, -1 on bad arguments / OOM.
+ * `flags`, `depth_eps`, `dsyn_out` / `g_dsyn`: the variants described at MDBO_RENDER_* above.  With
+ * FUSED_XYZ, xyz_tgt and d_xyz are NULL and the pose / disparity gradients include the path through xyz. */
+int mdbo_render_tgt_rgb_depth_ex(int W, int H, int Np, int B, const real* rgb, const real* sigma, const real* disparity_src,
+                                 const real* xyz_tgt, const real* rvec, const real* tvec, const real* Kinv_jl, const real* K_jl,
+                                 int flags, double depth_eps, real* rgb_out, real* depth_out, int32_t* mask_out, real* dsyn_out,
+                                 const real* g_rgb_out, const real* g_depth, const real* g_dsyn,
+                                 real* d_rgb, real* d_sigma, real* d_disp, real* d_xyz, real* d_rvec, real* d_tvec, int nthreads) {
+  const int fused = (flags & MDBO_RENDER_FUSED_XYZ) != 0;
+  if (W < 2 || H < 2 || Np < 1 || B < 1 || !rgb || !sigma || !disparity_src || !rvec || !tvec || !rgb_out ||
+      !depth_out || !mask_out || (!fused && !xyz_tgt))
     return -1;
-  if (g_rgb_out && (!d_rgb || !d_sigma || !d_disp || !d_xyz || !d_rvec || !d_tvec)) return -1;
+  if (g_rgb_out && (!d_rgb || !d_sigma || !d_disp || !d_rvec || !d_tvec || (!fused && !d_xyz))) return -1;
   double Km[9], iKm[9];
   for (int i = 0; i < 3; ++i)
     for (int j = 0; j < 3; ++j) { Km[3 * i + j] = (double)K_jl[3 * j + i]; iKm[3 * i + j] = (double)Kinv_jl[3 * j + i]; }
+  const size_t WH = (size_t)W * H, planes = (size_t)B * Np;
+  real *xs_own = NULL, *xt_own = NULL, *dx_own = NULL;
+  if (fused) {
+    xs_own = malloc(planes * WH * 3 * sizeof(real));
+    xt_own = malloc(planes * WH * 3 * sizeof(real));
+    if (g_rgb_out) dx_own = malloc(planes * WH * 3 * sizeof(real));
+    if (!xs_own || !xt_own || (g_rgb_out && !dx_own)) { free(xs_own); free(xt_own); free(dx_own); return -1; }
+    plane_xyz(W, H, Np, B, disparity_src, rvec, tvec, iKm, xs_own, xt_own);
+    xyz_tgt = xt_own;
+    d_xyz = dx_own;
+  }
   rjob_t J;
   memset(&J, 0, sizeof(J));
   J.W = W; J.H = H; J.Np = Np; J.B = B;
   J.rgb = rgb; J.sigma = sigma; J.xyz = xyz_tgt; J.disp = disparity_src; J.Km = Km; J.iKm = iKm; J.rvec = rvec; J.tvec = tvec;
   J.rgb_out = rgb_out; J.tacc = depth_out; J.mask = mask_out;
-  const size_t WH = (size_t)W * H, planes = (size_t)B * Np;
+  J.flags = flags; J.depth_eps = depth_eps; J.dsyn = dsyn_out; J.g_dsyn = g_dsyn;
   double* Hst = malloc(planes * 9 * sizeof(double));
-  if (!Hst) return -1;
+  if (!Hst) { free(xs_own); free(xt_own); free(dx_own); return -1; }
   for (int b = 0; b < B; ++b)
     for (int k = 0; k < Np; ++k) plane_homography(&J, b, k, Hst + 9 * (b * Np + k));
   int rc = 0;
@@ -867,7 +943,7 @@ int mdbo_render_tgt_rgb_depth(int W, int H, int Np, int B, const real* rgb, cons
     J.g_out = g_rgb_out; J.g_tacc = g_depth; J.d_rgb = d_rgb; J.d_sigma = d_sigma; J.d_xyz = d_xyz;
     J.gs = malloc(planes * WH * 9 * sizeof(real));
     J.Gacc = calloc(planes * 9, sizeof(double));
-    if (!J.gs || !J.Gacc) { free(J.gs); free(J.Gacc); free(Hst); return -1; }
+    if (!J.gs || !J.Gacc) { free(J.gs); free(J.Gacc); free(Hst); free(xs_own); free(xt_own); free(dx_own); return -1; }
     memset(d_rgb, 0, planes * 3 * WH * sizeof(real));
     memset(d_sigma, 0, planes * WH * sizeof(real));
     memset(d_xyz, 0, planes * 3 * WH * sizeof(real));
@@ -879,6 +955,9 @@ int mdbo_render_tgt_rgb_depth(int W, int H, int Np, int B, const real* rgb, cons
     /* H_src_tgt = inv(H_tgt_src), H_tgt_src = K M K^-1, M = R + t n^T disparity    src/render.jl:66-74 */
     for (int b = 0; b < B; ++b) {
       double gR[9] = {0}, gt[3] = {0};
+      double r[3] = {(double)rvec[3 * b], (double)rvec[3 * b + 1], (double)rvec[3 * b + 2]}, R[9], dr[3];
+      so3_aux a;
+      so3_exp_rm(r, R, &a);
       for (int k = 0; k < Np; ++k) {
         const double* Hs = Hst + 9 * (b * Np + k);
         const double* G = J.Gacc + 9 * (b * Np + k);
@@ -897,16 +976,49 @@ int mdbo_render_tgt_rgb_depth(int W, int H, int Np, int B, const real* rgb, cons
           gt[i] += gM[3 * i + 2] * dsp;
           gd += gM[3 * i + 2] * (double)tvec[3 * b + i];
         }
+        if (fused) {
+          /* xyz_tgt = R xyz_src + t (:60), xyz_src = K_inv m / disparity (:28-29) */
+          const real* gx = d_xyz + (size_t)(b * Np + k) * WH * 3;
+          const real* xs = xs_own + (size_t)(b * Np + k) * WH * 3;
+          double sd = 0;
+          for (size_t p = 0; p < WH; ++p) {
+            const double g3[3] = {(double)gx[3 * p], (double)gx[3 * p + 1], (double)gx[3 * p + 2]};
+            const double x3[3] = {(double)xs[3 * p], (double)xs[3 * p + 1], (double)xs[3 * p + 2]};
+            for (int i = 0; i < 3; ++i) {
+              gt[i] += g3[i];
+              for (int j = 0; j < 3; ++j) gR[3 * i + j] += g3[i] * x3[j];
+            }
+            for (int j = 0; j < 3; ++j) sd += (R[j] * g3[0] + R[3 + j] * g3[1] + R[6 + j] * g3[2]) * x3[j];   /* (R^T g) . xyz_src */
+          }
+          gd -= sd / dsp;
+        }
         d_disp[b * Np + k] = (real)gd;
       }
-      double r[3] = {(double)rvec[3 * b], (double)rvec[3 * b + 1], (double)rvec[3 * b + 2]}, R[9], dr[3];
-      so3_aux a;
-      so3_exp_rm(r, R, &a);
       so3_exp_bwd_rm(r, &a, gR, dr);
       for (int i = 0; i < 3; ++i) { d_rvec[3 * b + i] = (real)dr[i]; d_tvec[3 * b + i] = (real)gt[i]; }
     }
     free(J.gs); free(J.Gacc);
   }
-  free(Hst);
+  free(Hst); free(xs_own); free(xt_own); free(dx_own);
   return rc;
+}
+
+int mdbo_render_tgt_rgb_depth(int W, int H, int Np, int B, const real* rgb, const real* sigma, const real* disparity_src,
+                              const real* xyz_tgt, const real* rvec, const real* tvec, const real* Kinv_jl, const real* K_jl,
+                              real* rgb_out, real* depth_out, int32_t* mask_out, const real* g_rgb_out, const real* g_depth,
+                              real* d_rgb, real* d_sigma, real* d_disp, real* d_xyz, real* d_rvec, real* d_tvec, int nthreads) {
+  return mdbo_render_tgt_rgb_depth_ex(W, H, Np, B, rgb, sigma, disparity_src, xyz_tgt, rvec, tvec, Kinv_jl, K_jl, 0, 0.0, rgb_out,
+                                      depth_out, mask_out, NULL, g_rgb_out, g_depth, NULL, d_rgb, d_sigma, d_disp, d_xyz, d_rvec,
+                                      d_tvec, nthreads);
+}
+
+/* the producers alone, for the tests of mdb_plane_xyz_src / _tgt */
+int mdbo_plane_xyz(int W, int H, int Np, int B, const real* disparity_src, const real* rvec, const real* tvec,
+                   const real* Kinv_jl, real* xyz_src, real* xyz_tgt) {
+  if (W < 1 || H < 1 || Np < 1 || B < 1 || !disparity_src || !rvec || !tvec || !Kinv_jl || !xyz_tgt) return -1;
+  double iKm[9];
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) iKm[3 * i + j] = (double)Kinv_jl[3 * j + i];
+  plane_xyz(W, H, Np, B, disparity_src, rvec, tvec, iKm, xyz_src, xyz_tgt);
+  return 0;
 }

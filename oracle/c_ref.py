@@ -142,33 +142,58 @@ def compose_T_bwd(rvec, tvec, invert, dR, dt):
     return gr, gt
 
 
+RENDER_MINE_GRID, RENDER_MINE_MASK, RENDER_FUSED_XYZ = 1, 2, 4
+
+
 def render_tgt_rgb_depth(rgb, sigma, disparity_src, xyz_tgt, rvec, tvec, K_inv, K, *, g_rgb=None, g_depth=None,
+                         g_expected_depth=None, mine_grid=False, mine_mask=False, depth_eps=1e-5,
                          dtype=np.float64, threads: int = 1):
     """`render_tgt_rgb_depth` (src/render.jl:92-114) forward and, when `g_rgb` is given, the hand-written
-    pullback of  sum(g_rgb * rgb_out) + sum(g_depth * depth_out).  Arrays in the repo's reversed-dims
-    convention: rgb (B,Np,3,H,W), sigma (B,Np,1,H,W), disparity_src (B,Np), xyz_tgt (B,Np,H,W,3),
-    rvec / tvec (B,3).  Returns dict(rgb, depth, mask[, d_rgb, d_sigma, d_disparity_src, d_xyz_tgt, d_rvec, d_tvec])."""
+    pullback of  sum(g_rgb * rgb_out) + sum(g_depth * depth_out) + sum(g_expected_depth * expected_depth).
+    Arrays in the repo's reversed-dims convention: rgb (B,Np,3,H,W), sigma (B,Np,1,H,W), disparity_src (B,Np),
+    xyz_tgt (B,Np,H,W,3) or None (derived from the producers, src/render.jl:21-30, 51-62), rvec / tvec (B,3).
+    Returns dict(rgb, depth, mask, expected_depth[, d_rgb, d_sigma, d_disparity_src, d_xyz_tgt, d_rvec, d_tvec])."""
     L = lib(dtype)
-    L.mdbo_render_tgt_rgb_depth.restype = C.c_int
+    L.mdbo_render_tgt_rgb_depth_ex.restype = C.c_int
     c = lambda a: None if a is None else np.ascontiguousarray(a, dtype=dtype)
     rgb, sigma, disparity_src, xyz_tgt, rvec, tvec = map(c, (rgb, sigma, disparity_src, xyz_tgt, rvec, tvec))
     B, Np, _, H, W = rgb.shape
+    fused = xyz_tgt is None
+    flags = (RENDER_MINE_GRID if mine_grid else 0) | (RENDER_MINE_MASK if mine_mask else 0) | (RENDER_FUSED_XYZ if fused else 0)
     Ki, Kk = c(np.asarray(K_inv).reshape(9)), c(np.asarray(K).reshape(9))
     out = np.zeros((B, 3, H, W), dtype=dtype)
     depth = np.zeros((B, Np, 1, H, W), dtype=dtype)
     mask = np.zeros((B, 1, 1, H, W), dtype=np.int32)
-    g_rgb, g_depth = c(g_rgb), c(g_depth)
+    dsyn = np.zeros((B, 1, H, W), dtype=dtype)
+    g_rgb, g_depth, g_expected_depth = c(g_rgb), c(g_depth), c(g_expected_depth)
     grads = [None] * 6
     if g_rgb is not None:
-        grads = [np.zeros_like(rgb), np.zeros_like(sigma), np.zeros_like(disparity_src), np.zeros_like(xyz_tgt),
-                 np.zeros_like(rvec), np.zeros_like(tvec)]
-    rc = L.mdbo_render_tgt_rgb_depth(C.c_int(W), C.c_int(H), C.c_int(Np), C.c_int(B), _ptr(rgb), _ptr(sigma), _ptr(disparity_src),
-                                     _ptr(xyz_tgt), _ptr(rvec), _ptr(tvec), _ptr(Ki), _ptr(Kk), _ptr(out), _ptr(depth),
-                                     mask.ctypes.data_as(C.c_void_p), _ptr(g_rgb), _ptr(g_depth), _ptr(grads[0]), _ptr(grads[1]),
-                                     _ptr(grads[2]), _ptr(grads[3]), _ptr(grads[4]), _ptr(grads[5]), C.c_int(threads))
+        grads = [np.zeros_like(rgb), np.zeros_like(sigma), np.zeros_like(disparity_src),
+                 None if fused else np.zeros_like(xyz_tgt), np.zeros_like(rvec), np.zeros_like(tvec)]
+    rc = L.mdbo_render_tgt_rgb_depth_ex(C.c_int(W), C.c_int(H), C.c_int(Np), C.c_int(B), _ptr(rgb), _ptr(sigma), _ptr(disparity_src),
+                                        _ptr(xyz_tgt), _ptr(rvec), _ptr(tvec), _ptr(Ki), _ptr(Kk), C.c_int(flags),
+                                        C.c_double(depth_eps), _ptr(out), _ptr(depth), mask.ctypes.data_as(C.c_void_p), _ptr(dsyn),
+                                        _ptr(g_rgb), _ptr(g_depth), _ptr(g_expected_depth), _ptr(grads[0]), _ptr(grads[1]),
+                                        _ptr(grads[2]), _ptr(grads[3]), _ptr(grads[4]), _ptr(grads[5]), C.c_int(threads))
     if rc != 0:
-        raise RuntimeError(f"mdbo_render_tgt_rgb_depth failed ({rc})")
-    res = dict(rgb=out, depth=depth, mask=mask)
+        raise RuntimeError(f"mdbo_render_tgt_rgb_depth_ex failed ({rc})")
+    res = dict(rgb=out, depth=depth, mask=mask, expected_depth=dsyn)
     if g_rgb is not None:
         res.update(d_rgb=grads[0], d_sigma=grads[1], d_disparity_src=grads[2], d_xyz_tgt=grads[3], d_rvec=grads[4], d_tvec=grads[5])
     return res
+
+
+def plane_xyz(W, H, disparity_src, rvec, tvec, K_inv, dtype=np.float64):
+    """create_meshgrid -> get_src_xyz_from_plane_disparity -> get_tgt_xyz_from_plane_disparity
+    (src/render.jl:21-30, 51-62): returns (xyz_src, xyz_tgt), each (B,Np,H,W,3)."""
+    L = lib(dtype)
+    c = lambda a: np.ascontiguousarray(a, dtype=dtype)
+    disparity_src, rvec, tvec = c(disparity_src), c(rvec), c(tvec)
+    B, Np = disparity_src.shape
+    Ki = c(np.asarray(K_inv).reshape(9))
+    xs, xt = np.zeros((B, Np, H, W, 3), dtype=dtype), np.zeros((B, Np, H, W, 3), dtype=dtype)
+    rc = L.mdbo_plane_xyz(C.c_int(W), C.c_int(H), C.c_int(Np), C.c_int(B), _ptr(disparity_src), _ptr(rvec), _ptr(tvec), _ptr(Ki),
+                          _ptr(xs), _ptr(xt))
+    if rc != 0:
+        raise RuntimeError("mdbo_plane_xyz failed")
+    return xs, xt

@@ -353,19 +353,28 @@ def homography_src_tgt(depth_src: torch.Tensor, pose: Pose, K: torch.Tensor,
 
 
 def sample(src: torch.Tensor, depth_src: torch.Tensor, pose: Pose, K: torch.Tensor,
-           K_inv: torch.Tensor):
+           K_inv: torch.Tensor, *, mine_grid: bool = False, mine_mask: bool = False):
     """`sample` -- src/render.jl:64-90.  src (B*Np? ,C,H,W) given as (B,Np,C,H,W);
-    returns tgt (B,Np,C,H,W) and valid_mask (B,Np,H,W) bool."""
+    returns tgt (B,Np,C,H,W) and valid_mask (B,Np,H,W) bool.
+    `mine_grid` / `mine_mask`: what the reference's comparison script quotes from MINE
+    (test/test_sample.jl:123-137) instead of the code as written."""
     B, Np, C, H, W = src.shape
     Hm = homography_src_tgt(depth_src, pose, K, K_inv)  # (B,Np,3,3)
     mesh = create_meshgrid(H, W, src.dtype) - torch.tensor([1.0, 1.0, 0.0], dtype=src.dtype)
     ms = torch.einsum("bnij,hwj->bnhwi", Hm, mesh)
     xy = ms[..., 0:2] / ms[..., 2:3]
-    # Julia parses `a .< W .* a .>= 0` as (a < W a) & (W a >= 0)  (SURVEY F8c)
     gx, gy = xy[..., 0], xy[..., 1]
-    valid = ((gx < W * gx) & (W * gx >= 0)) & ((gy < H * gy) & (H * gy >= 0))
-    grid = torch.stack([(gx + 0.5) / (W / 2), (gy + 0.5) / (H / 2)], dim=-1)  # no "-1" (F8a)
-    tgt = grid_sample(src.reshape(B * Np, C, H, W), grid.reshape(B * Np, H, W, 2))
+    if mine_mask:   # test/test_sample.jl:123-125
+        valid = ((gx < W) & (gx > -1)) & ((gy < H) & (gy > -1))
+    else:           # Julia parses `a .< W .* a .>= 0` as (a < W a) & (W a >= 0)  (SURVEY F8c)
+        valid = ((gx < W * gx) & (W * gx >= 0)) & ((gy < H * gy) & (H * gy >= 0))
+    if mine_grid:   # test/test_sample.jl:131-137, torch's own sampler
+        grid = torch.stack([(gx + 0.5) / (W * 0.5) - 1, (gy + 0.5) / (H * 0.5) - 1], dim=-1)
+        tgt = torch.nn.functional.grid_sample(src.reshape(B * Np, C, H, W), grid.reshape(B * Np, H, W, 2),
+                                              mode="bilinear", padding_mode="border", align_corners=False)
+    else:
+        grid = torch.stack([(gx + 0.5) / (W / 2), (gy + 0.5) / (H / 2)], dim=-1)  # no "-1" (F8a)
+        tgt = grid_sample(src.reshape(B * Np, C, H, W), grid.reshape(B * Np, H, W, 2))
     return tgt.reshape(B, Np, C, H, W), valid
 
 
@@ -385,18 +394,29 @@ def plane_volume_rendering(rgb: torch.Tensor, sigma: torch.Tensor, xyz: torch.Te
     return rgb_out, tacc, weights
 
 
-def render_tgt_rgb_depth(rgb, sigma, disparity_src, xyz_tgt, pose: Pose, K_inv, K):
+def render_tgt_rgb_depth(rgb, sigma, disparity_src, xyz_tgt, pose: Pose, K_inv, K, *, mine_grid: bool = False,
+                         mine_mask: bool = False, depth_eps=None):
     """src/render.jl:92-114.  rgb (B,Np,3,H,W), sigma (B,Np,1,H,W), disparity_src (B,Np),
     xyz_tgt (B,Np,H,W,3) -> rgb (B,3,H,W), "depth" = transparency_acc (B,Np,1,H,W) (F8e),
-    mask (B,1,1,H,W) integer count of valid planes."""
+    mask (B,1,1,H,W) integer count of valid planes.
+    Variants (SURVEY 8(f) rank 2): `xyz_tgt=None` derives it from the producers (src/render.jl:21-30, 51-62);
+    `depth_eps` given -> a fourth output, the expected depth sum w z / (sum w + depth_eps), (B,1,H,W)
+    ("TODO: return depth?", src/render.jl:47)."""
     depth_src = 1.0 / disparity_src
+    if xyz_tgt is None:
+        H, W = rgb.shape[-2:]
+        xyz_tgt = get_tgt_xyz_from_plane_disparity(
+            get_src_xyz_from_plane_disparity(create_meshgrid(H, W, rgb.dtype), disparity_src, K_inv), pose)
     packed = torch.cat([rgb, sigma, xyz_tgt.permute(0, 1, 4, 2, 3)], dim=2)  # 7 channels
-    tgt, valid = sample(packed, depth_src, pose, K, K_inv)
+    tgt, valid = sample(packed, depth_src, pose, K, K_inv, mine_grid=mine_grid, mine_mask=mine_mask)
     rgb_s, sigma_s, xyz_s = tgt[:, :, 0:3], tgt[:, :, 3:4], tgt[:, :, 4:7]
     sigma_s = sigma_s * (sigma_s >= 0)
-    rgb_o, depth, _ = plane_volume_rendering(rgb_s, sigma_s, xyz_s.permute(0, 1, 3, 4, 2))
+    rgb_o, depth, weights = plane_volume_rendering(rgb_s, sigma_s, xyz_s.permute(0, 1, 3, 4, 2))
     mask = valid.sum(dim=1, keepdim=True).unsqueeze(1).to(torch.int64)  # (B,1,1,H,W)
-    return rgb_o, depth, mask
+    if depth_eps is None:
+        return rgb_o, depth, mask
+    dsyn = (weights * xyz_s[:, :, 2:3]).sum(dim=1) / (weights.sum(dim=1) + depth_eps)
+    return rgb_o, depth, mask, dsyn
 
 
 # --------------------------------------------------------------------------------------

@@ -143,3 +143,83 @@ def test_render_config4_full_size_vs_c_oracle():
         r = ref[name]
         err = np.abs(got.double().cpu().numpy() - r).max() / np.abs(r).max()
         assert err < 1e-4, (name, float(err))
+
+
+# ---- MINE grid / mask, expected depth, producers folded into the kernels -------------------
+def _check_variant(ri, W, H, Np, B, mine_grid, mine_mask, fused, seed=11, threads=8):
+    import mdb200
+    from oracle import c_ref
+    rng = np.random.default_rng(seed)
+    wr = rng.random((B, 3, H, W)).astype(np.float32)
+    wd = (0.1 * rng.random((B, Np, 1, H, W))).astype(np.float32)
+    wz = (0.01 * rng.random((B, 1, H, W))).astype(np.float32)
+    ref = c_ref.render_tgt_rgb_depth(ri.rgb, ri.sigma, ri.disparity_src, None if fused else ri.xyz_tgt, ri.rvec, ri.tvec,
+                                     ri.K_inv, ri.K, g_rgb=wr, g_depth=wd, g_expected_depth=wz, mine_grid=mine_grid,
+                                     mine_mask=mine_mask, depth_eps=1e-5, threads=threads)
+    plan = mdb200.RenderPlan(W, H, Np, B, ri.K_inv, ri.K, mine_grid=mine_grid, mine_mask=mine_mask, expected_depth=True,
+                             depth_eps=1e-5, fused_xyz=fused)
+    rg, dg, mg, zg = plan.forward(_dev(ri.rgb), _dev(ri.sigma), _dev(ri.disparity_src), None if fused else _dev(ri.xyz_tgt),
+                                  mdb200.Pose(_dev(ri.rvec), _dev(ri.tvec)))
+    assert np.abs(rg.double().cpu().numpy() - ref["rgb"]).max() < 1e-5
+    assert np.abs(dg.double().cpu().numpy() - ref["depth"]).max() < 1e-5
+    zr = ref["expected_depth"]
+    assert np.abs(zg.double().cpu().numpy() - zr).max() < 1e-5 * np.abs(zr).max()
+    assert np.array_equal(mg.cpu().numpy(), ref["mask"])
+    grads = plan.backward(_dev(wr), _dev(wd), _dev(wz))
+    for got, name in zip(grads, ["d_rgb", "d_sigma", "d_disparity_src", "d_xyz_tgt", "d_rvec", "d_tvec"]):
+        if fused and name == "d_xyz_tgt":
+            assert got is None
+            continue
+        r = ref[name]
+        err = np.abs(got.double().cpu().numpy() - r).max() / np.abs(r).max()
+        assert err < 1e-4, (name, float(err))
+    return ref
+
+
+@pytest.mark.parametrize("mine_grid,mine_mask,fused", [(False, False, True), (True, True, False), (True, False, True),
+                                                       (False, True, False), (True, True, True)])
+def test_render_variants_vs_c_oracle(mine_grid, mine_mask, fused):
+    from mdb200 import synth
+    W, H, Np, B = 96, 48, 12, 2
+    ri = synth.make_render_inputs(W, H, Np, B, seed=21, pose_scale=3.0)
+    ri.sigma = (np.random.default_rng(4).random(ri.sigma.shape) - 0.2).astype(np.float32)
+    _check_variant(ri, W, H, Np, B, mine_grid, mine_mask, fused)
+
+
+def test_render_variants_config4_full_size():
+    """Config-4 geometry with everything switched on: the sampler MINE intends, its mask, the expected depth and
+    no materialised xyz_tgt."""
+    from mdb200 import synth
+    ri = synth.make_render_inputs(416, 128, 32, 2)
+    ref = _check_variant(ri, 416, 128, 32, 2, True, True, True)
+    assert ref["mask"].max() == 32 and ref["mask"].min() < 32   # the MINE mask counts the planes that hit the image
+
+
+def test_render_fused_xyz_equals_materialised_producers():
+    """xyz_tgt=None is the same function as feeding the producers' output (src/render.jl:21-30, 51-62), through the
+    autograd wrapper: the gradient that would land in d_xyz_tgt flows on into disparity_src and the pose."""
+    import mdb200
+    from mdb200 import synth
+    W, H, Np, B = 64, 40, 8, 2
+    ri = synth.make_render_inputs(W, H, Np, B, seed=3, pose_scale=2.0)
+    mk = lambda: [_dev(a).requires_grad_() for a in (ri.rgb, ri.sigma, ri.disparity_src, ri.rvec, ri.tvec)]
+    a, b = mk(), mk()
+    mesh = mdb200.create_meshgrid(H, W, device=torch.device(DEV))
+    g = torch.Generator(device=DEV).manual_seed(2)
+    outs_a = mdb200.render_tgt_rgb_depth(a[0], a[1], a[2], None, mdb200.Pose(a[3], a[4]), ri.K_inv, ri.K, depth_eps=1e-5)
+    w = [torch.rand(o.shape, device=DEV, generator=g) for o in (outs_a[0], outs_a[1], outs_a[3])]
+    w[2] *= 0.01
+    (outs_a[0] * w[0]).sum().add((outs_a[1] * w[1]).sum()).add((outs_a[3] * w[2]).sum()).backward()
+    # materialised: d_xyz_tgt chained by hand through the producers in float64 on the host
+    xyz_src = mdb200.get_src_xyz_from_plane_disparity(mesh, b[2].detach(), ri.K_inv)
+    xyz_tgt = mdb200.get_tgt_xyz_from_plane_disparity(xyz_src, mdb200.Pose(b[3].detach(), b[4].detach())).requires_grad_()
+    outs_b = mdb200.render_tgt_rgb_depth(b[0], b[1], b[2], xyz_tgt, mdb200.Pose(b[3], b[4]), ri.K_inv, ri.K, depth_eps=1e-5)
+    for oa, ob in zip((outs_a[0], outs_a[1], outs_a[3]), (outs_b[0], outs_b[1], outs_b[3])):
+        assert (oa - ob).abs().max() <= 2e-5 * ob.abs().max()
+    assert torch.equal(outs_a[2], outs_b[2])
+    (outs_b[0] * w[0]).sum().add((outs_b[1] * w[1]).sum()).add((outs_b[3] * w[2]).sum()).backward()
+    assert (a[0].grad - b[0].grad).abs().max() <= 1e-4 * b[0].grad.abs().max()
+    assert (a[1].grad - b[1].grad).abs().max() <= 1e-4 * b[1].grad.abs().max()
+    # d tvec: the fused path adds sum(d_xyz_tgt) to what the homography path gives
+    gt = b[4].grad + xyz_tgt.grad.sum(dim=(1, 2, 3))
+    assert (a[4].grad - gt).abs().max() <= 1e-4 * gt.abs().max()

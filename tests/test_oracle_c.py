@@ -177,3 +177,41 @@ def test_render_c_oracle_reproduces_golden():
     for k in ("rgb", "sigma", "disparity_src", "xyz_tgt", "rvec", "tvec"):
         ref = z["d_" + k]
         assert np.abs(got["d_" + k] - ref).max() < 1e-9 * np.abs(ref).max(), k
+
+
+# ---- the variants (MINE grid / mask, expected depth, producers folded in) -----------
+@pytest.mark.parametrize("mine_grid,mine_mask,fused,rand_xyz", [(True, True, False, True), (True, False, True, False),
+                                                                (False, True, True, False), (False, False, False, True)])
+def test_render_variants_two_oracles_agree(mine_grid, mine_mask, fused, rand_xyz):
+    W, H, Np, B = 24, 16, 5, 2
+    ri = _render_case(W, H, Np, B, 90, 3.0, rand_xyz and not fused)
+    f = lambda a: torch.tensor(a, dtype=torch.float64, requires_grad=True)
+    rgb, sig, dsp, xyz, rv, tv = f(ri.rgb), f(ri.sigma), f(ri.disparity_src), f(ri.xyz_tgt), f(ri.rvec), f(ri.tvec)
+    ro, do, mo, zo = T.render_tgt_rgb_depth(rgb, sig, dsp, None if fused else xyz, T.Pose(rv, tv),
+                                            torch.tensor(ri.K_inv.astype(np.float64)), torch.tensor(ri.K.astype(np.float64)),
+                                            mine_grid=mine_grid, mine_mask=mine_mask, depth_eps=1e-5)
+    g = torch.Generator().manual_seed(2)
+    wr, wd, wz = (torch.rand(t.shape, generator=g, dtype=torch.float64) for t in (ro, do, zo))
+    leaves = (rgb, sig, dsp, rv, tv) if fused else (rgb, sig, dsp, xyz, rv, tv)
+    refs = torch.autograd.grad((ro * wr).sum() + (do * wd).sum() + (zo * wz).sum(), leaves)
+    got = c_ref.render_tgt_rgb_depth(ri.rgb, ri.sigma, ri.disparity_src, None if fused else ri.xyz_tgt, ri.rvec, ri.tvec,
+                                     ri.K_inv, ri.K, g_rgb=wr.numpy(), g_depth=wd.numpy(), g_expected_depth=wz.numpy(),
+                                     mine_grid=mine_grid, mine_mask=mine_mask, depth_eps=1e-5, threads=3)
+    assert np.abs(got["rgb"] - ro.detach().numpy()).max() < 1e-12
+    assert np.abs(got["depth"] - do.detach().numpy()).max() < 1e-12
+    assert np.abs(got["expected_depth"] - zo.detach().numpy()).max() < 1e-9 * np.abs(zo.detach().numpy()).max()
+    assert np.array_equal(got["mask"], mo.numpy())
+    names = ["d_rgb", "d_sigma", "d_disparity_src", "d_rvec", "d_tvec"] if fused else \
+            ["d_rgb", "d_sigma", "d_disparity_src", "d_xyz_tgt", "d_rvec", "d_tvec"]
+    for name, r in zip(names, refs):
+        _close(name, got[name], r, 1e-9)
+
+
+def test_plane_xyz_producers_match_torch():
+    ri = synth.make_render_inputs(20, 12, 4, 2, seed=5)
+    xs, xt = c_ref.plane_xyz(20, 12, ri.disparity_src, ri.rvec, ri.tvec, ri.K_inv)
+    f = lambda a: torch.tensor(a, dtype=torch.float64)
+    ts = T.get_src_xyz_from_plane_disparity(T.create_meshgrid(12, 20), f(ri.disparity_src), f(ri.K_inv))
+    tt = T.get_tgt_xyz_from_plane_disparity(ts, T.Pose(f(ri.rvec), f(ri.tvec)))
+    assert np.abs(xs - ts.numpy()).max() < 1e-12 * np.abs(xs).max()
+    assert np.abs(xt - tt.numpy()).max() < 1e-12 * np.abs(xt).max()
