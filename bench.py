@@ -397,38 +397,50 @@ def run_render(args):
     g_rgb = torch.rand((B, 3, H, W), device=dev)
     g_dep = torch.rand((B, Np, 1, H, W), device=dev) * 0.1
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-    f_ms, b_ms = [], []
-    l0 = None
-    plan = mdb200.RenderPlan(W, H, Np, B, ri.K_inv, ri.K, device=dev)
     pose = mdb200.Pose(rvec, tvec)
-    for it in range(args.warmup + args.steps):
-        if it == args.warmup:
-            l0 = mdb200.launch_count()
-        flush.zero_()
-        e = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
-        e[0].record()
-        plan.forward(rgb, sigma, disp, xyz, pose)
-        e[1].record()
-        flush.zero_()
-        e[2].record()
-        plan.backward(g_rgb, g_dep)
-        e[3].record()
-        torch.cuda.synchronize()
-        if it >= args.warmup:
-            f_ms.append(e[0].elapsed_time(e[1])); b_ms.append(e[2].elapsed_time(e[3]))
-    launches = mdb200.launch_count() - l0
-    fm, bm = sum(f_ms) / len(f_ms), sum(b_ms) / len(b_ms)
+
+    def time_plan(plan, xyz_in, g_z=None):
+        f_ms, b_ms, l0 = [], [], None
+        for it in range(args.warmup + args.steps):
+            if it == args.warmup:
+                l0 = mdb200.launch_count()
+            flush.zero_()
+            e = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+            e[0].record()
+            plan.forward(rgb, sigma, disp, xyz_in, pose)
+            e[1].record()
+            flush.zero_()
+            e[2].record()
+            plan.backward(g_rgb, g_dep, g_z)
+            e[3].record()
+            torch.cuda.synchronize()
+            if it >= args.warmup:
+                f_ms.append(e[0].elapsed_time(e[1])); b_ms.append(e[2].elapsed_time(e[3]))
+        return sum(f_ms) / len(f_ms), sum(b_ms) / len(b_ms), mdb200.launch_count() - l0
+
+    fm, bm, launches = time_plan(mdb200.RenderPlan(W, H, Np, B, ri.K_inv, ri.K, device=dev), xyz)
+    # SURVEY 8(f) rank 2 variants, same inputs: (a) as written but xyz_tgt never materialised; (b) the sampler MINE
+    # intends (samples land inside the image instead of on the border), its mask, the expected depth, no xyz_tgt
+    g_z = torch.rand((B, 1, H, W), device=dev) * 0.01
+    fa, ba, _ = time_plan(mdb200.RenderPlan(W, H, Np, B, ri.K_inv, ri.K, device=dev, fused_xyz=True), None)
+    fb, bb, _ = time_plan(mdb200.RenderPlan(W, H, Np, B, ri.K_inv, ri.K, device=dev, fused_xyz=True, mine_grid=True,
+                                            mine_mask=True, expected_depth=True), None, g_z)
+    fc, bc, _ = time_plan(mdb200.RenderPlan(W, H, Np, B, ri.K_inv, ri.K, device=dev, mine_grid=True, mine_mask=True), xyz)
     units = W * H * Np * B
     inp = 7 * units * 4
     outb = (3 * W * H * B + units) * 4
     peak, peak_src = load_peaks()
     fwd_b, bwd_b = inp + outb, 2 * inp + outb
+    variants = {
+        "fused_xyz (as written, xyz_tgt not an input: 4/7 of the input bytes)": {"fwd_ms": fa, "bwd_ms": ba},
+        "mine_grid + mine_mask (xyz_tgt given)": {"fwd_ms": fc, "bwd_ms": bc},
+        "mine_grid + mine_mask + expected_depth + fused_xyz": {"fwd_ms": fb, "bwd_ms": bb}}
     line = {"metric": "plane-px/s (render_tgt_rgb_depth fwd+bwd)", "value": units / ((fm + bm) * 1e-3), "unit": "plane_px/s",
             "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": fm + bm, "higher_is_better": True,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"config4: {W}x{H}, {Np} planes, B={B}, render_tgt_rgb_depth fwd+bwd", "l2": "flushed between calls",
                        "timing": "CUDA events around the pre-planned C-ABI calls (mdb200.RenderPlan: buffers allocated once)"},
-            "gpu_launches": int(launches),
+            "gpu_launches": int(launches), "variants": variants,
             "roofline": {"bound": "hbm", "kernel": "render_fwd_kernel + render_bwd_kernel", "unit": "GB/s", "peak": peak, "peak_source": peak_src,
                          "note": "ncu (profiles/r1_strip_summary.md): the forward issues 370 thread-instructions per plane-pixel and "
                                  "touches 39.5 MB of DRAM at B=2 (the reference's grid normalisation clamps 3/4 of the samples onto "

@@ -242,6 +242,75 @@ function ChainRulesCore.rrule(::typeof(render_tgt_rgb_depth), rgb, sigma, dispar
     (rgb_out, depth, mask), render_pullback
 end
 
+# ---- SURVEY 8(f) rank 2: render variants (mdb_render_opts) ------------------------------------------
+struct RenderOpts          # mdb_render_opts
+    mine_grid::Int32       # grid = (x + 0.5) / (W/2) - 1, align_corners=false   (test/test_sample.jl:131-137)
+    mine_mask::Int32       # valid = -1 < x < W                                    (test/test_sample.jl:123-125)
+    depth_eps::Cfloat      # expected depth = sum w z / (sum w + depth_eps)        (src/render.jl:47 TODO)
+    reserved::Int32
+end
+
+"""
+    render_tgt_rgb_depth_ex(rgb, sigma, disparity_src, xyz_tgt_or_nothing, pose, K_inv, K;
+                            mine_grid=false, mine_mask=false, depth_eps=1f-5)
+
+-> (rgb, transparency_acc, mask, expected_depth, weights_sum).  `xyz_tgt === nothing` folds
+`get_src_xyz_from_plane_disparity` / `get_tgt_xyz_from_plane_disparity` (src/render.jl:25-30, 51-62) into the
+kernels.  The rrule below calls `mdb_render_tgt_rgb_depth_bwd_ex` with the saved outputs.
+"""
+function render_tgt_rgb_depth_ex(rgb::CuArray{Float32,5}, sigma::CuArray{Float32,5}, disparity_src::CuArray{Float32,2},
+                                 xyz_tgt::Union{Nothing,CuArray{Float32,5}}, pose::Pose, K_inv, K;
+                                 mine_grid::Bool=false, mine_mask::Bool=false, depth_eps::Real=1f-5)
+    W, H, _, Np, B = size(rgb)
+    rgb_out = CUDA.zeros(Float32, W, H, 3, B); depth = CUDA.zeros(Float32, W, H, 1, Np, B)
+    mask = CUDA.zeros(Int32, W, H, 1, 1, B)
+    zexp = CUDA.zeros(Float32, W, H, 1, B); wsum = CUDA.zeros(Float32, W, H, 1, B)
+    nbytes = ccall((:mdb_render_workspace_bytes, libmdb200), Csize_t, (Int32, Int32, Int32, Int32), W, H, Np, B)
+    ws = CuArray{UInt8}(undef, nbytes)
+    Ki, Kk = collect(k9(K_inv)), collect(k9(K))
+    opts = Ref(RenderOpts(mine_grid, mine_mask, depth_eps, 0))
+    xp = xyz_tgt === nothing ? CuPtr{Cfloat}(0) : pointer(xyz_tgt)
+    GC.@preserve rgb sigma disparity_src xyz_tgt pose rgb_out depth mask zexp wsum ws opts check(ccall(
+        (:mdb_render_tgt_rgb_depth_fwd_ex, libmdb200), Int32,
+        (Ptr{Cvoid}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, Ptr{Cfloat}, Ptr{Cfloat},
+         Int32, Int32, Int32, Int32, Ptr{RenderOpts}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Int32}, CuPtr{Cfloat}, CuPtr{Cfloat},
+         CuPtr{Cvoid}, Csize_t, Ptr{Cvoid}),
+        handle(), rgb, sigma, disparity_src, xp, pose.rvec, pose.tvec, Ki, Kk, W, H, Np, B, opts, rgb_out, depth, mask, zexp, wsum,
+        ws, nbytes, stream_ptr()))
+    rgb_out, depth, mask, zexp, wsum
+end
+
+function ChainRulesCore.rrule(::typeof(render_tgt_rgb_depth_ex), rgb, sigma, disparity_src, xyz_tgt, pose::Pose, K_inv, K;
+                              mine_grid::Bool=false, mine_mask::Bool=false, depth_eps::Real=1f-5)
+    outs = render_tgt_rgb_depth_ex(rgb, sigma, disparity_src, xyz_tgt, pose, K_inv, K; mine_grid, mine_mask, depth_eps)
+    rgb_out, depth, mask, zexp, wsum = outs
+    function render_ex_pullback(Δ)
+        W, H, _, Np, B = size(rgb)
+        cot(i, like) = Δ[i] isa AbstractZero ? CUDA.zeros(Float32, size(like)) : CuArray{Float32}(unthunk(Δ[i]))
+        g_rgb, g_depth, g_z = cot(1, rgb_out), cot(2, depth), cot(4, zexp)
+        d_rgb, d_sigma = similar(rgb), similar(sigma)
+        d_xyz = xyz_tgt === nothing ? nothing : similar(xyz_tgt)
+        d_disp, d_r, d_t = similar(disparity_src), similar(pose.rvec), similar(pose.tvec)
+        nbytes = ccall((:mdb_render_workspace_bytes, libmdb200), Csize_t, (Int32, Int32, Int32, Int32), W, H, Np, B)
+        ws = CuArray{UInt8}(undef, nbytes)
+        Ki, Kk = collect(k9(K_inv)), collect(k9(K))
+        opts = Ref(RenderOpts(mine_grid, mine_mask, depth_eps, 0))
+        null = CuPtr{Cfloat}(0)
+        xp, dxp = xyz_tgt === nothing ? (null, null) : (pointer(xyz_tgt), pointer(d_xyz))
+        GC.@preserve rgb sigma disparity_src xyz_tgt pose depth zexp wsum g_rgb g_depth g_z d_rgb d_sigma d_xyz d_disp d_r d_t ws opts check(ccall(
+            (:mdb_render_tgt_rgb_depth_bwd_ex, libmdb200), Int32,
+            (Ptr{Cvoid}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, Ptr{Cfloat}, Ptr{Cfloat},
+             Int32, Int32, Int32, Int32, Ptr{RenderOpts}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat},
+             CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cfloat}, CuPtr{Cvoid},
+             Csize_t, Ptr{Cvoid}),
+            handle(), rgb, sigma, disparity_src, xp, pose.rvec, pose.tvec, Ki, Kk, W, H, Np, B, opts, depth, zexp, wsum, g_rgb, g_depth,
+            g_z, d_rgb, d_sigma, dxp, d_disp, d_r, d_t, ws, nbytes, stream_ptr()))
+        NoTangent(), d_rgb, d_sigma, d_disp, (d_xyz === nothing ? NoTangent() : d_xyz), Tangent{Pose}(rvec=d_r, tvec=d_t),
+        NoTangent(), NoTangent()
+    end
+    outs, render_ex_pullback
+end
+
 # ---- SURVEY 8(f) rank 1: slow_depth's optimiser loop on the device (src/simple_depth.jl:1-62) ---------
 struct AdamParams          # mdb_adam_params
     eta::Cdouble
