@@ -184,7 +184,7 @@ __global__ void min2_kernel(const float* __restrict__ a, const float* __restrict
 }
 
 // ---- smooth_loss (S2) -- src/utils.jl:163-177 -----------------------------------------
-constexpr int SM_THREADS = 256, SM_ROWS = 16;
+constexpr int SM_THREADS = 256, SM_ROWS = 16, SM_ROWS_MIN = 8;   // the workspace holds partials for 8-row blocks
 
 // Thread = column, walking down SM_ROWS rows: the row below is loaded one step ahead, the vertical edge
 // weight is carried to the next row, the horizontal one comes from the left lane by shuffle -- each edge's
@@ -269,6 +269,124 @@ smooth_kernel(const float* __restrict__ disp, const float* __restrict__ img, int
     float v = 0.0f;
     for (int w = 0; w < SM_THREADS / 32; ++w) v += red[w][threadIdx.x];
     part[((size_t)n * gridDim.x + rb) * 2 + threadIdx.x] = v;
+  }
+}
+
+// The same walk with four columns per thread (W % 4 == 0, 16-byte aligned rows): 128-bit loads and stores --
+// four times the bytes in flight per load instruction -- three of the four horizontal edges inside the thread,
+// one shuffle exchange per four columns.
+template <int C>
+__global__ void __launch_bounds__(SM_THREADS)
+smooth4_kernel(const float* __restrict__ disp, const float* __restrict__ img, int W, int H, int N, int rows,
+               float kx, float ky, float* __restrict__ part, float* __restrict__ grad) {
+  const int n = blockIdx.y, rb = blockIdx.x;
+  const size_t plane = (size_t)W * H;
+  const float* d = disp + n * plane;
+  const float* im = img + (size_t)n * C * plane;
+  const int y0 = rb * rows, y1 = min(y0 + rows, H);
+  const int lane = threadIdx.x & 31;
+  const float invC = 1.0f / (float)C;
+  float ax = 0.0f, ay = 0.0f;
+  auto ld4 = [](const float* p, float* o) { const float4 q = __ldg(reinterpret_cast<const float4*>(p)); o[0] = q.x; o[1] = q.y; o[2] = q.z; o[3] = q.w; };
+  for (int gx0 = 0; gx0 < W; gx0 += 4 * SM_THREADS) {
+    const int gx = gx0 + 4 * threadIdx.x;                  // first of this thread's four columns
+    const bool cv = gx < W;
+    const int gxc = cv ? gx : W - 4;
+    float v[5], I[C][5], vd[4], Id[C][4], tup[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+    ld4(d + (size_t)y0 * W + gxc, v);
+#pragma unroll
+    for (int c = 0; c < C; ++c) ld4(im + c * plane + (size_t)y0 * W + gxc, I[c]);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      vd[j] = 0.0f;
+#pragma unroll
+      for (int c = 0; c < C; ++c) Id[c][j] = 0.0f;
+    }
+    if (y0 > 0) {                                          // seam: the edges to the previous block's last row
+      float vu[4], Iu[C][4];
+      ld4(d + (size_t)(y0 - 1) * W + gxc, vu);
+#pragma unroll
+      for (int c = 0; c < C; ++c) ld4(im + c * plane + (size_t)(y0 - 1) * W + gxc, Iu[c]);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float e = 0.0f;
+#pragma unroll
+        for (int c = 0; c < C; ++c) e += fabsf(Iu[c][j] - I[c][j]);
+        tup[j] = ky * sgnf(vu[j] - v[j]) * __expf(-e * invC);
+      }
+    }
+    for (int gy = y0; gy < y1; ++gy) {
+      const bool has_dn = gy + 1 < H;
+      if (has_dn) {
+        ld4(d + (size_t)(gy + 1) * W + gxc, vd);
+#pragma unroll
+        for (int c = 0; c < C; ++c) ld4(im + c * plane + (size_t)(gy + 1) * W + gxc, Id[c]);
+      }
+      // fifth column = the right neighbour's first: lane + 1, or a load at the warp seam
+      v[4] = __shfl_down_sync(MDB_FULL, v[0], 1);
+#pragma unroll
+      for (int c = 0; c < C; ++c) I[c][4] = __shfl_down_sync(MDB_FULL, I[c][0], 1);
+      const bool has_r = gx + 4 < W;
+      if (lane == 31 && has_r) {
+        v[4] = ldg(d + (size_t)gy * W + gx + 4);
+#pragma unroll
+        for (int c = 0; c < C; ++c) I[c][4] = ldg(im + c * plane + (size_t)gy * W + gx + 4);
+      }
+      float tr[4], g[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float e = 0.0f;
+#pragma unroll
+        for (int c = 0; c < C; ++c) e += fabsf(I[c][j] - I[c][j + 1]);
+        const float w = __expf(-e * invC), df = v[j] - v[j + 1];
+        const bool on = cv && (j < 3 || has_r);
+        ax += on ? fabsf(df) * w : 0.0f;
+        tr[j] = on ? kx * sgnf(df) * w : 0.0f;
+      }
+      // left edge of column 0 = the left lane's right edge of its column 3
+      float tl = __shfl_up_sync(MDB_FULL, tr[3], 1);
+      if (lane == 0) {
+        tl = 0.0f;
+        if (cv && gx > 0) {
+          float e = 0.0f;
+#pragma unroll
+          for (int c = 0; c < C; ++c) e += fabsf(ldg(im + c * plane + (size_t)gy * W + gx - 1) - I[c][0]);
+          tl = kx * sgnf(ldg(d + (size_t)gy * W + gx - 1) - v[0]) * __expf(-e * invC);
+        }
+      }
+      g[0] = tr[0] - tl; g[1] = tr[1] - tr[0]; g[2] = tr[2] - tr[1]; g[3] = tr[3] - tr[2];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        g[j] -= tup[j];
+        tup[j] = 0.0f;
+        if (cv && has_dn) {
+          float e = 0.0f;
+#pragma unroll
+          for (int c = 0; c < C; ++c) e += fabsf(I[c][j] - Id[c][j]);
+          const float w = __expf(-e * invC), df = v[j] - vd[j];
+          ay += fabsf(df) * w;
+          tup[j] = ky * sgnf(df) * w;
+          g[j] += tup[j];
+        }
+      }
+      if (grad && cv) *reinterpret_cast<float4*>(grad + n * plane + (size_t)gy * W + gx) = make_float4(g[0], g[1], g[2], g[3]);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        v[j] = vd[j];
+#pragma unroll
+        for (int c = 0; c < C; ++c) I[c][j] = Id[c][j];
+      }
+    }
+  }
+  __shared__ float red[SM_THREADS / 32][2];
+  const int warp = threadIdx.x >> 5;
+  ax = warp_sum(ax); ay = warp_sum(ay);
+  if (lane == 0) { red[warp][0] = ax; red[warp][1] = ay; }
+  __syncthreads();
+  if (threadIdx.x < 2) {
+    float s = 0.0f;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) s += red[w][threadIdx.x];
+    part[((size_t)n * gridDim.x + rb) * 2 + threadIdx.x] = s;
   }
 }
 
@@ -425,7 +543,7 @@ int32_t mdb_apply_mask(mdb_handle* h, const float* mask, const float* warp_loss,
 
 size_t mdb_smooth_loss_workspace_bytes(int32_t W, int32_t H, int32_t N) {
   if (W < 1 || H < 1 || N < 1) return 0;
-  return mdb_align_up(sizeof(float) * 2 * (size_t)N * ((H + SM_ROWS - 1) / SM_ROWS), 256);
+  return mdb_align_up(sizeof(float) * 2 * (size_t)N * ((H + SM_ROWS_MIN - 1) / SM_ROWS_MIN), 256);
 }
 
 int32_t mdb_smooth_loss(mdb_handle* h, const float* disparity, const float* image, int32_t W, int32_t H,
@@ -436,11 +554,31 @@ int32_t mdb_smooth_loss(mdb_handle* h, const float* disparity, const float* imag
               "mdb_smooth_loss: need W,H >= 2, 1 <= C <= 4, N <= 65535");
   MDB_REQUIRE(h, workspace && workspace_bytes >= mdb_smooth_loss_workspace_bytes(W, H, N) && ((uintptr_t)workspace & 255) == 0,
               MDB_E_WORKSPACE, "mdb_smooth_loss: workspace too small or misaligned");
-  const int rb = (H + SM_ROWS - 1) / SM_ROWS;
+  int rb = (H + SM_ROWS - 1) / SM_ROWS;
   const double kx = 1.0 / ((double)(W - 1) * H * N), ky = 1.0 / ((double)W * (H - 1) * N);
-  dim3 grid(rb, N);
   cudaStream_t st = (cudaStream_t)stream;
   float* part = (float*)workspace;
+  const bool vec4 = W % 4 == 0 && W >= 8 && (((uintptr_t)disparity | (uintptr_t)image | (uintptr_t)d_disparity) & 15) == 0;
+  if (vec4) {
+    // four columns per thread: a CTA covers 4 x threads columns; rows per CTA 16, or 8 when that fills the SMs better
+    const int threads = std::min(SM_THREADS, ((W / 4 + 31) / 32) * 32);
+    int rows = SM_ROWS;
+    if ((long long)rb * N < (long long)h->num_sms * 8) rows = SM_ROWS_MIN;
+    if (const char* e = getenv("MDB_SMOOTH_ROWS")) rows = std::max(SM_ROWS_MIN, atoi(e));
+    rb = (H + rows - 1) / rows;
+    dim3 grid4(rb, N);
+    switch (C) {
+      case 1: smooth4_kernel<1><<<grid4, threads, 0, st>>>(disparity, image, W, H, N, rows, (float)kx, (float)ky, part, d_disparity); break;
+      case 2: smooth4_kernel<2><<<grid4, threads, 0, st>>>(disparity, image, W, H, N, rows, (float)kx, (float)ky, part, d_disparity); break;
+      case 3: smooth4_kernel<3><<<grid4, threads, 0, st>>>(disparity, image, W, H, N, rows, (float)kx, (float)ky, part, d_disparity); break;
+      default: smooth4_kernel<4><<<grid4, threads, 0, st>>>(disparity, image, W, H, N, rows, (float)kx, (float)ky, part, d_disparity); break;
+    }
+    MDB_LAUNCHED(h);
+    smooth_finalize_kernel<<<1, 256, 0, st>>>((const float*)workspace, rb * N, kx, ky, loss);
+    MDB_LAUNCHED(h);
+    return MDB_OK;
+  }
+  dim3 grid(rb, N);
   switch (C) {
     case 1: smooth_kernel<1><<<grid, SM_THREADS, 0, st>>>(disparity, image, W, H, N, (float)kx, (float)ky, part, d_disparity); break;
     case 2: smooth_kernel<2><<<grid, SM_THREADS, 0, st>>>(disparity, image, W, H, N, (float)kx, (float)ky, part, d_disparity); break;

@@ -92,11 +92,15 @@ def test_smooth_loss():  # runtests.jl:70-83
     assert abs(float(mdb200.smooth_loss(disp, image)) - 0.2542) < 1e-4
 
 
-def test_smooth_loss_grad_vs_oracle():
+@pytest.mark.parametrize("N,C,H,W", [(3, 3, 19, 45),      # W % 4 != 0: one column per thread
+                                     (2, 3, 37, 48),      # four columns per thread, three row blocks, partial warp
+                                     (1, 1, 9, 1160),     # wider than one CTA's 1024 columns, Gray image
+                                     (2, 3, 24, 136)])    # warp seams inside the row
+def test_smooth_loss_grad_vs_oracle(N, C, H, W):
     import mdb200
     from oracle import torch_ref as T
     g = torch.Generator().manual_seed(1)
-    d = torch.rand(3, 19, 45, generator=g); im = torch.rand(3, 3, 19, 45, generator=g)
+    d = torch.rand(N, H, W, generator=g); im = torch.rand(N, C, H, W, generator=g)
     d64 = d.double().requires_grad_()
     l64 = T.smooth_loss(d64, im.double())
     (g64,) = torch.autograd.grad(l64, d64)
