@@ -34,6 +34,9 @@ constexpr int STRIP_NHEAD = 3;   // record head: photometric sum, smoothness x-s
 #ifndef STRIP_UNROLL
 #define STRIP_UNROLL 1   // 3: the three-row rings rotate by renaming instead of ~90 MOVs per row
 #endif
+#ifndef STRIP_CBASE
+#define STRIP_CBASE 1   // one 64-bit base per channel plane: two more register pairs, one IMAD.WIDE per tap address (4.51 -> 4.47 ms)
+#endif
 #ifndef STRIP_PIPE
 #define STRIP_PIPE 0   // 1: issue the loads of row r+1 before stages C and D of row r (software pipelining)
 #endif
@@ -80,6 +83,11 @@ MDB_DEV float sgn1(float v) { return v == 0.0f ? 0.0f : copysignf(1.0f, v); }
 template <int S> MDB_DEV Pk<S> pfma(Pk<S> a, float b, Pk<S> c) { return pfma(a, Pk<S>(b), c); }
 template <int S> MDB_DEV Pk<S> operator*(Pk<S> a, float b) { return a * Pk<S>(b); }
 template <int S> MDB_DEV Pk<S> operator+(Pk<S> a, float b) { return a + Pk<S>(b); }
+
+// The image row that ring row r stands for: the rows just outside the image are the reflected rows
+// 1 and H-2 (pad_reflect(1) of the WARPED image, src/utils.jl:30-31 -- the warp of target row 1 is computed
+// a second time instead of being copied), everything further out is never read.
+MDB_DEV int geo_row(int r, int H) { return r == -1 ? 1 : (r == H ? H - 2 : r); }
 
 struct StripGeom {
   int nstrips, nsegs, seg_rows, total;  // total = N * nsegs * nstrips * Ls warps
@@ -133,6 +141,15 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
     asm volatile("" : "+l"(xbi));
     xb = reinterpret_cast<const float*>(xbi);
   }
+#if STRIP_CBASE
+  const float* xbc[C];   // per-channel bases (opaque, like xb)
+#pragma unroll
+  for (int c = 0; c < C; ++c) {
+    unsigned long long t = (unsigned long long)(xb + (size_t)c * plane);
+    asm volatile("" : "+l"(t));
+    xbc[c] = reinterpret_cast<const float*>(t);
+  }
+#endif
   const unsigned tgt_off = a.tgt * C * planei;
   unsigned src_off[S];
 #pragma unroll
@@ -148,7 +165,7 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   double p1[S], p2[S], p3[S], i1[S], i2[S], i3[S], b0[S], b1[S], b3e[S];
   float b0f[S], b1f[S], b3f[S];
   {
-    const double px = (double)(gx + 1), py = (double)(Y0 - 2 + 1);
+    const double px = (double)(gx + 1), py = (double)(geo_row(Y0 - 2, H) + 1);
 #pragma unroll
     for (int s = 0; s < S; ++s) {
       const PosePrepD& pp = a.ppd[(size_t)n * S + s];
@@ -201,14 +218,13 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   P tv00[C], tv01[C], tv10[C], tv11[C];
   float ty_[C], td_ = 0.0f;
   P tfx, tfy, tmzx, tmzy, tuu, tvv;
-  bool tvalid = false;
   float dq = 0.0f;   // native disparity of the NEXT row to be issued, loaded one call ahead
   const int gxc = min(max(gx, 0), W - 1);   // loads of dead lanes / rows go to a clamped (valid) address
-  if (native) dq = ldg(dsp + (min(max(Y0 - 2, 0), H - 1) * W + gxc));
+  if (native) dq = ldg(dsp + (min(max(geo_row(Y0 - 2, H), 0), H - 1) * W + gxc));
 
   auto issue = [&](int r) {
-    tvalid = r >= 0 && r < H && colv;
-    const int rc = min(max(r, 0), H - 1);
+    const int rg = geo_row(r, H), rgn = geo_row(r + 1, H);   // warp-uniform
+    const int rc = min(max(rg, 0), H - 1);
     {   // unconditional (clamped addresses): nothing in flight is carried from one row to the next
       double dd_;
       if (native) {
@@ -260,6 +276,21 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
         // u, v only multiply dP'1, dP'2, which vanish where clamped: the clamped position is good enough
         tuu.set(s, (float)ix + (fxs + 1.0f)); tvv.set(s, (float)iy + (fys + 1.0f));
       }
+#if STRIP_CBASE
+      unsigned ob[S];
+#pragma unroll
+      for (int s = 0; s < S; ++s) ob[s] = ot[s] + (unsigned)W;
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+          const float* p = xbc[c] + ot[s];    // one IMAD.WIDE per address: the channel plane is in the base
+          const float* pb = xbc[c] + ob[s];
+          tv00[c].set(s, ldg(p)); tv01[c].set(s, ldg(p + 1));
+          tv10[c].set(s, ldg(pb)); tv11[c].set(s, ldg(pb + 1));
+        }
+      }
+#else
 #pragma unroll
       for (int c = 0; c < C; ++c) {
 #pragma unroll
@@ -270,25 +301,29 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
           tv10[c].set(s, ldg(pb)); tv11[c].set(s, ldg(pb + 1));
         }
       }
+#endif
     }
-    if (native) dq = ldg(dsp + (min(max(r + 1, 0), H - 1) * W + gxc));
+    if (native) dq = ldg(dsp + (min(max(rgn, 0), H - 1) * W + gxc));
+    const double stp = (double)(rgn - rg);   // 1 except around the two reflected rows
 #pragma unroll
-    for (int s = 0; s < S; ++s) { p1[s] += i1[s]; p2[s] += i2[s]; p3[s] += i3[s]; }
+    for (int s = 0; s < S; ++s) { p1[s] = fma(stp, i1[s], p1[s]); p2[s] = fma(stp, i2[s], p2[s]); p3[s] = fma(stp, i3[s], p3[s]); }
   };
 
   // bilinear value and its derivatives of the issued row -> xn, yn, dn; park the derivatives in `wslot`
   auto consume = [&](int wslot, P (&xn)[C], float (&yn)[C], float& dn) {
     {
-      dn = tvalid ? td_ : 0.0f;
+      // rows outside the image and columns outside it carry the (finite) values of the clamped addresses:
+      // nothing reads them unmasked -- window rows reflect (stage C), window columns reflect (nl, nr), the
+      // smoothness weights vanish across the border, and columns that are not window columns select no source
+      dn = td_;
       float park[DRV];
 #pragma unroll
       for (int c = 0; c < C; ++c) {
-        yn[c] = tvalid ? ty_[c] : 0.0f;
+        yn[c] = ty_[c];
         const P h0 = tv01[c] - tv00[c], h1 = tv11[c] - tv10[c];
         const P top = pfma(tfx, h0, tv00[c]), bot = pfma(tfx, h1, tv10[c]);
         const P dyv = bot - top;
         xn[c] = pfma(tfy, dyv, top);
-        if (!tvalid) xn[c] = P(0.0f);
         const P dxv = pfma(tfy, h1 - h0, h0);
         const P dxz = dxv * tmzx, dyz = dyv * tmzy;   // d sample / d P'1, d P'2 up to the common 1/z''
 #pragma unroll
@@ -296,12 +331,10 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
       }
 #pragma unroll
       for (int s = 0; s < S; ++s) { park[2 * C * S + s] = tuu.get(s); park[(2 * C + 1) * S + s] = tvv.get(s); }
-      if (tvalid) {
 #pragma unroll
-        for (int k = 0; k < DRV4; ++k)
-          s_drv[(wslot * DRV4 + k) * STRIP_THREADS + threadIdx.x] =
-              make_float4(park[4 * k], park[4 * k + 1], park[4 * k + 2], park[4 * k + 3]);
-      }
+      for (int k = 0; k < DRV4; ++k)
+        s_drv[(wslot * DRV4 + k) * STRIP_THREADS + threadIdx.x] =
+            make_float4(park[4 * k], park[4 * k + 1], park[4 * k + 2], park[4 * k + 3]);
     }
   };
 
@@ -329,15 +362,16 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
 #pragma unroll
     for (int k = 0; k < 3 * C; ++k) Fn[k] = 0.0f;
     if (r >= Y0 && wr >= 0 && wr < H) {             // warp-uniform
-      const bool rt = wr == 0, rb = wr == H - 1;    // reflected rows
+      // pad_reflect(1) along H (src/utils.jl:30-31) costs nothing here: the rows -1 and H that the ring
+      // delivers ARE rows 1 and H-2 (geo_row below), so the first and last window read top / bottom as usual
       P Mxa[C], Qxa[C], Cxya[C];
       float Mya[C], Qya[C];
       P vm[C], vq[C], vc[C];
       float vmy[C], vqy[C];
 #pragma unroll
       for (int c = 0; c < C; ++c) {
-        const P top = rt ? xn[c] : xr2[c], bot = rb ? xr2[c] : xn[c], mid = xr1[c];
-        const float ty = rt ? yn[c] : yr2[c], by = rb ? yr2[c] : yn[c], my_ = yr1[c];
+        const P top = xr2[c], bot = xn[c], mid = xr1[c];
+        const float ty = yr2[c], by = yn[c], my_ = yr1[c];
         const float e1 = ty - my_, e2 = by - my_, se = e1 + e2, se3 = se * (-1.0f / 3.0f);
         vmy[c] = fmaf(se, 1.0f / 3.0f, my_);
         vqy[c] = fmaf(e1, e1, fmaf(e2, e2, se * se3));
