@@ -193,6 +193,156 @@ upsample_bwd_h_kernel(const __grid_constant__ UpArgs a) {
   }
 }
 
+// 5b. The same transpose as ONE streaming kernel (W <= 256 KC, KC <= 16): a CTA owns a band of native rows
+//     of one (item, scale), walks down the full-res rows that touch them (each element is fetched once by
+//     the CTA; neighbouring bands re-read 2/r rows of each other, from L2), keeps the running vertical sums
+//     of the two native rows under the current full-res row in registers (thread = KC full-res columns),
+//     and every time a native row is complete hands it through shared memory to the horizontal pass.
+//     No tmp[dh][W] round trip and no second launch; summation order per output element is the one of
+//     the V and H kernels above (ascending py, then ascending px), which stay as the path for W > 4096.
+struct UpBandArgs {
+  const float* gfull[MDB_MAX_SCALES];
+  float* gnat[MDB_MAX_SCALES];
+  int dw[MDB_MAX_SCALES], dh[MDB_MAX_SCALES];
+  int band[MDB_MAX_SCALES];             // native rows per CTA (0: native scale)
+  int blk_start[MDB_MAX_SCALES + 1];    // blockIdx.x -> (scale, band); native scales own H / UPB_NATIVE_ROWS blocks
+  int Ls, W, H, N;
+};
+constexpr int UPB_NATIVE_ROWS = 8;
+
+#ifndef UPB_ROWS
+#define UPB_ROWS 8      // full-res rows per batch of loads (independent 128-bit loads in flight per thread)
+#endif
+#ifndef UPB_MINB
+#define UPB_MINB 4
+#endif
+constexpr int UPB_BAND = 8;                 // native rows per CTA at most (accumulators of the horizontal pass)
+constexpr int UPB_SMEM_BYTES = 32 * 1024;   // the band's vertically summed rows: band x W floats
+
+// G = floats per load (4: 128-bit, needs W % 4 == 0), NG = column groups per thread: W <= 256 G NG
+template <int G, int NG>
+__global__ void __launch_bounds__(256, (G * NG <= 4) ? UPB_MINB : 1)
+upsample_bwd_band_kernel(const __grid_constant__ UpBandArgs a, const ScaleStat* __restrict__ stats) {
+  extern __shared__ float4 s_rows4[];   // [band][W]
+  float* s_rows = reinterpret_cast<float*>(s_rows4);
+  const int n = blockIdx.y, W = a.W, H = a.H, tid = threadIdx.x;
+  int sc = 0;
+  while (sc + 1 < a.Ls && (int)blockIdx.x >= a.blk_start[sc + 1]) ++sc;
+  const int blk = blockIdx.x - a.blk_start[sc];
+  const float cc = stats[(size_t)sc * a.N + n].cconst;
+  if (a.band[sc] == 0) {   // native: the strip kernel wrote the gradient in place; add the constant
+    if (cc == 0.0f) return;
+    const int r0 = blk * UPB_NATIVE_ROWS, r1 = min(H, r0 + UPB_NATIVE_ROWS);
+    float* o = a.gnat[sc] + ((size_t)n * H + r0) * W;
+    const int cnt = (r1 - r0) * W;
+    if (G == 4) {
+      float4* o4 = reinterpret_cast<float4*>(o);
+      for (int i = tid; i < cnt / 4; i += 256) {
+        float4 q = o4[i];
+        q.x += cc; q.y += cc; q.z += cc; q.w += cc;
+        o4[i] = q;
+      }
+    } else {
+      for (int i = tid; i < cnt; i += 256) o[i] += cc;
+    }
+    return;
+  }
+  const int dw = a.dw[sc], dh = a.dh[sc], dy1 = dh - 1, H1 = H - 1, dx1 = dw - 1, W1 = W - 1;
+  const float ih = 1.0f / (float)H1, iw = 1.0f / (float)W1;
+  const int j0 = blk * a.band[sc], j1 = min(dh, j0 + a.band[sc]);   // native rows [j0, j1) of this CTA
+  // full-res rows whose lower native neighbour floor(py dy1 / H1) lies in [j0 - 1, j1 - 1]
+  const int py_s = j0 > 0 ? ((j0 - 1) * H1 + dy1 - 1) / dy1 : 0;
+  const int py_e = min(H, (j1 * H1 + dy1 - 1) / dy1);
+  const float* g = a.gfull[sc] + (size_t)n * W * H;
+
+  // ---- vertical pass: thread = G NG full-res columns, no barrier; lo / hi are the running sums of the
+  // native rows jcur and jcur + 1 = the two neighbours of the current full-res row.  (jcur, rem) = floor
+  // and remainder of py dy1 / H1, carried down the rows without divisions.
+  float lo[NG][G], hi[NG][G];
+#pragma unroll
+  for (int q = 0; q < NG; ++q)
+#pragma unroll
+    for (int e = 0; e < G; ++e) lo[q][e] = hi[q][e] = 0.0f;
+  auto park = [&](int j) {   // row j is complete: into the band's buffer
+    if (j < j0 || j >= j1) return;
+#pragma unroll
+    for (int q = 0; q < NG; ++q) {
+      const int px = G * (tid + 256 * q);
+      if (px < W) {
+        if (G == 4) s_rows4[((j - j0) * W + px) >> 2] = make_float4(lo[q][0], lo[q][1], lo[q][2], lo[q][3]);
+        else s_rows[(j - j0) * W + px] = lo[q][0];
+      }
+    }
+  };
+  constexpr int R = ((G == 4 ? UPB_ROWS : 2 * UPB_ROWS) / NG) > 0 ? ((G == 4 ? UPB_ROWS : 2 * UPB_ROWS) / NG) : 1;
+  int jcur = (py_s * dy1) / H1, rem = py_s * dy1 - jcur * H1;
+  for (int pb = py_s; pb < py_e; pb += R) {
+    float v[R][NG][G];
+#pragma unroll
+    for (int i = 0; i < R; ++i) {
+      const float* row = g + (size_t)(pb + i) * W;
+#pragma unroll
+      for (int q = 0; q < NG; ++q) {
+        const int px = G * (tid + 256 * q);
+        const bool on = pb + i < py_e && px < W;
+        if (G == 4) {
+          const float4 t = on ? __ldg(reinterpret_cast<const float4*>(row + px)) : make_float4(0.f, 0.f, 0.f, 0.f);
+          v[i][q][0] = t.x; v[i][q][1] = t.y; v[i][q][2] = t.z; v[i][q][3] = t.w;
+        } else {
+          v[i][q][0] = on ? ldg(row + px) : 0.0f;
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < R; ++i) {
+      if (pb + i < py_e) {   // CTA-uniform
+        if (rem >= H1) {     // moved on by one native row (dh <= H): row jcur is complete
+          park(jcur);
+#pragma unroll
+          for (int q = 0; q < NG; ++q)
+#pragma unroll
+            for (int e = 0; e < G; ++e) { lo[q][e] = hi[q][e]; hi[q][e] = 0.0f; }
+          ++jcur;
+          rem -= H1;
+        }
+        // the hat weights of upsample_bwd_v_kernel, for j = jcur and j = jcur + 1
+        const float wlo = fmaxf(1.0f - (float)rem * ih, 0.0f), whi = fmaxf(1.0f - (float)(H1 - rem) * ih, 0.0f);
+#pragma unroll
+        for (int q = 0; q < NG; ++q)
+#pragma unroll
+          for (int e = 0; e < G; ++e) {
+            const float x = v[i][q][e] + cc;
+            lo[q][e] = fmaf(wlo, x, lo[q][e]); hi[q][e] = fmaf(whi, x, hi[q][e]);
+          }
+        rem += dy1;
+      }
+    }
+  }
+  park(jcur);   // the last row the band's rows end in; its upper neighbour jcur + 1 belongs to the next band
+  __syncthreads();
+
+  // ---- horizontal pass: thread = native column jx of ALL the band's rows, so the tap range and the hat
+  // weights (which do not depend on the row) are formed once per column and tap
+  const int nrows = j1 - j0;
+  float* out = a.gnat[sc] + ((size_t)n * dh + j0) * dw;
+  for (int jx = tid; jx < dw; jx += 256) {
+    const int p0 = max(0, ((jx - 1) * W1) / dx1), p1 = min(W1, ((jx + 1) * W1 + dx1 - 1) / dx1);
+    float acc[UPB_BAND];
+#pragma unroll
+    for (int r = 0; r < UPB_BAND; ++r) acc[r] = 0.0f;
+    int num = p0 * dx1 - jx * W1;
+    for (int px = p0; px <= p1; ++px, num += dx1) {
+      const float wx = fmaxf(1.0f - (float)abs(num) * iw, 0.0f);
+#pragma unroll
+      for (int r = 0; r < UPB_BAND; ++r)
+        if (r < nrows) acc[r] = fmaf(wx, s_rows[r * W + px], acc[r]);
+    }
+#pragma unroll
+    for (int r = 0; r < UPB_BAND; ++r)
+      if (r < nrows) out[r * dw + jx] = acc[r];
+  }
+}
+
 // 6. scalar loss = up * sum(item photometric sums) + sum(smoothness terms)
 __global__ void finalize_loss_kernel(const double* __restrict__ item_loss, int N, const ScaleStat* __restrict__ stats,
                                      int nstats, double up, float* __restrict__ loss) {
@@ -398,17 +548,46 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
   else finalize_item_kernel<1><<<N, FIN_THREADS, 0, st>>>(fa.partials, L.records, pa, fin, stats, item_loss);
   MDB_LAUNCHED(h);
   {
-    dim3 gv((ua.row_start[Ls] + UP_ROWS - 1) / UP_ROWS, N), gh = gv;
     bool any_low = false;
     for (int s = 0; s < Ls; ++s) any_low = any_low || !fa.native[s];
+    const bool force_split = getenv("MDB_UPSAMPLE_SPLIT") != nullptr;   // tests: the two-kernel path (W > 4096)
     // native scales only receive the normalisation constant here: nothing to do without it (slow_depth)
-    if (any_low || p->normalize_disparity) {
+    if (!(any_low || p->normalize_disparity)) {
+    } else if (W <= 4096 && !force_split) {
+      UpBandArgs ub{};
+      ub.Ls = Ls; ub.W = W; ub.H = H; ub.N = N;
+      // native rows per band: what the shared-memory row buffer holds (8 at W = 1024), fewer when the launch
+      // could not give every SM a few CTAs otherwise
+      int band = std::min(UPB_BAND, std::max(1, UPB_SMEM_BYTES / (4 * W)));
+      auto blocks_for = [&](int band_) {
+        int b = 0;
+        for (int s = 0; s < Ls; ++s)
+          if (!fa.native[s]) b += (io->dh[s] + band_ - 1) / band_;
+        return b;
+      };
+      while (band > 2 && (long long)blocks_for(band) * N < 4ll * h->num_sms) band /= 2;   // stays <= UPB_BAND
+      for (int s = 0; s < Ls; ++s) {
+        ub.gfull[s] = ua.gfull[s]; ub.gnat[s] = ua.gnat[s]; ub.dw[s] = io->dw[s]; ub.dh[s] = io->dh[s];
+        ub.band[s] = fa.native[s] ? 0 : band;
+        const int nb = fa.native[s] ? (p->normalize_disparity ? (H + UPB_NATIVE_ROWS - 1) / UPB_NATIVE_ROWS : 0)
+                                    : (io->dh[s] + band - 1) / band;
+        ub.blk_start[s + 1] = ub.blk_start[s] + nb;
+      }
+      dim3 gb(ub.blk_start[Ls], N);
+      const size_t smem = (size_t)band * W * sizeof(float);
+      if (W % 4 == 0 && W <= 1024) upsample_bwd_band_kernel<4, 1><<<gb, 256, smem, st>>>(ub, stats);
+      else if (W % 4 == 0) upsample_bwd_band_kernel<4, 4><<<gb, 256, smem, st>>>(ub, stats);
+      else if (W <= 1024) upsample_bwd_band_kernel<1, 4><<<gb, 256, smem, st>>>(ub, stats);
+      else upsample_bwd_band_kernel<1, 16><<<gb, 256, smem, st>>>(ub, stats);
+      MDB_LAUNCHED(h);
+    } else {
+      dim3 gv((ua.row_start[Ls] + UP_ROWS - 1) / UP_ROWS, N), gh = gv;
       upsample_bwd_v_kernel<<<gv, 256, 0, st>>>(ua, stats);
       MDB_LAUNCHED(h);
-    }
-    if (any_low) {
-      upsample_bwd_h_kernel<<<gh, 256, 0, st>>>(ua);
-      MDB_LAUNCHED(h);
+      if (any_low) {
+        upsample_bwd_h_kernel<<<gh, 256, 0, st>>>(ua);
+        MDB_LAUNCHED(h);
+      }
     }
   }
   mdb_prof_mark(h, pslot, 3, st);

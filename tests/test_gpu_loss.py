@@ -183,6 +183,28 @@ def test_forced_row_segments(monkeypatch):
         _compare(inp, ref, resn)
 
 
+@pytest.mark.parametrize("W,H,N,scales", [
+    (104, 64, 3, (0.125, 0.25, 0.5, 1.0)),   # KC = 1, several bands per scale
+    (300, 37, 2, (0.25, 0.5, 1.0)),          # KC = 4, ragged columns, odd ratios (dh - 1 does not divide H - 1)
+    (1100, 24, 1, (0.5, 1.0)),               # KC = 16 (W > 1024)
+])
+def test_upsample_transpose_band_vs_split(monkeypatch, W, H, N, scales):
+    """The streaming band kernel (upsample_bwd_band_kernel) against the two-kernel V/H path it replaced
+    (kept for W > 4096, forced here by MDB_UPSAMPLE_SPLIT) and against the oracle."""
+    from mdb200 import synth
+    inp = synth.make_loss_inputs(W, H, N, seed=31, scales=scales)
+    ref = P.oracle_train_loss(inp)
+    monkeypatch.delenv("MDB_UPSAMPLE_SPLIT", raising=False)
+    res_band, _ = _run_gpu(inp)
+    monkeypatch.setenv("MDB_UPSAMPLE_SPLIT", "1")
+    res_split, _ = _run_gpu(inp)
+    _compare(inp, ref, res_band)
+    _compare(inp, ref, res_split)
+    for a, b in zip(res_band.d_disparities, res_split.d_disparities):
+        scale = float(b.abs().max())
+        assert float((a - b).abs().max()) <= 1e-6 * scale, (float((a - b).abs().max()), scale)
+
+
 @pytest.mark.parametrize("C", [1, 3])
 def test_single_source(C):
     """S = 1 (the scalar, un-packed instantiation of the kernel)."""
