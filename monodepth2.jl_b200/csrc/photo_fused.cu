@@ -50,10 +50,16 @@ disp_mean_kernel(const __grid_constant__ FusedArgs a, double* __restrict__ part 
       const float4* d4 = reinterpret_cast<const float4*>(d + i0);
       const int n4 = (i1 - i0) / 4;
       float s0 = 0.0f, s1 = 0.0f, s2 = 0.0f, s3 = 0.0f;   // <= 16 rows x W / 256 / 4 terms each: float is ample here
-#pragma unroll 4
-      for (int i = threadIdx.x; i < n4; i += MEAN_THREADS) {
-        const float4 v = __ldg(d4 + i);
-        s0 += v.x; s1 += v.y; s2 += v.z; s3 += v.w;
+      // batches of 8 independent 128-bit loads per thread (all 16 of a 1024-wide slab in two batches)
+      for (int b = threadIdx.x; b < n4; b += 8 * MEAN_THREADS) {
+        float4 v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int i = b + k * MEAN_THREADS;
+          v[k] = i < n4 ? __ldg(d4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { s0 += v[k].x; s1 += v[k].y; s2 += v[k].z; s3 += v[k].w; }
       }
       acc = ((double)s0 + (double)s1) + ((double)s2 + (double)s3);
       for (int i = i0 + 4 * n4 + threadIdx.x; i < i1; i += MEAN_THREADS) acc += (double)ldg(d + i);
@@ -66,18 +72,22 @@ disp_mean_kernel(const __grid_constant__ FusedArgs a, double* __restrict__ part 
     const int dx1 = dw - 1, dy1 = dh - 1, W1 = W - 1, H1 = H - 1;
     const int rows_per = (dh + gridDim.x - 1) / gridDim.x;
     const int j0 = rb * rows_per, j1 = min(j0 + rows_per, dh);
+    // the row weights are the same for every column: one thread per row forms them once
+    __shared__ double s_wy[MEAN_THREADS];
+    for (int jy = j0 + threadIdx.x; jy < j1; jy += MEAN_THREADS) {
+      const int py_lo = max(0, ((jy - 1) * H1) / dy1), py_hi = min(H1, ((jy + 1) * H1 + dy1 - 1) / dy1);
+      int numy = 0;
+      for (int py = py_lo; py <= py_hi; ++py) numy += max(0, H1 - abs(py * dy1 - jy * H1));
+      s_wy[jy - j0] = (double)numy / (double)H1;
+    }
+    __syncthreads();
     for (int jx = threadIdx.x; jx < dw; jx += MEAN_THREADS) {
       const int px_lo = max(0, ((jx - 1) * W1) / dx1), px_hi = min(W1, ((jx + 1) * W1 + dx1 - 1) / dx1);
       int numx = 0;   // sum of (W1 - |p dx1 - jx W1|) over the support, exact in int (< 2^31 for W < 2^15)
       for (int px = px_lo; px <= px_hi; ++px) numx += max(0, W1 - abs(px * dx1 - jx * W1));
       const double wx = (double)numx / (double)W1;
       double col = 0.0;
-      for (int jy = j0; jy < j1; ++jy) {
-        const int py_lo = max(0, ((jy - 1) * H1) / dy1), py_hi = min(H1, ((jy + 1) * H1 + dy1 - 1) / dy1);
-        int numy = 0;
-        for (int py = py_lo; py <= py_hi; ++py) numy += max(0, H1 - abs(py * dy1 - jy * H1));
-        col = fma((double)numy / (double)H1, (double)ldg(d + jy * dw + jx), col);
-      }
+      for (int jy = j0; jy < j1; ++jy) col = fma(s_wy[jy - j0], (double)ldg(d + jy * dw + jx), col);
       acc = fma(wx, col, acc);
     }
   }
