@@ -14,8 +14,8 @@
 //   4. finalize_item_kernel    fixed-order sum of the records (double): photometric sum, pose chain
 //                              back to (rvec, tvec), smoothness loss and the constant the
 //                              mean-normalisation adds to every disparity gradient
-//   5. upsample_bwd_kernel     transpose of upsample_bilinear for the low-res scales (gather) and
-//                              the constant for the native ones
+//   5. upsample_bwd_band_kernel transpose of upsample_bilinear for the low-res scales (one streaming
+//                              gather pass per band of native rows) and the constant for the native ones
 //   6. finalize_loss_kernel    scalar loss
 // No float atomics anywhere: results are bit-reproducible run to run.
 #include "photo_fused.cuh"
