@@ -37,6 +37,10 @@ constexpr int STRIP_NHEAD = 3;   // record head: photometric sum, smoothness x-s
 #ifndef STRIP_CBASE
 #define STRIP_CBASE 1   // one 64-bit base per channel plane: two more register pairs, one IMAD.WIDE per tap address (4.51 -> 4.47 ms)
 #endif
+#ifndef STRIP_AM_EARLY
+#define STRIP_AM_EARLY 1   // fetch the automask value with the row's tap loads (stage A): ptxas sinks a load placed in stage C to 28-80
+                           // instructions before its use and the warp eats the latency every row (config 3: 0.939 -> 0.879 ms)
+#endif
 #ifndef STRIP_PIPE
 #define STRIP_PIPE 0   // 1: issue the loads of row r+1 before stages C and D of row r (software pipelining)
 #endif
@@ -155,6 +159,7 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
 #pragma unroll
   for (int s = 0; s < S; ++s) src_off[s] = a.src[s] * C * planei;
   const float* dsp = a.disp[sc] + (size_t)n * a.dw[sc] * a.dh[sc];
+  const float* amb = a.automask ? a.auto_loss + (size_t)n * plane : nullptr;
   float* gout = a.gout[sc] + (size_t)n * plane;
   const bool native = a.native[sc] != 0;
   const int dw = a.dw[sc], dh = a.dh[sc];
@@ -217,6 +222,9 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   // the bilinear weights and masks
   P tv00[C], tv01[C], tv10[C], tv11[C];
   float ty_[C], td_ = 0.0f;
+#if STRIP_AM_EARLY
+  float tam = 0.0f;
+#endif
   P tfx, tfy, tmzx, tmzy, tuu, tvv;
   float dq = 0.0f;   // native disparity of the NEXT row to be issued, loaded one call ahead
   const int gxc = min(max(gx, 0), W - 1);   // loads of dead lanes / rows go to a clamped (valid) address
@@ -247,6 +255,9 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
       const double invd = fma(dd_, a.dd_d, a.mind_d);   // 1 / depth (src/utils.jl:179-183)
 #pragma unroll
       for (int c = 0; c < C; ++c) ty_[c] = ldg(xb + (unsigned)(tgt_off + c * planei + rc * W + gxc));
+#if STRIP_AM_EARLY
+      if (a.automask) tam = ldg(amb + (unsigned)(min(max(r - 1, 0), H - 1) * W + gxc));   // window row r-1, used in stage C
+#endif
 
       unsigned ot[S];   // top-left tap; the other three are +1, +W, +W+1 (x0 <= W-2, y0 <= H-2 always)
 #pragma unroll
@@ -364,6 +375,13 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
     if (r >= Y0 && wr >= 0 && wr < H) {             // warp-uniform
       // pad_reflect(1) along H (src/utils.jl:30-31) costs nothing here: the rows -1 and H that the ring
       // delivers ARE rows 1 and H-2 (geo_row below), so the first and last window read top / bottom as usual
+#if STRIP_AM_EARLY
+      const float am = tam;
+#else
+      // the automask value of this window row, fetched before the ~300 instructions that precede its use
+      float am = 0.0f;
+      if (a.automask) am = ldg(amb + (unsigned)(wr * W + gxc));
+#endif
       P Mxa[C], Qxa[C], Cxya[C];
       float Mya[C], Qya[C];
       P vm[C], vq[C], vc[C];
@@ -435,10 +453,7 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
 #pragma unroll
       for (int s = 1; s < S; ++s)
         if (lossv.get(s) < val) { val = lossv.get(s); best = s; }   // first arg-min wins ties
-      if (a.automask && wcol) {
-        const float am = ldg(a.auto_loss + (size_t)n * plane + (size_t)wr * W + gx);
-        if (am <= val) { val = am; best = SEL_NONE; }               // mask precedes warp_loss
-      }
+      if (a.automask && wcol && am <= val) { val = am; best = SEL_NONE; }   // mask precedes warp_loss
       if (!wcol) best = SEL_NONE;
       seln = best;
 #pragma unroll
