@@ -42,7 +42,8 @@ constexpr int STRIP_NHEAD = 3;   // record head: photometric sum, smoothness x-s
                            // instructions before its use and the warp eats the latency every row (config 3: 0.939 -> 0.879 ms)
 #endif
 #ifndef STRIP_PIPE
-#define STRIP_PIPE 0   // 1: issue the loads of row r+1 before stages C and D of row r (software pipelining)
+#define STRIP_PIPE 0   // software pipelining: issue the loads of row r+1 before stages C and D of row r (1; needs
+                       // STRIP_AM_EARLY=0) or between them (2)
 #endif
 #if !defined(STRIP_MAXREG) && !defined(STRIP_MINB)
 #define STRIP_MAXREG 152   // 13 warps per SM, no spills: measured best of 128 / 136 / 144 / 152 / 160 / 168 / 184
@@ -351,6 +352,22 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
 
   P xn[C];
   float yn[C], dn = 0.0f;
+  float Fn[3 * C];
+  int seln = SEL_NONE;
+#pragma unroll
+  for (int c = 0; c < C; ++c) { xn[c] = P(0.0f); yn[c] = 0.0f; }
+#pragma unroll
+  for (int k = 0; k < 3 * C; ++k) Fn[k] = 0.0f;
+  // ---- rotate the rings: row r becomes row r-1 ... ---------------------------------------------
+  auto rotate = [&]() {
+#pragma unroll
+    for (int c = 0; c < C; ++c) { xr2[c] = xr1[c]; xr1[c] = xn[c]; yr2[c] = yr1[c]; yr1[c] = yn[c]; }
+#pragma unroll
+    for (int k = 0; k < 3 * C; ++k) { F2[k] = F1[k]; F1[k] = Fn[k]; }
+    sel2 = sel1; sel1 = seln;
+    d3 = d2; d2 = d1; d1 = dn;
+    slot = (slot + 1) % 3;
+  };
 #if STRIP_PIPE
   issue(Y0 - 2);
   consume(slot, xn, yn, dn);
@@ -358,18 +375,47 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   constexpr int kUnroll = STRIP_UNROLL;
 #pragma unroll kUnroll
   for (int r = Y0 - 2; r <= Y1 + 1; ++r) {
-#if STRIP_PIPE
+#if STRIP_PIPE == 1
     if (r < Y1 + 1) issue(r + 1);   // its loads are consumed after C and D below
-#else
+#elif STRIP_PIPE == 0
     issue(r);
+#endif
+    // ---- smoothness of pixel row r-2 (src/utils.jl:163-177): needs nothing of row r, so it runs in the
+    // shadow of the loads just issued; one register (its pullback) crosses stages C and D
+    const int pr = r - 2;
+    float gsm = 0.0f;
+    {
+      const float wy_up = wy_dn;
+      if (r >= Y0 + 1) {  // weight between rows r-2 and r-1 (and wy_up of the next iteration)
+        float e = 0.0f;
+#pragma unroll
+        for (int c = 0; c < C; ++c) e += fabsf(yr2[c] - yr1[c]);
+        wy_dn = (pr >= 0 && pr + 1 < H) ? __expf(-e * (1.0f / C)) : 0.0f;
+      }
+      if (r >= Y0 + 2) {  // warp-uniform; pr in [Y0, Y1)
+        const float dl = __shfl_sync(MDB_FULL, d2, max(lane - 1, 0)), dr = __shfl_sync(MDB_FULL, d2, min(lane + 1, 31));
+        float ex = 0.0f;
+#pragma unroll
+        for (int c = 0; c < C; ++c) ex += fabsf(yr2[c] - __shfl_sync(MDB_FULL, yr2[c], min(lane + 1, 31)));
+        const float wxr = (gx >= 0 && gx + 1 < W) ? __expf(-ex * (1.0f / C)) : 0.0f;
+        const float wxl = __shfl_sync(MDB_FULL, wxr, max(lane - 1, 0));
+        if (pcol) {
+          // the weights are already zero across the image border
+          const float gsx = sgn1(d2 - dr) * wxr - sgn1(dl - d2) * wxl;
+          const float gsy = sgn1(d2 - d1) * wy_dn - sgn1(d3 - d2) * wy_up;
+          gsm = skx * gsx + sky * gsy;
+          smx_acc = fmaf(fabsf(d2 - dr), wxr, smx_acc);
+          smy_acc = fmaf(fabsf(d2 - d1), wy_dn, smy_acc);
+        }
+      }
+    }
+#if !STRIP_PIPE
     consume(slot, xn, yn, dn);
 #endif
 
-
     // =========================== C: window row r-1 =============================================
     const int wr = r - 1;
-    float Fn[3 * C];
-    int seln = SEL_NONE;
+    seln = SEL_NONE;
 #pragma unroll
     for (int k = 0; k < 3 * C; ++k) Fn[k] = 0.0f;
     if (r >= Y0 && wr >= 0 && wr < H) {             // warp-uniform
@@ -471,15 +517,10 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
       }
     }
 
+#if STRIP_PIPE == 2
+    if (r < Y1 + 1) issue(r + 1);   // in flight during stage D only; consumed at the end of the iteration
+#endif
     // =========================== D: pixel row r-2 ==============================================
-    const int pr = r - 2;
-    const float wy_up = wy_dn;
-    if (r >= Y0 + 1) {  // weight between rows r-2 and r-1 (needed below, and as wy_up next iteration)
-      float e = 0.0f;
-#pragma unroll
-      for (int c = 0; c < C; ++c) e += fabsf(yr2[c] - yr1[c]);
-      wy_dn = (pr >= 0 && pr + 1 < H) ? __expf(-e * (1.0f / C)) : 0.0f;
-    }
     if (r >= Y0 + 2) {  // warp-uniform; pr in [Y0, Y1)
       // box sums of the coefficient fields over the 3x3 windows containing this pixel, per source
       const float wu = (pr == 1) ? 2.0f : 1.0f, wd = (pr == H - 2) ? 2.0f : 1.0f;
@@ -495,13 +536,6 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
         const P VL = V.shfl(lane - 1 < 0 ? 0 : lane - 1), VR = V.shfl(lane + 1 > 31 ? 31 : lane + 1);
         T[k] = pfma(VL, wl, pfma(VR, wr_, V));
       }
-      // smoothness neighbours (src/utils.jl:163-177)
-      const float dl = __shfl_sync(MDB_FULL, d2, max(lane - 1, 0)), dr = __shfl_sync(MDB_FULL, d2, min(lane + 1, 31));
-      float ex = 0.0f;
-#pragma unroll
-      for (int c = 0; c < C; ++c) ex += fabsf(yr2[c] - __shfl_sync(MDB_FULL, yr2[c], min(lane + 1, 31)));
-      const float wxr = (gx >= 0 && gx + 1 < W) ? __expf(-ex * (1.0f / C)) : 0.0f;
-      const float wxl = __shfl_sync(MDB_FULL, wxr, max(lane - 1, 0));
       if (pcol) {
         const float4* dv = s_drv + (size_t)((slot + 1) % 3 * DRV4) * STRIP_THREADS + threadIdx.x;
         float park[DRV];
@@ -542,26 +576,13 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
 #pragma unroll
         for (int s = 0; s < S; ++s)
           dinvd += dP0.get(s) * b0f[s] + dP1.get(s) * b1f[s] + dP2.get(s) * b3f[s];
-        float gr = dinvd * a.dd;   // d invd / d disparity = 1/min_depth - 1/max_depth
-        float gsx = 0.0f, gsy = 0.0f;
-        // the weights are already zero across the image border
-        gsx = sgn1(d2 - dr) * wxr - sgn1(dl - d2) * wxl;
-        gsy = sgn1(d2 - d1) * wy_dn - sgn1(d3 - d2) * wy_up;
-        gr += skx * gsx + sky * gsy;   // the mean-normalisation constant is added after the item's sum is known
-        smx_acc = fmaf(fabsf(d2 - dr), wxr, smx_acc);
-        smy_acc = fmaf(fabsf(d2 - d1), wy_dn, smy_acc);
-        gout[(size_t)pr * W + gx] = gr;
+        // d invd / d disparity = 1/min_depth - 1/max_depth; plus the smoothness pullback formed above
+        // (the mean-normalisation constant is added after the item's sum is known)
+        gout[(size_t)pr * W + gx] = fmaf(dinvd, a.dd, gsm);
       }
     }
 
-    // ---- rotate the rings ---------------------------------------------------------------------
-#pragma unroll
-    for (int c = 0; c < C; ++c) { xr2[c] = xr1[c]; xr1[c] = xn[c]; yr2[c] = yr1[c]; yr1[c] = yn[c]; }
-#pragma unroll
-    for (int k = 0; k < 3 * C; ++k) { F2[k] = F1[k]; F1[k] = Fn[k]; }
-    sel2 = sel1; sel1 = seln;
-    d3 = d2; d2 = d1; d1 = dn;
-    slot = (slot + 1) % 3;
+    rotate();
 #if STRIP_PIPE
     if (r < Y1 + 1) consume(slot, xn, yn, dn);
 #endif
