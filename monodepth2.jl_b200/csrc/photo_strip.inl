@@ -41,6 +41,9 @@ constexpr int STRIP_NHEAD = 3;   // record head: photometric sum, smoothness x-s
 #define STRIP_AM_EARLY 1   // fetch the automask value with the row's tap loads (stage A): ptxas sinks a load placed in stage C to 28-80
                            // instructions before its use and the warp eats the latency every row (config 3: 0.939 -> 0.879 ms)
 #endif
+#ifndef STRIP_DPF
+#define STRIP_DPF 1     // low-res disparity: the next native row is fetched one step ahead (its use no longer waits)
+#endif
 #ifndef STRIP_PIPE
 #define STRIP_PIPE 0   // software pipelining: issue the loads of row r+1 before stages C and D of row r (1; needs
                        // STRIP_AM_EARLY=0) or between them (2)
@@ -184,8 +187,14 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
     }
   }
   // bilinear up-sampling of the disparity (align-corners): the column part is per lane
+#if STRIP_DPF
+  int ux0 = 0, ux1 = 0, uy0 = -2;          // uy0: native row whose column-interpolated values are cached (-2: none)
+  double ulx = 0.0, utop = 0.0, ubot = 0.0;
+  float nv0 = 0.0f, nv1 = 0.0f;            // native row uy0 + 2 at columns ux0, ux1, fetched one step ahead
+#else
   int ux0 = 0, ux1 = 0, uy0 = -1;          // uy0: native row whose column-interpolated values are cached
   double ulx = 0.0, utop = 0.0, udif = 0.0;
+#endif
   if (!native) {
     const double f = (double)min(max(gx, 0), W - 1) * a.rxd[sc];
     ux0 = min((int)f, dw - 1);
@@ -242,6 +251,26 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
         // rows of the low-res map change every 1/ry full-res rows: keep the column-interpolated pair
         const double fy = (double)rc * ryd;
         const int y0 = min((int)fy, dh - 1);
+#if STRIP_DPF
+        if (y0 != uy0) {   // warp-uniform
+          if (y0 == uy0 + 1) {
+            // one native row further down (the usual step): the new bottom row was fetched when the
+            // previous step happened, >= 1 full-res row ago -- nothing to wait for
+            utop = ubot;
+            ubot = fma(ulx, (double)nv1 - (double)nv0, (double)nv0);
+          } else {   // first row of the segment, or a reflected row stepping back
+            const int y1 = min(y0 + 1, dh - 1);
+            const double v00 = ldg(dsp + (y0 * dw + ux0)), v01 = ldg(dsp + (y0 * dw + ux1));
+            const double v10 = ldg(dsp + (y1 * dw + ux0)), v11 = ldg(dsp + (y1 * dw + ux1));
+            utop = fma(ulx, v01 - v00, v00);
+            ubot = fma(ulx, v11 - v10, v10);
+          }
+          uy0 = y0;
+          const int y2 = min(y0 + 2, dh - 1);   // bottom row of the next step
+          nv0 = ldg(dsp + (y2 * dw + ux0)); nv1 = ldg(dsp + (y2 * dw + ux1));
+        }
+        dd_ = fma(fy - (double)y0, ubot - utop, utop);
+#else
         if (y0 != uy0) {   // warp-uniform
           uy0 = y0;
           const int y1 = min(y0 + 1, dh - 1);
@@ -251,6 +280,7 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
           udif = fma(ulx, v11 - v10, v10) - utop;
         }
         dd_ = fma(fy - (double)y0, udif, utop);
+#endif
       }
       td_ = (float)dd_;
       const double invd = fma(dd_, a.dd_d, a.mind_d);   // 1 / depth (src/utils.jl:179-183)
