@@ -216,12 +216,16 @@ constexpr int UPB_NATIVE_ROWS = 8;
 #ifndef UPB_MINB
 #define UPB_MINB 4
 #endif
+#ifndef UPB_NG
+#define UPB_NG 1        // 128-bit column groups per thread at W <= 1024 (the CTA has 256 / UPB_NG threads); measured
+                        // 1 / 2 / 4 -> segment 0.108 / 0.124 / 0.196 ms: parallelism matters more than the per-row bookkeeping
+#endif
 constexpr int UPB_BAND = 8;                 // native rows per CTA at most (accumulators of the horizontal pass)
 constexpr int UPB_SMEM_BYTES = 32 * 1024;   // the band's vertically summed rows: band x W floats
 
-// G = floats per load (4: 128-bit, needs W % 4 == 0), NG = column groups per thread: W <= 256 G NG
-template <int G, int NG>
-__global__ void __launch_bounds__(256, (G * NG <= 4) ? UPB_MINB : 1)
+// G = floats per load (4: 128-bit, needs W % 4 == 0), NG = column groups per thread, TPB threads: W <= TPB G NG.
+template <int G, int NG, int TPB>
+__global__ void __launch_bounds__(TPB, (G * NG * TPB <= 1024) ? (UPB_MINB * 256 / TPB) : 1)
 upsample_bwd_band_kernel(const __grid_constant__ UpBandArgs a, const ScaleStat* __restrict__ stats) {
   extern __shared__ float4 s_rows4[];   // [band][W]
   float* s_rows = reinterpret_cast<float*>(s_rows4);
@@ -237,13 +241,13 @@ upsample_bwd_band_kernel(const __grid_constant__ UpBandArgs a, const ScaleStat* 
     const int cnt = (r1 - r0) * W;
     if (G == 4) {
       float4* o4 = reinterpret_cast<float4*>(o);
-      for (int i = tid; i < cnt / 4; i += 256) {
+      for (int i = tid; i < cnt / 4; i += TPB) {
         float4 q = o4[i];
         q.x += cc; q.y += cc; q.z += cc; q.w += cc;
         o4[i] = q;
       }
     } else {
-      for (int i = tid; i < cnt; i += 256) o[i] += cc;
+      for (int i = tid; i < cnt; i += TPB) o[i] += cc;
     }
     return;
   }
@@ -267,7 +271,7 @@ upsample_bwd_band_kernel(const __grid_constant__ UpBandArgs a, const ScaleStat* 
     if (j < j0 || j >= j1) return;
 #pragma unroll
     for (int q = 0; q < NG; ++q) {
-      const int px = G * (tid + 256 * q);
+      const int px = G * (tid + TPB * q);
       if (px < W) {
         if (G == 4) s_rows4[((j - j0) * W + px) >> 2] = make_float4(lo[q][0], lo[q][1], lo[q][2], lo[q][3]);
         else s_rows[(j - j0) * W + px] = lo[q][0];
@@ -283,7 +287,7 @@ upsample_bwd_band_kernel(const __grid_constant__ UpBandArgs a, const ScaleStat* 
       const float* row = g + (size_t)(pb + i) * W;
 #pragma unroll
       for (int q = 0; q < NG; ++q) {
-        const int px = G * (tid + 256 * q);
+        const int px = G * (tid + TPB * q);
         const bool on = pb + i < py_e && px < W;
         if (G == 4) {
           const float4 t = on ? __ldg(reinterpret_cast<const float4*>(row + px)) : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -325,7 +329,7 @@ upsample_bwd_band_kernel(const __grid_constant__ UpBandArgs a, const ScaleStat* 
   // weights (which do not depend on the row) are formed once per column and tap
   const int nrows = j1 - j0;
   float* out = a.gnat[sc] + ((size_t)n * dh + j0) * dw;
-  for (int jx = tid; jx < dw; jx += 256) {
+  for (int jx = tid; jx < dw; jx += TPB) {
     const int p0 = max(0, ((jx - 1) * W1) / dx1), p1 = min(W1, ((jx + 1) * W1 + dx1 - 1) / dx1);
     float acc[UPB_BAND];
 #pragma unroll
@@ -575,10 +579,10 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
       }
       dim3 gb(ub.blk_start[Ls], N);
       const size_t smem = (size_t)band * W * sizeof(float);
-      if (W % 4 == 0 && W <= 1024) upsample_bwd_band_kernel<4, 1><<<gb, 256, smem, st>>>(ub, stats);
-      else if (W % 4 == 0) upsample_bwd_band_kernel<4, 4><<<gb, 256, smem, st>>>(ub, stats);
-      else if (W <= 1024) upsample_bwd_band_kernel<1, 4><<<gb, 256, smem, st>>>(ub, stats);
-      else upsample_bwd_band_kernel<1, 16><<<gb, 256, smem, st>>>(ub, stats);
+      if (W % 4 == 0 && W <= 1024) upsample_bwd_band_kernel<4, UPB_NG, 256 / UPB_NG><<<gb, 256 / UPB_NG, smem, st>>>(ub, stats);
+      else if (W % 4 == 0) upsample_bwd_band_kernel<4, 4, 256><<<gb, 256, smem, st>>>(ub, stats);
+      else if (W <= 1024) upsample_bwd_band_kernel<1, 4, 256><<<gb, 256, smem, st>>>(ub, stats);
+      else upsample_bwd_band_kernel<1, 16, 256><<<gb, 256, smem, st>>>(ub, stats);
       MDB_LAUNCHED(h);
     } else {
       dim3 gv((ua.row_start[Ls] + UP_ROWS - 1) / UP_ROWS, N), gh = gv;
