@@ -16,7 +16,7 @@
 //                              mean-normalisation adds to every disparity gradient
 //   5. upsample_bwd_band_kernel transpose of upsample_bilinear for the low-res scales (one streaming
 //                              gather pass per band of native rows) and the constant for the native ones
-//   6. finalize_loss_kernel    scalar loss
+//   6. (inside 4)              scalar loss, by the finalize CTA that finishes last
 // No float atomics anywhere: results are bit-reproducible run to run.
 #include "photo_fused.cuh"
 #include "pose_math.cuh"
@@ -107,8 +107,10 @@ disp_mean_kernel(const __grid_constant__ FusedArgs a, double* __restrict__ part 
 // 2. pose prep (threads [0, N S)) and mean -> normalisation factor (threads [N S, N S + Ls N))
 // ---------------------------------------------------------------------------------------
 __global__ void prep_kernel(PoseArgs a, PosePrepD* __restrict__ outd, const double* __restrict__ mean_part,
-                            int rowblocks, int Ls, int W, int H, int normalize, ScaleStat* __restrict__ stats) {
+                            int rowblocks, int Ls, int W, int H, int normalize, ScaleStat* __restrict__ stats,
+                            unsigned* __restrict__ done_counter) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx == 0) *done_counter = 0u;   // finalize_item_kernel's last-CTA election
   if (idx < a.N * a.S) {
     const int n = idx / a.S, s = idx % a.S;
     double r[3], t[3], Rp[9], tp[3], KR[9], A[9];

@@ -16,7 +16,10 @@ struct FinArgs {
   float kx[MDB_MAX_SCALES], ky[MDB_MAX_SCALES];
   int Ls, N, W, H, normalize;
   double up;          // 1 / (W H Ng Ls): weight of the photometric sum in the loss
-  float* loss_out;    // non-null only when N == 1: the scalar loss is written here (no separate launch)
+  float* loss_out;    // non-null only when N == 1: the scalar loss is written here by the item's own CTA
+  // N > 1: the CTA that finishes last (done_counter, zeroed by prep_kernel) sums the items in fixed order
+  unsigned* done_counter;
+  float* loss_final;
 };
 
 template <int S>
@@ -83,7 +86,7 @@ finalize_item_kernel(const float* __restrict__ partials, int records, PoseArgs p
   __syncthreads();
   if (threadIdx.x == 0) {
     item_loss[n] = tot[0];
-    if (fa.loss_out) *fa.loss_out = (float)(tot[0] * fa.up + sloss);   // N == 1: same sum as finalize_loss_kernel
+    if (fa.loss_out) *fa.loss_out = (float)(tot[0] * fa.up + sloss);   // N == 1: same sum as below
   }
   if (threadIdx.x < S) {
     const int s = threadIdx.x;
@@ -102,6 +105,32 @@ finalize_item_kernel(const float* __restrict__ partials, int records, PoseArgs p
     for (int k = 0; k < 3; ++k) {
       if (fa.d_rvec[s]) fa.d_rvec[s][3 * n + k] = (float)dr[k];
       if (fa.d_tvec[s]) fa.d_tvec[s][3 * n + k] = (float)dt[k];
+    }
+  }
+  // 6. scalar loss = up * sum(item photometric sums) + sum(smoothness terms), by the last CTA to get here
+  //    (fixed summation order whichever CTA that is: bit-reproducible)
+  if (fa.done_counter) {
+    __shared__ bool last;
+    __syncthreads();   // thread 0's item_loss / stats stores precede its fence below
+    if (threadIdx.x == 0) {
+      __threadfence();
+      last = atomicAdd(fa.done_counter, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (last) {
+      __threadfence();
+      double v = 0.0;
+      for (int i = threadIdx.x; i < fa.N; i += FIN_THREADS) v += __ldcg(item_loss + i) * fa.up;
+      for (int i = threadIdx.x; i < fa.Ls * fa.N; i += FIN_THREADS) v += (double)__ldcg(&stats[i].loss);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(MDB_FULL, v, o);
+      if (lane == 0) sred[warp][0] = v;
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < FIN_THREADS / 32; ++w) t += sred[w][0];
+        *fa.loss_final = (float)t;
+      }
     }
   }
 }
@@ -347,26 +376,8 @@ upsample_bwd_band_kernel(const __grid_constant__ UpBandArgs a, const ScaleStat* 
   }
 }
 
-// 6. scalar loss = up * sum(item photometric sums) + sum(smoothness terms)
-__global__ void finalize_loss_kernel(const double* __restrict__ item_loss, int N, const ScaleStat* __restrict__ stats,
-                                     int nstats, double up, float* __restrict__ loss) {
-  __shared__ double red[32];
-  double v = 0.0;
-  for (int i = threadIdx.x; i < N; i += blockDim.x) v += item_loss[i] * up;
-  for (int i = threadIdx.x; i < nstats; i += blockDim.x) v += (double)stats[i].loss;
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(MDB_FULL, v, o);
-  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    double s = 0.0;
-    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) s += red[w];
-    *loss = (float)s;
-  }
-}
-
 struct FusedLayout {
-  size_t o_ppd, o_meanpart, o_stats, o_partials, o_itemloss, o_gfull[MDB_MAX_SCALES], o_tmp[MDB_MAX_SCALES], total;
+  size_t o_ppd, o_meanpart, o_stats, o_partials, o_itemloss, o_counter, o_gfull[MDB_MAX_SCALES], o_tmp[MDB_MAX_SCALES], total;
   int rowblocks, npart;
   StripGeom strip;   // decomposition of the streaming kernel
   int records;       // partial-sum records per item = warps per item
@@ -408,6 +419,7 @@ FusedLayout fused_layout(const mdb_loss_io* io, int num_sms = 148) {
   L.records = L.strip.nsegs * L.strip.nstrips * io->Ls;
   L.o_partials = take(sizeof(float) * (size_t)io->N * L.records * L.npart);
   L.o_itemloss = take(sizeof(double) * io->N);
+  L.o_counter = take(sizeof(unsigned));
   for (int s = 0; s < io->Ls; ++s) {
     const bool native = io->dw[s] == io->W && io->dh[s] == io->H;
     L.o_gfull[s] = native ? 0 : take(sizeof(float) * (size_t)io->N * io->W * io->H);
@@ -521,6 +533,8 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
   fin.Ls = Ls; fin.N = N; fin.W = W; fin.H = H; fin.normalize = p->normalize_disparity;
   fin.up = up;
   fin.loss_out = (N == 1) ? io->loss : nullptr;
+  fin.done_counter = (N == 1) ? nullptr : (unsigned*)(ws + L.o_counter);
+  fin.loss_final = io->loss;
   ua.Ls = Ls; ua.W = W; ua.H = H; ua.N = N;
   ScaleStat* stats = (ScaleStat*)(ws + L.o_stats);
   double* mean_part = (double*)(ws + L.o_meanpart);
@@ -535,7 +549,7 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
     }
     const int threads = N * S + Ls * N;
     prep_kernel<<<(threads + 127) / 128, 128, 0, st>>>(pa, (PosePrepD*)(ws + L.o_ppd), mean_part, L.rowblocks, Ls, W, H,
-                                                       p->normalize_disparity, stats);
+                                                       p->normalize_disparity, stats, (unsigned*)(ws + L.o_counter));
     MDB_LAUNCHED(h);
   }
   mdb_prof_mark(h, pslot, 1, st);
@@ -595,10 +609,7 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
     }
   }
   mdb_prof_mark(h, pslot, 3, st);
-  if (N > 1) {   // N == 1: finalize_item_kernel already wrote the scalar
-    finalize_loss_kernel<<<1, 256, 0, st>>>(item_loss, N, stats, Ls * N, up, io->loss);
-    MDB_LAUNCHED(h);
-  }
+  // the scalar loss was written by finalize_item_kernel (its last CTA): no launch of its own
   mdb_prof_mark(h, pslot, 4, st);
   return MDB_OK;
 }
