@@ -593,8 +593,11 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
       }
       dim3 gb(ub.blk_start[Ls], N);
       const size_t smem = (size_t)band * W * sizeof(float);
-      if (W % 4 == 0 && W <= 1024) upsample_bwd_band_kernel<4, UPB_NG, 256 / UPB_NG><<<gb, 256 / UPB_NG, smem, st>>>(ub, stats);
-      else if (W % 4 == 0) upsample_bwd_band_kernel<4, 4, 256><<<gb, 256, smem, st>>>(ub, stats);
+      // 128-bit accesses need W % 4 == 0 and 16-byte aligned caller buffers (the native maps are updated in place)
+      bool vec = W % 4 == 0;
+      for (int s = 0; s < Ls; ++s) vec = vec && (!fa.native[s] || ((uintptr_t)io->d_disparity[s] & 15) == 0);
+      if (vec && W <= 1024) upsample_bwd_band_kernel<4, UPB_NG, 256 / UPB_NG><<<gb, 256 / UPB_NG, smem, st>>>(ub, stats);
+      else if (vec) upsample_bwd_band_kernel<4, 4, 256><<<gb, 256, smem, st>>>(ub, stats);
       else if (W <= 1024) upsample_bwd_band_kernel<1, 4, 256><<<gb, 256, smem, st>>>(ub, stats);
       else upsample_bwd_band_kernel<1, 16, 256><<<gb, 256, smem, st>>>(ub, stats);
       MDB_LAUNCHED(h);
