@@ -32,8 +32,7 @@ finalize_item_kernel(const float* __restrict__ partials, int records, PoseArgs p
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   __shared__ double red[FIN_THREADS / 32][NRED];
   __shared__ double tot[NRED];
-  __shared__ double sred[FIN_THREADS / 32][2];
-  __shared__ double sloss;   // sum of the smoothness losses of this item's scales (thread 0 only)
+  __shared__ double sred[FIN_THREADS / 32][MDB_MAX_SCALES][2];
 
   double acc[NRED];
 #pragma unroll
@@ -51,45 +50,49 @@ finalize_item_kernel(const float* __restrict__ partials, int records, PoseArgs p
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(MDB_FULL, v, o);
     if (lane == 0) red[warp][k] = v;
   }
-  __syncthreads();
-  if (threadIdx.x < NRED) {
-    double v = 0.0;
-    for (int w = 0; w < FIN_THREADS / 32; ++w) v += red[w][threadIdx.x];
-    tot[threadIdx.x] = v;
-  }
-  // smoothness (src/utils.jl:163-177, src/training.jl:64-67): records are ordered [..][scale]
+  // smoothness sums per scale (src/utils.jl:163-177, src/training.jl:64-67): records are ordered [..][scale]
   const int per_scale = records / fa.Ls;
-  for (int sc = 0; sc < fa.Ls; ++sc) {
-    double sx = 0.0, sy = 0.0;
-    for (int t = threadIdx.x; t < per_scale; t += FIN_THREADS) {
-      const float* p = partials + ((size_t)n * records + (size_t)t * fa.Ls + sc) * NPART;
-      sx += (double)p[1]; sy += (double)p[2];
-    }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) { sx += __shfl_xor_sync(MDB_FULL, sx, o); sy += __shfl_xor_sync(MDB_FULL, sy, o); }
-    __syncthreads();   // sred reuse (and, first time round, tot[] visible below)
-    if (lane == 0) { sred[warp][0] = sx; sred[warp][1] = sy; }
-    __syncthreads();
-    if (threadIdx.x == 0) {
+  for (int sc = 0; sc < MDB_MAX_SCALES; ++sc) {
+    if (sc < fa.Ls) {
+      double sx = 0.0, sy = 0.0;
+      for (int t = threadIdx.x; t < per_scale; t += FIN_THREADS) {
+        const float* p = partials + ((size_t)n * records + (size_t)t * fa.Ls + sc) * NPART;
+        sx += (double)p[1]; sy += (double)p[2];
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) { sx += __shfl_xor_sync(MDB_FULL, sx, o); sy += __shfl_xor_sync(MDB_FULL, sy, o); }
+      if (lane == 0) { sred[warp][sc][0] = sx; sred[warp][sc][1] = sy; }
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x >= 64 && threadIdx.x < 64 + NRED) {
+    double v = 0.0;
+    for (int w = 0; w < FIN_THREADS / 32; ++w) v += red[w][threadIdx.x - 64];
+    tot[threadIdx.x - 64] = v;
+  }
+  __syncthreads();
+  // from here two chains run side by side on different warps: thread 0 closes the smoothness terms and the
+  // item's loss, threads 32 .. 32+S-1 pull the pose sums back to (rvec, tvec) -- ~550 dependent FP64 operations
+  if (threadIdx.x == 0) {
+    double sloss = 0.0;
+    for (int sc = 0; sc < fa.Ls; ++sc) {
       double tx = 0.0, ty = 0.0;
-      for (int w = 0; w < FIN_THREADS / 32; ++w) { tx += sred[w][0]; ty += sred[w][1]; }
+      for (int w = 0; w < FIN_THREADS / 32; ++w) { tx += sred[w][sc][0]; ty += sred[w][sc][1]; }
       ScaleStat st = stats[(size_t)sc * fa.N + n];
       const double inv_mp = (double)st.inv_mp;
       const double l = ((double)fa.kx[sc] * tx + (double)fa.ky[sc] * ty) * inv_mp;
       st.loss = (float)l;
-      sloss = (sc ? sloss : 0.0) + (double)st.loss;
+      sloss += (double)st.loss;
       // d/dd of S(d / (m + eps)): the part through the mean is the constant -S / ((m + eps) W H)
       st.cconst = fa.normalize ? (float)(-l * inv_mp / ((double)fa.W * fa.H)) : 0.0f;
       stats[(size_t)sc * fa.N + n] = st;
     }
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {
     item_loss[n] = tot[0];
     if (fa.loss_out) *fa.loss_out = (float)(tot[0] * fa.up + sloss);   // N == 1: same sum as below
   }
-  if (threadIdx.x < S) {
-    const int s = threadIdx.x;
+  if (threadIdx.x >= 32 && threadIdx.x < 32 + S) {
+    const int s = threadIdx.x - 32;
     const double* dA = tot + 1 + s * NPOSE;  // row-major dL/dA
     const double* db = dA + 9;
     // A = K R' invK  ->  dR' = K^T dA invK^T ;  b = K t' -> dt' = K^T db
@@ -124,11 +127,11 @@ finalize_item_kernel(const float* __restrict__ partials, int records, PoseArgs p
       for (int i = threadIdx.x; i < fa.Ls * fa.N; i += FIN_THREADS) v += (double)__ldcg(&stats[i].loss);
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(MDB_FULL, v, o);
-      if (lane == 0) sred[warp][0] = v;
+      if (lane == 0) red[warp][0] = v;
       __syncthreads();
       if (threadIdx.x == 0) {
         double t = 0.0;
-        for (int w = 0; w < FIN_THREADS / 32; ++w) t += sred[w][0];
+        for (int w = 0; w < FIN_THREADS / 32; ++w) t += red[w][0];
         *fa.loss_final = (float)t;
       }
     }
