@@ -252,7 +252,10 @@ constexpr int UPB_NATIVE_ROWS = 8;
 #define UPB_NG 1        // 128-bit column groups per thread at W <= 1024 (the CTA has 256 / UPB_NG threads); measured
                         // 1 / 2 / 4 -> segment 0.108 / 0.124 / 0.196 ms: parallelism matters more than the per-row bookkeeping
 #endif
-constexpr int UPB_BAND = 8;                 // native rows per CTA at most (accumulators of the horizontal pass)
+#ifndef UPB_BAND_ROWS
+#define UPB_BAND_ROWS 4   // measured 4 / 6 / 8 -> segment 0.102 / 0.108 / 0.109 ms at config 5 (more CTAs beat less overlap)
+#endif
+constexpr int UPB_BAND = UPB_BAND_ROWS;     // native rows per CTA at most (accumulators of the horizontal pass; <= 8)
 constexpr int UPB_SMEM_BYTES = 32 * 1024;   // the band's vertically summed rows: band x W floats
 
 // G = floats per load (4: 128-bit, needs W % 4 == 0), NG = column groups per thread, TPB threads: W <= TPB G NG.
