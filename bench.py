@@ -353,20 +353,20 @@ def run_ours(args):
             "roofline": {"bound": "hbm", "kernel": "photo_strip_kernel<3,2>", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak,
                          # dram__bytes_read.sum + dram__bytes_write.sum of this launch at config 5, batch 64
-                         # (profiles/r1_step_b64_v8.csv); null for any other workload
-                         "traffic": 963130112 if (args.config == "config5" and N == 64) else None,
+                         # (profiles/r1_step_b64_v9.csv); null for any other workload
+                         "traffic": 965726464 if (args.config == "config5" and N == 64) else None,
                          "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": b_alg, "kernel_ms": k_ms,
                          "segments_ms": {"prep_stats": float(seg[:, 0].mean()), "fused": k_ms,
                                          "upsample_bwd": float(seg[:, 2].mean()), "finalize": float(seg[:, 3].mean())},
                          # what actually bounds the kernel (profiles/r1_strip_summary.md): instruction issue
-                         "issue_bound": {"thread_instr_per_warped_px": 595.1, "issue_peak_thread_instr_per_s": 148 * 4 * 32 * 1.965e9,
-                                         "floor_ms": units_per_rank * 595.1 / (148 * 4 * 32 * 1.965e9) * 1e3,
-                                         "frac": units_per_rank * 595.1 / (148 * 4 * 32 * 1.965e9) * 1e3 / k_ms,
-                                         "source": "smsp__inst_executed.sum x 32 / warped px (ncu, profiles/r1_step_b64_v8.csv); "
+                         "issue_bound": {"thread_instr_per_warped_px": 597.9, "issue_peak_thread_instr_per_s": 148 * 4 * 32 * 1.965e9,
+                                         "floor_ms": units_per_rank * 597.9 / (148 * 4 * 32 * 1.965e9) * 1e3,
+                                         "frac": units_per_rank * 597.9 / (148 * 4 * 32 * 1.965e9) * 1e3 / k_ms,
+                                         "source": "smsp__inst_executed.sum x 32 / warped px (ncu, profiles/r1_step_b64_v9.csv); "
                                                    "peak = 148 SM x 4 schedulers x 32 lanes x 1.965 GHz"},
-                         "note": "HBM traffic equals the compulsory bytes (traffic / algorithmic = 0.985) but the fused loss is "
-                                 "instruction-issue / FP32 bound (SURVEY F10): ~6 B per warped pixel against ~595 instructions"},
+                         "note": "HBM traffic equals the compulsory bytes (traffic / algorithmic = 0.988) but the fused loss is "
+                                 "instruction-issue / FP32 bound (SURVEY F10): ~6 B per warped pixel against ~598 instructions"},
         }
         if not args.no_cpu_baseline and world == 1:
             rate, cores, t, items = cpu_reference_rate(inp, args.cpu_sample_items, 3, 1)
