@@ -205,6 +205,22 @@ def test_upsample_transpose_band_vs_split(monkeypatch, W, H, N, scales):
         assert float((a - b).abs().max()) <= 1e-6 * scale, (float((a - b).abs().max()), scale)
 
 
+@pytest.mark.parametrize("seed", range(24))
+def test_random_geometries(seed):
+    """Seeded random shapes (odd sizes, any scale subset, C in {1, 3}, with and without the automask): strip /
+    segment / band bookkeeping against the oracle where no hand-picked case looks."""
+    from mdb200 import synth
+    rng = np.random.default_rng(1000 + seed)
+    W, H = int(rng.integers(9, 200)), int(rng.integers(9, 90))
+    N, C = int(rng.integers(1, 4)), int(rng.choice([1, 3]))
+    scales = [(1.0,), (0.5, 1.0), (0.25, 0.5, 1.0), (0.125, 0.25, 0.5, 1.0), (0.25, 1.0)][int(rng.integers(0, 5))]
+    auto = bool(rng.integers(0, 2))
+    inp = synth.make_loss_inputs(W, H, N, C=C, seed=40 + seed, scales=scales, automasking=auto)
+    ref = P.oracle_train_loss(inp)
+    res, _ = _run_gpu(inp, auto=ref["auto"])
+    _compare(inp, ref, res)
+
+
 @pytest.mark.parametrize("C", [1, 3])
 def test_single_source(C):
     """S = 1 (the scalar, un-packed instantiation of the kernel)."""
