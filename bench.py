@@ -48,7 +48,7 @@ def parse():
     ap.add_argument("--cpu-sample-items", type=int, default=0, help="items in the CPU sample (0 = one per host core)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--e2e-chunk", type=int, default=0, help="items per pipeline chunk of the host-buffer call (0 = N/8)")
+    ap.add_argument("--e2e-chunk", type=int, default=0, help="items per pipeline chunk of the host-buffer call (0 = HostLoss.default_chunk: N/8, at least ~16 MB)")
     return ap.parse_args()
 
 
@@ -285,7 +285,7 @@ def run_ours(args):
     # ---- e2e: host buffers, copies inside the timed region ---------------------------------
     e2e = None
     if not args.no_e2e:
-        e_chunk = args.e2e_chunk if args.e2e_chunk > 0 else max(1, N // 8)
+        e_chunk = args.e2e_chunk if args.e2e_chunk > 0 else None   # None: HostLoss.default_chunk
         hplan = mdb200.HostLoss(N=N, n_global=Ng, device=dev, chunk=e_chunk, **common)
         hposes = [mdb200.Pose(r, t) for r, t in zip(hr, ht)]
         e_steps = max(3, min(args.steps, 10))

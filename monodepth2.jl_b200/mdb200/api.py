@@ -700,7 +700,7 @@ class HostLoss:
     their sum.  Every chunk is one `mdb_train_loss_fwdbwd` call with `n_global = N`, the same
     contract the multi-GPU shards use, so chunk losses simply add."""
 
-    def __init__(self, *, W, H, C, L, N, disp_sizes, scales, target_id, source_ids, K, invK, chunk=8,
+    def __init__(self, *, W, H, C, L, N, disp_sizes, scales, target_id, source_ids, K, invK, chunk=None,
                  automasking=False, n_global=0, device=None, x_format="f32", ramp_up=None, **kw):
         """x_format "f32": x is the Float32 (N,L,C,H,W) stack.  "u8_strip": x is the dataset's own format,
         uint8 (N,H,3W,3) decoded triplet strips (src/dtk.jl:29-46) -- a quarter of the PCIe bytes; the
@@ -710,6 +710,8 @@ class HostLoss:
         if x_format == "u8_strip" and L != 3:
             raise ValueError("triplet strips hold L = 3 frames")
         self.x_format = x_format
+        if not chunk or chunk <= 0:
+            chunk = self.default_chunk(W, H, C, L, N, disp_sizes, automasking, x_format)
         if ramp_up is None:
             ramp_up = x_format == "u8_strip"
         self.dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
@@ -768,6 +770,14 @@ class HostLoss:
         self.h2d_bytes = x_bytes + 4 * (sum(N * w * h for (w, h) in self.disp_sizes) + 6 * N * self.S
                                         + (N * H * W if automasking else 0))
         self.d2h_bytes = 4 * (len(self.chunks) + sum(N * w * h for (w, h) in self.disp_sizes) + 6 * N * self.S)
+
+    @staticmethod
+    def default_chunk(W, H, C, L, N, disp_sizes, automasking=False, x_format="f32") -> int:
+        """Items per pipeline chunk: an eighth of the batch, but never chunks so small that the ~15 stream
+        operations a chunk costs on the host outweigh the copy they overlap (>= ~16 MB of input per chunk)."""
+        per_item = (4 * L * C * H * W if x_format == "f32" else 9 * H * W) \
+            + 4 * (sum(w * h for (w, h) in disp_sizes) + (H * W if automasking else 0))
+        return max(1, N // 8, min(N, -(-16 * 2 ** 20 // per_item)))
 
     def __call__(self, x, disparities, rvecs, tvecs, auto_loss=None, flips=None) -> HostLossResult:
         """All arguments are HOST tensors (pinned for full PCIe rate): float32, except x in the

@@ -109,3 +109,13 @@ def test_product_code_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".inl", ".jl")):
                 txt = open(os.path.join(dp, f)).read()
                 assert "torch_ref" not in txt and "from oracle" not in txt and "import oracle" not in txt, f
+
+
+def test_host_loss_default_chunk():
+    """HostLoss's pipeline chunk: an eighth of the batch at the bench size, whole small batches in few chunks."""
+    import mdb200
+    pyr = lambda W, H: [(W // 8, H // 8), (W // 4, H // 4), (W // 2, H // 2), (W, H)]
+    assert mdb200.HostLoss.default_chunk(1024, 320, 3, 3, 64, pyr(1024, 320)) == 8
+    assert mdb200.HostLoss.default_chunk(1024, 320, 3, 3, 64, pyr(1024, 320), x_format="u8_strip") == 8
+    assert mdb200.HostLoss.default_chunk(416, 128, 3, 3, 12, pyr(416, 128)) >= 6
+    assert mdb200.HostLoss.default_chunk(8, 8, 1, 3, 2, [(8, 8)]) == 2
