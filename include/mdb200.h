@@ -288,9 +288,10 @@ int32_t mdb_adam_update(mdb_handle* h, int32_t n_tensors, float* const* params, 
 /* `slow_depth` (src/simple_depth.jl:1-62) without its logging: `iters` iterations of
  *   grads = d/d(disp, poses) [ mean(prediction_loss(warp(disp, x, Ps))) + smooth_loss(disp, target) ];
  *   update!(ADAM(eta), (disp, poses), grads)
- * One iteration (the loss kernels of mdb_train_loss_fwdbwd + the ADAM kernel) is captured ONCE into a
- * CUDA graph at plan creation; mdb_slow_depth_run replays it `iters` times on the caller's stream with
- * no host round trip.  `io` must describe one full-resolution scale (Ls = 1, dw = W, dh = H); its
+ * One iteration is captured ONCE into a CUDA graph at plan creation -- the loss kernels of
+ * mdb_train_loss_fwdbwd, whose finalize kernel also applies the ADAM step of the poses, and beside it
+ * (forked after the fused kernel) the ADAM kernel of the disparity map; mdb_slow_depth_run replays it
+ * `iters` times on the caller's stream with no host round trip.  `io` must describe one full-resolution scale (Ls = 1, dw = W, dh = H); its
  * disparity / rvec / tvec buffers are the parameters and are UPDATED IN PLACE; its d_* buffers and
  * `loss` hold the last iteration's gradients and loss.  `params` should have normalize_disparity = 0
  * and smooth_weight_mode = 1 (src/simple_depth.jl:39).  `state` is caller-owned device memory of

@@ -9,6 +9,19 @@
 
 #include "../../include/mdb200.h"
 
+// slow_depth only (optim.cu).  When the handle carries one, finalize_item_kernel applies Flux's ADAM step to the
+// poses right where it forms their gradients and records the loss history, so the graph's ADAM kernel is left
+// with the disparity map and can run BESIDE the finalize kernel (forked after the strip kernel).
+struct mdb_pose_adam {
+  float* p_r[MDB_MAX_SOURCES]; float* p_t[MDB_MAX_SOURCES];   // parameters (3,N) each
+  float* m_r[MDB_MAX_SOURCES]; float* v_r[MDB_MAX_SOURCES];
+  float* m_t[MDB_MAX_SOURCES]; float* v_t[MDB_MAX_SOURCES];
+  int* step;        // this kernel's own step counter (the ADAM kernel keeps the one the API documents)
+  float* cbuf;      // [2][2] bias corrections 1 / (1 - beta^t), slot t & 1; 0 = not formed yet
+  float* hist; int hist_len;
+  double eta, b1, b2, eps;
+};
+
 struct mdb_handle {
   int device = 0;
   int num_sms = 0;
@@ -20,6 +33,8 @@ struct mdb_handle {
   static constexpr int kProfSegments = 4;  // 0 prep+stats, 1 fused kernel, 2 upsample_bwd, 3 finalize
   int prof_slots = 0, prof_next = 0;
   cudaEvent_t* prof_ev = nullptr;  // [slots][kProfSegments + 1]
+  const mdb_pose_adam* pose_adam = nullptr;   // set by mdb_slow_depth_create around its capture of the loss call
+  cudaEvent_t fork_event = nullptr;           // ditto: recorded right after the strip kernel (graph fork point)
   char err[512] = {0};
 };
 

@@ -1,8 +1,9 @@
 // optim.cu -- SURVEY 8(f) rank 1: the caller of the hot path in config 1.  `slow_depth`
 // (src/simple_depth.jl:1-62) runs 500 iterations of { Zygote.gradient of the single-scale loss;
 // Flux.Optimise.update!(ADAM(3e-4), theta, grads) } with a host round trip per op.  Here one iteration
-// is a CUDA graph (the loss kernels + ONE multi-tensor ADAM kernel that also advances the step counter
-// on the device), replayed back to back.
+// is a CUDA graph, replayed back to back: pose prep -> strip kernel -> { finalize kernel, which also applies the
+// ADAM step of the poses where it forms their gradients (mdb_pose_adam)  ||  the ADAM kernel of the disparity
+// map, whose gradient is complete after the strip kernel }.  Step counters live on the device.
 #include "mdb_common.cuh"
 
 namespace {
@@ -71,7 +72,8 @@ struct mdb_slow_depth_plan {
   mdb_handle* h = nullptr;
   cudaGraph_t graph = nullptr;
   cudaGraphExec_t exec = nullptr;
-  cudaStream_t capture_stream = nullptr;
+  cudaStream_t capture_stream = nullptr, side_stream = nullptr;
+  cudaEvent_t fork_ev = nullptr, join_ev = nullptr;
   int kernels_per_iter = 0;
 };
 
@@ -135,24 +137,49 @@ int32_t mdb_slow_depth_create(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
   };
   MDB_REQUIRE(h, io->disparity[0] && io->d_disparity[0], MDB_E_INVALID_ARG, "null disparity pointer");
   add(io->disparity[0], io->d_disparity[0], nd);
+  // the poses keep their (m, v) slots in the state, in this order, but their ADAM step runs inside the loss
+  // call's finalize kernel: the graph's ADAM kernel is left with the disparity map alone
+  mdb_pose_adam pad{};
   for (int s = 0; s < S; ++s) {
     MDB_REQUIRE(h, io->rvec[s] && io->tvec[s] && io->d_rvec[s] && io->d_tvec[s], MDB_E_INVALID_ARG, "null pose pointer");
-    add(io->rvec[s], io->d_rvec[s], (size_t)3 * N);
-    add(io->tvec[s], io->d_tvec[s], (size_t)3 * N);
+    const size_t n3 = (size_t)3 * N;
+    pad.p_r[s] = const_cast<float*>(io->rvec[s]); pad.m_r[s] = mv + off; pad.v_r[s] = mv + off + n3; off += 2 * n3;
+    pad.p_t[s] = const_cast<float*>(io->tvec[s]); pad.m_t[s] = mv + off; pad.v_t[s] = mv + off + n3; off += 2 * n3;
   }
   a.eta = adam->eta; a.b1 = adam->beta1; a.b2 = adam->beta2; a.eps = adam->eps;
+  // counters (int32): [0] step of the ADAM kernel (the documented one), [1] its ticket, [2] step of the finalize
+  // kernel's pose ADAM (kept equal to [0]); floats [4..7]: bias corrections handed from one iteration to the next
   int* counters = (int*)((char*)state + mdb_align_up(off * sizeof(float), 256));
+  pad.step = counters + 2;
+  pad.cbuf = (float*)(counters + 4);
+  pad.hist = loss_history; pad.hist_len = history_len;
+  pad.eta = adam->eta; pad.b1 = adam->beta1; pad.b2 = adam->beta2; pad.eps = adam->eps;
 
   mdb_slow_depth_plan* pl = new mdb_slow_depth_plan();
   pl->h = h;
   auto fail = [&](int32_t rc) { mdb_slow_depth_destroy(pl); return rc; };
   cudaError_t e = cudaStreamCreateWithFlags(&pl->capture_stream, cudaStreamNonBlocking);
-  if (e != cudaSuccess) return fail(mdb_fail(h, (int32_t)e, "cudaStreamCreateWithFlags: %s", cudaGetErrorString(e)));
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&pl->side_stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&pl->fork_ev, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&pl->join_ev, cudaEventDisableTiming);
+  if (e != cudaSuccess) return fail(mdb_fail(h, (int32_t)e, "stream / event creation: %s", cudaGetErrorString(e)));
   e = cudaStreamBeginCapture(pl->capture_stream, cudaStreamCaptureModeThreadLocal);
   if (e != cudaSuccess) return fail(mdb_fail(h, (int32_t)e, "cudaStreamBeginCapture: %s", cudaGetErrorString(e)));
   const int64_t before = h->launches;
+  // the loss call records fork_ev right after the strip kernel: the disparity's ADAM kernel branches off there
+  // and joins after the finalize kernel (which steps the poses and writes the loss history itself)
+  h->pose_adam = &pad;
+  h->fork_event = pl->fork_ev;
   int32_t rc = mdb_train_loss_fwdbwd(h, io, params, workspace, workspace_bytes, pl->capture_stream);
-  if (rc == MDB_OK) rc = launch_adam(h, a, counters, counters + 1, io->loss, loss_history, history_len, pl->capture_stream);
+  h->pose_adam = nullptr;
+  h->fork_event = nullptr;
+  if (rc == MDB_OK) {
+    cudaError_t e2 = cudaStreamWaitEvent(pl->side_stream, pl->fork_ev, 0);
+    if (e2 == cudaSuccess) rc = launch_adam(h, a, counters, counters + 1, nullptr, nullptr, 0, pl->side_stream);
+    if (e2 == cudaSuccess) e2 = cudaEventRecord(pl->join_ev, pl->side_stream);
+    if (e2 == cudaSuccess) e2 = cudaStreamWaitEvent(pl->capture_stream, pl->join_ev, 0);
+    if (e2 != cudaSuccess && rc == MDB_OK) rc = mdb_fail(h, (int32_t)e2, "graph fork / join: %s", cudaGetErrorString(e2));
+  }
   e = cudaStreamEndCapture(pl->capture_stream, &pl->graph);
   pl->kernels_per_iter = (int)(h->launches - before);
   h->launches = before;                       // nothing ran yet: launches are counted per replay
@@ -180,6 +207,9 @@ int32_t mdb_slow_depth_destroy(mdb_slow_depth_plan* pl) {
   if (pl->exec) cudaGraphExecDestroy(pl->exec);
   if (pl->graph) cudaGraphDestroy(pl->graph);
   if (pl->capture_stream) cudaStreamDestroy(pl->capture_stream);
+  if (pl->side_stream) cudaStreamDestroy(pl->side_stream);
+  if (pl->fork_ev) cudaEventDestroy(pl->fork_ev);
+  if (pl->join_ev) cudaEventDestroy(pl->join_ev);
   delete pl;
   return MDB_OK;
 }

@@ -20,7 +20,11 @@ struct FinArgs {
   // N > 1: the CTA that finishes last (done_counter, zeroed by prep_kernel) sums the items in fixed order
   unsigned* done_counter;
   float* loss_final;
+  int adam_on;          // slow_depth: ADAM step of the poses + loss history here (mdb_pose_adam)
+  mdb_pose_adam adam;
 };
+
+MDB_DEV float adam_bias_corr(double beta, int t) { return (float)(1.0 / (1.0 - pow(beta, (double)t))); }
 
 template <int S>
 __global__ void __launch_bounds__(FIN_THREADS)
@@ -89,7 +93,16 @@ finalize_item_kernel(const float* __restrict__ partials, int records, PoseArgs p
       stats[(size_t)sc * fa.N + n] = st;
     }
     item_loss[n] = tot[0];
-    if (fa.loss_out) *fa.loss_out = (float)(tot[0] * fa.up + sloss);   // N == 1: same sum as below
+    if (fa.loss_out) {   // N == 1: same sum as below
+      const float l = (float)(tot[0] * fa.up + sloss);
+      *fa.loss_out = l;
+      if (fa.adam_on && fa.adam.hist && *fa.adam.step < fa.adam.hist_len) fa.adam.hist[*fa.adam.step] = l;
+    }
+  }
+  // slow_depth: the bias corrections of the NEXT step, on a warp of their own (two pow() beside the pose chain)
+  if (fa.adam_on && n == 0 && warp == 2 && lane < 2) {
+    const int t1 = *fa.adam.step + 2;
+    fa.adam.cbuf[(t1 & 1) * 2 + lane] = adam_bias_corr(lane ? fa.adam.b2 : fa.adam.b1, t1);
   }
   if (threadIdx.x >= 32 && threadIdx.x < 32 + S) {
     const int s = threadIdx.x - 32;
@@ -108,6 +121,25 @@ finalize_item_kernel(const float* __restrict__ partials, int records, PoseArgs p
     for (int k = 0; k < 3; ++k) {
       if (fa.d_rvec[s]) fa.d_rvec[s][3 * n + k] = (float)dr[k];
       if (fa.d_tvec[s]) fa.d_tvec[s][3 * n + k] = (float)dt[k];
+    }
+    if (fa.adam_on) {   // Flux ADAM (apply! + update!), the expressions of adam_kernel (optim.cu)
+      const int t = *fa.adam.step + 1;
+      float c1 = fa.adam.cbuf[(t & 1) * 2], c2 = fa.adam.cbuf[(t & 1) * 2 + 1];
+      if (c1 == 0.0f || c2 == 0.0f) {   // first step after create / load_state: nothing handed on yet
+        c1 = adam_bias_corr(fa.adam.b1, t); c2 = adam_bias_corr(fa.adam.b2, t);
+      }
+      const float b1 = (float)fa.adam.b1, b2 = (float)fa.adam.b2, eta = (float)fa.adam.eta, eps = (float)fa.adam.eps;
+      auto step1 = [&](float* p, float* mm, float* vv, float g) {
+        const float m = b1 * *mm + (1.0f - b1) * g;
+        const float v = b2 * *vv + (1.0f - b2) * g * g;
+        *mm = m; *vv = v;
+        *p -= m * c1 / (sqrtf(v * c2) + eps) * eta;
+      };
+      for (int k = 0; k < 3; ++k) {
+        const int j = 3 * n + k;
+        step1(fa.adam.p_r[s] + j, fa.adam.m_r[s] + j, fa.adam.v_r[s] + j, (float)dr[k]);
+        step1(fa.adam.p_t[s] + j, fa.adam.m_t[s] + j, fa.adam.v_t[s] + j, (float)dt[k]);
+      }
     }
   }
   // 6. scalar loss = up * sum(item photometric sums) + sum(smoothness terms), by the last CTA to get here
@@ -133,8 +165,15 @@ finalize_item_kernel(const float* __restrict__ partials, int records, PoseArgs p
         double t = 0.0;
         for (int w = 0; w < FIN_THREADS / 32; ++w) t += red[w][0];
         *fa.loss_final = (float)t;
+        if (fa.adam_on) {   // every CTA has read the step counter before it took its ticket
+          if (fa.adam.hist && *fa.adam.step < fa.adam.hist_len) fa.adam.hist[*fa.adam.step] = (float)t;
+          *fa.adam.step += 1;
+        }
       }
     }
+  } else if (fa.adam_on) {   // N == 1: the one CTA advances its step counter once all its warps have read it
+    __syncthreads();
+    if (threadIdx.x == 0) *fa.adam.step += 1;
   }
 }
 
@@ -541,6 +580,8 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
   fin.loss_out = (N == 1) ? io->loss : nullptr;
   fin.done_counter = (N == 1) ? nullptr : (unsigned*)(ws + L.o_counter);
   fin.loss_final = io->loss;
+  fin.adam_on = h->pose_adam ? 1 : 0;
+  if (h->pose_adam) fin.adam = *h->pose_adam;
   ua.Ls = Ls; ua.W = W; ua.H = H; ua.N = N;
   ScaleStat* stats = (ScaleStat*)(ws + L.o_stats);
   double* mean_part = (double*)(ws + L.o_meanpart);
@@ -565,6 +606,7 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
   else if (io->C == 1 && S == 2) rc = launch_fused<1, 2>(h, fa, L, st);
   else rc = launch_fused<1, 1>(h, fa, L, st);
   if (rc != MDB_OK) return rc;
+  if (h->fork_event) MDB_CUDA(h, cudaEventRecord(h->fork_event, st));   // slow_depth's graph forks here
   mdb_prof_mark(h, pslot, 2, st);
 
   double* item_loss = (double*)(ws + L.o_itemloss);

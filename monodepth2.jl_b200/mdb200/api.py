@@ -542,7 +542,7 @@ class SlowDepth:
         return [self.disp] + [t for pz in self.poses for t in (pz.rvec, pz.tvec)]
 
     def _state_views(self):
-        """(m, v) float32 views into the state buffer per parameter, and the int32 [step, ticket] pair
+        """(m, v) float32 views into the state buffer per parameter, and the int32 counters [step, ticket, step', -, c...]
         (layout of mdb_slow_depth_create: per tensor m then v, counters at the next 256-byte boundary)."""
         f = self.state.view(torch.float32)
         off, ms, vs = 0, [], []
@@ -551,15 +551,17 @@ class SlowDepth:
             ms.append(f[off:off + n].view(t.shape)); vs.append(f[off + n:off + 2 * n].view(t.shape))
             off += 2 * n
         c = (off * 4 + 255) // 256 * 256
-        return ms, vs, self.state[c:c + 8].view(torch.int32)
+        return ms, vs, self.state[c:c + 32].view(torch.int32)
 
     def load_state(self, params: Sequence[torch.Tensor], m: Sequence[torch.Tensor], v: Sequence[torch.Tensor], step: int):
         """Resume from a checkpoint of (theta, ADAM moments, step count)."""
         ms, vs, counters = self._state_views()
         for dst, src in zip(self.parameters() + ms + vs, list(params) + list(m) + list(v)):
             dst.copy_(src.to(dst.device, torch.float32).reshape(dst.shape))
-        counters[0] = int(step)
+        counters[0] = int(step)     # the ADAM kernel's step (disparity map)
         counters[1] = 0
+        counters[2] = int(step)     # the finalize kernel's step (poses, loss history)
+        counters[4:8] = 0           # bias corrections handed on between iterations: re-formed on the next step
         self.iters_done = int(step)
 
     @property
