@@ -10,6 +10,7 @@
 #ifdef __CUDACC__
 struct So3Aux {
   double theta, theta_inv, f1, f2;
+  double s, c, omc;   // sin(theta), cos(theta), 1 - cos(theta)
   double S[9], S2[9];
 };
 
@@ -39,10 +40,16 @@ MDB_HD void so3_exp_d(const double r[3], double R[9], So3Aux& a) {
   mat3_mul(a.S, a.S, a.S2);
   a.theta = sqrt(r[0] * r[0] + r[1] * r[1] + r[2] * r[2]);
   a.theta_inv = 1.0 / fmax(a.theta, 1e-4);
-  a.f1 = a.theta_inv * sin(a.theta);
-  // 1 - cos(t) = 2 sin^2(t/2): same value, no cancellation
-  const double sh = sin(0.5 * a.theta);
-  a.f2 = a.theta_inv * a.theta_inv * (2.0 * sh * sh);
+  // ONE double-precision sincos, at the half angle, serves the forward and the pullback (the pose chains are
+  // single-thread latency: five separate sin / cos calls were most of it): sin t = 2 sh ch,
+  // 1 - cos t = 2 sh^2 (no cancellation), cos t = 1 - 2 sh^2
+  double sh, ch;
+  sincos(0.5 * a.theta, &sh, &ch);
+  a.s = 2.0 * sh * ch;
+  a.omc = 2.0 * sh * sh;
+  a.c = 1.0 - a.omc;
+  a.f1 = a.theta_inv * a.s;
+  a.f2 = a.theta_inv * a.theta_inv * a.omc;
   for (int k = 0; k < 9; ++k) R[k] = a.f1 * a.S[k] + a.f2 * a.S2[k];
   R[0] += 1.0; R[4] += 1.0; R[8] += 1.0;
 }
@@ -64,9 +71,7 @@ MDB_HD void so3_exp_bwd_d(const double r[3], const So3Aux& a, const double dR[9]
   dr[2] = dS[3 * 1 + 0] - dS[3 * 0 + 1];
   // theta path
   const double dtinv_dtheta = (a.theta > 1e-4) ? -a.theta_inv * a.theta_inv : 0.0;
-  const double s = sin(a.theta), c = cos(a.theta);
-  const double sh = sin(0.5 * a.theta);
-  const double omc = 2.0 * sh * sh;
+  const double s = a.s, c = a.c, omc = a.omc;
   const double df1_dtheta = a.theta_inv * c + s * dtinv_dtheta;
   const double df2_dtheta = a.theta_inv * a.theta_inv * s + 2.0 * a.theta_inv * omc * dtinv_dtheta;
   const double dtheta = df1 * df1_dtheta + df2 * df2_dtheta;
