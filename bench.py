@@ -48,6 +48,9 @@ def parse():
     ap.add_argument("--cpu-sample-items", type=int, default=0, help="items in the CPU sample (0 = one per host core)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--disp-noise", type=float, default=None,
+                    help="diagnostic: amplitude of the per-pixel disparity noise of the synthetic inputs (default 0.05 "
+                         "as SURVEY 8d specifies; 0 = smooth disparities, what a network predicts)")
     ap.add_argument("--e2e-chunk", type=int, default=0, help="items per pipeline chunk of the host-buffer call (0 = HostLoss.default_chunk: N/8, at least ~16 MB)")
     return ap.parse_args()
 
@@ -145,6 +148,8 @@ def make_inputs(args):
     kw = dict(synth.CONFIGS[args.config])
     if args.batch:
         kw["N"] = args.batch
+    if args.disp_noise is not None:   # diagnostic only: the bench line's workload is SURVEY 8d's (noise 0.05)
+        kw["disp_noise"] = args.disp_noise
     return synth.make_loss_inputs(**kw), kw
 
 
@@ -346,7 +351,9 @@ def run_ours(args):
                                    f"{Ls} scales, SSIM+L1 min-reprojection{' + automask' if inp.automasking else ''} "
                                    f"+ smoothness, fwd+bwd", "global_batch": Ng, "l2": "inputs_larger_than_l2",
                        "parallelism": f"batch-sharded x{world}, 1 all-reduce of [loss, pose grads] per step",
-                       "units_per_step": units_per_rank * world, "loss": loss_val},
+                       "units_per_step": units_per_rank * world, "loss": loss_val,
+                       **({"disp_noise": args.disp_noise, "diagnostic": "not SURVEY 8d's inputs"}
+                          if args.disp_noise is not None else {})},
             "clocks": clocks,
             "e2e": e2e,
             "gpu_launches": int(launches),

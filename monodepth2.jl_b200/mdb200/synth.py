@@ -85,14 +85,14 @@ def make_images(W: int, H: int, C: int, N: int, rng: np.random.Generator) -> np.
     return np.clip(img + shared + indep, 0.0, 1.0).astype(np.float32)
 
 
-def make_disparities(W: int, H: int, N: int, scales, rng: np.random.Generator):
+def make_disparities(W: int, H: int, N: int, scales, rng: np.random.Generator, noise: float = 0.05):
     out = []
     for s in scales:
         ws, hs = max(int(round(W * s)), 2), max(int(round(H * s)), 2)
         w = np.arange(1, ws + 1, dtype=np.float32)[None, None, None, :] / np.float32(ws)
         h = np.arange(1, hs + 1, dtype=np.float32)[None, None, :, None] / np.float32(hs)
         d = (0.3 + 0.2 * np.sin(2 * np.pi * w) * np.cos(2 * np.pi * h)
-             + 0.05 * rng.uniform(-1, 1, size=(N, 1, hs, ws)))
+             + noise * rng.uniform(-1, 1, size=(N, 1, hs, ws)))
         out.append(np.clip(d, 0.02, 0.98).astype(np.float32))
     return out
 
@@ -109,10 +109,12 @@ def make_poses(N: int, S: int, rng: np.random.Generator):
 
 
 def make_loss_inputs(W: int, H: int, N: int, *, C: int = 3, seed: int = 2,
-                     scales=(0.125, 0.25, 0.5, 1.0), automasking: bool = False) -> LossInputs:
+                     scales=(0.125, 0.25, 0.5, 1.0), automasking: bool = False, disp_noise: float = 0.05) -> LossInputs:
+    """`disp_noise`: amplitude of the per-pixel uniform noise on the disparities (SURVEY 8d's inputs use 0.05, i.e.
+    +-35 px of parallax jitter at config 5's focal length -- a worst case for the bilinear gathers)."""
     rng = np.random.Generator(np.random.PCG64(seed))
     x = make_images(W, H, C, N, rng)
-    disps = make_disparities(W, H, N, scales, rng)
+    disps = make_disparities(W, H, N, scales, rng, noise=disp_noise)
     rvecs, tvecs = make_poses(N, 2, rng)
     K, invK = intrinsics(W, H)
     return LossInputs(W=W, H=H, C=C, N=N, x=x, disparities=disps, scales=list(scales),
