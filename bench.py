@@ -148,7 +148,7 @@ def make_inputs(args):
     kw = dict(synth.CONFIGS[args.config])
     if args.batch:
         kw["N"] = args.batch
-    if args.disp_noise is not None:   # diagnostic only: the bench line's workload is SURVEY 8d's (noise 0.05)
+    if getattr(args, "disp_noise", None) is not None:   # diagnostic only: the bench line's workload is SURVEY 8d's (noise 0.05)
         kw["disp_noise"] = args.disp_noise
     return synth.make_loss_inputs(**kw), kw
 
@@ -190,7 +190,8 @@ def run_reference(args):
         return
     ncpu = os.cpu_count() or 1
     want = args.cpu_sample_items if args.cpu_sample_items > 0 else ncpu
-    inp, _ = make_inputs(argparse.Namespace(config=args.config, batch=min(args.batch or want, want)))
+    inp, _ = make_inputs(argparse.Namespace(config=args.config, batch=min(args.batch or want, want),
+                                            disp_noise=getattr(args, "disp_noise", None)))
     steps, warm = max(1, min(args.steps, 20)), max(1, min(args.warmup, 5))
     rate, cores, t, items = cpu_reference_rate(inp, args.cpu_sample_items, steps, warm)
     sample = (f"{items} of the per-GPU batch's items at {inp.W}x{inp.H}, {len(inp.disparities)} scales, "

@@ -119,3 +119,18 @@ def test_host_loss_default_chunk():
     assert mdb200.HostLoss.default_chunk(1024, 320, 3, 3, 64, pyr(1024, 320), x_format="u8_strip") == 8
     assert mdb200.HostLoss.default_chunk(416, 128, 3, 3, 12, pyr(416, 128)) >= 6
     assert mdb200.HostLoss.default_chunk(8, 8, 1, 3, 2, [(8, 8)]) == 2
+
+
+def test_bench_reference_arm_runs_on_the_host():
+    """`bench.py --impl reference` (the CPU arm the driver runs beside ours) needs no GPU: one JSON line with the
+    contract's keys."""
+    import json
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--config", "config2",
+                          "--steps", "1", "--warmup", "1", "--cpu-sample-items", "2"],
+                         capture_output=True, text=True, timeout=600, cwd=root)
+    assert out.returncode == 0, out.stderr[-2000:]
+    line = json.loads(out.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["value"] > 0 and line["unit"] == "warped_px/s"
+    assert line["cpu_baseline"]["kind"] == "port" and line["e2e"]["h2d_bytes_per_step"] == 0
