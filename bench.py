@@ -374,7 +374,8 @@ def run_ours(args):
                                          "source": "smsp__inst_executed.sum x 32 / warped px (ncu, profiles/r1_step_b64_v9.csv); "
                                                    "peak = 148 SM x 4 schedulers x 32 lanes x 1.965 GHz"},
                          "note": "HBM traffic equals the compulsory bytes (traffic / algorithmic = 0.988) but the fused loss is "
-                                 "instruction-issue / FP32 bound (SURVEY F10): ~6 B per warped pixel against ~598 instructions"},
+                                 "bound on the SM, not by HBM (SURVEY F10): ~6 B per warped pixel against ~598 instructions; "
+                                 "no pipe saturated (issue 63 %, LSU 65 %), per-warp latency at 13 warps per SM"},
         }
         if not args.no_cpu_baseline and world == 1:
             rate, cores, t, items = cpu_reference_rate(inp, args.cpu_sample_items, 3, 1)
