@@ -297,7 +297,11 @@ int32_t mdb_adam_update(mdb_handle* h, int32_t n_tensors, float* const* params, 
  * and smooth_weight_mode = 1 (src/simple_depth.jl:39).  `state` is caller-owned device memory of
  * mdb_slow_depth_state_bytes(io) bytes, zeroed by the caller before the first run (ADAM moments +
  * counters); `workspace` as for mdb_train_loss_fwdbwd.  All pointers must stay valid and unchanged
- * for the life of the plan.                                                                        */
+ * for the life of the plan.  Layout of `state`: per parameter tensor (disparity, then rvec, tvec per
+ * source) its m then its v, then at the next 256-byte boundary the int32 counter block
+ * [0] step of the disparity's ADAM kernel, [1] its ticket, [2] step of the pose ADAM inside the finalize
+ * kernel, floats [4..7] bias corrections handed from one iteration to the next.  To resume from a
+ * checkpoint set [0] = [2] = step and zero [1] and [4..7].                                           */
 typedef struct mdb_slow_depth_plan mdb_slow_depth_plan;
 size_t mdb_slow_depth_state_bytes(const mdb_loss_io* io);
 int32_t mdb_slow_depth_create(mdb_handle* h, const mdb_loss_io* io, const mdb_loss_params* params,
