@@ -5,10 +5,16 @@ Metric (BASELINE.json): warped px/s (loss fwd+bwd).  One *warped pixel* = one (i
 source, full-res target pixel); one step = one `train_loss` value+gradient evaluation
 (src/training.jl:21-78) over one batch: N * Ls * S * W * H warped pixels.
 
-Workload at every GPU count: BASELINE config 5 geometry -- 1024x320, batch 64 PER GPU
-("scaling": "weak"), 3-frame stacks, 2 sources, 4 scales -- synthetic images / disparities /
-poses from mdb200.synth (no dataset or checkpoint is reachable).  The step's inputs are larger
-than L2 (866 MB vs 126 MB), so no explicit flush is needed between iterations.
+Workload at every GPU count: BASELINE config 5 as stated -- 1024x320, GLOBAL batch 64, 3-frame
+stacks, 2 sources, 4 scales -- sharded over the ranks ("scaling": "strong": rank r owns the
+contiguous items shard_range(64, world, r) of ONE 64-item input, 32 / 16 / 8 items per GPU at
+2 / 4 / 8 GPUs), one all-reduce of [loss, pose gradients] per step.  Before timing, rank 0
+evaluates the whole batch on its own GPU and the all-reduced result is checked against it
+("shard_parity").  `weak_aux` repeats the run with 64 items PER GPU (round 1's line).
+Synthetic images / disparities / poses from mdb200.synth (no dataset or checkpoint is
+reachable).  At one GPU the step's inputs are larger than L2 (866 MB vs 126 MB); from 8 items
+per GPU down they are not, and a buffer larger than L2 is written between the timed steps
+OUTSIDE the event pairs (per-step events, `config.l2`).
 
   value     device-resident inputs, CUDA-event timed on the launching stream, max over ranks
   e2e       the same call made through mdb200.train_loss_host with PINNED HOST buffers: every
@@ -51,6 +57,12 @@ def parse():
     ap.add_argument("--disp-noise", type=float, default=None,
                     help="diagnostic: amplitude of the per-pixel disparity noise of the synthetic inputs (default 0.05 "
                          "as SURVEY 8d specifies; 0 = smooth disparities, what a network predicts)")
+    ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
+                    help="strong (default): the config's global batch sharded over the ranks; weak: the config's batch per GPU")
+    ap.add_argument("--transport", default="peer", choices=["peer", "nccl", "torch"],
+                    help="the all-reduce of [loss, pose grads]: the library's one-shot peer-write kernel, ncclAllReduce "
+                         "through the C ABI, or torch.distributed")
+    ap.add_argument("--no-weak-aux", action="store_true")
     ap.add_argument("--e2e-chunk", type=int, default=0, help="items per pipeline chunk of the host-buffer call (0 = HostLoss.default_chunk: N/8, at least ~16 MB)")
     return ap.parse_args()
 
@@ -143,8 +155,21 @@ class ClockSampler:
                 "source": "NVML, polled during the timed region"}
 
 
+def load_synth():
+    """mdb200/synth.py (numpy only) loaded by path: the reference arm must not import the mdb200 package, whose
+    __init__ dlopens the product library."""
+    import importlib.util
+    if "mdb200_synth" in sys.modules:
+        return sys.modules["mdb200_synth"]
+    spec = importlib.util.spec_from_file_location("mdb200_synth", os.path.join(ROOT, "monodepth2.jl_b200", "mdb200", "synth.py"))
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules["mdb200_synth"] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
 def make_inputs(args):
-    from mdb200 import synth
+    synth = load_synth()
     kw = dict(synth.CONFIGS[args.config])
     if args.batch:
         kw["N"] = args.batch
@@ -215,6 +240,7 @@ def run_ours(args):
     import torch
     import torch.distributed as dist
     import mdb200
+    from mdb200 import dist as mdist
 
     rank, local_rank, world = dist_env()
     assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU fallback for the product path)"
@@ -224,38 +250,41 @@ def run_ours(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
     # host threads (and, by first touch, the pinned staging buffers below) onto the GPU's own NUMA node
-    from mdb200 import dist as mdist
     numa = mdist.bind_host_to_device(dev)
 
-    inp, kw = make_inputs(args)
-    N, W, H, C = inp.N, inp.W, inp.H, inp.C
+    inp, kw = make_inputs(args)                       # the config's WHOLE batch, identical on every rank (seeded)
+    NB, W, H, C = inp.N, inp.W, inp.H, inp.C
     S, Ls = len(inp.source_ids), len(inp.disparities)
-    Ng = N * world                                    # weak scaling: the global batch grows with the GPU count
-    units_per_rank = N * Ls * S * W * H
+    strong = args.scaling == "strong"
+    Ng = NB if strong else NB * world                 # batch the means divide by
+    lo, hi = mdist.shard_range(NB, world, rank) if strong else (0, NB)
+    first = lo if strong else rank * NB               # this rank's first slot in the packed vector
+    N = hi - lo
+    units_total = Ng * Ls * S * W * H
     sizes = [(d.shape[-1], d.shape[-2]) for d in inp.disparities]
 
-    # pinned host copies (e2e) and device-resident copies (value)
-    hx = torch.from_numpy(inp.x).pin_memory()
-    hd = [torch.from_numpy(d).pin_memory() for d in inp.disparities]
-    hr = [torch.from_numpy(r).pin_memory() for r in inp.rvecs]
-    ht = [torch.from_numpy(t).pin_memory() for t in inp.tvecs]
+    # pinned host copies of the rank's shard (e2e) and device-resident copies (value)
+    hx = torch.from_numpy(inp.x[lo:hi]).pin_memory()
+    hd = [torch.from_numpy(d[lo:hi]).pin_memory() for d in inp.disparities]
+    hr = [torch.from_numpy(r[lo:hi]).pin_memory() for r in inp.rvecs]
+    ht = [torch.from_numpy(t[lo:hi]).pin_memory() for t in inp.tvecs]
     x = hx.to(dev); disps = [d.to(dev) for d in hd]
     poses = [mdb200.Pose(r.to(dev), t.to(dev)) for r, t in zip(hr, ht)]
-    auto = mdb200.automasking_loss(mdb200.SSIM(), x, inp.target_id, source_ids=inp.source_ids) if inp.automasking else None
+    auto = mdb200.automasking_loss(mdb200.SSIM(), x, x[:, inp.target_id - 1], source_ids=inp.source_ids) if inp.automasking else None
     hauto = auto.cpu().pin_memory() if auto is not None else None
 
     common = dict(W=W, H=H, C=C, L=3, disp_sizes=sizes, scales=inp.scales, target_id=inp.target_id,
                   source_ids=inp.source_ids, K=inp.K, invK=inp.invK, automasking=inp.automasking)
-    plan = mdb200.FusedLoss(N=N, n_global=Ng, device=dev, **common)
-    # [loss, d_rvec (S,N,3), d_tvec (S,N,3)] of every rank, all-reduced once per step
-    from mdb200 import dist as mdist
-    packed = torch.zeros(mdist.packed_size(Ng, S), device=dev)
+    # [loss, d_rvec (S,Ng,3), d_tvec (S,Ng,3)]: the finalize kernel writes this rank's slots of the send buffer in
+    # place (mdb_packed_bind); one out-of-place all-reduce per step
+    pg = mdist.PackedGrads(Ng, S, first, N, dev)
+    plan = mdb200.FusedLoss(N=N, n_global=Ng, device=dev, out=pg.out(), **common)
+    transport = mdist.init_comm(dev, pg.send.numel(), args.transport) if world > 1 else "none"
 
     def step():
         res = plan(x, disps, poses, auto)
         if world > 1:
-            mdist.pack(res.loss, [p.rvec for p in res.d_poses], [p.tvec for p in res.d_poses], Ng, rank * N, out=packed)
-            mdist.allreduce_loss_posegrads(packed)
+            mdist.allreduce(pg)
         return res
 
     def sync_all():
@@ -263,36 +292,109 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(args.warmup, 3)):
+    # ---- shard parity: the all-reduced [loss, pose grads] of the sharded batch == the whole batch on one GPU ----
+    shard_parity = None
+    if world > 1 and strong:
         step()
-    sync_all()
-    sampler = ClockSampler(dev)
-    mdb200.profile_begin(args.steps)
-    l0 = mdb200.launch_count()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    sampler.start()
-    sync_all()
-    ev0.record()
-    for _ in range(args.steps):
-        res = step()
-    ev1.record()
-    sampler.sample_now()   # the timed steps are queued or running: at least one sample under load
-    sync_all()
-    clocks = sampler.stop()
-    launches = mdb200.launch_count() - l0
-    ms = torch.tensor([ev0.elapsed_time(ev1)], device=dev)
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    ms_total = float(ms)
-    seg = np.array([mdb200.profile_read(i) for i in range(args.steps)])  # [steps][4] ms
-    mdb200.profile_begin(0)
-    loss_val = float(packed[0]) if world > 1 else float(res.loss)
+        torch.cuda.synchronize()
+        got = pg.recv.clone()
+        worst = torch.zeros(3, device=dev, dtype=torch.float64)
+        fx = torch.from_numpy(inp.x).to(dev)
+        fd = [torch.from_numpy(d).to(dev) for d in inp.disparities]
+        fposes = [mdb200.Pose(torch.from_numpy(r).to(dev), torch.from_numpy(t).to(dev)) for r, t in zip(inp.rvecs, inp.tvecs)]
+        fauto = mdb200.automasking_loss(mdb200.SSIM(), fx, fx[:, inp.target_id - 1], source_ids=inp.source_ids) if inp.automasking else None
+        fpg = mdist.PackedGrads(Ng, S, 0, NB, dev)
+        fplan = mdb200.FusedLoss(N=NB, n_global=Ng, device=dev, out=fpg.out(), **common)
+        fres = fplan(fx, fd, fposes, fauto)
+        torch.cuda.synchronize()
+        ref = fpg.send.double()
+        g = got.double()
+        nr = 1 + 3 * S * Ng
+        worst[0] = (g[0] - ref[0]).abs() / ref[0].abs()
+        worst[1] = (g[1:nr] - ref[1:nr]).abs().max() / ref[1:nr].abs().max()
+        worst[2] = (g[nr:] - ref[nr:]).abs().max() / ref[nr:].abs().max()
+        # the shard's disparity gradients (which stay sharded) against the same rows of the whole-batch run
+        dd = max(float((a.double() - b[lo:hi].double()).abs().max() / b.double().abs().max())
+                 for a, b in zip(plan.d_disp, fres.d_disparities))
+        worst = torch.cat([worst, torch.tensor([dd], device=dev, dtype=torch.float64)])
+        dist.all_reduce(worst, op=dist.ReduceOp.MAX)
+        shard_parity = {"ok": bool(float(worst.max()) <= 1e-6), "tol": 1e-6,
+                        "loss_rel": float(worst[0]), "d_rvec_rel_maxabs": float(worst[1]), "d_tvec_rel_maxabs": float(worst[2]),
+                        "d_disparity_rel_maxabs": float(worst[3]),
+                        "how": "every rank: all-reduced [loss, pose grads] and its own shard's disparity gradients vs the whole "
+                               f"{NB}-item batch evaluated on that rank's GPU alone; max over ranks"}
+        assert shard_parity["ok"], f"sharded result differs from the single-GPU result: {shard_parity}"
+        del fx, fd, fposes, fauto, fplan, fres, fpg
+        torch.cuda.empty_cache()
+
+    # ---- value: device-resident inputs, one CUDA-event pair per step on the launching stream --------------------
+    in_bytes = x.numel() * 4 + sum(d.numel() for d in disps) * 4
+    l2_bytes = torch.cuda.get_device_properties(dev).L2_cache_size
+    flush = torch.empty(2 * l2_bytes, dtype=torch.uint8, device=dev) if in_bytes < 2 * l2_bytes else None
+
+    def timed(step_fn, steps, warmup, profile=False):
+        for _ in range(warmup):
+            step_fn()
+        sync_all()
+        sampler = ClockSampler(dev)
+        if profile:
+            mdb200.profile_begin(steps)
+        l0 = mdb200.launch_count()
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        sampler.start()
+        sync_all()
+        t0 = time.perf_counter()
+        for e0, e1 in evs:
+            if flush is not None:
+                flush.zero_()          # outside the event pair
+            e0.record()
+            r = step_fn()
+            e1.record()
+        sampler.sample_now()   # the timed steps are queued or running: at least one sample under load
+        sync_all()
+        wall = time.perf_counter() - t0
+        clocks = sampler.stop()
+        launches = mdb200.launch_count() - l0
+        ms = torch.tensor([sum(e0.elapsed_time(e1) for e0, e1 in evs)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        seg = None
+        if profile:
+            seg = np.array([mdb200.profile_read(i) for i in range(steps)])  # [steps][4] ms
+            mdb200.profile_begin(0)
+        return float(ms), clocks, launches, seg, r, wall
+
+    warm = max(args.warmup, 3)
+    ms_total, clocks, launches, seg, res, wall = timed(step, args.steps, warm, profile=True)
+    loss_val = float(pg.recv[0]) if world > 1 else float(res.loss)
+
+    # ---- weak_aux: 64 items per GPU (round 1's line), same kernels, global batch 64 x world -------------------
+    weak_aux = None
+    if world > 1 and strong and not args.no_weak_aux:
+        wx = torch.from_numpy(inp.x).to(dev)
+        wd = [torch.from_numpy(d).to(dev) for d in inp.disparities]
+        wposes = [mdb200.Pose(torch.from_numpy(r).to(dev), torch.from_numpy(t).to(dev)) for r, t in zip(inp.rvecs, inp.tvecs)]
+        wauto = mdb200.automasking_loss(mdb200.SSIM(), wx, wx[:, inp.target_id - 1], source_ids=inp.source_ids) if inp.automasking else None
+        wpg = mdist.PackedGrads(NB * world, S, rank * NB, NB, dev)
+        wplan = mdb200.FusedLoss(N=NB, n_global=NB * world, device=dev, out=wpg.out(), **common)
+        keep_flush, flush = flush, None     # 866 MB of inputs per rank: larger than L2
+
+        def wstep():
+            r = wplan(wx, wd, wposes, wauto)
+            mdist.allreduce(wpg)
+            return r
+        wms, _, _, _, _, _ = timed(wstep, args.steps, warm)
+        flush = keep_flush
+        weak_aux = {"scaling": "weak", "batch_per_gpu": NB, "global_batch": NB * world, "ms_per_step": wms / args.steps,
+                    "value": NB * world * Ls * S * W * H * args.steps / (wms * 1e-3), "unit": UNIT}
+        del wx, wd, wposes, wauto, wplan, wpg
+        torch.cuda.empty_cache()
 
     # ---- e2e: host buffers, copies inside the timed region ---------------------------------
     e2e = None
     if not args.no_e2e:
         e_chunk = args.e2e_chunk if args.e2e_chunk > 0 else None   # None: HostLoss.default_chunk
-        hplan = mdb200.HostLoss(N=N, n_global=Ng, device=dev, chunk=e_chunk, **common)
+        hplan = mdb200.HostLoss(N=N, n_global=Ng, device=dev, chunk=e_chunk, packed=pg if world > 1 else None, **common)
         hposes = [mdb200.Pose(r, t) for r, t in zip(hr, ht)]
         e_steps = max(3, min(args.steps, 10))
         for _ in range(3):
@@ -300,92 +402,99 @@ def run_ours(args):
         sync_all()
         t0 = time.perf_counter()
         for _ in range(e_steps):
-            hres = mdb200.train_loss_host(hplan, hx, hd, hposes, hauto)   # returns after the D2H of the result
-            if world > 1:
-                dist.all_reduce(packed)                                    # same collective as the device path
+            hres = mdb200.train_loss_host(hplan, hx, hd, hposes, hauto)   # returns after the D2H of the (all-reduced) result
         sync_all()
         dt = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
         if world > 1:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        e2e = {"value": units_per_rank * world * e_steps / float(dt), "unit": UNIT,
-               "h2d_bytes_per_step": hplan.h2d_bytes * world, "d2h_bytes_per_step": hplan.d2h_bytes * world,
+        h2d = torch.tensor([hplan.h2d_bytes, hplan.d2h_bytes], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(h2d)
+        e2e = {"value": units_total * e_steps / float(dt), "unit": UNIT,
+               "h2d_bytes_per_step": int(h2d[0]), "d2h_bytes_per_step": int(h2d[1]),
                "ms_per_step": float(dt) / e_steps * 1e3, "steps": e_steps, "host_numa_binding": numa,
-               "loss_matches_device_path": bool(abs(hres.loss * (1 if world == 1 else 1) - float(res.loss)) <= 1e-5 * abs(float(res.loss)))}
+               "loss_matches_device_path": bool(abs(hres.loss - loss_val) <= 1e-5 * abs(loss_val))}
         # the same call fed the dataset's own format (src/dtk.jl:29-46): uint8 triplet strips, converted on the
         # device (mdb_ingest_triplet_u8) -- a quarter of the image bytes over PCIe.  Auxiliary: the headline
         # `e2e` stays the Float32 call above, which is what the reference's `transfer(x)` ships.
         if not inp.automasking and inp.C == 3:
             del hplan
             torch.cuda.empty_cache()
-            from mdb200 import synth
-            hu8 = torch.tensor(synth.to_u8_strips(inp.x)).pin_memory()
-            uplan = mdb200.HostLoss(N=N, n_global=Ng, device=dev, chunk=e_chunk, x_format="u8_strip", **common)
+            synth = load_synth()
+            hu8 = torch.tensor(synth.to_u8_strips(inp.x[lo:hi])).pin_memory()
+            uplan = mdb200.HostLoss(N=N, n_global=Ng, device=dev, chunk=e_chunk, x_format="u8_strip",
+                                    packed=pg if world > 1 else None, **common)
             for _ in range(3):
                 mdb200.train_loss_host(uplan, hu8, hd, hposes, None)
             sync_all()
             t0 = time.perf_counter()
             for _ in range(e_steps):
                 mdb200.train_loss_host(uplan, hu8, hd, hposes, None)
-                if world > 1:
-                    dist.all_reduce(packed)
             sync_all()
             dtu = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
             if world > 1:
                 dist.all_reduce(dtu, op=dist.ReduceOp.MAX)
-            e2e["u8_strip_input"] = {"value": units_per_rank * world * e_steps / float(dtu), "unit": UNIT,
-                                     "h2d_bytes_per_step": uplan.h2d_bytes * world, "d2h_bytes_per_step": uplan.d2h_bytes * world,
+            hu = torch.tensor([uplan.h2d_bytes, uplan.d2h_bytes], device=dev, dtype=torch.float64)
+            if world > 1:
+                dist.all_reduce(hu)
+            e2e["u8_strip_input"] = {"value": units_total * e_steps / float(dtu), "unit": UNIT,
+                                     "h2d_bytes_per_step": int(hu[0]), "d2h_bytes_per_step": int(hu[1]),
                                      "ms_per_step": float(dtu) / e_steps * 1e3,
                                      "note": "images as uint8 triplet strips (8-bit quantised copies of the same synthetic frames), "
                                              "disparities / poses / gradients Float32 as above"}
 
     if rank == 0:
-        peak, peak_src = load_peaks()
-        b_alg = algorithmic_bytes(inp, N)
-        k_ms = float(seg[:, 1].mean())
-        achieved = b_alg / (k_ms * 1e-3) / 1e9
         line = {
-            "metric": METRIC, "value": units_per_rank * world * args.steps / (ms_total * 1e-3), "unit": UNIT,
-            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
+            "metric": METRIC, "value": units_total * args.steps / (ms_total * 1e-3), "unit": UNIT,
+            "n_gpus": world, "steps": args.steps, "warmup": warm,
+            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": args.scaling,
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"{args.config}: {W}x{H} batch {N} per GPU, 3-frame stacks, {S} sources, "
+            "config": {"workload": f"{args.config}: {W}x{H} global batch {Ng} ({N} items on this rank), 3-frame stacks, {S} sources, "
                                    f"{Ls} scales, SSIM+L1 min-reprojection{' + automask' if inp.automasking else ''} "
-                                   f"+ smoothness, fwd+bwd", "global_batch": Ng, "l2": "inputs_larger_than_l2",
-                       "parallelism": f"batch-sharded x{world}, 1 all-reduce of [loss, pose grads] per step",
-                       "units_per_step": units_per_rank * world, "loss": loss_val,
+                                   f"+ smoothness, fwd+bwd", "global_batch": Ng, "batch_per_gpu": N,
+                       "l2": "inputs_larger_than_l2" if flush is None else
+                             f"flushed: {flush.numel() >> 20} MiB written between the timed steps, outside the per-step event pairs",
+                       "timing": "sum of one CUDA-event pair per step on the launching stream, max over ranks",
+                       "parallelism": f"batch-sharded x{world}, 1 all-reduce of [loss, pose grads] per step "
+                                      f"(transport: {transport})",
+                       "units_per_step": units_total, "loss": loss_val, "wall_s_timed_region": wall,
                        **({"disp_noise": args.disp_noise, "diagnostic": "not SURVEY 8d's inputs"}
                           if args.disp_noise is not None else {})},
             "clocks": clocks,
             "e2e": e2e,
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "photo_strip_kernel<3,2>", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": achieved / peak,
-                         # dram__bytes_read.sum + dram__bytes_write.sum of this launch at config 5, batch 64
-                         # (profiles/r1_step_b64_v9.csv); null for any other workload
-                         "traffic": 965726464 if (args.config == "config5" and N == 64) else None,
-                         "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": b_alg, "kernel_ms": k_ms,
-                         "segments_ms": {"prep_stats": float(seg[:, 0].mean()), "fused": k_ms,
-                                         "upsample_bwd": float(seg[:, 2].mean()), "finalize": float(seg[:, 3].mean())},
-                         # what actually bounds the kernel (profiles/r1_strip_summary.md): instruction issue
-                         "issue_bound": {"thread_instr_per_warped_px": 597.9, "issue_peak_thread_instr_per_s": 148 * 4 * 32 * 1.965e9,
-                                         "floor_ms": units_per_rank * 597.9 / (148 * 4 * 32 * 1.965e9) * 1e3,
-                                         "frac": units_per_rank * 597.9 / (148 * 4 * 32 * 1.965e9) * 1e3 / k_ms,
-                                         "source": "smsp__inst_executed.sum x 32 / warped px (ncu, profiles/r1_step_b64_v9.csv); "
-                                                   "peak = 148 SM x 4 schedulers x 32 lanes x 1.965 GHz"},
-                         "note": "HBM traffic equals the compulsory bytes (traffic / algorithmic = 0.988) but the fused loss is "
-                                 "bound on the SM, not by HBM (SURVEY F10): ~6 B per warped pixel against ~598 instructions; "
-                                 "no pipe saturated (issue 63 %, LSU 65 %), per-warp latency at 13 warps per SM"},
+            "roofline": roofline_block(args, inp, N, seg, dev),
         }
+        if shard_parity is not None:
+            line["shard_parity"] = shard_parity["ok"]
+            line["shard_parity_detail"] = shard_parity
+        if weak_aux is not None:
+            line["weak_aux"] = weak_aux
         if not args.no_cpu_baseline and world == 1:
             rate, cores, t, items = cpu_reference_rate(inp, args.cpu_sample_items, 3, 1)
             line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
                                     "one_thread_value": cpu_reference_rate.one_thread,
-                                    "sample": f"{items} of the batch's {N} items, 3 steps after 1 warm-up, plain-C float32 port "
+                                    "sample": f"{items} of the batch's {NB} items, 3 steps after 1 warm-up, plain-C float32 port "
                                               f"(oracle/c_port), one item per thread, {cores} threads ({t:.2f} s/step)"}
         print(json.dumps(line), flush=True)
     if world > 1:
+        sync_all()
+        mdb200._lib.lib.mdb_comm_destroy(mdb200.handle())
         dist.destroy_process_group()
+
+
+def roofline_block(args, inp, N, seg, dev):
+    """The dominant kernel (photo_strip_kernel) of THIS rank's launch: CUDA events recorded inside the C-ABI call
+    (mdb_profile_*) on the launching stream."""
+    peak, peak_src = load_peaks()
+    b_alg = algorithmic_bytes(inp, N)
+    k_ms = float(seg[:, 1].mean())
+    achieved = b_alg / (k_ms * 1e-3) / 1e9
+    return {"bound": "hbm", "kernel": "photo_strip_kernel<3,2>", "achieved": achieved, "peak": peak,
+            "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+            "algorithmic_bytes_per_launch": b_alg, "kernel_ms": k_ms,
+            "segments_ms": {"prep_stats": float(seg[:, 0].mean()), "fused": k_ms,
+                            "finalize": float(seg[:, 2].mean()), "upsample_bwd": float(seg[:, 3].mean())}}
 
 
 def run_render(args):

@@ -48,8 +48,9 @@ extern "C" {
 
 #define MDB_MAX_SCALES 8
 #define MDB_MAX_SOURCES 2
+#define MDB_COMM_MAX_RANKS 16 /* ranks of the one-shot peer-write reduce (one box) */
 
-typedef struct mdb_handle mdb_handle; /* opaque; caches device properties + TMA encoder */
+typedef struct mdb_handle mdb_handle; /* opaque; caches device properties, profiling events, the communicator */
 
 /* ---- handle ------------------------------------------------------------------------ */
 int32_t mdb_version(void);
@@ -61,12 +62,17 @@ int64_t mdb_launch_count(const mdb_handle* h);
 
 /* Optional segment timing of mdb_train_loss_fwdbwd for the bench roofline: after
  * mdb_profile_begin(h, slots) every call records CUDA events on the caller's stream around its
- * 4 segments (0 pose/stats pre-pass, 1 fused kernel, 2 upsample transpose, 3 finalize) into the
+ * 4 segments (0 pose/stats pre-pass, 1 fused kernel, 2 per-item finalize + scalar loss, 3 upsample transpose) into the
  * next slot; mdb_profile_read waits for that slot and returns the 4 durations in ms.
  * mdb_profile_begin(h, 0) switches it off.  No reference counterpart (the reference's only
  * timing is `CUDA.@time` in scratch files, src/test.jl:30).                                 */
 int32_t mdb_profile_begin(mdb_handle* h, int32_t slots);
 int32_t mdb_profile_read(mdb_handle* h, int32_t slot, float* ms_out /* 4 floats */);
+
+/* Test hooks, process-global, never read from the environment: "strip_segs" = n forces n row segments per strip
+ * in the fused kernel (0 = the library's choice), "upsample_split" = 1 forces the two-kernel transpose that
+ * W > 4096 takes.  Set BEFORE mdb_train_loss_workspace_bytes (the record count depends on the segments).     */
+int32_t mdb_debug_option(const char* name, int64_t value);
 
 /* ---- parameters of the loss ---------------------------------------------------------- */
 typedef struct mdb_loss_params {
@@ -136,11 +142,13 @@ int32_t mdb_photometric_loss(mdb_handle* h, const float* predicted, const float*
 int32_t mdb_prediction_loss(mdb_handle* h, const float* const* predictions, int32_t S,
                             const float* target, int32_t W, int32_t H, int32_t C, int32_t N,
                             float alpha, float c1, float c2, float* out, void* stream);
-/* automasking_loss(ssim, inputs (W,H,C,L,N), target; source_ids) src/training.jl:9-11 */
-int32_t mdb_automasking_loss(mdb_handle* h, const float* x, int32_t target_id,
-                             const int32_t* source_ids, int32_t S, int32_t W, int32_t H,
-                             int32_t C, int32_t L, int32_t N, float alpha, float c1, float c2,
-                             float* out, void* stream);
+/* automasking_loss(ssim, inputs (W,H,C,L,N), target (W,H,C,N); source_ids)  src/training.jl:9-11;
+ * callers src/dtk.jl:59-61 pass target = x[:, :, :, target_id, :].  `target` is the target ARRAY as in the
+ * reference; target_item_stride = elements between two items of it: 0 or W H C for a dense (W,H,C,N) array
+ * (what the reference's slicing copy produces), W H C L for a view into `inputs` (no copy).              */
+int32_t mdb_automasking_loss(mdb_handle* h, const float* inputs, const float* target, int64_t target_item_stride,
+                             const int32_t* source_ids, int32_t S, int32_t W, int32_t H, int32_t C, int32_t L,
+                             int32_t N, float alpha, float c1, float c2, float* out, void* stream);
 /* _apply_mask(mask, warp_loss): elementwise min over n values    src/training.jl:17-19 */
 int32_t mdb_apply_mask(mdb_handle* h, const float* mask, const float* warp_loss, int64_t n,
                        float* out, void* stream);
@@ -184,6 +192,36 @@ size_t mdb_train_loss_workspace_bytes(const mdb_loss_io* io);
  * cached gradients by the incoming scalar cotangent).                                    */
 int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_loss_params* p,
                               void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- the batch sharded over the GPUs of one box ------------------------------------------
+ * The reference is single-GPU; the only coupling between items is the mean over N (src/training.jl:69,
+ * src/utils.jl:176).  Rank r evaluates its contiguous shard with params.n_global = N_global, so shard losses
+ * add, and ONE sum over the ranks of the packed vector
+ *     [ loss | d_rvec[s][n] (3 floats) for s, n | d_tvec[s][n] (3 floats) for s, n ]    1 + 6 S N_global floats
+ * gives every rank the batch loss and the full (3,N) pose gradients; disparity gradients stay sharded.
+ * mdb_packed_bind points io->loss / d_rvec / d_tvec INTO the rank's slots of a packed SEND buffer (all other
+ * slots zero, written once by the caller), so mdb_train_loss_fwdbwd fills it in place and the step is the five
+ * loss kernels + one all-reduce: no packing kernels.                                                     */
+int64_t mdb_packed_size(int32_t n_global, int32_t S);
+int32_t mdb_packed_bind(mdb_loss_io* io, float* packed_send, int32_t n_global, int32_t first_item);
+/* transport 1: NCCL (libnccl.so.2 resolved at run time with dlopen; in a PyTorch process the already loaded
+ * copy).  Rank 0 calls mdb_comm_get_unique_id (128 bytes) and the launcher hands the bytes to every rank.   */
+int32_t mdb_comm_get_unique_id(void* out, size_t bytes);
+int32_t mdb_comm_init(mdb_handle* h, const void* unique_id, int32_t rank, int32_t world);
+/* transport 2: one-shot peer writes over NVLink, no library.  _export allocates this rank's symmetric buffer
+ * (the one allocation the library makes itself: CUDA IPC exports whole cudaMalloc allocations) and returns its
+ * 64-byte cudaIpcMemHandle; the launcher gathers the handles of all ranks (rank order) and calls _attach, then
+ * synchronises the ranks once.  Every all-reduce is then ONE kernel: write own vector into its slot on every
+ * peer, raise a flag there, wait (bounded) for the peers' flags, add the slots in rank order -- deterministic
+ * and bit-identical on all ranks.  When both transports are set up this one is used.                         */
+int32_t mdb_comm_peers_export(mdb_handle* h, int32_t world, int64_t max_count, void* ipc_handle_out, size_t bytes);
+int32_t mdb_comm_peers_attach(mdb_handle* h, const void* ipc_handles /* world x 64 bytes */, int32_t rank);
+/* recv[i] = sum over ranks of send[i] (send != recv allowed and intended: the send buffer keeps its zeros).
+ * Enqueued on `stream`.                                                                                     */
+int32_t mdb_allreduce_loss_posegrad(mdb_handle* h, const float* send, float* recv, int64_t count, void* stream);
+/* *timed_out = 1 if a one-shot reduce gave up waiting for a peer (~10 s); synchronises the device           */
+int32_t mdb_comm_status(mdb_handle* h, int32_t* timed_out);
+int32_t mdb_comm_destroy(mdb_handle* h); /* also done by mdb_destroy */
 
 /* ---- R1-R7: plane-disparity volume rendering  (src/render.jl) ------------------------------
  * Layouts: rgb (W,H,3,Np,B), sigma (W,H,1,Np,B), xyz (3,W,H,Np,B), disparity_src (Np,B),

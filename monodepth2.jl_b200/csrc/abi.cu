@@ -23,13 +23,6 @@ int32_t mdb_create(mdb_handle** out, int32_t device) {
   h->cc_major = prop.major;
   h->cc_minor = prop.minor;
   h->smem_optin = prop.sharedMemPerBlockOptin;
-  // driver entry point for TMA descriptors (no link-time dependency on libcuda)
-  cudaDriverEntryPointQueryResult qres;
-  void* fn = nullptr;
-  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) == cudaSuccess &&
-      qres == cudaDriverEntryPointSuccess)
-    h->encode_tiled = fn;
-  (void)cudaGetLastError();
   *out = h;
   return MDB_OK;
 }
@@ -43,7 +36,10 @@ static void prof_free(mdb_handle* h) {
 }
 
 int32_t mdb_destroy(mdb_handle* h) {
-  if (h) prof_free(h);
+  if (h) {
+    prof_free(h);
+    mdb_comm_destroy(h);
+  }
   delete h;
   return MDB_OK;
 }

@@ -28,9 +28,9 @@ struct mdb_handle {
   int cc_major = 0, cc_minor = 0;
   size_t smem_optin = 0;
   int64_t launches = 0;
-  void* encode_tiled = nullptr;  // cuTensorMapEncodeTiled, resolved at create time
+  struct mdb_comm* comm = nullptr;   // comm.cu: NCCL communicator and / or the peer-mapped buffers of the one-shot reduce
   // optional per-call segment timing (mdb_profile_*): events recorded on the caller's stream
-  static constexpr int kProfSegments = 4;  // 0 prep+stats, 1 fused kernel, 2 upsample_bwd, 3 finalize
+  static constexpr int kProfSegments = 4;  // 0 prep+stats, 1 fused kernel, 2 finalize, 3 upsample_bwd
   int prof_slots = 0, prof_next = 0;
   cudaEvent_t* prof_ev = nullptr;  // [slots][kProfSegments + 1]
   const mdb_pose_adam* pose_adam = nullptr;   // set by mdb_slow_depth_create around its capture of the loss call

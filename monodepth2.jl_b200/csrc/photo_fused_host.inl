@@ -1,6 +1,10 @@
 // photo_fused_host.inl -- finalize kernels, up-sample transpose and the C-ABI entry of the fused loss
 namespace {
 
+// test hooks (mdb_debug_option): process-global, read on the host only, default 0 = off
+int g_dbg_strip_segs = 0;       // force this many row segments per strip
+int g_dbg_upsample_split = 0;   // force the two-kernel V / H transpose (the W > 4096 path)
+
 // ---------------------------------------------------------------------------------------
 // 4. per-item finalize: fixed-order sum of the warp records (double); pose chain to rvec/tvec;
 //    smoothness loss per scale and the mean-normalisation constant of its gradient
@@ -443,7 +447,7 @@ inline StripGeom strip_geom(const mdb_loss_io* io, int num_sms) {
   const long long one_wave = (long long)13 * sms;
   if (base * max_segs < one_wave)
     max_segs = (int)std::max<long long>(max_segs, std::min<long long>(io->H / 4, (one_wave + base - 1) / base));
-  if (const char* e = getenv("MDB_STRIP_SEGS")) { want = atoll(e); max_segs = std::max(1, io->H / 2); }
+  if (g_dbg_strip_segs > 0) { want = g_dbg_strip_segs; max_segs = std::max(1, io->H / 2); }
   g.nsegs = (int)std::min<long long>(std::max<long long>(want, 1), max_segs);
   g.seg_rows = (io->H + g.nsegs - 1) / g.nsegs;
   g.nsegs = (io->H + g.seg_rows - 1) / g.seg_rows;
@@ -496,6 +500,14 @@ int32_t launch_fused(mdb_handle* h, const FusedArgs& fa, const FusedLayout& L, c
 }  // namespace
 
 extern "C" {
+
+int32_t mdb_debug_option(const char* name, int64_t value) {
+  if (!name) return MDB_E_INVALID_ARG;
+  if (!strcmp(name, "strip_segs")) g_dbg_strip_segs = (int)value;
+  else if (!strcmp(name, "upsample_split")) g_dbg_upsample_split = (int)value;
+  else return MDB_E_INVALID_ARG;
+  return MDB_OK;
+}
 
 size_t mdb_train_loss_workspace_bytes(const mdb_loss_io* io) {
   if (!io_shape_ok(io)) return 0;
@@ -613,10 +625,11 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
   if (S == 2) finalize_item_kernel<2><<<N, FIN_THREADS, 0, st>>>(fa.partials, L.records, pa, fin, stats, item_loss);
   else finalize_item_kernel<1><<<N, FIN_THREADS, 0, st>>>(fa.partials, L.records, pa, fin, stats, item_loss);
   MDB_LAUNCHED(h);
+  mdb_prof_mark(h, pslot, 3, st);
   {
     bool any_low = false;
     for (int s = 0; s < Ls; ++s) any_low = any_low || !fa.native[s];
-    const bool force_split = getenv("MDB_UPSAMPLE_SPLIT") != nullptr;   // tests: the two-kernel path (W > 4096)
+    const bool force_split = g_dbg_upsample_split != 0;   // tests: the two-kernel path (W > 4096)
     // native scales only receive the normalisation constant here: nothing to do without it (slow_depth)
     if (!(any_low || p->normalize_disparity)) {
     } else if (W <= 4096 && !force_split) {
@@ -659,7 +672,6 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
       }
     }
   }
-  mdb_prof_mark(h, pslot, 3, st);
   // the scalar loss was written by finalize_item_kernel (its last CTA): no launch of its own
   mdb_prof_mark(h, pslot, 4, st);
   return MDB_OK;

@@ -518,18 +518,20 @@ int32_t mdb_prediction_loss(mdb_handle* h, const float* const* predictions, int3
   return photo_launch(h, a, stream);
 }
 
-int32_t mdb_automasking_loss(mdb_handle* h, const float* x, int32_t target_id, const int32_t* source_ids,
-                             int32_t S, int32_t W, int32_t H, int32_t C, int32_t L, int32_t N,
-                             float alpha, float c1, float c2, float* out, void* stream) {
-  MDB_REQUIRE(h, h && x && source_ids && out && S >= 1 && S <= 4 && target_id >= 1 && target_id <= L,
-              MDB_E_INVALID_ARG, "mdb_automasking_loss: bad argument");
+int32_t mdb_automasking_loss(mdb_handle* h, const float* inputs, const float* target, int64_t target_item_stride,
+                             const int32_t* source_ids, int32_t S, int32_t W, int32_t H, int32_t C, int32_t L,
+                             int32_t N, float alpha, float c1, float c2, float* out, void* stream) {
+  MDB_REQUIRE(h, h && inputs && target && source_ids && out && S >= 1 && S <= 4, MDB_E_INVALID_ARG,
+              "mdb_automasking_loss: bad argument");
   PhotoArgs a{};
   const int64_t frame = (int64_t)W * H * C;
+  MDB_REQUIRE(h, target_item_stride == 0 || target_item_stride >= frame, MDB_E_INVALID_ARG,
+              "mdb_automasking_loss: target_item_stride must be 0 (dense) or >= W H C");
   for (int s = 0; s < S; ++s) {
     MDB_REQUIRE(h, source_ids[s] >= 1 && source_ids[s] <= L, MDB_E_INVALID_ARG, "source id out of range");
-    a.pred[s] = x + (source_ids[s] - 1) * frame; a.pred_nstride[s] = frame * L;
+    a.pred[s] = inputs + (source_ids[s] - 1) * frame; a.pred_nstride[s] = frame * L;
   }
-  a.target = x + (target_id - 1) * frame; a.tgt_nstride = frame * L;
+  a.target = target; a.tgt_nstride = target_item_stride > 0 ? target_item_stride : frame;
   a.S = S; a.W = W; a.H = H; a.C = C; a.N = N; a.mode = 2; a.alpha = alpha; a.c1 = c1; a.c2 = c2; a.out = out;
   return photo_launch(h, a, stream);
 }
@@ -564,7 +566,6 @@ int32_t mdb_smooth_loss(mdb_handle* h, const float* disparity, const float* imag
     const int threads = std::min(SM_THREADS, ((W / 4 + 31) / 32) * 32);
     int rows = SM_ROWS;
     if ((long long)rb * N < (long long)h->num_sms * 8) rows = SM_ROWS_MIN;
-    if (const char* e = getenv("MDB_SMOOTH_ROWS")) rows = std::max(SM_ROWS_MIN, atoi(e));
     rb = (H + rows - 1) / rows;
     dim3 grid4(rb, N);
     switch (C) {

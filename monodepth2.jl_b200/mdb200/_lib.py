@@ -95,7 +95,7 @@ PROTOTYPES = {
     "mdb_photometric_loss": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _f32, _f32, _f32, _vp, _vp]),
     "mdb_prediction_loss": (_i32, [_vp, C.POINTER(_vp), _i32, _vp, _i32, _i32, _i32, _i32, _f32, _f32,
                                    _f32, _vp, _vp]),
-    "mdb_automasking_loss": (_i32, [_vp, _vp, _i32, C.POINTER(_i32), _i32, _i32, _i32, _i32, _i32, _i32,
+    "mdb_automasking_loss": (_i32, [_vp, _vp, _vp, _i64, C.POINTER(_i32), _i32, _i32, _i32, _i32, _i32, _i32,
                                     _f32, _f32, _f32, _vp, _vp]),
     "mdb_apply_mask": (_i32, [_vp, _vp, _vp, _i64, _vp, _vp]),
     "mdb_smooth_loss_workspace_bytes": (_sz, [_i32, _i32, _i32]),
@@ -129,6 +129,16 @@ PROTOTYPES = {
     "mdb_pose_head": (_i32, [_vp, _vp, _i32, _i32, _i32, _f32, _vp, _vp, _vp]),
     "mdb_pose_head_bwd": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _f32, _vp, _vp]),
     "mdb_item_mean": (_i32, [_vp, _vp, _i64, _i32, _vp, _vp]),
+    "mdb_debug_option": (_i32, [C.c_char_p, _i64]),
+    "mdb_packed_size": (_i64, [_i32, _i32]),
+    "mdb_packed_bind": (_i32, [C.POINTER(LossIO), _vp, _i32, _i32]),
+    "mdb_comm_get_unique_id": (_i32, [_vp, _sz]),
+    "mdb_comm_init": (_i32, [_vp, _vp, _i32, _i32]),
+    "mdb_comm_peers_export": (_i32, [_vp, _i32, _i64, _vp, _sz]),
+    "mdb_comm_peers_attach": (_i32, [_vp, _vp, _i32]),
+    "mdb_allreduce_loss_posegrad": (_i32, [_vp, _vp, _vp, _i64, _vp]),
+    "mdb_comm_status": (_i32, [_vp, C.POINTER(_i32)]),
+    "mdb_comm_destroy": (_i32, [_vp]),
 }
 
 

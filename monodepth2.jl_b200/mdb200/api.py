@@ -48,8 +48,15 @@ def profile_begin(slots: int) -> None:
     check(handle(), lib.mdb_profile_begin(handle(), int(slots)))
 
 
+def debug_option(name: str, value: int) -> None:
+    """Test hooks of the library ("strip_segs", "upsample_split"); 0 restores the default."""
+    rc = lib.mdb_debug_option(name.encode(), int(value))
+    if rc != 0:
+        raise ValueError(f"unknown debug option {name!r}")
+
+
 def profile_read(slot: int):
-    """-> [prep+stats, fused kernel, upsample transpose, finalize] durations of that call, ms."""
+    """-> [prep+stats, fused kernel, finalize, upsample transpose] durations of that call, ms."""
     out = (ct.c_float * 4)()
     check(handle(), lib.mdb_profile_read(handle(), int(slot), out))
     return list(out)
@@ -260,15 +267,22 @@ def prediction_loss(ssim: SSIM, predictions: Sequence[torch.Tensor], target: tor
     return out
 
 
-def automasking_loss(ssim: SSIM, inputs: torch.Tensor, target_id: int, *, source_ids: Sequence[int], alpha: float = 0.85):
-    """src/training.jl:9-11.  `inputs` (N,L,C,H,W); the target is frame `target_id` of it
-    (the reference passes the slice; the ABI takes the index so no copy is made)."""
+def automasking_loss(ssim: SSIM, inputs: torch.Tensor, target: torch.Tensor, *, source_ids: Sequence[int], alpha: float = 0.85):
+    """`automasking_loss(ssim, inputs, target; source_ids)` -- src/training.jl:9-11, the reference's own
+    signature: `inputs` (N,L,C,H,W), `target` (N,C,H,W) the target ARRAY (callers pass
+    `x[:, :, :, target_id, :]`, src/dtk.jl:59-61).  A dense tensor or the view `inputs[:, target_id - 1]`
+    (frames dense, items strided: no copy) are both taken as they are."""
     _chk(inputs, "inputs")
     N, L, Cc, H, W = inputs.shape
+    if not (isinstance(target, torch.Tensor) and target.is_cuda and target.dtype == torch.float32
+            and tuple(target.shape) == (N, Cc, H, W) and target[0].is_contiguous() and (N == 1 or target.stride(0) >= Cc * H * W)):
+        raise TypeError("target: expected a CUDA float32 (N,C,H,W) tensor whose items are dense (a contiguous tensor or "
+                        "inputs[:, target_id - 1])")
     S = len(source_ids)
     ids = (ct.c_int32 * S)(*[int(s) for s in source_ids])
     out = torch.empty((N, 1, H, W), device=inputs.device, dtype=torch.float32)
-    check(handle(), lib.mdb_automasking_loss(handle(), _p(inputs), int(target_id), ids, S, W, H, Cc, L, N, alpha, ssim.c1, ssim.c2, _p(out), _stream()))
+    check(handle(), lib.mdb_automasking_loss(handle(), _p(inputs), _p(target), int(target.stride(0)) if N > 1 else 0, ids, S,
+                                             W, H, Cc, L, N, alpha, ssim.c1, ssim.c2, _p(out), _stream()))
     return out
 
 
@@ -346,20 +360,18 @@ class FusedLoss:
             io.K[i], io.invK[i] = kk[i], ik[i]
         self.io = io
         f32 = dict(device=self.dev, dtype=torch.float32)
-        if out is None:
-            self.loss = torch.zeros((), **f32)
-            self.d_disp = [torch.empty((N, 1, h, w), **f32) for (w, h) in self.disp_sizes]
-            self.d_rvec = [torch.empty((N, 3), **f32) for _ in range(self.S)]
-            self.d_tvec = [torch.empty((N, 1, 3), **f32) for _ in range(self.S)]
-        else:
-            self.loss, self.d_disp, self.d_rvec, self.d_tvec = out["loss"], list(out["d_disp"]), list(out["d_rvec"]), list(out["d_tvec"])
-            for t, shp in [(self.loss, None)] + [(t, (N, 1, h, w)) for t, (w, h) in zip(self.d_disp, self.disp_sizes)] + \
-                    [(t, (N, 3)) for t in self.d_rvec] + [(t, (N, 1, 3)) for t in self.d_tvec]:
-                _chk(t, "out")
-                if shp is not None and tuple(t.shape) != shp:
-                    raise ValueError(f"output buffer has shape {tuple(t.shape)}, expected {shp}")
-            if self.loss.numel() != 1:
-                raise ValueError("out['loss'] must hold one float")
+        out = dict(out or {})   # any subset of the outputs may be caller-provided; the plan owns the rest
+        self.loss = out["loss"] if "loss" in out else torch.zeros((), **f32)
+        self.d_disp = list(out["d_disp"]) if "d_disp" in out else [torch.empty((N, 1, h, w), **f32) for (w, h) in self.disp_sizes]
+        self.d_rvec = list(out["d_rvec"]) if "d_rvec" in out else [torch.empty((N, 3), **f32) for _ in range(self.S)]
+        self.d_tvec = list(out["d_tvec"]) if "d_tvec" in out else [torch.empty((N, 1, 3), **f32) for _ in range(self.S)]
+        for t, shp in [(self.loss, None)] + [(t, (N, 1, h, w)) for t, (w, h) in zip(self.d_disp, self.disp_sizes)] + \
+                [(t, (N, 3)) for t in self.d_rvec] + [(t, (N, 1, 3)) for t in self.d_tvec]:
+            _chk(t, "out")
+            if shp is not None and tuple(t.shape) != shp:
+                raise ValueError(f"output buffer has shape {tuple(t.shape)}, expected {shp}")
+        if self.loss.numel() != 1:
+            raise ValueError("out['loss'] must hold one float")
         self.vis = torch.empty((N, 1, H, W), **f32) if want_vis else None
         io.loss = self.loss.data_ptr()
         for k in range(self.Ls):
@@ -678,7 +690,7 @@ def find_static(x: torch.Tensor, alpha: float, *, target_id: int = 2, source_ids
     """`find_static(dataset, alpha)` -- src/dtk.jl:51-69, for a batch at once: a sample is kept as
     NON-static when `mean(automasking_loss(ssim, x, target; source_ids)) > alpha`.  x (N,L,C,H,W) on the
     device (e.g. from `ingest_triplet_u8`).  Returns (non_static bool (N,), per-item means (N,))."""
-    means = item_mean(automasking_loss(SSIM(), x, target_id, source_ids=source_ids))
+    means = item_mean(automasking_loss(SSIM(), x, x[:, target_id - 1], source_ids=source_ids))
     return means > alpha, means
 
 
@@ -703,12 +715,16 @@ class HostLoss:
     contract the multi-GPU shards use, so chunk losses simply add."""
 
     def __init__(self, *, W, H, C, L, N, disp_sizes, scales, target_id, source_ids, K, invK, chunk=None,
-                 automasking=False, n_global=0, device=None, x_format="f32", ramp_up=None, **kw):
+                 automasking=False, n_global=0, device=None, x_format="f32", ramp_up=None, packed=None, **kw):
         """x_format "f32": x is the Float32 (N,L,C,H,W) stack.  "u8_strip": x is the dataset's own format,
         uint8 (N,H,3W,3) decoded triplet strips (src/dtk.jl:29-46) -- a quarter of the PCIe bytes; the
         device converts with mdb_ingest_triplet_u8 (C = 1: Gray luma)."""
+        """packed: a `mdb200.dist.PackedGrads` of a batch sharded over ranks -- the chunks then write their pose
+        gradients into the rank's slots of its send buffer, the call ends with the path's all-reduce and returns the
+        GLOBAL loss and pose gradients (disparity gradients stay this rank's shard)."""
         if x_format not in ("f32", "u8_strip"):
             raise ValueError("x_format must be 'f32' or 'u8_strip'")
+        self.packed = packed
         if x_format == "u8_strip" and L != 3:
             raise ValueError("triplet strips hold L = 3 frames")
         self.x_format = x_format
@@ -751,8 +767,14 @@ class HostLoss:
             self.d_tv = [torch.empty((N, 1, 3), **f32) for _ in range(self.S)]
             self.d_a = torch.empty((N, 1, H, W), **f32) if automasking else None
             self.g_d = [torch.empty((N, 1, h, w), **f32) for (w, h) in self.disp_sizes]
-            self.g_rv = [torch.empty((N, 3), **f32) for _ in range(self.S)]
-            self.g_tv = [torch.empty((N, 1, 3), **f32) for _ in range(self.S)]
+            if packed is None:
+                self.g_rv = [torch.empty((N, 3), **f32) for _ in range(self.S)]
+                self.g_tv = [torch.empty((N, 1, 3), **f32) for _ in range(self.S)]
+            else:
+                if packed.n != N or packed.S != self.S:
+                    raise ValueError("packed was made for another shard size / source count")
+                po = packed.out()
+                self.g_rv, self.g_tv = po["d_rvec"], po["d_tvec"]
             self.g_loss = torch.zeros((len(self.chunks),), **f32)
             self.d_u8 = torch.empty((N, H, 3 * W, 3), device=self.dev, dtype=torch.uint8) if x_format == "u8_strip" else None
             self.d_flip = torch.zeros((N,), device=self.dev, dtype=torch.uint8) if x_format == "u8_strip" else None
@@ -766,12 +788,15 @@ class HostLoss:
         pin = dict(dtype=torch.float32, pin_memory=True)
         self.h_loss = torch.empty((len(self.chunks),), **pin)
         self.h_dd = [torch.empty((N, 1, h, w), **pin) for (w, h) in self.disp_sizes]
-        self.h_dr = [torch.empty((N, 3), **pin) for _ in range(self.S)]
-        self.h_dt = [torch.empty((N, 1, 3), **pin) for _ in range(self.S)]
+        ngl = packed.N if packed is not None else N
+        self.h_dr = [torch.empty((ngl, 3), **pin) for _ in range(self.S)]
+        self.h_dt = [torch.empty((ngl, 1, 3), **pin) for _ in range(self.S)]
+        self.h_packed = torch.empty((packed.send.numel(),), **pin) if packed is not None else None
         x_bytes = 4 * N * L * C * H * W if x_format == "f32" else N * H * 3 * W * 3 + N
         self.h2d_bytes = x_bytes + 4 * (sum(N * w * h for (w, h) in self.disp_sizes) + 6 * N * self.S
                                         + (N * H * W if automasking else 0))
-        self.d2h_bytes = 4 * (len(self.chunks) + sum(N * w * h for (w, h) in self.disp_sizes) + 6 * N * self.S)
+        self.d2h_bytes = 4 * (sum(N * w * h for (w, h) in self.disp_sizes)
+                              + (packed.send.numel() if packed is not None else len(self.chunks) + 6 * N * self.S))
 
     @staticmethod
     def default_chunk(W, H, C, L, N, disp_sizes, automasking=False, x_format="f32") -> int:
@@ -814,6 +839,19 @@ class HostLoss:
                 self.copy_out.wait_event(done)
                 for j in range(len(self.disp_sizes)):
                     self.h_dd[j][a:b].copy_(self.g_d[j][a:b], non_blocking=True)
+        if self.packed is not None:               # sharded batch: chunk losses -> slot 0, then the path's one all-reduce
+            from . import dist as mdist
+            pg = self.packed
+            torch.sum(self.g_loss, dim=0, keepdim=True, out=pg.send[0:1])
+            mdist.allreduce(pg)
+            done = compute.record_event()
+            with torch.cuda.stream(self.copy_out):
+                self.copy_out.wait_event(done)
+                self.h_packed.copy_(pg.recv, non_blocking=True)
+            self.copy_out.synchronize()
+            compute.wait_stream(self.copy_out)
+            loss, rv, tv = mdist.unpack(self.h_packed, pg.N, pg.S)
+            return HostLossResult(float(loss), self.h_dd, rv, tv)
         with torch.cuda.stream(self.copy_out):    # the small results once, after the last chunk
             self.h_loss.copy_(self.g_loss, non_blocking=True)
             for s in range(self.S):

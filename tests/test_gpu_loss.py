@@ -23,7 +23,7 @@ def _run_gpu(inp, normalize=True, smooth_mode=0, auto=None, n_global=0):
                             smooth_weight_mode=smooth_mode, n_global=n_global, want_vis=True)
     al = None
     if inp.automasking:
-        al = mdb200.automasking_loss(mdb200.SSIM(), x, inp.target_id, source_ids=inp.source_ids) if auto is None \
+        al = mdb200.automasking_loss(mdb200.SSIM(), x, x[:, inp.target_id - 1], source_ids=inp.source_ids) if auto is None \
             else auto.to(dev, torch.float32).contiguous()
     res = plan(x, disps, poses, al)
     torch.cuda.synchronize()
@@ -97,7 +97,7 @@ def test_automask_and_vis_maps():
     x64 = torch.tensor(inp.x, dtype=torch.float64)
     auto_ref = T.automasking_loss(x64, x64[:, 1], inp.source_ids)
     x = torch.tensor(inp.x, device="cuda:0")
-    auto = mdb200.automasking_loss(mdb200.SSIM(), x, 2, source_ids=inp.source_ids)
+    auto = mdb200.automasking_loss(mdb200.SSIM(), x, x[:, 1].contiguous(), source_ids=inp.source_ids)
     assert torch.allclose(auto.double().cpu(), auto_ref, atol=2e-6, rtol=1e-5)
     res, plan = _run_gpu(inp, auto=auto_ref)
     K = torch.tensor(inp.K.astype(np.float64)); invK = torch.tensor(inp.invK.astype(np.float64))
@@ -162,23 +162,37 @@ def test_strip_geometry_edges(W, H, scales):
     _compare(inp, ref, res)
 
 
-def test_forced_row_segments(monkeypatch):
-    """Three row segments per strip (MDB_STRIP_SEGS): the 2-row halos above and below a segment must
+@pytest.fixture
+def debug_option():
+    """mdb_debug_option test hooks, reset to the defaults afterwards."""
+    import mdb200
+    used = set()
+
+    def set_(name, value):
+        used.add(name)
+        mdb200.debug_option(name, value)
+    yield set_
+    for name in used:
+        mdb200.debug_option(name, 0)
+
+
+def test_forced_row_segments(debug_option):
+    """Three row segments per strip (mdb_debug_option "strip_segs"): the 2-row halos above and below a segment must
     reproduce the single-segment result, and both must match the oracle."""
     from mdb200 import synth
     inp = synth.make_loss_inputs(60, 96, 2, seed=22, automasking=True)
     ref = P.oracle_train_loss(inp)
-    monkeypatch.setenv("MDB_STRIP_SEGS", "1")
+    debug_option("strip_segs", 1)
     res1, _ = _run_gpu(inp, auto=ref["auto"])
-    monkeypatch.setenv("MDB_STRIP_SEGS", "3")
+    debug_option("strip_segs", 3)
     res3, _ = _run_gpu(inp, auto=ref["auto"])
     _compare(inp, ref, res1)
     _compare(inp, ref, res3)
     for a, b in zip(res1.d_disparities, res3.d_disparities):
         assert torch.allclose(a, b, rtol=1e-5, atol=1e-9)
     # 4-row and 2-row segments (what small problems get so that one wave fills the machine)
-    for segs in ("24", "48"):
-        monkeypatch.setenv("MDB_STRIP_SEGS", segs)
+    for segs in (24, 48):
+        debug_option("strip_segs", segs)
         resn, _ = _run_gpu(inp, auto=ref["auto"])
         _compare(inp, ref, resn)
 
@@ -188,15 +202,14 @@ def test_forced_row_segments(monkeypatch):
     (300, 37, 2, (0.25, 0.5, 1.0)),          # KC = 4, ragged columns, odd ratios (dh - 1 does not divide H - 1)
     (1100, 24, 1, (0.5, 1.0)),               # KC = 16 (W > 1024)
 ])
-def test_upsample_transpose_band_vs_split(monkeypatch, W, H, N, scales):
+def test_upsample_transpose_band_vs_split(debug_option, W, H, N, scales):
     """The streaming band kernel (upsample_bwd_band_kernel) against the two-kernel V/H path it replaced
-    (kept for W > 4096, forced here by MDB_UPSAMPLE_SPLIT) and against the oracle."""
+    (kept for W > 4096, forced here by the "upsample_split" debug option) and against the oracle."""
     from mdb200 import synth
     inp = synth.make_loss_inputs(W, H, N, seed=31, scales=scales)
     ref = P.oracle_train_loss(inp)
-    monkeypatch.delenv("MDB_UPSAMPLE_SPLIT", raising=False)
     res_band, _ = _run_gpu(inp)
-    monkeypatch.setenv("MDB_UPSAMPLE_SPLIT", "1")
+    debug_option("upsample_split", 1)
     res_split, _ = _run_gpu(inp)
     _compare(inp, ref, res_band)
     _compare(inp, ref, res_split)

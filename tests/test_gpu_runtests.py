@@ -157,7 +157,7 @@ def test_warp_and_losses_vs_oracle():
     pr = mdb200.prediction_loss(ssim, warped, tgt)
     pr64 = T.prediction_loss(w64, x64[:, 1])
     assert (pr.cpu().double() - pr64).abs().max() < 1e-5
-    auto = mdb200.automasking_loss(ssim, x, 2, source_ids=inp.source_ids)
+    auto = mdb200.automasking_loss(ssim, x, x[:, 1], source_ids=inp.source_ids)
     am = mdb200._apply_mask(auto, pr)
     assert (am.cpu().double() - T.apply_mask(T.automasking_loss(x64, x64[:, 1], inp.source_ids), pr64)).abs().max() < 1e-5
 

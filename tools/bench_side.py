@@ -26,7 +26,7 @@ for gray in (False, True):
     print(f"ingest_triplet_u8 gray={gray}: {ms*1e3:.1f} us, {b/1e6:.0f} MB, {b/ms/1e6:.0f} GB/s = {b/ms/1e6/peak*100:.1f} % of {peak:.0f}")
 x = out
 auto = None
-ms = timeit(lambda: mdb200.automasking_loss(mdb200.SSIM(), x, 2, source_ids=[1, 3]))
+ms = timeit(lambda: mdb200.automasking_loss(mdb200.SSIM(), x, x[:, 1], source_ids=[1, 3]))
 b = x.numel() * 4 + N * H * W * 4
 print(f"automasking_loss: {ms*1e3:.1f} us, {b/1e6:.0f} MB, {b/ms/1e6:.0f} GB/s = {b/ms/1e6/peak*100:.1f} %")
 m = torch.rand((N, 1, H, W), device=dev)
