@@ -71,7 +71,9 @@ int32_t mdb_profile_read(mdb_handle* h, int32_t slot, float* ms_out /* 4 floats 
 
 /* Test hooks, process-global, never read from the environment: "strip_segs" = n forces n row segments per strip
  * in the fused kernel (0 = the library's choice), "upsample_split" = 1 forces the two-kernel transpose that
- * W > 4096 takes.  Set BEFORE mdb_train_loss_workspace_bytes (the record count depends on the segments).     */
+ * W > 4096 takes; "decision_dump" = device pointer to Ls N (2C+2) H W int8 makes the fused kernel (a separate
+ * instantiation) record every discrete choice its pullback depends on (layout in csrc/photo_strip.inl), 0 = off.
+ * Set BEFORE mdb_train_loss_workspace_bytes (the record count depends on the segments).                       */
 int32_t mdb_debug_option(const char* name, int64_t value);
 
 /* ---- parameters of the loss ---------------------------------------------------------- */
@@ -88,6 +90,10 @@ typedef struct mdb_loss_params {
                                  1: weight 1 (src/simple_depth.jl:39)                    */
   int32_t upsample_align_corners; /* NNlib upsample_bilinear default = 1 (unpinned)      */
   int32_t n_global;           /* batch size the means divide by; 0 = N (single GPU)      */
+  int32_t abs_subgradient;    /* pullback of abs.() at exactly 0 (Zygote, unpinned): 0 = sign(0) = 0
+                                 (ChainRules' scalar rule); 1 = ForwardDiff's Dual rule, which Zygote's
+                                 broadcast uses on CuArrays: +1 at +0.0.  Decides the first iterations
+                                 of slow_depth, whose disparity starts constant (src/simple_depth.jl:8) */
 } mdb_loss_params;
 
 void mdb_loss_params_default(mdb_loss_params* p);
@@ -161,6 +167,10 @@ size_t mdb_smooth_loss_workspace_bytes(int32_t W, int32_t H, int32_t N);
 int32_t mdb_smooth_loss(mdb_handle* h, const float* disparity, const float* image, int32_t W,
                         int32_t H, int32_t C, int32_t N, float* loss, float* d_disparity,
                         void* workspace, size_t workspace_bytes, void* stream);
+/* the same with the pullback of abs at 0 chosen (see mdb_loss_params.abs_subgradient)   */
+int32_t mdb_smooth_loss_ex(mdb_handle* h, const float* disparity, const float* image, int32_t W,
+                           int32_t H, int32_t C, int32_t N, int32_t abs_subgradient, float* loss,
+                           float* d_disparity, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---- P12: the fused hot path  (src/training.jl:21-78; src/simple_depth.jl:25-41) ------ */
 typedef struct mdb_loss_io {
@@ -331,8 +341,8 @@ int32_t mdb_adam_update(mdb_handle* h, int32_t n_tensors, float* const* params, 
  * (forked after the fused kernel) the ADAM kernel of the disparity map; mdb_slow_depth_run replays it
  * `iters` times on the caller's stream with no host round trip.  `io` must describe one full-resolution scale (Ls = 1, dw = W, dh = H); its
  * disparity / rvec / tvec buffers are the parameters and are UPDATED IN PLACE; its d_* buffers and
- * `loss` hold the last iteration's gradients and loss.  `params` should have normalize_disparity = 0
- * and smooth_weight_mode = 1 (src/simple_depth.jl:39).  `state` is caller-owned device memory of
+ * `loss` hold the last iteration's gradients and loss.  `params` MUST have normalize_disparity = 0,
+ * smooth_weight_mode = 1 and automasking = 0 (src/simple_depth.jl:39; MDB_E_INVALID_ARG otherwise).  `state` is caller-owned device memory of
  * mdb_slow_depth_state_bytes(io) bytes, zeroed by the caller before the first run (ADAM moments +
  * counters); `workspace` as for mdb_train_loss_fwdbwd.  All pointers must stay valid and unchanged
  * for the life of the plan.  Layout of `state`: per parameter tensor (disparity, then rvec, tvec per

@@ -83,6 +83,7 @@ void mdb_loss_params_default(mdb_loss_params* p) {
   p->smooth_weight_mode = 0;
   p->upsample_align_corners = 1;
   p->n_global = 0;
+  p->abs_subgradient = 0;
 }
 
 }  // extern "C"

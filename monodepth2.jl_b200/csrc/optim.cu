@@ -120,6 +120,11 @@ int32_t mdb_slow_depth_create(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
   const size_t need = mdb_slow_depth_state_bytes(io);
   MDB_REQUIRE(h, need && state && state_bytes >= need && ((uintptr_t)state & 255) == 0, MDB_E_WORKSPACE,
               "mdb_slow_depth_create: state must be >= %zu bytes and 256-byte aligned", need);
+  // the graph forks the disparity map's ADAM kernel off right after the fused kernel: that is only safe when nothing
+  // later in the loss call still writes d_disparity -- i.e. no mean-normalisation constant (added after finalize)
+  MDB_REQUIRE(h, params->normalize_disparity == 0 && params->smooth_weight_mode == 1 && !params->automasking, MDB_E_INVALID_ARG,
+              "mdb_slow_depth_create: needs normalize_disparity = 0, smooth_weight_mode = 1, automasking = 0 "
+              "(the closure of src/simple_depth.jl:25-41)");
   MDB_REQUIRE(h, !h->prof_ev, MDB_E_INVALID_ARG, "mdb_slow_depth_create: switch segment profiling off first");
   const int S = io->S, N = io->N;
   const size_t nd = (size_t)io->W * io->H * N;

@@ -52,11 +52,13 @@ struct FusedArgs {
   double rxd[MDB_MAX_SCALES], ryd[MDB_MAX_SCALES];
   const PosePrepD* ppd;         // [N][S]
   float alpha, c1, c2;
+  float abs_tie;                // d|x|/dx at +0.0: 0 (sign(0) = 0) or 1 (ForwardDiff's Dual rule)
   int automask;
   float up;                     // 1 / (W H N_global Ls)
   const ScaleStat* stats;       // [Ls][N]
   float* partials;              // [N][tiles][1 + NPOSE*S]
   float* vis;
+  signed char* dbg;             // decision dump (photo_strip.inl; DBG instantiation only)
   int tiles_x, tiles_y;
 };
 
@@ -190,4 +192,6 @@ MDB_DEV float ssim_window(float Sx, float Sy, float Sxx, float Syy, float Sxy, f
 }
 
 MDB_DEV float sgnf(float v) { return (float)((v > 0.0f) - (v < 0.0f)); }
+// pullback of abs with a configurable value at 0 (mdb_loss_params.abs_subgradient)
+MDB_DEV float sgnt(float tie, float v) { return v == 0.0f ? tie : copysignf(1.0f, v); }
 #endif

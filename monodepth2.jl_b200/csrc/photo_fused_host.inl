@@ -4,6 +4,7 @@ namespace {
 // test hooks (mdb_debug_option): process-global, read on the host only, default 0 = off
 int g_dbg_strip_segs = 0;       // force this many row segments per strip
 int g_dbg_upsample_split = 0;   // force the two-kernel V / H transpose (the W > 4096 path)
+signed char* g_dbg_decisions = nullptr;   // device buffer [Ls][N][2C+2][H][W]: run the DBG instantiation and dump into it
 
 // ---------------------------------------------------------------------------------------
 // 4. per-item finalize: fixed-order sum of the warp records (double); pose chain to rvec/tvec;
@@ -492,7 +493,8 @@ template <int C, int S>
 int32_t launch_fused(mdb_handle* h, const FusedArgs& fa, const FusedLayout& L, cudaStream_t st) {
   constexpr size_t smem = (size_t)3 * (S * (2 * C + 2) / 4) * STRIP_THREADS * sizeof(float4);
   const int blocks = (L.strip.total + STRIP_WARPS - 1) / STRIP_WARPS;
-  photo_strip_kernel<C, S><<<blocks, STRIP_THREADS, smem, st>>>(fa, L.strip);
+  if (fa.dbg) photo_strip_kernel<C, S, true><<<blocks, STRIP_THREADS, smem, st>>>(fa, L.strip);
+  else photo_strip_kernel<C, S><<<blocks, STRIP_THREADS, smem, st>>>(fa, L.strip);
   MDB_LAUNCHED(h);
   return MDB_OK;
 }
@@ -505,6 +507,7 @@ int32_t mdb_debug_option(const char* name, int64_t value) {
   if (!name) return MDB_E_INVALID_ARG;
   if (!strcmp(name, "strip_segs")) g_dbg_strip_segs = (int)value;
   else if (!strcmp(name, "upsample_split")) g_dbg_upsample_split = (int)value;
+  else if (!strcmp(name, "decision_dump")) g_dbg_decisions = (signed char*)(intptr_t)value;
   else return MDB_E_INVALID_ARG;
   return MDB_OK;
 }
@@ -581,11 +584,13 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
   fa.dd = (float)fa.dd_d;
   fa.ppd = (const PosePrepD*)(ws + L.o_ppd);
   fa.alpha = p->alpha; fa.c1 = p->ssim_c1; fa.c2 = p->ssim_c2;
+  fa.abs_tie = p->abs_subgradient ? 1.0f : 0.0f;
   const double up = 1.0 / ((double)W * H * Ng * Ls);
   fa.up = (float)up;
   fa.stats = (const ScaleStat*)(ws + L.o_stats);
   fa.partials = (float*)(ws + L.o_partials);
   fa.vis = io->vis_warp_loss;
+  fa.dbg = g_dbg_decisions;
   for (int s = 0; s < S; ++s) { fin.d_rvec[s] = io->d_rvec[s]; fin.d_tvec[s] = io->d_tvec[s]; }
   fin.Ls = Ls; fin.N = N; fin.W = W; fin.H = H; fin.normalize = p->normalize_disparity;
   fin.up = up;

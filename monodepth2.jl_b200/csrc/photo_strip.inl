@@ -101,7 +101,17 @@ struct StripGeom {
   int nstrips, nsegs, seg_rows, total;  // total = N * nsegs * nstrips * Ls warps
 };
 
-template <int C, int S>
+// Decision dump (DBG instantiation only; tests/test_gpu_forced.py): every discrete choice the pullback
+// depends on, one int8 plane each, layout [scale][item][plane][H][W] with 2 C + 2 planes:
+//   0            winner of the window centred on the pixel: source index, -1 = the automask took it
+//   1 .. C       the winner's SSIM clamp gate per channel (1: inside [0,1], gradient passes)
+//   C+1 .. 2C    sign(x - y) of the winner's sample per channel (the L1 pullback)
+//   2C+1         smoothness signs: (sign(d - d_right) + 1) + 3 (sign(d - d_down) + 1)
+// The float64 oracle can be run with these forced (oracle/c_port mdbo_set_decisions), which separates
+// arithmetic error from sub-ulp ties that legitimately fall the other way in float32.
+MDB_DEV signed char sgn_code(float v) { return v == 0.0f ? 0 : (v > 0.0f ? 1 : -1); }
+
+template <int C, int S, bool DBG = false>
 #ifdef STRIP_MAXREG
 __global__ void __maxnreg__(STRIP_MAXREG)
 #else
@@ -168,6 +178,8 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   const bool native = a.native[sc] != 0;
   const int dw = a.dw[sc], dh = a.dh[sc];
   const double ryd = a.ryd[sc];
+  signed char* dbg = nullptr;
+  if (DBG) dbg = a.dbg + ((size_t)sc * a.N + n) * (2 * C + 2) * plane;
 
   // ---- per-lane projection state: P' = A q + invd b, q = [px, py, 1], A = I + dA -------------
   // p_i = A_i . q is carried down the rows by adding column 1 of A (double: no drift that matters)
@@ -431,9 +443,12 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
         const float wxl = __shfl_sync(MDB_FULL, wxr, max(lane - 1, 0));
         if (pcol) {
           // the weights are already zero across the image border
-          const float gsx = sgn1(d2 - dr) * wxr - sgn1(dl - d2) * wxl;
-          const float gsy = sgn1(d2 - d1) * wy_dn - sgn1(d3 - d2) * wy_up;
+          // every difference is (first - second) of a pair, so an exact tie is +0.0 and takes +abs_tie
+          const float gsx = sgnt(a.abs_tie, d2 - dr) * wxr - sgnt(a.abs_tie, dl - d2) * wxl;
+          const float gsy = sgnt(a.abs_tie, d2 - d1) * wy_dn - sgnt(a.abs_tie, d3 - d2) * wy_up;
           gsm = skx * gsx + sky * gsy;
+          if (DBG) dbg[(size_t)(2 * C + 1) * plane + (size_t)pr * W + gx] =
+              (signed char)((sgn_code(d2 - dr) + 1) + 3 * (sgn_code(d2 - d1) + 1));
           smx_acc = fmaf(fabsf(d2 - dr), wxr, smx_acc);
           smy_acc = fmaf(fabsf(d2 - d1), wy_dn, smy_acc);
         }
@@ -492,6 +507,7 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
       }
       P lossv(0.0f);
       P cA[C], cB[C], cC[C];
+      P dbg_ins[DBG ? C : 1];
 #pragma unroll
       for (int c = 0; c < C; ++c) {
         const P Mx = Mxa[c], Qx = Qxa[c], Cxy = Cxya[c];
@@ -522,6 +538,7 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
           ins.set(s, fabsf(r12.get(s)) <= 1.0f ? 1.0f : 0.0f);
         }
         cA[c] = A0 * ins; cB[c] = Bb * ins; cC[c] = Cb * ins;
+        if (DBG) dbg_ins[c] = ins;
         lossv = pfma(sv, ka, pfma(ab, kl, lossv));
       }
       int best = 0;
@@ -540,6 +557,13 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
           fa = (best == s) ? cA[c].get(s) : fa; fb = (best == s) ? cB[c].get(s) : fb; fc = (best == s) ? cC[c].get(s) : fc;
         }
         Fn[3 * c] = fa; Fn[3 * c + 1] = fb; Fn[3 * c + 2] = fc;   // SEL_NONE windows are gated out by the row masks in D
+      }
+      if (DBG && pcol && wr >= Y0 && wr < Y1) {
+        const size_t o = (size_t)wr * W + gx;
+        dbg[o] = best == SEL_NONE ? (signed char)-1 : (signed char)best;
+#pragma unroll
+        for (int c = 0; c < C; ++c)
+          dbg[(size_t)(1 + c) * plane + o] = best == SEL_NONE ? (signed char)1 : (signed char)(dbg_ins[c].get(best == SEL_NONE ? 0 : best) != 0.0f);
       }
       if (pcol && wr >= Y0 && wr < Y1) {
         loss_acc += val;
@@ -582,7 +606,9 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
           const P df = x + (-y);
           P sg;
 #pragma unroll
-          for (int s = 0; s < S; ++s) sg.set(s, sgn1(df.get(s)));
+          // |target - pred| (src/training.jl:5): target - pred = +0.0 at a tie, so d/d pred = -abs_tie there
+          for (int s = 0; s < S; ++s) sg.set(s, sgnt(-a.abs_tie, df.get(s)));
+          if (DBG) dbg[(size_t)(C + 1 + c) * plane + (size_t)pr * W + gx] = sel1 == SEL_NONE ? (signed char)0 : sgn_code(df.get(sel1 == SEL_NONE ? 0 : sel1));
           sg = sg * mb;
           // d loss / d sample = ks [T_A + 2 x T_B + y T_C] + kl sign(x - y) [this window chose s]
           const P G = pfma(pfma(x * 2.0f, T[3 * c + 1], pfma(T[3 * c + 2], y, T[3 * c])), ksu, sg * klu);

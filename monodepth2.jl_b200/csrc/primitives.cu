@@ -192,7 +192,7 @@ constexpr int SM_THREADS = 256, SM_ROWS = 16, SM_ROWS_MIN = 8;   // the workspac
 template <int C>
 __global__ void __launch_bounds__(SM_THREADS)
 smooth_kernel(const float* __restrict__ disp, const float* __restrict__ img, int W, int H, int N,
-              float kx, float ky, float* __restrict__ part, float* __restrict__ grad) {
+              float kx, float ky, float tie, float* __restrict__ part, float* __restrict__ grad) {
   const int n = blockIdx.y, rb = blockIdx.x;
   const size_t plane = (size_t)W * H;
   const float* d = disp + n * plane;
@@ -220,7 +220,7 @@ smooth_kernel(const float* __restrict__ disp, const float* __restrict__ img, int
 #pragma unroll
       for (int c = 0; c < C; ++c) Iu[c] = ldg(im + c * plane + (size_t)(y0 - 1) * W + gxc);
       const float df = ldg(d + (size_t)(y0 - 1) * W + gxc) - v;
-      tup = ky * sgnf(df) * edge(Iu, I);
+      tup = ky * sgnt(tie, df) * edge(Iu, I);
     }
     for (int gy = y0; gy < y1; ++gy) {
       const bool has_dn = gy + 1 < H;
@@ -240,7 +240,7 @@ smooth_kernel(const float* __restrict__ disp, const float* __restrict__ img, int
         for (int c = 0; c < C; ++c) Ir[c] = ldg(im + c * plane + (size_t)gy * W + gx + 1);
       }
       float g = 0.0f, tr = 0.0f;
-      if (cv && has_r) { const float df = v - vr, w = edge(I, Ir); ax += fabsf(df) * w; tr = kx * sgnf(df) * w; g += tr; }
+      if (cv && has_r) { const float df = v - vr, w = edge(I, Ir); ax += fabsf(df) * w; tr = kx * sgnt(tie, df) * w; g += tr; }
       // left edge = the left lane's right edge
       float tl = __shfl_up_sync(MDB_FULL, tr, 1);
       if (lane == 0 && cv && gx > 0) {
@@ -248,12 +248,12 @@ smooth_kernel(const float* __restrict__ disp, const float* __restrict__ img, int
 #pragma unroll
         for (int c = 0; c < C; ++c) Il[c] = ldg(im + c * plane + (size_t)gy * W + gx - 1);
         const float df = ldg(d + (size_t)gy * W + gx - 1) - v;
-        tl = kx * sgnf(df) * edge(Il, I);
+        tl = kx * sgnt(tie, df) * edge(Il, I);
       }
       if (cv && gx > 0) g -= tl;
       g -= tup;
       tup = 0.0f;
-      if (cv && has_dn) { const float df = v - vd, w = edge(I, Id); ay += fabsf(df) * w; tup = ky * sgnf(df) * w; g += tup; }
+      if (cv && has_dn) { const float df = v - vd, w = edge(I, Id); ay += fabsf(df) * w; tup = ky * sgnt(tie, df) * w; g += tup; }
       if (grad && cv) grad[n * plane + (size_t)gy * W + gx] = g;
       v = vd;
 #pragma unroll
@@ -278,7 +278,7 @@ smooth_kernel(const float* __restrict__ disp, const float* __restrict__ img, int
 template <int C>
 __global__ void __launch_bounds__(SM_THREADS)
 smooth4_kernel(const float* __restrict__ disp, const float* __restrict__ img, int W, int H, int N, int rows,
-               float kx, float ky, float* __restrict__ part, float* __restrict__ grad) {
+               float kx, float ky, float tie, float* __restrict__ part, float* __restrict__ grad) {
   const int n = blockIdx.y, rb = blockIdx.x;
   const size_t plane = (size_t)W * H;
   const float* d = disp + n * plane;
@@ -312,7 +312,7 @@ smooth4_kernel(const float* __restrict__ disp, const float* __restrict__ img, in
         float e = 0.0f;
 #pragma unroll
         for (int c = 0; c < C; ++c) e += fabsf(Iu[c][j] - I[c][j]);
-        tup[j] = ky * sgnf(vu[j] - v[j]) * __expf(-e * invC);
+        tup[j] = ky * sgnt(tie, vu[j] - v[j]) * __expf(-e * invC);
       }
     }
     for (int gy = y0; gy < y1; ++gy) {
@@ -341,7 +341,7 @@ smooth4_kernel(const float* __restrict__ disp, const float* __restrict__ img, in
         const float w = __expf(-e * invC), df = v[j] - v[j + 1];
         const bool on = cv && (j < 3 || has_r);
         ax += on ? fabsf(df) * w : 0.0f;
-        tr[j] = on ? kx * sgnf(df) * w : 0.0f;
+        tr[j] = on ? kx * sgnt(tie, df) * w : 0.0f;
       }
       // left edge of column 0 = the left lane's right edge of its column 3
       float tl = __shfl_up_sync(MDB_FULL, tr[3], 1);
@@ -351,7 +351,7 @@ smooth4_kernel(const float* __restrict__ disp, const float* __restrict__ img, in
           float e = 0.0f;
 #pragma unroll
           for (int c = 0; c < C; ++c) e += fabsf(ldg(im + c * plane + (size_t)gy * W + gx - 1) - I[c][0]);
-          tl = kx * sgnf(ldg(d + (size_t)gy * W + gx - 1) - v[0]) * __expf(-e * invC);
+          tl = kx * sgnt(tie, ldg(d + (size_t)gy * W + gx - 1) - v[0]) * __expf(-e * invC);
         }
       }
       g[0] = tr[0] - tl; g[1] = tr[1] - tr[0]; g[2] = tr[2] - tr[1]; g[3] = tr[3] - tr[2];
@@ -365,7 +365,7 @@ smooth4_kernel(const float* __restrict__ disp, const float* __restrict__ img, in
           for (int c = 0; c < C; ++c) e += fabsf(I[c][j] - Id[c][j]);
           const float w = __expf(-e * invC), df = v[j] - vd[j];
           ay += fabsf(df) * w;
-          tup[j] = ky * sgnf(df) * w;
+          tup[j] = ky * sgnt(tie, df) * w;
           g[j] += tup[j];
         }
       }
@@ -551,6 +551,13 @@ size_t mdb_smooth_loss_workspace_bytes(int32_t W, int32_t H, int32_t N) {
 int32_t mdb_smooth_loss(mdb_handle* h, const float* disparity, const float* image, int32_t W, int32_t H,
                         int32_t C, int32_t N, float* loss, float* d_disparity, void* workspace,
                         size_t workspace_bytes, void* stream) {
+  return mdb_smooth_loss_ex(h, disparity, image, W, H, C, N, 0, loss, d_disparity, workspace, workspace_bytes, stream);
+}
+
+int32_t mdb_smooth_loss_ex(mdb_handle* h, const float* disparity, const float* image, int32_t W, int32_t H,
+                           int32_t C, int32_t N, int32_t abs_subgradient, float* loss, float* d_disparity,
+                           void* workspace, size_t workspace_bytes, void* stream) {
+  const float tie = abs_subgradient ? 1.0f : 0.0f;   // d|x|/dx at +0.0 (every difference here is first - second of a pair)
   MDB_REQUIRE(h, h && disparity && image && loss, MDB_E_INVALID_ARG, "mdb_smooth_loss: null argument");
   MDB_REQUIRE(h, W >= 2 && H >= 2 && C >= 1 && C <= 4 && N >= 1 && N <= 65535, MDB_E_SHAPE,
               "mdb_smooth_loss: need W,H >= 2, 1 <= C <= 4, N <= 65535");
@@ -569,10 +576,10 @@ int32_t mdb_smooth_loss(mdb_handle* h, const float* disparity, const float* imag
     rb = (H + rows - 1) / rows;
     dim3 grid4(rb, N);
     switch (C) {
-      case 1: smooth4_kernel<1><<<grid4, threads, 0, st>>>(disparity, image, W, H, N, rows, (float)kx, (float)ky, part, d_disparity); break;
-      case 2: smooth4_kernel<2><<<grid4, threads, 0, st>>>(disparity, image, W, H, N, rows, (float)kx, (float)ky, part, d_disparity); break;
-      case 3: smooth4_kernel<3><<<grid4, threads, 0, st>>>(disparity, image, W, H, N, rows, (float)kx, (float)ky, part, d_disparity); break;
-      default: smooth4_kernel<4><<<grid4, threads, 0, st>>>(disparity, image, W, H, N, rows, (float)kx, (float)ky, part, d_disparity); break;
+      case 1: smooth4_kernel<1><<<grid4, threads, 0, st>>>(disparity, image, W, H, N, rows, (float)kx, (float)ky, tie, part, d_disparity); break;
+      case 2: smooth4_kernel<2><<<grid4, threads, 0, st>>>(disparity, image, W, H, N, rows, (float)kx, (float)ky, tie, part, d_disparity); break;
+      case 3: smooth4_kernel<3><<<grid4, threads, 0, st>>>(disparity, image, W, H, N, rows, (float)kx, (float)ky, tie, part, d_disparity); break;
+      default: smooth4_kernel<4><<<grid4, threads, 0, st>>>(disparity, image, W, H, N, rows, (float)kx, (float)ky, tie, part, d_disparity); break;
     }
     MDB_LAUNCHED(h);
     smooth_finalize_kernel<<<1, 256, 0, st>>>((const float*)workspace, rb * N, kx, ky, loss);
@@ -581,10 +588,10 @@ int32_t mdb_smooth_loss(mdb_handle* h, const float* disparity, const float* imag
   }
   dim3 grid(rb, N);
   switch (C) {
-    case 1: smooth_kernel<1><<<grid, SM_THREADS, 0, st>>>(disparity, image, W, H, N, (float)kx, (float)ky, part, d_disparity); break;
-    case 2: smooth_kernel<2><<<grid, SM_THREADS, 0, st>>>(disparity, image, W, H, N, (float)kx, (float)ky, part, d_disparity); break;
-    case 3: smooth_kernel<3><<<grid, SM_THREADS, 0, st>>>(disparity, image, W, H, N, (float)kx, (float)ky, part, d_disparity); break;
-    default: smooth_kernel<4><<<grid, SM_THREADS, 0, st>>>(disparity, image, W, H, N, (float)kx, (float)ky, part, d_disparity); break;
+    case 1: smooth_kernel<1><<<grid, SM_THREADS, 0, st>>>(disparity, image, W, H, N, (float)kx, (float)ky, tie, part, d_disparity); break;
+    case 2: smooth_kernel<2><<<grid, SM_THREADS, 0, st>>>(disparity, image, W, H, N, (float)kx, (float)ky, tie, part, d_disparity); break;
+    case 3: smooth_kernel<3><<<grid, SM_THREADS, 0, st>>>(disparity, image, W, H, N, (float)kx, (float)ky, tie, part, d_disparity); break;
+    default: smooth_kernel<4><<<grid, SM_THREADS, 0, st>>>(disparity, image, W, H, N, (float)kx, (float)ky, tie, part, d_disparity); break;
   }
   MDB_LAUNCHED(h);
   smooth_finalize_kernel<<<1, 256, 0, (cudaStream_t)stream>>>((const float*)workspace, rb * N, kx, ky, loss);

@@ -24,7 +24,7 @@ class LossParams(C.Structure):
         ("alpha", C.c_float), ("ssim_c1", C.c_float), ("ssim_c2", C.c_float),
         ("automasking", C.c_int32), ("normalize_disparity", C.c_int32),
         ("smooth_weight_mode", C.c_int32), ("upsample_align_corners", C.c_int32),
-        ("n_global", C.c_int32),
+        ("n_global", C.c_int32), ("abs_subgradient", C.c_int32),
     ]
 
 
@@ -100,6 +100,7 @@ PROTOTYPES = {
     "mdb_apply_mask": (_i32, [_vp, _vp, _vp, _i64, _vp, _vp]),
     "mdb_smooth_loss_workspace_bytes": (_sz, [_i32, _i32, _i32]),
     "mdb_smooth_loss": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _sz, _vp]),
+    "mdb_smooth_loss_ex": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _sz, _vp]),
     "mdb_train_loss_workspace_bytes": (_sz, [C.POINTER(LossIO)]),
     "mdb_train_loss_fwdbwd": (_i32, [_vp, C.POINTER(LossIO), C.POINTER(LossParams), _vp, _sz, _vp]),
     "mdb_inv3x3_batched": (_i32, [_vp, _vp, _i32, _vp, _vp]),

@@ -294,16 +294,17 @@ def _apply_mask(mask: torch.Tensor, warp_loss: torch.Tensor) -> torch.Tensor:
     return out
 
 
-def smooth_loss(disparity: torch.Tensor, image: torch.Tensor, with_grad: bool = False):
+def smooth_loss(disparity: torch.Tensor, image: torch.Tensor, with_grad: bool = False, abs_subgradient: int = 0):
     """src/utils.jl:163-177.  disparity (N,H,W), image (N,C,H,W) -> 0-dim loss tensor
-    (and d loss / d disparity when `with_grad`)."""
+    (and d loss / d disparity when `with_grad`; `abs_subgradient`: see mdb_loss_params)."""
     _chk(disparity, "disparity"); _chk(image, "image")
     N, Cc, H, W = image.shape
     wsb = lib.mdb_smooth_loss_workspace_bytes(W, H, N)
     ws = torch.empty(wsb, dtype=torch.uint8, device=image.device)
     loss = torch.empty((), dtype=torch.float32, device=image.device)
     grad = torch.empty_like(disparity) if with_grad else None
-    check(handle(), lib.mdb_smooth_loss(handle(), _p(disparity), _p(image), W, H, Cc, N, _p(loss), _p(grad), _p(ws), wsb, _stream()))
+    check(handle(), lib.mdb_smooth_loss_ex(handle(), _p(disparity), _p(image), W, H, Cc, N, int(abs_subgradient), _p(loss), _p(grad),
+                                           _p(ws), wsb, _stream()))
     return (loss, grad) if with_grad else loss
 
 
@@ -328,7 +329,7 @@ class FusedLoss:
                  min_depth: float = 0.1, max_depth: float = 100.0, disparity_smoothness: float = 1e-3,
                  automasking: bool = False, normalize_disparity: bool = True, smooth_weight_mode: int = 0,
                  n_global: int = 0, alpha: float = 0.85, want_vis: bool = False, device=None,
-                 out: Optional[dict] = None):
+                 out: Optional[dict] = None, abs_subgradient: int = 0):
         """`out` (optional): caller-provided output tensors {"loss": 0-dim or 1-element, "d_disp": [...],
         "d_rvec": [...], "d_tvec": [...]} of the right shapes -- e.g. row slices of whole-batch tensors --
         instead of buffers owned by the plan."""
@@ -344,6 +345,7 @@ class FusedLoss:
         p.normalize_disparity = int(normalize_disparity)
         p.smooth_weight_mode = int(smooth_weight_mode)
         p.n_global = int(n_global)
+        p.abs_subgradient = int(abs_subgradient)
         self.params = p
         io = _lib.LossIO()
         io.W, io.H, io.C, io.L, io.N = W, H, C, L, N
@@ -462,14 +464,15 @@ def train_loss(model: Callable, x: torch.Tensor, auto_loss: Optional[torch.Tenso
 
 
 def simple_depth_plan(x: torch.Tensor, K, invK, *, target_id: int = 2, source_ids: Sequence[int] = (1, 3),
-                      min_depth: float = 0.1, max_depth: float = 100.0) -> FusedLoss:
+                      min_depth: float = 0.1, max_depth: float = 100.0, abs_subgradient: int = 0) -> FusedLoss:
     """The closure `slow_depth` differentiates (src/simple_depth.jl:25-41): one full-res scale,
     `mean(prediction_loss) + smooth_loss(disp, target)` with un-normalised disparity and
     smoothness weight 1."""
     N, L, Cc, H, W = x.shape
     return FusedLoss(W=W, H=H, C=Cc, L=L, N=N, disp_sizes=[(W, H)], scales=[1.0], target_id=target_id,
                      source_ids=source_ids, K=K, invK=invK, min_depth=min_depth, max_depth=max_depth,
-                     automasking=False, normalize_disparity=False, smooth_weight_mode=1, device=x.device)
+                     automasking=False, normalize_disparity=False, smooth_weight_mode=1, device=x.device,
+                     abs_subgradient=abs_subgradient)
 
 
 # --------------------------------------------------------------------------------------
@@ -517,14 +520,14 @@ class SlowDepth:
 
     def __init__(self, x: torch.Tensor, K, invK, *, target_id: int = 2, source_ids: Sequence[int] = (1, 3),
                  min_depth: float = 0.1, max_depth: float = 100.0, eta: float = 3e-4, max_iters: int = 500,
-                 disp0: float = 0.5, rvec0=(0.0, 0.0, 0.01)):
+                 disp0: float = 0.5, rvec0=(0.0, 0.0, 0.01), abs_subgradient: int = 0):
         _chk(x, "x")
         N, L, Cc, H, W = x.shape
         self.x = x
         dev = x.device
         f32 = dict(device=dev, dtype=torch.float32)
         self.plan = simple_depth_plan(x, K, invK, target_id=target_id, source_ids=source_ids,
-                                      min_depth=min_depth, max_depth=max_depth)
+                                      min_depth=min_depth, max_depth=max_depth, abs_subgradient=abs_subgradient)
         S = self.plan.S
         self.disp = torch.full((N, 1, H, W), float(disp0), **f32)
         self.poses = [Pose(torch.tensor([list(rvec0)] * N, **f32), torch.zeros((N, 1, 3), **f32)) for _ in range(S)]

@@ -269,7 +269,31 @@ typedef struct mdbo_desc {
   int32_t normalize;       /* 1: disparity / (mean + 1e-7)                src/training.jl:64-65 */
   int32_t smooth_mode;     /* 0: smoothness * scale[k]; 1: weight 1       src/simple_depth.jl:39 */
   int32_t n_global;        /* batch size the means divide by; 0 = N */
+  int32_t abs_subgradient; /* pullback of abs at +-0 (Zygote, unpinned): 0 = sign(0) = 0 (ChainRules' rule);
+                              1 = ForwardDiff's Dual rule, which Zygote's broadcast uses on CuArrays:
+                              abs(d) = signbit(value) ? -d : d, i.e. +1 at +0.0 and -1 at -0.0 */
 } mdbo_desc;
+
+/* Decision forcing / dumping (tests/test_gpu_forced.py).  Every discrete choice the pullback depends on, one
+ * int8 plane each, layout [scale][item][2C+2][H][W] (the CUDA kernel's DBG dump has the same layout):
+ *   0          winner of the window: source index, -1 = the automask took it
+ *   1..C       the winner's SSIM clamp gate per channel
+ *   C+1..2C    sign(pred - target) of the winner per channel (L1 pullback)
+ *   2C+1       (sign(d - d_right) + 1) + 3 (sign(d - d_down) + 1)
+ * `force`: use these instead of the oracle's own; `dump`: record the oracle's own; `margin` [scale][item][H][W]:
+ * gap between the winner and the runner-up candidate (how close the arg-min was to a tie).  Static pointers,
+ * read by the next mdbo_train_loss call: test infrastructure, not re-entrant. */
+static const int8_t* g_force = NULL;
+static int8_t* g_dump = NULL;
+static float* g_margin = NULL;
+void mdbo_set_decisions(const int8_t* force, int8_t* dump, float* margin) { g_force = force; g_dump = dump; g_margin = margin; }
+static inline int sgn_i(real v) { return (v > 0) - (v < 0); }
+/* abs pullback with the configured convention at +-0 (v is the argument of abs) */
+static inline real abs_grad(real v, int mode) {
+  if (v > 0) return 1;
+  if (v < 0) return -1;
+  return mode ? (signbit((double)v) ? (real)-1 : (real)1) : (real)0;
+}
 
 typedef struct { double R[9], t[3]; } pose_t;
 
@@ -364,6 +388,18 @@ static double item_scale(const mdbo_desc* d, int n, int k, const real* x, const 
         if (si == 0 || v < best) { best = v; bs = si; }
       }
       if (d->automask && auto_n && auto_n[p] <= best) { best = auto_n[p]; bs = -1; }
+      if (g_margin) {          /* distance of the winner to the closest other candidate */
+        real gap = (real)1e30;
+        for (int si = 0; si < S; ++si)
+          if (si != bs && s->pl[si][p] - best < gap) gap = s->pl[si][p] - best;
+        if (d->automask && auto_n && bs >= 0 && auto_n[p] - best < gap) gap = auto_n[p] - best;
+        g_margin[((size_t)k * d->N + n) * hw + p] = (float)gap;
+      }
+      if (g_dump) g_dump[((size_t)k * d->N + n) * (2 * C + 2) * hw + p] = (int8_t)bs;
+      if (g_force) {
+        bs = g_force[((size_t)k * d->N + n) * (2 * C + 2) * hw + p];
+        best = bs < 0 ? auto_n[p] : s->pl[bs][p];
+      }
       s->wl[p] = best; s->sel[p] = bs;
       lsum += best;
     }
@@ -377,16 +413,22 @@ static double item_scale(const mdbo_desc* d, int n, int k, const real* x, const 
   double sxs = 0, sys = 0;
   if (gdisp_k) memset(s->gdn, 0, hw * sizeof(real));
   const real gscale = (real)(1.0 / d->Ls);
+  const size_t dec0 = ((size_t)k * d->N + n) * (2 * C + 2) * hw;     /* this (scale, item)'s decision planes */
   for (int py = 0; py < H; ++py)
     for (int px = 0; px < W; ++px) {
       const size_t p = (size_t)py * W + px;
+      int cx_code = 1, cy_code = 1;
+      const int fcode = g_force ? g_force[dec0 + (size_t)(2 * C + 1) * hw + p] : 0;
       if (px + 1 < W) {
         real e = 0;
         for (int c = 0; c < C; ++c) e += R_ABS(tgt[(size_t)c * hw + p] - tgt[(size_t)c * hw + p + 1]);
         const real w = R_EXP(-(e / (real)C));
         const real df = s->up[p] * inv - s->up[p + 1] * inv;
         sxs += R_ABS(df) * w;
-        if (gdisp_k) { const real g = sgn(df) * w * (real)cx * gscale; s->gdn[p] += g; s->gdn[p + 1] -= g; }
+        real sg = abs_grad(df, d->abs_subgradient);
+        cx_code = sgn_i(df) + 1;
+        if (g_force) sg = (fcode % 3 - 1) != 0 ? (real)(fcode % 3 - 1) : abs_grad((real)0, d->abs_subgradient);
+        if (gdisp_k) { const real g = sg * w * (real)cx * gscale; s->gdn[p] += g; s->gdn[p + 1] -= g; }
       }
       if (py + 1 < H) {
         real e = 0;
@@ -394,8 +436,12 @@ static double item_scale(const mdbo_desc* d, int n, int k, const real* x, const 
         const real w = R_EXP(-(e / (real)C));
         const real df = s->up[p] * inv - s->up[p + W] * inv;
         sys += R_ABS(df) * w;
-        if (gdisp_k) { const real g = sgn(df) * w * (real)cy * gscale; s->gdn[p] += g; s->gdn[p + W] -= g; }
+        real sg = abs_grad(df, d->abs_subgradient);
+        cy_code = sgn_i(df) + 1;
+        if (g_force) sg = (fcode / 3 - 1) != 0 ? (real)(fcode / 3 - 1) : abs_grad((real)0, d->abs_subgradient);
+        if (gdisp_k) { const real g = sg * w * (real)cy * gscale; s->gdn[p] += g; s->gdn[p + W] -= g; }
       }
+      if (g_dump) g_dump[dec0 + (size_t)(2 * C + 1) * hw + p] = (int8_t)(cx_code + 3 * cy_code);
     }
   loss += sxs * cx + sys * cy;
   if (!gdisp_k) return loss;
@@ -408,16 +454,27 @@ static double item_scale(const mdbo_desc* d, int n, int k, const real* x, const 
     for (int px = 0; px < W; ++px) {
       const size_t p = (size_t)py * W + px;
       const int si = s->sel[p];
-      if (si < 0) continue;                                 /* the automask took this pixel */
+      if (si < 0) {                                         /* the automask took this pixel */
+        if (g_dump) for (int c = 0; c < C; ++c) { g_dump[dec0 + (size_t)(1 + c) * hw + p] = 1; g_dump[dec0 + (size_t)(C + 1 + c) * hw + p] = 0; }
+        continue;
+      }
       for (int c = 0; c < C; ++c) {
         const real* Xc = s->warped[si] + (size_t)c * hw;
         const real* Yc = tgt + (size_t)c * hw;
         real* G = s->gwarp[si] + (size_t)c * hw;
-        /* L1: d |t - w| / dw = -sign(t - w) */
-        G[p] += gmean * (1 - alpha) / (real)C * (-sgn(Yc[p] - Xc[p]));
+        /* L1: d |t - w| / dw = -abs'(t - w) */
+        real l1g = -abs_grad(Yc[p] - Xc[p], d->abs_subgradient);
+        if (g_dump) g_dump[dec0 + (size_t)(C + 1 + c) * hw + p] = (int8_t)sgn_i(Xc[p] - Yc[p]);
+        if (g_force) {
+          const int fs = g_force[dec0 + (size_t)(C + 1 + c) * hw + p];
+          l1g = fs != 0 ? (real)fs : -abs_grad((real)0, d->abs_subgradient);
+        }
+        G[p] += gmean * (1 - alpha) / (real)C * l1g;
         /* SSIM through the 9 (reflected) taps of the window */
         real st[6];
         ssim_at(Xc, Yc, W, H, px, py, c1, c2, st);
+        if (g_dump) g_dump[dec0 + (size_t)(1 + c) * hw + p] = (int8_t)(st[5] != 0);
+        if (g_force) st[5] = (real)g_force[dec0 + (size_t)(1 + c) * hw + p];
         if (st[5] == 0) continue;
         const real q = gmean * alpha / (real)C;
         for (int dy = -1; dy <= 1; ++dy) {

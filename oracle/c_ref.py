@@ -33,6 +33,7 @@ class Desc(C.Structure):
         ("min_depth", C.c_double), ("max_depth", C.c_double), ("smoothness", C.c_double),
         ("alpha", C.c_double), ("c1", C.c_double), ("c2", C.c_double),
         ("automask", C.c_int32), ("normalize", C.c_int32), ("smooth_mode", C.c_int32), ("n_global", C.c_int32),
+        ("abs_subgradient", C.c_int32),
     ]
 
 
@@ -56,6 +57,8 @@ def lib(dtype=np.float64):
         L = C.CDLL(path)
         assert L.mdbo_sizeof_real() == np.dtype(dtype).itemsize
         L.mdbo_train_loss.restype = C.c_int
+        L.mdbo_set_decisions.restype = None
+        L.mdbo_set_decisions.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         _libs[key] = L
     return _libs[key]
 
@@ -69,11 +72,16 @@ def train_loss(x: np.ndarray, disparities: Sequence[np.ndarray], rvecs: Sequence
                target_id: int = 2, source_ids: Sequence[int] = (1, 3),
                scales: Sequence[float] = (0.125, 0.25, 0.5, 1.0), min_depth: float = 0.1, max_depth: float = 100.0,
                smoothness: float = 1e-3, alpha: float = 0.85, automasking: bool = True, normalize: bool = True,
-               smooth_mode: int = 0, n_global: int = 0, grad: bool = True, dtype=np.float64, threads: int = 1):
+               smooth_mode: int = 0, n_global: int = 0, grad: bool = True, dtype=np.float64, threads: int = 1,
+               abs_subgradient: int = 0, force_decisions: Optional[np.ndarray] = None, dump_decisions: bool = False):
     """Value and gradients of ``train_loss`` (or of the slow_depth closure with ``normalize=False,
     smooth_mode=1`` and one scale).  Arrays are in the repo's reversed-dims convention:
     x (N,L,C,H,W), disparities[k] (N,1,h,w), rvecs[s] (N,3), tvecs[s] (N,1,3) or (N,3), auto_loss
-    (N,1,H,W) or None, K / invK the 9 numbers Julia stores."""
+    (N,1,H,W) or None, K / invK the 9 numbers Julia stores.
+    abs_subgradient: pullback of abs at +-0 (0: sign(0) = 0; 1: ForwardDiff's rule, +1 at +0.0).
+    force_decisions: int8 (Ls,N,2C+2,H,W) -- every discrete choice of the pullback (layout in mdb_oracle.c) taken
+    from this array instead of the oracle's own arithmetic; dump_decisions: also return the oracle's own choices
+    (`decisions`) and the arg-min margins (`margin` (Ls,N,H,W))."""
     L = lib(dtype)
     x = np.ascontiguousarray(x, dtype=dtype)
     N, Lf, Cc, H, W = x.shape
@@ -89,6 +97,7 @@ def train_loss(x: np.ndarray, disparities: Sequence[np.ndarray], rvecs: Sequence
     d.min_depth, d.max_depth, d.smoothness, d.alpha = min_depth, max_depth, smoothness, alpha
     d.c1, d.c2 = 0.01 ** 2, 0.03 ** 2                       # src/utils.jl:23
     d.automask, d.normalize, d.smooth_mode, d.n_global = int(automasking), int(normalize), smooth_mode, n_global
+    d.abs_subgradient = int(abs_subgradient)
     rv = np.ascontiguousarray(np.stack([np.asarray(r, dtype=dtype).reshape(N, 3) for r in rvecs]))
     tv = np.ascontiguousarray(np.stack([np.asarray(t, dtype=dtype).reshape(N, 3) for t in tvecs]))
     au = None if (auto_loss is None or not automasking) else np.ascontiguousarray(auto_loss, dtype=dtype)
@@ -102,11 +111,23 @@ def train_loss(x: np.ndarray, disparities: Sequence[np.ndarray], rvecs: Sequence
         g_rv, g_tv = np.zeros_like(rv), np.zeros_like(tv)
     else:
         g_disp, g_ptrs, g_rv, g_tv = None, None, None, None
-    rc = L.mdbo_train_loss(C.byref(d), _ptr(x), _ptr(rv), _ptr(tv), disp_ptrs, _ptr(au), _ptr(Kc), _ptr(iKc),
-                           C.byref(loss), g_ptrs, _ptr(g_rv), _ptr(g_tv), C.c_int(threads))
+    force = None
+    if force_decisions is not None:
+        force = np.ascontiguousarray(force_decisions, dtype=np.int8)
+        assert force.shape == (Ls, N, 2 * Cc + 2, H, W), force.shape
+    dump = np.zeros((Ls, N, 2 * Cc + 2, H, W), dtype=np.int8) if dump_decisions else None
+    margin = np.zeros((Ls, N, H, W), dtype=np.float32) if dump_decisions else None
+    L.mdbo_set_decisions(_ptr(force), _ptr(dump), _ptr(margin))
+    try:
+        rc = L.mdbo_train_loss(C.byref(d), _ptr(x), _ptr(rv), _ptr(tv), disp_ptrs, _ptr(au), _ptr(Kc), _ptr(iKc),
+                               C.byref(loss), g_ptrs, _ptr(g_rv), _ptr(g_tv), C.c_int(threads))
+    finally:
+        L.mdbo_set_decisions(None, None, None)
     if rc != 0:
         raise RuntimeError(f"mdbo_train_loss failed ({rc})")
     out = dict(loss=loss.value)
+    if dump_decisions:
+        out.update(decisions=dump, margin=margin)
     if grad:
         out.update(d_disp=g_disp, d_rvec=[g_rv[s] for s in range(S)], d_tvec=[g_tv[s] for s in range(S)])
     return out

@@ -47,6 +47,31 @@ import torch.nn.functional as F
 
 DT = torch.float64
 
+# Pullback of `abs` at +-0 (Zygote, unpinned).  0: sign(0) = 0 (ChainRules' scalar rule).  1: ForwardDiff's
+# Dual rule -- what Zygote's broadcast differentiates `abs.(...)` with on CuArrays: abs(d) = signbit(value) ? -d : d,
+# i.e. +1 at +0.0 and -1 at -0.0.  Not measure-zero for `slow_depth`: disp starts as fill(0.5), so every
+# smoothness difference of iteration 1 is exactly +0.0 (src/simple_depth.jl:8,39).
+ABS_SUBGRADIENT = 0
+
+
+class _Abs(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        ctx.save_for_backward(x)
+        return x.abs()
+
+    @staticmethod
+    def backward(ctx, g):
+        (x,) = ctx.saved_tensors
+        s = torch.sign(x)
+        if ABS_SUBGRADIENT:
+            s = torch.where(x == 0, torch.where(torch.signbit(x), -torch.ones_like(x), torch.ones_like(x)), s)
+        return g * s
+
+
+def _abs(x: torch.Tensor) -> torch.Tensor:
+    return _Abs.apply(x)
+
 
 # --------------------------------------------------------------------------------------
 # helpers for the reversed-dims convention
@@ -208,7 +233,7 @@ def ssim(x: torch.Tensor, y: torch.Tensor, c1: float = 0.01 ** 2, c2: float = 0.
 
 def photometric_loss(pred: torch.Tensor, target: torch.Tensor, alpha: float = 0.85):
     """src/training.jl:1-7 -> (N,1,H,W)."""
-    l1 = (target - pred).abs().mean(dim=1, keepdim=True)
+    l1 = _abs(target - pred).mean(dim=1, keepdim=True)
     s = ssim(pred, target).mean(dim=1, keepdim=True)
     return alpha * s + (1.0 - alpha) * l1
 
@@ -237,8 +262,8 @@ def apply_mask(mask: torch.Tensor, warp_loss: torch.Tensor):
 
 def smooth_loss(disparity: torch.Tensor, image: torch.Tensor):
     """src/utils.jl:163-177.  disparity (N,H,W) [Julia (W,H,N)], image (N,C,H,W)."""
-    ddx = (disparity[:, :, :-1] - disparity[:, :, 1:]).abs()
-    ddy = (disparity[:, :-1, :] - disparity[:, 1:, :]).abs()
+    ddx = _abs(disparity[:, :, :-1] - disparity[:, :, 1:])
+    ddy = _abs(disparity[:, :-1, :] - disparity[:, 1:, :])
     dix = (image[:, :, :, :-1] - image[:, :, :, 1:]).abs().mean(dim=1)
     diy = (image[:, :, :-1, :] - image[:, :, 1:, :]).abs().mean(dim=1)
     return (ddx * torch.exp(-dix)).mean() + (ddy * torch.exp(-diy)).mean()

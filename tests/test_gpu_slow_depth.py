@@ -159,3 +159,71 @@ def test_error_codes_of_the_new_entry_points():
     assert lib.mdb_ingest_triplet_u8(h, x.data_ptr(), None, 0, 4, 1, 0, x.data_ptr(), None) == -2
     with pytest.raises(ValueError):
         mdb200.ingest_triplet_u8(torch.zeros(1, 4, 12, 3, device=DEV), 4)       # float strips: rejected by the glue
+
+
+def test_slow_depth_500_iterations_vs_oracle():
+    """BASELINE config 1 as the reference runs it (src/simple_depth.jl:22: 500 iterations of ADAM(3e-4) from
+    disp = 0.5, rvec = [0,0,0.01], tvec = 0) against the float64 oracle loop: the loss history, the final loss and the
+    final mean disparity.  The trajectories are not comparable entry by entry (ADAM's sign steps amplify float32 noise
+    of near-zero gradients), the functionals are: tolerances stated below."""
+    import mdb200
+    from mdb200 import synth
+    from oracle import torch_ref as T
+    inp = synth.make_config("config1")
+    iters = 500
+    x64 = torch.tensor(inp.x, dtype=torch.float64)
+    K64, iK64 = torch.tensor(inp.K, dtype=torch.float64), torch.tensor(inp.invK, dtype=torch.float64)
+    disp_ref, poses_ref, hist_ref = T.slow_depth(x64, K64, iK64, iters=iters)
+    sd = mdb200.SlowDepth(torch.tensor(inp.x, device=DEV), inp.K, inp.invK, max_iters=iters)
+    sd.run(iters)
+    torch.cuda.synchronize()
+    hist = sd.loss_history.cpu().double().numpy()
+    href = np.array(hist_ref)
+    rel = np.abs(hist - href) / href
+    print(f"slow_depth 500: loss {hist[0]:.6f} -> {hist[-1]:.6f} (oracle {href[0]:.6f} -> {href[-1]:.6f}), "
+          f"max rel dev of the history {rel.max():.2e}, final {rel[-1]:.2e}; mean disp {float(sd.disp.mean()):.6f} "
+          f"(oracle {float(disp_ref.mean()):.6f})")
+    assert rel[-1] < 2e-2, rel[-1]                         # final loss
+    assert rel.max() < 5e-2, rel.max()                     # whole history
+    assert hist[-1] < 0.2 * hist[0]                        # the loop optimises (0.1987 -> ~0.018)
+    assert abs(float(sd.disp.mean()) - float(disp_ref.mean())) < 1e-3 * float(disp_ref.mean())
+    for pg, pr in zip(sd.poses, poses_ref):
+        assert (pg.tvec.double().cpu() - pr.tvec).abs().max() < 0.05 * pr.tvec.abs().max()
+    sd.close()
+
+
+def test_slow_depth_create_rejects_unsafe_params():
+    """The graph forks the disparity's ADAM kernel off after the fused kernel, which is only safe without the
+    mean-normalisation constant (added to d_disparity later): mdb_slow_depth_create refuses anything else."""
+    import ctypes as ct
+    import mdb200
+    from mdb200 import synth, _lib
+    inp = synth.make_loss_inputs(64, 24, 1, seed=41, scales=(1.0,))
+    sd = mdb200.SlowDepth(torch.tensor(inp.x, device=DEV), inp.K, inp.invK, max_iters=2)
+    sd.plan.params.normalize_disparity = 1
+    h2 = ct.c_void_p()
+    rc = _lib.lib.mdb_slow_depth_create(mdb200.handle(), ct.byref(sd.plan.io), ct.byref(sd.plan.params), ct.byref(sd.adam),
+                                        ct.c_void_p(sd.state.data_ptr()), sd.state.numel(), ct.c_void_p(sd.plan.ws.data_ptr()),
+                                        sd.plan.ws_bytes, ct.c_void_p(sd.loss_history.data_ptr()), 2, ct.byref(h2))
+    assert rc == -1 and b"normalize_disparity" in _lib.lib.mdb_last_error(mdb200.handle())
+    sd.close()
+
+
+def test_slow_depth_batch_of_two():
+    """N > 1 takes finalize_item_kernel's done-counter branch (last CTA sums the items, advances the ADAM step):
+    two copies of the same triplet must follow the single-item trajectory, with the loss the mean over the batch."""
+    import mdb200
+    from mdb200 import synth
+    inp = synth.make_loss_inputs(64, 24, 1, seed=41, scales=(1.0,))
+    x1 = torch.tensor(inp.x, device=DEV)
+    x2 = torch.cat([x1, x1], 0).contiguous()
+    a = mdb200.SlowDepth(x1, inp.K, inp.invK, max_iters=6)
+    b = mdb200.SlowDepth(x2, inp.K, inp.invK, max_iters=6)
+    a.run(6); b.run(6)
+    torch.cuda.synchronize()
+    ha, hb = a.loss_history.cpu().numpy(), b.loss_history.cpu().numpy()
+    assert np.allclose(ha, hb, rtol=2e-5), (ha, hb)
+    for n in range(2):
+        assert (b.disp[n] - a.disp[0]).abs().max() <= 2.5 * 6 * ETA      # ADAM's +-eta random walk where g ~ 0
+        assert (b.disp[n] - a.disp[0]).abs().mean() < 0.05 * 6 * ETA
+    a.close(); b.close()
