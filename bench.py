@@ -279,7 +279,8 @@ def run_ours(args):
     # place (mdb_packed_bind); one out-of-place all-reduce per step
     pg = mdist.PackedGrads(Ng, S, first, N, dev)
     plan = mdb200.FusedLoss(N=N, n_global=Ng, device=dev, out=pg.out(), **common)
-    transport = mdist.init_comm(dev, pg.send.numel(), args.transport) if world > 1 else "none"
+    # the peer buffers are sized for the larger of the two packed vectors this run reduces (weak_aux: 64 items per rank)
+    transport = mdist.init_comm(dev, mdist.packed_size(NB * world, S), args.transport) if world > 1 else "none"
 
     def step():
         res = plan(x, disps, poses, auto)

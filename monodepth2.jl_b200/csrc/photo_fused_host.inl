@@ -1,4 +1,5 @@
 // photo_fused_host.inl -- finalize kernels, up-sample transpose and the C-ABI entry of the fused loss
+#include <cmath>
 namespace {
 
 // test hooks (mdb_debug_option): process-global, read on the host only, default 0 = off
@@ -433,24 +434,36 @@ struct FusedLayout {
   int records;       // partial-sum records per item = warps per item
 };
 
-// Rows per segment: long segments amortise the 4 halo rows, short ones give the machine enough
-// warps.  Aim for ~16 resident sets of 16 warps per SM, never below 32 rows -- unless the whole
-// problem cannot fill the machine once even then (config 1: 15 strips): a lone warp is latency
-// bound, so the step time is (rows per segment + 4 halo rows) x the row latency, and segments
-// shrink (down to 4 rows) until one wave of 13 warps per SM is resident.
+// Rows per segment.  Every warp costs (rows + 4 halo rows) row-times, and the launch runs in w = warps / resident
+// waves of 13 warps per SM.  Measured at 1024x320 for 8 / 16 / 32 / 64 items and 1 .. 20 segments (tools/sweep_segs.py,
+// profiles/r2_strip_summary.md): below ~3 waves the waves are what the clock sees, time = ceil(w) x (rows + 4) -- a
+// 1.2-wave launch is as slow as a 2-wave one; above it the block scheduler smooths them out and what is left is the
+// tail, about half a segment: time = (w + 0.5) x (rows + 4).  The segment count minimising that model is within 0.3 %
+// of the measured best at all four batch sizes (3 / 5 / 4 / 3 segments), where the old "16 resident sets" rule lost
+// 1.5 - 2.5 % below batch 64.  Segments never go below 8 rows unless one wave cannot be filled otherwise (config 1).
 inline StripGeom strip_geom(const mdb_loss_io* io, int num_sms) {
   StripGeom g{};
   g.nstrips = (io->W + STRIP_PX - 1) / STRIP_PX;
   const int sms = num_sms > 0 ? num_sms : 148;
   const long long base = (long long)io->N * io->Ls * g.nstrips;
-  long long want = ((long long)16 * 16 * sms + base - 1) / base;
-  int max_segs = std::max(1, io->H / 32);
-  const long long one_wave = (long long)13 * sms;
-  if (base * max_segs < one_wave)
-    max_segs = (int)std::max<long long>(max_segs, std::min<long long>(io->H / 4, (one_wave + base - 1) / base));
-  if (g_dbg_strip_segs > 0) { want = g_dbg_strip_segs; max_segs = std::max(1, io->H / 2); }
-  g.nsegs = (int)std::min<long long>(std::max<long long>(want, 1), max_segs);
-  g.seg_rows = (io->H + g.nsegs - 1) / g.nsegs;
+  const double resident = 13.0 * sms;
+  int best_n = 1;
+  if (g_dbg_strip_segs > 0) {
+    best_n = std::min(g_dbg_strip_segs, std::max(1, io->H / 2));
+  } else {
+    double best_cost = 1e300;
+    const int n_max = std::max(1, io->H / 4);
+    for (int n = 1; n <= n_max; ++n) {
+      const int rows = (io->H + n - 1) / n;
+      const int ne = (io->H + rows - 1) / rows;          // segments this row count really gives
+      if (ne != n) continue;
+      const double w = (double)(base * ne) / resident;
+      if (rows < 8 && w > 1.0) break;                      // 4-row segments only to fill the first wave
+      const double cost = (w >= 3.0 ? w + 0.5 : std::ceil(w)) * (rows + 4);
+      if (cost < best_cost * 0.999) { best_cost = cost; best_n = n; }   // ties: fewer, longer segments
+    }
+  }
+  g.seg_rows = (io->H + best_n - 1) / best_n;
   g.nsegs = (io->H + g.seg_rows - 1) / g.seg_rows;
   g.total = (int)(base * g.nsegs);
   return g;

@@ -7,7 +7,7 @@ fn = None; rows = []
 for line in sass.splitlines():
     if 'Function :' in line:
         fn = line.split(':', 1)[1].strip(); continue
-    if fn and 'photo_strip_kernelILi3ELi2' in fn:
+    if fn and 'photo_strip_kernelILi3ELi2ELb0' in fn:
         m = re.match(r'\s+/\*([0-9a-f]{4,})\*/\s+(.*?);', line)
         if m: rows.append((int(m.group(1), 16), m.group(2).strip()))
 back = [(a, int(re.search(r'0x([0-9a-f]+)', t).group(1), 16)) for a, t in rows if t.split()[0].startswith(('BRA', '@')) and 'BRA' in t and re.search(r'0x([0-9a-f]+)', t) and int(re.search(r'0x([0-9a-f]+)', t).group(1), 16) < a]
@@ -19,4 +19,4 @@ h = collections.Counter(re.sub(r'^@!?U?P\d+\s+', '', t).split()[0].split('.')[0]
 print(' '.join(f'{k}:{v}' for k, v in h.most_common(28)))
 res = subprocess.run(['cuobjdump', '-res-usage', obj], capture_output=True, text=True).stdout.splitlines()
 for i, l in enumerate(res):
-    if 'photo_strip_kernelILi3ELi2' in l: print(res[i + 1].strip())
+    if 'photo_strip_kernelILi3ELi2ELb0' in l: print(res[i + 1].strip())
