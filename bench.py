@@ -63,6 +63,7 @@ def parse():
                     help="the all-reduce of [loss, pose grads]: the library's one-shot peer-write kernel, ncclAllReduce "
                          "through the C ABI, or torch.distributed")
     ap.add_argument("--no-weak-aux", action="store_true")
+    ap.add_argument("--no-aux-configs", action="store_true", help="skip the compact records of configs 1-4 (N = 1 only)")
     ap.add_argument("--e2e-chunk", type=int, default=0, help="items per pipeline chunk of the host-buffer call (0 = HostLoss.default_chunk: N/8, at least ~16 MB)")
     return ap.parse_args()
 
@@ -282,9 +283,15 @@ def run_ours(args):
     # the peer buffers are sized for the larger of the two packed vectors this run reduces (weak_aux: 64 items per rank)
     transport = mdist.init_comm(dev, mdist.packed_size(NB * world, S), args.transport) if world > 1 else "none"
 
+    mid_events = []     # per step: recorded between the loss kernels and the all-reduce (what part of a step is exchange + waiting for the slowest rank)
+
     def step():
         res = plan(x, disps, poses, auto)
         if world > 1:
+            if mid_events is not None and len(mid_events) < 4096:
+                ev = torch.cuda.Event(enable_timing=True)
+                ev.record()
+                mid_events.append(ev)
             mdist.allreduce(pg)
         return res
 
@@ -344,6 +351,7 @@ def run_ours(args):
         evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
         sampler.start()
         sync_all()
+        del mid_events[:]
         t0 = time.perf_counter()
         for e0, e1 in evs:
             if flush is not None:
@@ -363,10 +371,20 @@ def run_ours(args):
         if profile:
             seg = np.array([mdb200.profile_read(i) for i in range(steps)])  # [steps][4] ms
             mdb200.profile_begin(0)
+        timed.split = None
+        if world > 1 and len(mid_events) == steps:
+            comp = sum(e0.elapsed_time(m) for (e0, _), m in zip(evs, mid_events)) / steps
+            exch = sum(m.elapsed_time(e1) for (_, e1), m in zip(evs, mid_events)) / steps
+            both = torch.tensor([comp, exch], device=dev, dtype=torch.float64)
+            allr = [torch.zeros_like(both) for _ in range(world)]
+            dist.all_gather(allr, both)
+            timed.split = {"loss_kernels_ms_per_rank": [float(t[0]) for t in allr],
+                           "allreduce_incl_wait_for_slowest_rank_ms_per_rank": [float(t[1]) for t in allr]}
         return float(ms), clocks, launches, seg, r, wall
 
     warm = max(args.warmup, 3)
     ms_total, clocks, launches, seg, res, wall = timed(step, args.steps, warm, profile=True)
+    step_split = timed.split
     loss_val = float(pg.recv[0]) if world > 1 else float(res.loss)
 
     # ---- weak_aux: 64 items per GPU (round 1's line), same kernels, global batch 64 x world -------------------
@@ -464,19 +482,25 @@ def run_ours(args):
             "clocks": clocks,
             "e2e": e2e,
             "gpu_launches": int(launches),
-            "roofline": roofline_block(args, inp, N, seg, dev),
+            "roofline": roofline_block(args, inp, N, seg, plan),
         }
+        if step_split is not None:
+            line["step_split"] = step_split
         if shard_parity is not None:
             line["shard_parity"] = shard_parity["ok"]
             line["shard_parity_detail"] = shard_parity
         if weak_aux is not None:
             line["weak_aux"] = weak_aux
         if not args.no_cpu_baseline and world == 1:
-            rate, cores, t, items = cpu_reference_rate(inp, args.cpu_sample_items, 3, 1)
+            rate, cores, t, items = cpu_reference_rate(inp, args.cpu_sample_items, 10, 2)
             line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
                                     "one_thread_value": cpu_reference_rate.one_thread,
-                                    "sample": f"{items} of the batch's {NB} items, 3 steps after 1 warm-up, plain-C float32 port "
+                                    "sample": f"{items} of the batch's {NB} items, 10 steps after 2 warm-up, plain-C float32 port "
                                               f"(oracle/c_port), one item per thread, {cores} threads ({t:.2f} s/step)"}
+        if world == 1 and not args.no_aux_configs and args.config == "config5" and not args.batch:
+            del plan, x, disps
+            torch.cuda.empty_cache()
+            line["aux_configs"] = aux_configs(args)
         print(json.dumps(line), flush=True)
     if world > 1:
         sync_all()
@@ -484,21 +508,74 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
-def roofline_block(args, inp, N, seg, dev):
-    """The dominant kernel (photo_strip_kernel) of THIS rank's launch: CUDA events recorded inside the C-ABI call
-    (mdb_profile_*) on the launching stream."""
+def _blob_hash(rel):
+    import hashlib
+    d = open(os.path.join(ROOT, rel), "rb").read()
+    return hashlib.sha1(b"blob %d\0" % len(d) + d).hexdigest()
+
+
+def _profile_record(name):
+    """A record under profiles/ (SASS histogram, ncu DRAM traffic) counts only for the kernel source it was captured
+    on: every record carries the git blob hash of the files it depends on; a stale record reads as None."""
+    path = os.path.join(ROOT, "profiles", name)
+    try:
+        rec = json.load(open(path))
+        for rel, want in rec["source_hash"].items():
+            if _blob_hash(rel) != want:
+                return None
+        return rec
+    except Exception:
+        return None
+
+
+def roofline_block(args, inp, N, seg, plan):
+    """The dominant kernel (photo_strip_kernel) of THIS rank's launch: timed live with CUDA events recorded inside the
+    C-ABI call (mdb_profile_*) on the launching stream.  The fused loss is bound by FP32 issue, not by HBM (SURVEY
+    F10, 8d "Honest roofline"): T_roof = max(B_alg / BW_hbm, F_alg / P_fp32) with P_fp32 MEASURED in this run
+    (mdb_measure_fp32_peak) and F_alg counted from the committed SASS histogram of the row loop."""
+    import mdb200
     peak, peak_src = load_peaks()
+    S, Ls = len(inp.source_ids), len(inp.disparities)
+    units = N * Ls * S * inp.W * inp.H
     b_alg = algorithmic_bytes(inp, N)
     k_ms = float(seg[:, 1].mean())
-    achieved = b_alg / (k_ms * 1e-3) / 1e9
-    return {"bound": "hbm", "kernel": "photo_strip_kernel<3,2>", "achieved": achieved, "peak": peak,
-            "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-            "algorithmic_bytes_per_launch": b_alg, "kernel_ms": k_ms,
-            "segments_ms": {"prep_stats": float(seg[:, 0].mean()), "fused": k_ms,
-                            "finalize": float(seg[:, 2].mean()), "upsample_bwd": float(seg[:, 3].mean())}}
+    hbm_gbs = b_alg / (k_ms * 1e-3) / 1e9
+    p_fp32, p_ms = mdb200.measure_fp32_peak(5)
+    geo = plan.strip_geometry()
+    sass = _profile_record("r2_strip_sass.json")
+    ncu = _profile_record("r2_strip_ncu.json")
+    traffic = None
+    if ncu is not None and ncu.get("config") == args.config and ncu.get("items") == N:
+        traffic = ncu["dram_bytes_read"] + ncu["dram_bytes_write"]
+    blk = {"kernel": "photo_strip_kernel<3,2>", "kernel_ms": k_ms, "traffic": traffic,
+           "segments_ms": {"prep_stats": float(seg[:, 0].mean()), "fused": k_ms,
+                           "finalize": float(seg[:, 2].mean()), "upsample_bwd": float(seg[:, 3].mean())},
+           "strip_geometry": geo,
+           "hbm": {"achieved": hbm_gbs, "peak": peak, "unit": "GB/s", "frac": hbm_gbs / peak, "peak_source": peak_src,
+                   "algorithmic_bytes_per_launch": b_alg, "T_mem_ms": b_alg / (peak * 1e9) * 1e3},
+           "P_fp32_tflops": p_fp32, "P_fp32_source": f"measured in this run: independent FFMA chains on every SM, best of 5 ({p_ms:.3f} ms)"}
+    t_mem = b_alg / (peak * 1e9) * 1e3
+    if sass is not None:
+        # executed fp32 flops per warped pixel: per lane and row from the SASS histogram, 32 lanes per 28-pixel strip
+        # (ragged last strip included), rows + 4 halo rows per segment, two sources per lane
+        lanes_per_px = 32.0 * geo["strips"] / inp.W
+        rows_f = (geo["rows_per_segment"] + 4.0) / geo["rows_per_segment"]
+        f_wpx = sass["fp32_flops_per_lane_row"] * lanes_per_px * rows_f / S
+        t_fp32 = units * f_wpx / (p_fp32 * 1e12) * 1e3
+        t_roof = max(t_mem, t_fp32)
+        blk.update({"bound": "fp32" if t_fp32 >= t_mem else "hbm", "F_alg_flop_per_warped_px": f_wpx,
+                    "F_alg_source": "profiles/r2_strip_sass.json (static SASS histogram of the row loop, source hash checked): "
+                                    f"{sass['fp32_flops_per_lane_row']} flop per lane and row x {lanes_per_px:.3f} lanes per pixel "
+                                    f"x {rows_f:.3f} (halo rows) / {S} sources",
+                    "T_fp32_ms": t_fp32, "T_mem_ms": t_mem,
+                    "achieved": units * f_wpx / (k_ms * 1e-3) / 1e12, "peak": p_fp32, "unit": "TFLOP/s", "frac": t_roof / k_ms})
+    else:   # the kernel source changed since the SASS record was made: no flop count to stand on
+        blk.update({"bound": "hbm", "achieved": hbm_gbs, "peak": peak, "unit": "GB/s", "frac": hbm_gbs / peak,
+                    "F_alg_flop_per_warped_px": None, "note": "profiles/r2_strip_sass.json is stale for this kernel source"})
+    return blk
 
 
-def run_render(args):
+def run_render(args, emit=True):
     """BASELINE config 4: render_tgt_rgb_depth forward + backward (src/render.jl:92-114), 32 planes at
     416x128.  Not the headline line (bench.py's default stays config 5); prints its own JSON line with
     the HBM roofline of the two render kernels.  The working set (110 MB at B=2) fits L2, so a buffer
@@ -583,10 +660,12 @@ def run_render(args):
                                 "sample": f"the whole config (B={B}), 3 calls after 1 warm-up of the plain-C float32 port "
                                           f"(oracle/c_port: forward + hand-written pullback, rows / planes over {cores} threads, "
                                           f"{t_cpu * 1e3:.0f} ms per call)"}
-    print(json.dumps(line), flush=True)
+    if emit:
+        print(json.dumps(line), flush=True)
+    return line
 
 
-def run_slow_depth(args):
+def run_slow_depth(args, emit=True):
     """BASELINE config 1: the `slow_depth` loop (src/simple_depth.jl:1-62) at 416x128, one triplet:
     500 iterations of {loss fwd+bwd, ADAM(3e-4)} replayed from one CUDA graph.  Prints its own JSON line
     (not the headline; the default stays config 5).  Compared with (a) the same kernels launched one by
@@ -654,7 +733,85 @@ def run_slow_depth(args):
         line["cpu_baseline"] = {"value": 1.0 / t_cpu, "unit": "iter/s", "cores": 1, "kind": "port",
                                 "sample": f"{n_cpu} loss+gradient evaluations of the plain-C float32 port on one core "
                                           f"({t_cpu * 1e3:.1f} ms each; one item cannot be spread over threads)"}
-    print(json.dumps(line), flush=True)
+    if emit:
+        print(json.dumps(line), flush=True)
+    return line
+
+
+def run_loss_aux(name, steps=20, warmup=5, cpu=True):
+    """One of the other loss configurations of BASELINE.json (config 2: 416x128 batch 12; config 3: 640x192 batch 32
+    with automasking) on one GPU, device-resident, L2 flushed between the timed steps: a compact record for the
+    `aux_configs` key of the headline line."""
+    import numpy as np
+    import torch
+    import mdb200
+    synth = load_synth()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    inp = synth.make_config(name)
+    N, W, H = inp.N, inp.W, inp.H
+    S, Ls = len(inp.source_ids), len(inp.disparities)
+    x = torch.from_numpy(inp.x).to(dev)
+    disps = [torch.from_numpy(d).to(dev) for d in inp.disparities]
+    poses = [mdb200.Pose(torch.from_numpy(r).to(dev), torch.from_numpy(t).to(dev)) for r, t in zip(inp.rvecs, inp.tvecs)]
+    auto = mdb200.automasking_loss(mdb200.SSIM(), x, x[:, inp.target_id - 1], source_ids=inp.source_ids) if inp.automasking else None
+    plan = mdb200.FusedLoss(W=W, H=H, C=inp.C, L=3, N=N, disp_sizes=[(d.shape[-1], d.shape[-2]) for d in disps], scales=inp.scales,
+                            target_id=inp.target_id, source_ids=inp.source_ids, K=inp.K, invK=inp.invK, automasking=inp.automasking,
+                            device=dev)
+    flush = torch.empty(2 * torch.cuda.get_device_properties(dev).L2_cache_size, dtype=torch.uint8, device=dev)
+    for _ in range(warmup):
+        plan(x, disps, poses, auto)
+    mdb200.profile_begin(steps)
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    torch.cuda.synchronize()
+    for e0, e1 in evs:
+        flush.zero_()
+        e0.record()
+        res = plan(x, disps, poses, auto)
+        e1.record()
+    torch.cuda.synchronize()
+    ms = sum(e0.elapsed_time(e1) for e0, e1 in evs) / steps
+    k_ms = float(np.mean([mdb200.profile_read(i)[1] for i in range(steps)]))
+    mdb200.profile_begin(0)
+    units = N * Ls * S * W * H
+    peak, _ = load_peaks()
+    b_alg = algorithmic_bytes(inp, N)
+    rec = {"workload": f"{name}: {W}x{H} batch {N}, {Ls} scales, {S} sources{', automask' if inp.automasking else ''}, fwd+bwd",
+           "ms_per_step": ms, "value": units / (ms * 1e-3), "unit": UNIT, "fused_kernel_ms": k_ms, "loss": float(res.loss),
+           "hbm_frac_of_step": b_alg / (ms * 1e-3) / 1e9 / peak, "algorithmic_bytes": b_alg, "l2": "flushed between steps"}
+    if cpu:
+        auto_np = auto.cpu().numpy() if auto is not None else None
+        from oracle import c_ref
+        cores = os.cpu_count() or 1
+        a = (inp.x, inp.disparities, inp.rvecs, inp.tvecs, auto_np, inp.K, inp.invK)
+        kw = dict(target_id=inp.target_id, source_ids=inp.source_ids, scales=inp.scales, automasking=inp.automasking,
+                  dtype=np.float32, threads=min(cores, N))
+        c_ref.train_loss(*a, **kw)
+        t0 = time.perf_counter()
+        for _ in range(3):
+            c_ref.train_loss(*a, **kw)
+        t = (time.perf_counter() - t0) / 3
+        rec["cpu_port"] = {"value": units / t, "unit": UNIT, "cores": min(cores, N), "ms_per_step": t * 1e3,
+                           "sample": "the whole batch, 3 steps after 1 warm-up, plain-C float32 port (oracle/c_port)"}
+    return rec
+
+
+def aux_configs(args):
+    """Configs 1-4 of BASELINE.json beside the headline (config 5), so that the driver's record carries them."""
+    import argparse as ap
+    a2 = ap.Namespace(**vars(args))
+    a2.steps, a2.warmup = min(args.steps, 10), 3
+    out = {}
+    c1 = run_slow_depth(a2, emit=False)
+    out["config1"] = {k: c1[k] for k in ("metric", "value", "unit", "ms_per_step", "us_per_iteration", "warped_px_per_s",
+                                         "eager_us_per_iteration", "loss_first_last", "cpu_baseline") if k in c1}
+    out["config1"]["workload"] = c1["config"]["workload"]
+    out["config2"] = run_loss_aux("config2", cpu=not args.no_cpu_baseline)
+    out["config3"] = run_loss_aux("config3", cpu=not args.no_cpu_baseline)
+    c4 = run_render(a2, emit=False)
+    out["config4"] = {"workload": c4["config"]["workload"], "metric": c4["metric"], "value": c4["value"], "unit": c4["unit"],
+                      "ms_per_step": c4["ms_per_step"], "fwd": c4["roofline"]["fwd"], "bwd": c4["roofline"]["bwd"],
+                      "variants": c4["variants"], "cpu_baseline": c4.get("cpu_baseline")}
+    return out
 
 
 if __name__ == "__main__":

@@ -69,6 +69,12 @@ int64_t mdb_launch_count(const mdb_handle* h);
 int32_t mdb_profile_begin(mdb_handle* h, int32_t slots);
 int32_t mdb_profile_read(mdb_handle* h, int32_t slot, float* ms_out /* 4 floats */);
 
+/* FP32 roofline denominator for the bench (MEASURED_PEAKS.json has none): best of `repeats` runs of a kernel of
+ * independent FFMA chains filling every SM, timed with CUDA events; returns 2 x FMAs / time in TFLOP/s.  `scratch`:
+ * device memory of at least num_sms x 8 x 256 floats.  Synchronises `stream` (bench-only entry).            */
+int32_t mdb_measure_fp32_peak(mdb_handle* h, void* scratch, size_t scratch_bytes, int32_t repeats,
+                              double* tflops_out, double* ms_out, void* stream);
+
 /* Test hooks, process-global, never read from the environment: "strip_segs" = n forces n row segments per strip
  * in the fused kernel (0 = the library's choice), "upsample_split" = 1 forces the two-kernel transpose that
  * W > 4096 takes; "decision_dump" = device pointer to Ls N (2C+2) H W int8 makes the fused kernel (a separate
@@ -135,6 +141,14 @@ int32_t mdb_warp(mdb_handle* h, const float* disp, const float* x, const float* 
                  const float* const* t, const int32_t* source_ids, int32_t S, const float* K,
                  const float* invK, int32_t W, int32_t H, int32_t C, int32_t L, int32_t N,
                  double min_depth, double max_depth, float* const* warped, void* stream);
+/* pullback of warp: g_warped[s] (W,H,C,N) -> d_disp (1,W,H,N), dR[s] (3,3,N), dt[s] (3,1,N) (dR / dt or single
+ * entries may be NULL).  With mdb_prediction_loss_bwd and mdb_smooth_loss this differentiates the closure of
+ * src/simple_depth.jl:25-41 function by function, as Zygote does in the reference (the fused
+ * mdb_train_loss_fwdbwd computes the same gradient in one pass).  Deterministic: no float atomics.            */
+int32_t mdb_warp_bwd(mdb_handle* h, const float* disp, const float* x, const float* const* R, const float* const* t,
+                     const int32_t* source_ids, int32_t S, const float* K, const float* invK, int32_t W, int32_t H,
+                     int32_t C, int32_t L, int32_t N, double min_depth, double max_depth, const float* const* g_warped,
+                     float* d_disp, float* const* dR, float* const* dt, void* stream);
 
 /* ---- P9-P11: SSIM / photometric / min-reprojection / automask ------------------------ */
 /* (ssim::SSIM)(x, y) -> (W,H,C,N)                                src/utils.jl:17-43   */
@@ -158,6 +172,20 @@ int32_t mdb_automasking_loss(mdb_handle* h, const float* inputs, const float* ta
 /* _apply_mask(mask, warp_loss): elementwise min over n values    src/training.jl:17-19 */
 int32_t mdb_apply_mask(mdb_handle* h, const float* mask, const float* warp_loss, int64_t n,
                        float* out, void* stream);
+/* pullbacks of SSIM / prediction_loss / _apply_mask w.r.t. the predictions (the target gets no gradient on the
+ * path).  g is the cotangent of the output: (W,H,C,N) for SSIM, (W,H,1,N) for prediction_loss.  The arg-min of
+ * `minimum(cat(...; dims=3); dims=3)` takes the whole cotangent (first arg-min on ties); abs_subgradient as in
+ * mdb_loss_params.  workspace: mdb_ssim_bwd_workspace_bytes(W,H,C,N) bytes, 256-byte aligned, for both.      */
+size_t mdb_ssim_bwd_workspace_bytes(int32_t W, int32_t H, int32_t C, int32_t N);
+int32_t mdb_ssim_bwd(mdb_handle* h, const float* x, const float* y, const float* g, int32_t W, int32_t H, int32_t C,
+                     int32_t N, float c1, float c2, float* dx, void* workspace, size_t workspace_bytes, void* stream);
+int32_t mdb_prediction_loss_bwd(mdb_handle* h, const float* const* predictions, int32_t S, const float* target,
+                                const float* g, int32_t W, int32_t H, int32_t C, int32_t N, float alpha, float c1,
+                                float c2, int32_t abs_subgradient, float* const* d_predictions, void* workspace,
+                                size_t workspace_bytes, void* stream);
+/* d_mask / d_warp_loss may be NULL; the mask keeps ties (it comes first in the cat, src/training.jl:18)        */
+int32_t mdb_apply_mask_bwd(mdb_handle* h, const float* mask, const float* warp_loss, const float* g, int64_t n,
+                           float* d_mask, float* d_warp_loss, void* stream);
 
 /* ---- S1-S2: smoothness  (src/utils.jl:163-177) ---------------------------------------- */
 /* smooth_loss(disparity (W,H,N), image (W,H,C,N)) -> scalar *loss (device); if d_disparity
@@ -198,6 +226,9 @@ typedef struct mdb_loss_io {
 } mdb_loss_io;
 
 size_t mdb_train_loss_workspace_bytes(const mdb_loss_io* io);
+/* launch decomposition of the fused kernel for this shape on the current device: out4 = { 28-column strips per
+ * row, row segments per strip, rows per segment, warps in the launch } (bench roofline: halo overhead)       */
+int32_t mdb_train_loss_strip_geometry(const mdb_loss_io* io, int32_t* out4);
 /* train_loss value AND gradient in one pass (forward of the rrule; the pullback scales the
  * cached gradients by the incoming scalar cotangent).                                    */
 int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_loss_params* p,
@@ -259,6 +290,18 @@ int32_t mdb_sample(mdb_handle* h, const float* src, const float* depth_src, cons
 int32_t mdb_plane_volume_rendering(mdb_handle* h, const float* rgb, const float* sigma, const float* xyz, int32_t W,
                                    int32_t H, int32_t Np, int32_t B, float* rgb_out, float* transparency_acc,
                                    float* weights, void* stream);
+/* pullbacks of the two (the reference has none: `sample` mutates in place).  mdb_sample_bwd: g_tgt
+ * (W,H,Cs,Np*B) -> d_src, the bilinear gather transposed with the homography held fixed (pose / depth gradients
+ * flow through mdb_render_tgt_rgb_depth_bwd); d_src is zeroed here and accumulated with red.global.add.f32.
+ * mdb_plane_volume_rendering_bwd: cotangents of (rgb_out, transparency_acc, weights), any of them NULL ->
+ * d_rgb, d_sigma, d_xyz (d_xyz may be NULL); NaN where two planes coincide, as the reference's sqrt would give. */
+int32_t mdb_sample_bwd(mdb_handle* h, const float* g_tgt, const float* depth_src, const float* rvec, const float* tvec,
+                       const float* K, const float* K_inv, int32_t W, int32_t H, int32_t Cs, int32_t Np, int32_t B,
+                       float* d_src, void* workspace, size_t workspace_bytes, void* stream);
+int32_t mdb_plane_volume_rendering_bwd(mdb_handle* h, const float* rgb, const float* sigma, const float* xyz, int32_t W,
+                                       int32_t H, int32_t Np, int32_t B, const float* g_rgb_out,
+                                       const float* g_transparency_acc, const float* g_weights, float* d_rgb,
+                                       float* d_sigma, float* d_xyz, void* stream);
 /* render_tgt_rgb_depth(rgb, sigma, disparity_src, xyz_tgt, pose, K_inv, K) -> rgb (W,H,3,B),
  * "depth" = transparency_acc (W,H,1,Np,B), mask (W,H,1,1,B) int32   src/render.jl:92-114  */
 int32_t mdb_render_tgt_rgb_depth_fwd(mdb_handle* h, const float* rgb, const float* sigma, const float* disparity_src,

@@ -525,6 +525,15 @@ int32_t mdb_debug_option(const char* name, int64_t value) {
   return MDB_OK;
 }
 
+int32_t mdb_train_loss_strip_geometry(const mdb_loss_io* io, int32_t* out4) {
+  if (!io_shape_ok(io) || !out4) return MDB_E_INVALID_ARG;
+  int dev = 0, sms = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const StripGeom g = strip_geom(io, sms);
+  out4[0] = g.nstrips; out4[1] = g.nsegs; out4[2] = g.seg_rows; out4[3] = g.total;
+  return MDB_OK;
+}
+
 size_t mdb_train_loss_workspace_bytes(const mdb_loss_io* io) {
   if (!io_shape_ok(io)) return 0;
   int dev = 0, sms = 148;

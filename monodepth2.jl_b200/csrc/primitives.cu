@@ -3,6 +3,7 @@
 // and drivers call by name has a device implementation behind the C ABI; the training hot
 // path uses the fused kernel in photo_fused.cu instead.
 #include "photo_fused.cuh"
+#include "pose_math.cuh"
 
 namespace {
 
@@ -120,6 +121,92 @@ __global__ void warp_pose_kernel(WarpPoseArgs a, PosePrep* __restrict__ out, Pos
   }
   out[idx] = p;
   outd[idx] = pd;
+}
+
+// pullback of warp (P13): d warped[s] (W,H,C,N) -> d disp (1,W,H,N), and per (item, source) the 12 sums dL/dA (9),
+// dL/db (3) of P' = A q + invd b, reduced warp -> block -> per-block record (no float atomics: deterministic)
+struct WarpBwdArgs {
+  const float* disp; const float* x; const float* g[MDB_MAX_SOURCES];
+  const PosePrepD* ppd; int src[MDB_MAX_SOURCES];
+  int S, W, H, C, L, N; double mind_d, dd_d;
+  float* d_disp; float* partials;   // [N][blocks][S][12]
+};
+constexpr int WB_THREADS = 256;
+
+__global__ void __launch_bounds__(WB_THREADS) warp_bwd_kernel(const __grid_constant__ WarpBwdArgs a) {
+  const int n = blockIdx.y, wh = a.W * a.H;
+  const int pix = blockIdx.x * WB_THREADS + threadIdx.x;
+  const bool on = pix < wh;
+  const int gx = on ? pix % a.W : 0, gy = on ? pix / a.W : 0;
+  __shared__ float red[WB_THREADS / 32][12];
+  double invd = 0.0;
+  if (on) invd = fma((double)a.disp[(size_t)n * wh + pix], a.dd_d, a.mind_d);
+  float dinvd = 0.0f;
+  for (int s = 0; s < a.S; ++s) {
+    float acc[12];
+#pragma unroll
+    for (int k = 0; k < 12; ++k) acc[k] = 0.0f;
+    if (on) {
+      const PosePrepD& pp = a.ppd[n * a.S + s];
+      const Samp sp = sample_coords(pp, invd, gx, gy, a.W, a.H);
+      const Taps& t = sp.t;
+      float gxs = 0.0f, gys = 0.0f;   // d L / d (sample position)
+      for (int c = 0; c < a.C; ++c) {
+        const float* p = a.x + (((size_t)n * a.L + a.src[s]) * a.C + c) * wh;
+        const float v00 = p[t.o00], v01 = p[t.o01], v10 = p[t.o10], v11 = p[t.o11];
+        const float h0 = v01 - v00, h1 = v11 - v10;
+        const float dxv = fmaf(t.fy, h1 - h0, h0);
+        const float dyv = fmaf(t.fx, h1, v10) - fmaf(t.fx, h0, v00);
+        const float g = a.g[s][((size_t)n * a.C + c) * wh + pix];
+        gxs = fmaf(g, dxv, gxs); gys = fmaf(g, dyv, gys);
+      }
+      // u = P'1 / z'', v = P'2 / z'' (1-based); no gradient where the sample was clamped (NNlib :border)
+      const float dP1 = gxs * t.mx * sp.zinv, dP2 = gys * t.my * sp.zinv;
+      const float u = (float)(gx + 1) + sp.fu, v = (float)(gy + 1) + sp.fv;
+      const float dP3 = -(u * dP1 + v * dP2);
+      const float q0 = (float)(gx + 1), q1 = (float)(gy + 1), fi = (float)invd;
+      acc[0] = dP1 * q0; acc[1] = dP1 * q1; acc[2] = dP1;
+      acc[3] = dP2 * q0; acc[4] = dP2 * q1; acc[5] = dP2;
+      acc[6] = dP3 * q0; acc[7] = dP3 * q1; acc[8] = dP3;
+      acc[9] = dP1 * fi; acc[10] = dP2 * fi; acc[11] = dP3 * fi;
+      dinvd += dP1 * (float)pp.b[0] + dP2 * (float)pp.b[1] + dP3 * (float)(pp.b[2] + 1e-7);
+    }
+#pragma unroll
+    for (int k = 0; k < 12; ++k) {
+      const float v = warp_sum(acc[k]);
+      if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5][k] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < 12) {
+      float v = 0.0f;
+      for (int w = 0; w < WB_THREADS / 32; ++w) v += red[w][threadIdx.x];
+      a.partials[(((size_t)n * gridDim.x + blockIdx.x) * a.S + s) * 12 + threadIdx.x] = v;
+    }
+    __syncthreads();
+  }
+  if (on) a.d_disp[(size_t)n * wh + pix] = dinvd * (float)a.dd_d;   // d invd / d disparity = 1/min - 1/max
+}
+
+// (dA, db) -> (dR, dt):  A = K R invK  =>  dR = K^T dA invK^T;  b = K t  =>  dt = K^T db.  Julia layouts out.
+struct WarpBwdFin { float* dR[MDB_MAX_SOURCES]; float* dt[MDB_MAX_SOURCES]; double K[9], invK[9]; int N, S, blocks; };
+__global__ void warp_bwd_finalize_kernel(const float* __restrict__ partials, WarpBwdFin f) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= f.N * f.S) return;
+  const int n = idx / f.S, s = idx % f.S;
+  double t[12];
+  for (int k = 0; k < 12; ++k) t[k] = 0.0;
+  for (int b = 0; b < f.blocks; ++b)
+    for (int k = 0; k < 12; ++k) t[k] += (double)partials[(((size_t)n * f.blocks + b) * f.S + s) * 12 + k];
+  double Kt[9], iKt[9], t1[9], dR[9];
+  mat3_T(f.K, Kt);
+  mat3_T(f.invK, iKt);
+  mat3_mul(Kt, t, t1);
+  mat3_mul(t1, iKt, dR);
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j)
+      if (f.dR[s]) f.dR[s][9 * n + 3 * j + i] = (float)dR[3 * i + j];
+  for (int i = 0; i < 3; ++i)
+    if (f.dt[s]) f.dt[s][3 * n + i] = (float)(Kt[3 * i] * t[9] + Kt[3 * i + 1] * t[10] + Kt[3 * i + 2] * t[11]);
 }
 
 // ---- SSIM / photometric, one thread per output pixel ----------------------------------
@@ -469,6 +556,43 @@ int32_t mdb_warp(mdb_handle* h, const float* disp, const float* x, const float* 
   wa.mind_d = 1.0 / max_depth; wa.dd_d = 1.0 / min_depth - 1.0 / max_depth;
   wa.mind = (float)wa.mind_d; wa.dd = (float)wa.dd_d;
   warp_kernel<<<grid_for(h, (int64_t)W * H * N, 256), 256, 0, st>>>(wa);
+  MDB_LAUNCHED(h);
+  MDB_CUDA(h, cudaFreeAsync(buf, st));
+  return MDB_OK;
+}
+
+int32_t mdb_warp_bwd(mdb_handle* h, const float* disp, const float* x, const float* const* R, const float* const* t,
+                     const int32_t* source_ids, int32_t S, const float* K, const float* invK, int32_t W, int32_t H,
+                     int32_t C, int32_t L, int32_t N, double min_depth, double max_depth, const float* const* g_warped,
+                     float* d_disp, float* const* dR, float* const* dt, void* stream) {
+  MDB_REQUIRE(h, h && disp && x && R && t && source_ids && K && invK && g_warped && d_disp, MDB_E_INVALID_ARG, "mdb_warp_bwd: null argument");
+  MDB_REQUIRE(h, S >= 1 && S <= MDB_MAX_SOURCES && W > 1 && H > 1 && C > 0 && L > 0 && N > 0 && N <= 65535, MDB_E_SHAPE, "mdb_warp_bwd: bad shape");
+  cudaStream_t st = (cudaStream_t)stream;
+  WarpPoseArgs pa{};
+  WarpBwdArgs wa{};
+  WarpBwdFin fin{};
+  pa.N = N; pa.S = S;
+  for (int s = 0; s < S; ++s) {
+    MDB_REQUIRE(h, R[s] && t[s] && g_warped[s] && source_ids[s] >= 1 && source_ids[s] <= L, MDB_E_INVALID_ARG, "mdb_warp_bwd: bad source %d", s);
+    pa.R[s] = R[s]; pa.t[s] = t[s]; wa.g[s] = g_warped[s]; wa.src[s] = source_ids[s] - 1;
+    fin.dR[s] = dR ? dR[s] : nullptr; fin.dt[s] = dt ? dt[s] : nullptr;
+  }
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) { pa.K[3 * i + j] = K[3 * j + i]; pa.invK[3 * i + j] = invK[3 * j + i]; fin.K[3 * i + j] = pa.K[3 * i + j]; fin.invK[3 * i + j] = pa.invK[3 * i + j]; }
+  const int blocks = (W * H + WB_THREADS - 1) / WB_THREADS;
+  char* buf = nullptr;
+  const size_t o_ppd = mdb_align_up(sizeof(PosePrep) * N * S, 256);
+  const size_t o_part = o_ppd + mdb_align_up(sizeof(PosePrepD) * N * S, 256);
+  MDB_CUDA(h, cudaMallocAsync((void**)&buf, o_part + sizeof(float) * 12 * (size_t)N * blocks * S, st));
+  warp_pose_kernel<<<nblk(N * S, 128), 128, 0, st>>>(pa, (PosePrep*)buf, (PosePrepD*)(buf + o_ppd));
+  MDB_LAUNCHED(h);
+  wa.disp = disp; wa.x = x; wa.ppd = (const PosePrepD*)(buf + o_ppd); wa.S = S; wa.W = W; wa.H = H; wa.C = C; wa.L = L; wa.N = N;
+  wa.mind_d = 1.0 / max_depth; wa.dd_d = 1.0 / min_depth - 1.0 / max_depth;
+  wa.d_disp = d_disp; wa.partials = (float*)(buf + o_part);
+  warp_bwd_kernel<<<dim3(blocks, N), WB_THREADS, 0, st>>>(wa);
+  MDB_LAUNCHED(h);
+  fin.N = N; fin.S = S; fin.blocks = blocks;
+  warp_bwd_finalize_kernel<<<nblk(N * S, 64), 64, 0, st>>>((const float*)(buf + o_part), fin);
   MDB_LAUNCHED(h);
   MDB_CUDA(h, cudaFreeAsync(buf, st));
   return MDB_OK;

@@ -598,3 +598,131 @@ int32_t mdb_render_tgt_rgb_depth_bwd(mdb_handle* h, const float* rgb, const floa
 }
 
 }  // extern "C"
+
+// ---- pullbacks of the stand-alone R5 / R6 (SURVEY 8b export list) -------------------------------------------------
+// The reference's `sample` mutates its grid in place and `render.jl` hard-codes CUDA allocations, so Zygote cannot
+// differentiate either; these are the pullbacks a hand-written rrule of the two functions calls.
+namespace {
+
+// d tgt -> d src: transpose of the bilinear gather (src/render.jl:88), the homography held fixed.  (The gradient
+// w.r.t. pose and plane depth flows through mdb_render_tgt_rgb_depth_bwd, which owns that chain.)
+__global__ void sample_bwd_kernel(const float* __restrict__ g_tgt, const PlanePrep* __restrict__ prep, int W, int H,
+                                  int Cs, int M, float* __restrict__ d_src) {
+  const int pix = blockIdx.x * blockDim.x + threadIdx.x;
+  const int m = blockIdx.y;
+  const int WH = W * H;
+  if (pix >= WH) return;
+  const RTaps t = render_taps(prep[m].Hst, pix % W, pix / W, W, H);
+  const float w00 = (1.0f - t.fx) * (1.0f - t.fy), w01 = t.fx * (1.0f - t.fy), w10 = (1.0f - t.fx) * t.fy, w11 = t.fx * t.fy;
+  for (int c = 0; c < Cs; ++c) {
+    const float g = ldg(g_tgt + ((size_t)m * Cs + c) * WH + pix);
+    if (g == 0.0f) continue;
+    float* p = d_src + ((size_t)m * Cs + c) * WH;
+    // border-clamped taps coincide (o01 == o00 at the right edge): their weights simply add up in the same cell
+    atomicAdd(p + t.o00, g * w00);
+    atomicAdd(p + t.o01, g * w01);
+    atomicAdd(p + t.o10, g * w10);
+    atomicAdd(p + t.o11, g * w11);
+  }
+}
+
+// pullback of plane_volume_rendering (src/render.jl:32-49): one thread per pixel, the forward chain recomputed into
+// local arrays, then the planes walked back to front.
+//   w_k = Tacc_k (1 - T_k),  Tacc_{k+1} = Tacc_k (T_k + 1e-6),  T_k = exp(-dist_k sigma_k),  rgb_out = sum_k w_k rgb_k
+__global__ void __launch_bounds__(128)
+pvr_bwd_kernel(const float* __restrict__ rgb, const float* __restrict__ sigma, const float* __restrict__ xyz, int WH, int Np,
+               const float* __restrict__ g_rgb, const float* __restrict__ g_tacc, const float* __restrict__ g_w,
+               float* __restrict__ d_rgb, float* __restrict__ d_sigma, float* __restrict__ d_xyz) {
+  const int pix = blockIdx.x * blockDim.x + threadIdx.x;
+  const int b = blockIdx.y;
+  if (pix >= WH) return;
+  float T[RB_MAXP], TA[RB_MAXP], D[RB_MAXP];
+  float tacc = 1.0f;
+  for (int k = 0; k < Np; ++k) {
+    const int kb = b * Np + k;
+    float dist = 1e3f;
+    if (k + 1 < Np) {
+      const float* p0 = xyz + ((size_t)kb * WH + pix) * 3;
+      const float* p1 = p0 + (size_t)WH * 3;
+      const float dx = p1[0] - p0[0], dy = p1[1] - p0[1], dz = p1[2] - p0[2];
+      dist = sqrtf(dx * dx + dy * dy + dz * dz);
+    }
+    D[k] = dist;
+    T[k] = expf(-dist * sigma[(size_t)kb * WH + pix]);
+    TA[k] = tacc;
+    tacc *= (T[k] + 1e-6f);
+  }
+  float gr[3];
+  for (int c = 0; c < 3; ++c) gr[c] = g_rgb ? g_rgb[((size_t)b * 3 + c) * WH + pix] : 0.0f;
+  float G = 0.0f;                         // d / d Tacc_{k+1}
+  float gd_next[3] = {0.0f, 0.0f, 0.0f};  // d dist_{k+1} * unit(diff_{k+1}): the part of d p_{k+1} already known
+  for (int k = Np - 1; k >= 0; --k) {
+    const int kb = b * Np + k;
+    const size_t o = (size_t)kb * WH + pix;
+    const float w = TA[k] * (1.0f - T[k]);
+    float gw = g_w ? g_w[o] : 0.0f;
+    for (int c = 0; c < 3; ++c) {
+      const size_t oc = ((size_t)kb * 3 + c) * WH + pix;
+      gw = fmaf(gr[c], rgb[oc], gw);
+      d_rgb[oc] = gr[c] * w;
+    }
+    const float dT = (G - gw) * TA[k];
+    G = (g_tacc ? g_tacc[o] : 0.0f) + gw * (1.0f - T[k]) + G * (T[k] + 1e-6f);
+    const float sg = sigma[o];
+    d_sigma[o] = dT * T[k] * (-D[k]);
+    float gd[3] = {0.0f, 0.0f, 0.0f};
+    if (k + 1 < Np) {
+      const float dd = dT * T[k] * (-sg);       // d / d dist_k
+      const float* p0 = xyz + o * 3;
+      const float* p1 = p0 + (size_t)WH * 3;
+      const float s = dd / D[k];                // sqrt pullback: NaN where two planes coincide, like the reference's
+      for (int i = 0; i < 3; ++i) gd[i] = s * (p1[i] - p0[i]);
+    }
+    if (d_xyz) {
+      // d p_{k+1} = gd_k - gd_{k+1}: complete now
+      if (k + 1 < Np)
+        for (int i = 0; i < 3; ++i) d_xyz[(o + WH) * 3 + i] = gd[i] - gd_next[i];
+      if (k == 0)
+        for (int i = 0; i < 3; ++i) d_xyz[o * 3 + i] = -gd[i];
+    }
+    for (int i = 0; i < 3; ++i) gd_next[i] = gd[i];
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t mdb_sample_bwd(mdb_handle* h, const float* g_tgt, const float* depth_src, const float* rvec, const float* tvec,
+                       const float* K, const float* K_inv, int32_t W, int32_t H, int32_t Cs, int32_t Np, int32_t B,
+                       float* d_src, void* workspace, size_t workspace_bytes, void* stream) {
+  MDB_REQUIRE(h, h && g_tgt && depth_src && rvec && tvec && K && K_inv && d_src, MDB_E_INVALID_ARG, "mdb_sample_bwd: null argument");
+  MDB_REQUIRE(h, W >= 2 && H >= 2 && Cs >= 1 && Np >= 1 && Np <= RB_MAXP && B >= 1, MDB_E_SHAPE, "mdb_sample_bwd: bad shape");
+  const RenderLayout L = render_layout(W, H, Np, B);
+  MDB_REQUIRE(h, workspace && workspace_bytes >= L.total && ((uintptr_t)workspace & 255) == 0, MDB_E_WORKSPACE,
+              "mdb_sample_bwd: workspace must be >= %zu bytes, 256-byte aligned", L.total);
+  cudaStream_t st = (cudaStream_t)stream;
+  PlanePrep* prep = (PlanePrep*)((char*)workspace + L.o_prep);
+  render_prep_kernel<<<(Np * B + 63) / 64, 64, 0, st>>>(depth_src, 1, rvec, tvec, make_rc(K, K_inv), Np, B, prep);
+  MDB_LAUNCHED(h);
+  MDB_CUDA(h, cudaMemsetAsync(d_src, 0, sizeof(float) * (size_t)W * H * Cs * Np * B, st));
+  dim3 grid((W * H + 127) / 128, Np * B);
+  sample_bwd_kernel<<<grid, 128, 0, st>>>(g_tgt, prep, W, H, Cs, Np * B, d_src);
+  MDB_LAUNCHED(h);
+  return MDB_OK;
+}
+
+int32_t mdb_plane_volume_rendering_bwd(mdb_handle* h, const float* rgb, const float* sigma, const float* xyz, int32_t W,
+                                       int32_t H, int32_t Np, int32_t B, const float* g_rgb_out,
+                                       const float* g_transparency_acc, const float* g_weights, float* d_rgb,
+                                       float* d_sigma, float* d_xyz, void* stream) {
+  MDB_REQUIRE(h, h && rgb && sigma && xyz && d_rgb && d_sigma && W > 0 && H > 0 && Np > 0 && Np <= RB_MAXP && B > 0,
+              MDB_E_INVALID_ARG, "mdb_plane_volume_rendering_bwd: bad argument (1 <= Np <= %d)", RB_MAXP);
+  dim3 grid((W * H + 127) / 128, B);
+  pvr_bwd_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(rgb, sigma, xyz, W * H, Np, g_rgb_out, g_transparency_acc, g_weights,
+                                                         d_rgb, d_sigma, d_xyz);
+  MDB_LAUNCHED(h);
+  return MDB_OK;
+}
+
+}  // extern "C"

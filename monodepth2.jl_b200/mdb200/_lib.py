@@ -91,6 +91,15 @@ PROTOTYPES = {
     "mdb_grid_sample": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
     "mdb_warp": (_i32, [_vp, _vp, _vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_i32), _i32, c_f32p,
                         c_f32p, _i32, _i32, _i32, _i32, _i32, _f64, _f64, C.POINTER(_vp), _vp]),
+    "mdb_warp_bwd": (_i32, [_vp, _vp, _vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_i32), _i32, c_f32p, c_f32p, _i32, _i32, _i32,
+                            _i32, _i32, _f64, _f64, C.POINTER(_vp), _vp, C.POINTER(_vp), C.POINTER(_vp), _vp]),
+    "mdb_ssim_bwd_workspace_bytes": (_sz, [_i32, _i32, _i32, _i32]),
+    "mdb_ssim_bwd": (_i32, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _f32, _f32, _vp, _vp, _sz, _vp]),
+    "mdb_prediction_loss_bwd": (_i32, [_vp, C.POINTER(_vp), _i32, _vp, _vp, _i32, _i32, _i32, _i32, _f32, _f32, _f32, _i32,
+                                       C.POINTER(_vp), _vp, _sz, _vp]),
+    "mdb_apply_mask_bwd": (_i32, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp]),
+    "mdb_sample_bwd": (_i32, [_vp, _vp, _vp, _vp, _vp, c_f32p, c_f32p, _i32, _i32, _i32, _i32, _i32, _vp, _vp, _sz, _vp]),
+    "mdb_plane_volume_rendering_bwd": (_i32, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "mdb_ssim": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _f32, _f32, _vp, _vp]),
     "mdb_photometric_loss": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _f32, _f32, _f32, _vp, _vp]),
     "mdb_prediction_loss": (_i32, [_vp, C.POINTER(_vp), _i32, _vp, _i32, _i32, _i32, _i32, _f32, _f32,
@@ -101,6 +110,7 @@ PROTOTYPES = {
     "mdb_smooth_loss_workspace_bytes": (_sz, [_i32, _i32, _i32]),
     "mdb_smooth_loss": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _sz, _vp]),
     "mdb_smooth_loss_ex": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _sz, _vp]),
+    "mdb_train_loss_strip_geometry": (_i32, [C.POINTER(LossIO), C.POINTER(_i32)]),
     "mdb_train_loss_workspace_bytes": (_sz, [C.POINTER(LossIO)]),
     "mdb_train_loss_fwdbwd": (_i32, [_vp, C.POINTER(LossIO), C.POINTER(LossParams), _vp, _sz, _vp]),
     "mdb_inv3x3_batched": (_i32, [_vp, _vp, _i32, _vp, _vp]),
@@ -130,6 +140,7 @@ PROTOTYPES = {
     "mdb_pose_head": (_i32, [_vp, _vp, _i32, _i32, _i32, _f32, _vp, _vp, _vp]),
     "mdb_pose_head_bwd": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _f32, _vp, _vp]),
     "mdb_item_mean": (_i32, [_vp, _vp, _i64, _i32, _vp, _vp]),
+    "mdb_measure_fp32_peak": (_i32, [_vp, _vp, _sz, _i32, C.POINTER(_f64), C.POINTER(_f64), _vp]),
     "mdb_debug_option": (_i32, [C.c_char_p, _i64]),
     "mdb_packed_size": (_i64, [_i32, _i32]),
     "mdb_packed_bind": (_i32, [C.POINTER(LossIO), _vp, _i32, _i32]),

@@ -48,6 +48,15 @@ def profile_begin(slots: int) -> None:
     check(handle(), lib.mdb_profile_begin(handle(), int(slots)))
 
 
+def measure_fp32_peak(repeats: int = 5):
+    """-> (TFLOP/s, ms): the FP32 FMA peak of the current device, measured (bench roofline denominator)."""
+    h = handle()
+    scratch = torch.empty(148 * 4 * 8 * 256, dtype=torch.float32, device="cuda")
+    tf, ms = ct.c_double(0.0), ct.c_double(0.0)
+    check(h, lib.mdb_measure_fp32_peak(h, _p(scratch), scratch.numel() * 4, int(repeats), ct.byref(tf), ct.byref(ms), _stream()))
+    return tf.value, ms.value
+
+
 def debug_option(name: str, value: int) -> None:
     """Test hooks of the library ("strip_segs", "upsample_split"); 0 restores the default."""
     rc = lib.mdb_debug_option(name.encode(), int(value))
@@ -111,11 +120,36 @@ class SSIM:
         self.c1, self.c2 = c1, c2
 
     def __call__(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        """Differentiable w.r.t. x (mdb_ssim_bwd), like the reference's SSIM under Zygote."""
+        return _SsimFn.apply(x, y, self.c1, self.c2)
+
+
+def _ssim_ws(W, H, Cc, N, dev):
+    n = int(lib.mdb_ssim_bwd_workspace_bytes(W, H, Cc, N))
+    return torch.empty(n, dtype=torch.uint8, device=dev), n
+
+
+class _SsimFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, y, c1, c2):
+        x, y = x.detach(), y.detach()
         _chk(x, "x"); _chk(y, "y")
         N, Cc, H, W = x.shape
         out = torch.empty_like(x)
-        check(handle(), lib.mdb_ssim(handle(), _p(x), _p(y), W, H, Cc, N, self.c1, self.c2, _p(out), _stream()))
+        check(handle(), lib.mdb_ssim(handle(), _p(x), _p(y), W, H, Cc, N, c1, c2, _p(out), _stream()))
+        ctx.save_for_backward(x, y)
+        ctx.c = (c1, c2)
         return out
+
+    @staticmethod
+    def backward(ctx, g):
+        x, y = ctx.saved_tensors
+        N, Cc, H, W = x.shape
+        ws, n = _ssim_ws(W, H, Cc, N, x.device)
+        dx = torch.empty_like(x)
+        check(handle(), lib.mdb_ssim_bwd(handle(), _p(x), _p(y), _p(g.contiguous()), W, H, Cc, N, ctx.c[0], ctx.c[1], _p(dx),
+                                         _p(ws), n, _stream()))
+        return dx, None, None, None
 
 
 class Backproject:
@@ -188,13 +222,31 @@ def so3_exp_map(rvec: torch.Tensor) -> torch.Tensor:
     return R
 
 
+class _ComposeTFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, rvec, t, invert):
+        rvec, t = rvec.detach(), t.detach()
+        _chk(rvec, "rvec"); _chk(t, "t")
+        N = rvec.shape[0]
+        R = torch.empty((N, 3, 3), device=rvec.device, dtype=torch.float32)
+        to = torch.empty((N, 1, 3), device=rvec.device, dtype=torch.float32)
+        check(handle(), lib.mdb_compose_T(handle(), _p(rvec), _p(t), int(bool(invert)), N, _p(R), _p(to), _stream()))
+        ctx.save_for_backward(rvec, t)
+        ctx.invert = bool(invert)
+        return R, to
+
+    @staticmethod
+    def backward(ctx, dR, dt):
+        rvec, t = ctx.saved_tensors
+        dR = torch.zeros((rvec.shape[0], 3, 3), device=rvec.device) if dR is None else dR.contiguous()
+        dt = torch.zeros_like(t) if dt is None else dt.contiguous()
+        dr, dtv = composeT_pullback(rvec, t, ctx.invert, dR, dt)
+        return dr, dtv, None
+
+
 def composeT(rvec: torch.Tensor, t: torch.Tensor, invert: bool):
-    _chk(rvec, "rvec"); _chk(t, "t")
-    N = rvec.shape[0]
-    R = torch.empty((N, 3, 3), device=rvec.device, dtype=torch.float32)
-    to = torch.empty((N, 1, 3), device=rvec.device, dtype=torch.float32)
-    check(handle(), lib.mdb_compose_T(handle(), _p(rvec), _p(t), int(bool(invert)), N, _p(R), _p(to), _stream()))
-    return R, to
+    """src/utils.jl:185-192 (differentiable: mdb_compose_T_bwd)."""
+    return _ComposeTFn.apply(rvec, t, invert)
 
 
 def composeT_pullback(rvec, t, invert, dR, dt):
@@ -230,21 +282,53 @@ def grid_sample(inp: torch.Tensor, grid: torch.Tensor, padding_mode: str = "bord
     return out
 
 
+class _WarpFn(torch.autograd.Function):
+    """warp forward (mdb_warp) and pullback (mdb_warp_bwd) w.r.t. disp and every (R, t)."""
+
+    @staticmethod
+    def forward(ctx, disp, x, Ks, invKs, min_depth, max_depth, source_ids, *Rt):
+        disp, x = disp.detach(), x.detach()
+        Rt = [t.detach() for t in Rt]
+        _chk(disp, "disp"); _chk(x, "x")
+        N, L, Cc, H, W = x.shape
+        S = len(Rt) // 2
+        outs = [torch.empty((N, Cc, H, W), device=x.device, dtype=torch.float32) for _ in range(S)]
+        Rp = (ct.c_void_p * S)(*[_chk(Rt[2 * s], "R").data_ptr() for s in range(S)])
+        tp = (ct.c_void_p * S)(*[_chk(Rt[2 * s + 1], "t").data_ptr() for s in range(S)])
+        op = (ct.c_void_p * S)(*[o.data_ptr() for o in outs])
+        ids = (ct.c_int32 * S)(*[int(s) for s in source_ids])
+        check(handle(), lib.mdb_warp(handle(), _p(disp), _p(x), Rp, tp, ids, S, _k9(Ks), _k9(invKs), W, H, Cc, L, N,
+                                     float(min_depth), float(max_depth), op, _stream()))
+        ctx.save_for_backward(disp, x, *Rt)
+        ctx.meta = (Ks, invKs, float(min_depth), float(max_depth), list(source_ids))
+        return tuple(outs)
+
+    @staticmethod
+    def backward(ctx, *gs):
+        disp, x, *Rt = ctx.saved_tensors
+        Ks, invKs, mind, maxd, source_ids = ctx.meta
+        N, L, Cc, H, W = x.shape
+        S = len(Rt) // 2
+        gs = [torch.zeros((N, Cc, H, W), device=x.device) if g is None else g.contiguous() for g in gs]
+        d_disp = torch.empty_like(disp)
+        dR = [torch.empty_like(Rt[2 * s]) for s in range(S)]
+        dt = [torch.empty_like(Rt[2 * s + 1]) for s in range(S)]
+        arr = lambda ts: (ct.c_void_p * S)(*[t.data_ptr() for t in ts])
+        ids = (ct.c_int32 * S)(*[int(s) for s in source_ids])
+        check(handle(), lib.mdb_warp_bwd(handle(), _p(disp), _p(x), arr([Rt[2 * s] for s in range(S)]),
+                                         arr([Rt[2 * s + 1] for s in range(S)]), ids, S, _k9(Ks), _k9(invKs), W, H, Cc, L, N,
+                                         mind, maxd, arr(gs), _p(d_disp), arr(dR), arr(dt), _stream()))
+        flat = [t for s in range(S) for t in (dR[s], dt[s])]
+        return (d_disp, None, None, None, None, None, None, *flat)
+
+
 def warp(disp: torch.Tensor, x: torch.Tensor, Ps, backprojections, projections, invKs, Ks, *,
          min_depth: float, max_depth: float, source_ids: Sequence[int]) -> List[torch.Tensor]:
     """`warp(...)` as called at src/simple_depth.jl:30-32 (body: src/training.jl:48-57).
-    disp (N,H,W,1) or (N,1,H,W); x (N,L,C,H,W); Ps = [(R (N,3,3), t (N,1,3))]."""
-    _chk(disp, "disp"); _chk(x, "x")
-    N, L, Cc, H, W = x.shape
-    S = len(Ps)
-    outs = [torch.empty((N, Cc, H, W), device=x.device, dtype=torch.float32) for _ in range(S)]
-    Rp = (ct.c_void_p * S)(*[_chk(P[0], "R").data_ptr() for P in Ps])
-    tp = (ct.c_void_p * S)(*[_chk(P[1], "t").data_ptr() for P in Ps])
-    op = (ct.c_void_p * S)(*[o.data_ptr() for o in outs])
-    ids = (ct.c_int32 * S)(*[int(s) for s in source_ids])
-    check(handle(), lib.mdb_warp(handle(), _p(disp), _p(x), Rp, tp, ids, S, _k9(Ks), _k9(invKs), W, H, Cc, L, N,
-                                 float(min_depth), float(max_depth), op, _stream()))
-    return outs
+    disp (N,H,W,1) or (N,1,H,W); x (N,L,C,H,W); Ps = [(R (N,3,3), t (N,1,3))].  Differentiable w.r.t. disp and the
+    (R, t) pairs (mdb_warp_bwd), so the closure of `slow_depth` can be differentiated function by function."""
+    flat = [t for P in Ps for t in (P[0], P[1])]
+    return list(_WarpFn.apply(disp, x, Ks, invKs, min_depth, max_depth, tuple(source_ids), *flat))
 
 
 def photometric_loss(ssim: SSIM, predicted: torch.Tensor, target: torch.Tensor, alpha: float = 0.85):
@@ -256,15 +340,39 @@ def photometric_loss(ssim: SSIM, predicted: torch.Tensor, target: torch.Tensor, 
     return out
 
 
-def prediction_loss(ssim: SSIM, predictions: Sequence[torch.Tensor], target: torch.Tensor, alpha: float = 0.85):
-    """src/training.jl:13-15."""
-    _chk(target, "target")
-    N, Cc, H, W = target.shape
-    S = len(predictions)
-    pp = (ct.c_void_p * S)(*[_chk(p, "prediction").data_ptr() for p in predictions])
-    out = torch.empty((N, 1, H, W), device=target.device, dtype=torch.float32)
-    check(handle(), lib.mdb_prediction_loss(handle(), pp, S, _p(target), W, H, Cc, N, alpha, ssim.c1, ssim.c2, _p(out), _stream()))
-    return out
+class _PredLossFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, target, alpha, c1, c2, abs_subgradient, *preds):
+        target = target.detach()
+        preds = [p.detach() for p in preds]
+        _chk(target, "target")
+        N, Cc, H, W = target.shape
+        S = len(preds)
+        pp = (ct.c_void_p * S)(*[_chk(p, "prediction").data_ptr() for p in preds])
+        out = torch.empty((N, 1, H, W), device=target.device, dtype=torch.float32)
+        check(handle(), lib.mdb_prediction_loss(handle(), pp, S, _p(target), W, H, Cc, N, alpha, c1, c2, _p(out), _stream()))
+        ctx.save_for_backward(target, *preds)
+        ctx.meta = (alpha, c1, c2, int(abs_subgradient))
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        target, *preds = ctx.saved_tensors
+        alpha, c1, c2, mode = ctx.meta
+        N, Cc, H, W = target.shape
+        S = len(preds)
+        ws, n = _ssim_ws(W, H, Cc, N, target.device)
+        d = [torch.empty_like(p) for p in preds]
+        arr = lambda ts: (ct.c_void_p * S)(*[t.data_ptr() for t in ts])
+        check(handle(), lib.mdb_prediction_loss_bwd(handle(), arr(preds), S, _p(target), _p(g.contiguous()), W, H, Cc, N, alpha, c1, c2,
+                                                    mode, arr(d), _p(ws), n, _stream()))
+        return (None, None, None, None, None, *d)
+
+
+def prediction_loss(ssim: SSIM, predictions: Sequence[torch.Tensor], target: torch.Tensor, alpha: float = 0.85,
+                    abs_subgradient: int = 0):
+    """src/training.jl:13-15.  Differentiable w.r.t. the predictions (mdb_prediction_loss_bwd: first arg-min)."""
+    return _PredLossFn.apply(target, alpha, ssim.c1, ssim.c2, abs_subgradient, *predictions)
 
 
 def automasking_loss(ssim: SSIM, inputs: torch.Tensor, target: torch.Tensor, *, source_ids: Sequence[int], alpha: float = 0.85):
@@ -286,17 +394,30 @@ def automasking_loss(ssim: SSIM, inputs: torch.Tensor, target: torch.Tensor, *, 
     return out
 
 
+class _ApplyMaskFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, mask, warp_loss):
+        mask, warp_loss = mask.detach(), warp_loss.detach()
+        _chk(mask, "mask"); _chk(warp_loss, "warp_loss")
+        out = torch.empty_like(warp_loss)
+        check(handle(), lib.mdb_apply_mask(handle(), _p(mask), _p(warp_loss), warp_loss.numel(), _p(out), _stream()))
+        ctx.save_for_backward(mask, warp_loss)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        mask, wl = ctx.saved_tensors
+        dm, dw = torch.empty_like(mask), torch.empty_like(wl)
+        check(handle(), lib.mdb_apply_mask_bwd(handle(), _p(mask), _p(wl), _p(g.contiguous()), wl.numel(), _p(dm), _p(dw), _stream()))
+        return dm, dw
+
+
 def _apply_mask(mask: torch.Tensor, warp_loss: torch.Tensor) -> torch.Tensor:
-    """src/training.jl:17-19."""
-    _chk(mask, "mask"); _chk(warp_loss, "warp_loss")
-    out = torch.empty_like(warp_loss)
-    check(handle(), lib.mdb_apply_mask(handle(), _p(mask), _p(warp_loss), warp_loss.numel(), _p(out), _stream()))
-    return out
+    """src/training.jl:17-19 (differentiable: the mask keeps ties)."""
+    return _ApplyMaskFn.apply(mask, warp_loss)
 
 
-def smooth_loss(disparity: torch.Tensor, image: torch.Tensor, with_grad: bool = False, abs_subgradient: int = 0):
-    """src/utils.jl:163-177.  disparity (N,H,W), image (N,C,H,W) -> 0-dim loss tensor
-    (and d loss / d disparity when `with_grad`; `abs_subgradient`: see mdb_loss_params)."""
+def _smooth_raw(disparity, image, with_grad, abs_subgradient):
     _chk(disparity, "disparity"); _chk(image, "image")
     N, Cc, H, W = image.shape
     wsb = lib.mdb_smooth_loss_workspace_bytes(W, H, N)
@@ -305,6 +426,29 @@ def smooth_loss(disparity: torch.Tensor, image: torch.Tensor, with_grad: bool = 
     grad = torch.empty_like(disparity) if with_grad else None
     check(handle(), lib.mdb_smooth_loss_ex(handle(), _p(disparity), _p(image), W, H, Cc, N, int(abs_subgradient), _p(loss), _p(grad),
                                            _p(ws), wsb, _stream()))
+    return loss, grad
+
+
+class _SmoothFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, disparity, image, abs_subgradient):
+        loss, grad = _smooth_raw(disparity.detach(), image.detach(), True, abs_subgradient)
+        ctx.save_for_backward(grad)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        (grad,) = ctx.saved_tensors
+        return grad * g, None, None
+
+
+def smooth_loss(disparity: torch.Tensor, image: torch.Tensor, with_grad: bool = False, abs_subgradient: int = 0):
+    """src/utils.jl:163-177.  disparity (N,H,W), image (N,C,H,W) -> 0-dim loss tensor
+    (and d loss / d disparity when `with_grad`; `abs_subgradient`: see mdb_loss_params).  When `disparity` requires
+    grad the returned loss is differentiable (value and gradient come from the same kernel launch)."""
+    if disparity.requires_grad and not with_grad:
+        return _SmoothFn.apply(disparity, image, abs_subgradient)
+    loss, grad = _smooth_raw(disparity.detach(), image, with_grad, abs_subgradient)
     return (loss, grad) if with_grad else loss
 
 
@@ -386,6 +530,12 @@ class FusedLoss:
         if self.ws_bytes == 0:
             raise _lib.MdbError(_lib.lib.mdb_version() * 0 - 2, "unsupported shape for the fused loss")
         self.ws = torch.empty(self.ws_bytes, dtype=torch.uint8, device=self.dev)
+
+    def strip_geometry(self) -> dict:
+        """Launch decomposition of the fused kernel for this plan (mdb_train_loss_strip_geometry)."""
+        g = (ct.c_int32 * 4)()
+        lib.mdb_train_loss_strip_geometry(ct.byref(self.io), g)
+        return dict(strips=g[0], segments=g[1], rows_per_segment=g[2], warps=g[3])
 
     def __call__(self, x: torch.Tensor, disparities: Sequence[torch.Tensor], poses: Sequence[Pose],
                  auto_loss: Optional[torch.Tensor] = None) -> LossResult:
@@ -919,28 +1069,68 @@ def _render_ws(W, H, Np, B, dev):
     return torch.empty(n, dtype=torch.uint8, device=dev), n
 
 
+class _SampleFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, src, depth_src, rvec, tvec, K, K_inv):
+        src = src.detach()
+        _chk(src, "src"); _chk(depth_src, "depth_src")
+        B, Np, Cs, H, W = src.shape
+        ws, n = _render_ws(W, H, Np, B, src.device)
+        tgt = torch.empty_like(src)
+        valid = torch.empty((B, Np, H, W), dtype=torch.uint8, device=src.device)
+        check(handle(), lib.mdb_sample(handle(), _p(src), _p(depth_src), _p(rvec), _p(tvec), _k9(K), _k9(K_inv),
+                                       W, H, Cs, Np, B, _p(tgt), ct.c_void_p(valid.data_ptr()), _p(ws), n, _stream()))
+        ctx.save_for_backward(depth_src, rvec, tvec)
+        ctx.meta = (K, K_inv, tuple(src.shape), ws, n)
+        valid = valid.bool()
+        ctx.mark_non_differentiable(valid)
+        return tgt, valid
+
+    @staticmethod
+    def backward(ctx, g, _gv):
+        depth_src, rvec, tvec = ctx.saved_tensors
+        K, K_inv, (B, Np, Cs, H, W), ws, n = ctx.meta
+        d_src = torch.empty((B, Np, Cs, H, W), device=g.device, dtype=torch.float32)
+        check(handle(), lib.mdb_sample_bwd(handle(), _p(g.contiguous()), _p(depth_src), _p(rvec), _p(tvec), _k9(K), _k9(K_inv),
+                                           W, H, Cs, Np, B, _p(d_src), _p(ws), n, _stream()))
+        return d_src, None, None, None, None, None
+
+
 def sample(src: torch.Tensor, depth_src: torch.Tensor, pose: Pose, K, K_inv):
     """`sample` -- src/render.jl:64-90.  src (B,Np,Cs,H,W) [Julia (W,H,Cs,Np*B)], depth_src (B,Np)
-    -> tgt (B,Np,Cs,H,W), valid_mask (B,Np,H,W) bool."""
-    _chk(src, "src"); _chk(depth_src, "depth_src")
-    B, Np, Cs, H, W = src.shape
-    ws, n = _render_ws(W, H, Np, B, src.device)
-    tgt = torch.empty_like(src)
-    valid = torch.empty((B, Np, H, W), dtype=torch.uint8, device=src.device)
-    check(handle(), lib.mdb_sample(handle(), _p(src), _p(depth_src), _p(pose.rvec), _p(pose.tvec), _k9(K), _k9(K_inv),
-                                   W, H, Cs, Np, B, _p(tgt), ct.c_void_p(valid.data_ptr()), _p(ws), n, _stream()))
-    return tgt, valid.bool()
+    -> tgt (B,Np,Cs,H,W), valid_mask (B,Np,H,W) bool.  Differentiable w.r.t. src (mdb_sample_bwd)."""
+    return _SampleFn.apply(src, depth_src, pose.rvec, pose.tvec, K, K_inv)
+
+
+class _PvrFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, rgb, sigma, xyz):
+        rgb, sigma, xyz = rgb.detach(), sigma.detach(), xyz.detach()
+        _chk(rgb, "rgb"); _chk(sigma, "sigma"); _chk(xyz, "xyz")
+        B, Np, _, H, W = rgb.shape
+        rgb_out = torch.empty((B, 3, H, W), device=rgb.device, dtype=torch.float32)
+        tacc = torch.empty((B, Np, 1, H, W), device=rgb.device, dtype=torch.float32)
+        wts = torch.empty_like(tacc)
+        check(handle(), lib.mdb_plane_volume_rendering(handle(), _p(rgb), _p(sigma), _p(xyz), W, H, Np, B, _p(rgb_out), _p(tacc),
+                                                       _p(wts), _stream()))
+        ctx.save_for_backward(rgb, sigma, xyz)
+        return rgb_out, tacc, wts
+
+    @staticmethod
+    def backward(ctx, g_rgb, g_tacc, g_w):
+        rgb, sigma, xyz = ctx.saved_tensors
+        B, Np, _, H, W = rgb.shape
+        c = lambda t: None if t is None else t.contiguous()
+        d_rgb, d_sigma, d_xyz = torch.empty_like(rgb), torch.empty_like(sigma), torch.empty_like(xyz)
+        check(handle(), lib.mdb_plane_volume_rendering_bwd(handle(), _p(rgb), _p(sigma), _p(xyz), W, H, Np, B, _p(c(g_rgb)),
+                                                           _p(c(g_tacc)), _p(c(g_w)), _p(d_rgb), _p(d_sigma), _p(d_xyz), _stream()))
+        return d_rgb, d_sigma, d_xyz
 
 
 def plane_volume_rendering(rgb: torch.Tensor, sigma: torch.Tensor, xyz: torch.Tensor):
-    """src/render.jl:32-49 -> rgb_out (B,3,H,W), transparency_acc (B,Np,1,H,W), weights (B,Np,1,H,W)."""
-    _chk(rgb, "rgb"); _chk(sigma, "sigma"); _chk(xyz, "xyz")
-    B, Np, _, H, W = rgb.shape
-    rgb_out = torch.empty((B, 3, H, W), device=rgb.device, dtype=torch.float32)
-    tacc = torch.empty((B, Np, 1, H, W), device=rgb.device, dtype=torch.float32)
-    wts = torch.empty_like(tacc)
-    check(handle(), lib.mdb_plane_volume_rendering(handle(), _p(rgb), _p(sigma), _p(xyz), W, H, Np, B, _p(rgb_out), _p(tacc), _p(wts), _stream()))
-    return rgb_out, tacc, wts
+    """src/render.jl:32-49 -> rgb_out (B,3,H,W), transparency_acc (B,Np,1,H,W), weights (B,Np,1,H,W).
+    Differentiable (mdb_plane_volume_rendering_bwd)."""
+    return _PvrFn.apply(rgb, sigma, xyz)
 
 
 def _render_opts(mine_grid: bool, mine_mask: bool, depth_eps) -> "_lib.RenderOpts":

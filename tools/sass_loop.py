@@ -1,7 +1,10 @@
 """Static size of photo_strip_kernel<3,2>'s row loop: instructions between the backward branch and its
-target, opcode histogram, registers / spills.  Usage: python tools/sass_loop.py [build/photo_fused.o] [-v]"""
-import re, subprocess, sys, collections
-obj = next((a for a in sys.argv[1:] if not a.startswith('-')), 'monodepth2.jl_b200/build/photo_fused.o')
+target, opcode histogram, registers / spills.  Usage: python tools/sass_loop.py [build/photo_fused.o] [-v] [--json out.json]
+--json records the histogram, the fp32 flops per lane and row (2 FFMA + FADD + FMUL + 4 FFMA2 + 2 FADD2 + 2 FMUL2), the
+-res-usage line and the git blob hash of csrc/photo_strip.inl it was built from: bench.py's roofline reads it and
+prints null when the kernel source has changed since."""
+import re, subprocess, sys, collections, json, hashlib, os
+obj = next((a for a in sys.argv[1:] if a.endswith('.o')), 'monodepth2.jl_b200/build/photo_fused.o')
 sass = subprocess.run(['cuobjdump', '-sass', obj], capture_output=True, text=True).stdout
 fn = None; rows = []
 for line in sass.splitlines():
@@ -20,3 +23,18 @@ print(' '.join(f'{k}:{v}' for k, v in h.most_common(28)))
 res = subprocess.run(['cuobjdump', '-res-usage', obj], capture_output=True, text=True).stdout.splitlines()
 for i, l in enumerate(res):
     if 'photo_strip_kernelILi3ELi2ELb0' in l: print(res[i + 1].strip())
+
+if '--json' in sys.argv:
+    out = sys.argv[sys.argv.index('--json') + 1]
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    def blob(path):
+        d = open(os.path.join(root, path), 'rb').read()
+        return hashlib.sha1(b'blob %d\0' % len(d) + d).hexdigest()
+    flops = 2 * h['FFMA'] + h['FADD'] + h['FMUL'] + 4 * h['FFMA2'] + 2 * h['FADD2'] + 2 * h['FMUL2']
+    usage = [res[i + 1].strip() for i, l in enumerate(res) if 'photo_strip_kernelILi3ELi2ELb0' in l]
+    json.dump({'kernel': 'photo_strip_kernel<3,2,false>', 'row_loop_instructions': len(body), 'histogram': dict(h.most_common()),
+               'fp32_flops_per_lane_row': flops, 'fp32_flop_formula': '2 FFMA + FADD + FMUL + 4 FFMA2 + 2 FADD2 + 2 FMUL2 (static count of the row loop)',
+               'res_usage': usage[0] if usage else None,
+               'source_hash': {'monodepth2.jl_b200/csrc/photo_strip.inl': blob('monodepth2.jl_b200/csrc/photo_strip.inl')},
+               'how': 'python tools/sass_loop.py --json ' + out}, open(out, 'w'), indent=1)
+    print('wrote', out, 'flops per lane and row:', flops)
