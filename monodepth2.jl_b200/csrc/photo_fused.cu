@@ -106,7 +106,7 @@ disp_mean_kernel(const __grid_constant__ FusedArgs a, double* __restrict__ part 
 // ---------------------------------------------------------------------------------------
 // 2. pose prep (threads [0, N S)) and mean -> normalisation factor (threads [N S, N S + Ls N))
 // ---------------------------------------------------------------------------------------
-__global__ void prep_kernel(PoseArgs a, PosePrepD* __restrict__ outd, const double* __restrict__ mean_part,
+__global__ void prep_kernel(PoseArgs a, PoseStrip* __restrict__ outd, const double* __restrict__ mean_part,
                             int rowblocks, int Ls, int W, int H, int normalize, ScaleStat* __restrict__ stats,
                             unsigned* __restrict__ done_counter) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -119,9 +119,12 @@ __global__ void prep_kernel(PoseArgs a, PosePrepD* __restrict__ outd, const doub
     compose_T_d(r, t, a.invert[s] != 0, Rp, tp, aux);
     mat3_mul(a.K, Rp, KR);
     mat3_mul(KR, a.invK, A);
-    PosePrepD pd;
+    PoseStrip pd;
     for (int k = 0; k < 9; ++k) pd.dA[k] = A[k] - ((k % 4 == 0) ? 1.0 : 0.0);
     for (int i = 0; i < 3; ++i) pd.b[i] = a.K[3 * i] * tp[0] + a.K[3 * i + 1] * tp[1] + a.K[3 * i + 2] * tp[2];
+    pd.i2 = 1.0 + pd.dA[4];
+    pd.b3e = pd.b[2] + 1e-7;
+    pd.b0f = (float)pd.b[0]; pd.b1f = (float)pd.b[1]; pd.b3f = (float)pd.b3e; pd.pad = 0.0f;
     outd[idx] = pd;
     return;
   }

@@ -27,6 +27,16 @@ struct PosePrepD {  // the same constants in double: the geometric chain runs in
   double b[3];
 };
 
+// What the strip kernel reads per (item, source): PosePrepD plus the derived constants its row loop uses, so that --
+// served from the constant bank (STRIP_CONSTPOSE) -- they are operands, not registers.
+struct PoseStrip {
+  double dA[9];   // row-major
+  double b[3];
+  double i2;      // 1 + dA[4]: the row step of P'2
+  double b3e;     // b[2] + 1e-7 (src/utils.jl:101, in units of depth)
+  float b0f, b1f, b3f, pad;
+};
+
 struct ScaleStat {
   float inv_mp;  // 1 / (mean(disparity) + 1e-7), or 1 when the disparity is not normalised
   float cconst;  // constant added to every full-res disparity gradient (mean-normalisation term)
@@ -50,8 +60,9 @@ struct FusedArgs {
   float mind, dd;               // 1/max_depth, 1/min_depth - 1/max_depth
   double mind_d, dd_d;          // the same in double
   double rxd[MDB_MAX_SCALES], ryd[MDB_MAX_SCALES];
-  const PosePrepD* ppd;         // [N][S]
+  const PoseStrip* ppd;         // [N][S]
   float alpha, c1, c2;
+  float ksu, klu, kl, ka;       // loss / pullback factors (photo_strip.inl)
   float abs_tie;                // d|x|/dx at +0.0: 0 (sign(0) = 0) or 1 (ForwardDiff's Dual rule)
   int automask;
   float up;                     // 1 / (W H N_global Ls)

@@ -1,5 +1,6 @@
 // photo_fused_host.inl -- finalize kernels, up-sample transpose and the C-ABI entry of the fused loss
 #include <cmath>
+#include <mutex>
 namespace {
 
 // test hooks (mdb_debug_option): process-global, read on the host only, default 0 = off
@@ -446,7 +447,7 @@ inline StripGeom strip_geom(const mdb_loss_io* io, int num_sms) {
   g.nstrips = (io->W + STRIP_PX - 1) / STRIP_PX;
   const int sms = num_sms > 0 ? num_sms : 148;
   const long long base = (long long)io->N * io->Ls * g.nstrips;
-  const double resident = 13.0 * sms;
+  const double resident = (double)(65536 / (STRIP_MAXREG * 32)) * sms;   // warps the register file holds per SM
   int best_n = 1;
   if (g_dbg_strip_segs > 0) {
     best_n = std::min(g_dbg_strip_segs, std::max(1, io->H / 2));
@@ -476,7 +477,7 @@ FusedLayout fused_layout(const mdb_loss_io* io, int num_sms = 148) {
   L.npart = STRIP_NHEAD + NPOSE * io->S;
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off = mdb_align_up(off + bytes, 256); return o; };
-  L.o_ppd = take(sizeof(PosePrepD) * io->N * io->S);
+  L.o_ppd = take(sizeof(PoseStrip) * io->N * io->S);
   L.o_meanpart = take(sizeof(double) * (size_t)io->N * L.rowblocks * io->Ls);
   L.o_stats = take(sizeof(ScaleStat) * (size_t)io->Ls * io->N);
   L.records = L.strip.nsegs * L.strip.nstrips * io->Ls;
@@ -502,13 +503,65 @@ bool io_shape_ok(const mdb_loss_io* io) {
   return true;
 }
 
+#if STRIP_CONSTPOSE
+// Regions of c_pose (per device): handed out round-robin; an event per region orders "the last kernel that read it" before
+// "the next copy that overwrites it", also across streams.  During stream capture (mdb_slow_depth_create) the same ordering
+// is recorded as external event nodes, so every replay of the graph takes part in it.
+struct PosePool {
+  std::mutex mu;
+  cudaEvent_t ev[STRIP_CONST_POOL] = {nullptr};
+  bool used[STRIP_CONST_POOL] = {false};
+  int next = 0;
+};
+PosePool* pose_pool(int device) {
+  static PosePool pools[64];
+  return &pools[device & 63];
+}
+#endif
+
 template <int C, int S>
 int32_t launch_fused(mdb_handle* h, const FusedArgs& fa, const FusedLayout& L, cudaStream_t st) {
   constexpr size_t smem = (size_t)3 * (S * (2 * C + 2) / 4) * STRIP_THREADS * sizeof(float4);
-  const int blocks = (L.strip.total + STRIP_WARPS - 1) / STRIP_WARPS;
-  if (fa.dbg) photo_strip_kernel<C, S, true><<<blocks, STRIP_THREADS, smem, st>>>(fa, L.strip);
-  else photo_strip_kernel<C, S><<<blocks, STRIP_THREADS, smem, st>>>(fa, L.strip);
-  MDB_LAUNCHED(h);
+  StripGeom g = L.strip;
+  const int per_item = g.nsegs * g.nstrips * fa.Ls;
+#if STRIP_CONSTPOSE
+  const int chunk = STRIP_CONST_CHUNK / S;
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  MDB_CUDA(h, cudaStreamIsCapturing(st, &cap));
+  const bool capturing = cap != cudaStreamCaptureStatusNone;
+  PosePool* pool = pose_pool(h->device);
+#else
+  const int chunk = fa.N;
+#endif
+  for (int n0 = 0; n0 < fa.N; n0 += chunk) {
+    const int items = std::min(chunk, fa.N - n0);
+    g.n0 = n0;
+    g.total = items * per_item;
+    g.cbase = 0;
+#if STRIP_CONSTPOSE
+    int region;
+    cudaEvent_t ev;
+    {
+      std::lock_guard<std::mutex> lock(pool->mu);
+      region = pool->next;
+      pool->next = (pool->next + 1) % STRIP_CONST_POOL;
+      if (!pool->ev[region]) MDB_CUDA(h, cudaEventCreateWithFlags(&pool->ev[region], cudaEventDisableTiming));
+      ev = pool->ev[region];
+      if (pool->used[region]) MDB_CUDA(h, cudaStreamWaitEvent(st, ev, capturing ? cudaEventWaitExternal : cudaEventWaitDefault));
+      pool->used[region] = true;
+    }
+    g.cbase = region * STRIP_CONST_CHUNK;
+    MDB_CUDA(h, cudaMemcpyToSymbolAsync(c_pose, fa.ppd + (size_t)n0 * S, sizeof(PoseStrip) * items * S,
+                                        sizeof(PoseStrip) * g.cbase, cudaMemcpyDeviceToDevice, st));
+#endif
+    const int blocks = (g.total + STRIP_WARPS - 1) / STRIP_WARPS;
+    if (fa.dbg) photo_strip_kernel<C, S, true><<<blocks, STRIP_THREADS, smem, st>>>(fa, g);
+    else photo_strip_kernel<C, S><<<blocks, STRIP_THREADS, smem, st>>>(fa, g);
+    MDB_LAUNCHED(h);
+#if STRIP_CONSTPOSE
+    MDB_CUDA(h, cudaEventRecordWithFlags(ev, st, capturing ? cudaEventRecordExternal : cudaEventRecordDefault));
+#endif
+  }
   return MDB_OK;
 }
 
@@ -604,11 +657,15 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
   fa.dd_d = 1.0 / p->min_depth - 1.0 / p->max_depth;
   fa.mind = (float)fa.mind_d;
   fa.dd = (float)fa.dd_d;
-  fa.ppd = (const PosePrepD*)(ws + L.o_ppd);
+  fa.ppd = (const PoseStrip*)(ws + L.o_ppd);
   fa.alpha = p->alpha; fa.c1 = p->ssim_c1; fa.c2 = p->ssim_c2;
   fa.abs_tie = p->abs_subgradient ? 1.0f : 0.0f;
   const double up = 1.0 / ((double)W * H * Ng * Ls);
   fa.up = (float)up;
+  fa.ksu = p->alpha / (9.0f * io->C) * fa.up;
+  fa.klu = (1.0f - p->alpha) / io->C * fa.up;
+  fa.kl = (1.0f - p->alpha) / io->C;
+  fa.ka = p->alpha / io->C;
   fa.stats = (const ScaleStat*)(ws + L.o_stats);
   fa.partials = (float*)(ws + L.o_partials);
   fa.vis = io->vis_warp_loss;
@@ -634,7 +691,7 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
       MDB_LAUNCHED(h);
     }
     const int threads = N * S + Ls * N;
-    prep_kernel<<<(threads + 127) / 128, 128, 0, st>>>(pa, (PosePrepD*)(ws + L.o_ppd), mean_part, L.rowblocks, Ls, W, H,
+    prep_kernel<<<(threads + 127) / 128, 128, 0, st>>>(pa, (PoseStrip*)(ws + L.o_ppd), mean_part, L.rowblocks, Ls, W, H,
                                                        p->normalize_disparity, stats, (unsigned*)(ws + L.o_counter));
     MDB_LAUNCHED(h);
   }

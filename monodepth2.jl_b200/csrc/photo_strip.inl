@@ -21,6 +21,7 @@
 //
 // The two sources ride in the two halves of packed f32x2 registers (FFMA2/FADD2/FMUL2, new in
 // sm_100): one issue slot does the arithmetic of both sources.
+#include <type_traits>
 namespace {
 
 constexpr int STRIP_PX = 28;
@@ -31,9 +32,6 @@ constexpr int STRIP_WARPS = STRIP_NWARPS;   // warps per CTA (independent of eac
 constexpr int STRIP_THREADS = 32 * STRIP_WARPS;
 constexpr int SEL_NONE = 255;
 constexpr int STRIP_NHEAD = 3;   // record head: photometric sum, smoothness x-sum, smoothness y-sum
-#ifndef STRIP_UNROLL
-#define STRIP_UNROLL 1   // 3: the three-row rings rotate by renaming instead of ~90 MOVs per row
-#endif
 #ifndef STRIP_CBASE
 #define STRIP_CBASE 1   // one 64-bit base per channel plane: two more register pairs, one IMAD.WIDE per tap address (4.51 -> 4.47 ms)
 #endif
@@ -44,15 +42,38 @@ constexpr int STRIP_NHEAD = 3;   // record head: photometric sum, smoothness x-s
 #ifndef STRIP_DPF
 #define STRIP_DPF 1     // low-res disparity: the next native row is fetched one step ahead (its use no longer waits)
 #endif
-#ifndef STRIP_PIPE
-#define STRIP_PIPE 0   // software pipelining: issue the loads of row r+1 before stages C and D of row r (1; needs
-                       // STRIP_AM_EARLY=0) or between them (2)
+#ifndef STRIP_CONSTPOSE
+#define STRIP_CONSTPOSE 1   // the per-(item, source) projection constants are served from the constant bank: they reach the
+                            // FP64 pipe as uniform-register operands instead of occupying ~36 vector registers per thread.
+                            // With STRIP_PEEL this is what makes the 160-register build spill-free (4.33 -> 4.18 ms at config 5;
+                            // every spilling build of the peeled loop is SLOWER than the unpeeled one, profiles/r2_strip_summary.md)
+#endif
+#ifndef STRIP_HOSTK
+#define STRIP_HOSTK 0
+#endif
+#ifndef STRIP_FENCE
+#define STRIP_FENCE 0   // experiment: scheduling fences between the stages of the steady-state body (1: after A, 2: after A and C)
+#endif
+#ifndef STRIP_PEEL
+#define STRIP_PEEL 1   // the row loop body exists twice: a generic copy for the <= 6 rows at a segment's / the image's edges, and
+                       // a steady-state copy in which every row-position test is a compile-time constant (no reflection, no
+                       // clamps, no stage gating): fewer instructions and one long basic block for ptxas to schedule
 #endif
 #if !defined(STRIP_MAXREG) && !defined(STRIP_MINB)
-#define STRIP_MAXREG 152   // 13 warps per SM, no spills: measured best of 128 / 136 / 144 / 152 / 160 / 168 / 184
+#define STRIP_MAXREG 160   // 12 warps per SM, no spills.  Round 1 (unpeeled loop, constants in registers): best of 128 .. 184 was
+                           // 152.  Round 2 (peeled loop, constants in the bank): 152 spills 148 B (4.83 ms), 160 and 168 are
+                           // spill-free (4.18 / 4.20 ms), 176 .. 224 spill again (ptxas trades) -- spills decide, not the 13th warp
 #endif
 #ifndef STRIP_MINB
 #define STRIP_MINB 4   // CTAs per SM the register allocation aims for (128 registers; measured best of 2/3/4)
+#endif
+
+#if STRIP_CONSTPOSE
+// A launch covers at most STRIP_CONST_CHUNK (item, source) pairs and reads them from one of STRIP_CONST_POOL regions of
+// the bank; the host side (pose_pool, photo_fused_host.inl) hands the regions out round-robin and orders their reuse
+// with events, so calls on different streams of one device never see each other's constants.
+constexpr int STRIP_CONST_CHUNK = 128, STRIP_CONST_POOL = 3;
+__constant__ PoseStrip c_pose[STRIP_CONST_POOL * STRIP_CONST_CHUNK];
 #endif
 
 // ---- S floats packed: S = 2 uses the sm_100 f32x2 pipe ----------------------------------
@@ -98,7 +119,9 @@ template <int S> MDB_DEV Pk<S> operator+(Pk<S> a, float b) { return a + Pk<S>(b)
 MDB_DEV int geo_row(int r, int H) { return r == -1 ? 1 : (r == H ? H - 2 : r); }
 
 struct StripGeom {
-  int nstrips, nsegs, seg_rows, total;  // total = N * nsegs * nstrips * Ls warps
+  int nstrips, nsegs, seg_rows, total;  // total = items * nsegs * nstrips * Ls warps of THIS launch
+  int n0;                               // first item of this launch (a launch covers a chunk of the batch's items)
+  int cbase;                            // first entry of this launch's region of c_pose
 };
 
 // Decision dump (DBG instantiation only; tests/test_gpu_forced.py): every discrete choice the pullback
@@ -129,11 +152,12 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   const int lane = threadIdx.x & 31, warp = __shfl_sync(MDB_FULL, (int)(threadIdx.x >> 5), 0);
   int w = blockIdx.x * STRIP_WARPS + warp;
   if (w >= g.total) return;
-  const int rec = w;
+  const int rec = g.n0 * (g.nsegs * g.nstrips * a.Ls) + w;   // record index in the whole batch
   const int sc = w % a.Ls; w /= a.Ls;
   const int strip = w % g.nstrips; w /= g.nstrips;
   const int seg = w % g.nsegs;
-  const int n = w / g.nsegs;
+  const int nl_item = w / g.nsegs;        // item inside this launch's chunk
+  const int n = g.n0 + nl_item;
 
   const int W = a.W, H = a.H;
   const size_t plane = (size_t)W * H;
@@ -183,19 +207,20 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
 
   // ---- per-lane projection state: P' = A q + invd b, q = [px, py, 1], A = I + dA -------------
   // p_i = A_i . q is carried down the rows by adding column 1 of A (double: no drift that matters)
-  double p1[S], p2[S], p3[S], i1[S], i2[S], i3[S], b0[S], b1[S], b3e[S];
-  float b0f[S], b1f[S], b3f[S];
+  double p1[S], p2[S], p3[S];
+#if STRIP_CONSTPOSE
+  const PoseStrip* const ppn = c_pose + g.cbase + nl_item * S;   // constant bank, warp-uniform index: operands, not registers
+#else
+  const PoseStrip* const ppn = a.ppd + (size_t)n * S;
+#endif
   {
     const double px = (double)(gx + 1), py = (double)(geo_row(Y0 - 2, H) + 1);
 #pragma unroll
     for (int s = 0; s < S; ++s) {
-      const PosePrepD& pp = a.ppd[(size_t)n * S + s];
+      const PoseStrip& pp = ppn[s];
       p1[s] = fma(1.0 + pp.dA[0], px, fma(pp.dA[1], py, pp.dA[2]));
-      p2[s] = fma(pp.dA[3], px, fma(1.0 + pp.dA[4], py, pp.dA[5]));
+      p2[s] = fma(pp.dA[3], px, fma(pp.i2, py, pp.dA[5]));
       p3[s] = fma(pp.dA[6], px, fma(pp.dA[7], py, 1.0 + pp.dA[8]));
-      i1[s] = pp.dA[1]; i2[s] = 1.0 + pp.dA[4]; i3[s] = pp.dA[7];
-      b0[s] = pp.b[0]; b1[s] = pp.b[1]; b3e[s] = pp.b[2] + 1e-7;
-      b0f[s] = (float)b0[s]; b1f[s] = (float)b1[s]; b3f[s] = (float)b3e[s];
     }
   }
   // bilinear up-sampling of the disparity (align-corners): the column part is per lane
@@ -214,9 +239,14 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
     ux1 = min(ux0 + 1, dw - 1);
   }
 
+#if STRIP_HOSTK
+  // experiment: the four factors formed on the host and read as constant-bank operands
+  const float ksu = a.ksu, klu = a.klu, kl = a.kl, ka = a.ka;
+#else
   const float ksu = a.alpha / (9.0f * C) * a.up;   // SSIM pullback factor alpha / C / 9, times 1/(W H N Ls)
   const float klu = (1.0f - a.alpha) / C * a.up;   // L1 factor
   const float kl = (1.0f - a.alpha) / C, ka = a.alpha / C;
+#endif
   const ScaleStat st = a.stats[(size_t)sc * a.N + n];
   const float skx = st.inv_mp * a.kx[sc], sky = st.inv_mp * a.ky[sc];
 
@@ -239,7 +269,7 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
 
   int slot = 0;  // ring slot of row r in s_drv
 
-  // ---- stage A in two halves, so that (STRIP_PIPE) the loads of row r+1 fly during C and D of row r ----
+  // ---- stage A in two halves: issue() starts the row's loads, consume() runs after the smoothness block ----
   // in flight between issue() and consume(): 4 taps x C channels (sources packed), the target row,
   // the bilinear weights and masks
   P tv00[C], tv01[C], tv10[C], tv11[C];
@@ -252,9 +282,10 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   const int gxc = min(max(gx, 0), W - 1);   // loads of dead lanes / rows go to a clamped (valid) address
   if (native) dq = ldg(dsp + (min(max(geo_row(Y0 - 2, H), 0), H - 1) * W + gxc));
 
-  auto issue = [&](int r) {
-    const int rg = geo_row(r, H), rgn = geo_row(r + 1, H);   // warp-uniform
-    const int rc = min(max(rg, 0), H - 1);
+  auto issue = [&](int r, auto steady) {
+    constexpr bool ST = decltype(steady)::value;   // steady-state row: 0 <= r, r + 1 <= H - 1, nothing reflected or clamped
+    const int rg = ST ? r : geo_row(r, H), rgn = ST ? r + 1 : geo_row(r + 1, H);   // warp-uniform
+    const int rc = ST ? r : min(max(rg, 0), H - 1);
     {   // unconditional (clamped addresses): nothing in flight is carried from one row to the next
       double dd_;
       if (native) {
@@ -299,7 +330,7 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
 #pragma unroll
       for (int c = 0; c < C; ++c) ty_[c] = ldg(xb + (unsigned)(tgt_off + c * planei + rc * W + gxc));
 #if STRIP_AM_EARLY
-      if (a.automask) tam = ldg(amb + (unsigned)(min(max(r - 1, 0), H - 1) * W + gxc));   // window row r-1, used in stage C
+      if (a.automask) tam = ldg(amb + (unsigned)((ST ? r - 1 : min(max(r - 1, 0), H - 1)) * W + gxc));   // window row r-1, used in stage C
 #endif
 
       unsigned ot[S];   // top-left tap; the other three are +1, +W, +W+1 (x0 <= W-2, y0 <= H-2 always)
@@ -307,7 +338,7 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
       for (int s = 0; s < S; ++s) {
         // Backproject -> Project -> normalize -> grid_sample's unnormalize (src/utils.jl:67-69,
         // 99-103; src/training.jl:56) cancel to u = P'1 / z'', z'' = P'3 + invd 1e-7 (in units of depth)
-        const double P1 = fma(invd, b0[s], p1[s]), P2 = fma(invd, b1[s], p2[s]), z = fma(invd, b3e[s], p3[s]);
+        const double P1 = fma(invd, ppn[s].b[0], p1[s]), P2 = fma(invd, ppn[s].b[1], p2[s]), z = fma(invd, ppn[s].b3e, p3[s]);
         double zi;
         asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(zi) : "d"(z));   // MUFU.RCP64H: ~2^-20, squared by the Newton step
         zi = fma(zi, fma(-z, zi, 1.0), zi);
@@ -357,10 +388,15 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
       }
 #endif
     }
-    if (native) dq = ldg(dsp + (min(max(rgn, 0), H - 1) * W + gxc));
-    const double stp = (double)(rgn - rg);   // 1 except around the two reflected rows
+    if (native) dq = ldg(dsp + ((ST ? rgn : min(max(rgn, 0), H - 1)) * W + gxc));
+    if (ST) {
 #pragma unroll
-    for (int s = 0; s < S; ++s) { p1[s] = fma(stp, i1[s], p1[s]); p2[s] = fma(stp, i2[s], p2[s]); p3[s] = fma(stp, i3[s], p3[s]); }
+      for (int s = 0; s < S; ++s) { p1[s] += ppn[s].dA[1]; p2[s] += ppn[s].i2; p3[s] += ppn[s].dA[7]; }
+    } else {
+      const double stp = (double)(rgn - rg);   // 1 except around the two reflected rows
+#pragma unroll
+      for (int s = 0; s < S; ++s) { p1[s] = fma(stp, ppn[s].dA[1], p1[s]); p2[s] = fma(stp, ppn[s].i2, p2[s]); p3[s] = fma(stp, ppn[s].dA[7], p3[s]); }
+    }
   };
 
   // bilinear value and its derivatives of the issued row -> xn, yn, dn; park the derivatives in `wslot`
@@ -410,31 +446,22 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
     d3 = d2; d2 = d1; d1 = dn;
     slot = (slot + 1) % 3;
   };
-#if STRIP_PIPE
-  issue(Y0 - 2);
-  consume(slot, xn, yn, dn);
-#endif
-  constexpr int kUnroll = STRIP_UNROLL;
-#pragma unroll kUnroll
-  for (int r = Y0 - 2; r <= Y1 + 1; ++r) {
-#if STRIP_PIPE == 1
-    if (r < Y1 + 1) issue(r + 1);   // its loads are consumed after C and D below
-#elif STRIP_PIPE == 0
-    issue(r);
-#endif
+  auto row = [&](int r, auto steady) {
+    constexpr bool ST = decltype(steady)::value;
+    issue(r, steady);
     // ---- smoothness of pixel row r-2 (src/utils.jl:163-177): needs nothing of row r, so it runs in the
     // shadow of the loads just issued; one register (its pullback) crosses stages C and D
     const int pr = r - 2;
     float gsm = 0.0f;
     {
       const float wy_up = wy_dn;
-      if (r >= Y0 + 1) {  // weight between rows r-2 and r-1 (and wy_up of the next iteration)
+      if (ST || r >= Y0 + 1) {  // weight between rows r-2 and r-1 (and wy_up of the next iteration)
         float e = 0.0f;
 #pragma unroll
         for (int c = 0; c < C; ++c) e += fabsf(yr2[c] - yr1[c]);
-        wy_dn = (pr >= 0 && pr + 1 < H) ? __expf(-e * (1.0f / C)) : 0.0f;
+        wy_dn = (ST || (pr >= 0 && pr + 1 < H)) ? __expf(-e * (1.0f / C)) : 0.0f;
       }
-      if (r >= Y0 + 2) {  // warp-uniform; pr in [Y0, Y1)
+      if (ST || r >= Y0 + 2) {  // warp-uniform; pr in [Y0, Y1)
         const float dl = __shfl_sync(MDB_FULL, d2, max(lane - 1, 0)), dr = __shfl_sync(MDB_FULL, d2, min(lane + 1, 31));
         float ex = 0.0f;
 #pragma unroll
@@ -454,16 +481,15 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
         }
       }
     }
-#if !STRIP_PIPE
     consume(slot, xn, yn, dn);
-#endif
+    if (ST && STRIP_FENCE >= 1) asm volatile("bar.warp.sync 0xffffffff;" ::: "memory");
 
     // =========================== C: window row r-1 =============================================
     const int wr = r - 1;
     seln = SEL_NONE;
 #pragma unroll
     for (int k = 0; k < 3 * C; ++k) Fn[k] = 0.0f;
-    if (r >= Y0 && wr >= 0 && wr < H) {             // warp-uniform
+    if (ST || (r >= Y0 && wr >= 0 && wr < H)) {             // warp-uniform
       // pad_reflect(1) along H (src/utils.jl:30-31) costs nothing here: the rows -1 and H that the ring
       // delivers ARE rows 1 and H-2 (geo_row below), so the first and last window read top / bottom as usual
 #if STRIP_AM_EARLY
@@ -558,26 +584,24 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
         }
         Fn[3 * c] = fa; Fn[3 * c + 1] = fb; Fn[3 * c + 2] = fc;   // SEL_NONE windows are gated out by the row masks in D
       }
-      if (DBG && pcol && wr >= Y0 && wr < Y1) {
+      if (DBG && pcol && (ST || (wr >= Y0 && wr < Y1))) {
         const size_t o = (size_t)wr * W + gx;
         dbg[o] = best == SEL_NONE ? (signed char)-1 : (signed char)best;
 #pragma unroll
         for (int c = 0; c < C; ++c)
           dbg[(size_t)(1 + c) * plane + o] = best == SEL_NONE ? (signed char)1 : (signed char)(dbg_ins[c].get(best == SEL_NONE ? 0 : best) != 0.0f);
       }
-      if (pcol && wr >= Y0 && wr < Y1) {
+      if (pcol && (ST || (wr >= Y0 && wr < Y1))) {
         loss_acc += val;
         if (a.vis && sc == a.Ls - 1) a.vis[(size_t)n * plane + (size_t)wr * W + gx] = val;
       }
     }
 
-#if STRIP_PIPE == 2
-    if (r < Y1 + 1) issue(r + 1);   // in flight during stage D only; consumed at the end of the iteration
-#endif
+    if (ST && STRIP_FENCE >= 2) asm volatile("bar.warp.sync 0xffffffff;" ::: "memory");
     // =========================== D: pixel row r-2 ==============================================
-    if (r >= Y0 + 2) {  // warp-uniform; pr in [Y0, Y1)
+    if (ST || r >= Y0 + 2) {  // warp-uniform; pr in [Y0, Y1)
       // box sums of the coefficient fields over the 3x3 windows containing this pixel, per source
-      const float wu = (pr == 1) ? 2.0f : 1.0f, wd = (pr == H - 2) ? 2.0f : 1.0f;
+      const float wu = (!ST && pr == 1) ? 2.0f : 1.0f, wd = (!ST && pr == H - 2) ? 2.0f : 1.0f;
       P ma, mb, mc;   // row weights gated by which source won the window
 #pragma unroll
       for (int s = 0; s < S; ++s) {
@@ -631,7 +655,7 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
         float dinvd = 0.0f;
 #pragma unroll
         for (int s = 0; s < S; ++s)
-          dinvd += dP0.get(s) * b0f[s] + dP1.get(s) * b1f[s] + dP2.get(s) * b3f[s];
+          dinvd += dP0.get(s) * ppn[s].b0f + dP1.get(s) * ppn[s].b1f + dP2.get(s) * ppn[s].b3f;
         // d invd / d disparity = 1/min_depth - 1/max_depth; plus the smoothness pullback formed above
         // (the mean-normalisation constant is added after the item's sum is known)
         gout[(size_t)pr * W + gx] = fmaf(dinvd, a.dd, gsm);
@@ -639,9 +663,20 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
     }
 
     rotate();
-#if STRIP_PIPE
-    if (r < Y1 + 1) consume(slot, xn, yn, dn);
-#endif
+  };
+  {
+    // steady-state rows: all three stages active (r >= Y0 + 2), window row r-1 and pixel row r-2 inside this segment
+    // (r <= Y1), no reflected row in sight (pixel row >= 2 and <= H-3, r + 1 <= H - 1)
+    const int s_lo = max(Y0 + 2, 4), s_hi = STRIP_PEEL ? min(Y1, H - 2) : -1000000;
+    int r = Y0 - 2;
+    while (r <= Y1 + 1) {
+      if (STRIP_PEEL && r >= s_lo && r <= s_hi) {
+        for (; r <= s_hi; ++r) row(r, std::true_type{});
+      } else {
+        row(r, std::false_type{});
+        ++r;
+      }
+    }
   }
 
   // ---- one record per warp: loss + 12 pose sums per source (no atomics) -------------------------

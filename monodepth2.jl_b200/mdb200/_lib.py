@@ -10,7 +10,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmdb200.so")
+# MDB200_LIB: development hook (tools/sweep_variants.sh builds the library with other -D settings and times them)
+LIB_PATH = os.environ.get("MDB200_LIB") or os.path.join(_HERE, "libmdb200.so")
 
 MAX_SCALES = 8
 MAX_SOURCES = 2

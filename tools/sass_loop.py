@@ -14,8 +14,10 @@ for line in sass.splitlines():
         m = re.match(r'\s+/\*([0-9a-f]{4,})\*/\s+(.*?);', line)
         if m: rows.append((int(m.group(1), 16), m.group(2).strip()))
 back = [(a, int(re.search(r'0x([0-9a-f]+)', t).group(1), 16)) for a, t in rows if t.split()[0].startswith(('BRA', '@')) and 'BRA' in t and re.search(r'0x([0-9a-f]+)', t) and int(re.search(r'0x([0-9a-f]+)', t).group(1), 16) < a]
-# the row loop is the longest backward branch
-a, tgt = max(back, key=lambda p: p[0] - p[1])
+# the steady-state row loop: the innermost of the long backward branches (the outer one also spans the generic copy of the
+# body that the <= 6 edge rows of a segment run, STRIP_PEEL)
+long_ = [p for p in back if (p[0] - p[1]) // 16 > 500]
+a, tgt = min(long_, key=lambda p: p[0] - p[1])
 body = [t for ad, t in rows if tgt <= ad <= a]
 print(f'total {len(rows)} instr; row loop {len(body)} instr (0x{tgt:x}..0x{a:x})')
 h = collections.Counter(re.sub(r'^@!?U?P\d+\s+', '', t).split()[0].split('.')[0] for t in body)
