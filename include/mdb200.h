@@ -234,6 +234,38 @@ int32_t mdb_train_loss_strip_geometry(const mdb_loss_io* io, int32_t* out4);
 int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_loss_params* p,
                               void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- train_loss for inputs in HOST memory (the reference: `transfer(x)` = gpu . f32, src/utils.jl:1-3, then
+ * train_loss).  A plan cuts the batch into chunks of items and pipelines host->device copies, the fused loss and the
+ * device->host drain of the disparity gradients over three streams, one cudaMemcpyAsync per array and chunk; every chunk
+ * is one mdb_train_loss_fwdbwd with n_global = the whole batch, so chunk losses add.  All pointers of mdb_host_io are
+ * HOST pointers (pinned memory gives the full PCIe rate); layouts as in mdb_loss_io.  x_format 0: x is the float32
+ * (W,H,C,L,N) stack; 1: x is uint8 triplet strips [N][H][3W][3] converted on the device (mdb_ingest_triplet_u8, L = 3),
+ * `flip` NULL or N bytes.  chunk_items <= 0 picks N/8 but at least ~16 MB of input per chunk.  first_item >= 0: the
+ * batch is a shard of params.n_global items starting there; the call then ends with the path's all-reduce
+ * (mdb_comm_* must be set up on the handle) and d_rvec / d_tvec receive the GLOBAL (3,n_global) gradients, loss the
+ * global loss; the disparity gradients stay the shard's.  The plan owns its device buffers (cudaMalloc at create).
+ * mdb_train_loss_host returns when every result is in host memory.                                               */
+typedef struct mdb_host_plan mdb_host_plan;
+typedef struct mdb_host_io {
+  const void* x;
+  const uint8_t* flip;
+  const float* disparity[MDB_MAX_SCALES];
+  const float* rvec[MDB_MAX_SOURCES];
+  const float* tvec[MDB_MAX_SOURCES];
+  const float* auto_loss;
+  float* loss;                          /* 1 float */
+  float* d_disparity[MDB_MAX_SCALES];
+  float* d_rvec[MDB_MAX_SOURCES];
+  float* d_tvec[MDB_MAX_SOURCES];
+} mdb_host_io;
+int32_t mdb_host_plan_create(mdb_handle* h, const mdb_loss_io* shape /* sizes, ids, K; pointers ignored */,
+                             const mdb_loss_params* params, int32_t chunk_items, int32_t x_format, int32_t first_item,
+                             mdb_host_plan** out);
+int32_t mdb_train_loss_host(mdb_host_plan* plan, const mdb_host_io* io, void* stream);
+/* out4 = { chunks, host->device bytes per call, device->host bytes per call, items d_rvec / d_tvec cover }      */
+int32_t mdb_host_plan_info(const mdb_host_plan* plan, int64_t* out4);
+int32_t mdb_host_plan_destroy(mdb_host_plan* plan);
+
 /* ---- the batch sharded over the GPUs of one box ------------------------------------------
  * The reference is single-GPU; the only coupling between items is the mean over N (src/training.jl:69,
  * src/utils.jl:176).  Rank r evaluates its contiguous shard with params.n_global = N_global, so shard losses

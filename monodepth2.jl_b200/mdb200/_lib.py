@@ -49,6 +49,19 @@ class LossIO(C.Structure):
     ]
 
 
+class HostIO(C.Structure):
+    """mdb_host_io: HOST pointers of one mdb_train_loss_host call."""
+    _fields_ = [
+        ("x", C.c_void_p), ("flip", C.c_void_p),
+        ("disparity", C.c_void_p * MAX_SCALES),
+        ("rvec", C.c_void_p * MAX_SOURCES), ("tvec", C.c_void_p * MAX_SOURCES),
+        ("auto_loss", C.c_void_p),
+        ("loss", C.c_void_p),
+        ("d_disparity", C.c_void_p * MAX_SCALES),
+        ("d_rvec", C.c_void_p * MAX_SOURCES), ("d_tvec", C.c_void_p * MAX_SOURCES),
+    ]
+
+
 class AdamParams(C.Structure):
     """mdb_adam_params (Flux ADAM defaults; eta from src/simple_depth.jl:16)."""
     _fields_ = [("eta", C.c_double), ("beta1", C.c_double), ("beta2", C.c_double), ("eps", C.c_double)]
@@ -143,6 +156,10 @@ PROTOTYPES = {
     "mdb_item_mean": (_i32, [_vp, _vp, _i64, _i32, _vp, _vp]),
     "mdb_measure_fp32_peak": (_i32, [_vp, _vp, _sz, _i32, C.POINTER(_f64), C.POINTER(_f64), _vp]),
     "mdb_debug_option": (_i32, [C.c_char_p, _i64]),
+    "mdb_host_plan_create": (_i32, [_vp, C.POINTER(LossIO), C.POINTER(LossParams), _i32, _i32, _i32, C.POINTER(_vp)]),
+    "mdb_train_loss_host": (_i32, [_vp, C.POINTER(HostIO), _vp]),
+    "mdb_host_plan_info": (_i32, [_vp, C.POINTER(_i64)]),
+    "mdb_host_plan_destroy": (_i32, [_vp]),
     "mdb_packed_size": (_i64, [_i32, _i32]),
     "mdb_packed_bind": (_i32, [C.POINTER(LossIO), _vp, _i32, _i32]),
     "mdb_comm_get_unique_id": (_i32, [_vp, _sz]),

@@ -859,160 +859,103 @@ class HostLossResult:
 
 
 class HostLoss:
-    """`train_loss` value + gradients for inputs that live in (pinned) HOST memory.
-
-    The batch is cut into chunks of `chunk` items; chunk k+1 is copied host->device on a copy
-    stream while chunk k runs on the compute stream and chunk k-1's gradients drain
-    device->host on a third stream, so the step costs about max(PCIe, compute) instead of
-    their sum.  Every chunk is one `mdb_train_loss_fwdbwd` call with `n_global = N`, the same
-    contract the multi-GPU shards use, so chunk losses simply add."""
+    """`train_loss` value + gradients for inputs that live in (pinned) HOST memory: the Python face of the C entry
+    `mdb_train_loss_host` (csrc/host_pipeline.cu), which cuts the batch into chunks and pipelines host->device
+    copies, the fused loss and the device->host drain over three streams.  Every chunk is one
+    `mdb_train_loss_fwdbwd` with `n_global = N`, the contract the multi-GPU shards use."""
 
     def __init__(self, *, W, H, C, L, N, disp_sizes, scales, target_id, source_ids, K, invK, chunk=None,
-                 automasking=False, n_global=0, device=None, x_format="f32", ramp_up=None, packed=None, **kw):
+                 automasking=False, n_global=0, device=None, x_format="f32", packed=None, min_depth=0.1, max_depth=100.0,
+                 disparity_smoothness=1e-3, normalize_disparity=True, smooth_weight_mode=0, alpha=0.85, abs_subgradient=0):
         """x_format "f32": x is the Float32 (N,L,C,H,W) stack.  "u8_strip": x is the dataset's own format,
         uint8 (N,H,3W,3) decoded triplet strips (src/dtk.jl:29-46) -- a quarter of the PCIe bytes; the
-        device converts with mdb_ingest_triplet_u8 (C = 1: Gray luma)."""
-        """packed: a `mdb200.dist.PackedGrads` of a batch sharded over ranks -- the chunks then write their pose
-        gradients into the rank's slots of its send buffer, the call ends with the path's all-reduce and returns the
-        GLOBAL loss and pose gradients (disparity gradients stay this rank's shard)."""
+        device converts with mdb_ingest_triplet_u8 (C = 1: Gray luma).
+        packed: a `mdb200.dist.PackedGrads` of a batch sharded over ranks -- the call then ends with the path's
+        all-reduce and returns the GLOBAL loss and pose gradients (disparity gradients stay this rank's shard)."""
         if x_format not in ("f32", "u8_strip"):
             raise ValueError("x_format must be 'f32' or 'u8_strip'")
-        self.packed = packed
         if x_format == "u8_strip" and L != 3:
             raise ValueError("triplet strips hold L = 3 frames")
         self.x_format = x_format
-        if not chunk or chunk <= 0:
-            chunk = self.default_chunk(W, H, C, L, N, disp_sizes, automasking, x_format)
-        if ramp_up is None:
-            ramp_up = x_format == "u8_strip"
         self.dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         self.N, self.L, self.C, self.H, self.W = N, L, C, H, W
         self.S = len(source_ids)
         self.disp_sizes = [(int(w), int(h)) for (w, h) in disp_sizes]
         self.automasking = automasking
-        # Pipeline shape.  The step is bound by the host->device copy, so compute always finishes a chunk
-        # before the next one has arrived; what is NOT hidden is the work on the LAST chunk after its copy
-        # lands.  Hence chunks of `chunk` items and a geometric tail (half, quarter, ... down to 1 item).
-        sizes, left = [], N
-        if ramp_up:            # compute-bound pipelines (uint8 input): start computing after one item has arrived
-            z = 1
-            while z < chunk and left - z > chunk:
-                sizes.append(z); left -= z; z *= 2
-        while left > chunk:
-            sizes.append(chunk); left -= chunk
-        while left > 1:
-            half = (left + 1) // 2
-            sizes.append(half); left -= half
-        if left == 1:
-            sizes.append(1)
-        self.chunks, s0 = [], 0
-        for z in sizes:
-            self.chunks.append((s0, s0 + z)); s0 += z
-        ng = n_global if n_global > 0 else N
-        f32 = dict(device=self.dev, dtype=torch.float32)
+        p = _lib.LossParams()
+        lib.mdb_loss_params_default(ct.byref(p))
+        p.min_depth, p.max_depth, p.disparity_smoothness, p.alpha = min_depth, max_depth, disparity_smoothness, alpha
+        p.automasking, p.normalize_disparity, p.smooth_weight_mode = int(automasking), int(normalize_disparity), int(smooth_weight_mode)
+        p.n_global = int(packed.N if packed is not None else (n_global if n_global > 0 else N))
+        p.abs_subgradient = int(abs_subgradient)
+        io = _lib.LossIO()
+        io.W, io.H, io.C, io.L, io.N = W, H, C, L, N
+        io.target_id, io.S, io.Ls = int(target_id), self.S, len(scales)
+        for s, sid in enumerate(source_ids):
+            io.source_ids[s], io.invert[s] = int(sid), int(sid < target_id)
+        for k, ((w, h), sc) in enumerate(zip(self.disp_sizes, scales)):
+            io.dw[k], io.dh[k], io.scale[k] = w, h, float(sc)
+        kk, ik = _k9(K), _k9(invK)
+        for i in range(9):
+            io.K[i], io.invK[i] = kk[i], ik[i]
+        self.params, self.io = p, io
+        self._h = ct.c_void_p()
         with torch.cuda.device(self.dev):
-            self.copy_in, self.copy_out = torch.cuda.Stream(), torch.cuda.Stream()
-            # whole-batch device buffers; every chunk's plan reads and writes row slices of them, so the
-            # per-chunk host work is 1 + Ls copies in, one launch sequence, Ls copies out
-            self.d_x = torch.empty((N, L, C, H, W), **f32)
-            self.d_d = [torch.empty((N, 1, h, w), **f32) for (w, h) in self.disp_sizes]
-            self.d_rv = [torch.empty((N, 3), **f32) for _ in range(self.S)]
-            self.d_tv = [torch.empty((N, 1, 3), **f32) for _ in range(self.S)]
-            self.d_a = torch.empty((N, 1, H, W), **f32) if automasking else None
-            self.g_d = [torch.empty((N, 1, h, w), **f32) for (w, h) in self.disp_sizes]
-            if packed is None:
-                self.g_rv = [torch.empty((N, 3), **f32) for _ in range(self.S)]
-                self.g_tv = [torch.empty((N, 1, 3), **f32) for _ in range(self.S)]
-            else:
-                if packed.n != N or packed.S != self.S:
-                    raise ValueError("packed was made for another shard size / source count")
-                po = packed.out()
-                self.g_rv, self.g_tv = po["d_rvec"], po["d_tvec"]
-            self.g_loss = torch.zeros((len(self.chunks),), **f32)
-            self.d_u8 = torch.empty((N, H, 3 * W, 3), device=self.dev, dtype=torch.uint8) if x_format == "u8_strip" else None
-            self.d_flip = torch.zeros((N,), device=self.dev, dtype=torch.uint8) if x_format == "u8_strip" else None
-            self.plans = []
-            for k, (a, b) in enumerate(self.chunks):
-                out = dict(loss=self.g_loss[k:k + 1], d_disp=[t[a:b] for t in self.g_d],
-                           d_rvec=[t[a:b] for t in self.g_rv], d_tvec=[t[a:b] for t in self.g_tv])
-                self.plans.append(FusedLoss(W=W, H=H, C=C, L=L, N=b - a, disp_sizes=disp_sizes, scales=scales,
-                                            target_id=target_id, source_ids=source_ids, K=K, invK=invK,
-                                            automasking=automasking, n_global=ng, device=self.dev, out=out, **kw))
+            hd = handle(self.dev.index)
+            check(hd, lib.mdb_host_plan_create(hd, ct.byref(io), ct.byref(p), int(chunk or 0), 1 if x_format == "u8_strip" else 0,
+                                               int(packed.lo) if packed is not None else -1, ct.byref(self._h)))
+        info = (ct.c_int64 * 4)()
+        lib.mdb_host_plan_info(self._h, info)
+        self.n_chunks, self.h2d_bytes, self.d2h_bytes, self.n_pose = int(info[0]), int(info[1]), int(info[2]), int(info[3])
         pin = dict(dtype=torch.float32, pin_memory=True)
-        self.h_loss = torch.empty((len(self.chunks),), **pin)
+        self.h_loss = torch.empty((1,), **pin)
         self.h_dd = [torch.empty((N, 1, h, w), **pin) for (w, h) in self.disp_sizes]
-        ngl = packed.N if packed is not None else N
-        self.h_dr = [torch.empty((ngl, 3), **pin) for _ in range(self.S)]
-        self.h_dt = [torch.empty((ngl, 1, 3), **pin) for _ in range(self.S)]
-        self.h_packed = torch.empty((packed.send.numel(),), **pin) if packed is not None else None
-        x_bytes = 4 * N * L * C * H * W if x_format == "f32" else N * H * 3 * W * 3 + N
-        self.h2d_bytes = x_bytes + 4 * (sum(N * w * h for (w, h) in self.disp_sizes) + 6 * N * self.S
-                                        + (N * H * W if automasking else 0))
-        self.d2h_bytes = 4 * (sum(N * w * h for (w, h) in self.disp_sizes)
-                              + (packed.send.numel() if packed is not None else len(self.chunks) + 6 * N * self.S))
+        self.h_dr = [torch.empty((self.n_pose, 3), **pin) for _ in range(self.S)]
+        self.h_dt = [torch.empty((self.n_pose, 1, 3), **pin) for _ in range(self.S)]
 
     @staticmethod
     def default_chunk(W, H, C, L, N, disp_sizes, automasking=False, x_format="f32") -> int:
-        """Items per pipeline chunk: an eighth of the batch, but never chunks so small that the ~15 stream
-        operations a chunk costs on the host outweigh the copy they overlap (>= ~16 MB of input per chunk)."""
+        """Items per pipeline chunk the C entry picks for chunk_items <= 0: an eighth of the batch, but never chunks so
+        small that the stream operations a chunk costs on the host outweigh the copy they overlap (>= ~16 MB)."""
         per_item = (4 * L * C * H * W if x_format == "f32" else 9 * H * W) \
             + 4 * (sum(w * h for (w, h) in disp_sizes) + (H * W if automasking else 0))
-        return max(1, N // 8, min(N, -(-16 * 2 ** 20 // per_item)))
+        return max(1, N // 8, min(N, 16 * 2 ** 20 // per_item + 1))
 
     def __call__(self, x, disparities, rvecs, tvecs, auto_loss=None, flips=None) -> HostLossResult:
         """All arguments are HOST tensors (pinned for full PCIe rate): float32, except x in the
         "u8_strip" format (uint8 (N,H,3W,3)) and its optional `flips` (uint8 (N,), FlipX per sample)."""
-        compute = torch.cuda.current_stream(self.dev)
-        self.copy_in.wait_stream(compute)
-        self.copy_out.wait_stream(compute)
-        u8 = self.x_format == "u8_strip"
-        with torch.cuda.stream(self.copy_in):     # 6 floats per item and source: whole batch at once
-            for s in range(self.S):
-                self.d_rv[s].copy_(rvecs[s].reshape(self.N, 3), non_blocking=True)
-                self.d_tv[s].copy_(tvecs[s].reshape(self.N, 1, 3), non_blocking=True)
-            if u8 and flips is not None:
-                self.d_flip.copy_(flips, non_blocking=True)
-        for k, (a, b) in enumerate(self.chunks):
-            with torch.cuda.stream(self.copy_in):
-                (self.d_u8 if u8 else self.d_x)[a:b].copy_(x[a:b], non_blocking=True)
-                for j, d in enumerate(disparities):
-                    self.d_d[j][a:b].copy_(d[a:b], non_blocking=True)
-                if self.automasking:
-                    self.d_a[a:b].copy_(auto_loss[a:b], non_blocking=True)
-                ready = self.copy_in.record_event()
-            compute.wait_event(ready)
-            if u8:
-                ingest_triplet_u8(self.d_u8[a:b], self.W, self.d_flip[a:b] if flips is not None else None,
-                                  grayscale=(self.C == 1), out=self.d_x[a:b])
-            self.plans[k](self.d_x[a:b], [t[a:b] for t in self.d_d],
-                          [Pose(r[a:b], t[a:b]) for r, t in zip(self.d_rv, self.d_tv)],
-                          self.d_a[a:b] if self.automasking else None)
-            done = compute.record_event()
-            with torch.cuda.stream(self.copy_out):
-                self.copy_out.wait_event(done)
-                for j in range(len(self.disp_sizes)):
-                    self.h_dd[j][a:b].copy_(self.g_d[j][a:b], non_blocking=True)
-        if self.packed is not None:               # sharded batch: chunk losses -> slot 0, then the path's one all-reduce
-            from . import dist as mdist
-            pg = self.packed
-            torch.sum(self.g_loss, dim=0, keepdim=True, out=pg.send[0:1])
-            mdist.allreduce(pg)
-            done = compute.record_event()
-            with torch.cuda.stream(self.copy_out):
-                self.copy_out.wait_event(done)
-                self.h_packed.copy_(pg.recv, non_blocking=True)
-            self.copy_out.synchronize()
-            compute.wait_stream(self.copy_out)
-            loss, rv, tv = mdist.unpack(self.h_packed, pg.N, pg.S)
-            return HostLossResult(float(loss), self.h_dd, rv, tv)
-        with torch.cuda.stream(self.copy_out):    # the small results once, after the last chunk
-            self.h_loss.copy_(self.g_loss, non_blocking=True)
-            for s in range(self.S):
-                self.h_dr[s].copy_(self.g_rv[s], non_blocking=True)
-                self.h_dt[s].copy_(self.g_tv[s], non_blocking=True)
-        self.copy_out.synchronize()
-        compute.wait_stream(self.copy_out)
-        return HostLossResult(float(self.h_loss.sum()), self.h_dd, self.h_dr, self.h_dt)
+        hio = _lib.HostIO()
+        keep = []
+
+        def hp(t, dt=torch.float32):
+            if t.is_cuda or t.dtype != dt or not t.is_contiguous():
+                raise TypeError("host pipeline arguments must be contiguous HOST tensors of the documented dtype")
+            keep.append(t)
+            return t.data_ptr()
+        hio.x = hp(x, torch.uint8 if self.x_format == "u8_strip" else torch.float32)
+        hio.flip = hp(flips, torch.uint8) if flips is not None else None
+        for k, d in enumerate(disparities):
+            hio.disparity[k] = hp(d)
+            hio.d_disparity[k] = self.h_dd[k].data_ptr()
+        for s in range(self.S):
+            hio.rvec[s], hio.tvec[s] = hp(rvecs[s]), hp(tvecs[s])
+            hio.d_rvec[s], hio.d_tvec[s] = self.h_dr[s].data_ptr(), self.h_dt[s].data_ptr()
+        hio.auto_loss = hp(auto_loss) if (self.automasking and auto_loss is not None) else None
+        hio.loss = self.h_loss.data_ptr()
+        with torch.cuda.device(self.dev):
+            check(handle(self.dev.index), lib.mdb_train_loss_host(self._h, ct.byref(hio), _stream()))
+        return HostLossResult(float(self.h_loss[0]), self.h_dd, self.h_dr, self.h_dt)
+
+    def close(self) -> None:
+        if self._h:
+            lib.mdb_host_plan_destroy(self._h)
+            self._h = ct.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def train_loss_host(plan: HostLoss, x, disparities, poses: Sequence[Pose], auto_loss=None, flips=None) -> HostLossResult:

@@ -67,11 +67,12 @@ def test_host_loss_from_u8_strips_matches_f32_path():
     pin = lambda a: torch.tensor(a).pin_memory()
     d, r, t = [pin(a) for a in inp.disparities], [pin(a) for a in inp.rvecs], [pin(a) for a in inp.tvecs]
     a = mdb200.HostLoss(**kw)(pin(x_ref), d, r, t)
-    # same chunk schedule on both sides (the u8 default ramps the chunk sizes up, which reorders the loss sum)
-    b = mdb200.HostLoss(x_format="u8_strip", ramp_up=False, **kw)(pin(strips), d, r, t, flips=pin(flips))
-    assert a.loss == b.loss
+    # the u8 pipeline ramps its chunk sizes up (1, 2, ...), so the chunk losses are summed in another order and an item may
+    # sit in a chunk of another size (another row segmentation): equal up to float32 summation order
+    b = mdb200.HostLoss(x_format="u8_strip", **kw)(pin(strips), d, r, t, flips=pin(flips))
+    assert abs(a.loss - b.loss) <= 1e-6 * abs(a.loss)
     for u, v in zip(a.d_disparities + a.d_rvec + a.d_tvec, b.d_disparities + b.d_rvec + b.d_tvec):
-        assert torch.equal(u, v)
+        assert torch.allclose(u, v, rtol=1e-5, atol=1e-6 * float(u.abs().max()))
     plan = mdb200.HostLoss(x_format="u8_strip", **kw)
     assert plan.h2d_bytes < mdb200.HostLoss(**kw).h2d_bytes * 0.45
 
