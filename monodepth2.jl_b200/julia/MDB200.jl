@@ -3,9 +3,16 @@
 #
 # NOT EXECUTED on the build / GPU boxes of this repository: neither has a Julia runtime (SURVEY F2).
 # The same C ABI is exercised end to end from Python (monodepth2.jl_b200/mdb200, tests/).  This file
-# is the binding a maintainer of the reference adds -- `include("MDB200.jl")` after
-# `include("training.jl")` in src/Monodepth.jl:62-74 -- and it only takes the fused path for
-# `CuArray{Float32}` arguments; every other method of the reference keeps working unchanged.
+# is the binding a maintainer of the reference adds -- `include("MDB200.jl")` as the LAST include of
+# src/Monodepth.jl:62-74 (after render.jl / simple_depth.jl, so every function named below exists).
+#
+# Dispatch: the functions are IMPORTED from the enclosing module (`import ..Monodepth: ...`), so the definitions
+# below are new METHODS of the reference's own functions, specialised on `CuArray{Float32}`; the reference's call
+# sites (`train_loss`, `slow_depth`, `find_static`, the test suite) reach them through ordinary dispatch, and every
+# other argument type (CPU `Array`s, Float64) keeps running the reference's pure-Julia methods.  Three names have no
+# generic function to extend in the fork and are DEFINED here for it: `warp` (called at src/simple_depth.jl:30-32
+# but missing, SURVEY F4), and the in-place-mutating `sample` / non-differentiable `render_tgt_rgb_depth`, whose
+# CuArray methods are replaced outright (same signature).
 #
 # Layout note: Julia's column-major (W,H,C,L,N) CuArray is passed as-is; the library reads the same
 # bytes as C order [N][L][C][H][W].  `K`/`invK` are passed as 9 host floats in column-major order.
@@ -13,7 +20,12 @@ module MDB200
 
 using CUDA
 using ChainRulesCore
-import ..Monodepth: Pose, Params, TrainCache, SSIM
+import ..Monodepth: Pose, Params, TrainCache, SSIM, Backproject, Project
+import ..Monodepth: hat, so3_exp_map, composeT, disparity_to_depth, smooth_loss,
+                    photometric_loss, prediction_loss, automasking_loss, _apply_mask, train_loss,
+                    inv, create_meshgrid, get_src_xyz_from_plane_disparity, get_tgt_xyz_from_plane_disparity,
+                    sample, plane_volume_rendering, render_tgt_rgb_depth, slow_depth, save_disparity, cpu
+using Statistics: mean
 
 const libmdb200 = get(ENV, "MDB200_LIB", joinpath(@__DIR__, "..", "mdb200", "libmdb200.so"))
 
@@ -33,6 +45,7 @@ struct LossParams
     smooth_weight_mode::Int32
     upsample_align_corners::Int32
     n_global::Int32
+    abs_subgradient::Int32       # 0: sign(0) = 0 (ChainRules); 1: ForwardDiff's Dual rule, what Zygote's CuArray broadcast uses
 end
 
 struct LossIO
@@ -124,15 +137,20 @@ function (ssim::SSIM)(x::CuArray{Float32,4}, y::CuArray{Float32,4})             
     out
 end
 
-function automasking_loss(ssim, inputs::CuArray{Float32,5}, target_id::Integer; source_ids)   # src/training.jl:9-11
+# automasking_loss(ssim, inputs, target; source_ids) -- src/training.jl:9-11, the reference's signature: `target` is the
+# target ARRAY (src/dtk.jl:59-61 passes x[:, :, :, target_id, :], a dense copy)
+function automasking_loss(ssim::SSIM, inputs::CuArray{Float32,5}, target::CuArray{Float32,4}; source_ids)
     W, H, C, L, N = size(inputs)
     out = CUDA.zeros(Float32, W, H, 1, N)
     ids = Int32.(collect(source_ids))
-    GC.@preserve inputs out ids check(ccall((:mdb_automasking_loss, libmdb200), Int32,
-        (Ptr{Cvoid}, CuPtr{Cfloat}, Int32, Ptr{Int32}, Int32, Int32, Int32, Int32, Int32, Int32, Cfloat, Cfloat, Cfloat, CuPtr{Cfloat}, Ptr{Cvoid}),
-        handle(), inputs, target_id, ids, length(ids), W, H, C, L, N, 0.85f0, Cfloat(ssim.c1), Cfloat(ssim.c2), out, stream_ptr()))
+    GC.@preserve inputs target out ids check(ccall((:mdb_automasking_loss, libmdb200), Int32,
+        (Ptr{Cvoid}, CuPtr{Cfloat}, CuPtr{Cfloat}, Int64, Ptr{Int32}, Int32, Int32, Int32, Int32, Int32, Int32, Cfloat, Cfloat, Cfloat,
+         CuPtr{Cfloat}, Ptr{Cvoid}),
+        handle(), inputs, target, Int64(0), ids, length(ids), W, H, C, L, N, 0.85f0, Cfloat(ssim.c1), Cfloat(ssim.c2), out, stream_ptr()))
     out
 end
+
+include("MDB200_ops.jl")      # the other fine-grained operators and their rrules
 
 # ---- the fused hot path ---------------------------------------------------------------------------
 """
@@ -143,7 +161,8 @@ kernels.  `n_global` is the batch size the means divide by (multi-GPU shards pas
 """
 function fused_loss(x::CuArray{Float32,5}, disparities::Vector{<:CuArray{Float32,4}}, poses::Vector{<:Pose},
                     auto_loss, cache::TrainCache, parameters::Params;
-                    normalize_disparity::Bool=true, smooth_weight_mode::Integer=0, n_global::Integer=0)
+                    normalize_disparity::Bool=true, smooth_weight_mode::Integer=0, n_global::Integer=0,
+                    abs_subgradient::Integer=0)
     W, H, C, L, N = size(x)
     S, Ls = length(poses), length(disparities)
     loss = CUDA.zeros(Float32, 1)
@@ -165,7 +184,7 @@ function fused_loss(x::CuArray{Float32,5}, disparities::Vector{<:CuArray{Float32
         pad(map(pointer, dt), MAX_SOURCES, nullp()), nullp())
     p = LossParams(parameters.min_depth, parameters.max_depth, parameters.disparity_smoothness, 0.85f0,
         Cfloat(cache.ssim.c1), Cfloat(cache.ssim.c2), Int32(parameters.automasking), Int32(normalize_disparity),
-        Int32(smooth_weight_mode), Int32(1), Int32(n_global))
+        Int32(smooth_weight_mode), Int32(1), Int32(n_global), Int32(abs_subgradient))
     nbytes = ccall((:mdb_train_loss_workspace_bytes, libmdb200), Csize_t, (Ref{LossIO},), io)
     nbytes > 0 || error("mdb200: unsupported shape for the fused loss")
     ws = CuArray{UInt8}(undef, nbytes)
@@ -179,6 +198,7 @@ end
 
 # The scalar loss is the only output, so the rrule's forward runs forward+backward with unit seed and
 # the pullback scales the cached gradients by the incoming cotangent (SURVEY 8b).
+# (Zygote needs the scalar on the host: this read is the step's one synchronisation, as `loss` is in the reference)
 loss_value(x, disparities, poses, auto_loss, cache, parameters) =
     Array(fused_loss(x, disparities, poses, auto_loss, cache, parameters)[1])[1]
 
@@ -344,7 +364,7 @@ function slow_depth(x::CuArray{Float32,5}, ssim, backprojections, projections, i
         pad([pointer(dd)], MAX_SCALES, nullp()), pad(map(pointer, dr), MAX_SOURCES, nullp()),
         pad(map(pointer, dt), MAX_SOURCES, nullp()), nullp())
     p = LossParams(min_depth, max_depth, 1e-3, 0.85f0, Cfloat(ssim.c1), Cfloat(ssim.c2), Int32(0),
-        Int32(0), Int32(1), Int32(1), Int32(0))                             # un-normalised, weight 1  (:39)
+        Int32(0), Int32(1), Int32(1), Int32(0), Int32(0))                   # un-normalised, weight 1  (:39)
     adam = AdamParams(3e-4, 0.9, 0.999, 1e-8)                               # ADAM(3e-4)              (:16)
     ws = CuArray{UInt8}(undef, ccall((:mdb_train_loss_workspace_bytes, libmdb200), Csize_t, (Ref{LossIO},), io))
     state = CUDA.zeros(UInt8, ccall((:mdb_slow_depth_state_bytes, libmdb200), Csize_t, (Ref{LossIO},), io))
