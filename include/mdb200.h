@@ -452,6 +452,14 @@ int32_t mdb_pose_head(mdb_handle* h, const float* conv_out, int32_t w, int32_t h
 /* its pullback: d_conv_out[w,h,c,n] = scale / (w h) * (c <= 3 ? d_rvec[c,n] : d_tvec[c-3,1,n])        */
 int32_t mdb_pose_head_bwd(mdb_handle* h, const float* d_rvec, const float* d_tvec, int32_t w, int32_t hh,
                           int32_t N, float scale, float* d_conv_out, void* stream);
+/* DepthDecoder output heads (src/depth_decoder.jl:46, 52-68): every scale level ends in Conv((3,3), ch => 1, σ); this is
+ * the σ of all Ls levels in one launch, logits[k] (w_k,h_k,1,N) -> disparity[k] (the loss path's input), with NNlib's
+ * overflow-safe σ; and its pullback d_logits[k] = d_disparity[k] .* disparity[k] .* (1 - disparity[k]) from the saved
+ * output, so the gradients of mdb_train_loss_fwdbwd reach the network's conv outputs in one more launch.         */
+int32_t mdb_disparity_heads(mdb_handle* h, const float* const* logits, const int32_t* dw, const int32_t* dh, int32_t Ls,
+                            int32_t N, float* const* disparity, void* stream);
+int32_t mdb_disparity_heads_bwd(mdb_handle* h, const float* const* disparity, const float* const* d_disparity, const int32_t* dw,
+                                const int32_t* dh, int32_t Ls, int32_t N, float* const* d_logits, void* stream);
 /* per-item mean of a map with `per_item` floats per item (deterministic): the reduction of find_static,
  * mean(automasking_loss(ssim, x, target; source_ids)) > alpha                    src/dtk.jl:51-69     */
 int32_t mdb_item_mean(mdb_handle* h, const float* map, int64_t per_item, int32_t N, float* out, void* stream);

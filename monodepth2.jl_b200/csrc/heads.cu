@@ -132,3 +132,86 @@ int32_t mdb_item_mean(mdb_handle* h, const float* map, int64_t per_item, int32_t
 }
 
 }  // extern "C"
+
+// ---- DepthDecoder output heads (src/depth_decoder.jl:46, 52-68) ----------------------------------------------------
+// Every scale level ends in `DecoderBlock(Conv((3,3), ch => 1, σ))`: the disparity of a level is σ of a one-channel
+// conv output.  The convolution is the network's (cuDNN, out of scope); the activation is the op on the boundary of
+// the loss path: all levels in ONE launch, logits (w_k,h_k,1,N) -> disparity (w_k,h_k,1,N), and its pullback
+// d logit = g σ (1 - σ) from the saved output, so the loss's d_disparity flows back into the network without an extra
+// elementwise pass per level.  σ is NNlib's overflow-safe form: t = exp(-|x|); x >= 0 ? 1 / (1 + t) : t / (1 + t).
+namespace {
+struct HeadsArgs {
+  const float* in[MDB_MAX_SCALES];      // fwd: logits;  bwd: saved disparities
+  const float* g[MDB_MAX_SCALES];       // bwd: d loss / d disparity
+  float* out[MDB_MAX_SCALES];
+  long long start[MDB_MAX_SCALES + 1];  // prefix sums of the element counts (in units of 4 floats where vectorised)
+  int Ls, vec;
+};
+
+MDB_DEV float sigmoid_nnlib(float x) {
+  const float t = expf(-fabsf(x));
+  return x >= 0.0f ? 1.0f / (1.0f + t) : t / (1.0f + t);
+}
+
+template <bool BWD>
+__global__ void __launch_bounds__(256) disparity_heads_kernel(const __grid_constant__ HeadsArgs a) {
+  const long long total = a.start[a.Ls];
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    int k = 0;
+    while (k + 1 < a.Ls && i >= a.start[k + 1]) ++k;
+    const long long j = i - a.start[k];
+    if (a.vec) {
+      const float4 v = __ldg(reinterpret_cast<const float4*>(a.in[k]) + j);
+      float4 o;
+      if (BWD) {
+        const float4 g = __ldg(reinterpret_cast<const float4*>(a.g[k]) + j);
+        o = make_float4(g.x * v.x * (1.0f - v.x), g.y * v.y * (1.0f - v.y), g.z * v.z * (1.0f - v.z), g.w * v.w * (1.0f - v.w));
+      } else {
+        o = make_float4(sigmoid_nnlib(v.x), sigmoid_nnlib(v.y), sigmoid_nnlib(v.z), sigmoid_nnlib(v.w));
+      }
+      reinterpret_cast<float4*>(a.out[k])[j] = o;
+    } else {
+      const float v = ldg(a.in[k] + j);
+      a.out[k][j] = BWD ? ldg(a.g[k] + j) * v * (1.0f - v) : sigmoid_nnlib(v);
+    }
+  }
+}
+
+int32_t heads_launch(mdb_handle* h, bool bwd, const float* const* in, const float* const* g, float* const* out,
+                     const int32_t* dw, const int32_t* dh, int32_t Ls, int32_t N, void* stream, const char* who) {
+  MDB_REQUIRE(h, h != nullptr, MDB_E_INVALID_ARG, "null handle");
+  MDB_REQUIRE(h, in && out && dw && dh && (!bwd || g) && Ls >= 1 && Ls <= MDB_MAX_SCALES && N >= 1, MDB_E_INVALID_ARG, "%s: bad argument", who);
+  HeadsArgs a{};
+  a.Ls = Ls;
+  a.vec = 1;
+  for (int k = 0; k < Ls; ++k) {
+    MDB_REQUIRE(h, in[k] && out[k] && (!bwd || g[k]) && dw[k] >= 1 && dh[k] >= 1, MDB_E_INVALID_ARG, "%s: bad level %d", who, k);
+    const long long n = (long long)dw[k] * dh[k] * N;
+    if (n % 4 || (((uintptr_t)in[k] | (uintptr_t)out[k] | (uintptr_t)(bwd ? g[k] : in[k])) & 15)) a.vec = 0;
+  }
+  for (int k = 0; k < Ls; ++k) {
+    const long long n = (long long)dw[k] * dh[k] * N;
+    a.in[k] = in[k]; a.g[k] = bwd ? g[k] : nullptr; a.out[k] = out[k];
+    a.start[k + 1] = a.start[k] + (a.vec ? n / 4 : n);
+  }
+  const long long blocks = std::max<long long>(1, std::min<long long>((a.start[Ls] + 255) / 256, (long long)h->num_sms * 16));
+  if (bwd) disparity_heads_kernel<true><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(a);
+  else disparity_heads_kernel<false><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(a);
+  MDB_LAUNCHED(h);
+  return MDB_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int32_t mdb_disparity_heads(mdb_handle* h, const float* const* logits, const int32_t* dw, const int32_t* dh, int32_t Ls,
+                            int32_t N, float* const* disparity, void* stream) {
+  return heads_launch(h, false, logits, nullptr, disparity, dw, dh, Ls, N, stream, "mdb_disparity_heads");
+}
+
+int32_t mdb_disparity_heads_bwd(mdb_handle* h, const float* const* disparity, const float* const* d_disparity, const int32_t* dw,
+                                const int32_t* dh, int32_t Ls, int32_t N, float* const* d_logits, void* stream) {
+  return heads_launch(h, true, disparity, d_disparity, d_logits, dw, dh, Ls, N, stream, "mdb_disparity_heads_bwd");
+}
+
+}  // extern "C"

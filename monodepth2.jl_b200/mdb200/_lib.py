@@ -153,6 +153,8 @@ PROTOTYPES = {
     "mdb_ingest_triplet_u8": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp]),
     "mdb_pose_head": (_i32, [_vp, _vp, _i32, _i32, _i32, _f32, _vp, _vp, _vp]),
     "mdb_pose_head_bwd": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _f32, _vp, _vp]),
+    "mdb_disparity_heads": (_i32, [_vp, C.POINTER(_vp), C.POINTER(_i32), C.POINTER(_i32), _i32, _i32, C.POINTER(_vp), _vp]),
+    "mdb_disparity_heads_bwd": (_i32, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_i32), C.POINTER(_i32), _i32, _i32, C.POINTER(_vp), _vp]),
     "mdb_item_mean": (_i32, [_vp, _vp, _i64, _i32, _vp, _vp]),
     "mdb_measure_fp32_peak": (_i32, [_vp, _vp, _sz, _i32, C.POINTER(_f64), C.POINTER(_f64), _vp]),
     "mdb_debug_option": (_i32, [C.c_char_p, _i64]),

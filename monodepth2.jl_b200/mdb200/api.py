@@ -830,6 +830,36 @@ def pose_head(conv_out: torch.Tensor, scale: float = 1e-2) -> Pose:
     return Pose(*_PoseHeadFn.apply(conv_out, scale))
 
 
+class _DispHeadsFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, *logits):
+        logits = [_chk(t.detach(), "logits") for t in logits]
+        Ls, N = len(logits), logits[0].shape[0]
+        outs = [torch.empty_like(t) for t in logits]
+        arr = lambda ts: (ct.c_void_p * Ls)(*[t.data_ptr() for t in ts])
+        dw = (ct.c_int32 * Ls)(*[t.shape[-1] for t in logits]); dh = (ct.c_int32 * Ls)(*[t.shape[-2] for t in logits])
+        check(handle(), lib.mdb_disparity_heads(handle(), arr(logits), dw, dh, Ls, N, arr(outs), _stream()))
+        ctx.save_for_backward(*outs)
+        return tuple(outs)
+
+    @staticmethod
+    def backward(ctx, *gs):
+        outs = ctx.saved_tensors
+        Ls, N = len(outs), outs[0].shape[0]
+        gs = [torch.zeros_like(o) if g is None else g.contiguous() for g, o in zip(gs, outs)]
+        d = [torch.empty_like(o) for o in outs]
+        arr = lambda ts: (ct.c_void_p * Ls)(*[t.data_ptr() for t in ts])
+        dw = (ct.c_int32 * Ls)(*[t.shape[-1] for t in outs]); dh = (ct.c_int32 * Ls)(*[t.shape[-2] for t in outs])
+        check(handle(), lib.mdb_disparity_heads_bwd(handle(), arr(outs), arr(gs), dw, dh, Ls, N, arr(d), _stream()))
+        return tuple(d)
+
+
+def disparity_heads(logits: Sequence[torch.Tensor]) -> List[torch.Tensor]:
+    """The σ of the DepthDecoder's output convolutions (src/depth_decoder.jl:46, 52-68), all scale levels in one launch:
+    logits[k] (N,1,h_k,w_k) -> disparities[k], differentiable (pullback g σ (1 - σ) in one launch too)."""
+    return list(_DispHeadsFn.apply(*logits))
+
+
 def item_mean(m: torch.Tensor) -> torch.Tensor:
     """mean over everything but the batch axis, one value per item (deterministic)."""
     _chk(m, "map")

@@ -60,3 +60,27 @@ def test_item_mean_cluster_reduction(N, per_item):
     pad = torch.zeros(N * per_item + 1, device=DEV)
     pad[1:] = m.reshape(-1).to(DEV)
     assert torch.equal(mdb200.item_mean(pad[1:].view(N, per_item)), got)
+
+
+@pytest.mark.parametrize("sizes", [[(52, 16), (104, 32), (208, 64), (416, 128)], [(13, 7), (27, 15)]])
+def test_disparity_heads_vs_torch(sizes):
+    """DepthDecoder output heads (src/depth_decoder.jl:46, 52-68): σ of every level's conv output in one launch, and
+    the pullback g σ (1 - σ); against float64 torch.sigmoid (the second shape has element counts that are not multiples
+    of four: the scalar path)."""
+    import mdb200
+    g = torch.Generator().manual_seed(17)
+    N = 3
+    logits = [torch.randn((N, 1, h, w), generator=g) * 6 for (w, h) in sizes]     # |x| up to ~25: the overflow-safe branch
+    cots = [torch.randn((N, 1, h, w), generator=g) for (w, h) in sizes]
+    l64 = [t.double().requires_grad_() for t in logits]
+    sum((torch.sigmoid(t) * c.double()).sum() for t, c in zip(l64, cots)).backward()
+    lg = [t.to("cuda:0").requires_grad_() for t in logits]
+    before = mdb200.launch_count()
+    outs = mdb200.disparity_heads(lg)
+    assert mdb200.launch_count() - before == 1
+    for o, t in zip(outs, l64):
+        assert (o.double().cpu() - torch.sigmoid(t.detach())).abs().max() < 2e-7
+        assert float(o.min()) >= 0.0 and float(o.max()) <= 1.0
+    sum((o * c.to("cuda:0")).sum() for o, c in zip(outs, cots)).backward()
+    for a, b in zip(lg, l64):
+        assert (a.grad.double().cpu() - b.grad).abs().max() <= 1e-6 * b.grad.abs().max() + 1e-9
