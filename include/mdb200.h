@@ -199,6 +199,17 @@ int32_t mdb_smooth_loss(mdb_handle* h, const float* disparity, const float* imag
 int32_t mdb_smooth_loss_ex(mdb_handle* h, const float* disparity, const float* image, int32_t W,
                            int32_t H, int32_t C, int32_t N, int32_t abs_subgradient, float* loss,
                            float* d_disparity, void* workspace, size_t workspace_bytes, void* stream);
+/* smooth_loss with NO allocation and no workspace argument.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same kernels and result as mdb_smooth_loss_ex; the scratch (per-block partial sums) is a
+ * static __device__ array inside the library of MDB_SMOOTH_NOALLOC_MAX_BYTES = 256 KiB, held by every GPU that loads the
+ * library until exit.  Limit: N * ceil(H / 8) <= 32768 (e.g. 64 items of 1024x320 need 2560); larger shapes are
+ * rejected with MDB_E_WORKSPACE.  All calls on a device share the array: calls that overlap on the GPU (different
+ * streams / threads) race on it -- serialise them.  Nothing in it needs clearing between calls.            */
+#define MDB_SMOOTH_NOALLOC_MAX_BYTES (256 * 1024)
+int32_t mdb_smooth_loss_noalloc(mdb_handle* h, const float* disparity, const float* image, int32_t W,
+                                int32_t H, int32_t C, int32_t N, int32_t abs_subgradient, float* loss,
+                                float* d_disparity, void* stream);
 
 /* ---- P12: the fused hot path  (src/training.jl:21-78; src/simple_depth.jl:25-41) ------ */
 typedef struct mdb_loss_io {

@@ -3,6 +3,7 @@
 // and drivers call by name has a device implementation behind the C ABI; the training hot
 // path uses the fused kernel in photo_fused.cu instead.
 #include "photo_fused.cuh"
+#include <mutex>
 #include "pose_math.cuh"
 
 namespace {
@@ -724,3 +725,58 @@ int32_t mdb_smooth_loss_ex(mdb_handle* h, const float* disparity, const float* i
 }
 
 }  // extern "C"
+
+// ---- smooth_loss without any allocation -----------------------------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same kernels and same result as
+// mdb_smooth_loss_ex, but the per-block partial sums live in the file-scope array below instead of a caller-provided
+// workspace.  Every GPU that loads the library holds these 256 KiB until the process exits.
+//  * The array's NAME is a host-side stand-in in host code, not a device address: the address the kernels get is
+//    looked up once per device, with that device current, by cudaGetSymbolAddress (smooth_scratch_ptr below).
+//  * All calls on a device share the array and it keeps the last call's contents.  Nothing in it has to start at zero:
+//    a call's kernels write every partial its finalize kernel then reads (2 floats per (row block, item)), so stale
+//    contents are never read.  Calls that OVERLAP on the GPU (two streams, two host threads) race on it: serialise them.
+constexpr size_t SMOOTH_NOALLOC_FLOATS = MDB_SMOOTH_NOALLOC_MAX_BYTES / sizeof(float);
+static __device__ __align__(256) float g_smooth_scratch[SMOOTH_NOALLOC_FLOATS];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_smooth_scratch_mu;
+float* g_smooth_scratch_ptr[kMaxDevices] = {nullptr};   // device address of g_smooth_scratch per device, nullptr = not looked up
+
+// once per device: the symbol's address ON THAT DEVICE (cudaGetSymbolAddress answers for the current device)
+cudaError_t smooth_scratch_ptr(int device, float** out) {
+  std::lock_guard<std::mutex> lock(g_smooth_scratch_mu);
+  if (device < 0 || device >= kMaxDevices) return cudaErrorInvalidDevice;
+  if (!g_smooth_scratch_ptr[device]) {
+    int prev = -1;
+    cudaError_t e = cudaGetDevice(&prev);
+    if (e != cudaSuccess) return e;
+    if (prev != device && (e = cudaSetDevice(device)) != cudaSuccess) return e;
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_smooth_scratch);
+    if (prev != device) cudaSetDevice(prev);
+    if (e != cudaSuccess) return e;
+    g_smooth_scratch_ptr[device] = (float*)p;
+  }
+  *out = g_smooth_scratch_ptr[device];
+  return cudaSuccess;
+}
+}  // namespace
+
+extern "C" int32_t mdb_smooth_loss_noalloc(mdb_handle* h, const float* disparity, const float* image, int32_t W, int32_t H,
+                                           int32_t C, int32_t N, int32_t abs_subgradient, float* loss, float* d_disparity,
+                                           void* stream) {
+  MDB_REQUIRE(h, h != nullptr, MDB_E_INVALID_ARG, "null handle");
+  MDB_REQUIRE(h, W >= 2 && H >= 2 && N >= 1, MDB_E_SHAPE, "mdb_smooth_loss_noalloc: need W,H >= 2, N >= 1");
+  const size_t need = mdb_smooth_loss_workspace_bytes(W, H, N);
+  MDB_REQUIRE(h, need != 0 && need <= MDB_SMOOTH_NOALLOC_MAX_BYTES, MDB_E_WORKSPACE,
+              "mdb_smooth_loss_noalloc: N * ceil(H / 8) = %lld exceeds the built-in scratch (%d): this shape needs %zu bytes, the "
+              "static array holds %d; use mdb_smooth_loss_ex with a workspace of your own",
+              (long long)N * ((H + 7) / 8), (int)(MDB_SMOOTH_NOALLOC_MAX_BYTES / 8), need, (int)MDB_SMOOTH_NOALLOC_MAX_BYTES);
+  float* scratch = nullptr;
+  MDB_CUDA(h, smooth_scratch_ptr(h->device, &scratch));
+  // the existing entry with the static array as its workspace: kernel launches only, no cudaMalloc / cudaFree anywhere
+  return mdb_smooth_loss_ex(h, disparity, image, W, H, C, N, abs_subgradient, loss, d_disparity, scratch,
+                            MDB_SMOOTH_NOALLOC_MAX_BYTES, stream);
+}

@@ -124,6 +124,7 @@ PROTOTYPES = {
     "mdb_smooth_loss_workspace_bytes": (_sz, [_i32, _i32, _i32]),
     "mdb_smooth_loss": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _sz, _vp]),
     "mdb_smooth_loss_ex": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _sz, _vp]),
+    "mdb_smooth_loss_noalloc": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp, _vp]),
     "mdb_train_loss_strip_geometry": (_i32, [C.POINTER(LossIO), C.POINTER(_i32)]),
     "mdb_train_loss_workspace_bytes": (_sz, [C.POINTER(LossIO)]),
     "mdb_train_loss_fwdbwd": (_i32, [_vp, C.POINTER(LossIO), C.POINTER(LossParams), _vp, _sz, _vp]),
