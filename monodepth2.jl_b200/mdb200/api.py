@@ -473,7 +473,7 @@ class FusedLoss:
                  min_depth: float = 0.1, max_depth: float = 100.0, disparity_smoothness: float = 1e-3,
                  automasking: bool = False, normalize_disparity: bool = True, smooth_weight_mode: int = 0,
                  n_global: int = 0, alpha: float = 0.85, want_vis: bool = False, device=None,
-                 out: Optional[dict] = None, abs_subgradient: int = 0):
+                 out: Optional[dict] = None, abs_subgradient: int = 0, ssim: Optional["SSIM"] = None):
         """`out` (optional): caller-provided output tensors {"loss": 0-dim or 1-element, "d_disp": [...],
         "d_rvec": [...], "d_tvec": [...]} of the right shapes -- e.g. row slices of whole-batch tensors --
         instead of buffers owned by the plan."""
@@ -490,6 +490,8 @@ class FusedLoss:
         p.smooth_weight_mode = int(smooth_weight_mode)
         p.n_global = int(n_global)
         p.abs_subgradient = int(abs_subgradient)
+        if ssim is not None:
+            p.ssim_c1, p.ssim_c2 = float(ssim.c1), float(ssim.c2)
         self.params = p
         io = _lib.LossIO()
         io.W, io.H, io.C, io.L, io.N = W, H, C, L, N
@@ -553,8 +555,10 @@ class FusedLoss:
             io.rvec[s] = _chk(pz.rvec, "rvec").data_ptr()
             io.tvec[s] = _chk(pz.tvec, "tvec").data_ptr()
         io.auto_loss = _chk(auto_loss, "auto_loss").data_ptr() if auto_loss is not None else None
-        h = handle()
-        check(h, lib.mdb_train_loss_fwdbwd(h, ct.byref(io), ct.byref(self.params), _p(self.ws), self.ws_bytes, _stream()))
+        # the plan's device, not whatever device happens to be current: handle, stream and launches all belong to it
+        with torch.cuda.device(self.dev):
+            h = handle(self.dev.index)
+            check(h, lib.mdb_train_loss_fwdbwd(h, ct.byref(io), ct.byref(self.params), _p(self.ws), self.ws_bytes, _stream()))
         return LossResult(self.loss, self.d_disp, [Pose(r, t) for r, t in zip(self.d_rvec, self.d_tvec)], self.vis)
 
 
@@ -588,15 +592,19 @@ def train_loss(model: Callable, x: torch.Tensor, auto_loss: Optional[torch.Tenso
     N, L, Cc, H, W = x.shape
     disparities, poses = model(x, cache.source_ids, cache.target_id)
     sizes = tuple((d.shape[-1], d.shape[-2]) for d in disparities)
+    # everything that is baked into the plan at construction is part of the key -- the intrinsics and the SSIM constants
+    # too (two datasets with different K in one process must not share a plan)
+    k9t = lambda K: tuple(torch.as_tensor(K, dtype=torch.float32, device="cpu").reshape(9).tolist())
     key = (N, L, Cc, H, W, sizes, tuple(cache.scales), cache.target_id, tuple(cache.source_ids),
            parameters.automasking, parameters.min_depth, parameters.max_depth, parameters.disparity_smoothness,
-           bool(do_visualization), x.device.index)
+           bool(do_visualization), x.device.index, k9t(cache.K), k9t(cache.invK), float(cache.ssim.c1), float(cache.ssim.c2))
     if key not in _plans:
         _plans[key] = FusedLoss(W=W, H=H, C=Cc, L=L, N=N, disp_sizes=sizes, scales=cache.scales,
                                 target_id=cache.target_id, source_ids=cache.source_ids, K=cache.K, invK=cache.invK,
                                 min_depth=parameters.min_depth, max_depth=parameters.max_depth,
                                 disparity_smoothness=parameters.disparity_smoothness,
-                                automasking=parameters.automasking, want_vis=bool(do_visualization), device=x.device)
+                                automasking=parameters.automasking, want_vis=bool(do_visualization), device=x.device,
+                                ssim=cache.ssim)
     plan = _plans[key]
     flat = list(disparities) + [t for pz in poses for t in (pz.rvec, pz.tvec)]
     loss = _TrainLossFn.apply(plan, x, auto_loss if parameters.automasking else None, len(disparities), *flat)

@@ -145,6 +145,28 @@ def test_autograd_wrapper_matches_plan():
     assert vl.shape == (inp.N, 1, inp.H, inp.W) and len(vw) == 2 and vd.shape == disps[-1].shape
 
 
+def test_train_loss_plan_cache_keys_on_the_intrinsics():
+    """Two TrainCaches with the same shapes but different K (two datasets in one process) must not share a plan:
+    the second call has to see ITS intrinsics, not the first call's."""
+    import mdb200
+    from mdb200 import synth
+    inp = synth.make_loss_inputs(72, 24, 1, seed=8, scales=(1.0,))
+    dev = torch.device("cuda:0")
+    x = torch.tensor(inp.x, device=dev)
+    disps = [torch.tensor(d, device=dev) for d in inp.disparities]
+    poses = [mdb200.Pose(torch.tensor(r, device=dev), torch.tensor(t, device=dev)) for r, t in zip(inp.rvecs, inp.tvecs)]
+    params = mdb200.Params(automasking=False, target_size=(inp.W, inp.H), batch_size=inp.N)
+    K2, iK2 = synth.intrinsics(inp.W * 2, inp.H * 2)          # another focal length and principal point
+    losses = []
+    for K, iK in ((inp.K, inp.invK), (K2.astype(np.float32), iK2.astype(np.float32)), (inp.K, inp.invK)):
+        cache = mdb200.TrainCache(mdb200.SSIM(), None, None, torch.tensor(K), torch.tensor(iK), 2, [1, 3], [1.0])
+        losses.append(float(mdb200.train_loss(lambda x_, s, t: (disps, poses), x, None, cache, params)[0]))
+        plan = mdb200.FusedLoss(W=inp.W, H=inp.H, C=3, L=3, N=1, disp_sizes=[(inp.W, inp.H)], scales=[1.0], target_id=2,
+                                source_ids=[1, 3], K=K, invK=iK)
+        assert losses[-1] == float(plan(x, disps, poses).loss)
+    assert losses[0] == losses[2] and losses[0] != losses[1]
+
+
 @pytest.mark.parametrize("W,H,scales", [
     (28, 8, (0.5, 1.0)),        # exactly one strip, no right halo inside the image
     (29, 9, (0.5, 1.0)),        # second strip owns a single pixel column
