@@ -134,7 +134,10 @@ struct StripGeom {
 // arithmetic error from sub-ulp ties that legitimately fall the other way in float32.
 MDB_DEV signed char sgn_code(float v) { return v == 0.0f ? 0 : (v > 0.0f ? 1 : -1); }
 
-template <int C, int S, bool DBG = false>
+// CP: the projection constants come from the constant bank (c_pose, filled by the host before the launch) instead of
+// global memory.  The throughput path uses CP = true; a call made under stream capture (slow_depth's graph: one item,
+// latency-bound) uses CP = false, which needs no copy node and no event nodes in the graph.
+template <int C, int S, bool DBG = false, bool CP = (STRIP_CONSTPOSE != 0)>
 #ifdef STRIP_MAXREG
 __global__ void __maxnreg__(STRIP_MAXREG)
 #else
@@ -209,7 +212,8 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   // p_i = A_i . q is carried down the rows by adding column 1 of A (double: no drift that matters)
   double p1[S], p2[S], p3[S];
 #if STRIP_CONSTPOSE
-  const PoseStrip* const ppn = c_pose + g.cbase + nl_item * S;   // constant bank, warp-uniform index: operands, not registers
+  // constant bank, warp-uniform index: operands, not registers
+  const PoseStrip* const ppn = CP ? c_pose + g.cbase + nl_item * S : a.ppd + (size_t)n * S;
 #else
   const PoseStrip* const ppn = a.ppd + (size_t)n * S;
 #endif
