@@ -455,6 +455,15 @@ int32_t mdb_slow_depth_destroy(mdb_slow_depth_plan* plan);
 int32_t mdb_ingest_triplet_u8(mdb_handle* h, const uint8_t* strips, const uint8_t* flip, int32_t W, int32_t H,
                               int32_t N, int32_t grayscale, float* x, void* stream);
 
+/* KittyDataset's `getindex` (src/kitty.jl:45-61): `frames` = the three consecutive `image_0` rasters of every sample as
+ * decoded, uint8 gray row-major [N][3][H_orig][W_orig], DEVICE memory.  Each is resized to (H, W) as
+ * `imresize(x, (height, width))` does for Matrix{Gray{N0f8}} (ImageTransformations.jl, third-party: half-pixel-centre
+ * bilinear in Float64, result rounded back to N0f8; restated in oracle/ingest_ref.py), then `Float32.`, transposed and
+ * stacked: x (W,H,1,3,N).  `flip` as for mdb_ingest_triplet_u8 (`d.augmentations`, :53-55).  Bit-exact against the numpy
+ * restatement.                                                                                                     */
+int32_t mdb_ingest_kitti_u8(mdb_handle* h, const uint8_t* frames, const uint8_t* flip, int32_t W_orig, int32_t H_orig,
+                            int32_t W, int32_t H, int32_t N, float* x, void* stream);
+
 /* ---- the operators on the network side of the path ---------------------------
  * PoseDecoder tail (src/pose_decoder.jl:27-32): pose = scale * mean(conv_out (w,h,6,N); dims=(1,2)),
  * Pose(pose[1:3,1,:], pose[4:6,:,:]) -> rvec (3,N), tvec (3,1,N); scale = 1e-2 in the reference.     */

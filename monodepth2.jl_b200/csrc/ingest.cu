@@ -61,6 +61,60 @@ ingest_triplet_u8_kernel(const unsigned char* __restrict__ strips, const unsigne
   }
 }
 
+
+// ---- KittyDataset.getindex, src/kitty.jl:45-61 ---------------------------------------------------------------------
+// Three consecutive `image_0` PNGs (Gray{N0f8}, e.g. 1241 x 376) -> imresize to (height, width) -> Float32 -> (W,H,1,3).
+// `imresize` is ImageTransformations.jl (third-party): per axis p = s i + (0.5 - 0.5 s) clamped to [1, m], s = m / n,
+// linear B-spline, rows outermost, Float64 arithmetic, result rounded back to N0f8 (ties to even) -- restated in
+// oracle/ingest_ref.py, which this kernel matches bit for bit: every Float64 operation below is an explicit
+// round-to-nearest intrinsic so that nvcc contracts nothing into an FMA numpy would not do.
+// One thread per output pixel: 4 byte taps + ~20 FP64 operations; (m / n)^2 bytes read + 4 written per output, HBM-bound.
+struct AxisTap { int i0, i1; double w0, w1; };
+
+MDB_DEV AxisTap axis_tap(int i /*0-based output index*/, int n_new, int m_old) {
+  const double s = __ddiv_rn((double)m_old, (double)n_new);
+  const double off = __dsub_rn(0.5, __dmul_rn(0.5, s));
+  double p = __dadd_rn(__dmul_rn(s, (double)(i + 1)), off);
+  p = fmin(fmax(p, 1.0), (double)m_old);
+  double f = floor(p);
+  if (f > (double)(m_old - 1)) f = __dsub_rn(f, 1.0);
+  const double d = __dsub_rn(p, f);
+  AxisTap t;
+  t.i0 = (int)f - 1;
+  t.i1 = min(t.i0 + 1, m_old - 1);
+  t.w0 = __dsub_rn(1.0, d);
+  t.w1 = d;
+  return t;
+}
+
+__global__ void __launch_bounds__(ING_THREADS)
+ingest_kitti_u8_kernel(const unsigned char* __restrict__ frames, const unsigned char* __restrict__ flip, int Wo, int Ho,
+                       int W, int H, float* __restrict__ x) {
+  __shared__ double lut64[256];   // Float64(::N0f8) = u / 255
+  __shared__ float lut32[256];    // Float32(::N0f8)
+  lut64[threadIdx.x] = __ddiv_rn((double)threadIdx.x, 255.0);
+  lut32[threadIdx.x] = n0f8((unsigned char)threadIdx.x);
+  __syncthreads();
+  const int w = blockIdx.x * ING_THREADS + threadIdx.x, h = blockIdx.y, fn = blockIdx.z;   // fn = 3 n + frame
+  if (w >= W) return;
+  const unsigned char* src = frames + (size_t)fn * Ho * Wo;
+  unsigned char q;
+  if (Wo == W && Ho == H) {
+    q = src[(size_t)h * Wo + w];                                    // imresize copies when the size already matches
+  } else {
+    const AxisTap ty = axis_tap(h, H, Ho), tx = axis_tap(w, W, Wo);
+    const unsigned char* r0 = src + (size_t)ty.i0 * Wo;
+    const unsigned char* r1 = src + (size_t)ty.i1 * Wo;
+    const double a00 = lut64[r0[tx.i0]], a01 = lut64[r0[tx.i1]], a10 = lut64[r1[tx.i0]], a11 = lut64[r1[tx.i1]];
+    const double top = __dadd_rn(__dmul_rn(tx.w0, a00), __dmul_rn(tx.w1, a01));
+    const double bot = __dadd_rn(__dmul_rn(tx.w0, a10), __dmul_rn(tx.w1, a11));
+    const double v = __dadd_rn(__dmul_rn(ty.w0, top), __dmul_rn(ty.w1, bot));
+    q = (unsigned char)(int)rint(__dmul_rn(255.0, v));             // N0f8(v): round(255 v), ties to even
+  }
+  const bool f = flip && flip[fn / 3];
+  __stcs(x + ((size_t)fn * H + h) * W + (f ? W - 1 - w : w), lut32[q]);
+}
+
 }  // namespace
 
 extern "C" int32_t mdb_ingest_triplet_u8(mdb_handle* h, const uint8_t* strips, const uint8_t* flip, int32_t W,
@@ -75,6 +129,18 @@ extern "C" int32_t mdb_ingest_triplet_u8(mdb_handle* h, const uint8_t* strips, c
     MDB_CUDA(h, cudaFuncSetAttribute(ingest_triplet_u8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid(H, N);
   ingest_triplet_u8_kernel<<<grid, ING_THREADS, smem, (cudaStream_t)stream>>>(strips, flip, W, H, grayscale ? 1 : 0, x);
+  MDB_LAUNCHED(h);
+  return MDB_OK;
+}
+
+extern "C" int32_t mdb_ingest_kitti_u8(mdb_handle* h, const uint8_t* frames, const uint8_t* flip, int32_t W_orig,
+                                       int32_t H_orig, int32_t W, int32_t H, int32_t N, float* x, void* stream) {
+  MDB_REQUIRE(h, h != nullptr, MDB_E_INVALID_ARG, "null handle");
+  MDB_REQUIRE(h, frames && x, MDB_E_INVALID_ARG, "mdb_ingest_kitti_u8: null pointer");
+  MDB_REQUIRE(h, W >= 1 && H >= 1 && N >= 1 && W_orig >= 1 && H_orig >= 1 && H <= 65535 && N <= 21845, MDB_E_SHAPE,
+              "mdb_ingest_kitti_u8: need W,H,N,W_orig,H_orig >= 1, H <= 65535 and N <= 21845");
+  dim3 grid((W + ING_THREADS - 1) / ING_THREADS, H, 3 * N);
+  ingest_kitti_u8_kernel<<<grid, ING_THREADS, 0, (cudaStream_t)stream>>>(frames, flip, W_orig, H_orig, W, H, x);
   MDB_LAUNCHED(h);
   return MDB_OK;
 }

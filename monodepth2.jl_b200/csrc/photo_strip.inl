@@ -60,6 +60,7 @@ constexpr int STRIP_NHEAD = 3;   // record head: photometric sum, smoothness x-s
                        // clamps, no stage gating): fewer instructions and one long basic block for ptxas to schedule
 #endif
 #if !defined(STRIP_MAXREG) && !defined(STRIP_MINB)
+#define STRIP_MAXREG_CAPTURED 152
 #define STRIP_MAXREG 160   // 12 warps per SM, no spills.  Round 1 (unpeeled loop, constants in registers): best of 128 .. 184 was
                            // 152.  Round 2 (peeled loop, constants in the bank): 152 spills 148 B (4.83 ms), 160 and 168 are
                            // spill-free (4.18 / 4.20 ms), 176 .. 224 spill again (ptxas trades) -- spills decide, not the 13th warp
@@ -137,9 +138,11 @@ MDB_DEV signed char sgn_code(float v) { return v == 0.0f ? 0 : (v > 0.0f ? 1 : -
 // CP: the projection constants come from the constant bank (c_pose, filled by the host before the launch) instead of
 // global memory.  The throughput path uses CP = true; a call made under stream capture (slow_depth's graph: one item,
 // latency-bound) uses CP = false, which needs no copy node and no event nodes in the graph.
+// The captured instantiation (CP = false, DBG = false) also keeps round 1's loop: no steady-state copy, 152 registers -- on the
+// 480-warp launch of config 1 the peeled loop is 1.5 us per iteration slower (24.2 against 22.7 us).
 template <int C, int S, bool DBG = false, bool CP = (STRIP_CONSTPOSE != 0)>
 #ifdef STRIP_MAXREG
-__global__ void __maxnreg__(STRIP_MAXREG)
+__global__ void __maxnreg__((CP || DBG) ? STRIP_MAXREG : STRIP_MAXREG_CAPTURED)
 #else
 __global__ void __launch_bounds__(STRIP_THREADS, STRIP_MINB)
 #endif
@@ -671,10 +674,11 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   {
     // steady-state rows: all three stages active (r >= Y0 + 2), window row r-1 and pixel row r-2 inside this segment
     // (r <= Y1), no reflected row in sight (pixel row >= 2 and <= H-3, r + 1 <= H - 1)
-    const int s_lo = max(Y0 + 2, 4), s_hi = STRIP_PEEL ? min(Y1, H - 2) : -1000000;
+    constexpr bool PEEL = STRIP_PEEL && (CP || DBG);
+    const int s_lo = max(Y0 + 2, 4), s_hi = PEEL ? min(Y1, H - 2) : -1000000;
     int r = Y0 - 2;
     while (r <= Y1 + 1) {
-      if (STRIP_PEEL && r >= s_lo && r <= s_hi) {
+      if (PEEL && r >= s_lo && r <= s_hi) {
         for (; r <= s_hi; ++r) row(r, std::true_type{});
       } else {
         row(r, std::false_type{});

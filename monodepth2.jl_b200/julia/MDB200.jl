@@ -388,4 +388,39 @@ function slow_depth(x::CuArray{Float32,5}, ssim, backprojections, projections, i
     disp, poses, Array(history)
 end
 
+# ---- datasets: ship the decoder's 8-bit raster, do the rest of `getindex` on the device -------------------------------
+# Both take ROW-MAJOR rasters as the PNG decoder produces them: a Julia `Matrix` from `load` is (rows, cols) column-major,
+# so pass `permutedims(rawview(channelview(img)), ...)` with the width axis first -- or decode straight into such a buffer.
+
+"""
+    depth10k_batch(strips::CuArray{UInt8,4}; flips = nothing, grayscale = false) -> CuArray{Float32,5} (W,H,C,3,N)
+
+`Depth10k.getindex` (src/dtk.jl:29-46) for a batch: `strips` is (3, 3W, H, N) = RGB-interleaved rows of the triplet image.
+"""
+function depth10k_batch(strips::CuArray{UInt8,4}; flips::Union{Nothing,CuArray{UInt8,1}} = nothing, grayscale::Bool = false)
+    _, W3, H, N = size(strips)
+    W = W3 ÷ 3
+    x = CuArray{Float32}(undef, W, H, grayscale ? 1 : 3, 3, N)
+    GC.@preserve strips flips x check(ccall((:mdb_ingest_triplet_u8, libmdb200), Int32,
+        (Ptr{Cvoid}, CuPtr{UInt8}, CuPtr{UInt8}, Int32, Int32, Int32, Int32, CuPtr{Cfloat}, Ptr{Cvoid}),
+        handle(), strips, flips === nothing ? CuPtr{UInt8}(0) : pointer(flips), W, H, N, Int32(grayscale), x, stream_ptr()))
+    x
+end
+
+"""
+    kitti_batch(frames::CuArray{UInt8,4}, width, height; flips = nothing) -> CuArray{Float32,5} (W,H,1,3,N)
+
+`KittyDataset.getindex` (src/kitty.jl:45-61) for a batch: `frames` is (W_orig, H_orig, 3, N), the three consecutive gray
+`image_0` rasters of every sample; `imresize` to `d.resolution`, `Float32.`, transpose and stack happen on the device.
+"""
+function kitti_batch(frames::CuArray{UInt8,4}, width::Integer, height::Integer; flips::Union{Nothing,CuArray{UInt8,1}} = nothing)
+    Wo, Ho, L, N = size(frames)
+    L == 3 || error("kitti_batch: need three frames per sample")
+    x = CuArray{Float32}(undef, width, height, 1, 3, N)
+    GC.@preserve frames flips x check(ccall((:mdb_ingest_kitti_u8, libmdb200), Int32,
+        (Ptr{Cvoid}, CuPtr{UInt8}, CuPtr{UInt8}, Int32, Int32, Int32, Int32, Int32, CuPtr{Cfloat}, Ptr{Cvoid}),
+        handle(), frames, flips === nothing ? CuPtr{UInt8}(0) : pointer(flips), Wo, Ho, width, height, N, x, stream_ptr()))
+    x
+end
+
 end # module

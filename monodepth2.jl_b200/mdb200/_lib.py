@@ -152,6 +152,7 @@ PROTOTYPES = {
     "mdb_slow_depth_run": (_i32, [_vp, _i32, _vp]),
     "mdb_slow_depth_destroy": (_i32, [_vp]),
     "mdb_ingest_triplet_u8": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp]),
+    "mdb_ingest_kitti_u8": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
     "mdb_pose_head": (_i32, [_vp, _vp, _i32, _i32, _i32, _f32, _vp, _vp, _vp]),
     "mdb_pose_head_bwd": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _f32, _vp, _vp]),
     "mdb_disparity_heads": (_i32, [_vp, C.POINTER(_vp), C.POINTER(_i32), C.POINTER(_i32), _i32, _i32, C.POINTER(_vp), _vp]),

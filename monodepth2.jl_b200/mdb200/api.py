@@ -804,6 +804,26 @@ def ingest_triplet_u8(strips: torch.Tensor, width: int, flips: Optional[torch.Te
     return out
 
 
+def ingest_kitti_u8(frames: torch.Tensor, height: int, width: int, flips: Optional[torch.Tensor] = None,
+                    out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """`KittyDataset.getindex` for a batch, on the device (src/kitty.jl:45-61): frames uint8 (N,3,Ho,Wo), the three
+    consecutive gray `image_0` rasters of every sample -> `imresize` to (height, width) -> x float32 (N,3,1,H,W)
+    [Julia (W,H,1,3,N)]; `flips` uint8 (N,) marks the samples FlipX applies to."""
+    if frames.dtype != torch.uint8 or not frames.is_cuda or not frames.is_contiguous() or frames.dim() != 4 or frames.shape[1] != 3:
+        raise ValueError("frames must be a contiguous CUDA uint8 tensor (N,3,Ho,Wo)")
+    N, _, Ho, Wo = frames.shape
+    if flips is not None and (flips.dtype != torch.uint8 or not flips.is_cuda or flips.numel() != N):
+        raise ValueError("flips must be a CUDA uint8 tensor of N entries")
+    if out is None:
+        out = torch.empty((N, 3, 1, height, width), device=frames.device, dtype=torch.float32)
+    elif tuple(out.shape) != (N, 3, 1, height, width):
+        raise ValueError("out has the wrong shape")
+    _chk(out, "out")
+    h = handle()
+    check(h, lib.mdb_ingest_kitti_u8(h, _p(frames), _p(flips), Wo, Ho, width, height, N, _p(out), _stream()))
+    return out
+
+
 # --------------------------------------------------------------------------------------
 # SURVEY 8(f) rank 4: the operators on the network side of the path
 # --------------------------------------------------------------------------------------

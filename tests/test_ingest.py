@@ -1,4 +1,4 @@
-"""sample ingestion (src/dtk.jl:29-46).  CPU part: the numpy restatement on
+"""sample ingestion (src/dtk.jl:29-46, src/kitty.jl:45-61).  CPU part: the numpy restatement on
 hand-checkable inputs.  GPU part: mdb_ingest_triplet_u8 is bit-exact against it, and the host-buffer loss
 fed uint8 strips equals the one fed the Float32 stack the oracle makes of the same strips."""
 import numpy as np
@@ -88,3 +88,65 @@ def test_dump_for_a_julia_run_round_trips(tmp_path):
     w, h, c, l, n = 5, 3, 2, 1, 2
     assert x[(w - 1) + 24 * ((h - 1) + 10 * ((c - 1) + 3 * ((l - 1) + 3 * (n - 1))))] == inp.x[n - 1, l - 1, c - 1, h - 1, w - 1]
     assert np.array_equal(np.fromfile(tmp_path / "rvec1.f32", dtype="<f4").reshape(2, 3), inp.rvecs[1])
+
+
+# ---- KittyDataset.getindex (src/kitty.jl:45-61) ---------------------------------------------------------------------
+def test_kitti_oracle_hand_checked():
+    # 2x down-sampling of a horizontal ramp: output pixel i sits at 2 i - 0.5 (1-based): the mean of two neighbours
+    g = np.tile((np.arange(8) * 10).astype(np.uint8), (8, 1))
+    assert np.array_equal(I.imresize_gray_n0f8(g, 4, 4)[0], [5, 25, 45, 65])
+    # the same size is a copy; a constant image stays constant under any resize
+    assert np.array_equal(I.imresize_gray_n0f8(g, 8, 8), g)
+    c = np.full((7, 9), 201, np.uint8)
+    assert np.unique(I.imresize_gray_n0f8(c, 3, 5)).tolist() == [201]
+    # up-sampling clamps the half-pixel positions at both ends (first output = first input, last = last)
+    up = I.imresize_gray_n0f8(g, 8, 16)[0]
+    assert up[0] == 0 and up[-1] == 70 and np.all(np.diff(up.astype(int)) >= 0)
+    # layout: (3, 1, H, W) float32 = u8 / 255, FlipX reverses the width axis of all three frames
+    fr = np.random.default_rng(3).integers(0, 256, size=(3, 20, 31), dtype=np.uint8)
+    out = I.kitti_getindex(fr, 10, 16)
+    assert out.shape == (3, 1, 10, 16) and out.dtype == np.float32
+    assert out[1, 0, 4, 7] == np.float32(I.imresize_gray_n0f8(fr[1], 10, 16)[4, 7]) / np.float32(255)
+    assert np.array_equal(I.kitti_getindex(fr, 10, 16, flip=True), out[..., ::-1])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("Wo,Ho,W,H,N", [(1241, 376, 416, 128, 3),     # KITTI odometry image_0 -> config 2's size
+                                         (1241, 376, 640, 192, 2), (1226, 370, 1024, 320, 1),
+                                         (832, 256, 416, 128, 2),      # integer factor: every sample an exact .5 tie candidate
+                                         (416, 128, 416, 128, 2),      # same size: a copy
+                                         (37, 11, 64, 24, 4),          # up-sampling, clamped ends
+                                         (5, 3, 1, 1, 1)])
+def test_ingest_kitti_bit_exact(Wo, Ho, W, H, N):
+    import mdb200
+    rng = np.random.default_rng(Wo + 3 * W)
+    frames = rng.integers(0, 256, size=(N, 3, Ho, Wo), dtype=np.uint8)
+    flips = (rng.random(N) < 0.5).astype(np.uint8)
+    flips[0] = 1
+    ref = I.kitti_batch(frames, H, W, flips)
+    got = mdb200.ingest_kitti_u8(torch.tensor(frames, device=DEV), H, W, torch.tensor(flips, device=DEV))
+    assert got.shape == (N, 3, 1, H, W)
+    assert np.array_equal(got.cpu().numpy(), ref)                      # bit-exact
+    got2 = mdb200.ingest_kitti_u8(torch.tensor(frames, device=DEV), H, W)
+    assert np.array_equal(got2.cpu().numpy(), I.kitti_batch(frames, H, W))
+
+
+@pytest.mark.gpu
+def test_kitti_frames_feed_the_loss():
+    """C = 1 stack from the KITTI ingest -> fused loss == the loss on the oracle's stack of the same frames."""
+    import mdb200
+    rng = np.random.default_rng(11)
+    base = synth.make_loss_inputs(104, 32, 2, C=1, seed=12)
+    big = np.clip(np.kron(base.x[:, :, 0], np.ones((2, 3))) * 255, 0, 255).astype(np.uint8)     # (N,3,64,312)
+    big = np.ascontiguousarray(big + rng.integers(0, 3, size=big.shape, dtype=np.uint8))
+    ref_x = I.kitti_batch(big, 32, 104)
+    x = mdb200.ingest_kitti_u8(torch.tensor(big, device=DEV), 32, 104)
+    assert np.array_equal(x.cpu().numpy(), ref_x)
+    sizes = [(d.shape[-1], d.shape[-2]) for d in base.disparities]
+    plan = mdb200.FusedLoss(W=104, H=32, C=1, L=3, N=2, disp_sizes=sizes, scales=base.scales, target_id=base.target_id,
+                            source_ids=base.source_ids, K=base.K, invK=base.invK)
+    poses = [mdb200.Pose(torch.tensor(r, device=DEV), torch.tensor(t, device=DEV)) for r, t in zip(base.rvecs, base.tvecs)]
+    disps = [torch.tensor(d, device=DEV) for d in base.disparities]
+    a = float(plan(x, disps, poses).loss)
+    b = float(plan(torch.tensor(ref_x, device=DEV), disps, poses).loss)
+    assert a == b and np.isfinite(a)
