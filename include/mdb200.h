@@ -94,7 +94,9 @@ typedef struct mdb_loss_params {
   int32_t normalize_disparity;/* 1: train_loss (src/training.jl:64-65); 0: slow_depth   */
   int32_t smooth_weight_mode; /* 0: disparity_smoothness*scale[k] (src/training.jl:66-67)
                                  1: weight 1 (src/simple_depth.jl:39)                    */
-  int32_t upsample_align_corners; /* NNlib upsample_bilinear default = 1 (unpinned)      */
+  int32_t upsample_align_corners; /* src/training.jl:45 upsample_bilinear: 1 = align-corners (NNlib's default, the
+                                   * throughput path); 0 = half-pixel centres max(0, (p + 0.5) w_k / W - 0.5) -- nothing in
+                                   * the reference pins which (unpinned NNlib); 0 runs the global-memory kernel instantiation */
   int32_t n_global;           /* batch size the means divide by; 0 = N (single GPU)      */
   int32_t abs_subgradient;    /* pullback of abs.() at exactly 0 (Zygote, unpinned): 0 = sign(0) = 0
                                  (ChainRules' scalar rule); 1 = ForwardDiff's Dual rule, which Zygote's

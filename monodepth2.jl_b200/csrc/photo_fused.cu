@@ -69,23 +69,25 @@ disp_mean_kernel(const __grid_constant__ FusedArgs a, double* __restrict__ part 
   } else {
     // sum over the full-res grid of the bilinear interpolant = sum_j d_j Wx(jx) Wy(jy), with
     // W(j) = sum_p max(0, 1 - |p r - j|) on the exact integer numerator: native pixels only
-    const int dx1 = dw - 1, dy1 = dh - 1, W1 = W - 1, H1 = H - 1;
+    const UpAxis uy = up_axis(dh, H, a.hp), ux = up_axis(dw, W, a.hp);
     const int rows_per = (dh + gridDim.x - 1) / gridDim.x;
     const int j0 = rb * rows_per, j1 = min(j0 + rows_per, dh);
     // the row weights are the same for every column: one thread per row forms them once
     __shared__ double s_wy[MEAN_THREADS];
     for (int jy = j0 + threadIdx.x; jy < j1; jy += MEAN_THREADS) {
-      const int py_lo = max(0, ((jy - 1) * H1) / dy1), py_hi = min(H1, ((jy + 1) * H1 + dy1 - 1) / dy1);
-      int numy = 0;
-      for (int py = py_lo; py <= py_hi; ++py) numy += max(0, H1 - abs(py * dy1 - jy * H1));
-      s_wy[jy - j0] = (double)numy / (double)H1;
+      int py_lo, py_hi;
+      up_range(uy, jy, py_lo, py_hi);
+      long long numy = 0;
+      for (int py = py_lo; py <= py_hi; ++py) numy += max(0ll, uy.D - llabs(up_num(uy, py) - jy * uy.D));
+      s_wy[jy - j0] = (double)numy / (double)uy.D;
     }
     __syncthreads();
     for (int jx = threadIdx.x; jx < dw; jx += MEAN_THREADS) {
-      const int px_lo = max(0, ((jx - 1) * W1) / dx1), px_hi = min(W1, ((jx + 1) * W1 + dx1 - 1) / dx1);
-      int numx = 0;   // sum of (W1 - |p dx1 - jx W1|) over the support, exact in int (< 2^31 for W < 2^15)
-      for (int px = px_lo; px <= px_hi; ++px) numx += max(0, W1 - abs(px * dx1 - jx * W1));
-      const double wx = (double)numx / (double)W1;
+      int px_lo, px_hi;
+      up_range(ux, jx, px_lo, px_hi);
+      long long numx = 0;   // sum of (D - |num(p) - jx D|) over the support, exact
+      for (int px = px_lo; px <= px_hi; ++px) numx += max(0ll, ux.D - llabs(up_num(ux, px) - jx * ux.D));
+      const double wx = (double)numx / (double)ux.D;
       double col = 0.0;
       for (int jy = j0; jy < j1; ++jy) col = fma(s_wy[jy - j0], (double)ldg(d + jy * dw + jx), col);
       acc = fma(wx, col, acc);

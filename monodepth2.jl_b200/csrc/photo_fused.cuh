@@ -60,6 +60,8 @@ struct FusedArgs {
   float mind, dd;               // 1/max_depth, 1/min_depth - 1/max_depth
   double mind_d, dd_d;          // the same in double
   double rxd[MDB_MAX_SCALES], ryd[MDB_MAX_SCALES];
+  double oxd[MDB_MAX_SCALES], oyd[MDB_MAX_SCALES];   // half-pixel up-sampling (hp): source coordinate = max(0, p r + o)
+  int hp;                       // upsample_align_corners == 0; served by the CP = false instantiations only
   const PoseStrip* ppd;         // [N][S]
   float alpha, c1, c2;
   float ksu, klu, kl, ka;       // loss / pullback factors (photo_strip.inl)
@@ -88,6 +90,29 @@ MDB_DEV float upsample_at(const float* __restrict__ d, int dw, int dh, float rx,
   const float v10 = ldg(d + (size_t)y1 * dw + x0), v11 = ldg(d + (size_t)y1 * dw + x1);
   const float top = v00 + lx * (v01 - v00), bot = v10 + lx * (v11 - v10);
   return top + ly * (bot - top);
+}
+
+// Up-sampling coordinate of full-res index p on a native axis of dn cells (Dn full-res): num(p) / D with the exact integer
+// numerator num(p) = clamp(A p + B, 0, (dn - 1) D).   align-corners (NNlib's default): A = dn - 1, B = 0, D = Dn - 1;
+// half-pixel centres (align_corners = false: max(0, (p + 0.5) dn / Dn - 0.5)): A = 2 dn, B = dn - Dn, D = 2 Dn.
+// The weight of p for native cell j is the hat function max(0, 1 - |num(p) - j D| / D) in both modes.
+struct UpAxis { long long A, B, D, nmax; int Dn; };
+MDB_DEV UpAxis up_axis(int dn, int Dn, int hp) {
+  UpAxis u;
+  if (hp) { u.A = 2ll * dn; u.B = (long long)dn - Dn; u.D = 2ll * Dn; }
+  else { u.A = dn - 1; u.B = 0; u.D = Dn - 1; }
+  u.nmax = (long long)(dn - 1) * u.D;
+  u.Dn = Dn;
+  return u;
+}
+MDB_DEV long long up_num(const UpAxis& u, int p) { return min(max(u.A * p + u.B, 0ll), u.nmax); }
+MDB_DEV long long up_fdiv(long long a, long long b) { return a >= 0 ? a / b : -((-a + b - 1) / b); }   // floor, b > 0
+// full-res indices that can carry weight for native cell j (a superset by at most one on either side)
+MDB_DEV void up_range(const UpAxis& u, int j, int& lo, int& hi) {
+  lo = (int)max(0ll, up_fdiv((long long)(j - 1) * u.D - u.B, u.A));
+  hi = (int)min((long long)u.Dn - 1, up_fdiv((long long)(j + 1) * u.D - u.B, u.A) + 1);
+  if (j == 0) lo = 0;                                    // clamped head: every p with A p + B <= 0 sits on cell 0
+  if ((long long)j * u.D >= u.nmax) hi = u.Dn - 1;       // clamped tail
 }
 
 // the same interpolation weights, for the transposed (backward) gather

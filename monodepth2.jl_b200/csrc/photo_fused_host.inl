@@ -199,6 +199,7 @@ struct UpArgs {
   int dw[MDB_MAX_SCALES], dh[MDB_MAX_SCALES];
   int row_start[MDB_MAX_SCALES + 1];    // prefix sums of dh: blockIdx.y -> (scale, native row)
   int Ls, W, H, N;
+  int hp;                               // half-pixel up-sampling (upsample_align_corners == 0)
 };
 
 constexpr int UP_ROWS = 4;   // (scale, native row) pairs per CTA: keeps the CTA count in the thousands
@@ -221,17 +222,17 @@ upsample_bwd_v_kernel(const __grid_constant__ UpArgs a, const ScaleStat* __restr
       continue;
     }
     g += (size_t)n * W * H;
-    const int dy1 = dh - 1, H1 = H - 1;
-    const float ih = 1.0f / (float)H1;
-    // full-res p with |p dy1 - jy H1| < H1  <=>  (jy-1) H1 / dy1 < p < (jy+1) H1 / dy1
-    const int py_lo = max(0, ((jy - 1) * H1) / dy1), py_hi = min(H1, ((jy + 1) * H1 + dy1 - 1) / dy1);
+    const UpAxis uy = up_axis(dh, H, a.hp);
+    const float ih = 1.0f / (float)uy.D;
+    int py_lo, py_hi;
+    up_range(uy, jy, py_lo, py_hi);
     float* t = a.tmp[sc] + ((size_t)n * dh + jy) * W;
     // four columns per thread with independent accumulators: 4 x 4 loads in flight per thread
     for (int px0 = threadIdx.x; px0 < W; px0 += 4 * 256) {
       float acc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
 #pragma unroll 4
       for (int py = py_lo; py <= py_hi; ++py) {
-        const float wy = fmaxf(1.0f - (float)abs(py * dy1 - jy * H1) * ih, 0.0f);
+        const float wy = fmaxf(1.0f - (float)llabs(up_num(uy, py) - jy * uy.D) * ih, 0.0f);
         const float* row = g + (size_t)py * W;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
@@ -256,14 +257,15 @@ upsample_bwd_h_kernel(const __grid_constant__ UpArgs a) {
     if (a.gfull[sc] == nullptr) continue;
     const int jy = rr - a.row_start[sc], dw = a.dw[sc], dh = a.dh[sc];
     const float* t = a.tmp[sc] + ((size_t)n * dh + jy) * W;
-    const int dx1 = dw - 1, W1 = W - 1;
-    const float iw = 1.0f / (float)W1;
+    const UpAxis ux = up_axis(dw, W, a.hp);
+    const float iw = 1.0f / (float)ux.D;
     for (int jx = threadIdx.x; jx < dw; jx += 256) {
-      const int px_lo = max(0, ((jx - 1) * W1) / dx1), px_hi = min(W1, ((jx + 1) * W1 + dx1 - 1) / dx1);
+      int px_lo, px_hi;
+      up_range(ux, jx, px_lo, px_hi);
       float acc = 0.0f;
 #pragma unroll 4
       for (int px = px_lo; px <= px_hi; ++px) {
-        const float wx = fmaxf(1.0f - (float)abs(px * dx1 - jx * W1) * iw, 0.0f);
+        const float wx = fmaxf(1.0f - (float)llabs(up_num(ux, px) - jx * ux.D) * iw, 0.0f);
         acc = fmaf(wx, ldg(t + px), acc);
       }
       a.gnat[sc][((size_t)n * dh + jy) * dw + jx] = acc;
@@ -529,7 +531,7 @@ int32_t launch_fused(mdb_handle* h, const FusedArgs& fa, const FusedLayout& L, c
   MDB_CUDA(h, cudaStreamIsCapturing(st, &cap));
   // under capture (slow_depth's per-iteration graph) the constants are read from global memory: the graph then holds
   // the kernel alone, no copy node and no event nodes (config 1: 30.1 -> 22.7 us per replayed iteration)
-  const bool use_bank = cap == cudaStreamCaptureStatusNone && !fa.dbg;
+  const bool use_bank = cap == cudaStreamCaptureStatusNone && !fa.dbg && !fa.hp;
   const int chunk = use_bank ? STRIP_CONST_CHUNK / S : fa.N;
   PosePool* pool = pose_pool(h->device);
 #else
@@ -609,8 +611,8 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
               MDB_MAX_SOURCES, MDB_MAX_SCALES);
   MDB_REQUIRE(h, io->x && io->loss, MDB_E_INVALID_ARG, "mdb_train_loss_fwdbwd: null x/loss");
   MDB_REQUIRE(h, io->target_id >= 1 && io->target_id <= io->L, MDB_E_INVALID_ARG, "target_id out of range");
-  MDB_REQUIRE(h, p->upsample_align_corners == 1, MDB_E_INVALID_ARG,
-              "only upsample_align_corners=1 (NNlib default) is implemented");
+  MDB_REQUIRE(h, p->upsample_align_corners == 0 || p->upsample_align_corners == 1, MDB_E_INVALID_ARG,
+              "upsample_align_corners must be 1 (NNlib's default) or 0 (half-pixel centres)");
   MDB_REQUIRE(h, !p->automasking || io->auto_loss, MDB_E_INVALID_ARG, "automasking needs auto_loss");
   for (int s = 0; s < io->S; ++s) {
     MDB_REQUIRE(h, io->source_ids[s] >= 1 && io->source_ids[s] <= io->L, MDB_E_INVALID_ARG, "source id out of range");
@@ -637,13 +639,20 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
   UpArgs ua{};
   fa.x = io->x; fa.W = W; fa.H = H; fa.L = io->L; fa.N = N;
   fa.tgt = io->target_id - 1;
+  fa.hp = p->upsample_align_corners == 0 ? 1 : 0;
+  ua.hp = fa.hp;
   for (int s = 0; s < S; ++s) fa.src[s] = io->source_ids[s] - 1;
   fa.Ls = Ls;
   for (int s = 0; s < Ls; ++s) {
     fa.disp[s] = io->disparity[s]; fa.dw[s] = io->dw[s]; fa.dh[s] = io->dh[s];
     fa.native[s] = (io->dw[s] == W && io->dh[s] == H) ? 1 : 0;
-    fa.rxd[s] = (double)(io->dw[s] - 1) / (double)(W - 1);
-    fa.ryd[s] = (double)(io->dh[s] - 1) / (double)(H - 1);
+    if (fa.hp) {   // half-pixel centres: coordinate = max(0, (p + 0.5) dn / Dn - 0.5)
+      fa.rxd[s] = (double)io->dw[s] / (double)W; fa.oxd[s] = 0.5 * fa.rxd[s] - 0.5;
+      fa.ryd[s] = (double)io->dh[s] / (double)H; fa.oyd[s] = 0.5 * fa.ryd[s] - 0.5;
+    } else {
+      fa.rxd[s] = (double)(io->dw[s] - 1) / (double)(W - 1);
+      fa.ryd[s] = (double)(io->dh[s] - 1) / (double)(H - 1);
+    }
     fa.rx[s] = (float)fa.rxd[s];
     fa.ry[s] = (float)fa.ryd[s];
     fa.gout[s] = fa.native[s] ? io->d_disparity[s] : (float*)(ws + L.o_gfull[s]);
@@ -722,7 +731,7 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
     const bool force_split = g_dbg_upsample_split != 0;   // tests: the two-kernel path (W > 4096)
     // native scales only receive the normalisation constant here: nothing to do without it (slow_depth)
     if (!(any_low || p->normalize_disparity)) {
-    } else if (W <= 4096 && !force_split) {
+    } else if (W <= 4096 && !force_split && !fa.hp) {   // the band kernel carries align-corners remainders down the rows
       UpBandArgs ub{};
       ub.Ls = Ls; ub.W = W; ub.H = H; ub.N = N;
       // native rows per band: what the shared-memory row buffer holds (8 at W = 1024), fewer when the launch

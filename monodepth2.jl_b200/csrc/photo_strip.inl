@@ -60,7 +60,13 @@ constexpr int STRIP_NHEAD = 3;   // record head: photometric sum, smoothness x-s
                        // clamps, no stage gating): fewer instructions and one long basic block for ptxas to schedule
 #endif
 #if !defined(STRIP_MAXREG) && !defined(STRIP_MINB)
-#define STRIP_MAXREG_CAPTURED 152
+#ifndef STRIP_PEEL_CAPTURED
+#define STRIP_PEEL_CAPTURED 0
+#endif
+#ifndef STRIP_MAXREG_CAPTURED
+#define STRIP_MAXREG_CAPTURED 216   // spill-free; config 1 per iteration: 152 (24 B spilled) 23.95 us, 184 (16 B) 24.18, 216 (0 B) 22.58;
+                                    // peeled copy at 160 / 200: 23.94 / 24.62.  Occupancy is no concern at 480 warps.
+#endif
 #define STRIP_MAXREG 160   // 12 warps per SM, no spills.  Round 1 (unpeeled loop, constants in registers): best of 128 .. 184 was
                            // 152.  Round 2 (peeled loop, constants in the bank): 152 spills 148 B (4.83 ms), 160 and 168 are
                            // spill-free (4.18 / 4.20 ms), 176 .. 224 spill again (ptxas trades) -- spills decide, not the 13th warp
@@ -138,8 +144,9 @@ MDB_DEV signed char sgn_code(float v) { return v == 0.0f ? 0 : (v > 0.0f ? 1 : -
 // CP: the projection constants come from the constant bank (c_pose, filled by the host before the launch) instead of
 // global memory.  The throughput path uses CP = true; a call made under stream capture (slow_depth's graph: one item,
 // latency-bound) uses CP = false, which needs no copy node and no event nodes in the graph.
-// The captured instantiation (CP = false, DBG = false) also keeps round 1's loop: no steady-state copy, 152 registers -- on the
-// 480-warp launch of config 1 the peeled loop is 1.5 us per iteration slower (24.2 against 22.7 us).
+// The captured instantiation (CP = false, DBG = false) keeps round 1's loop (no steady-state copy), its per-row constants in
+// registers, and a register cap under which nothing spills (STRIP_MAXREG_CAPTURED): 22.6 us per iteration at config 1, where
+// the peeled loop with constants re-loaded through a.ppd took 24.2 - 26.0 us.  It also serves upsample_align_corners = 0.
 template <int C, int S, bool DBG = false, bool CP = (STRIP_CONSTPOSE != 0)>
 #ifdef STRIP_MAXREG
 __global__ void __maxnreg__((CP || DBG) ? STRIP_MAXREG : STRIP_MAXREG_CAPTURED)
@@ -220,6 +227,19 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
 #else
   const PoseStrip* const ppn = a.ppd + (size_t)n * S;
 #endif
+  // CP = false: the per-row constants are copied into registers once (through a.ppd the compiler would have to re-load
+  // them every row: the gradient stores may alias); CP = true: they stay constant-bank operands and `pregs` vanishes
+  struct PoseRegs { double b0, b1, b3e, a1, i2, a7; float b0f, b1f, b3f; };
+  PoseRegs pregs[S];
+  if (!CP) {
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+      const PoseStrip& pp = ppn[s];
+      pregs[s].b0 = pp.b[0]; pregs[s].b1 = pp.b[1]; pregs[s].b3e = pp.b3e; pregs[s].a1 = pp.dA[1]; pregs[s].i2 = pp.i2; pregs[s].a7 = pp.dA[7];
+      pregs[s].b0f = pp.b0f; pregs[s].b1f = pp.b1f; pregs[s].b3f = pp.b3f;
+    }
+  }
+#define PPV(s, bank, reg) (CP ? ppn[s].bank : pregs[s].reg)
   {
     const double px = (double)(gx + 1), py = (double)(geo_row(Y0 - 2, H) + 1);
 #pragma unroll
@@ -240,7 +260,8 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   double ulx = 0.0, utop = 0.0, udif = 0.0;
 #endif
   if (!native) {
-    const double f = (double)min(max(gx, 0), W - 1) * a.rxd[sc];
+    double f = (double)min(max(gx, 0), W - 1) * a.rxd[sc];
+    if (!CP && a.hp) f = fmax(f + a.oxd[sc], 0.0);   // half-pixel centres: max(0, (p + 0.5) dw / W - 0.5)
     ux0 = min((int)f, dw - 1);
     ulx = f - (double)ux0;
     ux1 = min(ux0 + 1, dw - 1);
@@ -299,7 +320,8 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
         dd_ = (double)dq;
       } else {
         // rows of the low-res map change every 1/ry full-res rows: keep the column-interpolated pair
-        const double fy = (double)rc * ryd;
+        double fy = (double)rc * ryd;
+        if (!CP && a.hp) fy = fmax(fy + a.oyd[sc], 0.0);
         const int y0 = min((int)fy, dh - 1);
 #if STRIP_DPF
         if (y0 != uy0) {   // warp-uniform
@@ -345,7 +367,7 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
       for (int s = 0; s < S; ++s) {
         // Backproject -> Project -> normalize -> grid_sample's unnormalize (src/utils.jl:67-69,
         // 99-103; src/training.jl:56) cancel to u = P'1 / z'', z'' = P'3 + invd 1e-7 (in units of depth)
-        const double P1 = fma(invd, ppn[s].b[0], p1[s]), P2 = fma(invd, ppn[s].b[1], p2[s]), z = fma(invd, ppn[s].b3e, p3[s]);
+        const double P1 = fma(invd, PPV(s, b[0], b0), p1[s]), P2 = fma(invd, PPV(s, b[1], b1), p2[s]), z = fma(invd, PPV(s, b3e, b3e), p3[s]);
         double zi;
         asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(zi) : "d"(z));   // MUFU.RCP64H: ~2^-20, squared by the Newton step
         zi = fma(zi, fma(-z, zi, 1.0), zi);
@@ -398,11 +420,11 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
     if (native) dq = ldg(dsp + ((ST ? rgn : min(max(rgn, 0), H - 1)) * W + gxc));
     if (ST) {
 #pragma unroll
-      for (int s = 0; s < S; ++s) { p1[s] += ppn[s].dA[1]; p2[s] += ppn[s].i2; p3[s] += ppn[s].dA[7]; }
+      for (int s = 0; s < S; ++s) { p1[s] += PPV(s, dA[1], a1); p2[s] += PPV(s, i2, i2); p3[s] += PPV(s, dA[7], a7); }
     } else {
       const double stp = (double)(rgn - rg);   // 1 except around the two reflected rows
 #pragma unroll
-      for (int s = 0; s < S; ++s) { p1[s] = fma(stp, ppn[s].dA[1], p1[s]); p2[s] = fma(stp, ppn[s].i2, p2[s]); p3[s] = fma(stp, ppn[s].dA[7], p3[s]); }
+      for (int s = 0; s < S; ++s) { p1[s] = fma(stp, PPV(s, dA[1], a1), p1[s]); p2[s] = fma(stp, PPV(s, i2, i2), p2[s]); p3[s] = fma(stp, PPV(s, dA[7], a7), p3[s]); }
     }
   };
 
@@ -662,7 +684,7 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
         float dinvd = 0.0f;
 #pragma unroll
         for (int s = 0; s < S; ++s)
-          dinvd += dP0.get(s) * ppn[s].b0f + dP1.get(s) * ppn[s].b1f + dP2.get(s) * ppn[s].b3f;
+          dinvd += dP0.get(s) * PPV(s, b0f, b0f) + dP1.get(s) * PPV(s, b1f, b1f) + dP2.get(s) * PPV(s, b3f, b3f);
         // d invd / d disparity = 1/min_depth - 1/max_depth; plus the smoothness pullback formed above
         // (the mean-normalisation constant is added after the item's sum is known)
         gout[(size_t)pr * W + gx] = fmaf(dinvd, a.dd, gsm);
@@ -674,7 +696,7 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   {
     // steady-state rows: all three stages active (r >= Y0 + 2), window row r-1 and pixel row r-2 inside this segment
     // (r <= Y1), no reflected row in sight (pixel row >= 2 and <= H-3, r + 1 <= H - 1)
-    constexpr bool PEEL = STRIP_PEEL && (CP || DBG);
+    constexpr bool PEEL = STRIP_PEEL && (CP || DBG || STRIP_PEEL_CAPTURED);
     const int s_lo = max(Y0 + 2, 4), s_hi = PEEL ? min(Y1, H - 2) : -1000000;
     int r = Y0 - 2;
     while (r <= Y1 + 1) {

@@ -473,7 +473,8 @@ class FusedLoss:
                  min_depth: float = 0.1, max_depth: float = 100.0, disparity_smoothness: float = 1e-3,
                  automasking: bool = False, normalize_disparity: bool = True, smooth_weight_mode: int = 0,
                  n_global: int = 0, alpha: float = 0.85, want_vis: bool = False, device=None,
-                 out: Optional[dict] = None, abs_subgradient: int = 0, ssim: Optional["SSIM"] = None):
+                 out: Optional[dict] = None, abs_subgradient: int = 0, ssim: Optional["SSIM"] = None,
+                 upsample_align_corners: bool = True):
         """`out` (optional): caller-provided output tensors {"loss": 0-dim or 1-element, "d_disp": [...],
         "d_rvec": [...], "d_tvec": [...]} of the right shapes -- e.g. row slices of whole-batch tensors --
         instead of buffers owned by the plan."""
@@ -490,6 +491,7 @@ class FusedLoss:
         p.smooth_weight_mode = int(smooth_weight_mode)
         p.n_global = int(n_global)
         p.abs_subgradient = int(abs_subgradient)
+        p.upsample_align_corners = 1 if upsample_align_corners else 0
         if ssim is not None:
             p.ssim_c1, p.ssim_c2 = float(ssim.c1), float(ssim.c2)
         self.params = p

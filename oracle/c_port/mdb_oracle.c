@@ -174,10 +174,17 @@ static inline int reflect1(int i, int n) {          /* pad_reflect by 1: -1 -> 1
 }
 static inline real sgn(real v) { return (real)((v > 0) - (v < 0)); }   /* abs pullback = sign, 0 at 0 */
 
-/* align-corners source coordinate of upsample_bilinear: full-res index p -> (j0, j1, frac) */
-static inline void up_coord(int p, int full, int nat, int* j0, int* j1, real* f) {
+/* source coordinate of upsample_bilinear: full-res index p -> (j0, j1, frac).  align-corners (NNlib's default):
+ * p (nat-1)/(full-1); half_pixel (align_corners = false, NNlib >= 0.8 / torch): max(0, (p + 0.5) nat/full - 0.5) */
+static inline void up_coord(int p, int full, int nat, int half_pixel, int* j0, int* j1, real* f) {
   if (full <= 1 || nat <= 1) { *j0 = 0; *j1 = 0; *f = 0; return; }
-  const double s = (double)p * (double)(nat - 1) / (double)(full - 1);
+  double s;
+  if (half_pixel) {
+    s = ((double)p + 0.5) * (double)nat / (double)full - 0.5;
+    if (s < 0) s = 0;
+  } else {
+    s = (double)p * (double)(nat - 1) / (double)(full - 1);
+  }
   int a = (int)floor(s);
   if (a > nat - 1) a = nat - 1;
   *j0 = a;
@@ -272,6 +279,8 @@ typedef struct mdbo_desc {
   int32_t abs_subgradient; /* pullback of abs at +-0 (Zygote, unpinned): 0 = sign(0) = 0 (ChainRules' rule);
                               1 = ForwardDiff's Dual rule, which Zygote's broadcast uses on CuArrays:
                               abs(d) = signbit(value) ? -d : d, i.e. +1 at +0.0 and -1 at -0.0 */
+  int32_t upsample_half_pixel; /* 0: upsample_bilinear with align-corners (NNlib's default, src/training.jl:45);
+                                  1: half-pixel centres (align_corners = false) -- nothing in the reference pins it */
 } mdbo_desc;
 
 /* Decision forcing / dumping (tests/test_gpu_forced.py).  Every discrete choice the pullback depends on, one
@@ -316,13 +325,13 @@ static double item_scale(const mdbo_desc* d, int n, int k, const real* x, const 
   double msum = 0;
   for (int py = 0; py < H; ++py) {
     int y0, y1; real fy;
-    up_coord(py, H, dh, &y0, &y1, &fy);
+    up_coord(py, H, dh, d->upsample_half_pixel, &y0, &y1, &fy);
     for (int px = 0; px < W; ++px) {
       real v;
       if (native) v = disp_k[(size_t)py * W + px];
       else {
         int x0, x1; real fx;
-        up_coord(px, W, dw, &x0, &x1, &fx);
+        up_coord(px, W, dw, d->upsample_half_pixel, &x0, &x1, &fx);
         const real a = disp_k[(size_t)y0 * dw + x0], b = disp_k[(size_t)y0 * dw + x1];
         const real c = disp_k[(size_t)y1 * dw + x0], e = disp_k[(size_t)y1 * dw + x1];
         v = (a * (1 - fx) + b * fx) * (1 - fy) + (c * (1 - fx) + e * fx) * fy;
@@ -558,10 +567,10 @@ static double item_scale(const mdbo_desc* d, int n, int k, const real* x, const 
     memset(gdisp_k, 0, (size_t)dw * dh * sizeof(real));
     for (int py = 0; py < H; ++py) {
       int y0, y1; real fy;
-      up_coord(py, H, dh, &y0, &y1, &fy);
+      up_coord(py, H, dh, d->upsample_half_pixel, &y0, &y1, &fy);
       for (int px = 0; px < W; ++px) {
         int x0, x1; real fx;
-        up_coord(px, W, dw, &x0, &x1, &fx);
+        up_coord(px, W, dw, d->upsample_half_pixel, &x0, &x1, &fx);
         const real g = s->gup[(size_t)py * W + px];
         gdisp_k[(size_t)y0 * dw + x0] += g * (1 - fx) * (1 - fy);
         gdisp_k[(size_t)y0 * dw + x1] += g * fx * (1 - fy);

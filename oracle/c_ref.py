@@ -33,7 +33,7 @@ class Desc(C.Structure):
         ("min_depth", C.c_double), ("max_depth", C.c_double), ("smoothness", C.c_double),
         ("alpha", C.c_double), ("c1", C.c_double), ("c2", C.c_double),
         ("automask", C.c_int32), ("normalize", C.c_int32), ("smooth_mode", C.c_int32), ("n_global", C.c_int32),
-        ("abs_subgradient", C.c_int32),
+        ("abs_subgradient", C.c_int32), ("upsample_half_pixel", C.c_int32),
     ]
 
 
@@ -73,12 +73,14 @@ def train_loss(x: np.ndarray, disparities: Sequence[np.ndarray], rvecs: Sequence
                scales: Sequence[float] = (0.125, 0.25, 0.5, 1.0), min_depth: float = 0.1, max_depth: float = 100.0,
                smoothness: float = 1e-3, alpha: float = 0.85, automasking: bool = True, normalize: bool = True,
                smooth_mode: int = 0, n_global: int = 0, grad: bool = True, dtype=np.float64, threads: int = 1,
-               abs_subgradient: int = 0, force_decisions: Optional[np.ndarray] = None, dump_decisions: bool = False):
+               abs_subgradient: int = 0, force_decisions: Optional[np.ndarray] = None, dump_decisions: bool = False,
+               upsample_align_corners: bool = True):
     """Value and gradients of ``train_loss`` (or of the slow_depth closure with ``normalize=False,
     smooth_mode=1`` and one scale).  Arrays are in the repo's reversed-dims convention:
     x (N,L,C,H,W), disparities[k] (N,1,h,w), rvecs[s] (N,3), tvecs[s] (N,1,3) or (N,3), auto_loss
     (N,1,H,W) or None, K / invK the 9 numbers Julia stores.
     abs_subgradient: pullback of abs at +-0 (0: sign(0) = 0; 1: ForwardDiff's rule, +1 at +0.0).
+    upsample_align_corners: alignment of `upsample_bilinear` (src/training.jl:45): True = NNlib's default.
     force_decisions: int8 (Ls,N,2C+2,H,W) -- every discrete choice of the pullback (layout in mdb_oracle.c) taken
     from this array instead of the oracle's own arithmetic; dump_decisions: also return the oracle's own choices
     (`decisions`) and the arg-min margins (`margin` (Ls,N,H,W))."""
@@ -98,6 +100,7 @@ def train_loss(x: np.ndarray, disparities: Sequence[np.ndarray], rvecs: Sequence
     d.c1, d.c2 = 0.01 ** 2, 0.03 ** 2                       # src/utils.jl:23
     d.automask, d.normalize, d.smooth_mode, d.n_global = int(automasking), int(normalize), smooth_mode, n_global
     d.abs_subgradient = int(abs_subgradient)
+    d.upsample_half_pixel = 0 if upsample_align_corners else 1
     rv = np.ascontiguousarray(np.stack([np.asarray(r, dtype=dtype).reshape(N, 3) for r in rvecs]))
     tv = np.ascontiguousarray(np.stack([np.asarray(t, dtype=dtype).reshape(N, 3) for t in tvecs]))
     au = None if (auto_loss is None or not automasking) else np.ascontiguousarray(auto_loss, dtype=dtype)

@@ -208,10 +208,13 @@ def grid_sample(inp: torch.Tensor, grid: torch.Tensor) -> torch.Tensor:
     return F.grid_sample(inp, grid, mode="bilinear", padding_mode="border", align_corners=True)
 
 
+UPSAMPLE_ALIGN_CORNERS = True     # NNlib's default; False = half-pixel centres (nothing in the reference pins it)
+
+
 def upsample_bilinear(x: torch.Tensor, size_wh: Tuple[int, int]) -> torch.Tensor:
-    """NNlib `upsample_bilinear(x; size=(W,H))`, align-corners=true (UNPINNED)."""
+    """NNlib `upsample_bilinear(x; size=(W,H))`, align-corners=true (UNPINNED: `UPSAMPLE_ALIGN_CORNERS`)."""
     w, h = size_wh
-    return F.interpolate(x, size=(h, w), mode="bilinear", align_corners=True)
+    return F.interpolate(x, size=(h, w), mode="bilinear", align_corners=UPSAMPLE_ALIGN_CORNERS)
 
 
 # --------------------------------------------------------------------------------------

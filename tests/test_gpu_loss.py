@@ -10,7 +10,7 @@ import parity as P
 pytestmark = pytest.mark.gpu
 
 
-def _run_gpu(inp, normalize=True, smooth_mode=0, auto=None, n_global=0):
+def _run_gpu(inp, normalize=True, smooth_mode=0, auto=None, n_global=0, align=True):
     import mdb200
     dev = torch.device("cuda:0")
     x = torch.tensor(inp.x, device=dev)
@@ -20,7 +20,7 @@ def _run_gpu(inp, normalize=True, smooth_mode=0, auto=None, n_global=0):
                             disp_sizes=[(d.shape[-1], d.shape[-2]) for d in inp.disparities], scales=inp.scales,
                             target_id=inp.target_id, source_ids=inp.source_ids, K=inp.K, invK=inp.invK,
                             automasking=inp.automasking, normalize_disparity=normalize,
-                            smooth_weight_mode=smooth_mode, n_global=n_global, want_vis=True)
+                            smooth_weight_mode=smooth_mode, n_global=n_global, want_vis=True, upsample_align_corners=align)
     al = None
     if inp.automasking:
         al = mdb200.automasking_loss(mdb200.SSIM(), x, x[:, inp.target_id - 1], source_ids=inp.source_ids) if auto is None \
@@ -238,6 +238,36 @@ def test_upsample_transpose_band_vs_split(debug_option, W, H, N, scales):
     for a, b in zip(res_band.d_disparities, res_split.d_disparities):
         scale = float(b.abs().max())
         assert float((a - b).abs().max()) <= 1e-6 * scale, (float((a - b).abs().max()), scale)
+
+
+@pytest.mark.parametrize("W,H,N,C,auto,scales", [
+    (104, 64, 2, 3, False, (0.125, 0.25, 0.5, 1.0)),
+    (300, 37, 2, 3, True, (0.25, 0.5, 1.0)),      # odd ratios: 75 x 9 and 150 x 18 maps under 300 x 37
+    (61, 45, 3, 1, True, (0.25, 1.0)),
+    (416, 128, 2, 3, False, (0.125, 0.25, 0.5, 1.0)),
+])
+def test_half_pixel_upsampling(W, H, N, C, auto, scales):
+    """upsample_align_corners = 0: `upsample_bilinear` with half-pixel centres (src/training.jl:45 does not say which;
+    NNlib's default is align-corners).  Forward interpolation in the strip kernel, the mean of the up-sampled map and
+    the transposed gather, against the float64 oracle run in the same mode -- and the two modes must differ."""
+    from mdb200 import synth
+    from oracle import torch_ref as T
+    inp = synth.make_loss_inputs(W, H, N, C=C, seed=91, scales=scales, automasking=auto)
+    ref_align = P.oracle_train_loss(inp)
+    T.UPSAMPLE_ALIGN_CORNERS = False
+    try:
+        ref = P.oracle_train_loss(inp)
+    finally:
+        T.UPSAMPLE_ALIGN_CORNERS = True
+    res, _ = _run_gpu(inp, auto=ref["auto"], align=False)
+    _compare(inp, ref, res)
+    # the two alignments are different functions: the coarsest map's gradient moves by far more than the parity gate
+    g_hp, g_al = ref["d_disp"][0], ref_align["d_disp"][0]
+    assert float((g_hp - g_al).abs().max()) > 100 * P.GRAD_RTOL * float(g_al.abs().max())
+    assert float((res.d_disparities[0].double().cpu() - g_al).abs().max()) > 100 * P.GRAD_RTOL * float(g_al.abs().max())
+    # and the default mode is untouched by having run the other one
+    res_a, _ = _run_gpu(inp, auto=ref_align["auto"])
+    _compare(inp, ref_align, res_a)
 
 
 @pytest.mark.parametrize("seed", range(24))

@@ -46,6 +46,28 @@ def test_train_loss_two_oracles_agree(W, H, N, auto, seed):
         _close(f"d_tvec[{s}]", got["d_tvec"][s], ref["d_tvec"][s], 1e-9)
 
 
+@pytest.mark.parametrize("W,H,scales", [(48, 20, (0.125, 0.25, 0.5, 1.0)), (75, 37, (0.25, 0.5, 1.0))])
+def test_half_pixel_upsampling_two_oracles_agree(W, H, scales):
+    """`upsample_bilinear` with half-pixel centres (align_corners = false): the C restatement against torch's
+    F.interpolate(align_corners=False) + autograd; and it is a different function from the default."""
+    from oracle import torch_ref as T
+    inp = synth.make_loss_inputs(W, H, 2, seed=21, scales=scales, automasking=True)
+    ref_align = oracle_train_loss(inp)
+    T.UPSAMPLE_ALIGN_CORNERS = False
+    try:
+        ref = oracle_train_loss(inp)
+    finally:
+        T.UPSAMPLE_ALIGN_CORNERS = True
+    got = _c_loss(inp, ref["auto"].numpy(), threads=2, upsample_align_corners=False)
+    assert abs(got["loss"] - ref["loss"]) < 1e-11 * abs(ref["loss"])
+    assert abs(ref_align["loss"] - ref["loss"]) > 1e-5 * abs(ref["loss"])
+    for k in range(len(inp.disparities)):
+        _close(f"d_disp[{k}]", got["d_disp"][k], ref["d_disp"][k], 1e-9)
+    for s in range(2):
+        _close(f"d_rvec[{s}]", got["d_rvec"][s], ref["d_rvec"][s], 1e-9)
+        _close(f"d_tvec[{s}]", got["d_tvec"][s], ref["d_tvec"][s], 1e-9)
+
+
 def test_simple_depth_two_oracles_agree():  # src/simple_depth.jl:25-41
     inp = synth.make_loss_inputs(40, 16, 1, seed=14, scales=(1.0,))
     ref = oracle_train_loss(inp, normalize=False, smooth_mode=1)
