@@ -78,7 +78,8 @@ int32_t mdb_measure_fp32_peak(mdb_handle* h, void* scratch, size_t scratch_bytes
 /* Test hooks, process-global, never read from the environment: "strip_segs" = n forces n row segments per strip
  * in the fused kernel (0 = the library's choice), "upsample_split" = 1 forces the two-kernel transpose that
  * W > 4096 takes; "decision_dump" = device pointer to Ls N (2C+2) H W int8 makes the fused kernel (a separate
- * instantiation) record every discrete choice its pullback depends on (layout in csrc/photo_strip.inl), 0 = off.
+ * instantiation) record every discrete choice its pullback depends on (layout in csrc/photo_strip.inl), 0 = off;
+ * "render_precise" = 1 makes the render forward sample every plane through the double-precision homography.
  * Set BEFORE mdb_train_loss_workspace_bytes (the record count depends on the segments).                       */
 int32_t mdb_debug_option(const char* name, int64_t value);
 

@@ -96,3 +96,7 @@ MDB_DEV float ldg(const float* p) { return __ldg(p); }
 // streaming store (write-once outputs that are not re-read by this kernel)
 MDB_DEV void st_cs(float* p, float v) { __stcs(p, v); }
 #endif
+
+// test hook (mdb_debug_option "render_precise"): the render forward samples every plane through the double-precision
+// homography instead of the float displacement form (defined in render.cu)
+extern int mdb_dbg_render_precise;

@@ -582,6 +582,7 @@ int32_t mdb_debug_option(const char* name, int64_t value) {
   if (!strcmp(name, "strip_segs")) g_dbg_strip_segs = (int)value;
   else if (!strcmp(name, "upsample_split")) g_dbg_upsample_split = (int)value;
   else if (!strcmp(name, "decision_dump")) g_dbg_decisions = (signed char*)(intptr_t)value;
+  else if (!strcmp(name, "render_precise")) mdb_dbg_render_precise = (int)value;
   else return MDB_E_INVALID_ARG;
   return MDB_OK;
 }

@@ -11,10 +11,12 @@
 #include "mdb_common.cuh"
 #include "pose_math.cuh"
 
+int mdb_dbg_render_precise = 0;
+
 namespace {
 
-// per (plane, batch item) constants
-struct PlanePrep {
+// per (plane, batch item) constants (16-byte aligned: Ax/tx and hf are read with 128-bit loads)
+struct alignas(16) PlanePrep {
   double Hst[9];   // H_src_tgt = inv(K (R + t n^T / depth) K_inv), row-major
   float G1[9];     // K^T H_src_tgt^T : pulls d/d(homogeneous source coords) back to d/dM
   float disp;      // 1 / depth_src
@@ -22,7 +24,15 @@ struct PlanePrep {
   // Ax = R K_inv / disparity  (src/render.jl:25-30, 51-62) -- what the producers folded into the kernels use
   float Ax[9];
   float tx[3];
+  // H_src_tgt / H22 - I for the forward kernel:  x - u = (a0 u + h01 v + h02 - u e) / (1 + e),
+  // y - v = (h10 u + a1 v + h12 - v e) / (1 + e),  e = h20 u + h21 v.   hd = {a0, h01, h02, h10, a1, h12, h20, h21}.
+  // The two numerators and e are formed in double (8 operations, no cancellation error), everything after them in float.
+  double hd[8];   // byte offset 160
+  int fast;       // the displacement stays below RF_FAST_PX pixels on this image and |e| < 1/4: a float holds it to ~2e-6 px
+                  // and the forward takes the short path; otherwise the plane goes through the double-precision homography
+  int pad_[3];
 };
+constexpr double RF_FAST_PX = 64.0;
 
 // variants of the sampler / outputs (mdb_render_opts in include/mdb200.h)
 constexpr int RV_MINE_GRID = 1, RV_MINE_MASK = 2;
@@ -30,6 +40,7 @@ constexpr int RV_MINE_GRID = 1, RV_MINE_MASK = 2;
 struct RenderConst {
   double K[9], Kinv[9];  // math row-major
   float Kinv_f[9];
+  int W, H;              // image size (render_prep_kernel: range of the float sampling path); 0 = unknown
 };
 
 MDB_HD bool inv3_d(const double* A, double* B) {
@@ -132,6 +143,25 @@ __global__ void render_prep_kernel(const float* __restrict__ disp, int is_depth,
     for (int k = 0; k < 9; ++k) p.Ax[k] = (float)(RK[k] / dsp);
     for (int k = 0; k < 3; ++k) p.tx[k] = tvec[3 * b + k];
   }
+  {
+    const double i22 = 1.0 / p.Hst[8];
+    double hn[8];
+    for (int k = 0; k < 8; ++k) hn[k] = p.Hst[k] * i22;
+    hn[0] -= 1.0; hn[4] -= 1.0;
+    for (int k = 0; k < 8; ++k) p.hd[k] = hn[k];
+    // bound of |x - u|, |y - v| over the image: the displacement on a 3 x 3 grid of points (corners, edge midpoints,
+    // centre) with a quarter in hand -- the numerators are quadratic in (u, v), the denominator is within 1 +- em
+    const double Wm = rc.W - 1, Hm = rc.H - 1;
+    const double em = fabs(hn[6]) * Wm + fabs(hn[7]) * Hm;
+    double mx = 0.0, my = 0.0;
+    for (int c = 0; c < 9; ++c) {
+      const double u = 0.5 * (c % 3) * Wm, v = 0.5 * (c / 3) * Hm, e = hn[6] * u + hn[7] * v;
+      mx = fmax(mx, fabs((hn[0] * u + hn[1] * v + hn[2] - u * e) / (1.0 + e)));
+      my = fmax(my, fabs((hn[3] * u + hn[4] * v + hn[5] - v * e) / (1.0 + e)));
+    }
+    p.fast = (rc.W > 0 && em < 0.25 && 1.25 * mx < RF_FAST_PX && 1.25 * my < RF_FAST_PX) ? 1 : 0;   // NaN / inf compare false
+    p.pad_[0] = p.pad_[1] = p.pad_[2] = 0;
+  }
   out[idx] = p;
 }
 
@@ -141,6 +171,7 @@ struct RTaps {
   double X0, X1, X2;  // homogeneous source coordinates
   float x, y;         // source pixel (0-based, as the reference computes it)
   float q0, q1;       // clamped sample point, 1-based
+  int x0, y0;         // top-left cell
   bool valid;
 };
 
@@ -181,6 +212,7 @@ MDB_DEV RTaps render_taps(const double* __restrict__ H, int u, int v, int W, int
   t.fy = (float)(cy - fy0);
   const int x0 = (int)fx0, y0 = (int)fy0, x1 = min(x0 + 1, W - 1), y1 = min(y0 + 1, Hh - 1);
   t.o00 = y0 * W + x0; t.o01 = y0 * W + x1; t.o10 = y1 * W + x0; t.o11 = y1 * W + x1;
+  t.x0 = x0; t.y0 = y0;
   t.x = (float)x;
   t.y = (float)y;
   t.q0 = (float)(cx + 1.0);   // 1-based (create_meshgrid) coordinates of the clamped sample point
@@ -201,6 +233,7 @@ struct RenderArgs {
   float* edepth;      // [B][1][H][W] expected depth sum w z / (sum w + depth_eps), or null
   float* wsum;        // [B][1][H][W] sum w, or null
   float depth_eps;
+  double sx, sy, cx0, cy0;   // grid as written: coordinate = x sx + cx0, sx = (W-1)/W, cx0 = 0.5 sx + 0.5 (W-1) (host-computed)
 };
 
 // R7 forward.  A pixel's 32 planes are a serial chain (front-to-back compositing, and the distance to the
@@ -210,72 +243,191 @@ struct RenderArgs {
 // shared memory -- transparency_acc_k = (product of the earlier groups' (T + 1e-6)) x local value,
 // rgb = sum_g prefix_g rgb_g (and likewise sum w, sum w z).  The first plane of the following group is
 // sampled for its xyz only.
-constexpr int RF_PIX = 64, RF_G = 4, RF_THREADS = RF_PIX * RF_G;
-constexpr int RF_MAXKPG = 16;          // planes per group: ceil(64 / 4)
+#ifndef RF_GROUPS
+#define RF_GROUPS 4      // measured at config 4 (as written / MINE, us): 4 groups 59.6 / 69.6, 8: 64.5 / 74.7, 16: 76.9 / 88.5
+#endif
+#ifndef RF_MINB
+#define RF_MINB 8        // 128-thread CTAs per SM the register allocation aims for (64 registers; 6 -> 85 registers: 70.6 us)
+#endif
+constexpr int RF_PIX = 32, RF_G = RF_GROUPS, RF_THREADS = RF_PIX * RF_G;
+constexpr int RF_MAXKPG = (64 + RF_G - 1) / RF_G;   // planes per group at Np = 64
 
 struct RSample { float rgb[3], sig, xyz[3]; };
 
+// ---- forward taps -------------------------------------------------------------------------------------------------
+// Top-left cell (x0 <= W-2, y0 <= H-2: the other three taps are +1, +W, +W+1, immediates and one add) and the weights.
+struct FTap {
+  int o;            // y0 W + x0
+  float fx, fy;     // in [0, 1]; 1 only on the last column / row
+  float q0, q1;     // clamped sample point, 1-based (create_meshgrid coordinates; FUSED xyz)
+  bool valid;
+};
+
+// What a thread knows about its own pixel: the sample coordinate of plane k is  bi + (bf + t s)  with t = x - u (or y - v)
+// the plane's displacement.   MINE grid: the coordinate is the source pixel itself, bi = u, bf = 0, s = 1.
+// Grid as written (no "-1", align-corners un-normalisation):  (x + 0.5)(W-1)/W + (W-1)/2, whose
+// plane-independent part u (W-1)/W + 0.5 (W-1)/W + (W-1)/2 is split ONCE per thread, in double, into integer + fraction.
+struct PixBase { int u, v, bxi, byi; float uf, vf; double ud, vd, bxf, byf; };
+
+template <int FLAGS>
+MDB_DEV PixBase pix_base(int u, int v, double sx, double sy, double cx0, double cy0) {
+  PixBase p;
+  p.u = u; p.v = v; p.uf = (float)u; p.vf = (float)v; p.ud = (double)u; p.vd = (double)v;
+  if (FLAGS & RV_MINE_GRID) {
+    p.bxi = u; p.byi = v; p.bxf = p.byf = 0.0;
+  } else {
+    const double bx = fma(p.ud, sx, cx0), by = fma(p.vd, sy, cy0);
+    const double fx = floor(bx), fy = floor(by);
+    p.bxi = (int)fx; p.byi = (int)fy; p.bxf = bx - fx; p.byf = by - fy;
+  }
+  return p;
+}
+
+// one axis, coordinate = bi + r with r (double) small: cell index (<= n-2), weight in [0, 1], 1-based clamped point.
+// floor and fraction in double -- the LAST plane's transmittance exp(-1000 sigma) (src/render.jl:36) turns 1e-7 of sampled
+// sigma into 4e-5 of output, so the interpolation weight has to be good to a few 1e-8 -- the clamp on the integer part.
+MDB_DEV void axis_cell(double r, int bi, int n, int& i0, float& f, float& q) {
+  const double fl = floor(r);
+  i0 = bi + (int)fl;
+  f = (float)(r - fl);
+  if (i0 < 0) { i0 = 0; f = 0.0f; }                  // coordinate < 0: clamped onto the first sample
+  if (i0 > n - 2) { i0 = n - 2; f = 1.0f; }          // coordinate >= n - 1: the last sample = cell n-2 with weight 1
+  q = (float)(i0 + 1) + f;
+}
+
+// short path (PlanePrep::fast): displacement form, all in double but cheap: numerators 8 operations, reciprocal from a float
+// seed + one Newton step (|1 + e - 1| < 1/4), 2 products, 2 FMAs; no comparisons, clamps or un-normalisation in double.
+template <int FLAGS>
+MDB_DEV FTap ftap_fast(const double* __restrict__ hd, const PixBase& p, const RenderArgs& a) {
+  const double2 c0 = __ldg(reinterpret_cast<const double2*>(hd)), c1 = __ldg(reinterpret_cast<const double2*>(hd) + 1);
+  const double2 c2 = __ldg(reinterpret_cast<const double2*>(hd) + 2), c3 = __ldg(reinterpret_cast<const double2*>(hd) + 3);
+  const double e = fma(c3.x, p.ud, c3.y * p.vd), zd = 1.0 + e;      // zd in (3/4, 5/4)
+  const double N0 = fma(-p.ud, e, fma(c0.x, p.ud, fma(c0.y, p.vd, c1.x)));
+  const double N1 = fma(-p.vd, e, fma(c1.y, p.ud, fma(c2.x, p.vd, c2.y)));
+  float zf;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(zf) : "f"((float)zd));
+  double zi = (double)zf;
+  zi = fma(zi, fma(-zd, zi, 1.0), zi);                              // relative error ~1e-14
+  const double txd = N0 * zi, tyd = N1 * zi;                        // x - u, y - v
+  const float tx = (float)txd, ty = (float)tyd;
+  FTap t;
+  if (FLAGS & RV_MINE_MASK) t.valid = (tx < (float)(a.W - p.u)) && (tx > (float)(-1 - p.u)) && (ty < (float)(a.H - p.v)) && (ty > (float)(-1 - p.v));
+  else t.valid = (tx > -p.uf) && (ty > -p.vf);    // x > 0 & y > 0
+  int x0, y0;
+  axis_cell((FLAGS & RV_MINE_GRID) ? txd : fma(txd, a.sx, p.bxf), p.bxi, a.W, x0, t.fx, t.q0);
+  axis_cell((FLAGS & RV_MINE_GRID) ? tyd : fma(tyd, a.sy, p.byf), p.byi, a.H, y0, t.fy, t.q1);
+  t.o = y0 * a.W + x0;
+  return t;
+}
+
+// double path: any homography (the pullback and mdb_sample use render_taps, the same arithmetic)
+template <int FLAGS>
+__device__ __noinline__ FTap ftap_precise(const double* __restrict__ Hm, const PixBase& p, int W, int H) {
+  const RTaps r = render_taps<FLAGS>(Hm, p.u, p.v, W, H);
+  FTap t;
+  t.valid = r.valid;
+  int x0 = r.x0, y0 = r.y0;
+  t.fx = r.fx; t.fy = r.fy;
+  if (x0 > W - 2) { x0 = W - 2; t.fx = 1.0f; }
+  if (y0 > H - 2) { y0 = H - 2; t.fy = 1.0f; }
+  t.q0 = r.q0; t.q1 = r.q1;
+  t.o = y0 * W + x0;
+  return t;
+}
+
+template <int FLAGS>
+MDB_DEV FTap ftap(const PlanePrep* __restrict__ pp, const PixBase& p, const RenderArgs& a) {
+  if (__ldg(&pp->fast)) return ftap_fast<FLAGS>(pp->hd, p, a);   // warp-uniform
+  return ftap_precise<FLAGS>(pp->Hst, p, a.W, a.H);
+}
+
+struct FW { float w00, w01, w10, w11; };
+MDB_DEV FW ftap_weights(const FTap& t) {
+  FW w;
+  w.w11 = t.fx * t.fy; w.w01 = t.fx - w.w11; w.w10 = t.fy - w.w11; w.w00 = (1.0f - t.fx) - w.w10;
+  return w;
+}
+
 // FUSED: xyz_tgt is affine in the source pixel, and the bilinear interpolant of an affine map at the
 // (border-clamped) sample point is the map itself there: no xyz loads (12 of the 28 per sample)
+// the arrays of the current plane: advanced by one plane per iteration instead of re-deriving 64-bit products
+struct PlanePtr { const float* rgb; const float* sig; const float* xyz; const PlanePrep* prep; };
+
 template <bool FUSED>
-MDB_DEV void render_sample_xyz(const RenderArgs& a, const RTaps& t, int kb, int WH, float* xyz) {
+MDB_DEV void render_sample_xyz(const PlanePtr& pl, const FTap& t, const FW& w, int W, float* xyz) {
   if (FUSED) {
-    const PlanePrep& pp = a.prep[kb];
-#pragma unroll
-    for (int c = 0; c < 3; ++c)
-      xyz[c] = fmaf(ldg(pp.Ax + 3 * c), t.q0, fmaf(ldg(pp.Ax + 3 * c + 1), t.q1, ldg(pp.Ax + 3 * c + 2) + ldg(pp.tx + c)));
+    const float4* ax4 = reinterpret_cast<const float4*>(pl.prep->Ax);   // Ax[9], tx[3]: 48 bytes at offset 112
+    const float4 c0 = __ldg(ax4), c1 = __ldg(ax4 + 1), c2 = __ldg(ax4 + 2);
+    xyz[0] = fmaf(c0.x, t.q0, fmaf(c0.y, t.q1, c0.z + c2.y));
+    xyz[1] = fmaf(c0.w, t.q0, fmaf(c1.x, t.q1, c1.y + c2.z));
+    xyz[2] = fmaf(c1.z, t.q0, fmaf(c1.w, t.q1, c2.x + c2.w));
     return;
   }
-  const float* px = a.xyz + (size_t)kb * WH * 3;
+  const float* p0 = pl.xyz + 3 * t.o;
+  const float* p1 = p0 + 3 * W;
 #pragma unroll
   for (int c = 0; c < 3; ++c)
-    xyz[c] = bil(t, ldg(px + 3 * t.o00 + c), ldg(px + 3 * t.o01 + c), ldg(px + 3 * t.o10 + c), ldg(px + 3 * t.o11 + c));
+    xyz[c] = fmaf(w.w11, ldg(p1 + 3 + c), fmaf(w.w10, ldg(p1 + c), fmaf(w.w01, ldg(p0 + 3 + c), w.w00 * ldg(p0 + c))));
 }
 
 template <bool FUSED>
-MDB_DEV void render_sample7(const RenderArgs& a, const RTaps& t, int kb, int WH, RSample& s) {
-  const float* pr = a.rgb + (size_t)kb * 3 * WH;
+MDB_DEV void render_sample7(const PlanePtr& pl, const FTap& t, int W, int WH, RSample& s) {
+  const FW w = ftap_weights(t);
+  const float* p0 = pl.rgb + t.o;
 #pragma unroll
-  for (int c = 0; c < 3; ++c)
-    s.rgb[c] = bil(t, ldg(pr + c * WH + t.o00), ldg(pr + c * WH + t.o01), ldg(pr + c * WH + t.o10), ldg(pr + c * WH + t.o11));
-  const float* ps = a.sigma + (size_t)kb * WH;
-  const float sg = bil(t, ldg(ps + t.o00), ldg(ps + t.o01), ldg(ps + t.o10), ldg(ps + t.o11));
+  for (int c = 0; c < 3; ++c) {
+    const float* q0 = p0 + c * WH;
+    const float* q1 = q0 + W;
+    s.rgb[c] = fmaf(w.w11, ldg(q1 + 1), fmaf(w.w10, ldg(q1), fmaf(w.w01, ldg(q0 + 1), w.w00 * ldg(q0))));
+  }
+  const float* q0 = pl.sig + t.o;
+  const float* q1 = q0 + W;
+  const float sg = fmaf(w.w11, ldg(q1 + 1), fmaf(w.w10, ldg(q1), fmaf(w.w01, ldg(q0 + 1), w.w00 * ldg(q0))));
   s.sig = sg >= 0.0f ? sg : 0.0f;                                  // sigma .* (sigma .>= 0)
-  render_sample_xyz<FUSED>(a, t, kb, WH, s.xyz);
+  render_sample_xyz<FUSED>(pl, t, w, W, s.xyz);
 }
 
+// MUFU-based square root and exponential: ~2 ulp each.  The transmittance exp(-dist sigma) is in (0, 1], so its ABSOLUTE
+// error stays below 2e-7 whatever the argument (the relative error of ex2 grows with |argument|, the value shrinks faster).
+MDB_DEV float sqrt_approx(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+MDB_DEV float exp_neg_approx(float x) { float r; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x * -1.4426950408889634f)); return r; }
+
 template <int FLAGS, bool FUSED>
-__global__ void __launch_bounds__(RF_THREADS) render_fwd_kernel(const __grid_constant__ RenderArgs a) {
+__global__ void __launch_bounds__(RF_THREADS, RF_MINB) render_fwd_kernel(const __grid_constant__ RenderArgs a) {
   __shared__ float s_T[RF_G][RF_PIX];            // product of (T + 1e-6) over the group's planes
   __shared__ float s_out[RF_G][5][RF_PIX];       // rgb, sum w, sum w z of the group
   __shared__ int s_nv[RF_G][RF_PIX];
   __shared__ float s_tl[RF_MAXKPG][RF_THREADS];  // local transparency_acc of the group's planes
-  const int lp = threadIdx.x, g = threadIdx.y, tid = g * RF_PIX + lp;   // a warp = 32 consecutive pixels, one group
-  const int pix = blockIdx.x * RF_PIX + lp, b = blockIdx.y;
-  const int WH = a.W * a.H;
-  const bool live = pix < WH;
+  const int lp = threadIdx.x, g = threadIdx.y, tid = g * RF_PIX + lp;   // a warp = 32 consecutive pixels of a row, one group
+  const int u = blockIdx.x * RF_PIX + lp, v = blockIdx.y, b = blockIdx.z;
+  const int WH = a.W * a.H, pix = v * a.W + u;
+  const bool live = u < a.W;
   const int kpg = (a.Np + RF_G - 1) / RF_G, k0 = min(g * kpg, a.Np), k1 = min(k0 + kpg, a.Np);
   float out[5] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f}, tacc = 1.0f;
   int nvalid = 0;
   if (live && k0 < k1) {
-    const int u = pix % a.W, v = pix / a.W;
+    const PixBase pb = pix_base<FLAGS>(u, v, a.sx, a.sy, a.cx0, a.cy0);
+    const size_t kb0 = (size_t)b * a.Np + k0;
+    PlanePtr pl{a.rgb + kb0 * 3 * WH, a.sigma + kb0 * WH, FUSED ? nullptr : a.xyz + kb0 * WH * 3, a.prep + kb0};
     RSample p;
     {
-      const RTaps t = render_taps<FLAGS>(a.prep[b * a.Np + k0].Hst, u, v, a.W, a.H);
+      const FTap t = ftap<FLAGS>(pl.prep, pb, a);
       nvalid += t.valid ? 1 : 0;
-      render_sample7<FUSED>(a, t, b * a.Np + k0, WH, p);
+      render_sample7<FUSED>(pl, t, a.W, WH, p);
     }
     for (int k = k0 + 1; k <= k1; ++k) {
       RSample c;
       float dist = 1e3f;                                             // last plane (src/render.jl:36)
       if (k < a.Np) {
-        const RTaps t = render_taps<FLAGS>(a.prep[b * a.Np + k].Hst, u, v, a.W, a.H);
-        if (k < k1) { nvalid += t.valid ? 1 : 0; render_sample7<FUSED>(a, t, b * a.Np + k, WH, c); }
-        else render_sample_xyz<FUSED>(a, t, b * a.Np + k, WH, c.xyz);  // first plane of the next group
+        pl.rgb += 3 * WH; pl.sig += WH; pl.prep += 1;
+        if (!FUSED) pl.xyz += 3 * WH;
+        const FTap t = ftap<FLAGS>(pl.prep, pb, a);
+        if (k < k1) { nvalid += t.valid ? 1 : 0; render_sample7<FUSED>(pl, t, a.W, WH, c); }
+        else render_sample_xyz<FUSED>(pl, t, ftap_weights(t), a.W, c.xyz);  // first plane of the next group
         const float dx = c.xyz[0] - p.xyz[0], dy = c.xyz[1] - p.xyz[1], dz = c.xyz[2] - p.xyz[2];
-        dist = sqrtf(dx * dx + dy * dy + dz * dz);
+        dist = sqrt_approx(fmaf(dx, dx, fmaf(dy, dy, dz * dz)));
       }
-      const float T = expf(-dist * p.sig);
+      const float T = exp_neg_approx(dist * p.sig);
       s_tl[k - 1 - k0][tid] = tacc;
       const float w = tacc * (1.0f - T);
 #pragma unroll

@@ -378,8 +378,9 @@ __global__ void pvr_fwd_kernel(const float* __restrict__ rgb, const float* __res
   for (int c = 0; c < 3; ++c) rgb_out[((size_t)b * 3 + c) * WH + pix] = out[c];
 }
 
-RenderConst make_rc(const float* K, const float* Kinv) {
+RenderConst make_rc(const float* K, const float* Kinv, int W = 0, int H = 0) {
   RenderConst rc;
+  rc.W = W; rc.H = H;
   for (int i = 0; i < 3; ++i)
     for (int j = 0; j < 3; ++j) {
       rc.K[3 * i + j] = K ? K[3 * j + i] : (i == j);
@@ -514,11 +515,14 @@ int32_t mdb_render_tgt_rgb_depth_fwd_ex(mdb_handle* h, const float* rgb, const f
               "render workspace must be >= %zu bytes, 256-byte aligned", L.total);
   cudaStream_t st = (cudaStream_t)stream;
   PlanePrep* prep = (PlanePrep*)((char*)workspace + L.o_prep);
-  render_prep_kernel<<<(Np * B + 63) / 64, 64, 0, st>>>(disparity_src, 0, rvec, tvec, make_rc(K, K_inv), Np, B, prep);
+  render_prep_kernel<<<(Np * B + 63) / 64, 64, 0, st>>>(disparity_src, 0, rvec, tvec, make_rc(K, K_inv, mdb_dbg_render_precise ? 0 : W, H), Np, B, prep);
   MDB_LAUNCHED(h);
   RenderArgs a{rgb, sigma, xyz_tgt, prep, W, H, Np, B, rgb_out, depth_out, mask_out, expected_depth, weights_sum,
-               opts ? opts->depth_eps : 1e-5f};
-  dim3 grid((W * H + RF_PIX - 1) / RF_PIX, B), block(RF_PIX, RF_G);
+               opts ? opts->depth_eps : 1e-5f, 0.0, 0.0, 0.0, 0.0};
+  a.sx = (double)(W - 1) / W; a.sy = (double)(H - 1) / H;
+  a.cx0 = 0.5 * a.sx + 0.5 * (W - 1); a.cy0 = 0.5 * a.sy + 0.5 * (H - 1);
+  MDB_REQUIRE(h, H <= 65535 && B <= 65535, MDB_E_SHAPE, "mdb_render_tgt_rgb_depth_fwd: H and B must be <= 65535");
+  dim3 grid((W + RF_PIX - 1) / RF_PIX, H, B), block(RF_PIX, RF_G);
   if (xyz_tgt) launch_render_fwd<false>(opts_flags(opts), grid, block, st, a);
   else launch_render_fwd<true>(opts_flags(opts), grid, block, st, a);
   MDB_LAUNCHED(h);
@@ -558,7 +562,7 @@ int32_t mdb_render_tgt_rgb_depth_bwd_ex(mdb_handle* h, const float* rgb, const f
   cudaStream_t st = (cudaStream_t)stream;
   char* ws = (char*)workspace;
   PlanePrep* prep = (PlanePrep*)(ws + L.o_prep);
-  const RenderConst rc = make_rc(K, K_inv);
+  const RenderConst rc = make_rc(K, K_inv, W, H);
   render_prep_kernel<<<(Np * B + 63) / 64, 64, 0, st>>>(disparity_src, 0, rvec, tvec, rc, Np, B, prep);
   MDB_LAUNCHED(h);
   const size_t planes = (size_t)W * H * Np * B;

@@ -223,3 +223,31 @@ def test_render_fused_xyz_equals_materialised_producers():
     # d tvec: the fused path adds sum(d_xyz_tgt) to what the homography path gives
     gt = b[4].grad + xyz_tgt.grad.sum(dim=(1, 2, 3))
     assert (a[4].grad - gt).abs().max() <= 1e-4 * gt.abs().max()
+
+
+@pytest.mark.parametrize("mine_grid", [False, True])
+@pytest.mark.parametrize("pose_scale,expect_fast", [(1.0, True), (3.0, None), (20.0, False)])
+def test_render_forward_float_path_vs_double_path(mine_grid, pose_scale, expect_fast):
+    """The forward samples a plane through the float displacement form when render_prep_kernel bounds every term of the
+    displacement below 48 px (the near-identity homographies of config 4), else through the double-precision homography.
+    Same inputs through both (test hook "render_precise"): the outputs agree far inside the 1e-5 parity gate, masks are
+    equal, and with strongly non-identity poses the two runs are bit-identical (the float form was never taken)."""
+    import mdb200
+    ri = _rand_inputs(416, 128, 16, 2, 31, pose_scale)
+    plan = mdb200.RenderPlan(416, 128, 16, 2, ri.K_inv, ri.K, mine_grid=mine_grid, mine_mask=mine_grid)
+    args = (_dev(ri.rgb), _dev(ri.sigma), _dev(ri.disparity_src), _dev(ri.xyz_tgt), mdb200.Pose(_dev(ri.rvec), _dev(ri.tvec)))
+    a = [t.clone() for t in plan.forward(*args)[:3]]
+    mdb200.debug_option("render_precise", 1)
+    try:
+        b = [t.clone() for t in plan.forward(*args)[:3]]
+    finally:
+        mdb200.debug_option("render_precise", 0)
+    torch.cuda.synchronize()
+    d_rgb, d_t = float((a[0] - b[0]).abs().max()), float((a[1] - b[1]).abs().max())
+    assert d_rgb < 6e-6 and d_t < 6e-6, (d_rgb, d_t)
+    assert torch.equal(a[2], b[2])
+    same = torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
+    if expect_fast is True:
+        assert not same          # the float path ran (and differs in the last bits)
+    elif expect_fast is False:
+        assert same
