@@ -460,7 +460,27 @@ def run_ours(args):
                                      "h2d_bytes_per_step": int(hu[0]), "d2h_bytes_per_step": int(hu[1]),
                                      "ms_per_step": float(dtu) / e_steps * 1e3,
                                      "note": "images as uint8 triplet strips (8-bit quantised copies of the same synthetic frames), "
-                                             "disparities / poses / gradients Float32 as above"}
+                                             "disparities / poses / gradients Float32 as above; on the device the strips are "
+                                             "transposed to a planar uint8 stack that the fused kernel reads directly "
+                                             "(mdb_loss_io.x_format = 1: no Float32 stack is ever written)"}
+            # the same kernel with the uint8 stack resident on the device: what reading bytes costs / saves in the kernel itself
+            if world == 1:
+                del uplan
+                torch.cuda.empty_cache()
+                xu8 = mdb200.ingest_triplet_u8_planar(hu8.to(dev), W)
+                for _ in range(3):
+                    plan(xu8, disps, poses, None)
+                mdb200.profile_begin(e_steps)
+                evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(e_steps)]
+                for a_, b_ in evs:
+                    a_.record(); plan(xu8, disps, poses, None); b_.record()
+                torch.cuda.synchronize()
+                fused = sum(mdb200.profile_read(i)[1] for i in range(e_steps)) / e_steps
+                mdb200.profile_begin(0)
+                e2e["u8_strip_input"]["device_resident"] = {
+                    "ms_per_step": sum(a_.elapsed_time(b_) for a_, b_ in evs) / e_steps, "fused_kernel_ms": fused,
+                    "image_bytes": int(xu8.numel()), "image_bytes_float32": int(x.numel() * 4)}
+                del xu8
 
     if rank == 0:
         line = {

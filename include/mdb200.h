@@ -237,6 +237,11 @@ typedef struct mdb_loss_io {
   float* d_rvec[MDB_MAX_SOURCES]; /* (3,N)                                               */
   float* d_tvec[MDB_MAX_SOURCES]; /* (3,1,N)                                             */
   float* vis_warp_loss;           /* optional (W,H,1,N): warp_loss of the last scale     */
+  int32_t x_format;               /* 0: x is Float32; 1: x points to uint8 (N0f8) samples in the same (W,H,C,L,N) layout,
+                                   * read in the kernel as Float32(::N0f8) = u / 255 correctly rounded (src/dtk.jl:45) --
+                                   * bit-identical results, a quarter of the image bytes.  Not under stream capture, not
+                                   * with upsample_align_corners = 0 (MDB_E_INVALID_ARG).  mdb_ingest_triplet_u8_planar
+                                   * produces this layout from the dataset's strips.                                  */
 } mdb_loss_io;
 
 size_t mdb_train_loss_workspace_bytes(const mdb_loss_io* io);
@@ -466,6 +471,12 @@ int32_t mdb_ingest_triplet_u8(mdb_handle* h, const uint8_t* strips, const uint8_
  * restatement.                                                                                                     */
 int32_t mdb_ingest_kitti_u8(mdb_handle* h, const uint8_t* frames, const uint8_t* flip, int32_t W_orig, int32_t H_orig,
                             int32_t W, int32_t H, int32_t N, float* x, void* stream);
+
+/* The same split / FlipX / channel-planar transpose as mdb_ingest_triplet_u8 but WITHOUT the conversion: x_u8 is the uint8
+ * (W,H,3,3,N) stack that mdb_loss_io.x_format = 1 reads (C = 3 only: Gray luma is not an 8-bit value).  9 W H N bytes read
+ * and written instead of 9 read + 36 written.                                                                        */
+int32_t mdb_ingest_triplet_u8_planar(mdb_handle* h, const uint8_t* strips, const uint8_t* flip, int32_t W, int32_t H,
+                                     int32_t N, uint8_t* x_u8, void* stream);
 
 /* ---- the operators on the network side of the path ---------------------------
  * PoseDecoder tail (src/pose_decoder.jl:27-32): pose = scale * mean(conv_out (w,h,6,N); dims=(1,2)),

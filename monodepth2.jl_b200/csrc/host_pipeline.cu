@@ -39,6 +39,7 @@ struct mdb_host_plan {
   cudaEvent_t ev_start = nullptr, ev_small = nullptr;
   // device buffers, whole local batch
   float* d_x = nullptr; unsigned char* d_u8 = nullptr; unsigned char* d_flip = nullptr;
+  unsigned char* d_xu8 = nullptr;   // x_format 1 with C = 3: the planar uint8 stack the fused kernel reads directly (no Float32 stack)
   float* d_disp[MDB_MAX_SCALES] = {nullptr}; float* g_disp[MDB_MAX_SCALES] = {nullptr};
   float* d_rv[MDB_MAX_SOURCES] = {nullptr}; float* d_tv[MDB_MAX_SOURCES] = {nullptr};
   float* g_rv[MDB_MAX_SOURCES] = {nullptr}; float* g_tv[MDB_MAX_SOURCES] = {nullptr};
@@ -118,7 +119,9 @@ int32_t mdb_host_plan_create(mdb_handle* h, const mdb_loss_io* shape, const mdb_
   ok(cudaEventCreateWithFlags(&p->ev_small, cudaEventDisableTiming));
   for (Chunk& c : p->chunks) { ok(cudaEventCreateWithFlags(&c.ready, cudaEventDisableTiming)); ok(cudaEventCreateWithFlags(&c.done, cudaEventDisableTiming)); }
   const size_t frame = (size_t)W * H * C * L;
-  ok(plan_alloc(p, &p->d_x, frame * N));
+  const bool u8_direct = x_format == 1 && C == 3;   // Gray luma (C = 1) is not an 8-bit value: that case keeps the Float32 stack
+  if (u8_direct) ok(plan_alloc(p, &p->d_xu8, frame * N));
+  else ok(plan_alloc(p, &p->d_x, frame * N));
   if (x_format == 1) { ok(plan_alloc(p, &p->d_u8, (size_t)9 * W * H * N)); ok(plan_alloc(p, &p->d_flip, (size_t)N)); }
   for (int k = 0; k < Ls; ++k) {
     ok(plan_alloc(p, &p->d_disp[k], (size_t)shape->dw[k] * shape->dh[k] * N));
@@ -200,12 +203,15 @@ int32_t mdb_train_loss_host(mdb_host_plan* p, const mdb_host_io* io, void* strea
     MDB_CUDA(h, cudaEventRecord(c.ready, p->copy_in));
     MDB_CUDA(h, cudaStreamWaitEvent(st, c.ready, 0));
     if (p->x_format == 1) {
-      const int32_t rc = mdb_ingest_triplet_u8(h, p->d_u8 + strip * a, io->flip ? p->d_flip + a : nullptr, W, H, n, C == 1, p->d_x + frame * a, st);
+      const int32_t rc = p->d_xu8
+          ? mdb_ingest_triplet_u8_planar(h, p->d_u8 + strip * a, io->flip ? p->d_flip + a : nullptr, W, H, n, p->d_xu8 + frame * a, st)
+          : mdb_ingest_triplet_u8(h, p->d_u8 + strip * a, io->flip ? p->d_flip + a : nullptr, W, H, n, C == 1, p->d_x + frame * a, st);
       if (rc != MDB_OK) return rc;
     }
     mdb_loss_io ci = sh;
     ci.N = n;
-    ci.x = p->d_x + frame * a;
+    ci.x = p->d_xu8 ? reinterpret_cast<const float*>(p->d_xu8 + frame * a) : p->d_x + frame * a;
+    ci.x_format = p->d_xu8 ? 1 : 0;
     for (int j = 0; j < Ls; ++j) {
       const size_t per = (size_t)sh.dw[j] * sh.dh[j];
       ci.disparity[j] = p->d_disp[j] + per * a;

@@ -115,6 +115,48 @@ ingest_kitti_u8_kernel(const unsigned char* __restrict__ frames, const unsigned 
   __stcs(x + ((size_t)fn * H + h) * W + (f ? W - 1 - w : w), lut32[q]);
 }
 
+
+// The transpose alone (mdb_loss_io.x_format = 1: the fused kernel converts on the fly): same staging of the strip row,
+// bytes out.  One block per (strip row, item); 4 output bytes per thread and store where W % 4 == 0.
+__global__ void __launch_bounds__(ING_THREADS)
+ingest_triplet_u8_planar_kernel(const unsigned char* __restrict__ strips, const unsigned char* __restrict__ flip, int W, int H,
+                                unsigned char* __restrict__ x) {
+  extern __shared__ __align__(16) unsigned char row[];
+  const int h = blockIdx.x, n = blockIdx.y;
+  const int nbytes = 9 * W;
+  const unsigned char* src = strips + ((size_t)n * H + h) * nbytes;
+  if ((((uintptr_t)src) & 15) == 0 && (nbytes & 15) == 0) {
+    const uint4* s4 = reinterpret_cast<const uint4*>(src);
+    uint4* r4 = reinterpret_cast<uint4*>(row);
+    for (int i = threadIdx.x; i < nbytes / 16; i += ING_THREADS) r4[i] = __ldcs(s4 + i);
+  } else {
+    for (int i = threadIdx.x; i < nbytes; i += ING_THREADS) row[i] = src[i];
+  }
+  __syncthreads();
+  const bool f = flip && flip[n];
+  const size_t plane = (size_t)H * W;
+  unsigned char* out = x + (size_t)n * 9 * plane + (size_t)h * W;
+  const bool vec = (W & 3) == 0 && (((uintptr_t)x) & 3) == 0;
+  for (int lc = 0; lc < 9; ++lc) {
+    const int l = lc / 3, c = lc % 3;
+    const unsigned char* fr = row + (size_t)l * W * 3 + c;
+    unsigned char* o = out + (size_t)lc * plane;
+    if (vec) {
+      for (int w4 = threadIdx.x; w4 < W / 4; w4 += ING_THREADS) {
+        unsigned v = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int w = 4 * w4 + k;
+          v |= (unsigned)fr[(f ? W - 1 - w : w) * 3] << (8 * k);
+        }
+        reinterpret_cast<unsigned*>(o)[w4] = v;
+      }
+    } else {
+      for (int w = threadIdx.x; w < W; w += ING_THREADS) o[w] = fr[(f ? W - 1 - w : w) * 3];
+    }
+  }
+}
+
 }  // namespace
 
 extern "C" int32_t mdb_ingest_triplet_u8(mdb_handle* h, const uint8_t* strips, const uint8_t* flip, int32_t W,
@@ -141,6 +183,21 @@ extern "C" int32_t mdb_ingest_kitti_u8(mdb_handle* h, const uint8_t* frames, con
               "mdb_ingest_kitti_u8: need W,H,N,W_orig,H_orig >= 1, H <= 65535 and N <= 21845");
   dim3 grid((W + ING_THREADS - 1) / ING_THREADS, H, 3 * N);
   ingest_kitti_u8_kernel<<<grid, ING_THREADS, 0, (cudaStream_t)stream>>>(frames, flip, W_orig, H_orig, W, H, x);
+  MDB_LAUNCHED(h);
+  return MDB_OK;
+}
+
+extern "C" int32_t mdb_ingest_triplet_u8_planar(mdb_handle* h, const uint8_t* strips, const uint8_t* flip, int32_t W,
+                                                int32_t H, int32_t N, uint8_t* x_u8, void* stream) {
+  MDB_REQUIRE(h, h != nullptr, MDB_E_INVALID_ARG, "null handle");
+  MDB_REQUIRE(h, strips && x_u8, MDB_E_INVALID_ARG, "mdb_ingest_triplet_u8_planar: null pointer");
+  MDB_REQUIRE(h, W >= 1 && H >= 1 && N >= 1 && N <= 65535, MDB_E_SHAPE, "mdb_ingest_triplet_u8_planar: need W,H,N >= 1 and N <= 65535");
+  const size_t smem = mdb_align_up((size_t)9 * W, 16);
+  MDB_REQUIRE(h, smem <= 200 * 1024, MDB_E_SHAPE, "mdb_ingest_triplet_u8_planar: strip row of %d px does not fit shared memory", 3 * W);
+  if (smem > 48 * 1024)
+    MDB_CUDA(h, cudaFuncSetAttribute(ingest_triplet_u8_planar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  dim3 grid(H, N);
+  ingest_triplet_u8_planar_kernel<<<grid, ING_THREADS, smem, (cudaStream_t)stream>>>(strips, flip, W, H, x_u8);
   MDB_LAUNCHED(h);
   return MDB_OK;
 }

@@ -62,6 +62,7 @@ struct FusedArgs {
   double rxd[MDB_MAX_SCALES], ryd[MDB_MAX_SCALES];
   double oxd[MDB_MAX_SCALES], oyd[MDB_MAX_SCALES];   // half-pixel up-sampling (hp): source coordinate = max(0, p r + o)
   int hp;                       // upsample_align_corners == 0; served by the CP = false instantiations only
+  int x_u8;                     // x holds N0f8 bytes instead of Float32 (mdb_loss_io.x_format == 1); constant-bank instantiation only
   const PoseStrip* ppd;         // [N][S]
   float alpha, c1, c2;
   float ksu, klu, kl, ka;       // loss / pullback factors (photo_strip.inl)

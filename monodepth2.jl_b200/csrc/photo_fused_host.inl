@@ -538,6 +538,9 @@ int32_t launch_fused(mdb_handle* h, const FusedArgs& fa, const FusedLayout& L, c
   const bool use_bank = false;
   const int chunk = fa.N;
 #endif
+  MDB_REQUIRE(h, !fa.x_u8 || use_bank, MDB_E_INVALID_ARG,
+              "x_format = 1 (uint8 frames) is served by the throughput instantiation only: not under stream capture, not with "
+              "upsample_align_corners = 0, not with the decision dump");
   for (int n0 = 0; n0 < fa.N; n0 += chunk) {
     const int items = std::min(chunk, fa.N - n0);
     g.n0 = n0;
@@ -560,7 +563,8 @@ int32_t launch_fused(mdb_handle* h, const FusedArgs& fa, const FusedLayout& L, c
       g.cbase = region * STRIP_CONST_CHUNK;
       MDB_CUDA(h, cudaMemcpyToSymbolAsync(c_pose, fa.ppd + (size_t)n0 * S, sizeof(PoseStrip) * items * S,
                                           sizeof(PoseStrip) * g.cbase, cudaMemcpyDeviceToDevice, st));
-      photo_strip_kernel<C, S, false, true><<<blocks, STRIP_THREADS, smem, st>>>(fa, g);
+      if (fa.x_u8) photo_strip_kernel<C, S, false, true, true><<<blocks, STRIP_THREADS, smem, st>>>(fa, g);
+      else photo_strip_kernel<C, S, false, true><<<blocks, STRIP_THREADS, smem, st>>>(fa, g);
       MDB_LAUNCHED(h);
       MDB_CUDA(h, cudaEventRecord(ev, st));
       continue;
@@ -641,6 +645,7 @@ int32_t mdb_train_loss_fwdbwd(mdb_handle* h, const mdb_loss_io* io, const mdb_lo
   fa.x = io->x; fa.W = W; fa.H = H; fa.L = io->L; fa.N = N;
   fa.tgt = io->target_id - 1;
   fa.hp = p->upsample_align_corners == 0 ? 1 : 0;
+  fa.x_u8 = io->x_format == 1 ? 1 : 0;
   ua.hp = fa.hp;
   for (int s = 0; s < S; ++s) fa.src[s] = io->source_ids[s] - 1;
   fa.Ls = Ls;

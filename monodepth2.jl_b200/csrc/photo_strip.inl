@@ -116,6 +116,22 @@ template <> struct Pk<2> {
 // sign(v) with sign(0) = 0, without an int->float conversion
 MDB_DEV float sgn1(float v) { return v == 0.0f ? 0.0f : copysignf(1.0f, v); }
 
+// frame samples: Float32 as stored, or N0f8 bytes carried as 2^23 + u until first use (see the kernel's U8 parameter)
+MDB_DEV float ldx(const float* p) { return ldg(p); }
+MDB_DEV float ldx(const unsigned char* p) { return __uint_as_float(0x4B000000u | (unsigned)__ldg(p)); }
+constexpr float N0F8_R1 = 0.003921568859368562698f;      // fl(1 / 255)
+constexpr float N0F8_R2 = -2.3191758e-10f;               // fl(1 / 255 - r1)
+template <bool U8> MDB_DEV float cvx(float g) {
+  if (!U8) return g;
+  const float f = g - 8388608.0f;
+  return fmaf(f, N0F8_R1, f * N0F8_R2);
+}
+template <bool U8, int S> MDB_DEV Pk<S> cvx(Pk<S> g) {
+  if (!U8) return g;
+  const Pk<S> f = g + Pk<S>(-8388608.0f);
+  return pfma(f, Pk<S>(N0F8_R1), f * Pk<S>(N0F8_R2));
+}
+
 template <int S> MDB_DEV Pk<S> pfma(Pk<S> a, float b, Pk<S> c) { return pfma(a, Pk<S>(b), c); }
 template <int S> MDB_DEV Pk<S> operator*(Pk<S> a, float b) { return a * Pk<S>(b); }
 template <int S> MDB_DEV Pk<S> operator+(Pk<S> a, float b) { return a + Pk<S>(b); }
@@ -147,7 +163,13 @@ MDB_DEV signed char sgn_code(float v) { return v == 0.0f ? 0 : (v > 0.0f ? 1 : -
 // The captured instantiation (CP = false, DBG = false) keeps round 1's loop (no steady-state copy), its per-row constants in
 // registers, and a register cap under which nothing spills (STRIP_MAXREG_CAPTURED): 22.6 us per iteration at config 1, where
 // the peeled loop with constants re-loaded through a.ppd took 24.2 - 26.0 us.  It also serves upsample_align_corners = 0.
-template <int C, int S, bool DBG = false, bool CP = (STRIP_CONSTPOSE != 0)>
+// U8: the frame stack x holds 8-bit samples (N0f8, same (W,H,C,L,N) layout, 1 byte each) instead of Float32: a quarter of the
+// image bytes in HBM and in the gathers.  A loaded byte u travels as the float 2^23 + u (one LOP3 on the load's result), and
+// where the value is first used it becomes Float32(::N0f8) = u / 255 correctly rounded: f = (2^23 + u) - 2^23 (exact),
+// then fma(f, r1, f r2) with r1 = fl(1/255), r2 = fl(1/255 - r1) -- equal to the IEEE quotient for all 256 values (checked
+// exhaustively in tests/test_ingest.py), so the u8 path is bit-identical to the float path fed the converted stack.
+// (u * (1/255f) alone is NOT: it differs from u / 255f for 126 of the 256 values.)  Throughput instantiation only.
+template <int C, int S, bool DBG = false, bool CP = (STRIP_CONSTPOSE != 0), bool U8 = false>
 #ifdef STRIP_MAXREG
 __global__ void __maxnreg__((CP || DBG) ? STRIP_MAXREG : STRIP_MAXREG_CAPTURED)
 #else
@@ -189,20 +211,21 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
 
   // one 64-bit base per item; everything inside the item is addressed with 32-bit element offsets
   // (io_shape_ok guarantees L * C * W * H < 2^31)
-  const float* xb;
+  using XT = typename std::conditional<U8, unsigned char, float>::type;
+  const XT* xb;
   {
     // opaque to the optimiser: otherwise it re-derives this base from n in 64-bit arithmetic at every load
-    unsigned long long xbi = (unsigned long long)(a.x + (size_t)n * a.L * C * plane);
+    unsigned long long xbi = (unsigned long long)(reinterpret_cast<const XT*>(a.x) + (size_t)n * a.L * C * plane);
     asm volatile("" : "+l"(xbi));
-    xb = reinterpret_cast<const float*>(xbi);
+    xb = reinterpret_cast<const XT*>(xbi);
   }
 #if STRIP_CBASE
-  const float* xbc[C];   // per-channel bases (opaque, like xb)
+  const XT* xbc[C];   // per-channel bases (opaque, like xb)
 #pragma unroll
   for (int c = 0; c < C; ++c) {
     unsigned long long t = (unsigned long long)(xb + (size_t)c * plane);
     asm volatile("" : "+l"(t));
-    xbc[c] = reinterpret_cast<const float*>(t);
+    xbc[c] = reinterpret_cast<const XT*>(t);
   }
 #endif
   const unsigned tgt_off = a.tgt * C * planei;
@@ -357,7 +380,7 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
       td_ = (float)dd_;
       const double invd = fma(dd_, a.dd_d, a.mind_d);   // 1 / depth (src/utils.jl:179-183)
 #pragma unroll
-      for (int c = 0; c < C; ++c) ty_[c] = ldg(xb + (unsigned)(tgt_off + c * planei + rc * W + gxc));
+      for (int c = 0; c < C; ++c) ty_[c] = ldx(xb + (unsigned)(tgt_off + c * planei + rc * W + gxc));
 #if STRIP_AM_EARLY
       if (a.automask) tam = ldg(amb + (unsigned)((ST ? r - 1 : min(max(r - 1, 0), H - 1)) * W + gxc));   // window row r-1, used in stage C
 #endif
@@ -398,10 +421,10 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
       for (int c = 0; c < C; ++c) {
 #pragma unroll
         for (int s = 0; s < S; ++s) {
-          const float* p = xbc[c] + ot[s];    // one IMAD.WIDE per address: the channel plane is in the base
-          const float* pb = xbc[c] + ob[s];
-          tv00[c].set(s, ldg(p)); tv01[c].set(s, ldg(p + 1));
-          tv10[c].set(s, ldg(pb)); tv11[c].set(s, ldg(pb + 1));
+          const XT* p = xbc[c] + ot[s];    // one IMAD.WIDE per address: the channel plane is in the base
+          const XT* pb = xbc[c] + ob[s];
+          tv00[c].set(s, ldx(p)); tv01[c].set(s, ldx(p + 1));
+          tv10[c].set(s, ldx(pb)); tv11[c].set(s, ldx(pb + 1));
         }
       }
 #else
@@ -409,10 +432,10 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
       for (int c = 0; c < C; ++c) {
 #pragma unroll
         for (int s = 0; s < S; ++s) {
-          const float* p = xb + (ot[s] + (unsigned)(c * planei));
-          const float* pb = xb + (ot[s] + (unsigned)(c * planei + W));
-          tv00[c].set(s, ldg(p)); tv01[c].set(s, ldg(p + 1));
-          tv10[c].set(s, ldg(pb)); tv11[c].set(s, ldg(pb + 1));
+          const XT* p = xb + (ot[s] + (unsigned)(c * planei));
+          const XT* pb = xb + (ot[s] + (unsigned)(c * planei + W));
+          tv00[c].set(s, ldx(p)); tv01[c].set(s, ldx(p + 1));
+          tv10[c].set(s, ldx(pb)); tv11[c].set(s, ldx(pb + 1));
         }
       }
 #endif
@@ -438,9 +461,10 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
       float park[DRV];
 #pragma unroll
       for (int c = 0; c < C; ++c) {
-        yn[c] = ty_[c];
-        const P h0 = tv01[c] - tv00[c], h1 = tv11[c] - tv10[c];
-        const P top = pfma(tfx, h0, tv00[c]), bot = pfma(tfx, h1, tv10[c]);
+        yn[c] = cvx<U8>(ty_[c]);
+        const P v00 = cvx<U8, S>(tv00[c]), v01 = cvx<U8, S>(tv01[c]), v10 = cvx<U8, S>(tv10[c]), v11 = cvx<U8, S>(tv11[c]);
+        const P h0 = v01 - v00, h1 = v11 - v10;
+        const P top = pfma(tfx, h0, v00), bot = pfma(tfx, h1, v10);
         const P dyv = bot - top;
         xn[c] = pfma(tfy, dyv, top);
         const P dxv = pfma(tfy, h1 - h0, h0);

@@ -70,6 +70,7 @@ struct LossIO
     d_rvec::NTuple{MAX_SOURCES,CuPtr{Cfloat}}
     d_tvec::NTuple{MAX_SOURCES,CuPtr{Cfloat}}
     vis_warp_loss::CuPtr{Cfloat}
+    x_format::Int32          # 0: Float32 frames; 1: UInt8 (N0f8) frames, same layout
 end
 
 # ---- handle + error convention (status codes -> Julia errors) ------------------------------------
@@ -159,7 +160,8 @@ include("MDB200_ops.jl")      # the other fine-grained operators and their rrule
 Value and gradient of `train_loss`'s arithmetic (src/training.jl:27-77) in one pass of the fused
 kernels.  `n_global` is the batch size the means divide by (multi-GPU shards pass the global N).
 """
-function fused_loss(x::CuArray{Float32,5}, disparities::Vector{<:CuArray{Float32,4}}, poses::Vector{<:Pose},
+# `x` may also be the UInt8 (N0f8) stack of the same shape (`depth10k_batch_u8`): the kernel converts on the fly, bit-identically
+function fused_loss(x::Union{CuArray{Float32,5},CuArray{UInt8,5}}, disparities::Vector{<:CuArray{Float32,4}}, poses::Vector{<:Pose},
                     auto_loss, cache::TrainCache, parameters::Params;
                     normalize_disparity::Bool=true, smooth_weight_mode::Integer=0, n_global::Integer=0,
                     abs_subgradient::Integer=0)
@@ -169,7 +171,7 @@ function fused_loss(x::CuArray{Float32,5}, disparities::Vector{<:CuArray{Float32
     dd = [similar(d) for d in disparities]
     dr = [similar(p.rvec) for p in poses]
     dt = [similar(p.tvec) for p in poses]
-    io = LossIO(pointer(x), W, H, C, L, N, cache.target_id, S,
+    io = LossIO(reinterpret(CuPtr{Cfloat}, pointer(x)), W, H, C, L, N, cache.target_id, S,
         pad(Int32.(cache.source_ids), MAX_SOURCES, Int32(0)),
         pad(Int32.(cache.source_ids .< cache.target_id), MAX_SOURCES, Int32(0)),   # src/training.jl:28
         pad(map(p -> pointer(p.rvec), poses), MAX_SOURCES, nullp()),
@@ -181,7 +183,7 @@ function fused_loss(x::CuArray{Float32,5}, disparities::Vector{<:CuArray{Float32
         parameters.automasking ? pointer(auto_loss) : nullp(),
         k9(cache.K), k9(cache.invK), pointer(loss),
         pad(map(pointer, dd), MAX_SCALES, nullp()), pad(map(pointer, dr), MAX_SOURCES, nullp()),
-        pad(map(pointer, dt), MAX_SOURCES, nullp()), nullp())
+        pad(map(pointer, dt), MAX_SOURCES, nullp()), nullp(), Int32(eltype(x) === UInt8 ? 1 : 0))
     p = LossParams(parameters.min_depth, parameters.max_depth, parameters.disparity_smoothness, 0.85f0,
         Cfloat(cache.ssim.c1), Cfloat(cache.ssim.c2), Int32(parameters.automasking), Int32(normalize_disparity),
         Int32(smooth_weight_mode), Int32(1), Int32(n_global), Int32(abs_subgradient))
@@ -362,7 +364,7 @@ function slow_depth(x::CuArray{Float32,5}, ssim, backprojections, projections, i
         1, pad([pointer(disp)], MAX_SCALES, nullp()), pad(Int32[W], MAX_SCALES, Int32(0)), pad(Int32[H], MAX_SCALES, Int32(0)),
         pad(Cfloat[1], MAX_SCALES, 0f0), nullp(), k9(Ks), k9(invKs), pointer(loss),
         pad([pointer(dd)], MAX_SCALES, nullp()), pad(map(pointer, dr), MAX_SOURCES, nullp()),
-        pad(map(pointer, dt), MAX_SOURCES, nullp()), nullp())
+        pad(map(pointer, dt), MAX_SOURCES, nullp()), nullp(), Int32(0))
     p = LossParams(min_depth, max_depth, 1e-3, 0.85f0, Cfloat(ssim.c1), Cfloat(ssim.c2), Int32(0),
         Int32(0), Int32(1), Int32(1), Int32(0), Int32(0))                   # un-normalised, weight 1  (:39)
     adam = AdamParams(3e-4, 0.9, 0.999, 1e-8)                               # ADAM(3e-4)              (:16)
@@ -404,6 +406,21 @@ function depth10k_batch(strips::CuArray{UInt8,4}; flips::Union{Nothing,CuArray{U
     GC.@preserve strips flips x check(ccall((:mdb_ingest_triplet_u8, libmdb200), Int32,
         (Ptr{Cvoid}, CuPtr{UInt8}, CuPtr{UInt8}, Int32, Int32, Int32, Int32, CuPtr{Cfloat}, Ptr{Cvoid}),
         handle(), strips, flips === nothing ? CuPtr{UInt8}(0) : pointer(flips), W, H, N, Int32(grayscale), x, stream_ptr()))
+    x
+end
+
+"""
+    depth10k_batch_u8(strips::CuArray{UInt8,4}; flips = nothing) -> CuArray{UInt8,5} (W,H,3,3,N)
+
+The same split / FlipX / transpose without the conversion: the N0f8 stack `fused_loss` reads directly (a quarter of the bytes).
+"""
+function depth10k_batch_u8(strips::CuArray{UInt8,4}; flips::Union{Nothing,CuArray{UInt8,1}} = nothing)
+    _, W3, H, N = size(strips)
+    W = W3 ÷ 3
+    x = CuArray{UInt8}(undef, W, H, 3, 3, N)
+    GC.@preserve strips flips x check(ccall((:mdb_ingest_triplet_u8_planar, libmdb200), Int32,
+        (Ptr{Cvoid}, CuPtr{UInt8}, CuPtr{UInt8}, Int32, Int32, Int32, CuPtr{UInt8}, Ptr{Cvoid}),
+        handle(), strips, flips === nothing ? CuPtr{UInt8}(0) : pointer(flips), W, H, N, x, stream_ptr()))
     x
 end
 

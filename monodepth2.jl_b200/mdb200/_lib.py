@@ -46,6 +46,7 @@ class LossIO(C.Structure):
         ("d_disparity", C.c_void_p * MAX_SCALES),
         ("d_rvec", C.c_void_p * MAX_SOURCES), ("d_tvec", C.c_void_p * MAX_SOURCES),
         ("vis_warp_loss", C.c_void_p),
+        ("x_format", C.c_int32),
     ]
 
 
@@ -153,6 +154,7 @@ PROTOTYPES = {
     "mdb_slow_depth_destroy": (_i32, [_vp]),
     "mdb_ingest_triplet_u8": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp]),
     "mdb_ingest_kitti_u8": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
+    "mdb_ingest_triplet_u8_planar": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp]),
     "mdb_pose_head": (_i32, [_vp, _vp, _i32, _i32, _i32, _f32, _vp, _vp, _vp]),
     "mdb_pose_head_bwd": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _f32, _vp, _vp]),
     "mdb_disparity_heads": (_i32, [_vp, C.POINTER(_vp), C.POINTER(_i32), C.POINTER(_i32), _i32, _i32, C.POINTER(_vp), _vp]),

@@ -544,7 +544,13 @@ class FusedLoss:
     def __call__(self, x: torch.Tensor, disparities: Sequence[torch.Tensor], poses: Sequence[Pose],
                  auto_loss: Optional[torch.Tensor] = None) -> LossResult:
         io = self.io
-        _chk(x, "x")
+        if x.dtype == torch.uint8:      # N0f8 frames, converted in the kernel (mdb_loss_io.x_format = 1)
+            if not x.is_cuda or not x.is_contiguous():
+                raise ValueError("x must be a contiguous CUDA tensor")
+            io.x_format = 1
+        else:
+            _chk(x, "x")
+            io.x_format = 0
         if tuple(x.shape) != self.shape:
             raise ValueError(f"x has shape {tuple(x.shape)}, planned for {self.shape}")
         io.x = x.data_ptr()
@@ -803,6 +809,26 @@ def ingest_triplet_u8(strips: torch.Tensor, width: int, flips: Optional[torch.Te
     _chk(out, "out")
     h = handle()
     check(h, lib.mdb_ingest_triplet_u8(h, _p(strips), _p(flips), width, H, N, int(grayscale), _p(out), _stream()))
+    return out
+
+
+def ingest_triplet_u8_planar(strips: torch.Tensor, width: int, flips: Optional[torch.Tensor] = None,
+                             out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """The split / FlipX / transpose of `ingest_triplet_u8` without the conversion: strips uint8 (N,H,3W,3) -> uint8
+    (N,3,3,H,W), the stack `FusedLoss` reads directly when handed a uint8 `x` (Float32(::N0f8) happens in the kernel)."""
+    if strips.dtype != torch.uint8 or not strips.is_cuda or not strips.is_contiguous():
+        raise ValueError("strips must be a contiguous CUDA uint8 tensor (N,H,3W,3)")
+    N, H, W3, ch = strips.shape
+    if ch != 3 or W3 != 3 * width:
+        raise ValueError(f"strips has shape {tuple(strips.shape)}, expected (N,H,{3 * width},3)")
+    if flips is not None and (flips.dtype != torch.uint8 or not flips.is_cuda or flips.numel() != N):
+        raise ValueError("flips must be a CUDA uint8 tensor of N entries")
+    if out is None:
+        out = torch.empty((N, 3, 3, H, width), device=strips.device, dtype=torch.uint8)
+    elif tuple(out.shape) != (N, 3, 3, H, width) or out.dtype != torch.uint8 or not out.is_contiguous():
+        raise ValueError("out must be a contiguous uint8 tensor (N,3,3,H,W)")
+    h = handle()
+    check(h, lib.mdb_ingest_triplet_u8_planar(h, _p(strips), _p(flips), width, H, N, _p(out), _stream()))
     return out
 
 

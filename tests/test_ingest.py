@@ -150,3 +150,70 @@ def test_kitti_frames_feed_the_loss():
     a = float(plan(x, disps, poses).loss)
     b = float(plan(torch.tensor(ref_x, device=DEV), disps, poses).loss)
     assert a == b and np.isfinite(a)
+
+
+# ---- uint8 frames read by the fused kernel itself (mdb_loss_io.x_format = 1) --------------------------------------
+def test_n0f8_conversion_identities():
+    """What csrc/photo_strip.inl's cvx() does, in numpy, for all 256 values: (2^23 + u) - 2^23 == u, and
+    fma(f, r1, f r2) with r1 = fl(1/255), r2 = fl(1/255 - r1) == u / 255 correctly rounded -- whereas the one-multiply
+    shortcut u * (1/255f) is NOT (126 of 256 values differ), so that shortcut would not be Float32(::N0f8)."""
+    u = np.arange(256, dtype=np.float32)
+    exact = I.n0f8_to_f32(np.arange(256, dtype=np.uint8))
+    g = (np.uint32(0x4B000000) | np.arange(256, dtype=np.uint32)).view(np.float32)
+    assert np.array_equal(g - np.float32(8388608.0), u)
+    r1 = np.float32(0.003921568859368562698)
+    r2 = np.float32(-2.3191758e-10)
+    assert r1 == np.float32(1.0 / 255.0) and r2 == np.float32(1.0 / 255.0 - float(r1))
+    t = (u * r2).astype(np.float32)
+    fma = (u.astype(np.float64) * np.float64(r1) + t.astype(np.float64)).astype(np.float32)   # exact product, one rounding
+    assert np.array_equal(fma, exact)
+    assert int(((u * r1) != exact).sum()) == 126
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("W,H,N,auto,scales", [(416, 128, 3, False, (0.125, 0.25, 0.5, 1.0)), (100, 36, 2, True, (0.25, 1.0)),
+                                               (61, 45, 2, False, (1.0,))])
+def test_fused_loss_reads_u8_frames_bit_identically(W, H, N, auto, scales):
+    """Strips -> planar uint8 stack -> FusedLoss(x uint8)  ==  strips -> Float32 stack -> FusedLoss(x float32), bit for bit:
+    loss, every disparity gradient, every pose gradient."""
+    import mdb200
+    inp = synth.make_loss_inputs(W, H, N, seed=17, automasking=auto, scales=scales)
+    rng = np.random.default_rng(5)
+    strips = torch.tensor(synth.to_u8_strips(inp.x), device=DEV)
+    flips = torch.tensor((rng.random(N) < 0.5).astype(np.uint8), device=DEV)
+    xf = mdb200.ingest_triplet_u8(strips, W, flips)
+    xu = mdb200.ingest_triplet_u8_planar(strips, W, flips)
+    assert xu.dtype == torch.uint8 and tuple(xu.shape) == tuple(xf.shape)
+    assert np.array_equal(I.n0f8_to_f32(xu.cpu().numpy()), xf.cpu().numpy())
+    sizes = [(d.shape[-1], d.shape[-2]) for d in inp.disparities]
+    kw = dict(W=W, H=H, C=3, L=3, N=N, disp_sizes=sizes, scales=inp.scales, target_id=inp.target_id, source_ids=inp.source_ids,
+              K=inp.K, invK=inp.invK, automasking=auto)
+    poses = [mdb200.Pose(torch.tensor(r, device=DEV), torch.tensor(t, device=DEV)) for r, t in zip(inp.rvecs, inp.tvecs)]
+    disps = [torch.tensor(d, device=DEV) for d in inp.disparities]
+    al = mdb200.automasking_loss(mdb200.SSIM(), xf, xf[:, inp.target_id - 1], source_ids=inp.source_ids) if auto else None
+    pf, pu = mdb200.FusedLoss(**kw), mdb200.FusedLoss(**kw)
+    a, b = pf(xf, disps, poses, al), pu(xu, disps, poses, al)
+    torch.cuda.synchronize()
+    assert float(a.loss) == float(b.loss) and np.isfinite(float(a.loss))
+    for u, v in zip(a.d_disparities, b.d_disparities):
+        assert torch.equal(u, v)
+    for u, v in zip(a.d_poses, b.d_poses):
+        assert torch.equal(u.rvec, v.rvec) and torch.equal(u.tvec, v.tvec)
+    # the same plan serves both element types from one call to the next
+    c = pu(xf, disps, poses, al)
+    torch.cuda.synchronize()
+    assert float(c.loss) == float(a.loss)
+
+
+@pytest.mark.gpu
+def test_u8_frames_rejected_where_not_served():
+    import mdb200
+    inp = synth.make_loss_inputs(64, 32, 1, seed=3)
+    xu = torch.zeros((1, 3, 3, 32, 64), dtype=torch.uint8, device=DEV)
+    sizes = [(d.shape[-1], d.shape[-2]) for d in inp.disparities]
+    plan = mdb200.FusedLoss(W=64, H=32, C=3, L=3, N=1, disp_sizes=sizes, scales=inp.scales, target_id=2, source_ids=[1, 3],
+                            K=inp.K, invK=inp.invK, upsample_align_corners=False)
+    poses = [mdb200.Pose(torch.tensor(r, device=DEV), torch.tensor(t, device=DEV)) for r, t in zip(inp.rvecs, inp.tvecs)]
+    from mdb200 import _lib
+    with pytest.raises(_lib.MdbError, match="x_format = 1"):
+        plan(xu, [torch.tensor(d, device=DEV) for d in inp.disparities], poses)

@@ -10,7 +10,7 @@ fn = None; rows = []
 for line in sass.splitlines():
     if 'Function :' in line:
         fn = line.split(':', 1)[1].strip(); continue
-    if fn and 'photo_strip_kernelILi3ELi2ELb0ELb1' in fn:
+    if fn and 'photo_strip_kernelILi3ELi2ELb0ELb1ELb0' in fn:
         m = re.match(r'\s+/\*([0-9a-f]{4,})\*/\s+(.*?);', line)
         if m: rows.append((int(m.group(1), 16), m.group(2).strip()))
 back = [(a, int(re.search(r'0x([0-9a-f]+)', t).group(1), 16)) for a, t in rows if t.split()[0].startswith(('BRA', '@')) and 'BRA' in t and re.search(r'0x([0-9a-f]+)', t) and int(re.search(r'0x([0-9a-f]+)', t).group(1), 16) < a]
@@ -24,7 +24,7 @@ h = collections.Counter(re.sub(r'^@!?U?P\d+\s+', '', t).split()[0].split('.')[0]
 print(' '.join(f'{k}:{v}' for k, v in h.most_common(28)))
 res = subprocess.run(['cuobjdump', '-res-usage', obj], capture_output=True, text=True).stdout.splitlines()
 for i, l in enumerate(res):
-    if 'photo_strip_kernelILi3ELi2ELb0ELb1' in l: print(res[i + 1].strip())
+    if 'photo_strip_kernelILi3ELi2ELb0ELb1ELb0' in l: print(res[i + 1].strip())
 
 if '--json' in sys.argv:
     out = sys.argv[sys.argv.index('--json') + 1]
@@ -33,7 +33,7 @@ if '--json' in sys.argv:
         d = open(os.path.join(root, path), 'rb').read()
         return hashlib.sha1(b'blob %d\0' % len(d) + d).hexdigest()
     flops = 2 * h['FFMA'] + h['FADD'] + h['FMUL'] + 4 * h['FFMA2'] + 2 * h['FADD2'] + 2 * h['FMUL2']
-    usage = [res[i + 1].strip() for i, l in enumerate(res) if 'photo_strip_kernelILi3ELi2ELb0ELb1' in l]
+    usage = [res[i + 1].strip() for i, l in enumerate(res) if 'photo_strip_kernelILi3ELi2ELb0ELb1ELb0' in l]
     json.dump({'kernel': 'photo_strip_kernel<3,2,false>', 'row_loop_instructions': len(body), 'histogram': dict(h.most_common()),
                'fp32_flops_per_lane_row': flops, 'fp32_flop_formula': '2 FFMA + FADD + FMUL + 4 FFMA2 + 2 FADD2 + 2 FMUL2 (static count of the row loop)',
                'res_usage': usage[0] if usage else None,
