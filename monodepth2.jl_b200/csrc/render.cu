@@ -320,6 +320,40 @@ MDB_DEV FTap ftap_fast(const double* __restrict__ hd, const PixBase& p, const Re
   return t;
 }
 
+// The same short path with everything the pullback wants: four tap offsets, the clamp masks (no gradient where the
+// coordinate was clamped), homogeneous coordinates up to the common factor 1 / H22 (the pullback is invariant to it).
+struct GridC { double sx, sy, cx0, cy0; };
+MDB_DEV void axis_cell_mask(double r, int bi, int n, int& i0, float& f, float& m, float& q) {
+  const double fl = floor(r);
+  i0 = bi + (int)fl;
+  f = (float)(r - fl);
+  m = (i0 >= 0 && i0 <= n - 2 && (i0 > 0 || f > 0.0f)) ? 1.0f : 0.0f;   // 0 < coordinate < n - 1
+  if (i0 < 0) { i0 = 0; f = 0.0f; }
+  if (i0 > n - 2) { i0 = n - 2; f = 1.0f; }
+  q = (float)(i0 + 1) + f;
+}
+template <int FLAGS>
+MDB_DEV RTaps render_taps_fast(const double* __restrict__ hd, const PixBase& p, const GridC& gc, int W, int H) {
+  const double2 c0 = __ldg(reinterpret_cast<const double2*>(hd)), c1 = __ldg(reinterpret_cast<const double2*>(hd) + 1);
+  const double2 c2 = __ldg(reinterpret_cast<const double2*>(hd) + 2), c3 = __ldg(reinterpret_cast<const double2*>(hd) + 3);
+  const double e = fma(c3.x, p.ud, c3.y * p.vd), zd = 1.0 + e;
+  const double N0 = fma(-p.ud, e, fma(c0.x, p.ud, fma(c0.y, p.vd, c1.x)));
+  const double N1 = fma(-p.vd, e, fma(c1.y, p.ud, fma(c2.x, p.vd, c2.y)));
+  float zf;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(zf) : "f"((float)zd));
+  double zi = (double)zf;
+  zi = fma(zi, fma(-zd, zi, 1.0), zi);
+  const double txd = N0 * zi, tyd = N1 * zi;
+  RTaps t;
+  t.X0 = fma(p.ud, zd, N0); t.X1 = fma(p.vd, zd, N1); t.X2 = zd;
+  t.x = p.uf + (float)txd; t.y = p.vf + (float)tyd;
+  t.valid = true;   // not used by the pullback
+  axis_cell_mask((FLAGS & RV_MINE_GRID) ? txd : fma(txd, gc.sx, p.bxf), p.bxi, W, t.x0, t.fx, t.mx, t.q0);
+  axis_cell_mask((FLAGS & RV_MINE_GRID) ? tyd : fma(tyd, gc.sy, p.byf), p.byi, H, t.y0, t.fy, t.my, t.q1);
+  t.o00 = t.y0 * W + t.x0; t.o01 = t.o00 + 1; t.o10 = t.o00 + W; t.o11 = t.o10 + 1;
+  return t;
+}
+
 // double path: any homography (the pullback and mdb_sample use render_taps, the same arithmetic)
 template <int FLAGS>
 __device__ __noinline__ FTap ftap_precise(const double* __restrict__ Hm, const PixBase& p, int W, int H) {

@@ -17,6 +17,7 @@ struct RenderBwdArgs {
   const float* wsum;
   const float* g_edepth;
   float depth_eps;
+  GridC gc;                 // grid constants of the short tap path (render_taps_fast)
   float4* acc;              // [B Np][H W][2] zero-initialised: {d rgb, d sigma}, {d xyz, 0}; accumulated with
                             // 128-bit red.global.add.v4.f32 (one L2 reduction per tap and channel GROUP)
   float* part_pose;         // [B][blocks][12]
@@ -24,6 +25,10 @@ struct RenderBwdArgs {
 };
 
 constexpr int RB_THREADS = 128;
+#ifndef RB_MINB
+#define RB_MINB 6      // CTAs per SM the register allocation aims for: 85 registers (272 B spilled) beat 128 spill-free at config 4 --
+                       // bwd us, as written / folded / MINE / MINE+folded: 1: 271 / 236 / 293 / 245, 5: 294 / 259 / 314 / 266, 6: 262 / 209 / 271 / 210, 8: 280 / 226 / 305 / 244
+#endif
 constexpr int RB_MAXP = 64;   // planes supported by the per-warp shared accumulators
 
 struct Pend {
@@ -77,7 +82,7 @@ MDB_DEV void scatter4(float4* __restrict__ plane, int slot, const Pend& t, bool 
 }
 
 template <int FLAGS, bool FUSED>
-__global__ void __launch_bounds__(RB_THREADS) render_bwd_kernel(const __grid_constant__ RenderBwdArgs a) {
+__global__ void __launch_bounds__(RB_THREADS, RB_MINB) render_bwd_kernel(const __grid_constant__ RenderBwdArgs a) {
   __shared__ float s_disp[RB_THREADS / 32][RB_MAXP];
   __shared__ float s_pose[RB_THREADS / 32][12];
   const int pix = blockIdx.x * RB_THREADS + threadIdx.x;
@@ -107,6 +112,7 @@ __global__ void __launch_bounds__(RB_THREADS) render_bwd_kernel(const __grid_con
   for (int i = lane; i < RB_MAXP; i += 32) s_disp[warp][i] = 0.0f;
   __syncwarp();
 
+  const PixBase pb = pix_base<FLAGS>(u, v, a.gc.sx, a.gc.sy, a.gc.cx0, a.gc.cy0);
   float Q = 0.0f;
   float n_xyz[3] = {0, 0, 0};   // sampled xyz of plane k+1
   Pend pd;
@@ -165,7 +171,8 @@ __global__ void __launch_bounds__(RB_THREADS) render_bwd_kernel(const __grid_con
 
   for (int k = a.Np - 1; k >= 0; --k) {
     const int kb = b * a.Np + k;
-    const RTaps t = render_taps<FLAGS>(a.prep[kb].Hst, u, v, a.W, a.H);
+    const RTaps t = __ldg(&a.prep[kb].fast) ? render_taps_fast<FLAGS>(a.prep[kb].hd, pb, a.gc, a.W, a.H)   // warp-uniform
+                                             : render_taps<FLAGS>(a.prep[kb].Hst, u, v, a.W, a.H);
     Pend cur;
     cur.o00 = t.o00; cur.o01 = t.o01; cur.o10 = t.o10; cur.o11 = t.o11;
     cur.fx = t.fx; cur.fy = t.fy; cur.mx = t.mx; cur.my = t.my;
@@ -573,6 +580,8 @@ int32_t mdb_render_tgt_rgb_depth_bwd_ex(mdb_handle* h, const float* rgb, const f
   a.g_tacc = g_depth; a.W = W; a.H = H; a.Np = Np; a.B = B; a.tvec = tvec;
   a.edepth = expected_depth_saved; a.wsum = weights_sum_saved; a.g_edepth = g_expected_depth;
   a.depth_eps = opts ? opts->depth_eps : 1e-5f;
+  a.gc.sx = (double)(W - 1) / W; a.gc.sy = (double)(H - 1) / H;
+  a.gc.cx0 = 0.5 * a.gc.sx + 0.5 * (W - 1); a.gc.cy0 = 0.5 * a.gc.sy + 0.5 * (H - 1);
   for (int i = 0; i < 9; ++i) a.Kinv_f[i] = rc.Kinv_f[i];
   a.acc = acc;
   a.part_pose = (float*)(ws + L.o_pose); a.part_disp = (float*)(ws + L.o_disp);
