@@ -60,6 +60,9 @@ constexpr int STRIP_NHEAD = 3;   // record head: photometric sum, smoothness x-s
                        // clamps, no stage gating): fewer instructions and one long basic block for ptxas to schedule
 #endif
 #if !defined(STRIP_MAXREG) && !defined(STRIP_MINB)
+#ifndef STRIP_TMA_TGT
+#define STRIP_TMA_TGT 0   // experiment (profiles/r2_strip_summary.md): target rows by cp.async.bulk into a shared-memory ring
+#endif
 #ifndef STRIP_PEEL_CAPTURED
 #define STRIP_PEEL_CAPTURED 0
 #endif
@@ -229,6 +232,41 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   }
 #endif
   const unsigned tgt_off = a.tgt * C * planei;
+#if STRIP_TMA_TGT
+  // ---- experiment: the target rows (the one REGULAR image operand: 3 x 128 B per row, the same for every lane pattern) arrive
+  // by TMA bulk copies (cp.async.bulk, 144 B = 36 floats per channel from a 16-byte aligned column 2 left of lane 0) into a
+  // 4-row shared-memory ring, two rows ahead of their use, completion on one mbarrier per ring slot.  Interior strips only
+  // (a bulk copy cannot clamp at the image border); edge strips keep the register path.
+  static_assert(STRIP_WARPS == 1, "the TMA experiment assumes one-warp CTAs");
+  constexpr int TMA_SLOTS = 4, TMA_ROWF = 36;
+  __shared__ __align__(16) float s_tgt[TMA_SLOTS][C][TMA_ROWF];
+  __shared__ __align__(8) unsigned long long s_bar[TMA_SLOTS];
+  const bool tma_ok = !U8 && strip >= 1 && X0 + 32 <= W && (W & 3) == 0 && ((reinterpret_cast<uintptr_t>(a.x) & 15) == 0);
+  const unsigned bar0 = (unsigned)__cvta_generic_to_shared(&s_bar[0]);
+  const unsigned tg0 = (unsigned)__cvta_generic_to_shared(&s_tgt[0][0][0]);
+  if (tma_ok) {
+    if (lane == 0) {
+#pragma unroll
+      for (int i = 0; i < TMA_SLOTS; ++i) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8 * i));
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+  }
+  auto tma_issue = [&](int rr) {   // target row of ring row rr into slot (rr - (Y0 - 2)) & 3
+    __syncwarp();                  // every lane has read the slot's previous contents (row rr - 4)
+    if (lane == 0) {
+      const int rc2 = min(max(geo_row(rr, H), 0), H - 1);
+      const unsigned sl = (unsigned)(rr - (Y0 - 2)) & 3u, bar = bar0 + 8 * sl;
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((unsigned)(C * TMA_ROWF * 4)) : "memory");
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+        const XT* src = xb + (unsigned)(tgt_off + c * planei + rc2 * W + (X0 - 4));
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(tg0 + (unsigned)((sl * C + c) * TMA_ROWF * 4)), "l"(src), "r"((unsigned)(TMA_ROWF * 4)), "r"(bar) : "memory");
+      }
+    }
+  };
+#endif
   unsigned src_off[S];
 #pragma unroll
   for (int s = 0; s < S; ++s) src_off[s] = a.src[s] * C * planei;
@@ -379,6 +417,11 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
       }
       td_ = (float)dd_;
       const double invd = fma(dd_, a.dd_d, a.mind_d);   // 1 / depth (src/utils.jl:179-183)
+#if STRIP_TMA_TGT
+      if (tma_ok) {
+        if (r + 2 <= Y1 + 1) tma_issue(r + 2);
+      } else
+#endif
 #pragma unroll
       for (int c = 0; c < C; ++c) ty_[c] = ldx(xb + (unsigned)(tgt_off + c * planei + rc * W + gxc));
 #if STRIP_AM_EARLY
@@ -452,12 +495,28 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   };
 
   // bilinear value and its derivatives of the issued row -> xn, yn, dn; park the derivatives in `wslot`
-  auto consume = [&](int wslot, P (&xn)[C], float (&yn)[C], float& dn) {
+  auto consume = [&](int r, int wslot, P (&xn)[C], float (&yn)[C], float& dn) {
     {
       // rows outside the image and columns outside it carry the (finite) values of the clamped addresses:
       // nothing reads them unmasked -- window rows reflect (stage C), window columns reflect (nl, nr), the
       // smoothness weights vanish across the border, and columns that are not window columns select no source
       dn = td_;
+#if STRIP_TMA_TGT
+      if (tma_ok) {
+        const unsigned k = (unsigned)(r - (Y0 - 2)), sl = k & 3u, par = (k >> 2) & 1u, bar = bar0 + 8 * sl;
+        unsigned done = 0;
+        int spins = 0;
+        do {
+          asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                       : "=r"(done) : "r"(bar), "r"(par) : "memory");
+        } while (!done && ++spins < (1 << 22));
+        if (!done) __trap();   // a copy that never lands must not hang the GPU
+#pragma unroll
+        for (int c = 0; c < C; ++c) ty_[c] = s_tgt[sl][c][lane + 2];
+      }
+#else
+      (void)r;
+#endif
       float park[DRV];
 #pragma unroll
       for (int c = 0; c < C; ++c) {
@@ -534,7 +593,7 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
         }
       }
     }
-    consume(slot, xn, yn, dn);
+    consume(r, slot, xn, yn, dn);
     if (ST && STRIP_FENCE >= 1) asm volatile("bar.warp.sync 0xffffffff;" ::: "memory");
 
     // =========================== C: window row r-1 =============================================
@@ -720,6 +779,9 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   {
     // steady-state rows: all three stages active (r >= Y0 + 2), window row r-1 and pixel row r-2 inside this segment
     // (r <= Y1), no reflected row in sight (pixel row >= 2 and <= H-3, r + 1 <= H - 1)
+#if STRIP_TMA_TGT
+    if (tma_ok) { tma_issue(Y0 - 2); tma_issue(Y0 - 1); }
+#endif
     constexpr bool PEEL = STRIP_PEEL && (CP || DBG || STRIP_PEEL_CAPTURED);
     const int s_lo = max(Y0 + 2, 4), s_hi = PEEL ? min(Y1, H - 2) : -1000000;
     int r = Y0 - 2;
