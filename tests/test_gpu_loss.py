@@ -359,3 +359,52 @@ def test_large_single_image_vs_c_oracle():
     for s in range(2):
         e = np.abs(res.d_poses[s].rvec.double().cpu().numpy() - ref["d_rvec"][s]).max() / np.abs(ref["d_rvec"][s]).max()
         assert e < 5e-3, e
+
+
+# ---- size-independent properties at BASELINE.json's full size (config 5: 64 x 1024x320) --------------------------------
+def _config5_on_device(N=None):
+    import mdb200
+    from mdb200 import synth
+    inp = synth.make_config("config5") if N is None else synth.make_config("config5", N=N)
+    dev = torch.device("cuda:0")
+    x = torch.tensor(inp.x, device=dev)
+    disps = [torch.tensor(d, device=dev) for d in inp.disparities]
+    rv = [torch.tensor(r, device=dev) for r in inp.rvecs]
+    tv = [torch.tensor(t, device=dev) for t in inp.tvecs]
+    kw = dict(W=inp.W, H=inp.H, C=inp.C, L=3, N=inp.N, disp_sizes=[(d.shape[-1], d.shape[-2]) for d in inp.disparities],
+              scales=inp.scales, target_id=inp.target_id, source_ids=inp.source_ids, K=inp.K, invK=inp.invK, automasking=False)
+    return mdb200, inp, x, disps, rv, tv, kw
+
+
+def test_full_size_batch_permutation_equivariance():
+    """Items are independent (the only coupling is the mean over N, src/training.jl:69): permuting the 64 items of config 5
+    permutes every gradient bit for bit and leaves the loss alone up to the order of 64 additions."""
+    mdb200, inp, x, disps, rv, tv, kw = _config5_on_device()
+    perm = torch.randperm(inp.N, generator=torch.Generator().manual_seed(3)).to(x.device)
+    plan = mdb200.FusedLoss(**kw)
+    a = plan(x, disps, [mdb200.Pose(r, t) for r, t in zip(rv, tv)])
+    la, ga = float(a.loss), [g.clone() for g in a.d_disparities]
+    pa = [(p.rvec.clone(), p.tvec.clone()) for p in a.d_poses]
+    b = plan(x[perm].contiguous(), [d[perm].contiguous() for d in disps],
+             [mdb200.Pose(r[perm].contiguous(), t[perm].contiguous()) for r, t in zip(rv, tv)])
+    torch.cuda.synchronize()
+    assert abs(float(b.loss) - la) <= 1e-6 * abs(la)
+    for g0, g1 in zip(ga, b.d_disparities):
+        assert torch.equal(g0[perm], g1)
+    for (r0, t0), p1 in zip(pa, b.d_poses):
+        assert torch.equal(r0[perm], p1.rvec) and torch.equal(t0[perm], p1.tvec)
+
+
+def test_full_size_linearity_in_the_global_batch():
+    """n_global only scales: the same 64 items as a shard of a batch of 128 give exactly half the loss and half of every
+    gradient (a power of two: exact in float32) -- the contract the multi-GPU sharding rests on."""
+    mdb200, inp, x, disps, rv, tv, kw = _config5_on_device()
+    poses = [mdb200.Pose(r, t) for r, t in zip(rv, tv)]
+    a = mdb200.FusedLoss(**kw)(x, disps, poses)
+    b = mdb200.FusedLoss(n_global=2 * inp.N, **kw)(x, disps, poses)
+    torch.cuda.synchronize()
+    assert float(b.loss) * 2 == float(a.loss)
+    for g0, g1 in zip(a.d_disparities, b.d_disparities):
+        assert torch.equal(g0, g1 * 2)
+    for p0, p1 in zip(a.d_poses, b.d_poses):
+        assert torch.allclose(p0.rvec, p1.rvec * 2, rtol=1e-6, atol=0) and torch.allclose(p0.tvec, p1.tvec * 2, rtol=1e-6, atol=0)
