@@ -134,3 +134,69 @@ def test_bench_reference_arm_runs_on_the_host():
     line = json.loads(out.stdout.strip().splitlines()[-1])
     assert line["impl"] == "reference" and line["value"] > 0 and line["unit"] == "warped_px/s"
     assert line["cpu_baseline"]["kind"] == "port" and line["e2e"]["h2d_bytes_per_step"] == 0
+
+
+# ---- the Julia glue cannot be executed here (no Julia runtime): what CAN be checked statically is checked ----------------
+def _strip_c_comments(s):
+    return re.sub(r"/\*.*?\*/", "", s, flags=re.S)
+
+
+def _c_struct_fields(header, name):
+    end = re.search(r"\}\s*" + name + r"\s*;", header).start()
+    start = header.rfind("{", 0, end)
+    body = header[start + 1:end]
+    out = []
+    for decl in body.split(";"):
+        decl = decl.strip()
+        if not decl:
+            continue
+        for part in decl.split(","):                     # "int32_t W, H, C" / "float K[9], invK[9]"
+            m = re.search(r"(\w+)\s*(?:\[[^\]]*\])?\s*$", part.strip())
+            out.append(m.group(1))
+    return out
+
+
+def _julia_struct_fields(src, name):
+    body = re.search(r"^struct " + name + r"\b(.*?)^end", src, flags=re.S | re.M).group(1)
+    body = re.sub(r"#.*", "", body)
+    return re.findall(r"(\w+)::", body)
+
+
+def test_julia_struct_mirrors_follow_the_header():
+    """LossIO / LossParams / RenderOpts / AdamParams in julia/MDB200.jl list the fields of mdb_loss_io / mdb_loss_params /
+    mdb_render_opts / mdb_adam_params in the header's order (a `ccall` passes them by reference: order IS the ABI)."""
+    header = _strip_c_comments(open(os.path.join(ROOT, "include", "mdb200.h")).read())
+    jl = open(os.path.join(ROOT, "monodepth2.jl_b200", "julia", "MDB200.jl")).read()
+    for c_name, j_name in [("mdb_loss_io", "LossIO"), ("mdb_loss_params", "LossParams"), ("mdb_render_opts", "RenderOpts"),
+                           ("mdb_adam_params", "AdamParams")]:
+        assert _julia_struct_fields(jl, j_name) == _c_struct_fields(header, c_name), (c_name, j_name)
+
+
+def test_julia_ccalls_name_exported_symbols_with_the_right_arity():
+    """Every `ccall((:mdb_xxx, libmdb200), ret, (argtypes...), args...)` in the glue names a function the header declares,
+    with as many argument types as the C prototype has parameters."""
+    header = _strip_c_comments(open(os.path.join(ROOT, "include", "mdb200.h")).read())
+    protos = {}
+    for m in re.finditer(r"\b(mdb_\w+)\s*\(([^;{]*?)\)\s*;", header, flags=re.S):
+        params = m.group(2).strip()
+        protos[m.group(1)] = 0 if params in ("", "void") else len(params.split(","))
+    jdir = os.path.join(ROOT, "monodepth2.jl_b200", "julia")
+    seen = 0
+    for fn in ("MDB200.jl", "MDB200_ops.jl"):
+        src = re.sub(r"#.*", "", open(os.path.join(jdir, fn)).read())
+        for m in re.finditer(r"ccall\(\(:(\w+),\s*libmdb200\),\s*\w+,\s*\(", src):
+            sym, i, depth = m.group(1), m.end(), 1
+            j = i
+            while depth:                                    # the argument-type tuple, balanced
+                depth += {"(": 1, ")": -1}.get(src[j], 0)
+                j += 1
+            types = src[i:j - 1]
+            # top-level commas of the tuple (CuPtr{Cfloat} has none inside; NTuple{9,Cfloat} would: count at brace depth 0)
+            n, d = (1 if types.strip().rstrip(",").strip() else 0), 0
+            for ch in types.strip().rstrip(","):
+                d += {"{": 1, "}": -1, "(": 1, ")": -1}.get(ch, 0)
+                n += ch == "," and d == 0
+            assert sym in protos, f"{fn}: ccall of undeclared symbol {sym}"
+            assert n == protos[sym], f"{fn}: {sym} takes {protos[sym]} parameters, the ccall lists {n} types"
+            seen += 1
+    assert seen >= 30
