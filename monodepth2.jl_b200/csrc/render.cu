@@ -18,8 +18,10 @@ namespace {
 // per (plane, batch item) constants (16-byte aligned: Ax/tx and hf are read with 128-bit loads)
 struct alignas(16) PlanePrep {
   double Hst[9];   // H_src_tgt = inv(K (R + t n^T / depth) K_inv), row-major
+  float pad0_[2];  // G1 | disp | pad: 48 bytes at offset 80, read by the pullback with three 128-bit loads
   float G1[9];     // K^T H_src_tgt^T : pulls d/d(homogeneous source coords) back to d/dM
   float disp;      // 1 / depth_src
+  float pad1_[2];
   // xyz_tgt of this plane as a function of the 1-based source pixel m = (w, h, 1):  Ax m + tx  with
   // Ax = R K_inv / disparity  (src/render.jl:25-30, 51-62) -- what the producers folded into the kernels use
   float Ax[9];
@@ -27,12 +29,14 @@ struct alignas(16) PlanePrep {
   // H_src_tgt / H22 - I for the forward kernel:  x - u = (a0 u + h01 v + h02 - u e) / (1 + e),
   // y - v = (h10 u + a1 v + h12 - v e) / (1 + e),  e = h20 u + h21 v.   hd = {a0, h01, h02, h10, a1, h12, h20, h21}.
   // The two numerators and e are formed in double (8 operations, no cancellation error), everything after them in float.
-  double hd[8];   // byte offset 160
+  double hd[8];   // byte offset 176
   int fast;       // the displacement stays below RF_FAST_PX pixels on this image and |e| < 1/4: a float holds it to ~2e-6 px
                   // and the forward takes the short path; otherwise the plane goes through the double-precision homography
   int pad_[3];
 };
 constexpr double RF_FAST_PX = 64.0;
+static_assert(offsetof(PlanePrep, G1) % 16 == 0 && offsetof(PlanePrep, Ax) % 16 == 0 && offsetof(PlanePrep, hd) % 16 == 0 &&
+              sizeof(PlanePrep) % 16 == 0, "PlanePrep: the blocks read with 128-bit loads must be 16-byte aligned");
 
 // variants of the sampler / outputs (mdb_render_opts in include/mdb200.h)
 constexpr int RV_MINE_GRID = 1, RV_MINE_MASK = 2;
@@ -161,6 +165,7 @@ __global__ void render_prep_kernel(const float* __restrict__ disp, int is_depth,
     }
     p.fast = (rc.W > 0 && em < 0.25 && 1.25 * mx < RF_FAST_PX && 1.25 * my < RF_FAST_PX) ? 1 : 0;   // NaN / inf compare false
     p.pad_[0] = p.pad_[1] = p.pad_[2] = 0;
+    p.pad0_[0] = p.pad0_[1] = p.pad1_[0] = p.pad1_[1] = 0.0f;
   }
   out[idx] = p;
 }
@@ -390,7 +395,7 @@ struct PlanePtr { const float* rgb; const float* sig; const float* xyz; const Pl
 template <bool FUSED>
 MDB_DEV void render_sample_xyz(const PlanePtr& pl, const FTap& t, const FW& w, int W, float* xyz) {
   if (FUSED) {
-    const float4* ax4 = reinterpret_cast<const float4*>(pl.prep->Ax);   // Ax[9], tx[3]: 48 bytes at offset 112
+    const float4* ax4 = reinterpret_cast<const float4*>(pl.prep->Ax);   // Ax[9], tx[3]: 48 bytes at offset 128
     const float4 c0 = __ldg(ax4), c1 = __ldg(ax4 + 1), c2 = __ldg(ax4 + 2);
     xyz[0] = fmaf(c0.x, t.q0, fmaf(c0.y, t.q1, c0.z + c2.y));
     xyz[1] = fmaf(c0.w, t.q0, fmaf(c1.x, t.q1, c1.y + c2.z));

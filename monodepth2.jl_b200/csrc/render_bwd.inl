@@ -32,7 +32,7 @@ constexpr int RB_THREADS = 128;
 constexpr int RB_MAXP = 64;   // planes supported by the per-warp shared accumulators
 
 struct Pend {
-  int o00, o01, o10, o11;
+  int o00;                // top-left cell (x0 <= W-2, y0 <= H-2): the other three taps are +1, +W, +W+1
   float fx, fy, mx, my;
   float dxv[3], dyv[3];   // d(sampled xyz_c)/d(ix), d/d(iy)
   float dix, diy;         // contribution of the rgb + sigma channels, complete
@@ -55,12 +55,12 @@ MDB_DEV void red_v4(float4* p, float x, float y, float z, float w) {
 // (right column, corner) the warp sums its contribution first and lane 0 issues the reductions,
 // which takes a 32-way contention out of L2.
 MDB_DEV void scatter4(float4* __restrict__ plane, int slot, const Pend& t, bool on, float g0, float g1, float g2,
-                      float g3, int lane) {
+                      float g3, int lane, int W) {
   const unsigned M = __ballot_sync(MDB_FULL, on);
   if (M == 0u) return;
   const float w11 = t.fx * t.fy;
   float w[4] = {1.0f - t.fx - t.fy + w11, t.fx - w11, t.fy - w11, w11};
-  const int o[4] = {t.o00, t.o01, t.o10, t.o11};
+  const int o[4] = {t.o00, t.o00 + 1, t.o00 + W, t.o00 + W + 1};
   const int lead = __ffs(M) - 1;
   const int o_lead = __shfl_sync(MDB_FULL, t.o00, lead);
   const bool same = __all_sync(MDB_FULL, !on || t.o00 == o_lead);
@@ -76,9 +76,12 @@ MDB_DEV void scatter4(float4* __restrict__ plane, int slot, const Pend& t, bool 
     return;
   }
   if (!on) return;
-#pragma unroll
-  for (int j = 0; j < 4; ++j)
-    if (w[j] != 0.0f) red_v4(plane + 2 * o[j] + slot, g0 * w[j], g1 * w[j], g2 * w[j], g3 * w[j]);
+  float4* q = plane + 2 * t.o00 + slot;   // one address; the other three are constant offsets from it
+  if (w[0] != 0.0f) red_v4(q, g0 * w[0], g1 * w[0], g2 * w[0], g3 * w[0]);
+  if (w[1] != 0.0f) red_v4(q + 2, g0 * w[1], g1 * w[1], g2 * w[1], g3 * w[1]);
+  q += 2 * W;
+  if (w[2] != 0.0f) red_v4(q, g0 * w[2], g1 * w[2], g2 * w[2], g3 * w[2]);
+  if (w[3] != 0.0f) red_v4(q + 2, g0 * w[3], g1 * w[3], g2 * w[3], g3 * w[3]);
 }
 
 template <int FLAGS, bool FUSED>
@@ -115,8 +118,8 @@ __global__ void __launch_bounds__(RB_THREADS, RB_MINB) render_bwd_kernel(const _
   const PixBase pb = pix_base<FLAGS>(u, v, a.gc.sx, a.gc.sy, a.gc.cx0, a.gc.cy0);
   float Q = 0.0f;
   float n_xyz[3] = {0, 0, 0};   // sampled xyz of plane k+1
-  Pend pd;
-  pd.k = -1;
+  Pend pA, pB;   // the plane being sampled and the pending one, alternating roles (no 30-register copy per plane)
+  pA.k = pB.k = -1;
 
   // pullback of the pending plane's sample position into (dR, dt, d disparity)
   auto finish = [&](Pend& p, const float* gextra) {
@@ -135,10 +138,11 @@ __global__ void __launch_bounds__(RB_THREADS, RB_MINB) render_bwd_kernel(const _
       const float gxs = dix * p.mx * sxw, gys = diy * p.my * syh;   // d/dx_src, d/dy_src
       const float i2 = 1.0f / p.X2;
       const float g0 = gxs * i2, g1 = gys * i2, g2 = -(gxs * p.x + gys * p.y) * i2;
-      const float* G1 = a.prep[kb].G1;
-      const float a0 = G1[0] * g0 + G1[1] * g1 + G1[2] * g2;
-      const float a1 = G1[3] * g0 + G1[4] * g1 + G1[5] * g2;
-      const float a2 = G1[6] * g0 + G1[7] * g1 + G1[8] * g2;
+      const float4* G4 = reinterpret_cast<const float4*>(a.prep[kb].G1);   // G1[9], disp: three 128-bit loads
+      const float4 G0 = __ldg(G4), Ga = __ldg(G4 + 1), Gb = __ldg(G4 + 2);
+      const float a0 = G0.x * g0 + G0.y * g1 + G0.z * g2;
+      const float a1 = G0.w * g0 + Ga.x * g1 + Ga.y * g2;
+      const float a2 = Ga.z * g0 + Ga.w * g1 + Gb.x * g2;
       const float Y0 = a.Kinv_f[0] * p.X0 + a.Kinv_f[1] * p.X1 + a.Kinv_f[2] * p.X2;
       const float Y1 = a.Kinv_f[3] * p.X0 + a.Kinv_f[4] * p.X1 + a.Kinv_f[5] * p.X2;
       const float Y2 = a.Kinv_f[6] * p.X0 + a.Kinv_f[7] * p.X1 + a.Kinv_f[8] * p.X2;
@@ -146,7 +150,7 @@ __global__ void __launch_bounds__(RB_THREADS, RB_MINB) render_bwd_kernel(const _
       acc[0] -= a0 * Y0; acc[1] -= a0 * Y1; acc[2] -= a0 * Y2;
       acc[3] -= a1 * Y0; acc[4] -= a1 * Y1; acc[5] -= a1 * Y2;
       acc[6] -= a2 * Y0; acc[7] -= a2 * Y1; acc[8] -= a2 * Y2;
-      const float dsp = a.prep[kb].disp;
+      const float dsp = Gb.y;   // PlanePrep::disp
       acc[9] -= a0 * Y2 * dsp; acc[10] -= a1 * Y2 * dsp; acc[11] -= a2 * Y2 * dsp;
       ddisp = -(a0 * t0 + a1 * t1 + a2 * t2) * Y2;
       if (FUSED) {
@@ -164,36 +168,48 @@ __global__ void __launch_bounds__(RB_THREADS, RB_MINB) render_bwd_kernel(const _
     }
     if (!FUSED)
       scatter4(a.acc + (size_t)(b * a.Np + p.k) * WH * 2, 1, p, active && (gx[0] != 0.0f || gx[1] != 0.0f || gx[2] != 0.0f),
-               gx[0], gx[1], gx[2], 0.0f, lane);
+               gx[0], gx[1], gx[2], 0.0f, lane, a.W);
     ddisp = warp_sum(ddisp);
     if (lane == 0) s_disp[warp][p.k] += ddisp;
   };
 
-  for (int k = a.Np - 1; k >= 0; --k) {
+  auto step = [&](int k, Pend& cur, Pend& pd) {
     const int kb = b * a.Np + k;
     const RTaps t = __ldg(&a.prep[kb].fast) ? render_taps_fast<FLAGS>(a.prep[kb].hd, pb, a.gc, a.W, a.H)   // warp-uniform
                                              : render_taps<FLAGS>(a.prep[kb].Hst, u, v, a.W, a.H);
-    Pend cur;
-    cur.o00 = t.o00; cur.o01 = t.o01; cur.o10 = t.o10; cur.o11 = t.o11;
-    cur.fx = t.fx; cur.fy = t.fy; cur.mx = t.mx; cur.my = t.my;
+    {
+      // top-left cell <= (W-2, H-2) on both tap paths: the last column / row is that cell with weight 1
+      int x0 = t.x0, y0 = t.y0;
+      cur.fx = t.fx; cur.fy = t.fy;
+      if (x0 > a.W - 2) { x0 = a.W - 2; cur.fx = 1.0f; }
+      if (y0 > a.H - 2) { y0 = a.H - 2; cur.fy = 1.0f; }
+      cur.o00 = y0 * a.W + x0;
+    }
+    cur.mx = t.mx; cur.my = t.my;
+    RTaps tw = t;                      // the weights the value / derivative formulas below use
+    tw.fx = cur.fx; tw.fy = cur.fy;
     cur.X0 = (float)t.X0; cur.X1 = (float)t.X1; cur.X2 = (float)t.X2; cur.x = t.x; cur.y = t.y; cur.k = k;
     cur.q0 = t.q0; cur.q1 = t.q1;
     float rgbv[3], dxr[3], dyr[3], xyzv[3];
     const float* pr = a.rgb + (size_t)kb * 3 * WH;
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
-      const float v00 = ldg(pr + c * WH + t.o00), v01 = ldg(pr + c * WH + t.o01), v10 = ldg(pr + c * WH + t.o10), v11 = ldg(pr + c * WH + t.o11);
-      rgbv[c] = bil(t, v00, v01, v10, v11);
-      dxr[c] = fmaf(t.fy, (v11 - v10) - (v01 - v00), v01 - v00);
-      dyr[c] = fmaf(t.fx, (v11 - v01) - (v10 - v00), v10 - v00);
+      const float* q0 = pr + c * WH + cur.o00;
+      const float* q1 = q0 + a.W;
+      const float v00 = ldg(q0), v01 = ldg(q0 + 1), v10 = ldg(q1), v11 = ldg(q1 + 1);
+      rgbv[c] = bil(tw, v00, v01, v10, v11);
+      dxr[c] = fmaf(tw.fy, (v11 - v10) - (v01 - v00), v01 - v00);
+      dyr[c] = fmaf(tw.fx, (v11 - v01) - (v10 - v00), v10 - v00);
     }
     const float* ps = a.sigma + (size_t)kb * WH;
     float sraw, dxs, dys;
     {
-      const float v00 = ldg(ps + t.o00), v01 = ldg(ps + t.o01), v10 = ldg(ps + t.o10), v11 = ldg(ps + t.o11);
-      sraw = bil(t, v00, v01, v10, v11);
-      dxs = fmaf(t.fy, (v11 - v10) - (v01 - v00), v01 - v00);
-      dys = fmaf(t.fx, (v11 - v01) - (v10 - v00), v10 - v00);
+      const float* q0 = ps + cur.o00;
+      const float* q1 = q0 + a.W;
+      const float v00 = ldg(q0), v01 = ldg(q0 + 1), v10 = ldg(q1), v11 = ldg(q1 + 1);
+      sraw = bil(tw, v00, v01, v10, v11);
+      dxs = fmaf(tw.fy, (v11 - v10) - (v01 - v00), v01 - v00);
+      dys = fmaf(tw.fx, (v11 - v01) - (v10 - v00), v10 - v00);
     }
     if (FUSED) {
       const PlanePrep& pp_ = a.prep[kb];
@@ -208,10 +224,12 @@ __global__ void __launch_bounds__(RB_THREADS, RB_MINB) render_bwd_kernel(const _
       const float* px = a.xyz + (size_t)kb * WH * 3;
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
-        const float v00 = ldg(px + 3 * t.o00 + c), v01 = ldg(px + 3 * t.o01 + c), v10 = ldg(px + 3 * t.o10 + c), v11 = ldg(px + 3 * t.o11 + c);
-        xyzv[c] = bil(t, v00, v01, v10, v11);
-        cur.dxv[c] = fmaf(t.fy, (v11 - v10) - (v01 - v00), v01 - v00);
-        cur.dyv[c] = fmaf(t.fx, (v11 - v01) - (v10 - v00), v10 - v00);
+        const float* q0 = px + 3 * cur.o00 + c;
+        const float* q1 = q0 + 3 * a.W;
+        const float v00 = ldg(q0), v01 = ldg(q0 + 3), v10 = ldg(q1), v11 = ldg(q1 + 3);
+        xyzv[c] = bil(tw, v00, v01, v10, v11);
+        cur.dxv[c] = fmaf(tw.fy, (v11 - v10) - (v01 - v00), v01 - v00);
+        cur.dyv[c] = fmaf(tw.fx, (v11 - v01) - (v10 - v00), v10 - v00);
       }
     }
 #pragma unroll
@@ -250,7 +268,7 @@ __global__ void __launch_bounds__(RB_THREADS, RB_MINB) render_bwd_kernel(const _
     {
       const float g0 = gO[0] * w, g1 = gO[1] * w, g2 = gO[2] * w;
       scatter4(a.acc + (size_t)kb * WH * 2, 0, cur, active && (g0 != 0.0f || g1 != 0.0f || g2 != 0.0f || gsig != 0.0f),
-               g0, g1, g2, gsig, lane);
+               g0, g1, g2, gsig, lane, a.W);
     }
     if (active) {
       const float g0 = gO[0] * w, g1 = gO[1] * w, g2 = gO[2] * w;
@@ -260,13 +278,15 @@ __global__ void __launch_bounds__(RB_THREADS, RB_MINB) render_bwd_kernel(const _
       diy = fmaf(gsig, dys, diy);
     }
     cur.dix = dix; cur.diy = diy;
-    pd = cur;
 #pragma unroll
     for (int c = 0; c < 3; ++c) n_xyz[c] = xyzv[c];
-  }
+  };
   {
+    int k = a.Np - 1;
+    for (; k >= 1; k -= 2) { step(k, pA, pB); step(k - 1, pB, pA); }
     const float zero[3] = {0, 0, 0};
-    finish(pd, zero);   // plane 0
+    if (k == 0) { step(0, pA, pB); finish(pA, zero); }   // plane 0 is the last pending one
+    else finish(pB, zero);
   }
 #pragma unroll
   for (int i = 0; i < 12; ++i) {
