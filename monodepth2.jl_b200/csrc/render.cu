@@ -288,22 +288,28 @@ MDB_DEV PixBase pix_base(int u, int v, double sx, double sy, double cx0, double 
   return p;
 }
 
-// one axis, coordinate = bi + r with r (double) small: cell index (<= n-2), weight in [0, 1], 1-based clamped point.
-// floor and fraction in double -- the LAST plane's transmittance exp(-1000 sigma) (src/render.jl:36) turns 1e-7 of sampled
-// sigma into 4e-5 of output, so the interpolation weight has to be good to a few 1e-8 -- the clamp on the integer part.
-MDB_DEV void axis_cell(double r, int bi, int n, int& i0, float& f, float& q) {
+// One axis, coordinate = bi + r with r (double) small: cell index (<= n-2), weight in [0, 1], the clamp mask of the pullback
+// (1 where 0 < coordinate < n-1) and the 1-based clamped point.  Floor and fraction in double -- the LAST plane's
+// transmittance exp(-1000 sigma) (src/render.jl:36) turns 1e-7 of sampled sigma into 4e-5 of output, so the interpolation
+// weight has to be good to a few 1e-8 -- the clamp on the integer part.
+struct GridC { double sx, sy, cx0, cy0; };
+MDB_DEV void axis_cell(double r, int bi, int n, int& i0, float& f, float& m, float& q) {
   const double fl = floor(r);
   i0 = bi + (int)fl;
   f = (float)(r - fl);
+  m = (i0 >= 0 && i0 <= n - 2 && (i0 > 0 || f > 0.0f)) ? 1.0f : 0.0f;
   if (i0 < 0) { i0 = 0; f = 0.0f; }                  // coordinate < 0: clamped onto the first sample
   if (i0 > n - 2) { i0 = n - 2; f = 1.0f; }          // coordinate >= n - 1: the last sample = cell n-2 with weight 1
   q = (float)(i0 + 1) + f;
 }
 
-// short path (PlanePrep::fast): displacement form, all in double but cheap: numerators 8 operations, reciprocal from a float
-// seed + one Newton step (|1 + e - 1| < 1/4), 2 products, 2 FMAs; no comparisons, clamps or un-normalisation in double.
+// Short path (PlanePrep::fast): displacement form, all in double but cheap: numerators 8 operations, reciprocal from a
+// float seed + one Newton step (|e| < 1/4), 2 products, 2 FMAs; no comparisons, clamps or un-normalisation in double.
+// Fills everything the forward AND the pullback want (the forward's unused fields cost nothing: dead code): the four tap
+// offsets in the cell convention (top-left cell <= (W-2, H-2), the others +1, +W, +W+1), the clamp masks, homogeneous
+// coordinates up to the common factor 1 / H22 (the pullback is invariant to it).
 template <int FLAGS>
-MDB_DEV FTap ftap_fast(const double* __restrict__ hd, const PixBase& p, const RenderArgs& a) {
+MDB_DEV RTaps render_taps_fast(const double* __restrict__ hd, const PixBase& p, const GridC& gc, int W, int H) {
   const double2 c0 = __ldg(reinterpret_cast<const double2*>(hd)), c1 = __ldg(reinterpret_cast<const double2*>(hd) + 1);
   const double2 c2 = __ldg(reinterpret_cast<const double2*>(hd) + 2), c3 = __ldg(reinterpret_cast<const double2*>(hd) + 3);
   const double e = fma(c3.x, p.ud, c3.y * p.vd), zd = 1.0 + e;      // zd in (3/4, 5/4)
@@ -315,47 +321,23 @@ MDB_DEV FTap ftap_fast(const double* __restrict__ hd, const PixBase& p, const Re
   zi = fma(zi, fma(-zd, zi, 1.0), zi);                              // relative error ~1e-14
   const double txd = N0 * zi, tyd = N1 * zi;                        // x - u, y - v
   const float tx = (float)txd, ty = (float)tyd;
-  FTap t;
-  if (FLAGS & RV_MINE_MASK) t.valid = (tx < (float)(a.W - p.u)) && (tx > (float)(-1 - p.u)) && (ty < (float)(a.H - p.v)) && (ty > (float)(-1 - p.v));
+  RTaps t;
+  t.X0 = fma(p.ud, zd, N0); t.X1 = fma(p.vd, zd, N1); t.X2 = zd;
+  t.x = p.uf + tx; t.y = p.vf + ty;
+  if (FLAGS & RV_MINE_MASK) t.valid = (tx < (float)(W - p.u)) && (tx > (float)(-1 - p.u)) && (ty < (float)(H - p.v)) && (ty > (float)(-1 - p.v));
   else t.valid = (tx > -p.uf) && (ty > -p.vf);    // x > 0 & y > 0
-  int x0, y0;
-  axis_cell((FLAGS & RV_MINE_GRID) ? txd : fma(txd, a.sx, p.bxf), p.bxi, a.W, x0, t.fx, t.q0);
-  axis_cell((FLAGS & RV_MINE_GRID) ? tyd : fma(tyd, a.sy, p.byf), p.byi, a.H, y0, t.fy, t.q1);
-  t.o = y0 * a.W + x0;
+  axis_cell((FLAGS & RV_MINE_GRID) ? txd : fma(txd, gc.sx, p.bxf), p.bxi, W, t.x0, t.fx, t.mx, t.q0);
+  axis_cell((FLAGS & RV_MINE_GRID) ? tyd : fma(tyd, gc.sy, p.byf), p.byi, H, t.y0, t.fy, t.my, t.q1);
+  t.o00 = t.y0 * W + t.x0; t.o01 = t.o00 + 1; t.o10 = t.o00 + W; t.o11 = t.o10 + 1;
   return t;
 }
 
-// The same short path with everything the pullback wants: four tap offsets, the clamp masks (no gradient where the
-// coordinate was clamped), homogeneous coordinates up to the common factor 1 / H22 (the pullback is invariant to it).
-struct GridC { double sx, sy, cx0, cy0; };
-MDB_DEV void axis_cell_mask(double r, int bi, int n, int& i0, float& f, float& m, float& q) {
-  const double fl = floor(r);
-  i0 = bi + (int)fl;
-  f = (float)(r - fl);
-  m = (i0 >= 0 && i0 <= n - 2 && (i0 > 0 || f > 0.0f)) ? 1.0f : 0.0f;   // 0 < coordinate < n - 1
-  if (i0 < 0) { i0 = 0; f = 0.0f; }
-  if (i0 > n - 2) { i0 = n - 2; f = 1.0f; }
-  q = (float)(i0 + 1) + f;
-}
 template <int FLAGS>
-MDB_DEV RTaps render_taps_fast(const double* __restrict__ hd, const PixBase& p, const GridC& gc, int W, int H) {
-  const double2 c0 = __ldg(reinterpret_cast<const double2*>(hd)), c1 = __ldg(reinterpret_cast<const double2*>(hd) + 1);
-  const double2 c2 = __ldg(reinterpret_cast<const double2*>(hd) + 2), c3 = __ldg(reinterpret_cast<const double2*>(hd) + 3);
-  const double e = fma(c3.x, p.ud, c3.y * p.vd), zd = 1.0 + e;
-  const double N0 = fma(-p.ud, e, fma(c0.x, p.ud, fma(c0.y, p.vd, c1.x)));
-  const double N1 = fma(-p.vd, e, fma(c1.y, p.ud, fma(c2.x, p.vd, c2.y)));
-  float zf;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(zf) : "f"((float)zd));
-  double zi = (double)zf;
-  zi = fma(zi, fma(-zd, zi, 1.0), zi);
-  const double txd = N0 * zi, tyd = N1 * zi;
-  RTaps t;
-  t.X0 = fma(p.ud, zd, N0); t.X1 = fma(p.vd, zd, N1); t.X2 = zd;
-  t.x = p.uf + (float)txd; t.y = p.vf + (float)tyd;
-  t.valid = true;   // not used by the pullback
-  axis_cell_mask((FLAGS & RV_MINE_GRID) ? txd : fma(txd, gc.sx, p.bxf), p.bxi, W, t.x0, t.fx, t.mx, t.q0);
-  axis_cell_mask((FLAGS & RV_MINE_GRID) ? tyd : fma(tyd, gc.sy, p.byf), p.byi, H, t.y0, t.fy, t.my, t.q1);
-  t.o00 = t.y0 * W + t.x0; t.o01 = t.o00 + 1; t.o10 = t.o00 + W; t.o11 = t.o10 + 1;
+MDB_DEV FTap ftap_fast(const double* __restrict__ hd, const PixBase& p, const RenderArgs& a) {
+  const GridC gc{a.sx, a.sy, a.cx0, a.cy0};
+  const RTaps r = render_taps_fast<FLAGS>(hd, p, gc, a.W, a.H);
+  FTap t;
+  t.o = r.o00; t.fx = r.fx; t.fy = r.fy; t.q0 = r.q0; t.q1 = r.q1; t.valid = r.valid;
   return t;
 }
 
