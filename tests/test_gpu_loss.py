@@ -408,3 +408,43 @@ def test_full_size_linearity_in_the_global_batch():
         assert torch.equal(g0, g1 * 2)
     for p0, p1 in zip(a.d_poses, b.d_poses):
         assert torch.allclose(p0.rvec, p1.rvec * 2, rtol=1e-6, atol=0) and torch.allclose(p0.tvec, p1.tvec * 2, rtol=1e-6, atol=0)
+
+
+@pytest.mark.parametrize("seed", range(10))
+def test_random_geometries_half_pixel_and_u8(seed):
+    """The two round-2 input modes on seeded random shapes: upsample_align_corners = 0 against the float64 oracle in the same
+    mode, and (C = 3) uint8 frames against the Float32 path fed the converted stack, bit for bit."""
+    import mdb200
+    from mdb200 import synth
+    from oracle import torch_ref as T
+    rng = np.random.default_rng(2000 + seed)
+    W, H = int(rng.integers(12, 180)), int(rng.integers(10, 80))
+    N = int(rng.integers(1, 4))
+    scales = [(0.5, 1.0), (0.25, 0.5, 1.0), (0.125, 0.25, 0.5, 1.0), (0.25, 1.0), (0.125, 1.0)][int(rng.integers(0, 5))]
+    auto = bool(rng.integers(0, 2))
+    inp = synth.make_loss_inputs(W, H, N, C=3, seed=300 + seed, scales=scales, automasking=auto)
+    # frames quantised to 8 bits so that both element types describe the same images
+    q = np.clip(np.rint(inp.x * 255.0), 0, 255).astype(np.uint8)
+    inp.x = (q.astype(np.float32) / np.float32(255.0)).astype(np.float32)
+    T.UPSAMPLE_ALIGN_CORNERS = False
+    try:
+        ref = P.oracle_train_loss(inp)
+    finally:
+        T.UPSAMPLE_ALIGN_CORNERS = True
+    res, _ = _run_gpu(inp, auto=ref["auto"], align=False)
+    _compare(inp, ref, res)
+    # uint8 frames (default alignment: the uint8 path is the throughput instantiation)
+    dev = torch.device("cuda:0")
+    xf, xu = torch.tensor(inp.x, device=dev), torch.tensor(q, device=dev)
+    disps = [torch.tensor(d, device=dev) for d in inp.disparities]
+    poses = [mdb200.Pose(torch.tensor(r, device=dev), torch.tensor(t, device=dev)) for r, t in zip(inp.rvecs, inp.tvecs)]
+    al = mdb200.automasking_loss(mdb200.SSIM(), xf, xf[:, inp.target_id - 1], source_ids=inp.source_ids) if auto else None
+    kw = dict(W=W, H=H, C=3, L=3, N=N, disp_sizes=[(d.shape[-1], d.shape[-2]) for d in inp.disparities], scales=inp.scales,
+              target_id=inp.target_id, source_ids=inp.source_ids, K=inp.K, invK=inp.invK, automasking=auto)
+    a, b = mdb200.FusedLoss(**kw)(xf, disps, poses, al), mdb200.FusedLoss(**kw)(xu, disps, poses, al)
+    torch.cuda.synchronize()
+    assert float(a.loss) == float(b.loss)
+    for u, v in zip(a.d_disparities, b.d_disparities):
+        assert torch.equal(u, v)
+    for u, v in zip(a.d_poses, b.d_poses):
+        assert torch.equal(u.rvec, v.rvec) and torch.equal(u.tvec, v.tvec)
