@@ -97,8 +97,8 @@ _comm = {"transport": None}
 def init_comm(device, max_count: int, transport: str = "peer") -> str:
     """Set up the C-ABI communicator of this rank's handle; `torch.distributed` (already initialised) carries
     the bootstrap.  transport "peer": the one-shot peer-write reduce (falls back to "nccl" when the peers'
-    buffers cannot be mapped through CUDA IPC); "nccl": ncclAllReduce through the library; "torch":
-    torch.distributed.all_reduce.  Returns the transport in use."""
+    buffers cannot be mapped through CUDA IPC); "nccl": ncclAllReduce through the library (falls back to "torch" when
+    the communicator cannot be created); "torch": torch.distributed.all_reduce.  Returns the transport in use."""
     import ctypes as ct
     from . import api, _lib
     rank, world = dist.get_rank(), dist.get_world_size()
@@ -128,7 +128,13 @@ def init_comm(device, max_count: int, transport: str = "peer") -> str:
         _lib.check(h, _lib.lib.mdb_comm_get_unique_id(uid, 128))
     box = [bytes(uid)]
     dist.broadcast_object_list(box, src=0)
-    _lib.check(h, _lib.lib.mdb_comm_init(h, ct.c_char_p(box[0]), rank, world))
+    rc = _lib.lib.mdb_comm_init(h, ct.c_char_p(box[0]), rank, world)
+    ok = torch.tensor([1 if rc == 0 else 0], device=dev)
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN)          # every rank must take the same transport
+    if int(ok) != 1:                                    # e.g. no libnccl to dlopen: torch.distributed carries the reduction
+        _lib.lib.mdb_comm_destroy(h)
+        _comm["transport"] = "torch"
+        return "torch"
     _comm["transport"] = "nccl"
     return "nccl"
 
