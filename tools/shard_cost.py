@@ -1,5 +1,5 @@
 """Is the spread of the per-rank loss-kernel times at 8 GPUs (0.63 .. 0.69 ms) the items or the GPUs?  Times the fused kernel
-on ONE GPU for each of the eight 8-item shards of config 5.  python tools/shard_cost.py"""
+on ONE GPU for each of the eight 8-item shards of config 5.  python tools/shard_cost.py [--strided]"""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "monodepth2.jl_b200"))
@@ -11,11 +11,13 @@ sizes = [(d.shape[-1], d.shape[-2]) for d in inp.disparities]
 plan = mdb200.FusedLoss(W=inp.W, H=inp.H, C=3, L=3, N=8, n_global=64, disp_sizes=sizes, scales=inp.scales, target_id=2, source_ids=[1, 3],
                         K=inp.K, invK=inp.invK, automasking=False)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+import numpy as np
+strided = "--strided" in sys.argv      # item i -> shard i mod 8 (what torch's DistributedSampler does) instead of contiguous slabs
 for k in range(8):
-    lo, hi = 8 * k, 8 * k + 8
-    x = torch.tensor(inp.x[lo:hi], device=dev)
-    disps = [torch.tensor(d[lo:hi], device=dev) for d in inp.disparities]
-    poses = [mdb200.Pose(torch.tensor(r[lo:hi], device=dev), torch.tensor(t[lo:hi], device=dev)) for r, t in zip(inp.rvecs, inp.tvecs)]
+    idx = np.arange(k, 64, 8) if strided else np.arange(8 * k, 8 * k + 8)
+    x = torch.tensor(inp.x[idx], device=dev)
+    disps = [torch.tensor(d[idx], device=dev) for d in inp.disparities]
+    poses = [mdb200.Pose(torch.tensor(r[idx], device=dev), torch.tensor(t[idx], device=dev)) for r, t in zip(inp.rvecs, inp.tvecs)]
     for _ in range(3):
         plan(x, disps, poses)
     steps = 20
