@@ -658,9 +658,10 @@ def run_render(args, emit=True):
                        "timing": "CUDA events around the pre-planned C-ABI calls (mdb200.RenderPlan: buffers allocated once)"},
             "gpu_launches": int(launches), "variants": variants,
             "roofline": {"bound": "hbm", "kernel": "render_fwd_kernel + render_bwd_kernel", "unit": "GB/s", "peak": peak, "peak_source": peak_src,
-                         "note": "ncu (profiles/r1_strip_summary.md): the forward issues 370 thread-instructions per plane-pixel and "
-                                 "touches 39.5 MB of DRAM at B=2 (the reference's grid normalisation clamps 3/4 of the samples onto "
-                                 "the border): issue-bound; the backward is bound by L2 reductions onto those border cells",
+                         "note": "ncu (profiles/r2_render_ncu.json): the forward issues 259 warp-instructions per warp-sample and reads 25 MB "
+                                 "of DRAM at B=2 (the reference's grid normalisation clamps 3/4 of the samples onto the border): "
+                                 "issue- and latency-bound; the pullback (767 per sample, one thread per pixel, 32 planes in series) "
+                                 "is bound by that serial chain at 33 % occupancy",
                          "fwd": {"ms": fm, "algorithmic_bytes": fwd_b, "achieved": fwd_b / (fm * 1e-3) / 1e9, "frac": fwd_b / (fm * 1e-3) / 1e9 / peak},
                          "bwd": {"ms": bm, "algorithmic_bytes": bwd_b, "achieved": bwd_b / (bm * 1e-3) / 1e9, "frac": bwd_b / (bm * 1e-3) / 1e9 / peak},
                          "achieved": (fwd_b + bwd_b) / ((fm + bm) * 1e-3) / 1e9, "frac": (fwd_b + bwd_b) / ((fm + bm) * 1e-3) / 1e9 / peak}}
