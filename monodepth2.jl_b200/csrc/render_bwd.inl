@@ -84,6 +84,13 @@ MDB_DEV void scatter4(float4* __restrict__ plane, int slot, const Pend& t, bool 
   if (w[3] != 0.0f) red_v4(q + 2, g0 * w[3], g1 * w[3], g2 * w[3], g3 * w[3]);
 }
 
+// the double-precision tap path out of line: planes that need it are rare, and the pullback's hot loop (two copies of the
+// plane step) is large enough for instruction fetch to show in the profile (as written: 1.3 stall cycles per issue)
+template <int FLAGS>
+__device__ __noinline__ RTaps render_taps_outofline(const double* __restrict__ Hm, int u, int v, int W, int H) {
+  return render_taps<FLAGS>(Hm, u, v, W, H);
+}
+
 template <int FLAGS, bool FUSED>
 __global__ void __launch_bounds__(RB_THREADS, RB_MINB) render_bwd_kernel(const __grid_constant__ RenderBwdArgs a) {
   __shared__ float s_disp[RB_THREADS / 32][RB_MAXP];
@@ -176,7 +183,7 @@ __global__ void __launch_bounds__(RB_THREADS, RB_MINB) render_bwd_kernel(const _
   auto step = [&](int k, Pend& cur, Pend& pd) {
     const int kb = b * a.Np + k;
     const RTaps t = __ldg(&a.prep[kb].fast) ? render_taps_fast<FLAGS>(a.prep[kb].hd, pb, a.gc, a.W, a.H)   // warp-uniform
-                                             : render_taps<FLAGS>(a.prep[kb].Hst, u, v, a.W, a.H);
+                                             : render_taps_outofline<FLAGS>(a.prep[kb].Hst, u, v, a.W, a.H);
     {
       // top-left cell <= (W-2, H-2) on both tap paths: the last column / row is that cell with weight 1
       int x0 = t.x0, y0 = t.y0;
