@@ -60,6 +60,9 @@ constexpr int STRIP_NHEAD = 3;   // record head: photometric sum, smoothness x-s
                        // clamps, no stage gating): fewer instructions and one long basic block for ptxas to schedule
 #endif
 #if !defined(STRIP_MAXREG) && !defined(STRIP_MINB)
+#ifndef STRIP_ROWBAR
+#define STRIP_ROWBAR 0    // experiment (profiles/r2_strip_summary.md, 17): named barrier per row across the CTA's warps
+#endif
 #ifndef STRIP_TMA_TGT
 #define STRIP_TMA_TGT 0   // experiment (profiles/r2_strip_summary.md): target rows by cp.async.bulk into a shared-memory ring
 #endif
@@ -560,6 +563,11 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   };
   auto row = [&](int r, auto steady) {
     constexpr bool ST = decltype(steady)::value;
+#if STRIP_ROWBAR
+    // experiment: what a per-row rendezvous of the four scale-warps of a strip would cost BEFORE anything is shared
+    // (STRIP_NWARPS = 4, Ls = 4: the warps of a CTA are the four scales of one strip segment and walk the same rows)
+    asm volatile("bar.sync 1, %0;" ::"n"(STRIP_THREADS) : "memory");
+#endif
     issue(r, steady);
     // ---- smoothness of pixel row r-2 (src/utils.jl:163-177): needs nothing of row r, so it runs in the
     // shadow of the loads just issued; one register (its pullback) crosses stages C and D
