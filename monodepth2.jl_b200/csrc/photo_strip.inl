@@ -59,12 +59,18 @@ constexpr int STRIP_NHEAD = 3;   // record head: photometric sum, smoothness x-s
                        // a steady-state copy in which every row-position test is a compile-time constant (no reflection, no
                        // clamps, no stage gating): fewer instructions and one long basic block for ptxas to schedule
 #endif
-#if !defined(STRIP_MAXREG) && !defined(STRIP_MINB)
+// ---- switches of recorded experiments (profiles/r2_strip_summary.md); the defaults are the shipped kernel -------------
+#ifndef STRIP_UNROLL
+#define STRIP_UNROLL 1     // experiment 19: 2 or 3 steady-state rows per loop trip
+#endif
+#ifndef STRIP_FAKE_RGBX
+#define STRIP_FAKE_RGBX 0  // experiment 18 (timing only, wrong results)
+#endif
 #ifndef STRIP_ROWBAR
-#define STRIP_ROWBAR 0    // experiment (profiles/r2_strip_summary.md, 17): named barrier per row across the CTA's warps
+#define STRIP_ROWBAR 0     // experiment 17: named barrier per row across the CTA's warps
 #endif
 #ifndef STRIP_TMA_TGT
-#define STRIP_TMA_TGT 0   // experiment (profiles/r2_strip_summary.md): target rows by cp.async.bulk into a shared-memory ring
+#define STRIP_TMA_TGT 0    // experiment 15: target rows by cp.async.bulk into a shared-memory ring
 #endif
 #ifndef STRIP_PEEL_CAPTURED
 #define STRIP_PEEL_CAPTURED 0
@@ -73,6 +79,7 @@ constexpr int STRIP_NHEAD = 3;   // record head: photometric sum, smoothness x-s
 #define STRIP_MAXREG_CAPTURED 216   // spill-free; config 1 per iteration: 152 (24 B spilled) 23.95 us, 184 (16 B) 24.18, 216 (0 B) 22.58;
                                     // peeled copy at 160 / 200: 23.94 / 24.62.  Occupancy is no concern at 480 warps.
 #endif
+#if !defined(STRIP_MAXREG) && !defined(STRIP_MINB)
 #define STRIP_MAXREG 160   // 12 warps per SM, no spills.  Round 1 (unpeeled loop, constants in registers): best of 128 .. 184 was
                            // 152.  Round 2 (peeled loop, constants in the bank): 152 spills 148 B (4.83 ms), 160 and 168 are
                            // spill-free (4.18 / 4.20 ms), 176 .. 224 spill again (ptxas trades) -- spills decide, not the 13th warp
@@ -467,6 +474,11 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
       for (int c = 0; c < C; ++c) {
 #pragma unroll
         for (int s = 0; s < S; ++s) {
+#if STRIP_FAKE_RGBX
+          // TIMING ONLY (wrong results): channels 1, 2 reuse channel 0's taps -- the loads and address arithmetic an
+          // interleaved RGBX source layout would save, without its wider registers: an upper bound of that layout's gain
+          if (c > 0) { tv00[c] = tv00[0]; tv01[c] = tv01[0]; tv10[c] = tv10[0]; tv11[c] = tv11[0]; continue; }
+#endif
           const XT* p = xbc[c] + ot[s];    // one IMAD.WIDE per address: the channel plane is in the base
           const XT* pb = xbc[c] + ob[s];
           tv00[c].set(s, ldx(p)); tv01[c].set(s, ldx(p + 1));
@@ -795,6 +807,12 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
     int r = Y0 - 2;
     while (r <= Y1 + 1) {
       if (PEEL && r >= s_lo && r <= s_hi) {
+#if STRIP_UNROLL == 3
+        // experiment 19: three rows per trip, so that the compiler can rename the three-deep rings instead of moving them
+        for (; r + 2 <= s_hi; r += 3) { row(r, std::true_type{}); row(r + 1, std::true_type{}); row(r + 2, std::true_type{}); }
+#elif STRIP_UNROLL == 2
+        for (; r + 1 <= s_hi; r += 2) { row(r, std::true_type{}); row(r + 1, std::true_type{}); }
+#endif
         for (; r <= s_hi; ++r) row(r, std::true_type{});
       } else {
         row(r, std::false_type{});
