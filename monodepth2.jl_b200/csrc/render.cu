@@ -30,11 +30,10 @@ struct alignas(16) PlanePrep {
   // y - v = (h10 u + a1 v + h12 - v e) / (1 + e),  e = h20 u + h21 v.   hd = {a0, h01, h02, h10, a1, h12, h20, h21}.
   // The two numerators and e are formed in double (8 operations, no cancellation error), everything after them in float.
   double hd[8];   // byte offset 176
-  int fast;       // the displacement stays below RF_FAST_PX pixels on this image and |e| < 1/4: a float holds it to ~2e-6 px
-                  // and the forward takes the short path; otherwise the plane goes through the double-precision homography
+  int fast;       // |e| < 1/4 over the whole image: the short tap path applies (render_taps_fast); otherwise -- strong perspective,
+                  // a plane close to the camera's horizon -- the plane goes through the general double-precision homography
   int pad_[3];
 };
-constexpr double RF_FAST_PX = 64.0;
 static_assert(offsetof(PlanePrep, G1) % 16 == 0 && offsetof(PlanePrep, Ax) % 16 == 0 && offsetof(PlanePrep, hd) % 16 == 0 &&
               sizeof(PlanePrep) % 16 == 0, "PlanePrep: the blocks read with 128-bit loads must be 16-byte aligned");
 
@@ -153,17 +152,13 @@ __global__ void render_prep_kernel(const float* __restrict__ disp, int is_depth,
     for (int k = 0; k < 8; ++k) hn[k] = p.Hst[k] * i22;
     hn[0] -= 1.0; hn[4] -= 1.0;
     for (int k = 0; k < 8; ++k) p.hd[k] = hn[k];
-    // bound of |x - u|, |y - v| over the image: the displacement on a 3 x 3 grid of points (corners, edge midpoints,
-    // centre) with a quarter in hand -- the numerators are quadratic in (u, v), the denominator is within 1 +- em
-    const double Wm = rc.W - 1, Hm = rc.H - 1;
-    const double em = fabs(hn[6]) * Wm + fabs(hn[7]) * Hm;
-    double mx = 0.0, my = 0.0;
-    for (int c = 0; c < 9; ++c) {
-      const double u = 0.5 * (c % 3) * Wm, v = 0.5 * (c / 3) * Hm, e = hn[6] * u + hn[7] * v;
-      mx = fmax(mx, fabs((hn[0] * u + hn[1] * v + hn[2] - u * e) / (1.0 + e)));
-      my = fmax(my, fabs((hn[3] * u + hn[4] * v + hn[5] - v * e) / (1.0 + e)));
-    }
-    p.fast = (rc.W > 0 && em < 0.25 && 1.25 * mx < RF_FAST_PX && 1.25 * my < RF_FAST_PX) ? 1 : 0;   // NaN / inf compare false
+    // the short path needs 1 + e = 1 + h20 u + h21 v away from zero over the whole image (its reciprocal starts from a float
+    // seed and takes one Newton step): |e| < 1/4.  The size of the displacement does not matter: floor and fraction of the
+    // coordinate are taken in double.  NaN / inf compare false.
+    const double em = fabs(hn[6]) * (rc.W - 1) + fabs(hn[7]) * (rc.H - 1);
+    double big = 0.0;
+    for (int k = 0; k < 8; ++k) big = fmax(big, fabs(hn[k]));
+    p.fast = (rc.W > 0 && em < 0.25 && big < 1e6) ? 1 : 0;
     p.pad_[0] = p.pad_[1] = p.pad_[2] = 0;
     p.pad0_[0] = p.pad0_[1] = p.pad1_[0] = p.pad1_[1] = 0.0f;
   }

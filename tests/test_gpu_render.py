@@ -232,12 +232,13 @@ def test_render_fused_xyz_equals_materialised_producers():
 
 
 @pytest.mark.parametrize("mine_grid", [False, True])
-@pytest.mark.parametrize("pose_scale,expect_fast", [(1.0, True), (3.0, None), (20.0, False)])
+@pytest.mark.parametrize("pose_scale,expect_fast", [(1.0, True), (3.0, True), (20.0, None), (60.0, False)])   # 20: short path, but every sample lands outside the image
 def test_render_forward_float_path_vs_double_path(mine_grid, pose_scale, expect_fast):
-    """The forward samples a plane through the float displacement form when render_prep_kernel bounds every term of the
-    displacement below 48 px (the near-identity homographies of config 4), else through the double-precision homography.
-    Same inputs through both (test hook "render_precise"): the outputs agree far inside the 1e-5 parity gate, masks are
-    equal, and with strongly non-identity poses the two runs are bit-identical (the float form was never taken)."""
+    """The forward (and the pullback) sample a plane through the short displacement form wherever the homography's
+    denominator 1 + h20 u + h21 v stays within 1 +- 1/4 over the image (render_prep_kernel decides per plane), else through
+    the general double-precision homography.  Same inputs through both (test hook "render_precise"): the outputs agree
+    far inside the 1e-5 parity gate, masks are equal, and with poses of ~0.6 rad (denominator far from 1 on every plane)
+    the two runs are bit-identical: the short form was never taken."""
     import mdb200
     ri = _rand_inputs(416, 128, 16, 2, 31, pose_scale)
     plan = mdb200.RenderPlan(416, 128, 16, 2, ri.K_inv, ri.K, mine_grid=mine_grid, mine_mask=mine_grid)
