@@ -579,7 +579,7 @@ def roofline_block(args, inp, N, seg, plan):
         # executed fp32 flops per warped pixel: per lane and row from the SASS histogram, 32 lanes per 28-pixel strip
         # (ragged last strip included), rows + 4 halo rows per segment, two sources per lane
         lanes_per_px = 32.0 * geo["strips"] / inp.W
-        rows_f = (geo["rows_per_segment"] + 4.0) / geo["rows_per_segment"]
+        rows_f = (inp.H + 4.0 * geo["segments"]) / inp.H      # 4 halo rows per row segment (segments may differ in length)
         f_wpx = sass["fp32_flops_per_lane_row"] * lanes_per_px * rows_f / S
         t_fp32 = units * f_wpx / (p_fp32 * 1e12) * 1e3
         t_roof = max(t_mem, t_fp32)

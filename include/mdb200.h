@@ -80,6 +80,8 @@ int32_t mdb_measure_fp32_peak(mdb_handle* h, void* scratch, size_t scratch_bytes
  * W > 4096 takes; "decision_dump" = device pointer to Ls N (2C+2) H W int8 makes the fused kernel (a separate
  * instantiation) record every discrete choice its pullback depends on (layout in csrc/photo_strip.inl), 0 = off;
  * "render_precise" = 1 makes the render forward sample every plane through the double-precision homography.
+ * "strip_taper" = k (2..8) forces k row segments of decreasing length (long ones launched first), -1 forces equal segments,
+ * 0 = the library's choice.
  * Set BEFORE mdb_train_loss_workspace_bytes (the record count depends on the segments).                       */
 int32_t mdb_debug_option(const char* name, int64_t value);
 

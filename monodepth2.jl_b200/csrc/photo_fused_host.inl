@@ -6,6 +6,7 @@ namespace {
 // test hooks (mdb_debug_option): process-global, read on the host only, default 0 = off
 int g_dbg_strip_segs = 0;       // force this many row segments per strip
 int g_dbg_upsample_split = 0;   // force the two-kernel V / H transpose (the W > 4096 path)
+int g_dbg_strip_taper = 0;      // experiment 20: this many row segments of linearly decreasing length, long ones first
 signed char* g_dbg_decisions = nullptr;   // device buffer [Ls][N][2C+2][H][W]: run the DBG instantiation and dump into it
 
 // ---------------------------------------------------------------------------------------
@@ -468,6 +469,27 @@ inline StripGeom strip_geom(const mdb_loss_io* io, int num_sms) {
   }
   g.seg_rows = (io->H + best_n - 1) / best_n;
   g.nsegs = (io->H + g.seg_rows - 1) / g.seg_rows;
+  // Tapered segments (round 2, experiment 20): lengths proportional to k, k-1, ..., 1, launched long ones first, so that the
+  // launch ends evenly instead of with a tail of full-length warps.  Measured at 1024x320 with L2 flushed (tools/sweep_taper.py,
+  // fused kernel ms, equal -> tapered): 8 items 0.585 -> 0.569 (k = 6), 16: 1.106 -> 1.082 (k = 4), 32: 2.138 -> 2.099 (k = 3),
+  // 64: 4.207 -> 4.144 (k = 3); 12 items (exactly one resident wave of whole-height warps) and <= 4 items are better off
+  // with equal segments.  k by the number of resident waves ONE segment index fills.  "strip_taper" = -1 switches it off.
+  int k_taper = 0;
+  if (g_dbg_strip_taper >= 2) k_taper = g_dbg_strip_taper;
+  else if (g_dbg_strip_taper == 0 && g_dbg_strip_segs == 0) {
+    const double wb = (double)base / resident;
+    k_taper = wb >= 2.0 ? 3 : (wb >= 1.2 ? 4 : ((wb >= 0.55 && wb < 0.9) ? 6 : 0));
+  }
+  if (k_taper >= 2 && k_taper <= STRIP_MAX_TAPER && io->H >= 16 * k_taper) {
+    const int k = k_taper, tot = k * (k + 1) / 2;
+    g.taper = 1; g.nsegs = k; g.seg_y[0] = 0;
+    int acc = 0;
+    for (int i = 0; i < k; ++i) {
+      acc += k - i;
+      g.seg_y[i + 1] = (i == k - 1) ? io->H : std::max(g.seg_y[i] + 4, (int)((long long)io->H * acc / tot));
+    }
+    g.seg_rows = g.seg_y[1];
+  }
   g.total = (int)(base * g.nsegs);
   return g;
 }
@@ -544,6 +566,7 @@ int32_t launch_fused(mdb_handle* h, const FusedArgs& fa, const FusedLayout& L, c
   for (int n0 = 0; n0 < fa.N; n0 += chunk) {
     const int items = std::min(chunk, fa.N - n0);
     g.n0 = n0;
+    g.items = items;
     g.total = items * per_item;
     g.cbase = 0;
     const int blocks = (g.total + STRIP_WARPS - 1) / STRIP_WARPS;
@@ -587,6 +610,7 @@ int32_t mdb_debug_option(const char* name, int64_t value) {
   else if (!strcmp(name, "upsample_split")) g_dbg_upsample_split = (int)value;
   else if (!strcmp(name, "decision_dump")) g_dbg_decisions = (signed char*)(intptr_t)value;
   else if (!strcmp(name, "render_precise")) mdb_dbg_render_precise = (int)value;
+  else if (!strcmp(name, "strip_taper")) g_dbg_strip_taper = (int)value;
   else return MDB_E_INVALID_ARG;
   return MDB_OK;
 }

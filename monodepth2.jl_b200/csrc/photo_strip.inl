@@ -154,10 +154,16 @@ template <int S> MDB_DEV Pk<S> operator+(Pk<S> a, float b) { return a + Pk<S>(b)
 // a second time instead of being copied), everything further out is never read.
 MDB_DEV int geo_row(int r, int H) { return r == -1 ? 1 : (r == H ? H - 2 : r); }
 
+constexpr int STRIP_MAX_TAPER = 8;
 struct StripGeom {
   int nstrips, nsegs, seg_rows, total;  // total = items * nsegs * nstrips * Ls warps of THIS launch
   int n0;                               // first item of this launch (a launch covers a chunk of the batch's items)
   int cbase;                            // first entry of this launch's region of c_pose
+  int items;                            // items of this launch
+  // experiment 20 (test hook "strip_taper"): row segments of decreasing length, the long ones first in launch order, so that a
+  // launch of only ~2 resident waves ends evenly; seg_y[] holds the boundaries.  0 = equal segments, item-major order.
+  int taper;
+  int seg_y[STRIP_MAX_TAPER + 1];
 };
 
 // Decision dump (DBG instantiation only; tests/test_gpu_forced.py): every discrete choice the pullback
@@ -200,18 +206,19 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   const int lane = threadIdx.x & 31, warp = __shfl_sync(MDB_FULL, (int)(threadIdx.x >> 5), 0);
   int w = blockIdx.x * STRIP_WARPS + warp;
   if (w >= g.total) return;
-  const int rec = g.n0 * (g.nsegs * g.nstrips * a.Ls) + w;   // record index in the whole batch
   const int sc = w % a.Ls; w /= a.Ls;
   const int strip = w % g.nstrips; w /= g.nstrips;
-  const int seg = w % g.nsegs;
-  const int nl_item = w / g.nsegs;        // item inside this launch's chunk
+  // launch order: scales, strips, then segments inside an item -- or, tapered, items inside a segment (long segments first)
+  const int seg = g.taper ? w / g.items : w % g.nsegs;
+  const int nl_item = g.taper ? w % g.items : w / g.nsegs;        // item inside this launch's chunk
   const int n = g.n0 + nl_item;
+  const int rec = ((n * g.nsegs + seg) * g.nstrips + strip) * a.Ls + sc;   // record index in the whole batch: [item][seg][strip][scale]
 
   const int W = a.W, H = a.H;
   const size_t plane = (size_t)W * H;
   const int planei = W * H;   // io_shape_ok guarantees C * W * H < 2^31: plane offsets are 32-bit
   const int X0 = strip * STRIP_PX;
-  const int Y0 = seg * g.seg_rows, Y1 = min(Y0 + g.seg_rows, H);
+  const int Y0 = g.taper ? g.seg_y[seg] : seg * g.seg_rows, Y1 = g.taper ? g.seg_y[seg + 1] : min(Y0 + g.seg_rows, H);
   const int gx = X0 - 2 + lane;
   const bool colv = gx >= 0 && gx < W;                          // a real sample column
   const bool wcol = colv && lane >= 1 && lane <= 30;            // a window column of this strip

@@ -219,6 +219,31 @@ def test_forced_row_segments(debug_option):
         _compare(inp, ref, resn)
 
 
+@pytest.mark.parametrize("k", [2, 3, 6, 8])
+def test_tapered_row_segments(debug_option, k):
+    """Row segments of decreasing length, launched long ones first ("strip_taper"; what large launches get so that they end
+    evenly): the same result as one segment per strip, and the oracle's.  The launch order changes (items inside a segment
+    index instead of segments inside an item), the records' layout does not."""
+    import mdb200
+    from mdb200 import synth
+    inp = synth.make_loss_inputs(60, 136, 3, seed=23, automasking=True)
+    ref = P.oracle_train_loss(inp)
+    debug_option("strip_segs", 1)
+    res1, _ = _run_gpu(inp, auto=ref["auto"])
+    debug_option("strip_segs", 0)
+    debug_option("strip_taper", k)
+    resk, plan = _run_gpu(inp, auto=ref["auto"])
+    assert plan.strip_geometry()["segments"] == k
+    _compare(inp, ref, resk)
+    for a, b in zip(res1.d_disparities, resk.d_disparities):
+        assert torch.allclose(a, b, rtol=1e-5, atol=1e-9)
+    for a, b in zip(res1.d_poses, resk.d_poses):
+        assert torch.allclose(a.rvec, b.rvec, rtol=1e-4, atol=1e-9) and torch.allclose(a.tvec, b.tvec, rtol=1e-4, atol=1e-9)
+    debug_option("strip_taper", -1)
+    rese, plan_e = _run_gpu(inp, auto=ref["auto"])
+    _compare(inp, ref, rese)
+
+
 @pytest.mark.parametrize("W,H,N,scales", [
     (104, 64, 3, (0.125, 0.25, 0.5, 1.0)),   # KC = 1, several bands per scale
     (300, 37, 2, (0.25, 0.5, 1.0)),          # KC = 4, ragged columns, odd ratios (dh - 1 does not divide H - 1)
