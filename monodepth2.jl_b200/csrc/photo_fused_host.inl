@@ -480,6 +480,7 @@ inline StripGeom strip_geom(const mdb_loss_io* io, int num_sms) {
     const double wb = (double)base / resident;
     k_taper = wb >= 2.0 ? 3 : (wb >= 1.2 ? 4 : ((wb >= 0.55 && wb < 0.9) ? 6 : 0));
   }
+#if STRIP_TAPER
   if (k_taper >= 2 && k_taper <= STRIP_MAX_TAPER && io->H >= 16 * k_taper) {
     const int k = k_taper, tot = k * (k + 1) / 2;
     g.taper = 1; g.nsegs = k; g.seg_y[0] = 0;
@@ -490,6 +491,9 @@ inline StripGeom strip_geom(const mdb_loss_io* io, int num_sms) {
     }
     g.seg_rows = g.seg_y[1];
   }
+#else
+  (void)k_taper;
+#endif
   g.total = (int)(base * g.nsegs);
   return g;
 }
@@ -566,7 +570,9 @@ int32_t launch_fused(mdb_handle* h, const FusedArgs& fa, const FusedLayout& L, c
   for (int n0 = 0; n0 < fa.N; n0 += chunk) {
     const int items = std::min(chunk, fa.N - n0);
     g.n0 = n0;
+#if STRIP_TAPER || STRIP_TAPER_FIELDS
     g.items = items;
+#endif
     g.total = items * per_item;
     g.cbase = 0;
     const int blocks = (g.total + STRIP_WARPS - 1) / STRIP_WARPS;

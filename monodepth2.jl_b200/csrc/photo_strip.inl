@@ -60,6 +60,12 @@ constexpr int STRIP_NHEAD = 3;   // record head: photometric sum, smoothness x-s
                        // clamps, no stage gating): fewer instructions and one long basic block for ptxas to schedule
 #endif
 // ---- switches of recorded experiments (profiles/r2_strip_summary.md); the defaults are the shipped kernel -------------
+#ifndef STRIP_TAPER_FIELDS
+#define STRIP_TAPER_FIELDS 0
+#endif
+#ifndef STRIP_TAPER
+#define STRIP_TAPER 1      // experiment 20, shipped: tapered row segments (host side: strip_geom)
+#endif
 #ifndef STRIP_UNROLL
 #define STRIP_UNROLL 1     // experiment 19: 2 or 3 steady-state rows per loop trip
 #endif
@@ -159,11 +165,13 @@ struct StripGeom {
   int nstrips, nsegs, seg_rows, total;  // total = items * nsegs * nstrips * Ls warps of THIS launch
   int n0;                               // first item of this launch (a launch covers a chunk of the batch's items)
   int cbase;                            // first entry of this launch's region of c_pose
+#if STRIP_TAPER || STRIP_TAPER_FIELDS
   int items;                            // items of this launch
   // experiment 20 (test hook "strip_taper"): row segments of decreasing length, the long ones first in launch order, so that a
   // launch of only ~2 resident waves ends evenly; seg_y[] holds the boundaries.  0 = equal segments, item-major order.
   int taper;
   int seg_y[STRIP_MAX_TAPER + 1];
+#endif
 };
 
 // Decision dump (DBG instantiation only; tests/test_gpu_forced.py): every discrete choice the pullback
@@ -206,19 +214,35 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   const int lane = threadIdx.x & 31, warp = __shfl_sync(MDB_FULL, (int)(threadIdx.x >> 5), 0);
   int w = blockIdx.x * STRIP_WARPS + warp;
   if (w >= g.total) return;
+  const int w_lin = w;
   const int sc = w % a.Ls; w /= a.Ls;
   const int strip = w % g.nstrips; w /= g.nstrips;
   // launch order: scales, strips, then segments inside an item -- or, tapered, items inside a segment (long segments first)
-  const int seg = g.taper ? w / g.items : w % g.nsegs;
-  const int nl_item = g.taper ? w % g.items : w / g.nsegs;        // item inside this launch's chunk
+#if STRIP_TAPER
+  // ONE runtime division either way (a second one costs the 480-warp launch of config 1 two microseconds of prologue latency)
+  const int dv = g.taper ? g.items : g.nsegs, qd = w / dv, rd = w - qd * dv;
+  const int seg = g.taper ? qd : rd;
+  const int nl_item = g.taper ? rd : qd;        // item inside this launch's chunk
+#else
+  const int seg = w % g.nsegs, nl_item = w / g.nsegs;
+#endif
   const int n = g.n0 + nl_item;
-  const int rec = ((n * g.nsegs + seg) * g.nstrips + strip) * a.Ls + sc;   // record index in the whole batch: [item][seg][strip][scale]
+  // record index in the whole batch, layout [item][seg][strip][scale]: the launch order itself unless the segments are tapered
+#if STRIP_TAPER
+  const int rec = g.taper ? ((n * g.nsegs + seg) * g.nstrips + strip) * a.Ls + sc : g.n0 * (g.nsegs * g.nstrips * a.Ls) + w_lin;
+#else
+  const int rec = g.n0 * (g.nsegs * g.nstrips * a.Ls) + w_lin;
+#endif
 
   const int W = a.W, H = a.H;
   const size_t plane = (size_t)W * H;
   const int planei = W * H;   // io_shape_ok guarantees C * W * H < 2^31: plane offsets are 32-bit
   const int X0 = strip * STRIP_PX;
+#if STRIP_TAPER
   const int Y0 = g.taper ? g.seg_y[seg] : seg * g.seg_rows, Y1 = g.taper ? g.seg_y[seg + 1] : min(Y0 + g.seg_rows, H);
+#else
+  const int Y0 = seg * g.seg_rows, Y1 = min(Y0 + g.seg_rows, H);
+#endif
   const int gx = X0 - 2 + lane;
   const bool colv = gx >= 0 && gx < W;                          // a real sample column
   const bool wcol = colv && lane >= 1 && lane <= 30;            // a window column of this strip
