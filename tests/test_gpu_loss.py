@@ -219,6 +219,22 @@ def test_forced_row_segments(debug_option):
         _compare(inp, ref, resn)
 
 
+@pytest.mark.parametrize("taper", [-1, 3])
+def test_more_items_than_one_constant_bank_chunk(debug_option, taper):
+    """70 items: the throughput kernel takes its projection constants from the constant bank in chunks of 64 items (two
+    launches, two regions of the bank), with either launch order inside a chunk.  Against the oracle, item by item."""
+    from mdb200 import synth
+    inp = synth.make_loss_inputs(60, 48, 70, seed=29, scales=(0.5, 1.0))
+    ref = P.oracle_train_loss(inp)
+    debug_option("strip_taper", taper)
+    res, plan = _run_gpu(inp)
+    assert plan.strip_geometry()["segments"] == (3 if taper == 3 else plan.strip_geometry()["segments"])
+    _compare(inp, ref, res)
+    # a second call reuses the plan and cycles the bank's regions
+    res2, _ = _run_gpu(inp)
+    assert float(res2.loss) == float(res.loss)
+
+
 @pytest.mark.parametrize("k", [2, 3, 6, 8])
 def test_tapered_row_segments(debug_option, k):
     """Row segments of decreasing length, launched long ones first ("strip_taper"; what large launches get so that they end
