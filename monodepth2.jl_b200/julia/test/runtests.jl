@@ -9,6 +9,9 @@
 # Run from a checkout of jumerckx/Monodepth2.jl with `include("MDB200.jl")` added to src/Monodepth.jl:
 #   julia --project -e 'include("path/to/monodepth2.jl_b200/julia/test/runtests.jl")'
 using Test, CUDA, Zygote, LinearAlgebra, Random
+using FixedPointNumbers: N0f8
+using ImageCore: Gray, channelview
+using ImageTransformations: imresize
 using Monodepth
 const M = Monodepth
 CUDA.allowscalar(false)
@@ -117,6 +120,29 @@ end
     @test size(out) == (W, H, 3, B) && size(depth) == (W, H, 1, Np, B) && size(mask) == (W, H, 1, 1, B)
     g = Zygote.gradient(s -> sum(M.render_tgt_rgb_depth(rgb, s, disparity, xyz_tgt, pose, K_inv, K)[1]), sigma)[1]
     @test size(g) == size(sigma) && all(isfinite, Array(g))
+end
+
+@testset "dataset ingestion on the device" begin
+    # Depth10k (src/dtk.jl:29-46): the decoder's row-major RGB raster of a triplet image, (3, 3W, H, N) in Julia's order
+    W, H, N = 20, 12, 2
+    strips = rand(UInt8, 3, 3W, H, N)
+    x = M.MDB200.depth10k_batch(cu(strips))
+    @test size(x) == (W, H, 3, 3, N)
+    ref = [Float32(reinterpret(N0f8, strips[c, (l - 1) * W + w, h, n])) for w in 1:W, h in 1:H, c in 1:3, l in 1:3, n in 1:N]
+    @test Array(x) == ref                                   # Float32(::N0f8), bit for bit
+    xu = M.MDB200.depth10k_batch_u8(cu(strips))
+    @test eltype(xu) == UInt8 && Float32.(reinterpret.(N0f8, Array(xu))) == ref
+    flips = cu(UInt8[1, 0])
+    xf = M.MDB200.depth10k_batch(cu(strips); flips = flips)
+    @test Array(xf)[:, :, :, :, 1] == ref[end:-1:1, :, :, :, 1] && Array(xf)[:, :, :, :, 2] == ref[:, :, :, :, 2]
+    # KittyDataset (src/kitty.jl:45-61): three gray frames per sample, imresize + Float32 on the device
+    Wo, Ho = 62, 19
+    frames = rand(UInt8, Wo, Ho, 3, N)
+    xk = M.MDB200.kitti_batch(cu(frames), W, H)
+    @test size(xk) == (W, H, 1, 3, N)
+    img = reinterpret.(Gray{N0f8}, permutedims(frames[:, :, 2, 1], (2, 1)))              # what `load` returns: (rows, cols)
+    want = permutedims(Float32.(channelview(imresize(img, (H, W)))), (2, 1))
+    @test Array(xk)[:, :, 1, 2, 1] == want                  # pins the restatement of ImageTransformations.imresize
 end
 
 end
