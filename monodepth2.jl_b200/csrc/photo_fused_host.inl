@@ -7,6 +7,7 @@ namespace {
 int g_dbg_strip_segs = 0;       // force this many row segments per strip
 int g_dbg_upsample_split = 0;   // force the two-kernel V / H transpose (the W > 4096 path)
 int g_dbg_strip_taper = 0;      // experiment 20: this many row segments of linearly decreasing length, long ones first
+int g_dbg_strip_taper_pow10 = 20;   // lengths ~ (k - i)^(pow10 / 10): 20 = quadratic (shipped), measured 5 .. 40
 signed char* g_dbg_decisions = nullptr;   // device buffer [Ls][N][2C+2][H][W]: run the DBG instantiation and dump into it
 
 // ---------------------------------------------------------------------------------------
@@ -469,11 +470,13 @@ inline StripGeom strip_geom(const mdb_loss_io* io, int num_sms) {
   }
   g.seg_rows = (io->H + best_n - 1) / best_n;
   g.nsegs = (io->H + g.seg_rows - 1) / g.seg_rows;
-  // Tapered segments (round 2, experiment 20): lengths proportional to k, k-1, ..., 1, launched long ones first, so that the
+  // Tapered segments (round 2, experiment 20): lengths proportional to k^2, (k-1)^2, ..., 1, launched long ones first, so that the
   // launch ends evenly instead of with a tail of full-length warps.  Measured at 1024x320 with L2 flushed (tools/sweep_taper.py,
   // fused kernel ms, equal -> tapered): 8 items 0.585 -> 0.569 (k = 6), 16: 1.106 -> 1.082 (k = 4), 32: 2.138 -> 2.099 (k = 3),
   // 64: 4.207 -> 4.144 (k = 3); 12 items (exactly one resident wave of whole-height warps) and <= 4 items are better off
-  // with equal segments.  k by the number of resident waves ONE segment index fills.  "strip_taper" = -1 switches it off.
+  // with equal segments.  Those figures are for LINEAR lengths; quadratic ones (tools/sweep_taper_shape.py) take another 2.3 % at
+  // 8 items (0.567 -> 0.554), 3 % at 16, 0.2 % at 64.  k by the number of resident waves ONE segment index fills.
+  // "strip_taper" = -1 switches it off.
   int k_taper = 0;
   if (g_dbg_strip_taper >= 2) k_taper = g_dbg_strip_taper;
   else if (g_dbg_strip_taper == 0 && g_dbg_strip_segs == 0) {
@@ -482,12 +485,14 @@ inline StripGeom strip_geom(const mdb_loss_io* io, int num_sms) {
   }
 #if STRIP_TAPER
   if (k_taper >= 2 && k_taper <= STRIP_MAX_TAPER && io->H >= 16 * k_taper) {
-    const int k = k_taper, tot = k * (k + 1) / 2;
+    const int k = k_taper;
+    const double pw = g_dbg_strip_taper_pow10 / 10.0;
+    double tot = 0.0, acc = 0.0;
+    for (int i = 0; i < k; ++i) tot += std::pow((double)(k - i), pw);
     g.taper = 1; g.nsegs = k; g.seg_y[0] = 0;
-    int acc = 0;
     for (int i = 0; i < k; ++i) {
-      acc += k - i;
-      g.seg_y[i + 1] = (i == k - 1) ? io->H : std::max(g.seg_y[i] + 4, (int)((long long)io->H * acc / tot));
+      acc += std::pow((double)(k - i), pw);
+      g.seg_y[i + 1] = (i == k - 1) ? io->H : std::min(io->H - 4 * (k - 1 - i), std::max(g.seg_y[i] + 4, (int)(io->H * acc / tot)));
     }
     g.seg_rows = g.seg_y[1];
   }
@@ -617,6 +622,7 @@ int32_t mdb_debug_option(const char* name, int64_t value) {
   else if (!strcmp(name, "decision_dump")) g_dbg_decisions = (signed char*)(intptr_t)value;
   else if (!strcmp(name, "render_precise")) mdb_dbg_render_precise = (int)value;
   else if (!strcmp(name, "strip_taper")) g_dbg_strip_taper = (int)value;
+  else if (!strcmp(name, "strip_taper_pow10")) g_dbg_strip_taper_pow10 = value > 0 ? (int)value : 20;
   else return MDB_E_INVALID_ARG;
   return MDB_OK;
 }

@@ -204,7 +204,7 @@ def test_julia_ccalls_name_exported_symbols_with_the_right_arity():
 
 def test_strip_geometry_choices_need_no_gpu():
     """mdb_train_loss_strip_geometry is host arithmetic: the launch decomposition the docs quote.  Config 5 (64 x 1024x320, 4
-    scales): 37 strips, three tapered segments (the first 160 rows), 28 416 warps; 8 items (one rank of the 8-GPU run): six
+    scales): 37 strips, three tapered segments (205, 92 and 23 rows), 28 416 warps; 8 items (one rank of the 8-GPU run): six
     tapered segments; 12 items at 1024x320 fill exactly one resident wave with whole-height warps: one segment; config 1
     (1 x 416x128, 1 scale): 32 four-row segments so that one wave fills the machine."""
     import mdb200._lib as L
@@ -218,7 +218,7 @@ def test_strip_geometry_choices_need_no_gpu():
         assert L.lib.mdb_train_loss_strip_geometry(ctypes.byref(io), out) == 0
         return list(out)
 
-    assert geo(1024, 320, 64, 4) == [37, 3, 160, 64 * 4 * 37 * 3]
+    assert geo(1024, 320, 64, 4) == [37, 3, 205, 64 * 4 * 37 * 3]
     assert geo(1024, 320, 8, 4)[:2] == [37, 6]
     assert geo(1024, 320, 12, 4) == [37, 1, 320, 12 * 4 * 37]
     assert geo(416, 128, 1, 1) == [15, 32, 4, 480]
