@@ -554,7 +554,8 @@ PosePool* pose_pool(int device) {
 
 template <int C, int S>
 int32_t launch_fused(mdb_handle* h, const FusedArgs& fa, const FusedLayout& L, cudaStream_t st) {
-  constexpr size_t smem = (size_t)3 * (S * (2 * C + 2) / 4) * STRIP_THREADS * sizeof(float4);
+  constexpr size_t smem = ((size_t)3 * (S * (2 * C + 2) / 4) + (STRIP_SMEM_RING ? 2 * ((C * S + 3) / 4) + 2 * ((3 * C + 3) / 4) : 0)) *
+                          STRIP_THREADS * sizeof(float4);
   StripGeom g = L.strip;
   const int per_item = g.nsegs * g.nstrips * fa.Ls;
 #if STRIP_CONSTPOSE

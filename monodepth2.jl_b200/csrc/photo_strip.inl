@@ -81,6 +81,10 @@ constexpr int STRIP_NHEAD = 3;   // record head: photometric sum, smoothness x-s
 #ifndef STRIP_PEEL_CAPTURED
 #define STRIP_PEEL_CAPTURED 0
 #endif
+#ifndef STRIP_SMEM_RING
+#define STRIP_SMEM_RING 0  // experiment 21: the two-row rings of the warped samples and of the pullback coefficients (30 registers that
+                           // only cross rows) parked in thread-private shared memory, to run more warps per SM at a lower register cap
+#endif
 #ifndef STRIP_MAXREG_CAPTURED
 #define STRIP_MAXREG_CAPTURED 216   // spill-free; config 1 per iteration: 152 (24 B spilled) 23.95 us, 184 (16 B) 24.18, 216 (0 B) 22.58;
                                     // peeled copy at 160 / 200: 23.94 / 24.62.  Occupancy is no concern at 480 warps.
@@ -208,6 +212,10 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   constexpr int DRV = S * (2 * C + 2);  // floats parked per (thread, row): dx/du, dx/dv per channel, u, v
   constexpr int DRV4 = DRV / 4;
   extern __shared__ float4 s_drv[];     // [3 rows][DRV4][STRIP_THREADS]
+  constexpr bool SR = (STRIP_SMEM_RING != 0) && CP && !DBG;
+  constexpr int NX4 = (C * S + 3) / 4, NF4 = (3 * C + 3) / 4;
+  float4* const s_rx = s_drv + 3 * DRV4 * STRIP_THREADS;   // SR: [2 rows][NX4][STRIP_THREADS] warped samples
+  float4* const s_rf = s_rx + 2 * NX4 * STRIP_THREADS;     // SR: [2 rows][NF4][STRIP_THREADS] pullback coefficients
 
   // the shuffle makes the warp index provably warp-uniform, so every branch on the strip geometry
   // below is uniform for the compiler and the row shuffles need no WARPSYNC
@@ -398,6 +406,13 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   for (int i = 0; i < 3; ++i) { S0[i] = P(0.0f); SP[i] = P(0.0f); SI[i] = P(0.0f); }
 
   int slot = 0;  // ring slot of row r in s_drv
+  int par = 0;   // SR: slot of row r (and, until it is overwritten, of row r-2) in s_rx / s_rf
+  if (SR) {
+#pragma unroll
+    for (int k = 0; k < 2 * NX4; ++k) s_rx[k * STRIP_THREADS + threadIdx.x] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+#pragma unroll
+    for (int k = 0; k < 2 * NF4; ++k) s_rf[k * STRIP_THREADS + threadIdx.x] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+  }
 
   // ---- stage A in two halves: issue() starts the row's loads, consume() runs after the smoothness block ----
   // in flight between issue() and consume(): 4 taps x C channels (sources packed), the target row,
@@ -597,9 +612,15 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
   // ---- rotate the rings: row r becomes row r-1 ... ---------------------------------------------
   auto rotate = [&]() {
 #pragma unroll
-    for (int c = 0; c < C; ++c) { xr2[c] = xr1[c]; xr1[c] = xn[c]; yr2[c] = yr1[c]; yr1[c] = yn[c]; }
+    for (int c = 0; c < C; ++c) {
+      if (!SR) { xr2[c] = xr1[c]; xr1[c] = xn[c]; }
+      yr2[c] = yr1[c]; yr1[c] = yn[c];
+    }
+    if (!SR) {
 #pragma unroll
-    for (int k = 0; k < 3 * C; ++k) { F2[k] = F1[k]; F1[k] = Fn[k]; }
+      for (int k = 0; k < 3 * C; ++k) { F2[k] = F1[k]; F1[k] = Fn[k]; }
+    }
+    par ^= 1;
     sel2 = sel1; sel1 = seln;
     d3 = d2; d2 = d1; d1 = dn;
     slot = (slot + 1) % 3;
@@ -645,6 +666,25 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
       }
     }
     consume(r, slot, xn, yn, dn);
+    if (SR) {   // rows r-1 and r-2 come back from shared memory, row r takes row r-2's place
+      float4* const o1 = s_rx + ((par ^ 1) * NX4) * STRIP_THREADS + threadIdx.x;
+      float4* const o2 = s_rx + (par * NX4) * STRIP_THREADS + threadIdx.x;
+      float t1[4 * NX4], t2[4 * NX4], tn[4 * NX4];
+#pragma unroll
+      for (int k = 0; k < NX4; ++k) {
+        const float4 q1 = o1[k * STRIP_THREADS], q2 = o2[k * STRIP_THREADS];
+        t1[4 * k] = q1.x; t1[4 * k + 1] = q1.y; t1[4 * k + 2] = q1.z; t1[4 * k + 3] = q1.w;
+        t2[4 * k] = q2.x; t2[4 * k + 1] = q2.y; t2[4 * k + 2] = q2.z; t2[4 * k + 3] = q2.w;
+      }
+#pragma unroll
+      for (int k = 0; k < 4 * NX4; ++k) tn[k] = 0.0f;
+#pragma unroll
+      for (int c = 0; c < C; ++c)
+#pragma unroll
+        for (int s = 0; s < S; ++s) { xr1[c].set(s, t1[c * S + s]); xr2[c].set(s, t2[c * S + s]); tn[c * S + s] = xn[c].get(s); }
+#pragma unroll
+      for (int k = 0; k < NX4; ++k) o2[k * STRIP_THREADS] = make_float4(tn[4 * k], tn[4 * k + 1], tn[4 * k + 2], tn[4 * k + 3]);
+    }
     if (ST && STRIP_FENCE >= 1) asm volatile("bar.warp.sync 0xffffffff;" ::: "memory");
 
     // =========================== C: window row r-1 =============================================
@@ -762,6 +802,23 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
 
     if (ST && STRIP_FENCE >= 2) asm volatile("bar.warp.sync 0xffffffff;" ::: "memory");
     // =========================== D: pixel row r-2 ==============================================
+    if (SR) {
+      float4* const o1 = s_rf + ((par ^ 1) * NF4) * STRIP_THREADS + threadIdx.x;
+      float4* const o2 = s_rf + (par * NF4) * STRIP_THREADS + threadIdx.x;
+      float t1[4 * NF4], t2[4 * NF4], tn[4 * NF4];
+#pragma unroll
+      for (int k = 0; k < NF4; ++k) {
+        const float4 q1 = o1[k * STRIP_THREADS], q2 = o2[k * STRIP_THREADS];
+        t1[4 * k] = q1.x; t1[4 * k + 1] = q1.y; t1[4 * k + 2] = q1.z; t1[4 * k + 3] = q1.w;
+        t2[4 * k] = q2.x; t2[4 * k + 1] = q2.y; t2[4 * k + 2] = q2.z; t2[4 * k + 3] = q2.w;
+      }
+#pragma unroll
+      for (int k = 0; k < 4 * NF4; ++k) tn[k] = 0.0f;
+#pragma unroll
+      for (int k = 0; k < 3 * C; ++k) { F1[k] = t1[k]; F2[k] = t2[k]; tn[k] = Fn[k]; }
+#pragma unroll
+      for (int k = 0; k < NF4; ++k) o2[k * STRIP_THREADS] = make_float4(tn[4 * k], tn[4 * k + 1], tn[4 * k + 2], tn[4 * k + 3]);
+    }
     if (ST || r >= Y0 + 2) {  // warp-uniform; pr in [Y0, Y1)
       // box sums of the coefficient fields over the 3x3 windows containing this pixel, per source
       const float wu = (!ST && pr == 1) ? 2.0f : 1.0f, wd = (!ST && pr == H - 2) ? 2.0f : 1.0f;
