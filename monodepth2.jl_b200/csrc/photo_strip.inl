@@ -81,6 +81,14 @@ constexpr int STRIP_NHEAD = 3;   // record head: photometric sum, smoothness x-s
 #ifndef STRIP_PEEL_CAPTURED
 #define STRIP_PEEL_CAPTURED 0
 #endif
+#ifndef STRIP_PF
+#define STRIP_PF 0         // experiment 22: prefetch of the source row the NEXT target row's bottom taps will read (1: into L1, 2: into
+                           // L2; +4: the next target row as well), steady-state rows only
+#endif
+#ifndef STRIP_ROTATE
+#define STRIP_ROTATE 0     // experiment 23: the row loop rotated by half a row -- the NEXT row's loads are issued between stages C and D, so
+                           // that stage D and the next row's smoothness block run in their shadow (today: the smoothness block alone)
+#endif
 #ifndef STRIP_SMEM_RING
 #define STRIP_SMEM_RING 0  // experiment 21: the two-row rings of the warped samples and of the pullback coefficients (30 registers that
                            // only cross rows) parked in thread-private shared memory, to run more warps per SM at a lower register cap
@@ -142,6 +150,8 @@ MDB_DEV float sgn1(float v) { return v == 0.0f ? 0.0f : copysignf(1.0f, v); }
 // frame samples: Float32 as stored, or N0f8 bytes carried as 2^23 + u until first use (see the kernel's U8 parameter)
 MDB_DEV float ldx(const float* p) { return ldg(p); }
 MDB_DEV float ldx(const unsigned char* p) { return __uint_as_float(0x4B000000u | (unsigned)__ldg(p)); }
+MDB_DEV void pf_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+MDB_DEV void pf_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 constexpr float N0F8_R1 = 0.003921568859368562698f;      // fl(1 / 255)
 constexpr float N0F8_R2 = -2.3191758e-10f;               // fl(1 / 255 - r1)
 template <bool U8> MDB_DEV float cvx(float g) {
@@ -480,11 +490,23 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
 #endif
 #pragma unroll
       for (int c = 0; c < C; ++c) ty_[c] = ldx(xb + (unsigned)(tgt_off + c * planei + rc * W + gxc));
+#if STRIP_PF & 4
+      if (ST) {
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+          if ((STRIP_PF & 3) == 1) pf_l1(xb + (unsigned)(tgt_off + c * planei + (rc + 1) * W + gxc));
+          else pf_l2(xb + (unsigned)(tgt_off + c * planei + (rc + 1) * W + gxc));
+        }
+      }
+#endif
 #if STRIP_AM_EARLY
       if (a.automask) tam = ldg(amb + (unsigned)((ST ? r - 1 : min(max(r - 1, 0), H - 1)) * W + gxc));   // window row r-1, used in stage C
 #endif
 
       unsigned ot[S];   // top-left tap; the other three are +1, +W, +W+1 (x0 <= W-2, y0 <= H-2 always)
+#if STRIP_PF & 3
+      unsigned opf[S];
+#endif
 #pragma unroll
       for (int s = 0; s < S; ++s) {
         // Backproject -> Project -> normalize -> grid_sample's unnormalize (src/utils.jl:67-69,
@@ -505,6 +527,9 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
         if (!ry) fys = iy < 0 ? 0.0f : 1.0f;
         ix = min(max(ix, 0), W - 2);
         iy = min(max(iy, 0), H - 2);
+#if STRIP_PF & 3
+        if (ST) opf[s] = (unsigned)(min(iy + 2, H - 1) * W + ix) + src_off[s];   // iy already clamped to [0, H-2]
+#endif
         ot[s] = (unsigned)(iy * W + ix) + src_off[s];
         const float zf = (float)zi;
         tfx.set(s, fxs); tfy.set(s, fys);
@@ -529,6 +554,11 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
           const XT* pb = xbc[c] + ob[s];
           tv00[c].set(s, ldx(p)); tv01[c].set(s, ldx(p + 1));
           tv10[c].set(s, ldx(pb)); tv11[c].set(s, ldx(pb + 1));
+#if STRIP_PF & 3
+          if (ST) {
+            if ((STRIP_PF & 3) == 1) pf_l1(xbc[c] + opf[s]); else pf_l2(xbc[c] + opf[s]);
+          }
+#endif
         }
       }
 #else
@@ -632,7 +662,9 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
     // (STRIP_NWARPS = 4, Ls = 4: the warps of a CTA are the four scales of one strip segment and walk the same rows)
     asm volatile("bar.sync 1, %0;" ::"n"(STRIP_THREADS) : "memory");
 #endif
+#if !STRIP_ROTATE
     issue(r, steady);
+#endif
     // ---- smoothness of pixel row r-2 (src/utils.jl:163-177): needs nothing of row r, so it runs in the
     // shadow of the loads just issued; one register (its pullback) crosses stages C and D
     const int pr = r - 2;
@@ -801,6 +833,9 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
     }
 
     if (ST && STRIP_FENCE >= 2) asm volatile("bar.warp.sync 0xffffffff;" ::: "memory");
+#if STRIP_ROTATE
+    issue(r + 1, steady);   // steady rows end one row earlier under this switch, so that row r + 1 is a steady row for issue() too
+#endif
     // =========================== D: pixel row r-2 ==============================================
     if (SR) {
       float4* const o1 = s_rf + ((par ^ 1) * NF4) * STRIP_THREADS + threadIdx.x;
@@ -891,8 +926,11 @@ photo_strip_kernel(const __grid_constant__ FusedArgs a, const StripGeom g) {
     if (tma_ok) { tma_issue(Y0 - 2); tma_issue(Y0 - 1); }
 #endif
     constexpr bool PEEL = STRIP_PEEL && (CP || DBG || STRIP_PEEL_CAPTURED);
-    const int s_lo = max(Y0 + 2, 4), s_hi = PEEL ? min(Y1, H - 2) : -1000000;
+    const int s_lo = max(Y0 + 2, 4), s_hi = PEEL ? min(Y1, H - 2 - STRIP_ROTATE) : -1000000;
     int r = Y0 - 2;
+#if STRIP_ROTATE
+    issue(r, std::false_type{});
+#endif
     while (r <= Y1 + 1) {
       if (PEEL && r >= s_lo && r <= s_hi) {
 #if STRIP_UNROLL == 3
