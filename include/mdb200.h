@@ -82,6 +82,8 @@ int32_t mdb_measure_fp32_peak(mdb_handle* h, void* scratch, size_t scratch_bytes
  * "render_precise" = 1 makes the render forward sample every plane through the double-precision homography.
  * "strip_taper" = k (2..8) forces k row segments of decreasing length (long ones launched first), -1 forces equal segments,
  * 0 = the library's choice; "strip_taper_pow10" = 10 p makes those lengths proportional to (k - i)^p (0 = shipped: p = 2).
+ * "strip_seg_dump" = HOST pointer to 10 int32 (0 = off): mdb_train_loss_strip_geometry also writes { tapered?, the 9 row
+ * boundaries } there (tests of the host-side segment rule; needs no GPU).
  * Set BEFORE mdb_train_loss_workspace_bytes (the record count depends on the segments).                       */
 int32_t mdb_debug_option(const char* name, int64_t value);
 

@@ -7,6 +7,7 @@ namespace {
 int g_dbg_strip_segs = 0;       // force this many row segments per strip
 int g_dbg_upsample_split = 0;   // force the two-kernel V / H transpose (the W > 4096 path)
 int g_dbg_strip_taper = 0;      // experiment 20: this many row segments of linearly decreasing length, long ones first
+int32_t* g_dbg_strip_seg_dump = nullptr;   // tests: mdb_train_loss_strip_geometry also writes { taper, seg_y[0 .. 8] } here (host memory)
 int g_dbg_strip_taper_pow10 = 20;   // lengths ~ (k - i)^(pow10 / 10): 20 = quadratic (shipped), measured 5 .. 40
 signed char* g_dbg_decisions = nullptr;   // device buffer [Ls][N][2C+2][H][W]: run the DBG instantiation and dump into it
 
@@ -623,6 +624,7 @@ int32_t mdb_debug_option(const char* name, int64_t value) {
   else if (!strcmp(name, "decision_dump")) g_dbg_decisions = (signed char*)(intptr_t)value;
   else if (!strcmp(name, "render_precise")) mdb_dbg_render_precise = (int)value;
   else if (!strcmp(name, "strip_taper")) g_dbg_strip_taper = (int)value;
+  else if (!strcmp(name, "strip_seg_dump")) g_dbg_strip_seg_dump = reinterpret_cast<int32_t*>((uintptr_t)value);
   else if (!strcmp(name, "strip_taper_pow10")) g_dbg_strip_taper_pow10 = value > 0 ? (int)value : 20;
   else return MDB_E_INVALID_ARG;
   return MDB_OK;
@@ -634,6 +636,10 @@ int32_t mdb_train_loss_strip_geometry(const mdb_loss_io* io, int32_t* out4) {
   if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const StripGeom g = strip_geom(io, sms);
   out4[0] = g.nstrips; out4[1] = g.nsegs; out4[2] = g.seg_rows; out4[3] = g.total;
+  if (g_dbg_strip_seg_dump) {
+    g_dbg_strip_seg_dump[0] = g.taper;
+    for (int i = 0; i <= STRIP_MAX_TAPER; ++i) g_dbg_strip_seg_dump[1 + i] = g.taper ? g.seg_y[i] : 0;
+  }
   return MDB_OK;
 }
 

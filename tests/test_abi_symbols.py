@@ -223,3 +223,49 @@ def test_strip_geometry_choices_need_no_gpu():
     assert geo(1024, 320, 12, 4) == [37, 1, 320, 12 * 4 * 37]
     assert geo(416, 128, 1, 1) == [15, 32, 4, 480]
     assert geo(640, 192, 32, 4)[:2] == [23, 4]          # config 3: 1.66 resident waves per segment index
+
+
+def test_tapered_segment_boundaries_are_well_formed():
+    """The host-side rule that cuts an image into tapered row segments (strip_geom, csrc/photo_fused_host.inl), read back
+    through the "strip_seg_dump" test hook: for every forced count k, every exponent and a range of heights the boundaries
+    start at 0, end at H, every segment has at least four rows (the kernel's halo is two rows on either side), and the
+    segments never grow (long ones are launched first).  Where the image is too short for k segments (H < 16 k) the rule
+    falls back to equal segments."""
+    import mdb200._lib as L
+    dump = (ctypes.c_int32 * 10)()
+    L.lib.mdb_debug_option(b"strip_seg_dump", ctypes.addressof(dump))
+    try:
+        for H in (32, 37, 64, 100, 128, 192, 320, 375, 1080):
+            for k in range(2, 9):
+                for pow10 in (5, 10, 20, 40):
+                    L.lib.mdb_debug_option(b"strip_taper", k)
+                    L.lib.mdb_debug_option(b"strip_taper_pow10", pow10)
+                    io = L.LossIO()
+                    io.W, io.H, io.C, io.L, io.N, io.S, io.Ls = 416, H, 3, 3, 5, 2, 1
+                    io.dw[0], io.dh[0] = 416, H
+                    out = (ctypes.c_int32 * 4)()
+                    assert L.lib.mdb_train_loss_strip_geometry(ctypes.byref(io), out) == 0
+                    if H < 16 * k:
+                        assert dump[0] == 0, (H, k)
+                        continue
+                    assert dump[0] == 1 and out[1] == k, (H, k, pow10)
+                    y = [dump[1 + i] for i in range(k + 1)]
+                    assert y[0] == 0 and y[k] == H, (H, k, pow10, y)
+                    rows = [b - a for a, b in zip(y, y[1:])]
+                    assert min(rows) >= 4, (H, k, pow10, y)
+                    assert all(a >= b for a, b in zip(rows, rows[1:])), (H, k, pow10, y)
+                    assert out[2] == rows[0] and out[3] == 5 * 15 * k
+        # the shipped exponent at config 5: 205 / 92 / 23 rows
+        L.lib.mdb_debug_option(b"strip_taper", 0)
+        L.lib.mdb_debug_option(b"strip_taper_pow10", 0)
+        io = L.LossIO()
+        io.W, io.H, io.C, io.L, io.N, io.S, io.Ls = 1024, 320, 3, 3, 64, 2, 4
+        for s in range(4):
+            io.dw[s], io.dh[s] = 1024 >> (3 - s), 320 >> (3 - s)
+        out = (ctypes.c_int32 * 4)()
+        assert L.lib.mdb_train_loss_strip_geometry(ctypes.byref(io), out) == 0
+        assert [dump[i] for i in range(5)] == [1, 0, 205, 297, 320]
+    finally:
+        L.lib.mdb_debug_option(b"strip_taper", 0)
+        L.lib.mdb_debug_option(b"strip_taper_pow10", 0)
+        L.lib.mdb_debug_option(b"strip_seg_dump", 0)
