@@ -298,3 +298,114 @@ peers_attach(handles::Vector{UInt8}, rank::Integer) =
 allreduce_loss_posegrad!(recv::CuArray{Float32,1}, send::CuArray{Float32,1}) = (GC.@preserve send recv check(ccall(
     (:mdb_allreduce_loss_posegrad, libmdb200), Int32, (Ptr{Cvoid}, CuPtr{Cfloat}, CuPtr{Cfloat}, Int64, Ptr{Cvoid}),
     handle(), send, recv, length(send), stream_ptr())); recv)
+
+# ---- SURVEY 8(f) rank 4: the operators either side of the loss, on the network's side ----------------------------------------
+"""
+    pose_head(conv_out; scale = 1f-2) -> Pose
+
+The tail of `(decoder::PoseDecoder)(features)` (src/pose_decoder.jl:29-31): `conv_out (w,h,6,N)` is `decoder.pose(squeezed)`;
+spatial mean, `× 1e-2`, split into `Pose(rvec (3,N), tvec (3,1,N))`.  A maintainer replaces those three lines with
+`pose_head(decoder.pose(squeezed))`; the rrule below carries the loss path's pose gradients back to the conv output.
+"""
+function pose_head(conv_out::CuArray{Float32,4}; scale::Real = 1f-2)
+    w, h, c, N = size(conv_out)
+    c == 6 || error("pose_head: expected 6 channels, got $c")
+    rvec = CUDA.zeros(Float32, 3, N); tvec = CUDA.zeros(Float32, 3, 1, N)
+    GC.@preserve conv_out rvec tvec check(ccall((:mdb_pose_head, libmdb200), Int32,
+        (Ptr{Cvoid}, CuPtr{Cfloat}, Int32, Int32, Int32, Cfloat, CuPtr{Cfloat}, CuPtr{Cfloat}, Ptr{Cvoid}),
+        handle(), conv_out, w, h, N, Cfloat(scale), rvec, tvec, stream_ptr()))
+    Pose(rvec, tvec)
+end
+
+function ChainRulesCore.rrule(::typeof(pose_head), conv_out::CuArray{Float32,4}; scale::Real = 1f-2)
+    w, h, _, N = size(conv_out)
+    function pose_head_pullback(Δ)
+        Δ = unthunk(Δ)
+        d_r = zeros_or(Δ.rvec, CUDA.zeros(Float32, 3, N)); d_t = zeros_or(Δ.tvec, CUDA.zeros(Float32, 3, 1, N))
+        d_conv = similar(conv_out)
+        GC.@preserve d_r d_t d_conv check(ccall((:mdb_pose_head_bwd, libmdb200), Int32,
+            (Ptr{Cvoid}, CuPtr{Cfloat}, CuPtr{Cfloat}, Int32, Int32, Int32, Cfloat, CuPtr{Cfloat}, Ptr{Cvoid}),
+            handle(), d_r, d_t, w, h, N, Cfloat(scale), d_conv, stream_ptr()))
+        NoTangent(), d_conv
+    end
+    pose_head(conv_out; scale), pose_head_pullback
+end
+
+"""
+    disparity_heads(logits::Vector) -> Vector
+
+The `σ` that ends every scale level of the DepthDecoder (`Conv((3,3), ch => 1, σ)`, src/depth_decoder.jl:46), for all levels
+in one launch: `logits[k] (w_k,h_k,1,N)` are the convolutions' pre-activations (build the decoder's last `Conv` with
+`identity`), the result is the `disparities` vector `train_loss` consumes (src/training.jl:27,41-46).
+"""
+function disparity_heads(logits::Vector{<:CuArray{Float32,4}})
+    Ls = length(logits); N = size(logits[1], 4)
+    outs = [similar(l) for l in logits]
+    dw = Int32[size(l, 1) for l in logits]; dh = Int32[size(l, 2) for l in logits]
+    lp = map(pointer, logits); op = map(pointer, outs)
+    GC.@preserve logits outs lp op dw dh check(ccall((:mdb_disparity_heads, libmdb200), Int32,
+        (Ptr{Cvoid}, Ptr{CuPtr{Cfloat}}, Ptr{Int32}, Ptr{Int32}, Int32, Int32, Ptr{CuPtr{Cfloat}}, Ptr{Cvoid}),
+        handle(), lp, dw, dh, Ls, N, op, stream_ptr()))
+    outs
+end
+
+function ChainRulesCore.rrule(::typeof(disparity_heads), logits::Vector{<:CuArray{Float32,4}})
+    disp = disparity_heads(logits)
+    function disparity_heads_pullback(Δ)
+        Δ = unthunk(Δ)
+        Ls = length(disp); N = size(disp[1], 4)
+        g = [zeros_or(Δ[k], disp[k]) for k in 1:Ls]
+        d_logits = [similar(d) for d in disp]
+        dw = Int32[size(d, 1) for d in disp]; dh = Int32[size(d, 2) for d in disp]
+        dp = map(pointer, disp); gp = map(pointer, g); lp = map(pointer, d_logits)
+        GC.@preserve disp g d_logits dp gp lp dw dh check(ccall((:mdb_disparity_heads_bwd, libmdb200), Int32,
+            (Ptr{Cvoid}, Ptr{CuPtr{Cfloat}}, Ptr{CuPtr{Cfloat}}, Ptr{Int32}, Ptr{Int32}, Int32, Int32, Ptr{CuPtr{Cfloat}}, Ptr{Cvoid}),
+            handle(), dp, gp, dw, dh, Ls, N, lp, stream_ptr()))
+        NoTangent(), d_logits
+    end
+    disp, disparity_heads_pullback
+end
+
+"""
+    item_mean(map) -> Vector{Float32} (host), one mean per item (the last dimension), summed in a fixed order.
+"""
+function item_mean(map::CuArray{Float32})
+    N = size(map, ndims(map)); per = length(map) ÷ N
+    out = CUDA.zeros(Float32, N)
+    GC.@preserve map out check(ccall((:mdb_item_mean, libmdb200), Int32,
+        (Ptr{Cvoid}, CuPtr{Cfloat}, Int64, Int32, CuPtr{Cfloat}, Ptr{Cvoid}), handle(), map, Int64(per), N, out, stream_ptr()))
+    Array(out)
+end
+
+"""
+    static_scores(ssim, x, target_id; source_ids) -> Vector{Float32}
+
+`find_static`'s statistic (src/dtk.jl:51-69) for a whole batch at once: `mean(automasking_loss(ssim, x, target; source_ids))`
+per item of `x (W,H,C,L,N)`; the dataset filter keeps the files whose score exceeds `α`.
+"""
+function static_scores(ssim::SSIM, x::CuArray{Float32,5}, target_id::Integer; source_ids)
+    item_mean(automasking_loss(ssim, x, x[:, :, :, target_id, :]; source_ids))
+end
+
+"""
+    grid_sample_border(input (W,H,C,N), grid (2,Wo,Ho,N)) -> (Wo,Ho,C,N)
+
+`NNlib.grid_sample(input, grid; padding_mode=:border)` with NNlib's align-corners convention, as both call sites use it
+(src/training.jl:56, src/render.jl:88).  Not a method of `NNlib.grid_sample`: the glue does not pirate NNlib's function.
+"""
+function grid_sample_border(input::CuArray{Float32,4}, grid::CuArray{Float32,4})
+    W, H, C, N = size(input); _, Wo, Ho, _ = size(grid)
+    out = CUDA.zeros(Float32, Wo, Ho, C, N)
+    GC.@preserve input grid out check(ccall((:mdb_grid_sample, libmdb200), Int32,
+        (Ptr{Cvoid}, CuPtr{Cfloat}, CuPtr{Cfloat}, Int32, Int32, Int32, Int32, Int32, Int32, CuPtr{Cfloat}, Ptr{Cvoid}),
+        handle(), input, grid, W, H, C, N, Wo, Ho, out, stream_ptr()))
+    out
+end
+
+"release the library's per-process state (events, workspaces, the communicator); the next call creates it again"
+function destroy()
+    HANDLE[] == C_NULL && return nothing
+    ccall((:mdb_destroy, libmdb200), Int32, (Ptr{Cvoid},), HANDLE[])
+    HANDLE[] = C_NULL
+    nothing
+end

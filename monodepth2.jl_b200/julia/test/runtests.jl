@@ -8,7 +8,8 @@
 #
 # Run from a checkout of jumerckx/Monodepth2.jl with `include("MDB200.jl")` added to src/Monodepth.jl:
 #   julia --project -e 'include("path/to/monodepth2.jl_b200/julia/test/runtests.jl")'
-using Test, CUDA, Zygote, LinearAlgebra, Random
+using Test, CUDA, Zygote, LinearAlgebra, Random, Statistics
+import Flux, NNlib
 using FixedPointNumbers: N0f8
 using ImageCore: Gray, channelview
 using ImageTransformations: imresize
@@ -143,6 +144,34 @@ end
     img = reinterpret.(Gray{N0f8}, permutedims(frames[:, :, 2, 1], (2, 1)))              # what `load` returns: (rows, cols)
     want = permutedims(Float32.(channelview(imresize(img, (H, W)))), (2, 1))
     @test Array(xk)[:, :, 1, 2, 1] == want                  # pins the restatement of ImageTransformations.imresize
+end
+
+
+@testset "network-side operators" begin
+    # PoseDecoder tail (src/pose_decoder.jl:29-31) and its pullback
+    w, h, N = 5, 3, 4
+    conv = CUDA.randn(Float32, w, h, 6, N)
+    p = M.MDB200.pose_head(conv)
+    ref = 1f-2 .* reshape(mean(Array(conv); dims = (1, 2)), (6, 1, N))
+    @test Array(p.rvec) ≈ ref[1:3, 1, :] rtol = 1e-6
+    @test Array(p.tvec) ≈ ref[4:6, :, :] rtol = 1e-6
+    g = Zygote.gradient(c -> (q = M.MDB200.pose_head(c); sum(q.rvec) + 2 * sum(q.tvec)), conv)[1]
+    @test Array(g)[:, :, 1:3, :] ≈ fill(1f-2 / (w * h), w, h, 3, N) && Array(g)[:, :, 4:6, :] ≈ fill(2f-2 / (w * h), w, h, 3, N)
+    # DepthDecoder heads (src/depth_decoder.jl:46): σ of every level, and σ' from the saved output
+    logits = [CUDA.randn(Float32, 8 * 2^k, 4 * 2^k, 1, N) .* 8 for k in 0:3]
+    disp = M.MDB200.disparity_heads(logits)
+    @test all(Array(disp[k]) ≈ Flux.σ.(Array(logits[k])) for k in 1:4)
+    gl = Zygote.gradient(l -> sum(sum, M.MDB200.disparity_heads(l)), logits)[1]
+    @test all(Array(gl[k]) ≈ (s = Flux.σ.(Array(logits[k])); s .* (1 .- s)) for k in 1:4)
+    # find_static's statistic (src/dtk.jl:58-60), a whole batch at once
+    x = CUDA.rand(Float32, 32, 16, 3, 3, N)
+    s = M.MDB200.static_scores(M.SSIM(), x, 2; source_ids = [1, 3])
+    want = [mean(Array(M.automasking_loss(M.SSIM(), x[:, :, :, :, n:n], x[:, :, :, 2, n:n]; source_ids = [1, 3]))) for n in 1:N]
+    @test s ≈ want rtol = 1e-5
+    # grid_sample as both call sites use it
+    grid = CUDA.rand(Float32, 2, 7, 5, N) .* 2.4f0 .- 1.2f0
+    inp = CUDA.rand(Float32, 32, 16, 3, N)
+    @test Array(M.MDB200.grid_sample_border(inp, grid)) ≈ Array(NNlib.grid_sample(inp, grid; padding_mode = :border)) atol = 1e-6
 end
 
 end
