@@ -73,6 +73,20 @@ struct LossIO
     x_format::Int32          # 0: Float32 frames; 1: UInt8 (N0f8) frames, same layout
 end
 
+# mdb_host_io: every pointer is a HOST pointer (mdb_train_loss_host)
+struct HostIO
+    x::Ptr{Cvoid}
+    flip::Ptr{UInt8}
+    disparity::NTuple{MAX_SCALES,Ptr{Cfloat}}
+    rvec::NTuple{MAX_SOURCES,Ptr{Cfloat}}
+    tvec::NTuple{MAX_SOURCES,Ptr{Cfloat}}
+    auto_loss::Ptr{Cfloat}
+    loss::Ptr{Cfloat}
+    d_disparity::NTuple{MAX_SCALES,Ptr{Cfloat}}
+    d_rvec::NTuple{MAX_SOURCES,Ptr{Cfloat}}
+    d_tvec::NTuple{MAX_SOURCES,Ptr{Cfloat}}
+end
+
 # ---- handle + error convention (status codes -> Julia errors) ------------------------------------
 const HANDLE = Ref{Ptr{Cvoid}}(C_NULL)
 
@@ -196,6 +210,69 @@ function fused_loss(x::Union{CuArray{Float32,5},CuArray{UInt8,5}}, disparities::
             handle(), io, p, ws, nbytes, stream_ptr()))
     end
     loss, dd, [(rvec=dr[i], tvec=dt[i]) for i in 1:S]
+end
+
+# ---- the same step for a batch that is still in HOST memory ---------------------------------------------------------------
+# The reference moves a batch with `transfer(x)` = `gpu ∘ f32` (src/utils.jl:1-3) and then calls train_loss; here the copy-in,
+# the fused loss and the copy-out of the gradients are one C call that pipelines chunks of items over three streams.
+"""
+    HostPlan(W, H, C, N, disp_sizes, cache, parameters; x_u8_strips = false, chunk_items = 0, first_item = -1, kw...)
+
+Owns the device buffers of `fused_loss_host` for one batch shape (`cudaMalloc` once, at construction).  `x_u8_strips`:
+`x` is the dataset's UInt8 triplet strips `(3, 3W, H, N)` instead of the Float32 stack `(W,H,C,3,N)`.  `first_item >= 0`:
+the batch is a shard of `n_global` items starting there (see `comm_init` / `peers_attach` in MDB200_ops.jl).
+"""
+mutable struct HostPlan
+    ptr::Ptr{Cvoid}
+    W::Int; H::Int; C::Int; N::Int; S::Int
+    disp_sizes::Vector{Tuple{Int,Int}}
+    n_pose::Int
+end
+
+function HostPlan(W::Integer, H::Integer, C::Integer, N::Integer, disp_sizes, cache::TrainCache, parameters::Params;
+                  x_u8_strips::Bool = false, chunk_items::Integer = 0, first_item::Integer = -1,
+                  normalize_disparity::Bool = true, smooth_weight_mode::Integer = 0, n_global::Integer = 0,
+                  abs_subgradient::Integer = 0)
+    S, Ls = length(cache.source_ids), length(disp_sizes)
+    shape = LossIO(nullp(), W, H, C, 3, N, cache.target_id, S,
+        pad(Int32.(cache.source_ids), MAX_SOURCES, Int32(0)), pad(Int32.(cache.source_ids .< cache.target_id), MAX_SOURCES, Int32(0)),
+        pad((), MAX_SOURCES, nullp()), pad((), MAX_SOURCES, nullp()), Ls, pad((), MAX_SCALES, nullp()),
+        pad(Int32.(first.(disp_sizes)), MAX_SCALES, Int32(0)), pad(Int32.(last.(disp_sizes)), MAX_SCALES, Int32(0)),
+        pad(Cfloat.(cache.scales), MAX_SCALES, 0f0), nullp(), k9(cache.K), k9(cache.invK), nullp(),
+        pad((), MAX_SCALES, nullp()), pad((), MAX_SOURCES, nullp()), pad((), MAX_SOURCES, nullp()), nullp(), Int32(0))
+    p = LossParams(parameters.min_depth, parameters.max_depth, parameters.disparity_smoothness, 0.85f0,
+        Cfloat(cache.ssim.c1), Cfloat(cache.ssim.c2), Int32(parameters.automasking), Int32(normalize_disparity),
+        Int32(smooth_weight_mode), Int32(1), Int32(n_global), Int32(abs_subgradient))
+    out = Ref{Ptr{Cvoid}}(C_NULL)
+    check(ccall((:mdb_host_plan_create, libmdb200), Int32,
+        (Ptr{Cvoid}, Ref{LossIO}, Ref{LossParams}, Int32, Int32, Int32, Ref{Ptr{Cvoid}}),
+        handle(), shape, p, chunk_items, x_u8_strips ? 1 : 0, first_item, out))
+    info = zeros(Int64, 4)
+    check(ccall((:mdb_host_plan_info, libmdb200), Int32, (Ptr{Cvoid}, Ptr{Int64}), out[], info))
+    plan = HostPlan(out[], W, H, C, N, S, [(Int(a), Int(b)) for (a, b) in disp_sizes], Int(info[4]))
+    finalizer(pl -> (pl.ptr == C_NULL || ccall((:mdb_host_plan_destroy, libmdb200), Int32, (Ptr{Cvoid},), pl.ptr); pl.ptr = C_NULL), plan)
+    plan
+end
+
+"""
+    fused_loss_host(plan, x, disparities, poses, auto_loss; flips = nothing) -> (loss, ∇disparities, ∇poses)   (host Arrays)
+
+`x::Array{Float32,5}` (or the UInt8 strips the plan was built for), `disparities::Vector{Array{Float32,4}}`,
+`poses::Vector` of `(rvec (3,N), tvec (3,1,N))` host arrays.  Pinned arrays (`CUDA.pin`) reach the PCIe rate.
+"""
+function fused_loss_host(plan::HostPlan, x::Array, disparities::Vector{<:Array{Float32}}, poses::Vector, auto_loss;
+                         flips::Union{Nothing,Vector{UInt8}} = nothing)
+    loss = zeros(Float32, 1)
+    dd = [similar(d) for d in disparities]
+    dr = [zeros(Float32, 3, plan.n_pose) for _ in 1:plan.S]; dt = [zeros(Float32, 3, 1, plan.n_pose) for _ in 1:plan.S]
+    hp(a) = Ptr{Cfloat}(pointer(a)); hnull = Ptr{Cfloat}(C_NULL)
+    io = HostIO(Ptr{Cvoid}(pointer(x)), flips === nothing ? Ptr{UInt8}(C_NULL) : pointer(flips),
+        pad(map(hp, disparities), MAX_SCALES, hnull), pad(map(p -> hp(p.rvec), poses), MAX_SOURCES, hnull),
+        pad(map(p -> hp(p.tvec), poses), MAX_SOURCES, hnull), auto_loss === nothing ? hnull : hp(auto_loss), hp(loss),
+        pad(map(hp, dd), MAX_SCALES, hnull), pad(map(hp, dr), MAX_SOURCES, hnull), pad(map(hp, dt), MAX_SOURCES, hnull))
+    GC.@preserve x disparities poses auto_loss flips loss dd dr dt check(ccall((:mdb_train_loss_host, libmdb200), Int32,
+        (Ptr{Cvoid}, Ref{HostIO}, Ptr{Cvoid}), plan.ptr, io, stream_ptr()))
+    loss[1], dd, [(rvec = dr[i], tvec = dt[i]) for i in 1:plan.S]
 end
 
 # The scalar loss is the only output, so the rrule's forward runs forward+backward with unit seed and

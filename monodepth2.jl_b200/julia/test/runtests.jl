@@ -101,6 +101,12 @@ end
     @test l ≈ Array(lf)[1] rtol = 1e-5
     @test Array(gd) ≈ reshape(Array(dd[1]), 1, W, H, N) atol = 1e-4 * maximum(abs, Array(dd[1]))
     @test Array(gp[1].rvec) ≈ Array(dp[1].rvec) atol = 1e-4 * maximum(abs, Array(dp[1].rvec))
+    # the same step from HOST arrays through the one C call that pipelines copy-in, loss and copy-out
+    plan = M.MDB200.HostPlan(W, H, 3, N, [(W, H)], cache, params; normalize_disparity = false, smooth_weight_mode = 1)
+    hposes = [(rvec = Array(p.rvec), tvec = Array(p.tvec)) for p in poses]
+    lh, ddh, dph = M.MDB200.fused_loss_host(plan, Array(x), [reshape(Array(disp), W, H, 1, N)], hposes, nothing)
+    @test lh ≈ Array(lf)[1] rtol = 1e-6
+    @test ddh[1] ≈ Array(dd[1]) rtol = 1e-5 && dph[2].tvec ≈ Array(dp[2].tvec) rtol = 1e-5
 end
 
 @testset "render operators" begin

@@ -163,12 +163,12 @@ def _julia_struct_fields(src, name):
 
 
 def test_julia_struct_mirrors_follow_the_header():
-    """LossIO / LossParams / RenderOpts / AdamParams in julia/MDB200.jl list the fields of mdb_loss_io / mdb_loss_params /
-    mdb_render_opts / mdb_adam_params in the header's order (a `ccall` passes them by reference: order IS the ABI)."""
+    """LossIO / LossParams / RenderOpts / AdamParams / HostIO in julia/MDB200.jl list the fields of mdb_loss_io / mdb_loss_params /
+    mdb_render_opts / mdb_adam_params / mdb_host_io in the header's order (a `ccall` passes them by reference: order IS the ABI)."""
     header = _strip_c_comments(open(os.path.join(ROOT, "include", "mdb200.h")).read())
     jl = open(os.path.join(ROOT, "monodepth2.jl_b200", "julia", "MDB200.jl")).read()
     for c_name, j_name in [("mdb_loss_io", "LossIO"), ("mdb_loss_params", "LossParams"), ("mdb_render_opts", "RenderOpts"),
-                           ("mdb_adam_params", "AdamParams")]:
+                           ("mdb_adam_params", "AdamParams"), ("mdb_host_io", "HostIO")]:
         assert _julia_struct_fields(jl, j_name) == _c_struct_fields(header, c_name), (c_name, j_name)
 
 
