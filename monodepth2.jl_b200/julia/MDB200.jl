@@ -178,7 +178,7 @@ kernels.  `n_global` is the batch size the means divide by (multi-GPU shards pas
 function fused_loss(x::Union{CuArray{Float32,5},CuArray{UInt8,5}}, disparities::Vector{<:CuArray{Float32,4}}, poses::Vector{<:Pose},
                     auto_loss, cache::TrainCache, parameters::Params;
                     normalize_disparity::Bool=true, smooth_weight_mode::Integer=0, n_global::Integer=0,
-                    abs_subgradient::Integer=0)
+                    abs_subgradient::Integer=0, packed_send::Union{Nothing,CuArray{Float32,1}}=nothing, first_item::Integer=0)
     W, H, C, L, N = size(x)
     S, Ls = length(poses), length(disparities)
     loss = CUDA.zeros(Float32, 1)
@@ -204,10 +204,18 @@ function fused_loss(x::Union{CuArray{Float32,5},CuArray{UInt8,5}}, disparities::
     nbytes = ccall((:mdb_train_loss_workspace_bytes, libmdb200), Csize_t, (Ref{LossIO},), io)
     nbytes > 0 || error("mdb200: unsupported shape for the fused loss")
     ws = CuArray{UInt8}(undef, nbytes)
-    GC.@preserve x disparities poses auto_loss loss dd dr dt ws begin
+    ioref = Ref(io)
+    if packed_send !== nothing
+        # a shard of a batch of n_global items: loss and pose gradients are written straight into this rank's slots of the
+        # packed all-reduce buffer (packed_size(n_global, S) floats, the other slots zero); `allreduce_loss_posegrad!` is next
+        n_global > 0 || error("fused_loss: packed_send needs n_global")
+        GC.@preserve packed_send check(ccall((:mdb_packed_bind, libmdb200), Int32, (Ref{LossIO}, CuPtr{Cfloat}, Int32, Int32),
+            ioref, packed_send, n_global, first_item))
+    end
+    GC.@preserve x disparities poses auto_loss loss dd dr dt ws packed_send begin
         check(ccall((:mdb_train_loss_fwdbwd, libmdb200), Int32,
             (Ptr{Cvoid}, Ref{LossIO}, Ref{LossParams}, CuPtr{Cvoid}, Csize_t, Ptr{Cvoid}),
-            handle(), io, p, ws, nbytes, stream_ptr()))
+            handle(), ioref, p, ws, nbytes, stream_ptr()))
     end
     loss, dd, [(rvec=dr[i], tvec=dt[i]) for i in 1:S]
 end

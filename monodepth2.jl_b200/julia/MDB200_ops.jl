@@ -409,3 +409,12 @@ function destroy()
     HANDLE[] = C_NULL
     nothing
 end
+
+"1 if a one-shot peer reduce gave up waiting for a peer (synchronises the device)"
+comm_status() = (f = Ref{Int32}(0); check(ccall((:mdb_comm_status, libmdb200), Int32, (Ptr{Cvoid}, Ref{Int32}), handle(), f)); f[])
+comm_destroy() = check(ccall((:mdb_comm_destroy, libmdb200), Int32, (Ptr{Cvoid},), handle()))
+version() = ccall((:mdb_version, libmdb200), Int32, ())
+"kernels launched through the library's handle since it was created"
+launch_count() = ccall((:mdb_launch_count, libmdb200), Int64, (Ptr{Cvoid},), handle())
+"test hooks of include/mdb200.h (`strip_segs`, `strip_taper`, `render_precise`, ...); 0 restores the library's choice"
+debug_option(name::AbstractString, value::Integer) = check(ccall((:mdb_debug_option, libmdb200), Int32, (Cstring, Int64), name, value))
