@@ -482,7 +482,8 @@ inline StripGeom strip_geom(const mdb_loss_io* io, int num_sms) {
   if (g_dbg_strip_taper >= 2) k_taper = g_dbg_strip_taper;
   else if (g_dbg_strip_taper == 0 && g_dbg_strip_segs == 0) {
     const double wb = (double)base / resident;
-    k_taper = wb >= 2.0 ? 3 : (wb >= 1.2 ? 4 : ((wb >= 0.55 && wb < 0.9) ? 6 : 0));
+    // 1.5 and not 2: 20 .. 28 items at 1024x320 and config 3 (32 x 640x192, wb = 1.66: 0.798 against 0.809 ms) prefer three segments
+    k_taper = wb >= 1.5 ? 3 : (wb >= 1.2 ? 4 : ((wb >= 0.55 && wb < 0.9) ? 6 : 0));
   }
 #if STRIP_TAPER
   if (k_taper >= 2 && k_taper <= STRIP_MAX_TAPER && io->H >= 16 * k_taper) {

@@ -222,7 +222,8 @@ def test_strip_geometry_choices_need_no_gpu():
     assert geo(1024, 320, 8, 4)[:2] == [37, 6]
     assert geo(1024, 320, 12, 4) == [37, 1, 320, 12 * 4 * 37]
     assert geo(416, 128, 1, 1) == [15, 32, 4, 480]
-    assert geo(640, 192, 32, 4)[:2] == [23, 4]          # config 3: 1.66 resident waves per segment index
+    assert geo(640, 192, 32, 4)[:2] == [23, 3]          # config 3: 1.66 resident waves per segment index
+    assert geo(1024, 320, 16, 4)[:2] == [37, 4]         # 1.33 waves: four segments
 
 
 def test_tapered_segment_boundaries_are_well_formed():
