@@ -106,7 +106,8 @@ end
     hposes = [(rvec = Array(p.rvec), tvec = Array(p.tvec)) for p in poses]
     lh, ddh, dph = M.MDB200.fused_loss_host(plan, Array(x), [reshape(Array(disp), W, H, 1, N)], hposes, nothing)
     @test lh ≈ Array(lf)[1] rtol = 1e-6
-    @test ddh[1] ≈ Array(dd[1]) rtol = 1e-5 && dph[2].tvec ≈ Array(dp[2].tvec) rtol = 1e-5
+    @test ddh[1] ≈ Array(dd[1]) rtol = 1e-5
+    @test dph[2].tvec ≈ Array(dp[2].tvec) rtol = 1e-5
 end
 
 @testset "render operators" begin
